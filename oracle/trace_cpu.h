@@ -1,0 +1,250 @@
+// trace_cpu.h -- TEST INFRASTRUCTURE ONLY (oracle).  Never included by the product.
+//
+// CPU stand-in for the parts of the reference that live in un-vendored third-party code
+// ("parity unpinned"):
+//   * owl-project/owl @4416b979 -> NVIDIA OptiX 7 optixAccelBuild / optixTrace, i.e. the BVH
+//     build and the ray/triangle intersection behind owl::traceRay
+//     (call sites /root/reference/cuda_src/deviceCode.cu:76, cuda_include/ratio/ratio.cuh:50,
+//      cuda_include/path/path.cuh:219; build include/viewer.hpp:506-507,516-517);
+//   * the CUDA texture unit behind tex2D<float4>
+//     (cuda_include/ltc/ltc_utils.cuh:14-16, cuda_include/hit_miss.cuh:42;
+//      creation include/viewer.hpp:322-327 LINEAR/CLAMP RGBA32F, :441-447 NEAREST/CLAMP RGBA8).
+// Both algorithms are not public, so this file DEFINES the stand-ins the whole repo is
+// checked against:
+//   closest hit = Moeller-Trumbore in fp32 with the exact operation order of tri_test() below
+//   (explicit fmaf, no contraction), no culling, t in (tmin, tmax), closest t wins, ties on t
+//   go to the LOWEST global primitive id (global id = triangles of earlier meshes + local
+//   primitive index, meshes in scene order: surfaces first, lights last -- src/scene.cpp:5-13).
+//   The result is independent of traversal order, so brute force and any BVH agree bit for bit.
+// Compile with -ffp-contract=off -mfma so fmaf is one correctly rounded instruction.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+
+namespace ocpu {
+
+struct Hit {
+    float t, u, v;
+    int prim;  // global primitive id, -1 = miss
+};
+
+// d x e style helper: a*b - c*d with one rounding on the product a*b (fma) -- the GPU kernel
+// spells the same thing with __fmaf_rn / __fmul_rn.
+static inline float fms(float a, float b, float c, float d) { return __builtin_fmaf(a, b, -(c * d)); }
+static inline float dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return __builtin_fmaf(az, bz, __builtin_fmaf(ay, by, ax * bx));
+}
+
+// One ray/triangle test.  Returns true and (t,u,v) when the ray hits inside (tmin,tmax).
+static inline bool tri_test(const float* v0, const float* v1, const float* v2, const float o[3],
+                            const float d[3], float tmin, float tmax, float* t, float* u, float* v) {
+    const float e1x = v1[0] - v0[0], e1y = v1[1] - v0[1], e1z = v1[2] - v0[2];
+    const float e2x = v2[0] - v0[0], e2y = v2[1] - v0[1], e2z = v2[2] - v0[2];
+    const float px = fms(d[1], e2z, d[2], e2y);
+    const float py = fms(d[2], e2x, d[0], e2z);
+    const float pz = fms(d[0], e2y, d[1], e2x);
+    const float det = dot3(e1x, e1y, e1z, px, py, pz);
+    if (det == 0.f) return false;
+    const float inv = 1.f / det;
+    const float sx = o[0] - v0[0], sy = o[1] - v0[1], sz = o[2] - v0[2];
+    const float uu = dot3(sx, sy, sz, px, py, pz) * inv;
+    if (!(uu >= 0.f && uu <= 1.f)) return false;
+    const float qx = fms(sy, e1z, sz, e1y);
+    const float qy = fms(sz, e1x, sx, e1z);
+    const float qz = fms(sx, e1y, sy, e1x);
+    const float vv = dot3(d[0], d[1], d[2], qx, qy, qz) * inv;
+    if (!(vv >= 0.f && uu + vv <= 1.f)) return false;
+    const float tt = dot3(e2x, e2y, e2z, qx, qy, qz) * inv;
+    if (!(tt > tmin && tt < tmax)) return false;
+    *t = tt;
+    *u = uu;
+    *v = vv;
+    return true;
+}
+
+struct Node {  // plain BVH2, leaves hold [first, first+count) of primIdx
+    float lo[3], hi[3];
+    int left, right;  // children (inner) ; left = -1 for leaves
+    int first, count;
+};
+
+struct TriSoup {
+    std::vector<float> v;  // 9 floats per global primitive: v0 v1 v2
+    std::vector<int> primIdx;
+    std::vector<Node> nodes;
+
+    size_t size() const { return v.size() / 9; }
+
+    void clear() {
+        v.clear();
+        primIdx.clear();
+        nodes.clear();
+    }
+
+    void bounds(int first, int count, float lo[3], float hi[3], bool centroid) const {
+        for (int a = 0; a < 3; a++) { lo[a] = INFINITY; hi[a] = -INFINITY; }
+        for (int i = first; i < first + count; i++) {
+            const float* t = &v[9 * (size_t)primIdx[i]];
+            if (centroid) {
+                for (int a = 0; a < 3; a++) {
+                    float c = (t[a] + t[3 + a] + t[6 + a]) * (1.f / 3.f);
+                    lo[a] = std::min(lo[a], c);
+                    hi[a] = std::max(hi[a], c);
+                }
+            } else {
+                for (int k = 0; k < 3; k++)
+                    for (int a = 0; a < 3; a++) {
+                        lo[a] = std::min(lo[a], t[3 * k + a]);
+                        hi[a] = std::max(hi[a], t[3 * k + a]);
+                    }
+            }
+        }
+    }
+
+    int build_rec(int first, int count) {
+        int me = (int)nodes.size();
+        nodes.push_back(Node());
+        {
+            Node& n = nodes[me];
+            bounds(first, count, n.lo, n.hi, false);
+            n.first = first;
+            n.count = count;
+            n.left = n.right = -1;
+        }
+        if (count <= 4) return me;
+        float clo[3], chi[3];
+        bounds(first, count, clo, chi, true);
+        int axis = 0;
+        for (int a = 1; a < 3; a++)
+            if (chi[a] - clo[a] > chi[axis] - clo[axis]) axis = a;
+        int mid = first + count / 2;
+        const std::vector<float>& vv = v;
+        std::nth_element(primIdx.begin() + first, primIdx.begin() + mid, primIdx.begin() + first + count,
+                         [&](int a, int b) {
+                             const float* ta = &vv[9 * (size_t)a];
+                             const float* tb = &vv[9 * (size_t)b];
+                             float ca = ta[axis] + ta[3 + axis] + ta[6 + axis];
+                             float cb = tb[axis] + tb[3 + axis] + tb[6 + axis];
+                             return ca < cb || (ca == cb && a < b);
+                         });
+        int l = build_rec(first, mid - first);
+        int r = build_rec(mid, first + count - mid);
+        nodes[me].left = l;
+        nodes[me].right = r;
+        return me;
+    }
+
+    void build() {
+        size_t n = size();
+        primIdx.resize(n);
+        for (size_t i = 0; i < n; i++) primIdx[i] = (int)i;
+        nodes.clear();
+        nodes.reserve(n ? n : 1);
+        if (n) build_rec(0, (int)n);
+    }
+
+    static inline void consider(Hit& best, float t, float u, float v, int prim) {
+        if (t < best.t || (t == best.t && prim < best.prim)) {
+            best.t = t;
+            best.u = u;
+            best.v = v;
+            best.prim = prim;
+        }
+    }
+
+    Hit brute(const float o[3], const float d[3], float tmin, float tmax) const {
+        Hit best = {INFINITY, 0.f, 0.f, -1};
+        size_t n = size();
+        for (size_t i = 0; i < n; i++) {
+            float t, u, w;
+            if (tri_test(&v[9 * i], &v[9 * i + 3], &v[9 * i + 6], o, d, tmin, tmax, &t, &u, &w))
+                consider(best, t, u, w, (int)i);
+        }
+        return best;
+    }
+
+    // Conservative slab test: the far distance is widened by a few ulp so a box is never
+    // rejected for a triangle tri_test() would accept at t <= best.t.
+    static inline bool box_test(const Node& n, const float o[3], const float inv[3], float tbest, float tmin) {
+        float t0 = tmin, t1 = tbest;
+        for (int a = 0; a < 3; a++) {
+            float ta = (n.lo[a] - o[a]) * inv[a];
+            float tb = (n.hi[a] - o[a]) * inv[a];
+            float tn = fminf(ta, tb), tf = fmaxf(ta, tb);
+            tn = tn - fabsf(tn) * 4e-7f;
+            tf = tf + fabsf(tf) * 4e-7f;
+            t0 = fmaxf(t0, tn);
+            t1 = fminf(t1, tf);
+        }
+        return t0 <= t1;
+    }
+
+    Hit closest(const float o[3], const float d[3], float tmin, float tmax) const {
+        Hit best = {INFINITY, 0.f, 0.f, -1};
+        if (nodes.empty()) return best;
+        float inv[3] = {1.f / d[0], 1.f / d[1], 1.f / d[2]};
+        int stack[128];
+        int sp = 0;
+        stack[sp++] = 0;
+        while (sp) {
+            const Node& n = nodes[stack[--sp]];
+            float lim = best.prim < 0 ? tmax : best.t;
+            if (!box_test(n, o, inv, lim, tmin)) continue;
+            if (n.left < 0) {
+                for (int i = n.first; i < n.first + n.count; i++) {
+                    int p = primIdx[i];
+                    float t, u, w;
+                    if (tri_test(&v[9 * (size_t)p], &v[9 * (size_t)p + 3], &v[9 * (size_t)p + 6], o, d, tmin,
+                                 tmax, &t, &u, &w))
+                        consider(best, t, u, w, p);
+                }
+            } else {
+                stack[sp++] = n.left;
+                stack[sp++] = n.right;
+            }
+        }
+        return best;
+    }
+};
+
+// ---- texture unit stand-ins ------------------------------------------------------------------
+// CUDA linear filtering, normalised coordinates, clamp addressing (CUDA C Programming Guide,
+// "Texture Fetching": xB = N*x - 0.5, i = floor(xB), a = frac(xB), a stored in 9-bit fixed
+// point with 8 fractional bits).  quantise=1 applies the 1/256 weight quantisation.
+static inline void tex2d_linear_clamp_f4(const float* texels, int w, int h, float x, float y, int quantise,
+                                         float out[4]) {
+    float xb = x * (float)w - 0.5f, yb = y * (float)h - 0.5f;
+    float fx = floorf(xb), fy = floorf(yb);
+    float a = xb - fx, b = yb - fy;
+    if (quantise) {
+        a = floorf(a * 256.f + 0.5f) * (1.f / 256.f);
+        b = floorf(b * 256.f + 0.5f) * (1.f / 256.f);
+    }
+    int i0 = (int)fx, j0 = (int)fy;
+    int i1 = i0 + 1, j1 = j0 + 1;
+    i0 = std::min(std::max(i0, 0), w - 1);
+    i1 = std::min(std::max(i1, 0), w - 1);
+    j0 = std::min(std::max(j0, 0), h - 1);
+    j1 = std::min(std::max(j1, 0), h - 1);
+    const float* t00 = texels + 4 * ((size_t)j0 * w + i0);
+    const float* t10 = texels + 4 * ((size_t)j0 * w + i1);
+    const float* t01 = texels + 4 * ((size_t)j1 * w + i0);
+    const float* t11 = texels + 4 * ((size_t)j1 * w + i1);
+    float w00 = (1.f - a) * (1.f - b), w10 = a * (1.f - b), w01 = (1.f - a) * b, w11 = a * b;
+    for (int c = 0; c < 4; c++) out[c] = w00 * t00[c] + w10 * t10[c] + w01 * t01[c] + w11 * t11[c];
+}
+
+// Point sampling of an RGBA8 texture read as normalised float (x/255), clamp addressing.
+static inline void tex2d_nearest_clamp_rgba8(const uint8_t* texels, int w, int h, float x, float y,
+                                             float out[4]) {
+    int i = (int)floorf(x * (float)w), j = (int)floorf(y * (float)h);
+    i = std::min(std::max(i, 0), w - 1);
+    j = std::min(std::max(j, 0), h - 1);
+    const uint8_t* t = texels + 4 * ((size_t)j * w + i);
+    for (int c = 0; c < 4; c++) out[c] = (float)t[c] * (1.f / 255.f);
+}
+
+}  // namespace ocpu
