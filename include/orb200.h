@@ -1,0 +1,219 @@
+/* orb200.h -- C-ABI of liborb200.so: the B200 (sm_100a) per-pixel hot path of the renderer.
+ *
+ * This library replaces what the reference reaches through the OWL host API in
+ * include/viewer.hpp (context/module :177-178, buffers :181-225, launch params :271-364,
+ * geometry + GAS/IAS build :375-517, miss/raygen programs :522-543, owlLaunch2D :565,
+ * owlBufferGetPointer :701) together with the three OptiX device programs it launches
+ * (cuda_src/deviceCode.cu:59-175 rayGen; cuda_include/hit_miss.cuh:14-63 triangleMeshCH, miss).
+ * Plain pointers and sizes only; no C++ or torch types.  All `const T*` inputs are HOST
+ * pointers borrowed for the duration of the call unless a name says `_dev`.  Every function
+ * returns 0 on success or an OrbStatus code; orb_last_error() gives the text for the calling
+ * thread.  A context is single-threaded (externally synchronised) and owns one CUDA stream.
+ * There is no CPU fallback: without a CUDA device orb_create() fails.
+ */
+#ifndef ORB200_H
+#define ORB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORB_API_VERSION 1
+
+typedef enum OrbStatus {
+    ORB_OK = 0,
+    ORB_ERR_INVALID = 1,   /* bad argument / call order */
+    ORB_ERR_CUDA = 2,      /* a CUDA call failed; text in orb_last_error() */
+    ORB_ERR_NO_DEVICE = 3, /* no usable CUDA device */
+    ORB_ERR_NOMEM = 4
+} OrbStatus;
+
+/* RendererType, cuda_include/common.cuh:17-29 (same values). */
+typedef enum OrbRendererType {
+    ORB_DIFFUSE = 0,
+    ORB_ALPHA = 1,
+    ORB_NORMALS = 2,
+    ORB_SHADE_NORMALS = 3,
+    ORB_POSITION = 4,
+    ORB_MASK = 5,
+    ORB_MATERIAL_ID = 6,
+    ORB_LTC_BASELINE = 7,
+    ORB_RATIO = 8,
+    ORB_PATH = 9
+} OrbRendererType;
+
+/* Frame buffers.  0..12 are the 13 float4 screen buffers of LaunchParams
+ * (cuda_include/common.cuh:84-100) in declaration order, row 0 = bottom image row, w = 1 as
+ * rayGen writes them (cuda_src/deviceCode.cu:158-168).  The rest are this library's own. */
+typedef enum OrbBufferId {
+    ORB_BUF_POSITION = 0,
+    ORB_BUF_NORMAL = 1,
+    ORB_BUF_UV = 2,
+    ORB_BUF_ALBEDO = 3,
+    ORB_BUF_ALPHA = 4,
+    ORB_BUF_MATERIAL_ID = 5,
+    ORB_BUF_BOUNCE0 = 6,
+    ORB_BUF_BOUNCE1 = 7,
+    ORB_BUF_BOUNCE2 = 8,
+    ORB_BUF_LTC = 9,
+    ORB_BUF_STO_DIRECT = 10,
+    ORB_BUF_STO_NO_VIS = 11,
+    ORB_BUF_ACCUM = 12,
+    ORB_BUF_RGBA8 = 13,        /* uint32 per pixel: RayGenData.frameBuffer, owl::make_rgba        */
+    ORB_BUF_HIT = 14,          /* int32 prim, float u, float v, float t per pixel (primary hit)    */
+    ORB_BUF_STO_DIRECT_DN = 15, /* float4: denoised sto_direct  (stodirectDenoise.exr)             */
+    ORB_BUF_STO_NO_VIS_DN = 16, /* float4: denoised sto_no_vis  (stoNoVisDenoise.exr)              */
+    ORB_BUF_RATIO_FINAL = 17,  /* float4: ltc * (stoDirect / stoNoVis) (final_ratio_estimator.exr) */
+    ORB_BUF_COUNT = 18
+} OrbBufferId;
+
+/* TriLight, cuda_include/common.cuh:64-72 -- 76 bytes, same field order. */
+typedef struct OrbTriLight {
+    float v1[3], v2[3], v3[3];
+    float cg[3];
+    float normal[3];
+    float emit[3];
+    float area;
+} OrbTriLight;
+
+/* One triangle mesh = one OWL geometry + GAS of the reference (TriangleMeshData,
+ * cuda_include/common.cuh:130-151; upload include/viewer.hpp:421-501). */
+typedef struct OrbMeshDesc {
+    const float* vertex;   /* n_vertices * 3 */
+    const float* normal;   /* n_vertices * 3 */
+    const float* texcoord; /* n_vertices * 2 */
+    int32_t n_vertices;
+    const int32_t* index; /* n_triangles * 3, indices into this mesh's vertices */
+    int32_t n_triangles;
+    float diffuse[3];
+    float alpha; /* clamped to [0.01, 1] at hit time, hit_miss.cuh:45-46 */
+    float emit[3];
+    int32_t is_light;
+    uint32_t material_id;
+    const uint8_t* diffuse_tex_rgba8; /* NULL = no texture; nearest / clamp, viewer.hpp:441-447 */
+    int32_t tex_w, tex_h;
+} OrbMeshDesc;
+
+typedef struct OrbBvhOptions {
+    int32_t max_leaf_tris; /* 0 = default (4) */
+    int32_t reserved[3];
+} OrbBvhOptions;
+
+typedef struct OrbRenderConfig {
+    int32_t renderer_type; /* OrbRendererType */
+    int32_t accum_id;      /* LaunchParams.accumId */
+    int32_t mode;          /* 0 literal (committed source), 1 intended (patches P1-P3) */
+    int32_t shadow_spp;    /* RATIO: shadow samples per pixel; literal fixes 4 (deviceCode.cu:128) */
+    int32_t max_depth;     /* PATH: bounces; literal fixes 1 (deviceCode.cu:151) */
+    int32_t y0, y1;        /* rows [y0, y1) rendered by this context (tile partition); 0,0 = all */
+    int32_t reserved[1];
+} OrbRenderConfig;
+
+typedef struct OrbDenoiseConfig {
+    int32_t iterations; /* a-trous passes, step 1,2,4,...; default 5 */
+    float sigma_normal; /* edge stop on normal (power of the dot product), default 32 */
+    float sigma_position; /* edge stop on camera-distance difference, per unit of tap spacing; default 0.25 */
+    float sigma_colour; /* edge stop on colour difference; <= 0 disables (default) */
+} OrbDenoiseConfig;
+
+typedef struct OrbCounters {
+    uint64_t rays_primary;
+    uint64_t rays_shadow;
+    uint64_t rays_bounce;
+    uint64_t kernel_launches; /* kernels launched by this context since creation */
+    uint64_t nan_pixels;      /* pixels of the last frame whose colour had a NaN channel */
+    uint64_t bvh_nodes;
+    uint64_t bvh_triangles;
+    uint64_t bvh_height;     /* inner-node levels of the hierarchy (sizes the traversal stack) */
+    uint64_t active_pixels;  /* last frame: non-light hit pixels (length of the active-pixel queue) */
+    uint64_t nodes_visited;  /* last orb_trace_rays_host call (instrumented traversal) */
+    uint64_t tris_tested;
+} OrbCounters;
+
+typedef struct OrbContext OrbContext;
+
+/* ---- context ---- replaces owlContextCreate/ModuleCreate, viewer.hpp:177-178 */
+int orb_api_version(void);
+const char* orb_last_error(void);
+int orb_create(int device, OrbContext** out);
+void orb_destroy(OrbContext* ctx);
+void* orb_stream(OrbContext* ctx); /* cudaStream_t the context launches on */
+/* Launch on a caller-owned cudaStream_t instead (e.g. the stream a host framework times with). */
+int orb_set_stream(OrbContext* ctx, void* cuda_stream);
+int orb_sync(OrbContext* ctx);
+
+/* ---- scene ---- replaces owlGeom*, owlTriangles*, owlGroupBuildAccel, viewer.hpp:375-517 */
+int orb_scene_clear(OrbContext* ctx);
+int orb_scene_add_mesh(OrbContext* ctx, const OrbMeshDesc* mesh); /* returns mesh index via *mesh order */
+int orb_scene_set_lights(OrbContext* ctx, const OrbTriLight* lights, int32_t n); /* viewer.hpp:336-338 */
+/* Three RGBA32F tables of w*h texels, rows = alpha, columns = theta (viewer.hpp:321-331).
+ * quantise_weights = 1 filters with 8-bit fractional weights like the CUDA texture unit. */
+int orb_scene_set_ltc_lut(OrbContext* ctx, const float* m1, const float* m2, const float* m3, int32_t w,
+                          int32_t h, int32_t quantise_weights);
+int orb_scene_commit(OrbContext* ctx, const OrbBvhOptions* opt); /* builds the BVH on the GPU */
+
+/* ---- camera / frame ---- replaces owlParamsSet3f camera.*, viewer.hpp:647-650, and resize :571-612 */
+int orb_set_camera(OrbContext* ctx, const float pos[3], const float dir_00[3], const float dir_du[3],
+                   const float dir_dv[3]);
+int orb_resize(OrbContext* ctx, int32_t width, int32_t height);
+
+/* ---- launch ---- replaces owlLaunch2D(rayGen, W, H, launchParams), viewer.hpp:553-568.
+ * Blocking, like owlLaunch2D.  orb_render_async() enqueues on orb_stream() and returns. */
+int orb_render(OrbContext* ctx, const OrbRenderConfig* cfg);
+int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
+
+/* ---- stand-alone passes over RESIDENT frame buffers (rows [y0,y1), 0,0 = all) ---- */
+/* ltcDirectLighingBaseline over the G-buffer (position, normal, albedo, alpha) -> ORB_BUF_LTC;
+ * pixels whose normal is (0,0,0) give 0. */
+int orb_ltc_gbuffer_pass(OrbContext* ctx, int32_t y0, int32_t y1);
+/* a-trous edge-avoiding filter: STO_DIRECT -> STO_DIRECT_DN, STO_NO_VIS -> STO_NO_VIS_DN */
+int orb_denoise(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1);
+/* ltc_ratio_estimator.py:8: RATIO_FINAL = LTC * (STO_DIRECT[_DN] / STO_NO_VIS[_DN]) */
+int orb_ratio_combine(OrbContext* ctx, int32_t use_denoised, int32_t y0, int32_t y1);
+
+/* ---- buffers ---- replaces owlBufferGetPointer + cudaMemcpy, viewer.hpp:695-713 */
+size_t orb_buffer_bytes(OrbContext* ctx, int32_t buffer_id);
+void* orb_buffer_device_ptr(OrbContext* ctx, int32_t buffer_id);
+int orb_buffer_download(OrbContext* ctx, int32_t buffer_id, void* host_dst, size_t bytes);
+int orb_buffer_download_rows(OrbContext* ctx, int32_t buffer_id, void* host_dst, int32_t y0, int32_t y1);
+int orb_buffer_upload(OrbContext* ctx, int32_t buffer_id, const void* host_src, size_t bytes);
+int orb_get_counters(OrbContext* ctx, OrbCounters* out);
+
+/* ---- host-buffer entry point of BASELINE config 1 (ltc_ratio_estimator.py:4-9):
+ * out = ltc * (sto_direct / sto_no_vis) element-wise on n floats; copies in, runs the kernel,
+ * copies out. */
+int orb_ratio_estimator_host(OrbContext* ctx, const float* ltc, const float* sto_direct, const float* sto_no_vis,
+                             float* out, size_t n);
+
+/* ---- ray casting over the committed scene (owl::traceRay semantics, tmin=0, tmax=1e30):
+ * n rays, origin/direction as n*3 floats; outputs prim (global id, -1 miss), t, u, v.
+ * brute_force != 0 tests every triangle instead of walking the BVH (hit-id parity checks). */
+int orb_trace_rays_host(OrbContext* ctx, const float* origin, const float* direction, size_t n, int32_t brute_force,
+                        int32_t* prim, float* t, float* u, float* v);
+
+/* ---- known-answer entry points: run ONE device function in a one-thread kernel ---- */
+int orb_unit_rng(OrbContext* ctx, int frame_id, uint32_t px, uint32_t py, uint32_t W, int n, uint32_t* state0,
+                 uint32_t* raw, float* flt);
+int orb_unit_clip(OrbContext* ctx, const float* abc9, int quad, int* n_out, float* form_factor);
+int orb_unit_integrate_edge(OrbContext* ctx, const float* a, const float* b, float* out);
+int orb_unit_fetch_ltc(OrbContext* ctx, float alpha, float theta, float* m9_amp);
+int orb_unit_mat_inverse(OrbContext* ctx, const float* m9, float* out9);
+int orb_unit_onb(OrbContext* ctx, const float* n, float* rows9);
+int orb_unit_sample_direction(OrbContext* ctx, const float* wo, float u1, float u2, const float* base, float alpha,
+                              float* wi_pdf4);
+int orb_unit_evaluate(OrbContext* ctx, const float* wi, const float* wo, const float* base, float alpha,
+                      float* out3);
+int orb_unit_pdf(OrbContext* ctx, const float* wi, const float* wo, const float* base, float alpha, float* out);
+int orb_unit_make_rgba(OrbContext* ctx, const float* c3, uint32_t* out);
+int orb_unit_sample_tri(OrbContext* ctx, const float* v9, float u1, float u2, float* out3);
+int orb_unit_pdf_a2w(OrbContext* ctx, float pdf, float dist2, float cos_theta, float* out);
+/* ltcDirectLighingBaseline for one shading point against the context's lights and LUT */
+int orb_unit_ltc_pixel(OrbContext* ctx, const float* cam3, const float* p3, const float* n3, const float* diffuse3,
+                       float alpha, float* out3);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORB200_H */

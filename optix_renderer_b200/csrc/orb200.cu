@@ -1,0 +1,1273 @@
+// orb200.cu -- liborb200.so: frame kernels (sm_100a) and the C-ABI declared in include/orb200.h.
+//
+// One frame of the reference's raygen megakernel (cuda_src/deviceCode.cu:59-175) becomes a
+// short wavefront of kernels over buffers that stay resident in HBM:
+//
+//   k_primary        camera ray -> BVH closest hit -> closest-hit shading -> 16-B hit record,
+//                    six float4 G-buffers, per-pixel flags; non-light hit pixels are appended to
+//                    the ACTIVE-PIXEL QUEUE by warp ballot (one atomic per warp)
+//   k_ltc            queue -> LTC area-light sum (lights + LUT staged in shared memory)
+//   k_ratio_shadow   queue -> n closest-hit shadow rays per pixel -> sto_direct / sto_no_vis
+//   k_path_bounce    queue / path-state SoA -> one bounce, survivors re-compacted by ballot
+//   k_accumulate     colour + running sum -> accum, RGBA8, NaN count
+//   k_denoise_*      edge-avoiding a-trous on the packed (direct, no_vis) image
+//   k_ratio_combine  ltc * (direct / no_vis)
+//
+// Queue kernels are persistent (grid = SMs x resident CTAs, grid-stride over a DEVICE-side
+// count), so a frame needs no host synchronisation.  No kernel is a dense contraction: there
+// is no tensor-core work (BASELINE.json north_star).  There is no CPU fallback.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/orb200.h"
+#include "bvh_build.cuh"
+#include "pixel.cuh"
+
+using namespace orb;
+
+// ---------------------------------------------------------------------------------------------
+// error handling
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(x)                                                                                      \
+    do {                                                                                           \
+        cudaError_t e_ = (x);                                                                      \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(ORB_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_));            \
+    } while (0)
+#define NEED(c, msg) \
+    do {             \
+        if (!(c)) return fail(ORB_ERR_INVALID, msg); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// device-side frame description
+// ---------------------------------------------------------------------------------------------
+#define FLAG_HIT 1u
+#define FLAG_LIGHT 2u
+
+struct DevCounters {
+    unsigned queue_n;       // active (non-light hit) pixels of this frame
+    unsigned path_n[2];     // live paths, ping-pong
+    unsigned nan_pixels;
+    unsigned long long rays_shadow, rays_bounce;
+    unsigned long long nodes_visited, tris_tested;  // filled by the instrumented trace only
+};
+
+struct FrameView {
+    int W, H, y0, y1;
+    float4 *position, *normal, *uv, *albedo, *alpha, *material_id;
+    float4 *ltc, *sto_direct, *sto_no_vis, *accum, *hit, *colour;
+    uint32_t* rgba8;
+    uint32_t* flags;
+    uint32_t* queue;
+    DevCounters* cnt;
+};
+
+#define TRACE_BLOCK 128
+
+// shared-memory traversal stack, one column per thread: entry e of thread t at [e * TRACE_BLOCK + t]
+// (any mix of stack depths inside a warp is bank-conflict free)
+extern __shared__ int s_dyn[];
+
+struct SmemTracer {
+    const SceneView& s;
+    int* stk;
+    float* stk_t;
+    unsigned* rays;
+    __device__ Hit operator()(float3 o, float3 d) const {
+        ++*rays;
+        return trace_closest(s, o, d, stk, stk_t, TRACE_BLOCK);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// k_primary
+// ---------------------------------------------------------------------------------------------
+// A warp covers an 8x4 pixel tile (coherent rays, 128-byte row segments on the float4 stores);
+// a 128-thread block covers 16x8.
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int height) {
+    int* stk = s_dyn + threadIdx.x;
+    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int px = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = f.y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < f.W && py < f.y1;
+    bool active = false;
+    size_t ofs = 0;
+    if (inside) {
+        ofs = (size_t)py * f.W + px;
+        float3 o, d;
+        primary_ray(cam, frame_id, px, py, f.W, f.H, o, d);
+        const Hit h = trace_closest(s, o, d, stk, stk_t, TRACE_BLOCK);
+        const Surface si = shade_hit(s, h.prim, h.u, h.v);
+        st_stream(f.hit + ofs, make_float4(__int_as_float(h.prim), h.u, h.v, h.t));
+        st_stream(f.position + ofs, make_float4(si.p.x, si.p.y, si.p.z, 1.f));
+        st_stream(f.normal + ofs, make_float4(si.n.x, si.n.y, si.n.z, 1.f));
+        st_stream(f.albedo + ofs, make_float4(si.diffuse.x, si.diffuse.y, si.diffuse.z, 1.f));
+        st_stream(f.alpha + ofs, make_float4(si.alpha, 0.f, 0.f, 1.f));
+        st_stream(f.uv + ofs, make_float4(si.u, si.v, si.diffuse.z, 1.f));
+        st_stream(f.material_id + ofs, make_float4((float)si.material_id, 0.f, 0.f, 1.f));
+        f.flags[ofs] = (si.hit ? FLAG_HIT : 0u) | (si.is_light ? FLAG_LIGHT : 0u);
+        // everything rayGen's mode switch decides without further rays (deviceCode.cu:91-124,146-149)
+        float3 c = v3(0.f);
+        bool staged = false;  // colour comes from a later stage
+        if (!si.hit) c = si.n;
+        else if (renderer == ORB_MASK) c = v3(1.f);
+        else if (renderer == ORB_POSITION) c = si.p;
+        else if (renderer == ORB_DIFFUSE) c = si.diffuse;
+        else if (renderer == ORB_ALPHA) c = v3(si.alpha);
+        else if (renderer == ORB_NORMALS) c = si.n;
+        else if (renderer == ORB_SHADE_NORMALS) c = v3(0.f);  // n_shad is never written
+        else if (renderer == ORB_MATERIAL_ID) c = v3((float)si.material_id);
+        else if (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO || renderer == ORB_PATH) {
+            if (si.is_light) {
+                c = si.emit;
+                if (renderer == ORB_RATIO) {
+                    const float4 e = make_float4(c.x, c.y, c.z, 1.f);
+                    st_stream(f.ltc + ofs, e);
+                    st_stream(f.sto_direct + ofs, e);
+                    st_stream(f.sto_no_vis + ofs, e);
+                }
+            } else {
+                staged = true;
+            }
+        } else {
+            c = v3(1.f, 0.f, 0.f);
+        }
+        if (!staged) st_stream(f.colour + ofs, make_float4(c.x, c.y, c.z, 1.f));
+        active = staged;
+    }
+    // warp-ballot compaction into the active-pixel queue
+    const unsigned m = __ballot_sync(0xffffffffu, active);
+    if (m) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&f.cnt->queue_n, (unsigned)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (active) f.queue[base + __popc(m & ((1u << lane) - 1u))] = (uint32_t)ofs;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_ltc  (FROM_QUEUE: in-frame over the active queue; else stand-alone over a saved G-buffer)
+// ---------------------------------------------------------------------------------------------
+#define LTC_BLOCK 128
+#define LTC_SMEM_LIGHTS 128        // 9.5 KB of lights in shared memory; more are read from global
+#define LTC_SMEM_LUT_TEXELS 3 * 64  // the reference's 8x8 x 3 tables (3 KB); larger LUTs stay global
+
+template <bool FROM_QUEUE>
+__global__ void __launch_bounds__(LTC_BLOCK)
+k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4* __restrict__ out2) {
+    __shared__ TriLight sh_lights[LTC_SMEM_LIGHTS];
+    __shared__ float4 sh_lut[LTC_SMEM_LUT_TEXELS];
+    const bool lights_sm = s.n_lights <= LTC_SMEM_LIGHTS;
+    const int lut_texels = 3 * s.lut.w * s.lut.h;
+    const bool lut_sm = lut_texels <= LTC_SMEM_LUT_TEXELS;
+    if (lights_sm) {
+        const float* src = reinterpret_cast<const float*>(s.lights);
+        float* dst = reinterpret_cast<float*>(sh_lights);
+        for (int i = threadIdx.x; i < s.n_lights * 19; i += LTC_BLOCK) dst[i] = src[i];
+    }
+    if (lut_sm)
+        for (int i = threadIdx.x; i < lut_texels; i += LTC_BLOCK) sh_lut[i] = s.lut.data[i];
+    __syncthreads();
+    LtcLut lut = s.lut;
+    if (lut_sm) lut.data = sh_lut;
+    const TriLight* lights = lights_sm ? sh_lights : s.lights;
+    const size_t first = (size_t)f.y0 * f.W;
+    const unsigned n = FROM_QUEUE ? f.cnt->queue_n : (unsigned)((size_t)(f.y1 - f.y0) * f.W);
+    for (unsigned i = blockIdx.x * LTC_BLOCK + threadIdx.x; i < n; i += gridDim.x * LTC_BLOCK) {
+        const size_t ofs = FROM_QUEUE ? (size_t)f.queue[i] : first + i;
+        const float4 nn = ld_stream(f.normal + ofs);
+        float3 c = v3(0.f);
+        if (FROM_QUEUE || !(nn.x == 0.f && nn.y == 0.f && nn.z == 0.f)) {
+            const float4 pp = ld_stream(f.position + ofs);
+            const float4 dd = ld_stream(f.albedo + ofs);
+            const float4 aa = ld_stream(f.alpha + ofs);
+            c = ltc_pixel(lut, lights, s.n_lights, cam_pos, v3(pp), v3(nn), v3(dd), aa.x);
+        }
+        const float4 o = make_float4(c.x, c.y, c.z, 1.f);
+        st_stream(out + ofs, o);
+        if (out2) st_stream(out2 + ofs, o);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_ratio_shadow: n light samples per active pixel, each one closest-hit ray
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, int mode, int height) {
+    int* stk = s_dyn + threadIdx.x;
+    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    unsigned rays = 0;
+    SmemTracer tr{s, stk, stk_t, &rays};
+    const unsigned n = f.cnt->queue_n;
+    const float nf = (float)spp;
+    for (unsigned i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
+        const size_t ofs = f.queue[i];
+        const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+        const float4 pp = ld_stream(f.position + ofs), nn = ld_stream(f.normal + ofs);
+        const float4 dd = ld_stream(f.albedo + ofs), aa = ld_stream(f.alpha + ofs);
+        Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+        rng_next(rng);  // the two jitter draws of the primary ray
+        rng_next(rng);
+        float3 sd = v3(0.f), sn = v3(0.f);
+        for (int k = 0; k < spp; k++) {
+            float3 d, nv;
+            ratio_shadow_sample(s, tr, cam_pos, v3(pp), v3(nn), v3(dd), aa.x, rng, mode, d, nv);
+            sd += d;
+            sn += nv;
+        }
+        sd = sd / nf;  // colors[k] /= n
+        sn = sn / nf;
+        const float gd = (sd.x + sd.y + sd.z) / 3.f, gn = (sn.x + sn.y + sn.z) / 3.f;
+        st_stream(f.sto_direct + ofs, make_float4(gd, gd, gd, 1.f));
+        st_stream(f.sto_no_vis + ofs, make_float4(gn, gn, gn, 1.f));
+    }
+    // one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
+    if ((threadIdx.x & 31) == 0 && rays) atomicAdd(&f.cnt->rays_shadow, (unsigned long long)rays);
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_path_bounce: one iteration of the bounce loop for every live path
+// ---------------------------------------------------------------------------------------------
+// Path state SoA, 5 float4 per path: (p, alpha) (n, pixel) (diffuse, -) (V, -) (tp, -)
+struct PathBuffers {
+    float4* s[5];
+};
+
+template <bool FIRST>
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_path_bounce(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce, int mode, int last, PathBuffers in,
+              PathBuffers out, int in_slot, int height) {
+    int* stk = s_dyn + threadIdx.x;
+    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    unsigned rays = 0;
+    SmemTracer tr{s, stk, stk_t, &rays};
+    const unsigned n = FIRST ? f.cnt->queue_n : f.cnt->path_n[in_slot];
+    const int lane = threadIdx.x & 31;
+    // round the trip count up so whole warps reach the ballot
+    const unsigned n_round = (n + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n_round; i += gridDim.x * TRACE_BLOCK) {
+        bool survive = false;
+        PathState st;
+        size_t ofs = 0;
+        if (i < n) {
+            if (FIRST) {
+                ofs = f.queue[i];
+                const float4 pp = ld_stream(f.position + ofs), nn = ld_stream(f.normal + ofs);
+                const float4 dd = ld_stream(f.albedo + ofs), aa = ld_stream(f.alpha + ofs);
+                st.p = v3(pp);
+                st.n = v3(nn);
+                st.diffuse = v3(dd);
+                st.alpha = aa.x;
+                st.V = normalize(cam_pos - st.p);  // si.wo
+                st.tp = v3(1.f);
+            } else {
+                const float4 a = in.s[0][i], b = in.s[1][i], c = in.s[2][i], d = in.s[3][i], e = in.s[4][i];
+                st.p = v3(a);
+                st.alpha = a.w;
+                st.n = v3(b);
+                ofs = (size_t)__float_as_uint(b.w);
+                st.diffuse = v3(c);
+                st.V = v3(d);
+                st.tp = v3(e);
+            }
+            const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+            Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+            rng_skip(rng, 2 + 5 * bounce);
+            float3 colour;
+            bool traced;
+            const int r = path_bounce(s, tr, st, rng, mode, last != 0, colour, traced);
+            if (r == ORB_PATH_DONE) st_stream(f.colour + ofs, make_float4(colour.x, colour.y, colour.z, 1.f));
+            else survive = true;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, survive);
+        if (m) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&f.cnt->path_n[in_slot ^ 1], (unsigned)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (survive) {
+                const unsigned o = base + __popc(m & ((1u << lane) - 1u));
+                out.s[0][o] = make_float4(st.p.x, st.p.y, st.p.z, st.alpha);
+                out.s[1][o] = make_float4(st.n.x, st.n.y, st.n.z, __uint_as_float((unsigned)ofs));
+                out.s[2][o] = make_float4(st.diffuse.x, st.diffuse.y, st.diffuse.z, 0.f);
+                out.s[3][o] = make_float4(st.V.x, st.V.y, st.V.z, 0.f);
+                out.s[4][o] = make_float4(st.tp.x, st.tp.y, st.tp.z, 0.f);
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
+    if (lane == 0 && rays) atomicAdd(&f.cnt->rays_bounce, (unsigned long long)rays);
+}
+
+__global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
+
+// ---------------------------------------------------------------------------------------------
+// k_accumulate: deviceCode.cu:158-161,172-174
+// ---------------------------------------------------------------------------------------------
+__global__ void k_accumulate(FrameView f, const float4* __restrict__ src, int accum_id) {
+    const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
+    const float scale = 1.f / ((float)accum_id + 1.f);
+    unsigned nan = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t ofs = first + i;
+        float3 c = v3(0.f);
+        if (f.flags[ofs] & FLAG_HIT) c = v3(ld_stream(src + ofs));
+        if (accum_id > 0) c = c + v3(__ldcs(f.accum + ofs));  // read-modify-write: no .nc load here
+        __stcs(f.accum + ofs, make_float4(c.x, c.y, c.z, 1.f));
+        nan += (c.x != c.x || c.y != c.y || c.z != c.z) ? 1u : 0u;
+        f.rgba8[ofs] = make_rgba(scale * c);
+    }
+    for (int o = 16; o > 0; o >>= 1) nan += __shfl_xor_sync(0xffffffffu, nan, o);
+    if ((threadIdx.x & 31) == 0 && nan) atomicAdd(&f.cnt->nan_pixels, nan);
+}
+
+// ---------------------------------------------------------------------------------------------
+// denoise: edge-avoiding a-trous wavelet filter (own definition -- the reference's
+// cuda_include/denoise/bilateral.cuh is an empty file).  CPU statement of the same
+// filter: oracle/restate.cpp ora_denoise().
+//   value  v(q) = (sto_direct.x, sto_no_vis.x)                       packed float2
+//   guide  g(q) = (n.xyz, depth = |p - cam|), depth < 0 for pixels with materialID == 0 or
+//                 n == 0 (lights, misses): passed through unfiltered and never used as a tap
+//   weight w(q) = B3(dx) B3(dy) * max(0, n_c . n_q)^sigma_n * exp(-|d_c - d_q| / (sigma_p * step))
+//                 (* exp(-|v_c - v_q| / sigma_c) per image when sigma_c > 0); NaN taps are skipped
+// ---------------------------------------------------------------------------------------------
+__global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__ guide, float2* __restrict__ val) {
+    const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t ofs = first + i;
+        const float4 nn = ld_stream(f.normal + ofs), pp = ld_stream(f.position + ofs);
+        const float4 mm = ld_stream(f.material_id + ofs);
+        const float4 a = ld_stream(f.sto_direct + ofs), b = ld_stream(f.sto_no_vis + ofs);
+        const bool skip = (nn.x == 0.f && nn.y == 0.f && nn.z == 0.f) || mm.x == 0.f;
+        const float depth = skip ? -1.f : length(v3(pp) - cam_pos);
+        guide[ofs] = make_float4(nn.x, nn.y, nn.z, depth);
+        val[ofs] = make_float2(a.x, b.x);
+    }
+}
+
+__constant__ float c_b3[5] = {1.f / 16.f, 1.f / 4.f, 3.f / 8.f, 1.f / 4.f, 1.f / 16.f};
+
+template <bool FINAL>
+__global__ void __launch_bounds__(256)
+k_denoise_atrous(FrameView f, const float4* __restrict__ guide, const float2* __restrict__ vin, float2* __restrict__ vout,
+                 float4* __restrict__ out_d, float4* __restrict__ out_n, int step, float sigma_n, float inv_sigma_p,
+                 float inv_sigma_c) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int y = f.y0 + blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= f.W || y >= f.y1) return;
+    const size_t ofs = (size_t)y * f.W + x;
+    const float4 gc = __ldg(guide + ofs);
+    const float2 vc = __ldg(vin + ofs);
+    float2 r = vc;
+    if (gc.w >= 0.f) {
+        float sd = 0.f, sn = 0.f, wd = 0.f, wn = 0.f;
+#pragma unroll
+        for (int j = -2; j <= 2; j++) {
+            const int yy = y + j * step;
+            if (yy < 0 || yy >= f.H) continue;
+#pragma unroll
+            for (int i = -2; i <= 2; i++) {
+                const int xx = x + i * step;
+                if (xx < 0 || xx >= f.W) continue;
+                const size_t q = (size_t)yy * f.W + xx;
+                const float4 g = __ldg(guide + q);
+                if (g.w < 0.f) continue;
+                const float2 v = __ldg(vin + q);
+                const float nd = fmaxf(0.f, gc.x * g.x + gc.y * g.y + gc.z * g.z);
+                float w = c_b3[i + 2] * c_b3[j + 2] * powf(nd, sigma_n) * expf(-fabsf(gc.w - g.w) * inv_sigma_p);
+                float w0 = w, w1 = w;
+                if (inv_sigma_c > 0.f) {
+                    w0 *= expf(-fabsf(vc.x - v.x) * inv_sigma_c);
+                    w1 *= expf(-fabsf(vc.y - v.y) * inv_sigma_c);
+                }
+                if (v.x == v.x && w0 == w0) { sd += w0 * v.x; wd += w0; }
+                if (v.y == v.y && w1 == w1) { sn += w1 * v.y; wn += w1; }
+            }
+        }
+        if (wd > 0.f) r.x = sd / wd;
+        if (wn > 0.f) r.y = sn / wn;
+    }
+    if (FINAL) {
+        if (gc.w >= 0.f) {
+            out_d[ofs] = make_float4(r.x, r.x, r.x, 1.f);
+            out_n[ofs] = make_float4(r.y, r.y, r.y, 1.f);
+        } else {  // lights / misses: the unfiltered float4 (emit on light pixels, deviceCode.cu:121-123)
+            out_d[ofs] = f.sto_direct[ofs];
+            out_n[ofs] = f.sto_no_vis[ofs];
+        }
+    } else {
+        vout[ofs] = r;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ratio combine: ltc_ratio_estimator.py:8  colors = ltc * (stoDirect / stoNoVis)
+// ---------------------------------------------------------------------------------------------
+__global__ void k_ratio_combine(const float4* __restrict__ ltc, const float4* __restrict__ sd,
+                                const float4* __restrict__ sn, float4* __restrict__ out, size_t first, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 a = ld_stream(ltc + first + i), b = ld_stream(sd + first + i), c = ld_stream(sn + first + i);
+        st_stream(out + first + i, make_float4(a.x * (b.x / c.x), a.y * (b.y / c.y), a.z * (b.z / c.z), 1.f));
+    }
+}
+
+// flat float arrays (the python RGB layout): n4 float4 groups + scalar tail
+__global__ void k_ratio_combine_flat(const float* __restrict__ ltc, const float* __restrict__ sd,
+                                     const float* __restrict__ sn, float* __restrict__ out, size_t n) {
+    const size_t n4 = n / 4;
+    const float4 *a4 = reinterpret_cast<const float4*>(ltc), *b4 = reinterpret_cast<const float4*>(sd),
+                 *c4 = reinterpret_cast<const float4*>(sn);
+    float4* o4 = reinterpret_cast<float4*>(out);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 a = ld_stream(a4 + i), b = ld_stream(b4 + i), c = ld_stream(c4 + i);
+        st_stream(o4 + i, make_float4(a.x * (b.x / c.x), a.y * (b.y / c.y), a.z * (b.z / c.z), a.w * (b.w / c.w)));
+    }
+    if (blockIdx.x == 0)
+        for (size_t i = 4 * n4 + threadIdx.x; i < n; i += blockDim.x) out[i] = ltc[i] * (sd[i] / sn[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ray casting entry point (tests, tools) and unit kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_trace_rays(SceneView s, const float* __restrict__ org, const float* __restrict__ dir, size_t n, int brute,
+             int* __restrict__ prim, float* __restrict__ t, float* __restrict__ u, float* __restrict__ v, int height,
+             DevCounters* cnt) {
+    int* stk = s_dyn + threadIdx.x;
+    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    const size_t i = (size_t)blockIdx.x * TRACE_BLOCK + threadIdx.x;
+    if (i >= n) return;
+    const float3 o = v3(org[3 * i], org[3 * i + 1], org[3 * i + 2]), d = v3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+    unsigned nn = 0, nt = 0;
+    const Hit h = brute ? trace_brute(s, o, d) : trace_closest(s, o, d, stk, stk_t, TRACE_BLOCK, &nn, &nt);
+    prim[i] = h.prim;
+    t[i] = h.t;
+    u[i] = h.u;
+    v[i] = h.v;
+    if (cnt) {
+        atomicAdd(&cnt->nodes_visited, (unsigned long long)nn);
+        atomicAdd(&cnt->tris_tested, (unsigned long long)nt);
+    }
+}
+
+enum { U_RNG, U_CLIP, U_EDGE, U_FETCH, U_MINV, U_ONB, U_SAMPLE, U_EVAL, U_PDF, U_RGBA, U_SAMPLE_TRI, U_A2W, U_LTC_PIXEL };
+
+__global__ void k_unit(int op, SceneView s, const float* in, float* out) {
+    if (threadIdx.x || blockIdx.x) return;
+    switch (op) {
+        case U_RNG: {  // in: frame, px, py, W, n   out: state0, raw[n], flt[n] (as bits / floats)
+            Rng r = rng_seed((int)in[0], (uint32_t)in[1], (uint32_t)in[2], (uint32_t)in[3]);
+            const int n = (int)in[4];
+            out[0] = __uint_as_float(r.s);
+            for (int i = 0; i < n; i++) out[1 + i] = __uint_as_float(rng_next(r));
+            for (int i = 0; i < n; i++) out[1 + n + i] = rng_nextf(r);
+        } break;
+        case U_CLIP: {  // in: a b c quad  out: n_out, form factor
+            int n_out = 0;
+            const float ff = clipped_form_factor(v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]), v3(in[6], in[7], in[8]),
+                                                 in[9] != 0.f, n_out);
+            out[0] = (float)n_out;
+            out[1] = ff;
+        } break;
+        case U_EDGE:
+            out[0] = edge_integral(v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]));
+            break;
+        case U_FETCH: {
+            Mat3 m;
+            float amp;
+            s.lut.fetch(in[0], in[1], m, amp);
+            out[0] = m.r0.x; out[1] = m.r0.y; out[2] = m.r0.z;
+            out[3] = m.r1.x; out[4] = m.r1.y; out[5] = m.r1.z;
+            out[6] = m.r2.x; out[7] = m.r2.y; out[8] = m.r2.z;
+            out[9] = amp;
+        } break;
+        case U_MINV: {
+            Mat3 m;
+            m.r0 = v3(in[0], in[1], in[2]); m.r1 = v3(in[3], in[4], in[5]); m.r2 = v3(in[6], in[7], in[8]);
+            const Mat3 r = mat3_inverse(m);
+            out[0] = r.r0.x; out[1] = r.r0.y; out[2] = r.r0.z;
+            out[3] = r.r1.x; out[4] = r.r1.y; out[5] = r.r1.z;
+            out[6] = r.r2.x; out[7] = r.r2.y; out[8] = r.r2.z;
+        } break;
+        case U_ONB: {
+            const Mat3 r = onb_rows(v3(in[0], in[1], in[2]));
+            out[0] = r.r0.x; out[1] = r.r0.y; out[2] = r.r0.z;
+            out[3] = r.r1.x; out[4] = r.r1.y; out[5] = r.r1.z;
+            out[6] = r.r2.x; out[7] = r.r2.y; out[8] = r.r2.z;
+        } break;
+        case U_SAMPLE: {  // in: wo, u1, u2, base, alpha
+            float pdf = 0.f;
+            const float3 wi = bsdf_sample(v3(in[0], in[1], in[2]), in[3], in[4], pdf, v3(in[5], in[6], in[7]), in[8]);
+            out[0] = wi.x; out[1] = wi.y; out[2] = wi.z; out[3] = pdf;
+        } break;
+        case U_EVAL: {  // in: wi, wo, base, alpha
+            const float3 r = bsdf_evaluate(v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]), v3(in[6], in[7], in[8]), in[9]);
+            out[0] = r.x; out[1] = r.y; out[2] = r.z;
+        } break;
+        case U_PDF:
+            out[0] = bsdf_pdf(v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]), v3(in[6], in[7], in[8]), in[9]);
+            break;
+        case U_RGBA:
+            out[0] = __uint_as_float(make_rgba(v3(in[0], in[1], in[2])));
+            break;
+        case U_SAMPLE_TRI: {
+            const float3 r = sample_point_on_triangle(v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]),
+                                                      v3(in[6], in[7], in[8]), in[9], in[10]);
+            out[0] = r.x; out[1] = r.y; out[2] = r.z;
+        } break;
+        case U_A2W:
+            out[0] = pdf_area_to_solid_angle(in[0], in[1], in[2]);
+            break;
+        case U_LTC_PIXEL: {  // in: cam(3) p(3) n(3) diffuse(3) alpha
+            const float3 c = ltc_pixel(s.lut, s.lights, s.n_lights, v3(in[0], in[1], in[2]), v3(in[3], in[4], in[5]),
+                                       v3(in[6], in[7], in[8]), v3(in[9], in[10], in[11]), in[12]);
+            out[0] = c.x; out[1] = c.y; out[2] = c.z;
+        } break;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: context
+// ---------------------------------------------------------------------------------------------
+struct HostMesh {
+    int n_tris;
+    MeshRec rec;  // tex filled at commit
+    std::vector<uint8_t> tex;
+};
+
+struct OrbContext {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    int n_sm = 148;
+    // scene staging (host)
+    std::vector<float> h_pos, h_nrm, h_uv;
+    std::vector<int> h_prim_mesh;
+    std::vector<HostMesh> meshes;
+    std::vector<OrbTriLight> h_lights;
+    std::vector<float> h_lut;
+    int lut_w = 0, lut_h = 0, lut_quant = 0;
+    // scene (device)
+    float *d_pos = nullptr, *d_nrm = nullptr, *d_uv = nullptr;
+    int* d_prim_mesh = nullptr;
+    MeshRec* d_meshes = nullptr;
+    std::vector<void*> d_tex;
+    TriLight* d_lights = nullptr;
+    float4* d_lut = nullptr;
+    BvhBuildResult bvh;
+    SceneView view;
+    bool committed = false;
+    int height = 1;  // stack entries per thread
+    // frame
+    int W = 0, H = 0;
+    void* buf[ORB_BUF_COUNT] = {nullptr};
+    float4* colour = nullptr;
+    uint32_t* flags = nullptr;
+    uint32_t* queue = nullptr;
+    DevCounters* cnt = nullptr;
+    float4* path_state[2][5] = {{nullptr}};
+    float4* dn_guide = nullptr;
+    float2* dn_val[2] = {nullptr, nullptr};
+    float* unit_in = nullptr;
+    float* unit_out = nullptr;
+    Camera cam;
+    bool have_cam = false;
+    OrbCounters counters;
+    int last_spp = 0;
+};
+
+static size_t buffer_elem_bytes(int id) { return id == ORB_BUF_RGBA8 ? 4 : 16; }
+
+static void free_scene(OrbContext* c) {
+    cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_prim_mesh); cudaFree(c->d_meshes);
+    for (void* p : c->d_tex) cudaFree(p);
+    c->d_tex.clear();
+    cudaFree(c->bvh.tri); cudaFree(c->bvh.nodes);
+    c->d_pos = c->d_nrm = c->d_uv = nullptr;
+    c->d_prim_mesh = nullptr;
+    c->d_meshes = nullptr;
+    c->bvh = BvhBuildResult();
+    c->committed = false;
+}
+
+static void free_frame(OrbContext* c) {
+    for (int i = 0; i < ORB_BUF_COUNT; i++) { cudaFree(c->buf[i]); c->buf[i] = nullptr; }
+    cudaFree(c->colour); cudaFree(c->flags); cudaFree(c->queue);
+    for (int a = 0; a < 2; a++) for (int b = 0; b < 5; b++) { cudaFree(c->path_state[a][b]); c->path_state[a][b] = nullptr; }
+    cudaFree(c->dn_guide); cudaFree(c->dn_val[0]); cudaFree(c->dn_val[1]);
+    c->colour = nullptr; c->flags = nullptr; c->queue = nullptr; c->dn_guide = nullptr; c->dn_val[0] = c->dn_val[1] = nullptr;
+    c->W = c->H = 0;
+}
+
+static void refresh_view(OrbContext* c) {
+    SceneView& v = c->view;
+    v.tri = c->bvh.tri;
+    v.nodes = c->bvh.nodes;
+    v.root_ref = c->bvh.root_ref;
+    v.n_tris = (int)c->h_prim_mesh.size();
+    v.pos = c->d_pos;
+    v.nrm = c->d_nrm;
+    v.uv = c->d_uv;
+    v.prim_mesh = c->d_prim_mesh;
+    v.meshes = c->d_meshes;
+    v.lights = c->d_lights;
+    v.n_lights = (int)c->h_lights.size();
+    v.lut.data = c->d_lut;
+    v.lut.w = c->lut_w;
+    v.lut.h = c->lut_h;
+    v.lut.quantise = c->lut_quant;
+    if (!c->committed) v.n_tris = 0;
+}
+
+static FrameView frame_view(OrbContext* c, int y0, int y1) {
+    FrameView f;
+    f.W = c->W; f.H = c->H; f.y0 = y0; f.y1 = y1;
+    f.position = (float4*)c->buf[ORB_BUF_POSITION]; f.normal = (float4*)c->buf[ORB_BUF_NORMAL];
+    f.uv = (float4*)c->buf[ORB_BUF_UV]; f.albedo = (float4*)c->buf[ORB_BUF_ALBEDO];
+    f.alpha = (float4*)c->buf[ORB_BUF_ALPHA]; f.material_id = (float4*)c->buf[ORB_BUF_MATERIAL_ID];
+    f.ltc = (float4*)c->buf[ORB_BUF_LTC]; f.sto_direct = (float4*)c->buf[ORB_BUF_STO_DIRECT];
+    f.sto_no_vis = (float4*)c->buf[ORB_BUF_STO_NO_VIS]; f.accum = (float4*)c->buf[ORB_BUF_ACCUM];
+    f.hit = (float4*)c->buf[ORB_BUF_HIT]; f.colour = c->colour; f.rgba8 = (uint32_t*)c->buf[ORB_BUF_RGBA8];
+    f.flags = c->flags; f.queue = c->queue; f.cnt = c->cnt;
+    return f;
+}
+
+static bool rows_ok(OrbContext* c, int& y0, int& y1) {
+    if (y0 == 0 && y1 == 0) y1 = c->H;
+    return y0 >= 0 && y1 <= c->H && y0 < y1;
+}
+
+static size_t trace_smem(OrbContext* c) { return (size_t)c->height * TRACE_BLOCK * 8; }
+
+template <class K>
+static cudaError_t allow_smem(K kernel, size_t bytes) {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+// persistent grid: resident CTAs per SM x SM count
+template <class K>
+static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem) {
+    int per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    return per_sm * c->n_sm;
+}
+
+extern "C" {
+
+int orb_api_version(void) { return ORB_API_VERSION; }
+const char* orb_last_error(void) { return g_err.c_str(); }
+
+int orb_create(int device, OrbContext** out) {
+    NEED(out, "orb_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(ORB_ERR_NO_DEVICE, "orb_create: no CUDA device (this library has no CPU path)");
+    }
+    NEED(device >= 0 && device < n, "orb_create: bad device index");
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    OrbContext* c = new OrbContext();
+    c->device = device;
+    c->n_sm = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaMalloc(&c->cnt, sizeof(DevCounters)));
+    CK(cudaMemset(c->cnt, 0, sizeof(DevCounters)));
+    CK(cudaMalloc(&c->unit_in, 64 * sizeof(float)));
+    CK(cudaMalloc(&c->unit_out, 4096 * sizeof(float)));
+    memset(&c->counters, 0, sizeof(c->counters));
+    memset(&c->view, 0, sizeof(c->view));
+    *out = c;
+    return ORB_OK;
+}
+
+void orb_destroy(OrbContext* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    free_frame(c);
+    cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->cnt); cudaFree(c->unit_in); cudaFree(c->unit_out);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+void* orb_stream(OrbContext* c) { return c ? (void*)c->stream : nullptr; }
+
+int orb_set_stream(OrbContext* c, void* stream) {
+    NEED(c, "orb_set_stream: ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)stream;
+    c->own_stream = false;
+    return ORB_OK;
+}
+
+int orb_sync(OrbContext* c) {
+    NEED(c, "orb_sync: ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+// ---- scene -----------------------------------------------------------------------------------
+int orb_scene_clear(OrbContext* c) {
+    NEED(c, "orb_scene_clear: ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    c->h_pos.clear(); c->h_nrm.clear(); c->h_uv.clear(); c->h_prim_mesh.clear(); c->meshes.clear();
+    refresh_view(c);
+    return ORB_OK;
+}
+
+int orb_scene_add_mesh(OrbContext* c, const OrbMeshDesc* m) {
+    NEED(c && m, "orb_scene_add_mesh: NULL argument");
+    NEED(!c->committed, "orb_scene_add_mesh: scene already committed (orb_scene_clear first)");
+    NEED(m->n_triangles >= 0 && m->n_vertices >= 0, "orb_scene_add_mesh: negative count");
+    NEED(m->n_triangles == 0 || (m->vertex && m->normal && m->texcoord && m->index), "orb_scene_add_mesh: NULL array");
+    NEED(c->h_prim_mesh.size() + (size_t)m->n_triangles < (1u << 28), "orb_scene_add_mesh: too many triangles");
+    const int mesh_id = (int)c->meshes.size();
+    for (int t = 0; t < m->n_triangles; t++)
+        for (int k = 0; k < 3; k++) {
+            const int vi = m->index[3 * t + k];
+            NEED(vi >= 0 && vi < m->n_vertices, "orb_scene_add_mesh: index out of range");
+        }
+    // un-index: 3 corners per global primitive (gathered only at the closest hit)
+    const size_t base = c->h_prim_mesh.size();
+    c->h_pos.resize(9 * (base + m->n_triangles));
+    c->h_nrm.resize(9 * (base + m->n_triangles));
+    c->h_uv.resize(6 * (base + m->n_triangles));
+    for (int t = 0; t < m->n_triangles; t++) {
+        for (int k = 0; k < 3; k++) {
+            const int vi = m->index[3 * t + k];
+            for (int a = 0; a < 3; a++) {
+                c->h_pos[9 * (base + t) + 3 * k + a] = m->vertex[3 * (size_t)vi + a];
+                c->h_nrm[9 * (base + t) + 3 * k + a] = m->normal[3 * (size_t)vi + a];
+            }
+            c->h_uv[6 * (base + t) + 2 * k] = m->texcoord[2 * (size_t)vi];
+            c->h_uv[6 * (base + t) + 2 * k + 1] = m->texcoord[2 * (size_t)vi + 1];
+        }
+        c->h_prim_mesh.push_back(mesh_id);
+    }
+    HostMesh hm;
+    hm.n_tris = m->n_triangles;
+    memset(&hm.rec, 0, sizeof(hm.rec));
+    hm.rec.diffuse = v3(m->diffuse[0], m->diffuse[1], m->diffuse[2]);
+    hm.rec.alpha = m->alpha;
+    hm.rec.emit = v3(m->emit[0], m->emit[1], m->emit[2]);
+    hm.rec.is_light = m->is_light != 0;
+    hm.rec.material_id = m->material_id;
+    if (m->diffuse_tex_rgba8) {
+        NEED(m->tex_w > 0 && m->tex_h > 0, "orb_scene_add_mesh: bad texture size");
+        hm.rec.tex_w = m->tex_w;
+        hm.rec.tex_h = m->tex_h;
+        hm.tex.assign(m->diffuse_tex_rgba8, m->diffuse_tex_rgba8 + 4 * (size_t)m->tex_w * m->tex_h);
+    }
+    c->meshes.push_back(std::move(hm));
+    return ORB_OK;
+}
+
+int orb_scene_set_lights(OrbContext* c, const OrbTriLight* lights, int32_t n) {
+    NEED(c && n >= 0 && (n == 0 || lights), "orb_scene_set_lights: bad argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    c->h_lights.assign(lights, lights + n);
+    cudaFree(c->d_lights);
+    c->d_lights = nullptr;
+    if (n) {
+        CK(cudaMalloc(&c->d_lights, sizeof(TriLight) * n));
+        CK(cudaMemcpy(c->d_lights, lights, sizeof(TriLight) * n, cudaMemcpyHostToDevice));
+    }
+    refresh_view(c);
+    return ORB_OK;
+}
+
+int orb_scene_set_ltc_lut(OrbContext* c, const float* m1, const float* m2, const float* m3, int32_t w, int32_t h,
+                          int32_t quantise) {
+    NEED(c && m1 && m2 && m3 && w > 0 && h > 0, "orb_scene_set_ltc_lut: bad argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    const size_t n = 4 * (size_t)w * h;
+    c->h_lut.resize(3 * n);
+    memcpy(c->h_lut.data(), m1, n * 4);
+    memcpy(c->h_lut.data() + n, m2, n * 4);
+    memcpy(c->h_lut.data() + 2 * n, m3, n * 4);
+    cudaFree(c->d_lut);
+    CK(cudaMalloc(&c->d_lut, 3 * n * 4));
+    CK(cudaMemcpy(c->d_lut, c->h_lut.data(), 3 * n * 4, cudaMemcpyHostToDevice));
+    c->lut_w = w; c->lut_h = h; c->lut_quant = quantise;
+    refresh_view(c);
+    return ORB_OK;
+}
+
+int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
+    NEED(c, "orb_scene_commit: ctx is NULL");
+    NEED(!c->committed, "orb_scene_commit: already committed");
+    CK(cudaSetDevice(c->device));
+    const size_t n = c->h_prim_mesh.size();
+    if (n) {
+        CK(cudaMalloc(&c->d_pos, 36 * n)); CK(cudaMalloc(&c->d_nrm, 36 * n)); CK(cudaMalloc(&c->d_uv, 24 * n));
+        CK(cudaMalloc(&c->d_prim_mesh, 4 * n));
+        CK(cudaMemcpyAsync(c->d_pos, c->h_pos.data(), 36 * n, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_nrm, c->h_nrm.data(), 36 * n, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_uv, c->h_uv.data(), 24 * n, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_prim_mesh, c->h_prim_mesh.data(), 4 * n, cudaMemcpyHostToDevice, c->stream));
+    }
+    std::vector<MeshRec> recs;
+    for (auto& hm : c->meshes) {
+        MeshRec r = hm.rec;
+        r.tex = nullptr;
+        if (!hm.tex.empty()) {
+            void* p = nullptr;
+            CK(cudaMalloc(&p, hm.tex.size()));
+            CK(cudaMemcpyAsync(p, hm.tex.data(), hm.tex.size(), cudaMemcpyHostToDevice, c->stream));
+            c->d_tex.push_back(p);
+            r.tex = (const uchar4*)p;
+        }
+        recs.push_back(r);
+    }
+    if (!recs.empty()) {
+        CK(cudaMalloc(&c->d_meshes, sizeof(MeshRec) * recs.size()));
+        CK(cudaMemcpyAsync(c->d_meshes, recs.data(), sizeof(MeshRec) * recs.size(), cudaMemcpyHostToDevice, c->stream));
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    CK(build_bvh(c->d_pos, (int)n, opt ? opt->max_leaf_tris : 0, c->stream, c->bvh));
+    c->counters.kernel_launches += c->bvh.launches;
+    c->counters.bvh_nodes = (uint64_t)c->bvh.n_nodes;
+    c->counters.bvh_triangles = (uint64_t)n;
+    c->height = c->bvh.height + 2;
+    if (trace_smem(c) > 200 * 1024)
+        return fail(ORB_ERR_INVALID, "orb_scene_commit: BVH too deep for the shared-memory traversal stack");
+    CK(allow_smem(k_primary, trace_smem(c)));
+    CK(allow_smem(k_ratio_shadow, trace_smem(c)));
+    CK(allow_smem(k_path_bounce<true>, trace_smem(c)));
+    CK(allow_smem(k_path_bounce<false>, trace_smem(c)));
+    CK(allow_smem(k_trace_rays, trace_smem(c)));
+    c->committed = true;
+    // host staging is no longer needed
+    std::vector<float>().swap(c->h_pos);
+    std::vector<float>().swap(c->h_nrm);
+    std::vector<float>().swap(c->h_uv);
+    refresh_view(c);
+    return ORB_OK;
+}
+
+// ---- camera / frame --------------------------------------------------------------------------
+int orb_set_camera(OrbContext* c, const float pos[3], const float d00[3], const float du[3], const float dv[3]) {
+    NEED(c && pos && d00 && du && dv, "orb_set_camera: NULL argument");
+    c->cam.pos = v3(pos[0], pos[1], pos[2]);
+    c->cam.d00 = v3(d00[0], d00[1], d00[2]);
+    c->cam.du = v3(du[0], du[1], du[2]);
+    c->cam.dv = v3(dv[0], dv[1], dv[2]);
+    c->have_cam = true;
+    return ORB_OK;
+}
+
+int orb_resize(OrbContext* c, int32_t W, int32_t H) {
+    NEED(c && W > 0 && H > 0, "orb_resize: bad size");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_frame(c);
+    const size_t n = (size_t)W * H;
+    for (int i = 0; i < ORB_BUF_COUNT; i++) {
+        CK(cudaMalloc(&c->buf[i], n * buffer_elem_bytes(i)));
+        CK(cudaMemset(c->buf[i], 0, n * buffer_elem_bytes(i)));
+    }
+    CK(cudaMalloc(&c->colour, n * 16)); CK(cudaMemset(c->colour, 0, n * 16));
+    CK(cudaMalloc(&c->flags, n * 4)); CK(cudaMemset(c->flags, 0, n * 4));
+    CK(cudaMalloc(&c->queue, n * 4));
+    c->W = W; c->H = H;
+    return ORB_OK;
+}
+
+// ---- launch ----------------------------------------------------------------------------------
+static int ensure_path_state(OrbContext* c) {
+    if (c->path_state[0][0]) return ORB_OK;
+    const size_t n = (size_t)c->W * c->H;
+    for (int a = 0; a < 2; a++)
+        for (int b = 0; b < 5; b++) CK(cudaMalloc(&c->path_state[a][b], n * 16));
+    return ORB_OK;
+}
+
+int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
+    NEED(c && cfg, "orb_render: NULL argument");
+    NEED(c->committed, "orb_render: scene not committed");
+    NEED(c->W > 0, "orb_render: orb_resize first");
+    NEED(c->have_cam, "orb_render: orb_set_camera first");
+    NEED(c->lut_w > 0 || (cfg->renderer_type != ORB_LTC_BASELINE && cfg->renderer_type != ORB_RATIO),
+         "orb_render: orb_scene_set_ltc_lut first");
+    int y0 = cfg->y0, y1 = cfg->y1;
+    NEED(rows_ok(c, y0, y1), "orb_render: bad row range");
+    const int mode = cfg->mode;
+    NEED(mode == 0 || mode == 1, "orb_render: mode must be 0 (literal) or 1 (intended)");
+    const int renderer = cfg->renderer_type;
+    const int spp = mode == 0 ? 4 : (cfg->shadow_spp > 0 ? cfg->shadow_spp : 4);      // deviceCode.cu:128
+    const int depth = mode == 0 ? 1 : (cfg->max_depth > 0 ? cfg->max_depth : 1);      // deviceCode.cu:151
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    FrameView f = frame_view(c, y0, y1);
+    const int frame_id = cfg->accum_id + 10007;  // deviceCode.cu:65
+    const size_t smem = trace_smem(c);
+    CK(cudaMemsetAsync(c->cnt, 0, sizeof(DevCounters), st));
+    {
+        dim3 grid((c->W + 15) / 16, (y1 - y0 + 7) / 8);
+        k_primary<<<grid, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
+        c->counters.kernel_launches++;
+        c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
+    }
+    const float4* colour_src = c->colour;
+    if (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) {
+        const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
+        if (renderer == ORB_RATIO) {
+            // light pixels already hold emit in `ltc` (k_primary), so `ltc` IS the frame colour
+            k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+            colour_src = f.ltc;
+        } else {
+            k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.colour, nullptr);
+        }
+        c->counters.kernel_launches++;
+    }
+    if (renderer == ORB_RATIO) {
+        const int g = persistent_grid(c, k_ratio_shadow, TRACE_BLOCK, smem);
+        k_ratio_shadow<<<g, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->height);
+        c->counters.kernel_launches++;
+        c->last_spp = spp;
+    }
+    if (renderer == ORB_PATH) {
+        int rc = ensure_path_state(c);
+        if (rc) return rc;
+        PathBuffers pb[2];
+        for (int a = 0; a < 2; a++)
+            for (int b = 0; b < 5; b++) pb[a].s[b] = c->path_state[a][b];
+        const int g1 = persistent_grid(c, k_path_bounce<true>, TRACE_BLOCK, smem);
+        const int g2 = persistent_grid(c, k_path_bounce<false>, TRACE_BLOCK, smem);
+        for (int b = 0; b < depth; b++) {
+            const int last = b == depth - 1;
+            const int in_slot = b & 1;  // bounce b reads path_n[in_slot] (b > 0), writes path_n[in_slot ^ 1]
+            if (b == 0) {
+                k_path_bounce<true><<<g1, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, b, mode, last, pb[0],
+                                                                    pb[1], in_slot, c->height);
+            } else {
+                k_reset_slot<<<1, 1, 0, st>>>(c->cnt, in_slot ^ 1);
+                k_path_bounce<false><<<g2, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, b, mode, last,
+                                                                     pb[in_slot], pb[in_slot ^ 1], in_slot, c->height);
+                c->counters.kernel_launches++;
+            }
+            c->counters.kernel_launches++;
+        }
+    }
+    {
+        const size_t n = (size_t)(y1 - y0) * c->W;
+        const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
+        k_accumulate<<<g, 256, 0, st>>>(f, colour_src, cfg->accum_id);
+        c->counters.kernel_launches++;
+    }
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+int orb_render(OrbContext* c, const OrbRenderConfig* cfg) {
+    int rc = orb_render_async(c, cfg);
+    if (rc) return rc;
+    return orb_sync(c);
+}
+
+// ---- stand-alone passes ----------------------------------------------------------------------
+int orb_ltc_gbuffer_pass(OrbContext* c, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_ltc_gbuffer_pass: orb_resize first");
+    NEED(c->have_cam, "orb_ltc_gbuffer_pass: orb_set_camera first");
+    NEED(c->lut_w > 0, "orb_ltc_gbuffer_pass: orb_scene_set_ltc_lut first");
+    NEED(rows_ok(c, y0, y1), "orb_ltc_gbuffer_pass: bad row range");
+    CK(cudaSetDevice(c->device));
+    refresh_view(c);
+    FrameView f = frame_view(c, y0, y1);
+    const int g = persistent_grid(c, k_ltc<false>, LTC_BLOCK, 0);
+    k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_denoise: orb_resize first");
+    NEED(c->have_cam, "orb_denoise: orb_set_camera first");
+    NEED(rows_ok(c, y0, y1), "orb_denoise: bad row range");
+    OrbDenoiseConfig d = {5, 32.f, 0.25f, 0.f};
+    if (cfg) d = *cfg;
+    if (d.iterations <= 0) d.iterations = 5;
+    NEED(d.iterations <= 8, "orb_denoise: at most 8 iterations");
+    CK(cudaSetDevice(c->device));
+    const size_t n = (size_t)c->W * c->H;
+    if (!c->dn_guide) {
+        CK(cudaMalloc(&c->dn_guide, n * 16));
+        CK(cudaMalloc(&c->dn_val[0], n * 8));
+        CK(cudaMalloc(&c->dn_val[1], n * 8));
+    }
+    // The filter reads up to 2 * 2^(iters-1) rows beyond the band, so the pack covers the whole frame
+    // (rows outside the band must hold valid G-buffer / sto data, e.g. rendered as a halo).
+    FrameView all = frame_view(c, 0, c->H);
+    FrameView f = frame_view(c, y0, y1);
+    const int gp = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
+    k_denoise_pack<<<gp, 256, 0, c->stream>>>(all, c->cam.pos, c->dn_guide, c->dn_val[0]);
+    c->counters.kernel_launches++;
+    dim3 grid((c->W + 31) / 32, (c->H + 7) / 8);
+    int cur = 0;
+    for (int it = 0; it < d.iterations; it++) {
+        const int step = 1 << it;
+        const float isp = 1.f / (d.sigma_position * (float)step);
+        const float isc = d.sigma_colour > 0.f ? 1.f / d.sigma_colour : 0.f;
+        if (it == d.iterations - 1) {
+            dim3 gb((c->W + 31) / 32, (y1 - y0 + 7) / 8);
+            k_denoise_atrous<true><<<gb, 256, 0, c->stream>>>(f, c->dn_guide, c->dn_val[cur], nullptr,
+                                                               (float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
+                                                               (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN], step,
+                                                               d.sigma_normal, isp, isc);
+        } else {
+            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(all, c->dn_guide, c->dn_val[cur], c->dn_val[cur ^ 1],
+                                                                  nullptr, nullptr, step, d.sigma_normal, isp, isc);
+            cur ^= 1;
+        }
+        c->counters.kernel_launches++;
+    }
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+int orb_ratio_combine(OrbContext* c, int32_t use_denoised, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_ratio_combine: orb_resize first");
+    NEED(rows_ok(c, y0, y1), "orb_ratio_combine: bad row range");
+    CK(cudaSetDevice(c->device));
+    const size_t first = (size_t)y0 * c->W, n = (size_t)(y1 - y0) * c->W;
+    const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
+    k_ratio_combine<<<g, 256, 0, c->stream>>>(
+        (const float4*)c->buf[ORB_BUF_LTC],
+        (const float4*)c->buf[use_denoised ? ORB_BUF_STO_DIRECT_DN : ORB_BUF_STO_DIRECT],
+        (const float4*)c->buf[use_denoised ? ORB_BUF_STO_NO_VIS_DN : ORB_BUF_STO_NO_VIS],
+        (float4*)c->buf[ORB_BUF_RATIO_FINAL], first, n);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+// ---- buffers ---------------------------------------------------------------------------------
+size_t orb_buffer_bytes(OrbContext* c, int32_t id) {
+    if (!c || id < 0 || id >= ORB_BUF_COUNT) return 0;
+    return (size_t)c->W * c->H * buffer_elem_bytes(id);
+}
+
+void* orb_buffer_device_ptr(OrbContext* c, int32_t id) {
+    if (!c || id < 0 || id >= ORB_BUF_COUNT) return nullptr;
+    return c->buf[id];
+}
+
+int orb_buffer_download(OrbContext* c, int32_t id, void* dst, size_t bytes) {
+    NEED(c && dst && id >= 0 && id < ORB_BUF_COUNT, "orb_buffer_download: bad argument");
+    NEED(bytes <= orb_buffer_bytes(c, id), "orb_buffer_download: too many bytes");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst, c->buf[id], bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_buffer_download_rows(OrbContext* c, int32_t id, void* dst, int32_t y0, int32_t y1) {
+    NEED(c && dst && id >= 0 && id < ORB_BUF_COUNT, "orb_buffer_download_rows: bad argument");
+    NEED(rows_ok(c, y0, y1), "orb_buffer_download_rows: bad row range");
+    CK(cudaSetDevice(c->device));
+    const size_t row = (size_t)c->W * buffer_elem_bytes(id);
+    CK(cudaMemcpyAsync(dst, (const char*)c->buf[id] + row * y0, row * (y1 - y0), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_buffer_upload(OrbContext* c, int32_t id, const void* src, size_t bytes) {
+    NEED(c && src && id >= 0 && id < ORB_BUF_COUNT, "orb_buffer_upload: bad argument");
+    NEED(bytes <= orb_buffer_bytes(c, id), "orb_buffer_upload: too many bytes");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(c->buf[id], src, bytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_get_counters(OrbContext* c, OrbCounters* out) {
+    NEED(c && out, "orb_get_counters: NULL argument");
+    CK(cudaSetDevice(c->device));
+    DevCounters d;
+    CK(cudaMemcpyAsync(&d, c->cnt, sizeof(d), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    *out = c->counters;
+    out->rays_shadow = d.rays_shadow;   // of the last frame
+    out->rays_bounce = d.rays_bounce;
+    out->nan_pixels = d.nan_pixels;
+    out->active_pixels = d.queue_n;
+    out->nodes_visited = d.nodes_visited;
+    out->tris_tested = d.tris_tested;
+    out->bvh_height = (uint64_t)c->bvh.height;
+    return ORB_OK;
+}
+
+// ---- host-buffer entry points ----------------------------------------------------------------
+int orb_ratio_estimator_host(OrbContext* c, const float* ltc, const float* sd, const float* sn, float* out, size_t n) {
+    NEED(c && ltc && sd && sn && out, "orb_ratio_estimator_host: NULL argument");
+    if (n == 0) return ORB_OK;
+    CK(cudaSetDevice(c->device));
+    const size_t np = (n + 3) & ~(size_t)3;  // 16-byte aligned sub-arrays
+    float* d = nullptr;
+    CK(cudaMalloc(&d, 4 * np * sizeof(float)));
+    CK(cudaMemcpyAsync(d, ltc, n * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d + np, sd, n * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d + 2 * np, sn, n * 4, cudaMemcpyHostToDevice, c->stream));
+    const int g = (int)std::max<size_t>(1, std::min<size_t>((n / 4 + 255) / 256, (size_t)c->n_sm * 8));
+    k_ratio_combine_flat<<<g, 256, 0, c->stream>>>(d, d + np, d + 2 * np, d + 3 * np, n);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, d + 3 * np, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaFree(d));
+    return ORB_OK;
+}
+
+int orb_trace_rays_host(OrbContext* c, const float* origin, const float* direction, size_t n, int32_t brute,
+                        int32_t* prim, float* t, float* u, float* v) {
+    NEED(c && origin && direction && prim && t && u && v, "orb_trace_rays_host: NULL argument");
+    NEED(c->committed, "orb_trace_rays_host: scene not committed");
+    if (n == 0) return ORB_OK;
+    CK(cudaSetDevice(c->device));
+    float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr;
+    int* d_p = nullptr;
+    CK(cudaMalloc(&d_o, 12 * n)); CK(cudaMalloc(&d_d, 12 * n)); CK(cudaMalloc(&d_t, 12 * n)); CK(cudaMalloc(&d_p, 4 * n));
+    CK(cudaMemcpyAsync(d_o, origin, 12 * n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(d_d, direction, 12 * n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemsetAsync(c->cnt, 0, sizeof(DevCounters), c->stream));
+    const int g = (int)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+    k_trace_rays<<<g, TRACE_BLOCK, trace_smem(c), c->stream>>>(c->view, d_o, d_d, n, brute, d_p, d_t, d_t + n, d_t + 2 * n,
+                                                               c->height, c->cnt);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(prim, d_p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(t, d_t, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(u, d_t + n, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(v, d_t + 2 * n, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_p);
+    return ORB_OK;
+}
+
+// ---- known-answer entry points ---------------------------------------------------------------
+static int run_unit(OrbContext* c, int op, const float* in, int n_in, float* out, int n_out) {
+    NEED(c, "orb_unit: ctx is NULL");
+    NEED(n_in <= 64 && n_out <= 4096, "orb_unit: too many values");
+    CK(cudaSetDevice(c->device));
+    refresh_view(c);
+    CK(cudaMemcpyAsync(c->unit_in, in, n_in * 4, cudaMemcpyHostToDevice, c->stream));
+    k_unit<<<1, 32, 0, c->stream>>>(op, c->view, c->unit_in, c->unit_out);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, c->unit_out, n_out * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_unit_rng(OrbContext* c, int frame_id, uint32_t px, uint32_t py, uint32_t W, int n, uint32_t* state0,
+                 uint32_t* raw, float* flt) {
+    NEED(n >= 0 && n <= 1000, "orb_unit_rng: n out of range");
+    const float in[5] = {(float)frame_id, (float)px, (float)py, (float)W, (float)n};
+    std::vector<float> out(1 + 2 * n);
+    int rc = run_unit(c, U_RNG, in, 5, out.data(), 1 + 2 * n);
+    if (rc) return rc;
+    memcpy(state0, &out[0], 4);
+    if (n) memcpy(raw, &out[1], 4 * n);
+    if (n) memcpy(flt, &out[1 + n], 4 * n);
+    return ORB_OK;
+}
+
+int orb_unit_clip(OrbContext* c, const float* abc9, int quad, int* n_out, float* form_factor) {
+    float in[10];
+    memcpy(in, abc9, 36);
+    in[9] = quad ? 1.f : 0.f;
+    float out[2];
+    int rc = run_unit(c, U_CLIP, in, 10, out, 2);
+    if (rc) return rc;
+    *n_out = (int)out[0];
+    *form_factor = out[1];
+    return ORB_OK;
+}
+
+int orb_unit_integrate_edge(OrbContext* c, const float* a, const float* b, float* out) {
+    float in[6];
+    memcpy(in, a, 12);
+    memcpy(in + 3, b, 12);
+    return run_unit(c, U_EDGE, in, 6, out, 1);
+}
+
+int orb_unit_fetch_ltc(OrbContext* c, float alpha, float theta, float* m9_amp) {
+    NEED(c && c->lut_w > 0, "orb_unit_fetch_ltc: orb_scene_set_ltc_lut first");
+    const float in[2] = {alpha, theta};
+    return run_unit(c, U_FETCH, in, 2, m9_amp, 10);
+}
+
+int orb_unit_mat_inverse(OrbContext* c, const float* m9, float* out9) { return run_unit(c, U_MINV, m9, 9, out9, 9); }
+int orb_unit_onb(OrbContext* c, const float* n, float* rows9) { return run_unit(c, U_ONB, n, 3, rows9, 9); }
+
+int orb_unit_sample_direction(OrbContext* c, const float* wo, float u1, float u2, const float* base, float alpha,
+                              float* wi_pdf4) {
+    const float in[9] = {wo[0], wo[1], wo[2], u1, u2, base[0], base[1], base[2], alpha};
+    return run_unit(c, U_SAMPLE, in, 9, wi_pdf4, 4);
+}
+
+int orb_unit_evaluate(OrbContext* c, const float* wi, const float* wo, const float* base, float alpha, float* out3) {
+    const float in[10] = {wi[0], wi[1], wi[2], wo[0], wo[1], wo[2], base[0], base[1], base[2], alpha};
+    return run_unit(c, U_EVAL, in, 10, out3, 3);
+}
+
+int orb_unit_pdf(OrbContext* c, const float* wi, const float* wo, const float* base, float alpha, float* out) {
+    const float in[10] = {wi[0], wi[1], wi[2], wo[0], wo[1], wo[2], base[0], base[1], base[2], alpha};
+    return run_unit(c, U_PDF, in, 10, out, 1);
+}
+
+int orb_unit_make_rgba(OrbContext* c, const float* c3, uint32_t* out) {
+    float o;
+    int rc = run_unit(c, U_RGBA, c3, 3, &o, 1);
+    if (rc) return rc;
+    memcpy(out, &o, 4);
+    return ORB_OK;
+}
+
+int orb_unit_sample_tri(OrbContext* c, const float* v9, float u1, float u2, float* out3) {
+    float in[11];
+    memcpy(in, v9, 36);
+    in[9] = u1;
+    in[10] = u2;
+    return run_unit(c, U_SAMPLE_TRI, in, 11, out3, 3);
+}
+
+int orb_unit_pdf_a2w(OrbContext* c, float pdf, float dist2, float cos_theta, float* out) {
+    const float in[3] = {pdf, dist2, cos_theta};
+    return run_unit(c, U_A2W, in, 3, out, 1);
+}
+
+int orb_unit_ltc_pixel(OrbContext* c, const float* cam3, const float* p3, const float* n3, const float* diffuse3,
+                       float alpha, float* out3) {
+    NEED(c && c->lut_w > 0, "orb_unit_ltc_pixel: orb_scene_set_ltc_lut first");
+    const float in[13] = {cam3[0], cam3[1], cam3[2], p3[0], p3[1], p3[2], n3[0], n3[1], n3[2],
+                          diffuse3[0], diffuse3[1], diffuse3[2], alpha};
+    return run_unit(c, U_LTC_PIXEL, in, 13, out3, 3);
+}
+
+}  // extern "C"

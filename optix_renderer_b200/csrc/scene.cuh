@@ -1,0 +1,260 @@
+// scene.cuh -- scene data as the kernels see it in HBM, the ray/triangle test, BVH traversal and
+// the closest-hit / miss shading record.
+//
+// Replaces, for the per-pixel hot path:
+//   owl::traceRay -> optixTrace over OWL's IAS -> per-mesh GAS        (call sites
+//       cuda_src/deviceCode.cu:76, cuda_include/ratio/ratio.cuh:50, cuda_include/path/path.cuh:219;
+//       build include/viewer.hpp:506-507,516-517)                      -> trace_closest()
+//   __closesthit__triangleMeshCH, cuda_include/hit_miss.cuh:14-50      -> shade_hit()
+//   __miss__miss, cuda_include/hit_miss.cuh:52-63                      -> Surface defaults
+//   barycentricInterpolate, cuda_include/utils.cuh:10-29
+//
+// HBM layout (all arrays 16-byte aligned, built once per scene, replicated per GPU):
+//   tri      3 x float4 per triangle in BVH-leaf order: (v0.xyz, global prim id), (e1.xyz, 0),
+//            (e2.xyz, 0) with e1 = v1 - v0, e2 = v2 - v0 rounded in fp32 -- the operands the
+//            checker's Moeller-Trumbore forms at test time.  48 B, three 128-bit loads.
+//   nodes    64-byte BVH2 nodes, each holding BOTH child boxes and both child references, so
+//            one node fetch (four 128-bit loads, one 64-B sector pair) decides two subtrees.
+//   pos/nrm/uv  per-global-primitive corner attributes, un-indexed like the reference's meshes
+//            (src/Model.cpp:186-201): 9 + 9 + 6 floats, gathered only at the closest hit.
+//   prim_mesh, meshes   global prim -> mesh record (TriangleMeshData without the pointers).
+// Global primitive id = triangles of earlier meshes + local primitive index, meshes in scene
+// order (surfaces, then lights; src/scene.cpp:5-13) = (instance, primitive) of the reference.
+#pragma once
+#include "ltc.cuh"
+#include "vec.cuh"
+
+namespace orb {
+
+struct BvhNode {
+    float4 a;  // c0.lo.x c0.lo.y c0.lo.z c0.hi.x
+    float4 b;  // c0.hi.y c0.hi.z c1.lo.x c1.lo.y
+    float4 c;  // c1.lo.z c1.hi.x c1.hi.y c1.hi.z
+    int c0, c1;  // child reference: >= 0 inner node index, < 0 leaf = ~((first << 3) | (count-1))
+    int pad0, pad1;
+};
+static_assert(sizeof(BvhNode) == 64, "BvhNode layout");
+
+ORB_HD int leaf_ref(int first, int count) { return ~((first << 3) | (count - 1)); }
+
+struct MeshRec {  // TriangleMeshData, cuda_include/common.cuh:130-151, minus pointers
+    float3 diffuse;
+    float alpha;
+    float3 emit;
+    int is_light;
+    uint32_t material_id;
+    int tex_w, tex_h;
+    int pad;
+    const uchar4* tex;  // RGBA8 diffuse texture or nullptr (nearest / clamp, viewer.hpp:441-447)
+};
+
+struct SceneView {
+    const float4* tri;
+    const BvhNode* nodes;
+    int root_ref;  // child-style reference of the root; 0 triangles -> n_tris == 0
+    int n_tris;
+    const float* pos;
+    const float* nrm;
+    const float* uv;
+    const int* prim_mesh;
+    const MeshRec* meshes;
+    const TriLight* lights;
+    int n_lights;
+    LtcLut lut;
+};
+
+struct Hit {
+    float t, u, v;
+    int prim;  // global primitive id, -1 = miss
+};
+
+#define ORB_TMAX 1e30f  // owl::RayT default tmax; tmin = 0
+
+// Moeller-Trumbore exactly as oracle/trace_cpu.h tri_test(): every rounding step is explicit.
+ORB_HD bool tri_test(float4 t0, float4 t1, float4 t2, float3 o, float3 d, float tmin, float tmax, float& t, float& u,
+                     float& v) {
+    const float px = xfma(d.y, t2.z, -xmul(d.z, t2.y));
+    const float py = xfma(d.z, t2.x, -xmul(d.x, t2.z));
+    const float pz = xfma(d.x, t2.y, -xmul(d.y, t2.x));
+    const float det = xfma(t1.z, pz, xfma(t1.y, py, xmul(t1.x, px)));
+    if (det == 0.f) return false;
+    const float inv = xdiv(1.f, det);
+    const float sx = xsub(o.x, t0.x), sy = xsub(o.y, t0.y), sz = xsub(o.z, t0.z);
+    const float uu = xmul(xfma(sz, pz, xfma(sy, py, xmul(sx, px))), inv);
+    if (!(uu >= 0.f && uu <= 1.f)) return false;
+    const float qx = xfma(sy, t1.z, -xmul(sz, t1.y));
+    const float qy = xfma(sz, t1.x, -xmul(sx, t1.z));
+    const float qz = xfma(sx, t1.y, -xmul(sy, t1.x));
+    const float vv = xmul(xfma(d.z, qz, xfma(d.y, qy, xmul(d.x, qx))), inv);
+    if (!(vv >= 0.f && xadd(uu, vv) <= 1.f)) return false;
+    const float tt = xmul(xfma(t2.z, qz, xfma(t2.y, qy, xmul(t2.x, qx))), inv);
+    if (!(tt > tmin && tt < tmax)) return false;
+    t = tt;
+    u = uu;
+    v = vv;
+    return true;
+}
+
+// closest t wins; equal t goes to the lowest global primitive id (deterministic in any order)
+ORB_HD void hit_consider(Hit& best, float t, float u, float v, int prim) {
+    if (t < best.t || (t == best.t && prim < best.prim)) {
+        best.t = t;
+        best.u = u;
+        best.v = v;
+        best.prim = prim;
+    }
+}
+
+// Conservative slab test: entry distance (widened by a few ulp) or a negative value on a miss.
+// Boxes are already padded by the builder, so a box is never rejected for a triangle the test
+// above would accept at t <= tbest.
+ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 o, float3 inv,
+                     float tbest, float& tnear) {
+    const float ax = (lox - o.x) * inv.x, bx = (hix - o.x) * inv.x;
+    const float ay = (loy - o.y) * inv.y, by = (hiy - o.y) * inv.y;
+    const float az = (loz - o.z) * inv.z, bz = (hiz - o.z) * inv.z;
+    float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+    float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tbest));
+    t0 = t0 - fabsf(t0) * 1e-6f;
+    t1 = t1 + fabsf(t1) * 1e-6f;
+    tnear = t0;
+    return t0 <= t1;
+}
+
+// Closest-hit traversal.  STACK entries live where the caller put them (`stk`/`stk_t` index
+// stride `stride`): shared memory interleaved per lane in the kernels, a plain array on the CPU.
+template <class IntPtr, class FltPtr>
+ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, FltPtr stk_t, int stride,
+                         unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+    Hit best;
+    best.t = INFINITY;
+    best.u = best.v = 0.f;
+    best.prim = -1;
+    if (s.n_tris == 0) return best;
+    const float3 inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    int sp = 0;
+    int cur = s.root_ref;
+    for (;;) {
+        if (cur >= 0) {
+            const BvhNode* np = s.nodes + cur;
+#ifdef __CUDA_ARCH__
+            const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
+            const int4 nd = __ldg(reinterpret_cast<const int4*>(&np->c0));
+            const int c0 = nd.x, c1 = nd.y;
+#else
+            const float4 na = np->a, nb = np->b, nc = np->c;
+            const int c0 = np->c0, c1 = np->c1;
+#endif
+            if (n_nodes) ++*n_nodes;
+            const float lim = best.prim < 0 ? ORB_TMAX : best.t;
+            float tn0, tn1;
+            const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, o, inv, lim, tn0);
+            const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, o, inv, lim, tn1);
+            if (h0 && h1) {
+                const bool swap = tn1 < tn0;
+                const int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
+                stk[sp * stride] = farc;
+                stk_t[sp * stride] = swap ? tn0 : tn1;
+                ++sp;
+                cur = nearc;
+                continue;
+            }
+            if (h0) { cur = c0; continue; }
+            if (h1) { cur = c1; continue; }
+        } else {
+            const int lr = ~cur;
+            const int first = lr >> 3, count = (lr & 7) + 1;
+            for (int i = 0; i < count; i++) {
+                const float4* tp = s.tri + 3 * (size_t)(first + i);
+#ifdef __CUDA_ARCH__
+                const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+#else
+                const float4 t0 = tp[0], t1 = tp[1], t2 = tp[2];
+#endif
+                if (n_tris) ++*n_tris;
+                float t, u, v;
+                if (tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(t0.w));
+            }
+        }
+        // pop, skipping subtrees that start beyond the current closest hit
+        for (;;) {
+            if (sp == 0) return best;
+            --sp;
+            cur = stk[sp * stride];
+            if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) break;
+        }
+    }
+}
+
+// Brute force over every triangle record: the GPU-side reference for hit-id parity tests.
+ORB_HD Hit trace_brute(const SceneView& s, float3 o, float3 d) {
+    Hit best;
+    best.t = INFINITY;
+    best.u = best.v = 0.f;
+    best.prim = -1;
+    for (int i = 0; i < s.n_tris; i++) {
+        const float4* tp = s.tri + 3 * (size_t)i;
+        float t, u, v;
+        if (tri_test(tp[0], tp[1], tp[2], o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(tp[0].w));
+    }
+    return best;
+}
+
+// ---- closest-hit / miss record ---------------------------------------------------------------
+// SurfaceInteraction (cuda_include/common.cuh:163-183) reduced to the fields the path reads.
+struct Surface {
+    bool hit, is_light;
+    uint32_t material_id;
+    float3 p, n, diffuse, emit;
+    float u, v;  // si.uv
+    float alpha, area;
+};
+
+ORB_HD Surface surface_miss() {  // __miss__miss + SurfaceInteraction defaults, const_color = 0 (viewer.hpp:530)
+    Surface s;
+    s.hit = false;
+    s.is_light = false;
+    s.material_id = 0;
+    s.p = s.n = s.diffuse = s.emit = v3(0.f);
+    s.u = s.v = 0.f;
+    s.alpha = 0.f;
+    s.area = 0.f;
+    return s;
+}
+
+// (1-u-v)*a + u*b + v*c, each step rounded (barycentricInterpolate, utils.cuh:10-29)
+ORB_HD float bary1(float w, float u, float v, float a, float b, float c) {
+    return xadd(xadd(xmul(w, a), xmul(u, b)), xmul(v, c));
+}
+
+ORB_HD Surface shade_hit(const SceneView& s, int prim, float u, float v) {
+    if (prim < 0) return surface_miss();
+    Surface r;
+    const MeshRec& m = s.meshes[s.prim_mesh[prim]];
+    r.hit = true;
+    r.material_id = m.material_id;
+    const float* P = s.pos + 9 * (size_t)prim;
+    const float* N = s.nrm + 9 * (size_t)prim;
+    const float* T = s.uv + 6 * (size_t)prim;
+    const float3 v1 = v3(P[0], P[1], P[2]), v2 = v3(P[3], P[4], P[5]), v3_ = v3(P[6], P[7], P[8]);
+    r.area = 0.5f * length(cross(v1 - v2, v3_ - v2));
+    const float w = xsub(xsub(1.f, u), v);
+    r.p = v3(bary1(w, u, v, v1.x, v2.x, v3_.x), bary1(w, u, v, v1.y, v2.y, v3_.y), bary1(w, u, v, v1.z, v2.z, v3_.z));
+    r.u = fabsf(fmodf(bary1(w, u, v, T[0], T[2], T[4]), 1.f));
+    r.v = fabsf(fmodf(bary1(w, u, v, T[1], T[3], T[5]), 1.f));
+    r.n = xnormalize(v3(bary1(w, u, v, N[0], N[3], N[6]), bary1(w, u, v, N[1], N[4], N[7]), bary1(w, u, v, N[2], N[5], N[8])));
+    r.diffuse = m.diffuse;
+    if (m.tex) {  // point sampling, normalised coordinates, clamp; texel read as unorm8 -> float
+        int i = (int)floorf(r.u * (float)m.tex_w), j = (int)floorf(r.v * (float)m.tex_h);
+        i = imin(imax(i, 0), m.tex_w - 1);
+        j = imin(imax(j, 0), m.tex_h - 1);
+        const uchar4 c = m.tex[(size_t)j * m.tex_w + i];
+        r.diffuse = v3((float)c.x * (1.f / 255.f), (float)c.y * (1.f / 255.f), (float)c.z * (1.f / 255.f));
+    }
+    r.alpha = owl_max(0.01f, owl_min(m.alpha, 1.f));  // owl::clamp, hit_miss.cuh:45-46
+    r.emit = m.emit;
+    r.is_light = m.is_light != 0;
+    return r;
+}
+
+}  // namespace orb
