@@ -83,6 +83,13 @@ uint32_t ora_u_make_rgba(const float* c3);
 /* ltc_ratio_estimator.py:8  colors = ltc * (stoDirect / stoNoVis), n float elements */
 void ora_ratio_combine(long long n, const float* ltc, const float* sto_direct, const float* sto_no_vis, float* out);
 
+/* Edge-avoiding a-trous filter over the two grey sto_* images (float4 buffers of W*H pixels).
+ * liboracle.so ONLY: the reference has no denoiser (cuda_include/denoise/bilateral.cuh is empty),
+ * so this is the definition the CUDA kernel is checked against, not a restatement. */
+void ora_denoise(int W, int H, const float* normal, const float* position, const float* materialID,
+                 const float* sto_direct, const float* sto_no_vis, const float* cam_pos, int iterations,
+                 float sigma_n, float sigma_p, float sigma_c, float* out_direct, float* out_no_vis, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

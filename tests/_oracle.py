@@ -81,6 +81,9 @@ class Oracle:
         L.ora_u_make_rgba.restype = C.c_uint32
         L.ora_ratio_combine.argtypes = [C.c_longlong, _f, _f, _f, _f]
         self.kind = L.ora_kind().decode()
+        if self.kind == "restatement":
+            L.ora_denoise.argtypes = [C.c_int, C.c_int, _f, _f, _f, _f, _f, _f, C.c_int, C.c_float, C.c_float,
+                                      C.c_float, _f, _f, C.c_int]
         self._keep = []
 
     # ---- scene ----
@@ -162,6 +165,17 @@ class Oracle:
         out = np.empty_like(ltc)
         self.lib.ora_ratio_combine(ltc.size, _fp(ltc), _fp(sd), _fp(snv), _fp(out))
         return out
+
+    def denoise(self, normal, position, material_id, sto_direct, sto_no_vis, cam_pos, iterations=5,
+                sigma_normal=32.0, sigma_position=0.25, sigma_colour=0.0, nthreads=1):
+        """Own definition (no reference denoiser exists); liboracle.so only."""
+        a = [f32(x) for x in (normal, position, material_id, sto_direct, sto_no_vis)]
+        H, W = a[0].shape[:2]
+        c = f32(cam_pos)
+        od, on = np.empty_like(a[3]), np.empty_like(a[4])
+        self.lib.ora_denoise(W, H, *[_fp(x) for x in a], _fp(c), int(iterations), sigma_normal, sigma_position,
+                             sigma_colour, _fp(od), _fp(on), int(nthreads))
+        return od, on
 
     # ---- units ----
     def u_rng(self, frame, px, py, W, H, n):
