@@ -1,0 +1,327 @@
+"""bench.py -- BASELINE.json's metric on the hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ratio|path]
+
+A step = one pass of the hot path over one frame of the synthetic scene:
+  ratio (default; BASELINE configs[2], the config the "1080p frames/s" metric is quoted on):
+      1920x1080, ~1M triangles, 16 quad lights (32 TriLights), RATIO renderer in intended mode
+      -- primary rays, LTC sum over all lights, 4 shadow rays per pixel -- + 5-pass a-trous
+      denoise of the two stochastic images + ratio combine.  accumId advances every step.
+  path  (configs[3]): 8-bounce PATH frame of the same scene.
+Metric: Mrays/s = device-counted rays (primary + shadow + bounce) / second, whole job.
+N > 1 (torchrun, one rank per GPU): the frame is split into row bands (strong scaling), the
+BVH is replicated, and the finished band of the output (float4 ratio image + RGBA8) is
+assembled with one NCCL all-gather per buffer inside the timed region.
+
+--impl reference times the reference's own CPU code for the same frame (oracle/_ref = the
+reference's device source compiled as host C++; falls back to the oracle restatement) on all host
+cores, each step a bounded sample of rows of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 1920, 1080
+N_TRIS, N_QUADS = 1_000_000, 16
+SPP, DEPTH, DN_ITERS = 4, 8, 5
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                if o.returncode == 0:
+                    self.rows.append([x.strip() for x in o.stdout.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "samples": len(sm),
+                "power_w_max": max(float(r[2]) for r in self.rows), "reasons": reasons}
+
+
+# ALGORITHMIC bytes per stage, float4 AoS as at the boundary.
+def stage_bytes(stage, px, active, accum_id_gt0=True):
+    if stage == "primary":        # 6 G-buffers + hit record written, flags
+        return px * (6 * 16 + 16 + 4) + active * 4
+    if stage in ("ltc", "ltc_gbuffer"):  # position, normal, albedo, alpha read; ltc written (+ queue index)
+        return active * (80 + (4 if stage == "ltc" else 0))
+    if stage == "shadow":         # same 4 reads; sto_direct + sto_no_vis written
+        return active * (64 + 32 + 4)
+    if stage == "accumulate":     # colour + flags read, accum read/write, RGBA8 written
+        return px * (16 + 4 + 16 + (16 if accum_id_gt0 else 0) + 4)
+    if stage == "denoise_pack":   # normal, position, materialID, 2 sto read; guide + packed value written
+        return px * (5 * 16 + 16 + 8)
+    if stage == "denoise":        # per pass: guide + value read, value written; last pass writes 2 float4
+        return px * ((DN_ITERS - 1) * (16 + 8 + 8) + (16 + 8 + 32))
+    if stage == "combine":        # 3 float4 read, 1 written
+        return px * 64
+    return 0
+
+
+def run_reference(args):
+    """The reference's CPU implementation of the frame on the host cores (bounded sample)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    from optix_renderer_b200 import scenes
+
+    kind = "reference-intended" if _oracle.available("reference-intended") else "restatement"
+    o = _oracle.Oracle(kind)
+    sc = scenes.scene_synthetic(N_TRIS, N_QUADS, W, H)
+    o.load_scene(sc)
+    cores = os.cpu_count() or 1
+    rt = _oracle.RATIO if args.workload == "ratio" else _oracle.PATH
+    o.set_options(1, SPP, DEPTH if args.workload == "path" else 1)
+    # calibrate the sample: rows of the middle of the frame worth ~1.5 s per step
+    t = time.perf_counter()
+    o.render(W, H, rt, 0, rows=(536, 544), nthreads=cores)
+    per_row = (time.perf_counter() - t) / 8
+    budget = min(150.0, max(10.0, 2.0 * (args.steps + args.warmup))) / (args.steps + args.warmup)
+    rows = int(max(8, min(H, budget / per_row)))
+    y0 = (H - rows) // 2
+    for i in range(args.warmup):
+        o.render(W, H, rt, i, rows=(y0, y0 + rows), nthreads=cores)
+    rays, t0 = 0, time.perf_counter()
+    for i in range(args.steps):
+        rays += o.render(W, H, rt, args.warmup + i, rows=(y0, y0 + rows), nthreads=cores)["rays"]
+    dt = time.perf_counter() - t0
+    v = rays / dt / 1e6
+    sample = "%d of %d rows (y %d..%d) of the %s frame per step, %d threads" % (rows, H, y0, y0 + rows, args.workload, cores)
+    line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "ms_per_full_frame_extrapolated": dt / args.steps * 1e3 * H / rows,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, 1),
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores,
+                             "kind": "reference" if kind.startswith("reference") else "port", "sample": sample},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "CPU: reference device source (rayGen) compiled as host C++ behind the OWL shim; denoise not "
+                    "included (the reference has none)"}
+    print(json.dumps(line))
+
+
+def workload_config(args, n):
+    return {"workload": ("BASELINE configs[2]: synthetic %d-triangle scene %dx%d, %d quad lights (%d TriLights), RATIO "
+                         "intended mode %d spp shadow rays + %d-pass a-trous denoise + ratio combine" %
+                         (N_TRIS, W, H, N_QUADS, 2 * N_QUADS, SPP, DN_ITERS)) if args.workload == "ratio" else
+            ("BASELINE configs[3]: same scene, PATH intended mode, %d bounces, progressive" % DEPTH),
+            "width": W, "height": H, "triangles": N_TRIS, "tri_lights": 2 * N_QUADS, "shadow_spp": SPP,
+            "max_depth": DEPTH if args.workload == "path" else 1, "lut": "8x8 (reference ltc_isotropic.h)",
+            "partition": "row bands x%d, BVH replicated, NCCL all-gather assembly" % n if n > 1 else "single GPU",
+            "l2": "working set per frame (13+ float4 frame buffers of 33 MB, 48 MB triangles, 64 MB BVH) exceeds the "
+                  "126 MB L2; no explicit flush"}
+
+
+def cpu_baseline_sample(workload, seconds=12.0):
+    """Rank 0, N = 1: the reference's CPU code on a bounded sample of the same frame."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    from optix_renderer_b200 import scenes
+
+    kind = "reference-intended" if _oracle.available("reference-intended") else "restatement"
+    o = _oracle.Oracle(kind)
+    o.load_scene(scenes.scene_synthetic(N_TRIS, N_QUADS, W, H))
+    cores = os.cpu_count() or 1
+    rt = _oracle.RATIO if workload == "ratio" else _oracle.PATH
+    o.set_options(1, SPP, DEPTH if workload == "path" else 1)
+    t = time.perf_counter()
+    o.render(W, H, rt, 0, rows=(536, 544), nthreads=cores)
+    per_row = (time.perf_counter() - t) / 8
+    rows = int(max(8, min(H, seconds / per_row)))
+    y0 = (H - rows) // 2
+    t = time.perf_counter()
+    rays = o.render(W, H, rt, 1, rows=(y0, y0 + rows), nthreads=cores)["rays"]
+    dt = time.perf_counter() - t
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores,
+            "kind": "reference" if kind.startswith("reference") else "port",
+            "sample": "%d of %d rows (y %d..%d) of the same %s frame, %d threads, %.1f s; denoise excluded (the "
+                      "reference has none)" % (rows, H, y0, y0 + rows, workload, cores, dt),
+            "frames_per_s_extrapolated": 1.0 / (dt * H / rows)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from optix_renderer_b200 import api, scenes, tiles
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ratio = args.workload == "ratio"
+
+    sc = scenes.scene_synthetic(N_TRIS, N_QUADS, W, H)
+    r = api.Renderer(sc, device=local)
+    stream = torch.cuda.Stream()
+    r.set_stream(stream.cuda_stream)
+    T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
+    out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
+
+    def step(i):
+        if ratio:
+            T.render_ratio_frame(i, mode=api.INTENDED, shadow_spp=SPP)
+        else:
+            T.render_path_frame(i, mode=api.INTENDED, max_depth=DEPTH)
+        T.assemble(out_names)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(x, op):
+        if world == 1:
+            return x
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    with torch.cuda.stream(stream):
+        for i in range(args.warmup):
+            step(i)
+        barrier()
+        r.set_profiling(True)
+        r.stage_times()
+        c0 = r.counters()
+        sampler = ClockSampler(local)
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record(stream)
+        for i in range(args.steps):
+            step(args.warmup + i)
+        ev1.record(stream)
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clocks = sampler.summary()
+        st = r.stage_times()
+        c1 = r.counters()
+        r.set_profiling(False)
+        ms = reduce(ms, dist.ReduceOp.MAX) if world > 1 else ms
+        d = {k: c1[k] - c0[k] for k in ("rays_primary", "rays_shadow_total", "rays_bounce_total", "kernel_launches",
+                                         "active_pixels_total")}
+        rays = reduce(d["rays_primary"] + d["rays_shadow_total"] + d["rays_bounce_total"], dist.ReduceOp.SUM if world > 1 else None)
+        launches = reduce(d["kernel_launches"], dist.ReduceOp.SUM if world > 1 else None)
+        value = rays / (ms * 1e-3) / 1e6
+
+        # ---- end to end through the C-ABI with host buffers: camera in (host), frame out (pinned host) ----
+        cam = sc["camera"]
+        y0, y1 = (0, H)
+        host_f4 = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
+        host_u32 = torch.empty((H, W), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        e_steps = max(3, min(args.steps, 10))
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e_steps):
+            r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
+            step(args.warmup + args.steps + i)
+            if rank == 0:
+                r.download(out_names[0], rows=(y0, y1), out=host_f4)      # D2H, synchronises
+                r.download("rgba8", rows=(y0, y1), out=host_u32)
+        barrier()
+        e_ms = (time.perf_counter() - t0) * 1e3
+        e_ms = reduce(e_ms, dist.ReduceOp.MAX) if world > 1 else e_ms
+        e_value = (rays / args.steps) * e_steps / (e_ms * 1e-3) / 1e6
+
+    if rank == 0:
+        px = W * H // world  # per rank (bands); stage times are rank 0's
+        active = d["active_pixels_total"] / args.steps
+        peak, peak_src = peaks()
+        passes = {}
+        for name, (t_ms, n_launch) in st.items():
+            if n_launch == 0:
+                continue
+            per = t_ms / args.steps
+            b = stage_bytes(name, px, active)
+            passes[name] = {"ms_per_frame": per, "launches_per_frame": n_launch / args.steps, "algorithmic_bytes": b,
+                            "gbs": b / (per * 1e-3) / 1e9 if per > 0 else None,
+                            "frac_of_hbm_peak": b / (per * 1e-3) / 1e9 / peak if per > 0 else None}
+        top = max(passes, key=lambda k: passes[k]["ms_per_frame"])
+        tp = passes[top]
+        n_top = tp["launches_per_frame"]
+        roofline = {"kernel": top, "bound": "hbm", "achieved": tp["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": tp["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                    "avg_launch_ms": tp["ms_per_frame"] / n_top, "algorithmic_bytes_per_launch": tp["algorithmic_bytes"] / n_top,
+                    "share_of_step": tp["ms_per_frame"] / (ms / args.steps),
+                    "note": "ltc (32 TriLights/px) and the two trace stages are issue/latency-bound, not HBM-bound "
+                            "(SURVEY.md 8(d)); their HBM fraction is reported for completeness, see passes"}
+        line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "frames_per_s": args.steps / (ms * 1e-3),
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": workload_config(args, world), "rays_per_frame": rays / args.steps,
+                "e2e": {"value": e_value, "unit": "Mrays/s", "ms_per_step": e_ms / e_steps,
+                        "frames_per_s": e_steps / (e_ms * 1e-3), "h2d_bytes_per_step": 48 + 32,
+                        "d2h_bytes_per_step": W * H * 20, "steps": e_steps,
+                        "what": "orb_set_camera + orb_render_async(+denoise+combine) + orb_buffer_download_rows of the "
+                                "float4 result and the RGBA8 frame into pinned host memory"},
+                "gpu_launches": int(launches), "roofline": roofline, "passes": passes, "clocks": clocks}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_sample(args.workload)
+        print(json.dumps(line))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ratio", choices=["ratio", "path"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -108,8 +108,10 @@ typedef struct OrbRenderConfig {
     int32_t shadow_spp;    /* RATIO: shadow samples per pixel; literal fixes 4 (deviceCode.cu:128) */
     int32_t max_depth;     /* PATH: bounces; literal fixes 1 (deviceCode.cu:151) */
     int32_t y0, y1;        /* rows [y0, y1) rendered by this context (tile partition); 0,0 = all */
-    int32_t reserved[1];
+    int32_t flags;         /* ORB_RENDER_* */
 } OrbRenderConfig;
+#define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
+                                 a tile owner renders redundantly for the denoise filter) */
 
 typedef struct OrbDenoiseConfig {
     int32_t iterations; /* a-trous passes, step 1,2,4,...; default 5 */
@@ -130,7 +132,29 @@ typedef struct OrbCounters {
     uint64_t active_pixels;  /* last frame: non-light hit pixels (length of the active-pixel queue) */
     uint64_t nodes_visited;  /* last orb_trace_rays_host call (instrumented traversal) */
     uint64_t tris_tested;
+    uint64_t rays_shadow_total; /* since orb_create, summed on the device at the end of every frame */
+    uint64_t rays_bounce_total;
+    uint64_t active_pixels_total;
 } OrbCounters;
+
+/* Stages of a frame, for orb_get_stage_times(): one entry per kernel family. */
+typedef enum OrbStage {
+    ORB_STAGE_PRIMARY = 0,      /* camera rays + closest hit + G-buffer write + queue compaction */
+    ORB_STAGE_LTC = 1,          /* LTC area-light sum over the active-pixel queue                */
+    ORB_STAGE_SHADOW = 2,       /* ratio estimator shadow rays                                   */
+    ORB_STAGE_PATH = 3,         /* all bounce kernels of a PATH frame                            */
+    ORB_STAGE_ACCUMULATE = 4,   /* accum += colour, RGBA8                                        */
+    ORB_STAGE_DENOISE_PACK = 5, /* guide / value packing                                         */
+    ORB_STAGE_DENOISE = 6,      /* a-trous iterations                                            */
+    ORB_STAGE_COMBINE = 7,      /* ratio combine                                                 */
+    ORB_STAGE_LTC_GBUFFER = 8,  /* stand-alone LTC pass over a saved G-buffer                    */
+    ORB_STAGE_COUNT = 9
+} OrbStage;
+
+typedef struct OrbStageTimes {
+    double ms[ORB_STAGE_COUNT];        /* summed CUDA-event time of the stage's launches */
+    uint64_t launches[ORB_STAGE_COUNT]; /* kernels launched in the stage                  */
+} OrbStageTimes;
 
 typedef struct OrbContext OrbContext;
 
@@ -143,6 +167,11 @@ void* orb_stream(OrbContext* ctx); /* cudaStream_t the context launches on */
 /* Launch on a caller-owned cudaStream_t instead (e.g. the stream a host framework times with). */
 int orb_set_stream(OrbContext* ctx, void* cuda_stream);
 int orb_sync(OrbContext* ctx);
+/* Per-stage timing with cudaEvents recorded on the context's stream around each stage (off by
+ * default).  orb_get_stage_times() synchronises, returns the sums since the previous call and
+ * resets them.  New in this library (the reference has no timing code at all). */
+int orb_set_profiling(OrbContext* ctx, int enable);
+int orb_get_stage_times(OrbContext* ctx, OrbStageTimes* out);
 
 /* ---- scene ---- replaces owlGeom*, owlTriangles*, owlGroupBuildAccel, viewer.hpp:375-517 */
 int orb_scene_clear(OrbContext* ctx);

@@ -53,7 +53,7 @@ class OrbBvhOptions(C.Structure):
 class OrbRenderConfig(C.Structure):
     _fields_ = [("renderer_type", C.c_int32), ("accum_id", C.c_int32), ("mode", C.c_int32),
                 ("shadow_spp", C.c_int32), ("max_depth", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32),
-                ("reserved", C.c_int32 * 1)]
+                ("flags", C.c_int32)]
 
 
 class OrbDenoiseConfig(C.Structure):
@@ -64,7 +64,15 @@ class OrbDenoiseConfig(C.Structure):
 class OrbCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_shadow", "rays_bounce", "kernel_launches",
                                           "nan_pixels", "bvh_nodes", "bvh_triangles", "bvh_height",
-                                          "active_pixels", "nodes_visited", "tris_tested")]
+                                          "active_pixels", "nodes_visited", "tris_tested",
+                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total")]
+
+
+STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "denoise", "combine", "ltc_gbuffer"]
+
+
+class OrbStageTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 9), ("launches", C.c_uint64 * 9)]
 
 
 _lib = None
@@ -87,6 +95,8 @@ def load_library():
     L.orb_stream.restype = vp
     L.orb_set_stream.argtypes = [vp, vp]
     L.orb_sync.argtypes = [vp]
+    L.orb_set_profiling.argtypes = [vp, C.c_int]
+    L.orb_get_stage_times.argtypes = [vp, C.POINTER(OrbStageTimes)]
     L.orb_scene_clear.argtypes = [vp]
     L.orb_scene_add_mesh.argtypes = [vp, C.POINTER(OrbMeshDesc)]
     L.orb_scene_set_lights.argtypes = [vp, _f, C.c_int32]
@@ -216,15 +226,17 @@ class Renderer:
         self.W, self.H = int(W), int(H)
 
     # ---- launch (Viewer::render, viewer.hpp:553-568) ----
-    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows):
+    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True):
         c = OrbRenderConfig()
+        c.flags = 0 if count_rays else 1  # ORB_RENDER_NO_COUNT
         c.renderer_type, c.accum_id, c.mode = int(renderer_type), int(accum_id), int(mode)
         c.shadow_spp, c.max_depth = int(shadow_spp), int(max_depth)
         c.y0, c.y1 = rows if rows else (0, 0)
         return c
 
-    def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True):
-        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows)
+    def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True,
+               count_rays=True):
+        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays)
         self._ck((self.lib.orb_render if sync else self.lib.orb_render_async)(self._h, C.byref(c)))
 
     def ltc_gbuffer_pass(self, rows=None):
@@ -248,6 +260,15 @@ class Renderer:
 
     def set_stream(self, cuda_stream):
         self._ck(self.lib.orb_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def set_profiling(self, enable=True):
+        self._ck(self.lib.orb_set_profiling(self._h, int(enable)))
+
+    def stage_times(self):
+        """{stage: (summed ms, kernel launches)} since the previous call (synchronises)."""
+        t = OrbStageTimes()
+        self._ck(self.lib.orb_get_stage_times(self._h, C.byref(t)))
+        return {n: (t.ms[i], int(t.launches[i])) for i, n in enumerate(STAGES)}
 
     # ---- buffers (savebuffer, viewer.hpp:695-713) ----
     def device_ptr(self, name):

@@ -61,7 +61,10 @@ struct DevCounters {
     unsigned nan_pixels;
     unsigned long long rays_shadow, rays_bounce;
     unsigned long long nodes_visited, tris_tested;  // filled by the instrumented trace only
+    // ---- everything above is cleared at the start of a frame; the totals below are not ----
+    unsigned long long tot_shadow, tot_bounce, tot_active;
 };
+#define DEVCOUNTERS_FRAME_BYTES offsetof(DevCounters, tot_shadow)
 
 struct FrameView {
     int W, H, y0, y1;
@@ -317,7 +320,12 @@ __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
 // ---------------------------------------------------------------------------------------------
 // k_accumulate: deviceCode.cu:158-161,172-174
 // ---------------------------------------------------------------------------------------------
-__global__ void k_accumulate(FrameView f, const float4* __restrict__ src, int accum_id) {
+__global__ void k_accumulate(FrameView f, const float4* __restrict__ src, int accum_id, int count_rays) {
+    if (count_rays && blockIdx.x == 0 && threadIdx.x == 0) {  // every earlier kernel of the frame has finished
+        f.cnt->tot_shadow += f.cnt->rays_shadow;
+        f.cnt->tot_bounce += f.cnt->rays_bounce;
+        f.cnt->tot_active += f.cnt->queue_n;
+    }
     const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
     const float scale = 1.f / ((float)accum_id + 1.f);
     unsigned nan = 0;
@@ -587,6 +595,35 @@ struct OrbContext {
     bool have_cam = false;
     OrbCounters counters;
     int last_spp = 0;
+    // per-stage timing (orb_set_profiling)
+    bool profiling = false;
+    struct StageSpan { int stage; int launches; cudaEvent_t e0, e1; };
+    std::vector<StageSpan> spans;          // recorded since the last orb_get_stage_times
+    std::vector<cudaEvent_t> free_events;  // recycled
+};
+
+// RAII span: records an event pair around the launches of one stage when profiling is on
+struct StageTimer {
+    OrbContext* c;
+    OrbContext::StageSpan sp;
+    bool on;
+    static cudaEvent_t get(OrbContext* c) {
+        cudaEvent_t e = nullptr;
+        if (!c->free_events.empty()) { e = c->free_events.back(); c->free_events.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
+    StageTimer(OrbContext* ctx, int stage, int launches) : c(ctx), on(ctx->profiling) {
+        if (!on) return;
+        sp.stage = stage; sp.launches = launches;
+        sp.e0 = get(c); sp.e1 = get(c);
+        cudaEventRecord(sp.e0, c->stream);
+    }
+    ~StageTimer() {
+        if (!on) return;
+        cudaEventRecord(sp.e1, c->stream);
+        c->spans.push_back(sp);
+    }
 };
 
 static size_t buffer_elem_bytes(int id) { return id == ORB_BUF_RGBA8 ? 4 : 16; }
@@ -702,6 +739,8 @@ void orb_destroy(OrbContext* c) {
     cudaStreamSynchronize(c->stream);
     free_scene(c);
     free_frame(c);
+    for (auto& sp : c->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
+    for (auto e : c->free_events) cudaEventDestroy(e);
     cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->cnt); cudaFree(c->unit_in); cudaFree(c->unit_out);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -723,6 +762,29 @@ int orb_sync(OrbContext* c) {
     NEED(c, "orb_sync: ctx is NULL");
     CK(cudaSetDevice(c->device));
     CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_set_profiling(OrbContext* c, int enable) {
+    NEED(c, "orb_set_profiling: ctx is NULL");
+    c->profiling = enable != 0;
+    return ORB_OK;
+}
+
+int orb_get_stage_times(OrbContext* c, OrbStageTimes* out) {
+    NEED(c && out, "orb_get_stage_times: NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    memset(out, 0, sizeof(*out));
+    for (auto& sp : c->spans) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, sp.e0, sp.e1));
+        out->ms[sp.stage] += (double)ms;
+        out->launches[sp.stage] += (uint64_t)sp.launches;
+        c->free_events.push_back(sp.e0);
+        c->free_events.push_back(sp.e1);
+    }
+    c->spans.clear();
     return ORB_OK;
 }
 
@@ -925,15 +987,18 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     FrameView f = frame_view(c, y0, y1);
     const int frame_id = cfg->accum_id + 10007;  // deviceCode.cu:65
     const size_t smem = trace_smem(c);
-    CK(cudaMemsetAsync(c->cnt, 0, sizeof(DevCounters), st));
+    const int count_rays = (cfg->flags & ORB_RENDER_NO_COUNT) ? 0 : 1;
+    CK(cudaMemsetAsync(c->cnt, 0, DEVCOUNTERS_FRAME_BYTES, st));
     {
+        StageTimer tm(c, ORB_STAGE_PRIMARY, 1);
         dim3 grid((c->W + 15) / 16, (y1 - y0 + 7) / 8);
         k_primary<<<grid, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
         c->counters.kernel_launches++;
-        c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
+        if (count_rays) c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
     }
     const float4* colour_src = c->colour;
     if (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) {
+        StageTimer tm(c, ORB_STAGE_LTC, 1);
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
         if (renderer == ORB_RATIO) {
             // light pixels already hold emit in `ltc` (k_primary), so `ltc` IS the frame colour
@@ -945,6 +1010,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         c->counters.kernel_launches++;
     }
     if (renderer == ORB_RATIO) {
+        StageTimer tm(c, ORB_STAGE_SHADOW, 1);
         const int g = persistent_grid(c, k_ratio_shadow, TRACE_BLOCK, smem);
         k_ratio_shadow<<<g, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->height);
         c->counters.kernel_launches++;
@@ -953,6 +1019,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     if (renderer == ORB_PATH) {
         int rc = ensure_path_state(c);
         if (rc) return rc;
+        StageTimer tm(c, ORB_STAGE_PATH, 2 * depth - 1);
         PathBuffers pb[2];
         for (int a = 0; a < 2; a++)
             for (int b = 0; b < 5; b++) pb[a].s[b] = c->path_state[a][b];
@@ -974,9 +1041,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
     }
     {
+        StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
         const size_t n = (size_t)(y1 - y0) * c->W;
         const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
-        k_accumulate<<<g, 256, 0, st>>>(f, colour_src, cfg->accum_id);
+        k_accumulate<<<g, 256, 0, st>>>(f, colour_src, cfg->accum_id, count_rays);
         c->counters.kernel_launches++;
     }
     CK(cudaGetLastError());
@@ -999,7 +1067,10 @@ int orb_ltc_gbuffer_pass(OrbContext* c, int32_t y0, int32_t y1) {
     refresh_view(c);
     FrameView f = frame_view(c, y0, y1);
     const int g = persistent_grid(c, k_ltc<false>, LTC_BLOCK, 0);
-    k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+    {
+        StageTimer tm(c, ORB_STAGE_LTC_GBUFFER, 1);
+        k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+    }
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
     return ORB_OK;
@@ -1020,14 +1091,22 @@ int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t 
         CK(cudaMalloc(&c->dn_val[0], n * 8));
         CK(cudaMalloc(&c->dn_val[1], n * 8));
     }
-    // The filter reads up to 2 * 2^(iters-1) rows beyond the band, so the pack covers the whole frame
-    // (rows outside the band must hold valid G-buffer / sto data, e.g. rendered as a halo).
-    FrameView all = frame_view(c, 0, c->H);
+    // Pass `it` (step 2^it) reads 2 * 2^it rows either side of the rows it writes, so for the band
+    // [y0, y1) pass `it` must write [y0 - R, y1 + R) with R = sum of 2 * 2^j over the LATER passes
+    // j > it, and the pack covers R of pass -1 = 2 * (2^iters - 1) rows (rows outside the band must
+    // hold valid G-buffer / sto data, e.g. rendered as a halo by the tile's owner).
+    auto reach = [&](int it) { return 2 * ((1 << d.iterations) - (1 << (it + 1))); };
+    const int p0 = std::max(0, y0 - reach(-1)), p1 = std::min(c->H, y1 + reach(-1));
+    FrameView all = frame_view(c, p0, p1);
     FrameView f = frame_view(c, y0, y1);
-    const int gp = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
-    k_denoise_pack<<<gp, 256, 0, c->stream>>>(all, c->cam.pos, c->dn_guide, c->dn_val[0]);
+    const size_t np = (size_t)(p1 - p0) * c->W;
+    const int gp = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
+    {
+        StageTimer tm(c, ORB_STAGE_DENOISE_PACK, 1);
+        k_denoise_pack<<<gp, 256, 0, c->stream>>>(all, c->cam.pos, c->dn_guide, c->dn_val[0]);
+    }
     c->counters.kernel_launches++;
-    dim3 grid((c->W + 31) / 32, (c->H + 7) / 8);
+    StageTimer tm_dn(c, ORB_STAGE_DENOISE, d.iterations);
     int cur = 0;
     for (int it = 0; it < d.iterations; it++) {
         const int step = 1 << it;
@@ -1040,7 +1119,9 @@ int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t 
                                                                (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN], step,
                                                                d.sigma_normal, isp, isc);
         } else {
-            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(all, c->dn_guide, c->dn_val[cur], c->dn_val[cur ^ 1],
+            FrameView part = frame_view(c, std::max(0, y0 - reach(it)), std::min(c->H, y1 + reach(it)));
+            dim3 grid((c->W + 31) / 32, (part.y1 - part.y0 + 7) / 8);
+            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(part, c->dn_guide, c->dn_val[cur], c->dn_val[cur ^ 1],
                                                                   nullptr, nullptr, step, d.sigma_normal, isp, isc);
             cur ^= 1;
         }
@@ -1056,6 +1137,7 @@ int orb_ratio_combine(OrbContext* c, int32_t use_denoised, int32_t y0, int32_t y
     CK(cudaSetDevice(c->device));
     const size_t first = (size_t)y0 * c->W, n = (size_t)(y1 - y0) * c->W;
     const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
+    StageTimer tm(c, ORB_STAGE_COMBINE, 1);
     k_ratio_combine<<<g, 256, 0, c->stream>>>(
         (const float4*)c->buf[ORB_BUF_LTC],
         (const float4*)c->buf[use_denoised ? ORB_BUF_STO_DIRECT_DN : ORB_BUF_STO_DIRECT],
@@ -1119,6 +1201,9 @@ int orb_get_counters(OrbContext* c, OrbCounters* out) {
     out->nodes_visited = d.nodes_visited;
     out->tris_tested = d.tris_tested;
     out->bvh_height = (uint64_t)c->bvh.height;
+    out->rays_shadow_total = d.tot_shadow;
+    out->rays_bounce_total = d.tot_bounce;
+    out->active_pixels_total = d.tot_active;
     return ORB_OK;
 }
 
@@ -1154,7 +1239,7 @@ int orb_trace_rays_host(OrbContext* c, const float* origin, const float* directi
     CK(cudaMalloc(&d_o, 12 * n)); CK(cudaMalloc(&d_d, 12 * n)); CK(cudaMalloc(&d_t, 12 * n)); CK(cudaMalloc(&d_p, 4 * n));
     CK(cudaMemcpyAsync(d_o, origin, 12 * n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(d_d, direction, 12 * n, cudaMemcpyHostToDevice, c->stream));
-    CK(cudaMemsetAsync(c->cnt, 0, sizeof(DevCounters), c->stream));
+    CK(cudaMemsetAsync(c->cnt, 0, DEVCOUNTERS_FRAME_BYTES, c->stream));
     const int g = (int)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
     k_trace_rays<<<g, TRACE_BLOCK, trace_smem(c), c->stream>>>(c->view, d_o, d_d, n, brute, d_p, d_t, d_t + n, d_t + 2 * n,
                                                                c->height, c->cnt);

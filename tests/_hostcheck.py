@@ -128,3 +128,64 @@ class HostCheck:
         c = f32(cam_pos)
         self.lib.hc_ltc_gbuffer(position.size // 4, _fp(position), _fp(normal), _fp(albedo), _fp(alpha), _fp(c), _fp(out))
         return out
+
+    # ---- unit wrappers: same names / meaning as optix_renderer_b200.api.Renderer.u_* ----
+    def u_rng(self, frame, px, py, W, n):
+        s = np.zeros(1, np.uint32)
+        raw, flt = np.zeros(n, np.uint32), np.zeros(n, np.float32)
+        self.lib.hc_u_rng(frame, px, py, W, n, s.ctypes.data_as(_u), raw.ctypes.data_as(_u), _fp(flt))
+        return int(s[0]), raw, flt
+
+    def u_rng_skip(self, frame, px, py, W, n):
+        return int(self.lib.hc_u_rng_skip(frame, px, py, W, n))
+
+    def u_clip(self, abc, quad=False):
+        a = f32(abc).reshape(9)
+        n = np.zeros(1, np.int32)
+        ff = self.lib.hc_u_clip(_fp(a), int(quad), n.ctypes.data_as(_i))
+        return int(n[0]), float(ff)
+
+    def u_integrate_edge(self, a, b):
+        a, b = f32(a), f32(b)
+        return float(self.lib.hc_u_integrate_edge(_fp(a), _fp(b)))
+
+    def u_fetch_ltc(self, alpha, theta):
+        o = np.zeros(10, np.float32)
+        self.lib.hc_u_fetch_ltc(alpha, theta, _fp(o))
+        return o[:9].reshape(3, 3).copy(), float(o[9])
+
+    def u_mat_inverse(self, m):
+        m, o = f32(m).reshape(9), np.zeros(9, np.float32)
+        self.lib.hc_u_mat_inverse(_fp(m), _fp(o))
+        return o.reshape(3, 3)
+
+    def u_onb(self, n):
+        n, o = f32(n), np.zeros(9, np.float32)
+        self.lib.hc_u_onb(_fp(n), _fp(o))
+        return o.reshape(3, 3)
+
+    def u_sample_direction(self, wo, u1, u2, base, alpha):
+        wo, base, o = f32(wo), f32(base), np.zeros(4, np.float32)
+        self.lib.hc_u_sample_direction(_fp(wo), u1, u2, _fp(base), alpha, _fp(o))
+        return o[:3].copy(), float(o[3])
+
+    def u_evaluate(self, wi, wo, base, alpha):
+        wi, wo, base, o = f32(wi), f32(wo), f32(base), np.zeros(3, np.float32)
+        self.lib.hc_u_evaluate(_fp(wi), _fp(wo), _fp(base), alpha, _fp(o))
+        return o
+
+    def u_pdf(self, wi, wo, base, alpha):
+        wi, wo, base = f32(wi), f32(wo), f32(base)
+        return float(self.lib.hc_u_pdf(_fp(wi), _fp(wo), _fp(base), alpha))
+
+    def u_make_rgba(self, c):
+        c = f32(c)
+        return int(self.lib.hc_u_make_rgba(_fp(c)))
+
+    def u_sample_tri(self, v9, u1, u2):
+        v, o = f32(v9).reshape(9), np.zeros(3, np.float32)
+        self.lib.hc_u_sample_tri(_fp(v), u1, u2, _fp(o))
+        return o
+
+    def u_pdf_a2w(self, pdf, d2, c):
+        return float(self.lib.hc_u_pdf_a2w(pdf, d2, c))

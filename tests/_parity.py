@@ -1,0 +1,110 @@
+"""Shared parity checks: the same assertions run against the product's device headers compiled
+for the host (tests/test_hostcheck.py, CPU) and against the CUDA kernels through the C-ABI
+(tests/test_gpu_*.py).  `dut` = device under test with the u_* / render interface of
+optix_renderer_b200.api.Renderer; golden = tests/golden/units.npz (from the reference source).
+
+Tolerances (written here once):
+  integer / index / RNG work ............ bit-exact
+  single fp32 device functions .......... <= 4 ulp-ish (rtol 5e-7 + tiny atol): CUDA libdevice
+                                          sqrt/div are IEEE, sinf/cosf/acosf differ from glibc
+                                          by <= 2 ulp, and nvcc contracts a*b+c into fma
+  LTC radiance per pixel ................ <= 1e-4 relative (BASELINE.json north_star)
+  stochastic images ..................... RMSE <= 1e-3 (north_star)
+"""
+import os
+
+import numpy as np
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RT = 2e-6
+AT = 2e-7
+
+
+def units():
+    return np.load(os.path.join(G, "units.npz"))
+
+
+def close(a, b, rtol=RT, atol=AT):
+    np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=rtol, atol=atol)
+
+
+def check_rng(dut, u):
+    for c, s, raw, flt in zip(u["rng_cases"], u["rng_state"], u["rng_raw"], u["rng_flt"]):
+        fr, px, py, W, _ = [int(x) for x in c]
+        s2, r2, f2 = dut.u_rng(fr, px, py, W, 8)
+        assert s2 == s and np.array_equal(r2, raw) and np.array_equal(f2, flt)  # bit-exact
+
+
+def oracle_polygon_sum(ora, v, n):
+    if n < 3:
+        return 0.0
+    s = np.float32(0)
+    for i in range(n):
+        s = np.float32(s + np.float32(ora.u_integrate_edge(v[i], v[(i + 1) % n])))
+    return float(abs(s))
+
+
+def check_clip(dut, ora, u):
+    """clipPolygon + the closed edge sum (product API returns the clipped form factor)."""
+    flips = 0
+    for v, vc, n, out in zip(u["clip_in"], u["clip_vc"], u["clip_n"], u["clip_out"]):
+        if vc != 3:
+            continue  # a first clip always starts from a triangle light
+        n2, ff = dut.u_clip(v[:3].reshape(9), quad=False)
+        if min(abs(v[:3, 2])) < 1e-6:
+            flips += n2 != n
+            continue
+        assert n2 == n
+        close(ff, oracle_polygon_sum(ora, out, int(n)), rtol=2e-5, atol=2e-6)
+    assert flips == 0
+
+
+def check_scalar_units(dut, u):
+    for a, r in zip(u["edge_in"], u["edge_out"]):
+        close(dut.u_integrate_edge(a[0], a[1]), r, rtol=5e-6, atol=5e-7)
+    for (al, th), m, amp, inv in zip(u["fetch_in"], u["fetch_m"], u["fetch_amp"], u["minv"]):
+        m2, a2 = dut.u_fetch_ltc(float(al), float(th))
+        close(m2, m, rtol=5e-6, atol=1e-6)
+        close(a2, amp, rtol=5e-6)
+        close(dut.u_mat_inverse(m), inv, rtol=1e-5, atol=1e-6)
+    for n, r in zip(u["onb_in"], u["onb_out"]):
+        close(dut.u_onb(n), r)
+    for t, uu, r in zip(u["tri_in"], u["tri_u"], u["tri_out"]):
+        close(dut.u_sample_tri(t.reshape(9), float(uu[0]), float(uu[1])), r, rtol=1e-6, atol=1e-6)
+    for p, r in zip(u["a2w_in"], u["a2w_out"]):
+        close(dut.u_pdf_a2w(float(p[0]), float(p[1]), float(p[2])), r)
+    for c, r in zip(u["rgba_in"], u["rgba_out"]):
+        assert dut.u_make_rgba(c) == r  # bit-exact
+
+
+def check_bsdf(dut, u):
+    for i in range(len(u["bsdf_alpha"])):
+        wo, uu, b, al = u["bsdf_wo"][i], u["bsdf_u"][i], u["bsdf_base"][i], float(u["bsdf_alpha"][i])
+        wi, p = dut.u_sample_direction(wo, float(uu[0]), float(uu[1]), b, al)
+        close(wi, u["bsdf_wi"][i], rtol=1e-5, atol=1e-6)
+        close(p, u["bsdf_pdf"][i], rtol=2e-5, atol=1e-7)
+        close(dut.u_evaluate(u["bsdf_wi"][i], wo, b, al), u["bsdf_eval"][i], rtol=1e-5)
+        close(dut.u_pdf(u["bsdf_wi"][i], wo, b, al), u["bsdf_pdf2"][i], rtol=2e-5, atol=1e-7)
+
+
+def rel_err(got, ref, floor=1e-3):
+    """per-pixel max relative error over rgb, |ref| floored (dark pixels are judged absolutely)."""
+    got, ref = np.asarray(got, np.float64)[..., :3], np.asarray(ref, np.float64)[..., :3]
+    return (np.abs(got - ref) / np.maximum(np.abs(ref), floor)).max(axis=-1)
+
+
+def frame_report(got, ref, hit_got, hit_ref):
+    """Parity summary of one frame against the oracle (north_star's reporting rules):
+    hit-id mismatches are counted; radiance compared on pixels whose primary hit agrees."""
+    same = hit_got == hit_ref
+    out = {"pixels": int(same.size), "hit_mismatch": int((~same).sum())}
+    for k in got:
+        g, r = got[k], ref[k]
+        nan_g, nan_r = np.isnan(g[..., :3]).any(-1), np.isnan(r[..., :3]).any(-1)
+        m = same & ~nan_g & ~nan_r
+        e = rel_err(g[m], r[m]) if m.any() else np.zeros(1)
+        d = (np.asarray(g[m], np.float64)[..., :3] - np.asarray(r[m], np.float64)[..., :3])
+        out[k] = {"max_rel": float(e.max()), "frac_le_1e-4": float((e <= 1e-4).mean()),
+                  "rmse": float(np.sqrt((d * d).mean())) if d.size else 0.0,
+                  "nan_mismatch": int((nan_g != nan_r)[same].sum()), "nan_ref": int(nan_r.sum())}
+    return out

@@ -1,0 +1,276 @@
+"""GPU: whole frames of the CUDA wavefront path through the C-ABI against the oracle (the
+reference's own device source compiled for the CPU when oracle/_ref is present, else the
+restatement pinned to it), plus size-independent properties at full BASELINE sizes.
+
+Tolerances: hit primitive ids exact except ties (counted); G-buffers 1e-5 relative; LTC radiance
+<= 1e-4 relative on >= 99.9 % of pixels (case-flip pixels counted); stochastic
+images RMSE <= 1e-3; integer outputs (ray counts, queue lengths) exact."""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle
+import _parity as P
+from conftest import best_oracle
+from optix_renderer_b200 import api, scenes
+
+pytestmark = pytest.mark.gpu
+
+BUFS = ("position", "normal", "uv", "albedo", "alpha", "materialID", "ltc", "sto_direct", "sto_no_vis", "accum")
+
+
+def gpu_frame(r, rt, accum_id=0, mode=0, spp=4, depth=1, rows=None):
+    r.render(rt, accum_id=accum_id, mode=mode, shadow_spp=spp, max_depth=depth, rows=rows)
+    out = {k: r.download(k) for k in BUFS}
+    out["rgba8"] = r.download("rgba8")
+    out["hit_prim"], out["hit_uv"], _ = r.hit_records()
+    out["counters"] = r.counters()
+    return out
+
+
+def check_frame(got, ref, rt, strict_hits=True):
+    rep = P.frame_report({k: got[k] for k in BUFS}, ref, got["hit_prim"], ref["hit_prim"])
+    n = rep["pixels"]
+    assert rep["hit_mismatch"] <= (0 if strict_hits else max(2, n // 2000)), rep["hit_mismatch"]
+    for k in ("position", "normal", "uv", "albedo", "alpha", "materialID"):
+        assert rep[k]["max_rel"] <= 1e-5, (k, rep[k])
+    if rt in (_oracle.LTC_BASELINE, _oracle.RATIO):
+        k = "accum" if rt == _oracle.LTC_BASELINE else "ltc"
+        assert rep[k]["frac_le_1e-4"] >= 0.999, (k, rep[k])
+        assert rep[k]["nan_mismatch"] <= max(1, n // 5000)
+    if rt == _oracle.RATIO:
+        for k in ("sto_direct", "sto_no_vis"):
+            assert rep[k]["rmse"] <= 1e-3, (k, rep[k])
+            assert rep[k]["nan_mismatch"] <= max(1, n // 5000)
+    if rt == _oracle.PATH:
+        assert rep["accum"]["rmse"] <= 1e-3, rep["accum"]
+        assert rep["accum"]["nan_mismatch"] <= max(2, n // 1000)
+    return rep
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("scene_fn,W,H", [(scenes.scene_floor_blocker, 64, 64), (scenes.scene_cornell, 96, 80)])
+def test_frames_vs_oracle(renderer_factory, scene_fn, W, H, mode):
+    sc = scene_fn(W, H)
+    r = renderer_factory(sc)
+    o = best_oracle(mode)
+    o.load_scene(sc)
+    depth = 8 if mode else 1
+    assert o.set_options(mode, 4, depth) == 0
+    for rt in (_oracle.LTC_BASELINE, _oracle.RATIO, _oracle.PATH):
+        ref = o.render(W, H, rt, 0, nthreads=8)
+        got = gpu_frame(r, rt, 0, mode, 4, depth)
+        check_frame(got, ref, rt)
+        c = got["counters"]
+        assert c["rays_primary"] > 0
+        assert W * H + c["rays_shadow"] + c["rays_bounce"] == ref["rays"]   # device-counted rays, exact
+
+
+def test_debug_aov_modes(renderer_factory):
+    sc = scenes.scene_floor_blocker(48, 48)
+    r = renderer_factory(sc)
+    o = best_oracle(0)
+    o.load_scene(sc)
+    for rt in range(7):
+        ref = o.render(48, 48, rt, 0)
+        got = gpu_frame(r, rt)
+        assert P.rel_err(got["accum"], ref["accum"]).max() <= 1e-5
+        assert (got["rgba8"] != ref["rgba8"]).mean() < 0.01
+
+
+def test_golden_frames(renderer_factory):
+    """The committed fixtures (reference source output), no oracle library involved."""
+    g = np.load(os.path.join(P.G, "frames_floor32.npz"))
+    r = renderer_factory(scenes.scene_floor_blocker(32, 32))
+    for mode in (0, 1):
+        for rt, name in ((_oracle.LTC_BASELINE, "ltc"), (_oracle.RATIO, "ratio"), (_oracle.PATH, "path")):
+            pre = "%s_m%d_a0_" % (name, mode)
+            ref = {k: g[pre + k] for k in BUFS + ("hit_prim",)}
+            got = gpu_frame(r, rt, 0, mode, 4, 4 if mode else 1)
+            check_frame(got, ref, rt)
+            r.render(rt, accum_id=1, mode=mode, shadow_spp=4, max_depth=4 if mode else 1)
+            acc = r.download("accum")
+            ref1 = g["%s_m%d_a1_accum" % (name, mode)]
+            m = np.isfinite(acc) & np.isfinite(ref1)
+            assert np.sqrt(np.mean((acc[m] - ref1[m]) ** 2)) <= 1e-3
+            assert P.rel_err(acc, ref1)[np.isfinite(ref1).all(-1) & np.isfinite(acc).all(-1)].mean() < 1e-4
+
+
+def test_progressive_accumulation_and_rgba8(renderer_factory):
+    sc = scenes.scene_cornell(64, 64)
+    r = renderer_factory(sc)
+    o = best_oracle(1)
+    o.load_scene(sc)
+    o.set_options(1, 4, 5)
+    acc = None
+    for i in range(4):
+        ref = o.render(64, 64, _oracle.PATH, i, accum=acc, nthreads=8)
+        acc = ref["accum"]
+        r.render(api.PATH, accum_id=i, mode=1, max_depth=5)
+    got = r.download("accum")
+    m = np.isfinite(got).all(-1) & np.isfinite(acc).all(-1)
+    assert (np.isnan(got).any(-1) != np.isnan(acc).any(-1)).sum() <= 4
+    assert np.sqrt(np.mean((got[m] - acc[m]) ** 2)) <= 1e-3
+    assert (r.download("rgba8")[m] != ref["rgba8"][m]).mean() < 0.02
+
+
+def test_row_tiles_are_bit_identical_to_full_frame(renderer_factory):
+    """8(e): pixels do not depend on the partition (RNG keyed by global pixel and dims)."""
+    sc = scenes.scene_cornell(64, 48)
+    r = renderer_factory(sc)
+    full = gpu_frame(r, api.RATIO, 2, 1, 4, 1)
+    r2 = renderer_factory(sc)
+    for rows in ((0, 13), (13, 32), (32, 48)):
+        r2.render(api.RATIO, accum_id=2, mode=1, shadow_spp=4, rows=rows)
+    for k in ("ltc", "sto_direct", "sto_no_vis", "position", "accum"):
+        a, b = full[k], r2.download(k)
+        assert np.array_equal(a, b, equal_nan=True), k
+    r3 = renderer_factory(sc)
+    r3.render(api.PATH, accum_id=0, mode=1, max_depth=6)
+    a = r3.download("accum")
+    for rows in ((0, 20), (20, 48)):
+        r2.render(api.PATH, accum_id=0, mode=1, max_depth=6, rows=rows)
+    assert np.array_equal(a, r2.download("accum"), equal_nan=True)
+
+
+def test_trace_hit_ids_bvh_vs_brute_force_and_oracle(renderer_factory):
+    sc = scenes.scene_synthetic(n_tris=20000, n_quad_lights=4, width=32, height=32)
+    r = renderer_factory(sc)
+    rng = np.random.default_rng(11)
+    n = 20000
+    org = (rng.uniform(-1, 1, (n, 3)) * 3).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) + 0.3
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    p1, t1, u1, v1 = r.trace_rays(org, d, brute_force=False)
+    p2, t2, u2, v2 = r.trace_rays(org, d, brute_force=True)
+    assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
+    c = r.counters()
+    assert 0 < c["tris_tested"] < 0.05 * n * c["bvh_triangles"]      # the BVH actually prunes
+    # against the oracle's stand-in closest hit through a rendered frame
+    o = best_oracle(0)
+    o.load_scene(sc)
+    ref = o.render(32, 32, _oracle.NORMALS, 0, nthreads=8)
+    got = gpu_frame(r, api.NORMALS)
+    ties = int((got["hit_prim"] != ref["hit_prim"]).sum())
+    assert ties <= 2, ties
+
+
+def test_ltc_gbuffer_pass_and_ratio_combine(renderer_factory):
+    """BASELINE config 1 shape: saved G-buffer in, LTC pass + ratio arithmetic out."""
+    g = np.load(os.path.join(P.G, "gbuffer48.npz"))
+    sc = scenes.scene_floor_blocker(48, 48)
+    r = renderer_factory(sc)
+    for k in ("position", "normal", "albedo", "alpha"):
+        r.upload(k, g[k])
+    r.ltc_gbuffer_pass()
+    out = r.download("ltc")
+    e = P.rel_err(out, g["ltc_gbuffer"])
+    assert (e <= 1e-4).mean() >= 0.999 and np.array_equal(out[..., 3], np.ones((48, 48), np.float32))
+    r.upload("ltc", g["ltc_frame"])
+    r.upload("sto_direct", g["sto_direct"])
+    r.upload("sto_no_vis", g["sto_no_vis"])
+    r.ratio_combine(use_denoised=False)
+    with np.errstate(all="ignore"):
+        want = g["ltc_frame"][..., :3] * (g["sto_direct"][..., :3] / g["sto_no_vis"][..., :3])
+    got = r.download("ratio_final")[..., :3]
+    assert np.array_equal(got, want, equal_nan=True)        # IEEE mul/div: bit-exact
+    # host-buffer entry point, ragged length (not a multiple of 4), zeros -> inf/nan like numpy
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 3, 4, 1001, 48 * 48 * 3):
+        a, b, c = (rng.uniform(0, 2, n).astype(np.float32) for _ in range(3))
+        if n > 10:
+            c[::7] = 0
+            b[::14] = 0
+        with np.errstate(all="ignore"):
+            want = a * (b / c)
+        assert np.array_equal(r.ratio_estimator_host(a, b, c), want, equal_nan=True)
+
+
+def test_denoise_vs_definition(renderer_factory, restatement):
+    sc = scenes.scene_cornell(96, 64)
+    r = renderer_factory(sc)
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    f = {k: r.download(k) for k in ("normal", "position", "materialID", "sto_direct", "sto_no_vis")}
+    for iters, sc_ in ((1, 0.0), (5, 0.0), (3, 0.5)):
+        r.denoise(iterations=iters, sigma_colour=sc_)
+        gd, gn = r.download("sto_direct_dn"), r.download("sto_no_vis_dn")
+        od, on = restatement.denoise(f["normal"], f["position"], f["materialID"], f["sto_direct"], f["sto_no_vis"],
+                                     sc["camera"]["pos"], iterations=iters, sigma_colour=sc_, nthreads=8)
+        for a, b in ((gd, od), (gn, on)):
+            m = np.isfinite(a) & np.isfinite(b)
+            assert (np.isnan(a) != np.isnan(b)).sum() == 0
+            np.testing.assert_allclose(a[m], b[m], rtol=2e-4, atol=1e-6)
+    r.ratio_combine(use_denoised=True)
+    with np.errstate(all="ignore"):
+        want = r.download("ltc")[..., :3] * (gd[..., :3] / gn[..., :3])
+    assert np.array_equal(r.download("ratio_final")[..., :3], want, equal_nan=True)
+
+
+def test_edge_cases(renderer_factory):
+    # a scene with no surface hit at all: every pixel is a miss
+    sc = scenes.scene_floor_blocker(16, 16)
+    cam = scenes.camera_from_lookat((0, 0, 50), (0, 0, 100), (0, 1, 0), 0.66, 16, 16)
+    sc2 = dict(sc, camera=cam)
+    r = renderer_factory(sc2)
+    for rt in (api.LTC_BASELINE, api.RATIO, api.PATH):
+        r.render(rt, mode=1, max_depth=4)
+        assert not r.download("accum")[..., :3].any()
+        assert np.array_equal(r.download("position")[..., 3], np.ones((16, 16), np.float32))
+        c = r.counters()
+        assert c["active_pixels"] == 0 and c["rays_shadow"] == 0 and c["rays_bounce"] == 0
+    # 1x1 frame and a non-multiple-of-tile frame
+    for W, H in ((1, 1), (17, 9)):
+        scx = scenes.scene_floor_blocker(W, H)
+        rr = renderer_factory(scx)
+        o = best_oracle(1)
+        o.load_scene(scx)
+        o.set_options(1, 4, 3)
+        ref = o.render(W, H, _oracle.RATIO, 0)
+        got = gpu_frame(rr, api.RATIO, 0, 1, 4, 3)
+        check_frame(got, ref, _oracle.RATIO)
+    # error behaviour: bad arguments return status codes with a message, never crash
+    with pytest.raises(api.OrbError):
+        r.render(api.RATIO, rows=(5, 3))
+    with pytest.raises(api.OrbError):
+        r.render(api.RATIO, mode=7)
+    with pytest.raises(api.OrbError):
+        api.Renderer().render(api.RATIO)
+
+
+def test_full_size_properties(renderer_factory):
+    """BASELINE config 3 size (1920x1080, ~1M triangles, 16 quad lights): properties that need
+    no oracle -- exact ray accounting, idempotence, tile independence, finite LTC."""
+    sc = scenes.scene_synthetic(n_tris=1_000_000, n_quad_lights=16, width=1920, height=1080)
+    r = renderer_factory(sc)
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    c = r.counters()
+    assert c["rays_primary"] == 1920 * 1080
+    assert c["rays_shadow"] == 4 * c["active_pixels"]
+    assert c["bvh_triangles"] == scenes.n_triangles(sc)
+    ltc = r.download("ltc")
+    band = r.download("ltc", rows=(500, 540))
+    sd = r.download("sto_direct", rows=(500, 540))
+    sn = r.download("sto_no_vis", rows=(500, 540))
+    fin = np.isfinite(sd[..., 0]) & np.isfinite(sn[..., 0])
+    hit = r.download("materialID", rows=(500, 540))[..., 0] != 0
+    assert (sd[..., 0][fin & hit] <= sn[..., 0][fin & hit] * (1 + 1e-5) + 1e-7).all()    # shadowed <= unshadowed
+    assert np.isfinite(ltc[..., :3]).mean() > 0.999
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)                      # idempotent
+    assert np.array_equal(ltc, r.download("ltc"), equal_nan=True)
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4, rows=(500, 540))     # tile == full
+    assert np.array_equal(band, r.download("ltc", rows=(500, 540)), equal_nan=True)
+    assert np.array_equal(sd, r.download("sto_direct", rows=(500, 540)), equal_nan=True)
+    # hit ids of the BVH against brute force on a sample of camera rays
+    prim, _, _ = r.hit_records()
+    ys, xs = np.random.default_rng(1).integers(0, 1080, 300), np.random.default_rng(2).integers(0, 1920, 300)
+    pos = r.download("position")
+    cam = np.asarray(sc["camera"]["pos"], np.float32)
+    m = prim[ys, xs] >= 0
+    d = pos[ys, xs, :3][m] - cam
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    o = np.repeat(cam[None], d.shape[0], 0)
+    p1, t1, _, _ = r.trace_rays(o, d, brute_force=False)
+    p2, t2, _, _ = r.trace_rays(o, d, brute_force=True)
+    assert np.array_equal(p1, p2) and np.array_equal(t1, t2)

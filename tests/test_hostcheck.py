@@ -1,0 +1,101 @@
+"""CPU: the product's own __host__ __device__ headers (optix_renderer_b200/csrc/*.cuh), compiled
+with g++ by tests/hostcheck, against the oracle.  This is NOT the product path (that is the
+CUDA library, tested under -m gpu); it lets the arithmetic be checked where there is no GPU."""
+import numpy as np
+import pytest
+
+import _oracle
+import _parity as P
+from conftest import best_oracle
+from optix_renderer_b200 import scenes
+
+
+@pytest.fixture(scope="module")
+def hc(hostcheck):
+    hostcheck.load_scene(scenes.scene_floor_blocker(8, 8))
+    return hostcheck
+
+
+@pytest.fixture(scope="module")
+def ora(restatement):
+    restatement.load_scene(scenes.scene_floor_blocker(8, 8))
+    return restatement
+
+
+def test_units(hc, ora):
+    u = P.units()
+    P.check_rng(hc, u)
+    P.check_clip(hc, ora, u)
+    P.check_scalar_units(hc, u)
+    P.check_bsdf(hc, u)
+
+
+def test_rng_skip_equals_sequential_draws(hc):
+    for n in (0, 1, 2, 7, 42, 1000):
+        s, raw, _ = hc.u_rng(10011, 17, 3, 640, n)
+        want = s if n == 0 else int(raw[-1])
+        assert hc.u_rng_skip(10011, 17, 3, 640, n) == want
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("scene_fn,W,H", [(scenes.scene_floor_blocker, 48, 40), (scenes.scene_cornell, 40, 40)])
+def test_frames(hostcheck, scene_fn, W, H, mode):
+    sc = scene_fn(W, H)
+    hostcheck.load_scene(sc)
+    o = best_oracle(mode)
+    o.load_scene(sc)
+    depth = 6 if mode else 1
+    assert o.set_options(mode, 4, depth) == 0
+    for rt in (_oracle.LTC_BASELINE, _oracle.RATIO, _oracle.PATH, _oracle.NORMALS, _oracle.MATERIAL_ID):
+        a = o.render(W, H, rt, 0)
+        b = hostcheck.render(W, H, rt, 0, mode=mode, spp=4, depth=depth)
+        rep = P.frame_report({k: b[k] for k in ("accum", "ltc", "sto_direct", "sto_no_vis", "position", "normal")},
+                             a, b["hit_prim"], a["hit_prim"])
+        assert rep["hit_mismatch"] == 0
+        assert a["rays"] == b["rays"]
+        for k in ("accum", "ltc", "position", "normal"):
+            assert rep[k]["max_rel"] <= 1e-4, (rt, k, rep[k])
+            assert rep[k]["nan_mismatch"] == 0
+        for k in ("sto_direct", "sto_no_vis"):
+            assert rep[k]["rmse"] <= 1e-3 and rep[k]["nan_mismatch"] == 0, (rt, k, rep[k])
+        assert np.array_equal(a["rgba8"] == b["rgba8"], np.ones_like(a["rgba8"], bool)) or \
+            (a["rgba8"] != b["rgba8"]).mean() < 0.01  # 8-bit flips from last-ulp differences
+
+
+def test_accumulation(hostcheck):
+    sc = scenes.scene_floor_blocker(32, 32)
+    hostcheck.load_scene(sc)
+    o = best_oracle(1)
+    o.load_scene(sc)
+    o.set_options(1, 4, 4)
+    acc_a = acc_b = None
+    for i in range(3):
+        a = o.render(32, 32, _oracle.PATH, i, accum=acc_a)
+        b = hostcheck.render(32, 32, _oracle.PATH, i, accum=acc_b, mode=1, spp=4, depth=4)
+        acc_a, acc_b = a["accum"], b["accum"]
+    m = np.isfinite(acc_a) & np.isfinite(acc_b)
+    assert np.abs(acc_a[m] - acc_b[m]).max() <= 1e-4 * 3
+    assert (np.isnan(acc_a) != np.isnan(acc_b)).sum() == 0
+
+
+def test_bvh_traversal_equals_brute_force(hostcheck):
+    sc = scenes.scene_synthetic(n_tris=3000, n_quad_lights=2, width=16, height=16)
+    hostcheck.load_scene(sc)
+    rng = np.random.default_rng(3)
+    org = rng.uniform(-1, 1, (4000, 3)).astype(np.float32) * np.float32(3)
+    org[:, 2] = np.abs(org[:, 2]) + 0.5
+    d = rng.normal(size=(4000, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    p1, t1, u1, v1 = hostcheck.trace(org, d, brute=False)
+    p2, t2, u2, v2 = hostcheck.trace(org, d, brute=True)
+    assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
+    assert (p1 >= 0).mean() > 0.2
+
+
+def test_ltc_gbuffer_pass(hostcheck, restatement):
+    import os
+    g = np.load(os.path.join(P.G, "gbuffer48.npz"))
+    hostcheck.load_scene(scenes.scene_floor_blocker(48, 48))
+    out = hostcheck.ltc_gbuffer(g["position"], g["normal"], g["albedo"], g["alpha"], g["cam"])
+    e = P.rel_err(out, g["ltc_gbuffer"])
+    assert e.max() <= 1e-4
