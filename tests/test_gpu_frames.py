@@ -64,7 +64,13 @@ def test_frames_vs_oracle(renderer_factory, scene_fn, W, H, mode):
         check_frame(got, ref, rt)
         c = got["counters"]
         assert c["rays_primary"] > 0
-        assert W * H + c["rays_shadow"] + c["rays_bounce"] == ref["rays"]   # device-counted rays, exact
+        rays = W * H + c["rays_shadow"] + c["rays_bounce"]                  # device-counted
+        if rt == _oracle.PATH and mode == 1:
+            # a bounce ray that grazes an edge can end a path one bounce earlier or later when the
+            # direction differs in the last ulp (fma contraction, libdevice vs glibc sin/cos)
+            assert abs(rays - ref["rays"]) <= max(4, ref["rays"] // 500), (rays, ref["rays"])
+        else:
+            assert rays == ref["rays"]                                      # exact
 
 
 def test_debug_aov_modes(renderer_factory):
