@@ -213,13 +213,16 @@ struct LtcLut {
 };
 
 // ---- edge integral (z component of the vector irradiance of one great-circle edge) ------------
+// Branch-free: both forms of theta/sin(theta) are evaluated and one is selected, so lanes whose
+// edges have opposite signs of x stay converged.
 ORB_HD float edge_integral(float3 p, float3 q) {
     const float x = dot(p, q);
     const float y = fabsf(x);
     const float num = 0.8543985f + (0.4965155f + 0.0145206f * y) * y;
     const float den = 3.4175940f + (4.1616724f + y) * y;
     const float v = num / den;
-    const float theta_sintheta = (x > 0.0f) ? v : 0.5f * (1.0f / sqrtf(fmaxf(1.0f - x * x, 1e-7f))) - v;
+    const float w = 0.5f * orb_rsqrt(fmaxf(1.0f - x * x, 1e-7f)) - v;
+    const float theta_sintheta = (x > 0.0f) ? v : w;
     return (p.x * q.y - p.y * q.x) * theta_sintheta;
 }
 
@@ -230,76 +233,45 @@ ORB_HD float3 horizon_cut(float3 lhs, float3 rhs) {
     return normalize(v3(s * rhs.x + cx, s * rhs.y + cy, 0.f));
 }
 
+ORB_HD float3 sel3(bool c, float3 a, float3 b) { return v3(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z); }
+
 // Clip triangle (a,b,c) -- or, when `quad` is set, the degenerate quad (a,b,c,a) the reference
 // feeds its second clip -- against z > 0 and return the absolute edge sum.  n_out receives the
 // vertex count the reference's clipPolygon would have returned (0, 3, 4 or 5).
+//
+// The reference's 25-way switch (polygon_utils.cuh:33-120) is a large block of code per case;
+// inlined twice per light it made k_ltc 92 KB of SASS and the kernel stalled on instruction
+// fetch (ncu profiles/r1a: stall_no_instruction 11.8 per issue).  Here ALL cases share one
+// instruction stream: the three possible horizon cuts are computed, the (up to four) polygon
+// vertices are picked with selects in the reference's vertex order per case, and at most four
+// edge integrals are summed in that order.  Unused cuts may be inf/NaN; they are never selected.
+//   mask (a,b,c above)   polygon                 reference case
+//   7                    a  b  c                 59
+//   1                    a  ab ca                11
+//   2                    ab b  bc                19
+//   4                    ca bc c                 35
+//   3                    a  b  bc ca             27
+//   6                    ab b  c  ca             51
+//   5                    a  ab bc c              43      (quad: ab bc c a, case 108)
 ORB_HD float clipped_form_factor(float3 a, float3 b, float3 c, bool quad, int& n_out) {
     const int mask = (a.z > 0.f ? 1 : 0) | (b.z > 0.f ? 2 : 0) | (c.z > 0.f ? 4 : 0);
-    float s;
-    switch (mask) {
-        case 0:
-            n_out = 0;
-            return 0.f;
-        case 7:
-            n_out = quad ? 4 : 3;
-            s = edge_integral(a, b);
-            s += edge_integral(b, c);
-            s += edge_integral(c, a);
-            break;
-        case 1: {  // a above
-            const float3 ab = horizon_cut(a, b), ca = horizon_cut(c, a);
-            n_out = quad ? 4 : 3;
-            s = edge_integral(a, ab);
-            s += edge_integral(ab, ca);
-            s += edge_integral(ca, a);
-        } break;
-        case 2: {  // b above
-            const float3 ab = horizon_cut(a, b), bc = horizon_cut(b, c);
-            n_out = 3;
-            s = edge_integral(ab, b);
-            s += edge_integral(b, bc);
-            s += edge_integral(bc, ab);
-        } break;
-        case 4: {  // c above
-            const float3 ca = horizon_cut(c, a), bc = horizon_cut(b, c);
-            n_out = 3;
-            s = edge_integral(ca, bc);
-            s += edge_integral(bc, c);
-            s += edge_integral(c, ca);
-        } break;
-        case 3: {  // a, b above
-            const float3 ca = horizon_cut(c, a), bc = horizon_cut(b, c);
-            n_out = quad ? 5 : 4;
-            s = edge_integral(a, b);
-            s += edge_integral(b, bc);
-            s += edge_integral(bc, ca);
-            s += edge_integral(ca, a);
-        } break;
-        case 6: {  // b, c above
-            const float3 ca = horizon_cut(c, a), ab = horizon_cut(a, b);
-            n_out = 4;
-            s = edge_integral(ab, b);
-            s += edge_integral(b, c);
-            s += edge_integral(c, ca);
-            s += edge_integral(ca, ab);
-        } break;
-        default: {  // 5: a, c above
-            const float3 ab = horizon_cut(a, b), bc = horizon_cut(b, c);
-            if (quad) {  // reference order (ab, bc, c, a, a)
-                n_out = 5;
-                s = edge_integral(ab, bc);
-                s += edge_integral(bc, c);
-                s += edge_integral(c, a);
-                s += edge_integral(a, ab);
-            } else {  // reference order (a, ab, bc, c)
-                n_out = 4;
-                s = edge_integral(a, ab);
-                s += edge_integral(ab, bc);
-                s += edge_integral(bc, c);
-                s += edge_integral(c, a);
-            }
-        } break;
+    if (mask == 0) {
+        n_out = 0;
+        return 0.f;
     }
+    const float3 ab = horizon_cut(a, b), bc = horizon_cut(b, c), ca = horizon_cut(c, a);
+    const bool m5q = mask == 5 && quad;
+    const bool four = mask == 3 || mask == 6 || mask == 5;
+    const float3 p0 = sel3(mask == 2 || mask == 6 || m5q, ab, sel3(mask == 4, ca, a));
+    const float3 p1 = sel3(mask == 1 || (mask == 5 && !quad), ab, sel3(mask == 4 || m5q, bc, b));
+    const float3 p2 = sel3(mask == 1, ca, sel3(mask == 2 || mask == 3 || (mask == 5 && !quad), bc, c));
+    const float3 p3 = sel3(!four, p0, sel3(mask == 5, sel3(quad, a, c), ca));
+    float s = edge_integral(p0, p1);
+    s += edge_integral(p1, p2);
+    s += edge_integral(p2, p3);
+    if (four) s += edge_integral(p3, p0);
+    const bool plus1 = quad && (mask == 7 || mask == 1 || mask == 3 || mask == 5);
+    n_out = (four ? 4 : 3) + (plus1 ? 1 : 0);
     return fabsf(s);
 }
 
@@ -363,6 +335,7 @@ ORB_HD float3 integrate_tri_light(const LtcFrame& f, float3 lv1, float3 lv2, flo
 ORB_HD float3 ltc_direct(const LtcFrame& f, const TriLight* lights, int n_lights) {
     float3 colour = v3(0.f);
     if (!f.valid) return colour;
+#pragma unroll 1
     for (int l = 0; l < n_lights; l++) {
         const TriLight& L = lights[l];
         colour += integrate_tri_light(f, L.v1, L.v2, L.v3, L.normal, L.emit);

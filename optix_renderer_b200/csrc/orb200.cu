@@ -394,12 +394,15 @@ k_denoise_atrous(FrameView f, const float4* __restrict__ guide, const float2* __
                 const float4 g = __ldg(guide + q);
                 if (g.w < 0.f) continue;
                 const float2 v = __ldg(vin + q);
+                // nd^sigma_n * exp(-|dz| / (sigma_p step)) as ONE exp2 of a sum of logs (MUFU lg2 + ex2:
+                // the libm powf/expf pair made this pass issue-bound at 8 % of the HBM rate)
                 const float nd = fmaxf(0.f, gc.x * g.x + gc.y * g.y + gc.z * g.z);
-                float w = c_b3[i + 2] * c_b3[j + 2] * powf(nd, sigma_n) * expf(-fabsf(gc.w - g.w) * inv_sigma_p);
+                const float ln = sigma_n > 0.f ? sigma_n * __log2f(nd) : 0.f;
+                float w = c_b3[i + 2] * c_b3[j + 2] * exp2f(ln - fabsf(gc.w - g.w) * inv_sigma_p);
                 float w0 = w, w1 = w;
                 if (inv_sigma_c > 0.f) {
-                    w0 *= expf(-fabsf(vc.x - v.x) * inv_sigma_c);
-                    w1 *= expf(-fabsf(vc.y - v.y) * inv_sigma_c);
+                    w0 *= exp2f(-fabsf(vc.x - v.x) * inv_sigma_c);
+                    w1 *= exp2f(-fabsf(vc.y - v.y) * inv_sigma_c);
                 }
                 if (v.x == v.x && w0 == w0) { sd += w0 * v.x; wd += w0; }
                 if (v.y == v.y && w1 == w1) { sn += w1 * v.y; wn += w1; }
@@ -1110,8 +1113,9 @@ int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t 
     int cur = 0;
     for (int it = 0; it < d.iterations; it++) {
         const int step = 1 << it;
-        const float isp = 1.f / (d.sigma_position * (float)step);
-        const float isc = d.sigma_colour > 0.f ? 1.f / d.sigma_colour : 0.f;
+        const float log2e = 1.4426950408889634f;  // the kernel evaluates exp(x) as exp2(x log2 e)
+        const float isp = log2e / (d.sigma_position * (float)step);
+        const float isc = d.sigma_colour > 0.f ? log2e / d.sigma_colour : 0.f;
         if (it == d.iterations - 1) {
             dim3 gb((c->W + 31) / 32, (y1 - y0 + 7) / 8);
             k_denoise_atrous<true><<<gb, 256, 0, c->stream>>>(f, c->dn_guide, c->dn_val[cur], nullptr,

@@ -121,8 +121,25 @@ ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, floa
     return t0 <= t1;
 }
 
-// Closest-hit traversal.  STACK entries live where the caller put them (`stk`/`stk_t` index
-// stride `stride`): shared memory interleaved per lane in the kernels, a plain array on the CPU.
+// Closest-hit traversal, "while-while" form (Aila & Laine, HPG 2009): a lane walks INNER nodes
+// until it holds a leaf (or is finished) and only then does the warp run the triangle tests, so
+// the expensive Moeller-Trumbore block executes with most lanes active instead of the two or
+// three that happened to reach a leaf in the same iteration (ncu, profiles/r1a: 2.3 active lanes
+// in the leaf block of the if-if form).  STACK entries live where the caller put them
+// (`stk`/`stk_t` index stride `stride`): shared memory interleaved per lane in the kernels, a
+// plain array on the CPU.  The result does not depend on the visiting order (closest t, ties to
+// the lowest primitive id), so any BVH and any order agree bit for bit.
+#define ORB_TRAVERSAL_DONE ((int)0x80000000)  // never a leaf reference: first + count < 2^28
+
+template <class IntPtr, class FltPtr>
+ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& best) {
+    for (;;) {  // skip subtrees that start beyond the current closest hit
+        if (sp == 0) return ORB_TRAVERSAL_DONE;
+        --sp;
+        if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) return stk[sp * stride];
+    }
+}
+
 template <class IntPtr, class FltPtr>
 ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, FltPtr stk_t, int stride,
                          unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
@@ -134,12 +151,12 @@ ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, Flt
     const float3 inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
     int sp = 0;
     int cur = s.root_ref;
-    for (;;) {
-        if (cur >= 0) {
+    while (cur != ORB_TRAVERSAL_DONE) {
+        while (cur >= 0) {  // ---- inner nodes: both child boxes per 64-byte fetch
             const BvhNode* np = s.nodes + cur;
 #ifdef __CUDA_ARCH__
             const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-            const int4 nd = __ldg(reinterpret_cast<const int4*>(&np->c0));
+            const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
             const int c0 = nd.x, c1 = nd.y;
 #else
             const float4 na = np->a, nb = np->b, nc = np->c;
@@ -152,16 +169,20 @@ ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, Flt
             const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, o, inv, lim, tn1);
             if (h0 && h1) {
                 const bool swap = tn1 < tn0;
-                const int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
-                stk[sp * stride] = farc;
+                stk[sp * stride] = swap ? c0 : c1;
                 stk_t[sp * stride] = swap ? tn0 : tn1;
                 ++sp;
-                cur = nearc;
-                continue;
+                cur = swap ? c1 : c0;
+            } else if (h0) {
+                cur = c0;
+            } else if (h1) {
+                cur = c1;
+            } else {
+                cur = stack_pop(stk, stk_t, stride, sp, best);
             }
-            if (h0) { cur = c0; continue; }
-            if (h1) { cur = c1; continue; }
-        } else {
+        }
+        if (cur == ORB_TRAVERSAL_DONE) break;
+        {  // ---- leaf
             const int lr = ~cur;
             const int first = lr >> 3, count = (lr & 7) + 1;
             for (int i = 0; i < count; i++) {
@@ -175,15 +196,10 @@ ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, Flt
                 float t, u, v;
                 if (tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(t0.w));
             }
-        }
-        // pop, skipping subtrees that start beyond the current closest hit
-        for (;;) {
-            if (sp == 0) return best;
-            --sp;
-            cur = stk[sp * stride];
-            if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) break;
+            cur = stack_pop(stk, stk_t, stride, sp, best);
         }
     }
+    return best;
 }
 
 // Brute force over every triangle record: the GPU-side reference for hit-id parity tests.

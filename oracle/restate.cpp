@@ -1015,7 +1015,7 @@ void ora_ratio_combine(long long n, const float* ltc, const float* sto_direct, c
 //   value  v(q) = (sto_direct.x, sto_no_vis.x)
 //   guide  g(q) = (n.xyz, depth = |p - cam|); pixels with materialID == 0 or n == 0 (lights,
 //                 misses) are passed through unfiltered and never used as a tap
-//   weight w(q) = B3(dx) B3(dy) * max(0, n_c . n_q)^sigma_n * exp(-|d_c - d_q| / (sigma_p * step))
+//   weight w(q) = B3(dx) B3(dy) * max(0, n_c . n_q)^sigma_n (sigma_n <= 0: factor 1) * exp(-|d_c - d_q| / (sigma_p * step))
 //                 (* exp(-|v_c - v_q| / sigma_c) per image when sigma_c > 0); NaN taps skipped
 //   passes step = 1, 2, 4, ... (iterations of them), 5x5 taps, B3 = (1/16, 1/4, 3/8, 1/4, 1/16)
 // ================================================================================================
@@ -1060,7 +1060,7 @@ extern "C" void ora_denoise(int W, int H, const float* normal, const float* posi
                             if (g[3] < 0.f) continue;
                             const float v0 = vin[2 * q], v1 = vin[2 * q + 1];
                             const float nd = fmaxf(0.f, gc[0] * g[0] + gc[1] * g[1] + gc[2] * g[2]);
-                            const float w = b3[i + 2] * b3[j + 2] * powf(nd, sigma_n) * expf(-fabsf(gc[3] - g[3]) * isp);
+                            const float w = b3[i + 2] * b3[j + 2] * (sigma_n > 0.f ? powf(nd, sigma_n) : 1.f) * expf(-fabsf(gc[3] - g[3]) * isp);
                             float w0 = w, w1 = w;
                             if (isc > 0.f) {
                                 w0 *= expf(-fabsf(r0 - v0) * isc);

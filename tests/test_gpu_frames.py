@@ -21,6 +21,11 @@ BUFS = ("position", "normal", "uv", "albedo", "alpha", "materialID", "ltc", "sto
 
 
 def gpu_frame(r, rt, accum_id=0, mode=0, spp=4, depth=1, rows=None):
+    # rayGen leaves ltc / sto_* of MISS pixels untouched (deviceCode.cu:91-95,117-145), so they keep
+    # whatever an earlier frame with another jitter wrote; the oracle starts from zeroed buffers
+    z = np.zeros((r.H, r.W, 4), np.float32)
+    for k in ("ltc", "sto_direct", "sto_no_vis"):
+        r.upload(k, z)
     r.render(rt, accum_id=accum_id, mode=mode, shadow_spp=spp, max_depth=depth, rows=rows)
     out = {k: r.download(k) for k in BUFS}
     out["rgba8"] = r.download("rgba8")
@@ -150,9 +155,9 @@ def test_trace_hit_ids_bvh_vs_brute_force_and_oracle(renderer_factory):
     d = rng.normal(size=(n, 3)).astype(np.float32)
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     p1, t1, u1, v1 = r.trace_rays(org, d, brute_force=False)
+    c = r.counters()
     p2, t2, u2, v2 = r.trace_rays(org, d, brute_force=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
-    c = r.counters()
     assert 0 < c["tris_tested"] < 0.05 * n * c["bvh_triangles"]      # the BVH actually prunes
     # against the oracle's stand-in closest hit through a rendered frame
     o = best_oracle(0)
