@@ -110,6 +110,8 @@ typedef struct OrbRenderConfig {
     int32_t y0, y1;        /* rows [y0, y1) rendered by this context (tile partition); 0,0 = all */
     int32_t flags;         /* ORB_RENDER_* */
 } OrbRenderConfig;
+#define ORB_RENDER_FUSED_SHADOW 2 /* RATIO: trace the shadow rays inside one per-pixel kernel instead of the
+                                     ray-stream kernels (kept for A/B measurement; same results) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 

@@ -226,17 +226,17 @@ class Renderer:
         self.W, self.H = int(W), int(H)
 
     # ---- launch (Viewer::render, viewer.hpp:553-568) ----
-    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True):
+    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True, fused_shadow=False):
         c = OrbRenderConfig()
-        c.flags = 0 if count_rays else 1  # ORB_RENDER_NO_COUNT
+        c.flags = (0 if count_rays else 1) | (2 if fused_shadow else 0)  # ORB_RENDER_NO_COUNT, _FUSED_SHADOW
         c.renderer_type, c.accum_id, c.mode = int(renderer_type), int(accum_id), int(mode)
         c.shadow_spp, c.max_depth = int(shadow_spp), int(max_depth)
         c.y0, c.y1 = rows if rows else (0, 0)
         return c
 
     def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True,
-               count_rays=True):
-        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays)
+               count_rays=True, fused_shadow=False):
+        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays, fused_shadow)
         self._ck((self.lib.orb_render if sync else self.lib.orb_render_async)(self._h, C.byref(c)))
 
     def ltc_gbuffer_pass(self, rows=None):

@@ -46,47 +46,78 @@ ORB_HD float3 ltc_pixel(const LtcLut& lut, const TriLight* lights, int n_lights,
     return ltc_direct(f, lights, n_lights);
 }
 
-// One call of ratio_based_shadow(si, rng, 1): five draws, one closest-hit "shadow" ray.
-// `trace(o, d)` returns the Hit.  Outputs: colours[0] (shadowed) and colours[1] (unshadowed).
-// Returns false when no ray was traced (no lights).
-template <class Tracer>
-ORB_HD bool ratio_shadow_sample(const SceneView& s, Tracer&& trace, float3 cam_pos, float3 p, float3 n, float3 diffuse,
-                                float alpha, Rng& rng, int mode, float3& direct, float3& novis) {
-    direct = novis = v3(0.f);
+// One call of ratio_based_shadow(si, rng, 1): five draws, one closest-hit "shadow" ray.  Split
+// in two so the wavefront can put a ray-stream traversal kernel between them:
+//   shadow_ray_setup()   draws + light sample -> the ray and what the resolve step needs
+//   shadow_ray_resolve() closest hit -> colours[0] (shadowed) and colours[1] (unshadowed)
+struct ShadowSample {
+    float3 origin, L;   // the ray: p + 1e-3 n_geom, towards the sampled light point
+    float3 emit;        // the SELECTED light's emit (unshadowed term)
+    float dist2;        // squared distance to the sampled point
+    float light_pdf;    // area pdf of the selection, 1 / (area * numTriLights)
+    bool valid;         // false: no lights
+};
+
+ORB_HD ShadowSample shadow_ray_setup(const SceneView& s, float3 p, float3 n, Rng& rng) {
+    ShadowSample q;
     const float r1x = rng_nextf(rng), r1y = rng_nextf(rng);
     rng_nextf(rng);  // rand2 is drawn and unused (ratio.cuh:30)
     rng_nextf(rng);
     const float sel = rng_nextf(rng);
-    if (s.n_lights <= 0) return false;
+    q.valid = s.n_lights > 0;
+    q.origin = q.L = q.emit = v3(0.f);
+    q.dist2 = q.light_pdf = 0.f;
+    if (!q.valid) return q;
     // int(rand * (numTriLights - 1)): the last light is never selected
     const int idx = imin(imax((int)(sel * (float)(s.n_lights - 1)), 0), s.n_lights - 1);
     const TriLight lt = s.lights[idx];
-    const float light_pdf = 1.f / (lt.area * (float)s.n_lights);
+    q.emit = lt.emit;
+    q.light_pdf = 1.f / (lt.area * (float)s.n_lights);
     // samplePointOnTriangle, utils.cuh:194-199 -- defines the ray, so exact arithmetic
     const float su1 = xsqrt(r1x);
     const float3 inner = xadd(xmul(xsub(1.f, r1y), lt.v2), xmul(r1y, lt.v3));
     const float3 new_pos = xadd(xmul(xsub(1.f, su1), lt.v1), xmul(su1, inner));
     const float3 diff = xsub(new_pos, p);
-    const float3 L = xnormalize(diff);
-    float dist = xlength(diff);
-    dist = dist * dist;
-    const float3 origin = xadd(p, xmul(n, 1e-3f));
-    const Hit h = trace(origin, L);
+    q.L = xnormalize(diff);
+    const float dist = xlength(diff);
+    q.dist2 = dist * dist;
+    q.origin = xadd(p, xmul(n, 1e-3f));
+    return q;
+}
+
+ORB_HD void shadow_ray_resolve(const SceneView& s, const ShadowSample& q, const Hit& h, float3 cam_pos, float3 p,
+                               float3 n, float3 diffuse, float alpha, int mode, float3& direct, float3& novis) {
+    direct = novis = v3(0.f);
+    if (!q.valid) return;
     const Surface ls = shade_hit(s, h.prim, h.u, h.v);
-    const float light_pdf_w = pdf_area_to_solid_angle(light_pdf, dist, dot(-L, ls.n));
+    const float light_pdf_w = pdf_area_to_solid_angle(q.light_pdf, q.dist2, dot(-q.L, ls.n));
     float3 brdf = v3(0.f);  // committed source (ratio.cuh:58)
     if (mode == ORB_MODE_INTENDED) {  // patch P1: evaluate() as in the commented tail of that line
         const float3 wo = normalize(cam_pos - p);
         const Mat3 to_local = onb_rows(n);
         const float3 wo_local = normalize(apply(to_local, wo));
-        const float3 wi_local = normalize(apply(to_local, L));
+        const float3 wi_local = normalize(apply(to_local, q.L));
         brdf = bsdf_evaluate(wi_local, wo_local, diffuse, alpha);
     }
     const float mis_w = light_pdf_w / (light_pdf_w + 0.f);  // brdfPdf = 0
-    const float cd = clamp_dot_eps(n, L);
+    const float cd = clamp_dot_eps(n, q.L);
     const float3 tp = v3(1.f);
     if (ls.is_light) direct = check_positive(check_positive(mis_w * ls.emit * tp * brdf * cd / light_pdf_w));
-    novis = check_positive(check_positive(mis_w * lt.emit * tp * brdf * cd / light_pdf_w));
+    novis = check_positive(check_positive(mis_w * q.emit * tp * brdf * cd / light_pdf_w));
+}
+
+// Both halves around a caller-supplied tracer (megakernel form: tests/hostcheck, k_unit).
+// Returns false when no ray was traced (no lights).
+template <class Tracer>
+ORB_HD bool ratio_shadow_sample(const SceneView& s, Tracer&& trace, float3 cam_pos, float3 p, float3 n, float3 diffuse,
+                                float alpha, Rng& rng, int mode, float3& direct, float3& novis) {
+    const ShadowSample q = shadow_ray_setup(s, p, n, rng);
+    if (!q.valid) {
+        direct = novis = v3(0.f);
+        return false;
+    }
+    const Hit h = trace(q.origin, q.L);
+    shadow_ray_resolve(s, q, h, cam_pos, p, n, diffuse, alpha, mode, direct, novis);
     return true;
 }
 

@@ -140,66 +140,83 @@ ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& b
     }
 }
 
+// Traversal state of one ray; a "macro step" walks inner nodes until a leaf is reached, tests
+// that leaf, and pops.  trace_closest() runs macro steps to completion; the ray-stream kernel
+// (orb200.cu k_trace_stream) interleaves them with refills so finished lanes get new rays.
+struct TravState {
+    float3 o, d, inv;
+    Hit best;
+    int cur, sp;
+};
+
+ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
+    t.o = o;
+    t.d = d;
+    t.inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    t.best.t = INFINITY;
+    t.best.u = t.best.v = 0.f;
+    t.best.prim = -1;
+    t.sp = 0;
+    t.cur = s.n_tris == 0 ? ORB_TRAVERSAL_DONE : s.root_ref;
+}
+
+template <class IntPtr, class FltPtr>
+ORB_HD void trav_macro_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
+                            unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+    while (t.cur >= 0) {  // ---- inner nodes: both child boxes per 64-byte fetch
+        const BvhNode* np = s.nodes + t.cur;
+#ifdef __CUDA_ARCH__
+        const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
+        const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
+        const int c0 = nd.x, c1 = nd.y;
+#else
+        const float4 na = np->a, nb = np->b, nc = np->c;
+        const int c0 = np->c0, c1 = np->c1;
+#endif
+        if (n_nodes) ++*n_nodes;
+        const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
+        float tn0, tn1;
+        const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.o, t.inv, lim, tn0);
+        const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.o, t.inv, lim, tn1);
+        if (h0 && h1) {
+            const bool swap = tn1 < tn0;
+            stk[t.sp * stride] = swap ? c0 : c1;
+            stk_t[t.sp * stride] = swap ? tn0 : tn1;
+            ++t.sp;
+            t.cur = swap ? c1 : c0;
+        } else if (h0) {
+            t.cur = c0;
+        } else if (h1) {
+            t.cur = c1;
+        } else {
+            t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+        }
+    }
+    if (t.cur == ORB_TRAVERSAL_DONE) return;
+    // ---- leaf
+    const int lr = ~t.cur;
+    const int first = lr >> 3, count = (lr & 7) + 1;
+    for (int i = 0; i < count; i++) {
+        const float4* tp = s.tri + 3 * (size_t)(first + i);
+#ifdef __CUDA_ARCH__
+        const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+#else
+        const float4 t0 = tp[0], t1 = tp[1], t2 = tp[2];
+#endif
+        if (n_tris) ++*n_tris;
+        float tt, u, v;
+        if (tri_test(t0, t1, t2, t.o, t.d, 0.f, ORB_TMAX, tt, u, v)) hit_consider(t.best, tt, u, v, __float_as_int_hd(t0.w));
+    }
+    t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+}
+
 template <class IntPtr, class FltPtr>
 ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, FltPtr stk_t, int stride,
                          unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
-    Hit best;
-    best.t = INFINITY;
-    best.u = best.v = 0.f;
-    best.prim = -1;
-    if (s.n_tris == 0) return best;
-    const float3 inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
-    int sp = 0;
-    int cur = s.root_ref;
-    while (cur != ORB_TRAVERSAL_DONE) {
-        while (cur >= 0) {  // ---- inner nodes: both child boxes per 64-byte fetch
-            const BvhNode* np = s.nodes + cur;
-#ifdef __CUDA_ARCH__
-            const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-            const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
-            const int c0 = nd.x, c1 = nd.y;
-#else
-            const float4 na = np->a, nb = np->b, nc = np->c;
-            const int c0 = np->c0, c1 = np->c1;
-#endif
-            if (n_nodes) ++*n_nodes;
-            const float lim = best.prim < 0 ? ORB_TMAX : best.t;
-            float tn0, tn1;
-            const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, o, inv, lim, tn0);
-            const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, o, inv, lim, tn1);
-            if (h0 && h1) {
-                const bool swap = tn1 < tn0;
-                stk[sp * stride] = swap ? c0 : c1;
-                stk_t[sp * stride] = swap ? tn0 : tn1;
-                ++sp;
-                cur = swap ? c1 : c0;
-            } else if (h0) {
-                cur = c0;
-            } else if (h1) {
-                cur = c1;
-            } else {
-                cur = stack_pop(stk, stk_t, stride, sp, best);
-            }
-        }
-        if (cur == ORB_TRAVERSAL_DONE) break;
-        {  // ---- leaf
-            const int lr = ~cur;
-            const int first = lr >> 3, count = (lr & 7) + 1;
-            for (int i = 0; i < count; i++) {
-                const float4* tp = s.tri + 3 * (size_t)(first + i);
-#ifdef __CUDA_ARCH__
-                const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-#else
-                const float4 t0 = tp[0], t1 = tp[1], t2 = tp[2];
-#endif
-                if (n_tris) ++*n_tris;
-                float t, u, v;
-                if (tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(t0.w));
-            }
-            cur = stack_pop(stk, stk_t, stride, sp, best);
-        }
-    }
-    return best;
+    TravState t;
+    trav_begin(t, s, o, d);
+    while (t.cur != ORB_TRAVERSAL_DONE) trav_macro_step(t, s, stk, stk_t, stride, n_nodes, n_tris);
+    return t.best;
 }
 
 // Brute force over every triangle record: the GPU-side reference for hit-id parity tests.

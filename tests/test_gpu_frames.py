@@ -285,3 +285,22 @@ def test_full_size_properties(renderer_factory):
     p1, t1, _, _ = r.trace_rays(o, d, brute_force=False)
     p2, t2, _, _ = r.trace_rays(o, d, brute_force=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2)
+
+
+def test_ray_stream_equals_fused_shadow_kernel(renderer_factory):
+    """The ray-stream form (generate / persistent traversal with refill / resolve) and the fused
+    per-pixel kernel are two schedules of the same arithmetic: bit-identical outputs."""
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
+    r = renderer_factory(sc)
+    for spp in (1, 4, 3):
+        r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=spp, fused_shadow=True)
+        a = {k: r.download(k) for k in ("sto_direct", "sto_no_vis", "ltc", "accum")}
+        ca = r.counters()
+        r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=spp, fused_shadow=False)
+        cb = r.counters()
+        for k in a:
+            b = r.download(k)
+            assert np.array_equal(np.isnan(a[k]), np.isnan(b)), (spp, k)
+            m = np.isfinite(a[k]) & np.isfinite(b)
+            np.testing.assert_allclose(a[k][m], b[m], rtol=3e-5, atol=5e-7)
+        assert ca["rays_shadow"] == cb["rays_shadow"] == spp * cb["active_pixels"]
