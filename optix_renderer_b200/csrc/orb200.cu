@@ -18,6 +18,7 @@
 // is no tensor-core work (BASELINE.json north_star).  There is no CPU fallback.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -254,12 +255,20 @@ k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, 
 // is ~3 % of the kernel's time at the measured copy rate.
 // ---------------------------------------------------------------------------------------------
 #define STREAM_CHUNK 128u
+#define STREAM_BURST 8
 
+#define LOCAL_STACK_MAX 64
+template <bool LOCAL_STACK>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits, const unsigned* __restrict__ n_items,
-               unsigned mult, unsigned* __restrict__ cursor, int refill_min, int height) {
-    int* stk = s_dyn + threadIdx.x;
-    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+               unsigned mult, unsigned* __restrict__ cursor, int refill_min, int leaf_min, int height) {
+    // Traversal stack: per-lane columns of shared memory (bank-conflict free, but 8 B x height x 128
+    // threads of shared memory per CTA caps residency), or thread-local memory behind L1.
+    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
+    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
     const unsigned n = *n_items * mult;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned FULL = 0xffffffffu;
@@ -304,7 +313,22 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
             }
         }
         if (__ballot_sync(FULL, t.cur != ORB_TRAVERSAL_DONE) == 0u) break;
-        if (t.cur != ORB_TRAVERSAL_DONE) trav_macro_step(t, s, stk, stk_t, TRACE_BLOCK);
+        // A burst of single steps.  Lanes on an inner node advance every iteration; lanes that hold
+        // a LEAF wait until `leaf_min` of them do (or nobody has an inner node left) and then run
+        // the triangle tests together -- the while-while form left 10 of 32 lanes active in the
+        // node loop because each macro step lasted as long as its slowest lane (profiles/r1b).
+#pragma unroll 1
+        for (int it = 0; it < STREAM_BURST; ++it) {
+            if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
+            const bool at_leaf = t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE;
+            const unsigned leaves = __ballot_sync(FULL, at_leaf);
+            const unsigned inner = __ballot_sync(FULL, t.cur >= 0);
+            if (leaves && ((int)__popc(leaves) >= leaf_min || inner == 0u)) {
+                if (at_leaf) trav_leaf_step(t, s, stk, stk_t, stride);
+            } else if (inner == 0u) {
+                break;  // everyone is finished: go and refill
+            }
+        }
     }
 }
 
@@ -720,7 +744,9 @@ struct OrbContext {
     float4* stream_hits = nullptr;   // 1 float4 per ray
     size_t stream_cap = 0;
     unsigned* stream_cursor = nullptr;
-    int refill_min = 8;
+    int refill_min = 12;
+    int leaf_min = 12;
+    int local_stack = 0;
     float4* dn_guide = nullptr;
     float2* dn_val[2] = {nullptr, nullptr};
     float* unit_in = nullptr;
@@ -866,6 +892,9 @@ int orb_create(int device, OrbContext** out) {
     CK(cudaMalloc(&c->unit_out, 4096 * sizeof(float)));
     memset(&c->counters, 0, sizeof(c->counters));
     memset(&c->view, 0, sizeof(c->view));
+    if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
+    if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
+    if (const char* e = getenv("ORB_LEAF_MIN")) c->leaf_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
     return ORB_OK;
 }
@@ -1057,7 +1086,7 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
         return fail(ORB_ERR_INVALID, "orb_scene_commit: BVH too deep for the shared-memory traversal stack");
     CK(allow_smem(k_primary, trace_smem(c)));
     CK(allow_smem(k_ratio_shadow, trace_smem(c)));
-    CK(allow_smem(k_trace_stream, trace_smem(c)));
+    CK(allow_smem(k_trace_stream<false>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<true>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<false>, trace_smem(c)));
     CK(allow_smem(k_trace_rays, trace_smem(c)));
@@ -1177,9 +1206,17 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                 CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
                 const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
                 k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
-                const int g = persistent_grid(c, k_trace_stream, TRACE_BLOCK, smem);
-                k_trace_stream<<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits, &c->cnt->queue_n,
-                                                             (unsigned)spp, c->stream_cursor, c->refill_min, c->height);
+                if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
+                    const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
+                    k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, &c->cnt->queue_n,
+                                                                    (unsigned)spp, c->stream_cursor, c->refill_min,
+                                                                    c->leaf_min, c->height);
+                } else {
+                    const int g = persistent_grid(c, k_trace_stream<false>, TRACE_BLOCK, smem);
+                    k_trace_stream<false><<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits,
+                                                                         &c->cnt->queue_n, (unsigned)spp, c->stream_cursor,
+                                                                         c->refill_min, c->leaf_min, c->height);
+                }
                 c->counters.kernel_launches += 2;
             }
             const int gr = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);

@@ -160,40 +160,41 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
     t.cur = s.n_tris == 0 ? ORB_TRAVERSAL_DONE : s.root_ref;
 }
 
+// One inner node (t.cur >= 0): both child boxes of a 64-byte node, near child next, far pushed.
 template <class IntPtr, class FltPtr>
-ORB_HD void trav_macro_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
-                            unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
-    while (t.cur >= 0) {  // ---- inner nodes: both child boxes per 64-byte fetch
-        const BvhNode* np = s.nodes + t.cur;
+ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride) {
+    const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
-        const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-        const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
-        const int c0 = nd.x, c1 = nd.y;
+    const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
+    const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
+    const int c0 = nd.x, c1 = nd.y;
 #else
-        const float4 na = np->a, nb = np->b, nc = np->c;
-        const int c0 = np->c0, c1 = np->c1;
+    const float4 na = np->a, nb = np->b, nc = np->c;
+    const int c0 = np->c0, c1 = np->c1;
 #endif
-        if (n_nodes) ++*n_nodes;
-        const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
-        float tn0, tn1;
-        const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.o, t.inv, lim, tn0);
-        const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.o, t.inv, lim, tn1);
-        if (h0 && h1) {
-            const bool swap = tn1 < tn0;
-            stk[t.sp * stride] = swap ? c0 : c1;
-            stk_t[t.sp * stride] = swap ? tn0 : tn1;
-            ++t.sp;
-            t.cur = swap ? c1 : c0;
-        } else if (h0) {
-            t.cur = c0;
-        } else if (h1) {
-            t.cur = c1;
-        } else {
-            t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
-        }
+    const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
+    float tn0, tn1;
+    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.o, t.inv, lim, tn0);
+    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.o, t.inv, lim, tn1);
+    if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        stk[t.sp * stride] = swap ? c0 : c1;
+        stk_t[t.sp * stride] = swap ? tn0 : tn1;
+        ++t.sp;
+        t.cur = swap ? c1 : c0;
+    } else if (h0) {
+        t.cur = c0;
+    } else if (h1) {
+        t.cur = c1;
+    } else {
+        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
     }
-    if (t.cur == ORB_TRAVERSAL_DONE) return;
-    // ---- leaf
+}
+
+// One leaf (t.cur < 0, not DONE): its 1..8 triangles, then pop.
+template <class IntPtr, class FltPtr>
+ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
+                           unsigned* n_tris = nullptr) {
     const int lr = ~t.cur;
     const int first = lr >> 3, count = (lr & 7) + 1;
     for (int i = 0; i < count; i++) {
@@ -208,6 +209,17 @@ ORB_HD void trav_macro_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr
         if (tri_test(t0, t1, t2, t.o, t.d, 0.f, ORB_TMAX, tt, u, v)) hit_consider(t.best, tt, u, v, __float_as_int_hd(t0.w));
     }
     t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+}
+
+template <class IntPtr, class FltPtr>
+ORB_HD void trav_macro_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
+                            unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+    while (t.cur >= 0) {
+        if (n_nodes) ++*n_nodes;
+        trav_node_step(t, s, stk, stk_t, stride);
+    }
+    if (t.cur == ORB_TRAVERSAL_DONE) return;
+    trav_leaf_step(t, s, stk, stk_t, stride, n_tris);
 }
 
 template <class IntPtr, class FltPtr>

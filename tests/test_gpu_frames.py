@@ -293,10 +293,10 @@ def test_ray_stream_equals_fused_shadow_kernel(renderer_factory):
     sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
     r = renderer_factory(sc)
     for spp in (1, 4, 3):
-        r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=spp, fused_shadow=True)
+        r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=spp, fused_shadow=True)
         a = {k: r.download(k) for k in ("sto_direct", "sto_no_vis", "ltc", "accum")}
         ca = r.counters()
-        r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=spp, fused_shadow=False)
+        r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=spp, fused_shadow=False)
         cb = r.counters()
         for k in a:
             b = r.download(k)
