@@ -746,7 +746,7 @@ struct OrbContext {
     unsigned* stream_cursor = nullptr;
     int refill_min = 12;
     int leaf_min = 12;
-    int local_stack = 0;
+    int local_stack = 1;  // measured: 2.96 -> 2.51 ms for the 1080p shadow stage (more resident warps)
     float4* dn_guide = nullptr;
     float2* dn_val[2] = {nullptr, nullptr};
     float* unit_in = nullptr;

@@ -131,53 +131,77 @@ struct PathState {  // the part of current_si / loop state that survives an iter
 #define ORB_PATH_DONE 1
 
 // One iteration of estimatePathTracing's loop for a path whose current vertex is a non-light
-// hit.  mode literal = the committed debug stub (path.cuh:216-217): colour = sampled local
-// direction.  On ORB_PATH_DONE `colour` holds the value the function would return
-// (max(colour, EPS) applied); on ORB_PATH_CONTINUE `st` is the next vertex.
-template <class Tracer>
-ORB_HD int path_bounce(const SceneView& s, Tracer&& trace, PathState& st, Rng& rng, int mode, bool last, float3& colour,
-                       bool& traced) {
-    traced = false;
+// hit, split like the shadow sample so a ray-stream traversal can sit in the middle:
+//   path_ray_setup()  frame, five draws, sample_direction -> the bounce ray (+ what resolve needs)
+//   path_resolve()    closest hit -> colour (ORB_PATH_DONE) or the next vertex (ORB_PATH_CONTINUE)
+// mode literal = the committed debug stub (path.cuh:216-217): colour = sampled local direction,
+// no ray.  On ORB_PATH_DONE `colour` holds the value the function would return (max(colour, EPS)
+// applied).
+struct PathSample {
+    float3 origin, dir;       // p + EPS n_geom, to_world * wi_local (normalised)
+    float3 wi_local, wo_local;
+    float bsdf_pdf;
+};
+
+ORB_HD PathSample path_ray_setup(const PathState& st, Rng& rng) {
+    PathSample q;
     // orthonormalBasis(n, to_world, to_local): the outputs are swapped w.r.t. rayGen
     const Mat3 to_world = onb_rows(st.n);
     const Mat3 to_local = transpose(to_world);
-    const float3 wo_local = normalize(apply(to_local, st.V));
+    q.wo_local = normalize(apply(to_local, st.V));
     rng_nextf(rng);  // rand1, unused
     rng_nextf(rng);
     const float r2x = rng_nextf(rng), r2y = rng_nextf(rng);
     rng_nextf(rng);  // light selection draw, unused
-    float bsdf_pdf = 0.f;
-    const float3 wi_local = bsdf_sample(wo_local, r2x, r2y, bsdf_pdf, st.diffuse, st.alpha);
-    if (mode == ORB_MODE_LITERAL) {
-        colour = v3(owl_max(wi_local.x, ORB_EPS), owl_max(wi_local.y, ORB_EPS), owl_max(wi_local.z, ORB_EPS));
-        return ORB_PATH_DONE;
-    }
-    const float3 origin = xadd(st.p, xmul(ORB_EPS, st.n));
-    const float3 dir = normalize(apply(to_world, wi_local));
-    const Hit h = trace(origin, dir);
-    traced = true;
+    q.bsdf_pdf = 0.f;
+    q.wi_local = bsdf_sample(q.wo_local, r2x, r2y, q.bsdf_pdf, st.diffuse, st.alpha);
+    q.origin = xadd(st.p, xmul(ORB_EPS, st.n));
+    q.dir = normalize(apply(to_world, q.wi_local));
+    return q;
+}
+
+ORB_HD float3 path_literal_colour(const PathSample& q) {
+    return v3(owl_max(q.wi_local.x, ORB_EPS), owl_max(q.wi_local.y, ORB_EPS), owl_max(q.wi_local.z, ORB_EPS));
+}
+
+ORB_HD int path_resolve(const SceneView& s, PathState& st, const PathSample& q, const Hit& h, bool last, float3& colour) {
     colour = v3(ORB_EPS);
     if (h.prim < 0) return ORB_PATH_DONE;
     const Surface hs = shade_hit(s, h.prim, h.u, h.v);
-    const float3 brdf = bsdf_evaluate(wi_local, wo_local, st.diffuse, st.alpha);
+    const float3 brdf = bsdf_evaluate(q.wi_local, q.wo_local, st.diffuse, st.alpha);
     if (hs.is_light) {
         const float light_pdf = 1.f / (hs.area * (float)s.n_lights);
         float dist = length(hs.p - st.p);
         dist *= dist;
-        const float light_pdf_w = pdf_area_to_solid_angle(light_pdf, dist, cos_theta(wi_local));
-        const float mis_w = bsdf_pdf / (bsdf_pdf + light_pdf_w);
-        const float3 c = mis_w * hs.emit * st.tp / bsdf_pdf;
+        const float light_pdf_w = pdf_area_to_solid_angle(light_pdf, dist, cos_theta(q.wi_local));
+        const float mis_w = q.bsdf_pdf / (q.bsdf_pdf + light_pdf_w);
+        const float3 c = mis_w * hs.emit * st.tp / q.bsdf_pdf;
         colour = v3(owl_max(c.x, ORB_EPS), owl_max(c.y, ORB_EPS), owl_max(c.z, ORB_EPS));
         return ORB_PATH_DONE;
     }
     if (last) return ORB_PATH_DONE;
-    st.tp *= cos_theta(wi_local) * brdf / bsdf_pdf;
+    st.tp *= cos_theta(q.wi_local) * brdf / q.bsdf_pdf;
     st.V = normalize(st.p - hs.p);
     st.p = hs.p;
     st.n = hs.n;
     st.diffuse = hs.diffuse;
     st.alpha = 0.f;  // path.cuh:251 (not re-clamped)
     return ORB_PATH_CONTINUE;
+}
+
+// Both halves around a caller-supplied tracer (megakernel form: tests/hostcheck, k_path_bounce).
+template <class Tracer>
+ORB_HD int path_bounce(const SceneView& s, Tracer&& trace, PathState& st, Rng& rng, int mode, bool last, float3& colour,
+                       bool& traced) {
+    traced = false;
+    const PathSample q = path_ray_setup(st, rng);
+    if (mode == ORB_MODE_LITERAL) {
+        colour = path_literal_colour(q);
+        return ORB_PATH_DONE;
+    }
+    const Hit h = trace(q.origin, q.dir);
+    traced = true;
+    return path_resolve(s, st, q, h, last, colour);
 }
 
 // owl::make_rgba: min(255, max(0, int(f * 256))) per channel, alpha 0xff.

@@ -157,7 +157,11 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
     t.best.u = t.best.v = 0.f;
     t.best.prim = -1;
     t.sp = 0;
-    t.cur = s.n_tris == 0 ? ORB_TRAVERSAL_DONE : s.root_ref;
+    // A ray with a NaN component can never pass tri_test (every comparison there is false), but the
+    // slab test would ACCEPT every box for it (fminf/fmaxf drop NaNs) and walk the whole tree:
+    // the literal path tracer produces such rays (NaN sources Q16/Q17).  Miss at once.
+    const float chk = (o.x + o.y + o.z) + (d.x + d.y + d.z);
+    t.cur = (s.n_tris == 0 || chk != chk) ? ORB_TRAVERSAL_DONE : s.root_ref;
 }
 
 // One inner node (t.cur >= 0): both child boxes of a 64-byte node, near child next, far pushed.
