@@ -255,7 +255,15 @@ k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, 
 // is ~3 % of the kernel's time at the measured copy rate.
 // ---------------------------------------------------------------------------------------------
 #define STREAM_CHUNK 128u
-#define STREAM_BURST 8
+
+// (Tried and removed: longest-first scheduling by the ray's chord through the scene bounds, two
+// bins filled by warp-aggregated atomics.  It cost 0.07 ms of coherence on the shadow stage and
+// gained nothing: the per-launch floor was not late long rays but the chunk granularity, fixed by
+// the guided chunk sizes in k_trace_stream.)
+__device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsigned id, float3 o, float3 d) {
+    st_stream(rays + 2 * (size_t)id, make_float4(o.x, o.y, o.z, 0.f));
+    st_stream(rays + 2 * (size_t)id + 1, make_float4(d.x, d.y, d.z, 0.f));
+}
 
 #define LOCAL_STACK_MAX 64
 template <bool LOCAL_STACK>
@@ -290,16 +298,28 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
             const unsigned need = __popc(want);
             const unsigned left = w_end - w_next;
             unsigned base = w_next;
+            unsigned chunk = STREAM_CHUNK;
             if (left < need) {  // uniform: claim another chunk, finish the old range first
-                if (lane == 0) base = atomicAdd(cursor, STREAM_CHUNK);
+                // Guided self-scheduling: chunks shrink (128 -> 32 rays) as the stream runs dry, so a
+                // small launch or the end of a large one is spread over all resident warps instead of
+                // being served 4 rounds deep by the few warps that grabbed the last full chunks
+                // (ncu, PATH bounces 2-7: 0.4 ms each for a few 10k rays before this).
+                if (lane == 0) {
+                    const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
+                    const unsigned rem = n > seen ? n - seen : 0u;
+                    const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
+                    chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
+                    base = atomicAdd(cursor, chunk);
+                }
                 base = __shfl_sync(FULL, base, 0);
+                chunk = __shfl_sync(FULL, chunk, 0);
             }
             const unsigned rank = __popc(want & ((1u << lane) - 1u));
             if (idle && !exhausted) {
                 const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
                 if (idx < n) {
-                    ray = idx;
                     const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
+                    ray = idx;
                     trav_begin(t, s, v3(ro), v3(rd));
                 } else {
                     exhausted = true;
@@ -309,7 +329,7 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
                 w_next += need;
             } else {
                 w_next = base + (need - left);
-                w_end = base + STREAM_CHUNK;
+                w_end = base + chunk;
             }
         }
         if (__ballot_sync(FULL, t.cur != ORB_TRAVERSAL_DONE) == 0u) break;
@@ -344,8 +364,7 @@ k_shadow_gen(SceneView s, FrameView f, int frame_id, int spp, float4* __restrict
         Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
         rng_skip(rng, 2 + 5 * (int)k);  // two jitter draws, five per earlier sample
         const ShadowSample q = shadow_ray_setup(s, v3(pp), v3(nn), rng);
-        st_stream(rays + 2 * (size_t)r, make_float4(q.origin.x, q.origin.y, q.origin.z, 0.f));
-        st_stream(rays + 2 * (size_t)r + 1, make_float4(q.L.x, q.L.y, q.L.z, 0.f));
+        stream_put_ray(rays, r, q.origin, q.L);
     }
 }
 
@@ -463,6 +482,95 @@ k_path_bounce(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce
     }
     for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
     if (lane == 0 && rays) atomicAdd(&f.cnt->rays_bounce, (unsigned long long)rays);
+}
+
+// ---- ray-stream form of one bounce: k_path_gen -> k_trace_stream -> k_path_shade ----------------
+template <bool FIRST>
+__device__ __forceinline__ void path_load_state(const FrameView& f, float3 cam_pos, const PathBuffers& in, unsigned i,
+                                                PathState& st, size_t& ofs) {
+    if (FIRST) {
+        ofs = f.queue[i];
+        const float4 pp = ld_stream(f.position + ofs), nn = ld_stream(f.normal + ofs);
+        const float4 dd = ld_stream(f.albedo + ofs), aa = ld_stream(f.alpha + ofs);
+        st.p = v3(pp);
+        st.n = v3(nn);
+        st.diffuse = v3(dd);
+        st.alpha = aa.x;
+        st.V = normalize(cam_pos - st.p);  // si.wo
+        st.tp = v3(1.f);
+    } else {
+        const float4 a = in.s[0][i], b = in.s[1][i], c = in.s[2][i], d = in.s[3][i], e = in.s[4][i];
+        st.p = v3(a);
+        st.alpha = a.w;
+        st.n = v3(b);
+        ofs = (size_t)__float_as_uint(b.w);
+        st.diffuse = v3(c);
+        st.V = v3(d);
+        st.tp = v3(e);
+    }
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(256)
+k_path_gen(FrameView f, float3 cam_pos, int frame_id, int bounce, PathBuffers in, int in_slot, float4* __restrict__ rays) {
+    const unsigned n = FIRST ? f.cnt->queue_n : f.cnt->path_n[in_slot];
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        PathState st;
+        size_t ofs;
+        path_load_state<FIRST>(f, cam_pos, in, i, st, ofs);
+        const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+        Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+        rng_skip(rng, 2 + 5 * bounce);
+        const PathSample q = path_ray_setup(st, rng);
+        stream_put_ray(rays, i, q.origin, q.dir);
+    }
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(128)
+k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce, int last, PathBuffers in, PathBuffers out,
+             int in_slot, const float4* __restrict__ hits) {
+    const unsigned n = FIRST ? f.cnt->queue_n : f.cnt->path_n[in_slot];
+    const int lane = threadIdx.x & 31;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&f.cnt->rays_bounce, (unsigned long long)n);
+    const unsigned n_round = (n + 31u) & ~31u;  // whole warps reach the ballot
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        bool survive = false;
+        PathState st;
+        size_t ofs = 0;
+        if (i < n) {
+            path_load_state<FIRST>(f, cam_pos, in, i, st, ofs);
+            const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+            Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+            rng_skip(rng, 2 + 5 * bounce);
+            const PathSample q = path_ray_setup(st, rng);  // same arithmetic as k_path_gen
+            const float4 hr = ld_stream(hits + i);
+            Hit h;
+            h.prim = __float_as_int(hr.x);
+            h.u = hr.y;
+            h.v = hr.z;
+            h.t = hr.w;
+            float3 colour;
+            if (path_resolve(s, st, q, h, last != 0, colour) == ORB_PATH_DONE)
+                st_stream(f.colour + ofs, make_float4(colour.x, colour.y, colour.z, 1.f));
+            else
+                survive = true;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, survive);
+        if (m) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&f.cnt->path_n[in_slot ^ 1], (unsigned)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (survive) {
+                const unsigned o = base + __popc(m & ((1u << lane) - 1u));
+                out.s[0][o] = make_float4(st.p.x, st.p.y, st.p.z, st.alpha);
+                out.s[1][o] = make_float4(st.n.x, st.n.y, st.n.z, __uint_as_float((unsigned)ofs));
+                out.s[2][o] = make_float4(st.diffuse.x, st.diffuse.y, st.diffuse.z, 0.f);
+                out.s[3][o] = make_float4(st.V.x, st.V.y, st.V.z, 0.f);
+                out.s[4][o] = make_float4(st.tp.x, st.tp.y, st.tp.z, 0.f);
+            }
+        }
+    }
 }
 
 __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
@@ -1141,6 +1249,24 @@ static int ensure_stream(OrbContext* c, size_t n_rays) {
     return ORB_OK;
 }
 
+// closest hits of the rays in c->stream_rays -> c->stream_hits; the ray count is *n_items * mult on the device
+static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned mult) {
+    cudaStream_t st = c->stream;
+    CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
+    if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
+        const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
+        k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
+                                                        c->stream_cursor, c->refill_min, c->leaf_min, c->height);
+    } else {
+        const size_t smem = trace_smem(c);
+        const int g = persistent_grid(c, k_trace_stream<false>, TRACE_BLOCK, smem);
+        k_trace_stream<false><<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
+                                                             c->stream_cursor, c->refill_min, c->leaf_min, c->height);
+    }
+    c->counters.kernel_launches++;
+    return ORB_OK;
+}
+
 static int ensure_path_state(OrbContext* c) {
     if (c->path_state[0][0]) return ORB_OK;
     const size_t n = (size_t)c->W * c->H;
@@ -1203,21 +1329,11 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
             StageTimer tm(c, ORB_STAGE_SHADOW, 3);
             const int n_lights = (int)c->h_lights.size();
             if (n_lights > 0) {
-                CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
                 const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
                 k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
-                if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
-                    const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
-                    k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, &c->cnt->queue_n,
-                                                                    (unsigned)spp, c->stream_cursor, c->refill_min,
-                                                                    c->leaf_min, c->height);
-                } else {
-                    const int g = persistent_grid(c, k_trace_stream<false>, TRACE_BLOCK, smem);
-                    k_trace_stream<false><<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits,
-                                                                         &c->cnt->queue_n, (unsigned)spp, c->stream_cursor,
-                                                                         c->refill_min, c->leaf_min, c->height);
-                }
-                c->counters.kernel_launches += 2;
+                rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp);
+                if (rc) return rc;
+                c->counters.kernel_launches++;
             }
             const int gr = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);
             k_shadow_resolve<<<gr, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->stream_hits);
@@ -1228,25 +1344,51 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     if (renderer == ORB_PATH) {
         int rc = ensure_path_state(c);
         if (rc) return rc;
-        StageTimer tm(c, ORB_STAGE_PATH, 2 * depth - 1);
+        const bool stream = mode == ORB_MODE_INTENDED && !(cfg->flags & ORB_RENDER_FUSED_SHADOW);
+        StageTimer tm(c, ORB_STAGE_PATH, stream ? 4 * depth - 1 : 2 * depth - 1);
         PathBuffers pb[2];
         for (int a = 0; a < 2; a++)
             for (int b = 0; b < 5; b++) pb[a].s[b] = c->path_state[a][b];
+        const size_t npx = (size_t)(y1 - y0) * c->W;
+        if (stream) {
+            rc = ensure_stream(c, npx);
+            if (rc) return rc;
+        }
         const int g1 = persistent_grid(c, k_path_bounce<true>, TRACE_BLOCK, smem);
         const int g2 = persistent_grid(c, k_path_bounce<false>, TRACE_BLOCK, smem);
+        const int gg = (int)std::min<size_t>((npx + 255) / 256, (size_t)c->n_sm * 8);
+        const int gs = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);
         for (int b = 0; b < depth; b++) {
             const int last = b == depth - 1;
             const int in_slot = b & 1;  // bounce b reads path_n[in_slot] (b > 0), writes path_n[in_slot ^ 1]
-            if (b == 0) {
+            if (b > 0) {
+                k_reset_slot<<<1, 1, 0, st>>>(c->cnt, in_slot ^ 1);
+                c->counters.kernel_launches++;
+            }
+            if (stream) {  // generate -> persistent traversal with refill -> shade + compaction
+                if (b == 0) {
+                    k_path_gen<true><<<gg, 256, 0, st>>>(f, c->cam.pos, frame_id, b, pb[0], in_slot, c->stream_rays);
+                    rc = launch_trace_stream(c, &c->cnt->queue_n, 1u);
+                    if (rc) return rc;
+                    k_path_shade<true><<<gs, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, b, last, pb[0], pb[1], in_slot,
+                                                           c->stream_hits);
+                } else {
+                    k_path_gen<false><<<gg, 256, 0, st>>>(f, c->cam.pos, frame_id, b, pb[in_slot], in_slot, c->stream_rays);
+                    rc = launch_trace_stream(c, &c->cnt->path_n[in_slot], 1u);
+                    if (rc) return rc;
+                    k_path_shade<false><<<gs, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, b, last, pb[in_slot],
+                                                            pb[in_slot ^ 1], in_slot, c->stream_hits);
+                }
+                c->counters.kernel_launches += 2;
+            } else if (b == 0) {
                 k_path_bounce<true><<<g1, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, b, mode, last, pb[0],
                                                                     pb[1], in_slot, c->height);
+                c->counters.kernel_launches++;
             } else {
-                k_reset_slot<<<1, 1, 0, st>>>(c->cnt, in_slot ^ 1);
                 k_path_bounce<false><<<g2, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, b, mode, last,
                                                                      pb[in_slot], pb[in_slot ^ 1], in_slot, c->height);
                 c->counters.kernel_launches++;
             }
-            c->counters.kernel_launches++;
         }
     }
     {
