@@ -255,6 +255,7 @@ k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, 
 // is ~3 % of the kernel's time at the measured copy rate.
 // ---------------------------------------------------------------------------------------------
 #define STREAM_CHUNK 128u
+#define STREAM_BURST 8
 
 // (Tried and removed: longest-first scheduling by the ray's chord through the scene bounds, two
 // bins filled by warp-aggregated atomics.  It cost 0.07 ms of coherence on the shadow stage and
