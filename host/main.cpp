@@ -1,0 +1,281 @@
+// orb_render -- headless host of the B200 hot path.
+//
+// Takes the place of src/hostCode.cpp:8-55 + the non-window parts of include/viewer.hpp: parses
+// the reference's scene JSON, ingests its OBJ/MTL files, builds the light list and the camera
+// vectors, drives liborb200.so through the C-ABI (include/orb200.h) where the reference drives
+// OWL, and writes what the reference's mouse-click dump writes (viewer.hpp:715-800: raw float4
+// `.btc` buffers under the same file names, consumed by save.py / ltc_ratio_estimator.py) plus
+// a binary PPM of the RGBA8 frame.  No window, no GL, no ImGui: frames are rendered for a fixed
+// count instead of until the window closes (Viewer::render, viewer.hpp:553-568, once per frame).
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+
+#include <chrono>
+#include <string>
+#include <vector>
+
+#include "scene_io.h"
+
+using namespace orbhost;
+
+static const char* kRendererNames[] = {"diffuse", "alpha", "normals", "shade_normals", "position", "mask",
+                                       "material_id", "ltc_baseline", "ratio", "path"};
+
+static void usage() {
+    fprintf(stderr,
+            "usage: orb_render SCENE.json [options]\n"
+            "  --out DIR            output directory (default: saves)\n"
+            "  --renderer N|NAME    0..9 or diffuse|alpha|normals|shade_normals|position|mask|material_id|\n"
+            "                       ltc_baseline|ratio|path (default: the scene's renderers[0], else path like\n"
+            "                       src/hostCode.cpp:32)\n"
+            "  --frames N           frames to accumulate, accumId = 0..N-1 (default: the scene's spp)\n"
+            "  --size WxH           frame size (default: the scene's width x height)\n"
+            "  --camera I           index into the scene's cameras (default 0)\n"
+            "  --mode literal|intended   committed source vs patches P1-P3 (default intended)\n"
+            "  --shadow-spp N       RATIO shadow samples per pixel per frame (default 4, deviceCode.cu:128)\n"
+            "  --depth N            PATH bounces (default 8; literal mode fixes 1)\n"
+            "  --denoise            RATIO: a-trous denoise of stoDirect/stoNoVis + ratio combine\n"
+            "  --lut FILE.npy       LTC table (default: optix_renderer_b200/data/ltc_isotropic_8x8.npy)\n"
+            "  --device D           CUDA device (default 0)\n"
+            "  --dump-scene         print a JSON summary of the parsed scene and exit (no GPU needed)\n");
+}
+
+static bool write_file(const std::string& path, const void* data, size_t bytes) {
+    FILE* fp = fopen(path.c_str(), "wb");
+    if (!fp) return false;
+    const bool ok = fwrite(data, 1, bytes, fp) == bytes;
+    fclose(fp);
+    return ok;
+}
+
+// Viewer::savebuffer, viewer.hpp:695-713: the raw float4 buffer, every float divided by avg_factor
+static bool save_btc(OrbContext* ctx, int buffer_id, const std::string& path, int avg_factor, std::vector<float>& tmp) {
+    const size_t bytes = orb_buffer_bytes(ctx, buffer_id);
+    tmp.resize(bytes / 4);
+    if (orb_buffer_download(ctx, buffer_id, tmp.data(), bytes)) return false;
+    for (auto& x : tmp) x = x / (float)avg_factor;
+    return write_file(path, tmp.data(), bytes);
+}
+
+static bool save_ppm(OrbContext* ctx, int W, int H, const std::string& path) {
+    std::vector<uint32_t> px((size_t)W * H);
+    if (orb_buffer_download(ctx, ORB_BUF_RGBA8, px.data(), px.size() * 4)) return false;
+    std::vector<unsigned char> rgb((size_t)3 * W * H);
+    for (int y = 0; y < H; y++)  // buffer row 0 is the bottom image row
+        for (int x = 0; x < W; x++) {
+            const uint32_t p = px[(size_t)(H - 1 - y) * W + x];
+            unsigned char* d = &rgb[3 * ((size_t)y * W + x)];
+            d[0] = p & 255; d[1] = (p >> 8) & 255; d[2] = (p >> 16) & 255;
+        }
+    char hd[64];
+    const int n = snprintf(hd, sizeof hd, "P6\n%d %d\n255\n", W, H);
+    FILE* fp = fopen(path.c_str(), "wb");
+    if (!fp) return false;
+    fwrite(hd, 1, n, fp);
+    fwrite(rgb.data(), 1, rgb.size(), fp);
+    fclose(fp);
+    return true;
+}
+
+static unsigned long long fnv1a(const void* p, size_t n, unsigned long long h = 1469598103934665603ull) {
+    const unsigned char* b = (const unsigned char*)p;
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+
+static void dump_scene(const Scene& sc, int W, int H, int cam_i) {
+    const std::vector<OrbTriLight> lights = build_tri_lights(sc);
+    float pos[3], d00[3], du[3], dv[3];
+    camera_vectors(sc.cameras[cam_i], W, H, pos, d00, du, dv);
+    printf("{\"spp\": %d, \"width\": %d, \"height\": %d, \"renderers\": [", sc.spp, sc.width, sc.height);
+    for (size_t i = 0; i < sc.renderers.size(); i++) printf("%s%d", i ? ", " : "", sc.renderers[i]);
+    printf("], \"n_cameras\": %zu, \"n_surface_meshes\": %zu, \"meshes\": [", sc.cameras.size(), sc.n_surface_meshes);
+    for (size_t i = 0; i < sc.meshes.size(); i++) {
+        const Mesh& m = sc.meshes[i];
+        printf("%s{\"triangles\": %zu, \"material_id\": %u, \"is_light\": %s, \"diffuse\": [%.9g, %.9g, %.9g], \"alpha\": %.9g, "
+               "\"emit\": [%.9g, %.9g, %.9g], \"tex\": [%d, %d], \"vertex_hash\": \"%016llx\", \"normal_hash\": \"%016llx\", "
+               "\"texcoord_hash\": \"%016llx\"}",
+               i ? ", " : "", m.index.size() / 3, m.material_id, m.is_light ? "true" : "false", m.diffuse[0], m.diffuse[1],
+               m.diffuse[2], m.alpha, m.emit[0], m.emit[1], m.emit[2], m.tex_w, m.tex_h,
+               fnv1a(m.vertex.data(), m.vertex.size() * 4), fnv1a(m.normal.data(), m.normal.size() * 4),
+               fnv1a(m.texcoord.data(), m.texcoord.size() * 4));
+    }
+    printf("], \"n_tri_lights\": %zu, \"tri_lights_hash\": \"%016llx\", \"camera\": {\"pos\": [%.9g, %.9g, %.9g], "
+           "\"d00\": [%.9g, %.9g, %.9g], \"du\": [%.9g, %.9g, %.9g], \"dv\": [%.9g, %.9g, %.9g]}}\n",
+           lights.size(), fnv1a(lights.data(), lights.size() * sizeof(OrbTriLight)), pos[0], pos[1], pos[2], d00[0], d00[1],
+           d00[2], du[0], du[1], du[2], dv[0], dv[1], dv[2]);
+}
+
+#define ORB_CHECK(call)                                                        \
+    do {                                                                       \
+        if ((call) != ORB_OK) {                                                \
+            fprintf(stderr, "orb_render: %s: %s\n", #call, orb_last_error()); \
+            return 2;                                                          \
+        }                                                                      \
+    } while (0)
+
+int main(int argc, char** argv) {
+    std::string scene_file, out_dir = "saves", lut_path, renderer_arg, mode_arg = "intended";
+    int frames = -1, W = 0, H = 0, cam_i = 0, shadow_spp = 4, depth = 8, device = 0;
+    bool denoise = false, only_dump = false;
+    for (int i = 1; i < argc; i++) {
+        const std::string a = argv[i];
+        auto next = [&](const char* what) -> const char* {
+            if (i + 1 >= argc) {
+                fprintf(stderr, "orb_render: %s needs a value\n", what);
+                exit(1);
+            }
+            return argv[++i];
+        };
+        if (a == "--out") out_dir = next("--out");
+        else if (a == "--renderer") renderer_arg = next("--renderer");
+        else if (a == "--frames") frames = atoi(next("--frames"));
+        else if (a == "--size") {
+            if (sscanf(next("--size"), "%dx%d", &W, &H) != 2 || W <= 0 || H <= 0) { usage(); return 1; }
+        }
+        else if (a == "--camera") cam_i = atoi(next("--camera"));
+        else if (a == "--mode") mode_arg = next("--mode");
+        else if (a == "--shadow-spp") shadow_spp = atoi(next("--shadow-spp"));
+        else if (a == "--depth") depth = atoi(next("--depth"));
+        else if (a == "--denoise") denoise = true;
+        else if (a == "--lut") lut_path = next("--lut");
+        else if (a == "--device") device = atoi(next("--device"));
+        else if (a == "--dump-scene") only_dump = true;
+        else if (a == "-h" || a == "--help") { usage(); return 0; }
+        else if (!a.empty() && a[0] != '-' && scene_file.empty()) scene_file = a;
+        else { fprintf(stderr, "orb_render: unknown argument %s\n", a.c_str()); usage(); return 1; }
+    }
+    if (scene_file.empty()) { usage(); return 1; }
+    if (mode_arg != "literal" && mode_arg != "intended") { usage(); return 1; }
+
+    fprintf(stderr, "Loading scene %s\n", scene_file.c_str());
+    Scene scene;
+    std::string err;
+    if (!parse_scene(scene_file, scene, &err)) {
+        fprintf(stderr, "%s\nError loading scene\n", err.c_str());
+        return -1;  // src/hostCode.cpp:23-27
+    }
+    if (W == 0) { W = scene.width; H = scene.height; }
+    if (cam_i < 0 || cam_i >= (int)scene.cameras.size()) { fprintf(stderr, "orb_render: no camera %d\n", cam_i); return 1; }
+    if (only_dump) { dump_scene(scene, W, H, cam_i); return 0; }
+
+    int renderer = scene.renderers.empty() ? ORB_PATH : scene.renderers[0];
+    if (!renderer_arg.empty()) {
+        renderer = -1;
+        for (int k = 0; k < 10; k++)
+            if (renderer_arg == kRendererNames[k]) renderer = k;
+        if (renderer < 0 && isdigit((unsigned char)renderer_arg[0])) renderer = atoi(renderer_arg.c_str());
+    }
+    if (renderer < 0 || renderer > ORB_PATH) { fprintf(stderr, "orb_render: bad renderer\n"); return 1; }
+    if (frames <= 0) frames = scene.spp > 0 ? scene.spp : 1;
+
+    // ---- LTC table ----
+    if (lut_path.empty()) {
+        std::string exe = argv[0];
+        size_t k = exe.rfind('/');
+        const std::string here = k == std::string::npos ? "./" : exe.substr(0, k + 1);
+        lut_path = here + "../optix_renderer_b200/data/ltc_isotropic_8x8.npy";
+    }
+    std::vector<float> m1, m2, m3;
+    int lw = 0, lh = 0;
+    if (!load_ltc_lut_npy(lut_path, m1, m2, m3, lw, lh, &err)) { fprintf(stderr, "orb_render: %s\n", err.c_str()); return 1; }
+
+    // ---- upload: what the Viewer constructor does through OWL (viewer.hpp:163-551) ----
+    OrbContext* ctx = nullptr;
+    ORB_CHECK(orb_create(device, &ctx));
+    size_t n_tris = 0;
+    for (const Mesh& m : scene.meshes) {
+        OrbMeshDesc d;
+        memset(&d, 0, sizeof d);
+        d.vertex = m.vertex.data(); d.normal = m.normal.data(); d.texcoord = m.texcoord.data();
+        d.n_vertices = (int32_t)(m.vertex.size() / 3);
+        d.index = m.index.data();
+        d.n_triangles = (int32_t)(m.index.size() / 3);
+        for (int a = 0; a < 3; a++) { d.diffuse[a] = m.diffuse[a]; d.emit[a] = m.emit[a]; }
+        d.alpha = m.alpha;
+        d.is_light = m.is_light ? 1 : 0;
+        d.material_id = m.material_id;
+        if (!m.tex.empty()) { d.diffuse_tex_rgba8 = m.tex.data(); d.tex_w = m.tex_w; d.tex_h = m.tex_h; }
+        ORB_CHECK(orb_scene_add_mesh(ctx, &d));
+        n_tris += d.n_triangles;
+    }
+    const std::vector<OrbTriLight> lights = build_tri_lights(scene);
+    ORB_CHECK(orb_scene_set_lights(ctx, lights.data(), (int32_t)lights.size()));
+    ORB_CHECK(orb_scene_set_ltc_lut(ctx, m1.data(), m2.data(), m3.data(), lw, lh, 0));
+    const auto t_build0 = std::chrono::steady_clock::now();
+    ORB_CHECK(orb_scene_commit(ctx, nullptr));
+    ORB_CHECK(orb_sync(ctx));
+    const double build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build0).count();
+    ORB_CHECK(orb_resize(ctx, W, H));
+    float pos[3], d00[3], du[3], dv[3];
+    camera_vectors(scene.cameras[cam_i], W, H, pos, d00, du, dv);
+    ORB_CHECK(orb_set_camera(ctx, pos, d00, du, dv));
+    fprintf(stderr, "framebuffer reso %d %d; %zu meshes, %zu triangles, %zu triangle lights; BVH build %.2f ms\n", W, H,
+            scene.meshes.size(), n_tris, lights.size(), build_ms);
+
+    // ---- frames: Viewer::render once per frame, accumId = 0, 1, ... ----
+    OrbRenderConfig cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.renderer_type = renderer;
+    cfg.mode = mode_arg == "intended" ? 1 : 0;
+    cfg.shadow_spp = shadow_spp;
+    cfg.max_depth = depth;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int f = 0; f < frames; f++) {
+        cfg.accum_id = f;
+        ORB_CHECK(orb_render_async(ctx, &cfg));
+    }
+    if (renderer == ORB_RATIO && denoise) {
+        ORB_CHECK(orb_denoise(ctx, nullptr, 0, 0));
+        ORB_CHECK(orb_ratio_combine(ctx, 1, 0, 0));
+    }
+    ORB_CHECK(orb_sync(ctx));
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    OrbCounters cnt;
+    ORB_CHECK(orb_get_counters(ctx, &cnt));
+    const double rays = (double)cnt.rays_primary + (double)cnt.rays_shadow_total + (double)cnt.rays_bounce_total;
+    fprintf(stderr, "%s: %d frame(s) in %.2f ms (%.2f ms/frame, %.1f Mrays/s), %llu NaN pixels in the last frame\n",
+            kRendererNames[renderer], frames, ms, ms / frames, rays / (ms * 1e-3) / 1e6, (unsigned long long)cnt.nan_pixels);
+
+    // ---- dumps: Viewer::mouseButtonLeft, viewer.hpp:715-800 (same names, same avg_factor) ----
+    mkdir(out_dir.c_str(), 0777);
+    const std::string o = out_dir + "/";
+    std::vector<float> tmp;
+    const int accum = frames;  // Viewer::accumId after `frames` calls of render()
+    bool ok = true;
+    if (renderer == ORB_RATIO) {
+        ok &= save_btc(ctx, ORB_BUF_STO_DIRECT, o + "stoDirect.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_STO_NO_VIS, o + "stoNoVis.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_LTC, o + "ltc.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_NORMAL, o + "normal_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_MATERIAL_ID, o + "materialID_screen_buffer.btc", 1, tmp);
+        if (denoise) {  // the inputs ltc_ratio_estimator.py:5-6 expects from an external denoiser, and its output
+            ok &= save_btc(ctx, ORB_BUF_STO_DIRECT_DN, o + "stodirectDenoise.btc", 1, tmp);
+            ok &= save_btc(ctx, ORB_BUF_STO_NO_VIS_DN, o + "stoNoVisDenoise.btc", 1, tmp);
+            ok &= save_btc(ctx, ORB_BUF_RATIO_FINAL, o + "final_ratio_estimator.btc", 1, tmp);
+        }
+    } else if (renderer == ORB_PATH) {
+        ok &= save_btc(ctx, ORB_BUF_POSITION, o + "position_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_NORMAL, o + "normal_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_UV, o + "uv_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_ALPHA, o + "alpha_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_ALBEDO, o + "albedo_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_MATERIAL_ID, o + "materialID_screen_buffer.btc", 1, tmp);
+        ok &= save_btc(ctx, ORB_BUF_BOUNCE0, o + "bounce0_screen_buffer.btc", accum, tmp);
+        ok &= save_btc(ctx, ORB_BUF_BOUNCE1, o + "bounce1_screen_buffer.btc", accum, tmp);
+        ok &= save_btc(ctx, ORB_BUF_BOUNCE2, o + "bounce2_screen_buffer.btc", accum, tmp);
+        ok &= save_btc(ctx, ORB_BUF_ACCUM, o + "path.btc", accum, tmp);
+    } else if (renderer == ORB_LTC_BASELINE) {
+        ok &= save_btc(ctx, ORB_BUF_ACCUM, o + "ltc_baseline.btc", 1, tmp);
+    } else {  // debug AOVs: not dumped by the reference; the accumulated frame is the useful output
+        ok &= save_btc(ctx, ORB_BUF_ACCUM, o + std::string(kRendererNames[renderer]) + ".btc", accum, tmp);
+    }
+    ok &= save_ppm(ctx, W, H, o + "rendered_output.ppm");
+    orb_destroy(ctx);
+    if (!ok) { fprintf(stderr, "orb_render: writing to %s failed\n", out_dir.c_str()); return 3; }
+    fprintf(stderr, "wrote %s\n", out_dir.c_str());
+    return 0;
+}

@@ -61,7 +61,9 @@ def camera_from_lookat(frm, at, up, cos_fovy, width, height):
     ddv = (F(cos_fovy) * _norm(np.cross(ddu, d00).astype(F))).astype(F)
     d00 = (d00 - F(0.5) * ddu).astype(F)
     d00 = (d00 - F(0.5) * ddv).astype(F)
-    return {"pos": frm.copy(), "d00": d00, "du": ddu, "dv": ddv}
+    return {"pos": frm.copy(), "d00": d00, "du": ddu, "dv": ddv,
+            "lookat": {"from": [float(x) for x in frm], "to": [float(x) for x in at], "up": [float(x) for x in up],
+                       "cos_fovy": float(cos_fovy)}}
 
 
 def make_mesh(tri_pos, tri_nrm, tri_uv, diffuse, alpha, emit=(0, 0, 0), is_light=False, material_id=1, tex=None):
@@ -253,3 +255,83 @@ def scene_synthetic(n_tris=1_000_000, n_quad_lights=16, width=1920, height=1080,
             cnt += 1
     cam = camera_from_lookat((13, -13, 9), (0, 0, 0.5), (0, 0, 1), .66, width, height)
     return finish(meshes, cam, width, height)
+
+
+# ------------------------------------------------------------------------------------------------
+# Reference file formats: scene JSON (src/scene.cpp:38-98) + OBJ/MTL as src/Model.cpp:130-252 reads
+# them.  Used to feed the headless C++ host (host/orb_render) the same scenes the Python harness builds.
+# ------------------------------------------------------------------------------------------------
+def _g(x):
+    return "%.9g" % float(x)
+
+
+def _write_obj(path, meshes, light_file):
+    """One `o` shape + one material per mesh; material k of the .mtl gets materialID k + 1 in the
+    loader (Model.cpp:222), so surface materials are written at index material_id - 1."""
+    mtl = os.path.splitext(path)[0] + ".mtl"
+    if light_file:
+        mats = list(range(len(meshes)))
+        slot = {i: i for i in mats}
+    else:
+        n = max(m["material_id"] for m in meshes)
+        mats = [None] * n
+        slot = {}
+        for i, m in enumerate(meshes):
+            k = m["material_id"] - 1
+            assert k >= 0, "surface meshes need material_id >= 1"
+            if mats[k] is not None:
+                o = meshes[mats[k]]
+                assert np.array_equal(o["diffuse"], m["diffuse"]) and o["alpha"] == m["alpha"], "material id reused"
+            else:
+                mats[k] = i
+            slot[i] = k
+    with open(mtl, "w") as f:
+        for k, i in enumerate(mats):
+            f.write("newmtl m%d\n" % k)
+            if i is None:
+                f.write("Kd 0 0 0\nNs 1\nKe 0 0 0\n")
+                continue
+            m = meshes[i]
+            f.write("Kd %s %s %s\nNs %s\nKe %s %s %s\n" % (*map(_g, m["diffuse"]), _g(m["alpha"]), *map(_g, m["emit"])))
+            if m.get("tex") is not None:
+                tex = np.asarray(m["tex"], np.uint8)
+                name = os.path.basename(os.path.splitext(path)[0]) + "_tex%d.ppm" % k
+                with open(os.path.join(os.path.dirname(path), name), "wb") as t:
+                    t.write(b"P6\n%d %d\n255\n" % (tex.shape[1], tex.shape[0]))
+                    t.write(np.ascontiguousarray(tex[::-1, :, :3]).tobytes())  # file rows top-down; loader mirrors y
+                f.write("map_Kd %s\n" % name)
+    with open(path, "w") as f:
+        f.write("mtllib %s\n" % os.path.basename(mtl))
+        base = 0
+        for i, m in enumerate(meshes):
+            f.write("o mesh%d\nusemtl m%d\n" % (i, slot[i]))
+            for v in m["vtx"]:
+                f.write("v %s %s %s\n" % tuple(map(_g, v)))
+            for v in m["nrm"]:
+                f.write("vn %s %s %s\n" % tuple(map(_g, v)))
+            for v in m["uv"]:
+                f.write("vt %s %s\n" % tuple(map(_g, v)))
+            for a, b, c in m["idx"]:
+                f.write("f %d/%d/%d %d/%d/%d %d/%d/%d\n" % ((base + a + 1,) * 3 + (base + b + 1,) * 3 + (base + c + 1,) * 3))
+            base += len(m["vtx"])
+
+
+def export_scene(scene, directory, name="scene", spp=1, renderers=(8,)):
+    """Write `scene` as name.json + name_surface.obj/.mtl + name_lights.obj/.mtl; returns the JSON path."""
+    import json
+
+    os.makedirs(directory, exist_ok=True)
+    surf = [m for m in scene["meshes"] if not m["is_light"]]
+    lights = [m for m in scene["meshes"] if m["is_light"]]
+    s_obj = os.path.join(directory, name + "_surface.obj")
+    l_obj = os.path.join(directory, name + "_lights.obj")
+    _write_obj(s_obj, surf, False)
+    _write_obj(l_obj, lights, True)
+    la = scene["camera"]["lookat"]
+    doc = {"spp": spp, "width": scene["width"], "height": scene["height"], "renderers": list(renderers),
+           "cameras": [{"from": la["from"], "to": la["to"], "up": la["up"], "cos_fovy": la["cos_fovy"]}],
+           "surface_geometry": os.path.basename(s_obj), "area_lights": os.path.basename(l_obj)}
+    path = os.path.join(directory, name + ".json")
+    with open(path, "w") as f:
+        json.dump(doc, f, indent=1)
+    return path

@@ -1,0 +1,180 @@
+"""The headless C++ host (host/orb_render): reference file formats in, reference dump formats out.
+
+CPU: the host parses scene JSON + OBJ/MTL written by scenes.export_scene() and must arrive at exactly the
+arrays the Python harness hands to the C-ABI (mesh order, un-indexed corners, material mapping of
+src/Model.cpp:204-223, light list of include/viewer.hpp:236-265, camera of :635-641), and must fail the
+way parseScene does (src/scene.cpp:20-101).  GPU: `.btc` dumps of the host equal the frames rendered
+through the ctypes binding, byte for byte."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from optix_renderer_b200 import scenes
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "host", "orb_render")
+
+
+def fnv1a(a):
+    h = 1469598103934665603
+    for b in np.ascontiguousarray(a).view(np.uint8).ravel().tolist():
+        h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return "%016x" % h
+
+
+@pytest.fixture(scope="module")
+def host():
+    if not os.path.exists(HOST):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "host")])
+    return HOST
+
+
+def dump(host, path, *extra):
+    o = subprocess.run([host, path, "--dump-scene", *extra], capture_output=True, text=True)
+    return o.returncode, (json.loads(o.stdout) if o.returncode == 0 else None), o.stderr
+
+
+@pytest.mark.parametrize("make", [scenes.scene_floor_blocker, scenes.scene_cornell])
+def test_host_parses_exported_scene(host, tmp_path, make):
+    sc = make(48, 32)
+    path = scenes.export_scene(sc, str(tmp_path), spp=3, renderers=(8, 9))
+    rc, d, err = dump(host, path)
+    assert rc == 0, err
+    assert (d["spp"], d["width"], d["height"], d["renderers"]) == (3, 48, 32, [8, 9])
+    assert len(d["meshes"]) == len(sc["meshes"])
+    assert d["n_surface_meshes"] == sum(not m["is_light"] for m in sc["meshes"])
+    for got, m in zip(d["meshes"], sc["meshes"]):
+        assert got["triangles"] == len(m["idx"])
+        assert got["material_id"] == m["material_id"] and got["is_light"] == m["is_light"]
+        assert np.array_equal(np.float32(got["diffuse"]), m["diffuse"])
+        assert np.float32(got["alpha"]) == np.float32(m["alpha"])
+        assert np.array_equal(np.float32(got["emit"]), m["emit"])
+        assert got["vertex_hash"] == fnv1a(m["vtx"]) and got["normal_hash"] == fnv1a(m["nrm"])
+        assert got["texcoord_hash"] == fnv1a(m["uv"])
+    assert d["n_tri_lights"] == len(sc["tri_lights"])
+    assert d["tri_lights_hash"] == fnv1a(sc["tri_lights"])
+    for k in ("pos", "d00", "du", "dv"):
+        assert np.array_equal(np.float32(d["camera"][k]), sc["camera"][k]), k
+
+
+def test_host_camera_follows_size(host, tmp_path):
+    sc = scenes.scene_floor_blocker(64, 64)
+    path = scenes.export_scene(sc, str(tmp_path))
+    rc, d, err = dump(host, path, "--size", "128x32")
+    assert rc == 0, err
+    ref = scenes.camera_from_lookat(**{k: v for k, v in zip(("frm", "at", "up", "cos_fovy"),
+                                                            [sc["camera"]["lookat"][x] for x in ("from", "to", "up", "cos_fovy")])},
+                                    width=128, height=32)
+    for k in ("pos", "d00", "du", "dv"):
+        assert np.array_equal(np.float32(d["camera"][k]), ref[k]), k
+
+
+def test_host_scene_errors(host, tmp_path):
+    sc = scenes.scene_floor_blocker(16, 16)
+    path = scenes.export_scene(sc, str(tmp_path))
+    doc = json.load(open(path))
+    # missing file
+    rc, _, err = dump(host, str(tmp_path / "nope.json"))
+    assert rc != 0 and "Could not load scene" in err
+    # no cameras (src/scene.cpp:56-74)
+    bad = dict(doc, cameras=[])
+    p = tmp_path / "nocam.json"
+    p.write_text(json.dumps(bad))
+    rc, _, err = dump(host, str(p))
+    assert rc != 0 and "No cameras defined." in err
+    # no renderers (:44-54)
+    bad = {k: v for k, v in doc.items() if k != "renderers"}
+    p = tmp_path / "norend.json"
+    p.write_text(json.dumps(bad))
+    rc, _, err = dump(host, str(p))
+    assert rc != 0 and "No renderers defined." in err
+    # OBJ without normals: the reference dereferences normal_index unconditionally (Model.cpp:193-201)
+    (tmp_path / "flat.obj").write_text("mtllib scene_surface.mtl\nusemtl m0\nv 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    bad = dict(doc, surface_geometry="flat.obj")
+    p = tmp_path / "flat.json"
+    p.write_text(json.dumps(bad))
+    rc, _, err = dump(host, str(p))
+    assert rc != 0 and "v/vt/vn" in err
+    # malformed JSON
+    p = tmp_path / "broken.json"
+    p.write_text("{\"spp\": 1,")
+    rc, _, err = dump(host, str(p))
+    assert rc != 0 and "Could not load scene" in err
+
+
+def test_host_obj_features(host, tmp_path):
+    """Negative (relative) indices, polygon fan, several materials in one shape -> one mesh per
+    (shape, material) in ascending material order, texture through map_Kd."""
+    (tmp_path / "a.mtl").write_text("newmtl red\nKd 1 0 0\nNs 0.5\nnewmtl green\nKd 0 1 0\nNs 0.25\nKe 2 3 4\nmap_Kd t.ppm\n")
+    (tmp_path / "t.ppm").write_bytes(b"P6\n2 1\n255\n" + bytes([255, 0, 0, 0, 255, 0]))
+    (tmp_path / "a.obj").write_text(
+        "mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\n"
+        "o s\nusemtl green\nf 1/1/1 2/2/1 3/3/1 4/4/1\nusemtl red\nf -4/-4/-1 -3/-3/-1 -2/-2/-1\n")
+    (tmp_path / "l.obj").write_text("mtllib a.mtl\nv 0 0 1\nv 1 0 1\nv 0 1 1\nvn 0 0 -1\nvt 0 0\nusemtl green\nf 1/1/1 2/1/1 3/1/1\n")
+    (tmp_path / "s.json").write_text(json.dumps({
+        "spp": 1, "width": 8, "height": 8, "renderers": [9],
+        "cameras": [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 0.66}],
+        "surface_geometry": "a.obj", "area_lights": "l.obj"}))
+    rc, d, err = dump(host, str(tmp_path / "s.json"))
+    assert rc == 0, err
+    red, green, light = d["meshes"]
+    assert (red["material_id"], red["triangles"], red["diffuse"]) == (1, 1, [1, 0, 0])
+    assert (green["material_id"], green["triangles"], green["alpha"], green["tex"]) == (2, 2, 0.25, [2, 1])
+    assert light["is_light"] and light["material_id"] == 0 and light["emit"] == [2, 3, 4]
+    assert d["n_tri_lights"] == 1
+    fan = np.float32([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 0, 0], [1, 1, 0], [0, 1, 0]])
+    assert green["vertex_hash"] == fnv1a(fan)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("renderer,frames", [("ratio", 2), ("path", 3), ("ltc_baseline", 1)])
+def test_host_dumps_equal_binding(host, tmp_path, renderer, frames):
+    from optix_renderer_b200 import api
+
+    sc = scenes.scene_cornell(96, 64)
+    path = scenes.export_scene(sc, str(tmp_path))
+    out = tmp_path / "saves"
+    args = [host, path, "--out", str(out), "--renderer", renderer, "--frames", str(frames), "--depth", "3"]
+    if renderer == "ratio":
+        args.append("--denoise")
+    o = subprocess.run(args, capture_output=True, text=True)
+    assert o.returncode == 0, o.stderr
+    r = api.Renderer(sc)
+    rt = {"ratio": api.RATIO, "path": api.PATH, "ltc_baseline": api.LTC_BASELINE}[renderer]
+    for f in range(frames):
+        r.render(rt, accum_id=f, mode=api.INTENDED, shadow_spp=4, max_depth=3)
+
+    def btc(name):
+        return np.fromfile(str(out / (name + ".btc")), np.float32).reshape(64, 96, 4)
+
+    if renderer == "ratio":
+        r.denoise()
+        r.ratio_combine(use_denoised=True)
+        pairs = [("stoDirect", "sto_direct", 1), ("stoNoVis", "sto_no_vis", 1), ("ltc", "ltc", 1),
+                 ("normal_screen_buffer", "normal", 1), ("materialID_screen_buffer", "materialID", 1),
+                 ("stodirectDenoise", "sto_direct_dn", 1), ("stoNoVisDenoise", "sto_no_vis_dn", 1),
+                 ("final_ratio_estimator", "ratio_final", 1)]
+    elif renderer == "path":
+        pairs = [("path", "accum", frames), ("position_screen_buffer", "position", 1), ("albedo_screen_buffer", "albedo", 1)]
+    else:
+        pairs = [("ltc_baseline", "accum", 1)]
+    for fname, buf, avg in pairs:
+        want = (r.download(buf) / np.float32(avg)).astype(np.float32)
+        assert np.array_equal(btc(fname), want, equal_nan=True), fname
+    # PPM = the RGBA8 frame, top row first
+    raw = (out / "rendered_output.ppm").read_bytes()
+    assert raw.startswith(b"P6\n96 64\n255\n")
+    rgb = np.frombuffer(raw[len(b"P6\n96 64\n255\n"):], np.uint8).reshape(64, 96, 3)
+    px = r.download("rgba8")
+    want = np.stack([px & 255, (px >> 8) & 255, (px >> 16) & 255], -1).astype(np.uint8)[::-1]
+    assert np.array_equal(rgb, want)
+    # the reference's offline pipeline on the dumps: save.py's reshape/flip, ltc_ratio_estimator.py:8
+    if renderer == "ratio":
+        ltc, sd, sn = (np.flipud(btc(n))[..., :3] for n in ("ltc", "stodirectDenoise", "stoNoVisDenoise"))
+        with np.errstate(all="ignore"):
+            final = ltc * (sd / sn)
+        assert np.array_equal(final, np.flipud(btc("final_ratio_estimator"))[..., :3], equal_nan=True)
+    r.close()
