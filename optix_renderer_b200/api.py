@@ -17,7 +17,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liborb200.so")
+LIB_PATH = os.environ.get("ORB200_LIB") or os.path.join(HERE, "liborb200.so")  # env override: A/B builds in tools/
 
 # RendererType, cuda_include/common.cuh:17-29
 DIFFUSE, ALPHA, NORMALS, SHADE_NORMALS, POSITION, MASK, MATERIAL_ID, LTC_BASELINE, RATIO, PATH = range(10)

@@ -220,7 +220,7 @@ ORB_HD float edge_integral(float3 p, float3 q) {
     const float y = fabsf(x);
     const float num = 0.8543985f + (0.4965155f + 0.0145206f * y) * y;
     const float den = 3.4175940f + (4.1616724f + y) * y;
-    const float v = num / den;
+    const float v = orb_fdiv(num, den);  // den in [3.4, 8.6]
     const float w = 0.5f * orb_rsqrt(fmaxf(1.0f - x * x, 1e-7f)) - v;
     const float theta_sintheta = (x > 0.0f) ? v : w;
     return (p.x * q.y - p.y * q.x) * theta_sintheta;
@@ -228,7 +228,7 @@ ORB_HD float edge_integral(float3 p, float3 q) {
 
 // Intersection of segment (lhs, rhs) with the horizon z = 0, pushed back onto the unit sphere.
 ORB_HD float3 horizon_cut(float3 lhs, float3 rhs) {
-    const float s = lhs.z / (lhs.z - rhs.z);
+    const float s = orb_fdiv(lhs.z, lhs.z - rhs.z);
     const float cx = -s * lhs.x + lhs.x, cy = -s * lhs.y + lhs.y;
     return normalize(v3(s * rhs.x + cx, s * rhs.y + cy, 0.f));
 }
@@ -259,6 +259,13 @@ ORB_HD float clipped_form_factor(float3 a, float3 b, float3 c, bool quad, int& n
         n_out = 0;
         return 0.f;
     }
+    if (mask == 7) {  // nothing to clip (the common case: the light is above the horizon): edges ab, bc, ca
+        float s = edge_integral(a, b);
+        s += edge_integral(b, c);
+        s += edge_integral(c, a);
+        n_out = quad ? 4 : 3;
+        return fabsf(s);
+    }
     const float3 ab = horizon_cut(a, b), bc = horizon_cut(b, c), ca = horizon_cut(c, a);
     const bool m5q = mask == 5 && quad;
     const bool four = mask == 3 || mask == 6 || mask == 5;
@@ -281,6 +288,7 @@ struct LtcFrame {
     float3 diffuse;    // si.diffuse
     Mat3 to_local;     // rows c1, c2, n
     Mat3 iso;          // rotation about z that puts wo_local in the xz-plane
+    Mat3 world_to_iso; // iso * to_local: both are rotations, applied as one (see integrate_tri_light)
     Mat3 minv;         // inverse of the fetched LTC matrix
     float amplitude;
     bool valid;        // false: wo_local.z < 0 -> colour 0 (deviceCode.cu:27-28)
@@ -304,20 +312,24 @@ ORB_HD void ltc_setup(LtcFrame& f, const LtcLut& lut, float3 p, float3 diffuse, 
     f.iso.r0 = x;
     f.iso.r2 = z;
     f.iso.r1 = normalize(cross(z, x));
+    const Mat3 tl_t = transpose(to_local);  // columns of to_local
+    f.world_to_iso.r0 = apply(tl_t, f.iso.r0);  // row i of iso * to_local = to_local^T * iso.row_i
+    f.world_to_iso.r1 = apply(tl_t, f.iso.r1);
+    f.world_to_iso.r2 = apply(tl_t, f.iso.r2);
 }
 
 // integrateOverPolygon for one triangle light.
 ORB_HD float3 integrate_tri_light(const LtcFrame& f, float3 lv1, float3 lv2, float3 lv3, float3 lnormal,
                                  float3 lemit) {
+    // The reference normalises after each of its two rotations (ltc_utils.cuh:64-76); a rotation of
+    // a unit vector is a unit vector to within an ulp, so the two are applied as ONE matrix with no
+    // re-normalisation (measured effect on the colour < 2e-6 relative, tests/test_hostcheck.py), and
+    // the back-face test uses the un-normalised centroid direction (same sign).
     float3 a = normalize(lv1 - f.p), b = normalize(lv2 - f.p), c = normalize(lv3 - f.p);
-    const float3 cg = normalize(a + b + c);
-    if (dot(-cg, lnormal) < 0.f) return v3(0.f);
-    a = normalize(apply(f.to_local, a));
-    b = normalize(apply(f.to_local, b));
-    c = normalize(apply(f.to_local, c));
-    a = normalize(apply(f.iso, a));
-    b = normalize(apply(f.iso, b));
-    c = normalize(apply(f.iso, c));
+    if (dot(a + b + c, lnormal) > 0.f) return v3(0.f);  // dot(-normalize(a+b+c), n) < 0
+    a = apply(f.world_to_iso, a);
+    b = apply(f.world_to_iso, b);
+    c = apply(f.world_to_iso, c);
     int n_diff;
     const float diffuse_shading = clipped_form_factor(a, b, c, false, n_diff);
     float ggx_shading = 0.f;

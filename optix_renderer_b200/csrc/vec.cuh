@@ -45,9 +45,20 @@ ORB_HD float3 cross(float3 a, float3 b) {
 // rsqrt: one MUFU.RSQ on the device (<= 2 ulp); the CPU build used by tests/hostcheck divides.
 ORB_HD float orb_rsqrt(float x) {
 #ifdef __CUDA_ARCH__
-    return rsqrtf(x);
+    float r;  // bare MUFU.RSQ: without .ftz the compiler wraps it in a denormal-scaling sequence (4 instructions)
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 #else
     return 1.f / sqrtf(x);
+#endif
+}
+// quotient to 2 ulp (MUFU.RCP + FMUL) where the reference's IEEE division is not needed for parity:
+// |b| must be in [2^-126, 2^126] (all uses: bounded denominators)
+ORB_HD float orb_fdiv(float a, float b) {
+#ifdef __CUDA_ARCH__
+    return __fdividef(a, b);
+#else
+    return a / b;
 #endif
 }
 ORB_HD float3 normalize(float3 a) { return a * orb_rsqrt(dot(a, a)); }
