@@ -98,11 +98,19 @@ struct SmemTracer {
 // k_primary
 // ---------------------------------------------------------------------------------------------
 // A warp covers an 8x4 pixel tile (coherent rays, 128-byte row segments on the float4 stores);
-// a 128-thread block covers 16x8.
+// a 128-thread block covers 16x8.  LOCAL_STACK: traversal stack in thread-local memory (behind L1)
+// instead of shared-memory columns -- no shared memory, so residency is limited by registers only
+// (ncu profiles/r1c: 28 % warps active and 30 % of the samples waiting on the node fetch with the
+// shared-memory stack).
+#define LOCAL_STACK_MAX 64
+template <bool LOCAL_STACK>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int height) {
-    int* stk = s_dyn + threadIdx.x;
-    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
+    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    const int stk_stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = f.y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -113,7 +121,7 @@ k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int 
         ofs = (size_t)py * f.W + px;
         float3 o, d;
         primary_ray(cam, frame_id, px, py, f.W, f.H, o, d);
-        const Hit h = trace_closest(s, o, d, stk, stk_t, TRACE_BLOCK);
+        const Hit h = trace_closest(s, o, d, stk, stk_t, stk_stride);
         const Surface si = shade_hit(s, h.prim, h.u, h.v);
         st_stream(f.hit + ofs, make_float4(__int_as_float(h.prim), h.u, h.v, h.t));
         st_stream(f.position + ofs, make_float4(si.p.x, si.p.y, si.p.z, 1.f));
@@ -266,7 +274,6 @@ __device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsign
     st_stream(rays + 2 * (size_t)id + 1, make_float4(d.x, d.y, d.z, 0.f));
 }
 
-#define LOCAL_STACK_MAX 64
 template <bool LOCAL_STACK>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits, const unsigned* __restrict__ n_items,
@@ -1186,14 +1193,16 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
         CK(cudaMemcpyAsync(c->d_meshes, recs.data(), sizeof(MeshRec) * recs.size(), cudaMemcpyHostToDevice, c->stream));
     }
     CK(cudaStreamSynchronize(c->stream));
-    CK(build_bvh(c->d_pos, (int)n, opt ? opt->max_leaf_tris : 0, c->stream, c->bvh));
+    int max_leaf = opt ? opt->max_leaf_tris : 0;
+    if (const char* e = getenv("ORB_MAX_LEAF")) max_leaf = atoi(e);  // tuning knob
+    CK(build_bvh(c->d_pos, (int)n, max_leaf, c->stream, c->bvh));
     c->counters.kernel_launches += c->bvh.launches;
     c->counters.bvh_nodes = (uint64_t)c->bvh.n_nodes;
     c->counters.bvh_triangles = (uint64_t)n;
     c->height = c->bvh.height + 2;
     if (trace_smem(c) > 200 * 1024)
         return fail(ORB_ERR_INVALID, "orb_scene_commit: BVH too deep for the shared-memory traversal stack");
-    CK(allow_smem(k_primary, trace_smem(c)));
+    CK(allow_smem(k_primary<false>, trace_smem(c)));
     CK(allow_smem(k_ratio_shadow, trace_smem(c)));
     CK(allow_smem(k_trace_stream<false>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<true>, trace_smem(c)));
@@ -1300,7 +1309,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     {
         StageTimer tm(c, ORB_STAGE_PRIMARY, 1);
         dim3 grid((c->W + 15) / 16, (y1 - y0 + 7) / 8);
-        k_primary<<<grid, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
+        if (c->local_stack && c->height <= LOCAL_STACK_MAX)
+            k_primary<true><<<grid, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
+        else
+            k_primary<false><<<grid, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
         c->counters.kernel_launches++;
         if (count_rays) c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
     }

@@ -108,11 +108,14 @@ ORB_HD void hit_consider(Hit& best, float t, float u, float v, int prim) {
 // Conservative slab test: entry distance (widened by a few ulp) or a negative value on a miss.
 // Boxes are already padded by the builder, so a box is never rejected for a triangle the test
 // above would accept at t <= tbest.
-ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 o, float3 inv,
+// Plane distances as ONE fma each, plane * inv + (-o * inv): half the arithmetic of (plane - o) * inv.
+// Its extra error is about one ulp of the origin's coordinate in space, far inside the builder's
+// padding of 1e-5 x scene extent.
+ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 noi, float3 inv,
                      float tbest, float& tnear) {
-    const float ax = (lox - o.x) * inv.x, bx = (hix - o.x) * inv.x;
-    const float ay = (loy - o.y) * inv.y, by = (hiy - o.y) * inv.y;
-    const float az = (loz - o.z) * inv.z, bz = (hiz - o.z) * inv.z;
+    const float ax = xfma(lox, inv.x, noi.x), bx = xfma(hix, inv.x, noi.x);
+    const float ay = xfma(loy, inv.y, noi.y), by = xfma(hiy, inv.y, noi.y);
+    const float az = xfma(loz, inv.z, noi.z), bz = xfma(hiz, inv.z, noi.z);
     float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
     float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), tbest));
     t0 = t0 - fabsf(t0) * 1e-6f;
@@ -144,7 +147,7 @@ ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& b
 // that leaf, and pops.  trace_closest() runs macro steps to completion; the ray-stream kernel
 // (orb200.cu k_trace_stream) interleaves them with refills so finished lanes get new rays.
 struct TravState {
-    float3 o, d, inv;
+    float3 o, d, inv, noi;  // noi = -o * inv
     Hit best;
     int cur, sp;
 };
@@ -153,6 +156,7 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
     t.o = o;
     t.d = d;
     t.inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    t.noi = v3(-(o.x * t.inv.x), -(o.y * t.inv.y), -(o.z * t.inv.z));
     t.best.t = INFINITY;
     t.best.u = t.best.v = 0.f;
     t.best.prim = -1;
@@ -178,8 +182,8 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
 #endif
     const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
     float tn0, tn1;
-    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.o, t.inv, lim, tn0);
-    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.o, t.inv, lim, tn1);
+    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
+    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
     if (h0 && h1) {
         const bool swap = tn1 < tn0;
         stk[t.sp * stride] = swap ? c0 : c1;
