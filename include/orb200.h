@@ -98,8 +98,11 @@ typedef struct OrbMeshDesc {
 
 typedef struct OrbBvhOptions {
     int32_t max_leaf_tris; /* 0 = default (4) */
-    int32_t reserved[3];
+    int32_t builder;       /* ORB_BVH_SAH (default) or ORB_BVH_LBVH; both run on the GPU */
+    int32_t reserved[2];
 } OrbBvhOptions;
+#define ORB_BVH_SAH 0  /* breadth-first binned surface-area heuristic, 16 bins x 3 axes per node */
+#define ORB_BVH_LBVH 1 /* Morton codes + Karras hierarchy: ~10x faster to build, ~25 % more node visits per ray */
 
 typedef struct OrbRenderConfig {
     int32_t renderer_type; /* OrbRendererType */
@@ -137,6 +140,7 @@ typedef struct OrbCounters {
     uint64_t rays_shadow_total; /* since orb_create, summed on the device at the end of every frame */
     uint64_t rays_bounce_total;
     uint64_t active_pixels_total;
+    uint64_t bvh_build_us; /* device time of the last orb_scene_commit's hierarchy build (CUDA events) */
 } OrbCounters;
 
 /* Stages of a frame, for orb_get_stage_times(): one entry per kernel family. */

@@ -46,8 +46,11 @@ class OrbMeshDesc(C.Structure):
                 ("diffuse_tex_rgba8", _b), ("tex_w", C.c_int32), ("tex_h", C.c_int32)]
 
 
+BVH_SAH, BVH_LBVH = 0, 1
+
+
 class OrbBvhOptions(C.Structure):
-    _fields_ = [("max_leaf_tris", C.c_int32), ("reserved", C.c_int32 * 3)]
+    _fields_ = [("max_leaf_tris", C.c_int32), ("builder", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class OrbRenderConfig(C.Structure):
@@ -65,7 +68,7 @@ class OrbCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_shadow", "rays_bounce", "kernel_launches",
                                           "nan_pixels", "bvh_nodes", "bvh_triangles", "bvh_height",
                                           "active_pixels", "nodes_visited", "tris_tested",
-                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total")]
+                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total", "bvh_build_us")]
 
 
 STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "denoise", "combine", "ltc_gbuffer"]
@@ -147,7 +150,7 @@ def _fp(a):
 class Renderer:
     """One context on one GPU.  `scene` is the dict made by optix_renderer_b200.scenes."""
 
-    def __init__(self, scene=None, device=0, quantise_lut=0, max_leaf_tris=0):
+    def __init__(self, scene=None, device=0, quantise_lut=0, max_leaf_tris=0, builder=BVH_SAH):
         self.lib = load_library()
         h = C.c_void_p()
         self._h = None
@@ -155,7 +158,7 @@ class Renderer:
         self._h = h
         self.W = self.H = 0
         if scene is not None:
-            self.load_scene(scene, quantise_lut, max_leaf_tris)
+            self.load_scene(scene, quantise_lut, max_leaf_tris, builder)
 
     def _ck(self, rc):
         if rc != 0:
@@ -200,22 +203,23 @@ class Renderer:
         self._ck(self.lib.orb_scene_set_ltc_lut(self._h, _fp(m1), _fp(m2), _fp(m3), m1.shape[1], m1.shape[0],
                                                 int(quantise)))
 
-    def commit(self, max_leaf_tris=0):
+    def commit(self, max_leaf_tris=0, builder=BVH_SAH):
         o = OrbBvhOptions()
         o.max_leaf_tris = int(max_leaf_tris)
+        o.builder = int(builder)
         self._ck(self.lib.orb_scene_commit(self._h, C.byref(o)))
 
     def set_camera(self, pos, d00, du, dv):
         a = [f32(x) for x in (pos, d00, du, dv)]
         self._ck(self.lib.orb_set_camera(self._h, *[_fp(x) for x in a]))
 
-    def load_scene(self, scene, quantise_lut=0, max_leaf_tris=0):
+    def load_scene(self, scene, quantise_lut=0, max_leaf_tris=0, builder=BVH_SAH):
         self._ck(self.lib.orb_scene_clear(self._h))
         for m in scene["meshes"]:
             self.add_mesh(m)
         self.set_lights(scene["tri_lights"])
         self.set_ltc_lut(scene["lut"], quantise_lut)
-        self.commit(max_leaf_tris)
+        self.commit(max_leaf_tris, builder)
         cam = scene["camera"]
         self.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])
         if "width" in scene:

@@ -155,7 +155,10 @@ struct TravState {
 ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
     t.o = o;
     t.d = d;
-    t.inv = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    // a zero (or denormal) component would make plane * inv + noi an inf - inf; 1e30 keeps every slab
+    // distance finite with the right sign for coordinates up to 1e7
+    t.inv = v3(fabsf(d.x) < 1e-30f ? copysignf(1e30f, d.x) : 1.f / d.x, fabsf(d.y) < 1e-30f ? copysignf(1e30f, d.y) : 1.f / d.y,
+               fabsf(d.z) < 1e-30f ? copysignf(1e30f, d.z) : 1.f / d.z);
     t.noi = v3(-(o.x * t.inv.x), -(o.y * t.inv.y), -(o.z * t.inv.z));
     t.best.t = INFINITY;
     t.best.u = t.best.v = 0.f;
@@ -173,9 +176,16 @@ template <class IntPtr, class FltPtr>
 ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride) {
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
-    const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-    const int2 nd = __ldg(reinterpret_cast<const int2*>(&np->c0));
-    const int c0 = nd.x, c1 = nd.y;
+    // two 256-bit loads (sm_100: LDG.E.256) instead of four 128-bit ones: the node fetch is the
+    // kernel's L1 bottleneck (ncu profiles/r1c: l1tex 81 % busy), every lane reading its own node
+    float4 na, nb, nc;
+    int c0, c1, pad0, pad1;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(na.x), "=f"(na.y), "=f"(na.z), "=f"(na.w), "=f"(nb.x), "=f"(nb.y), "=f"(nb.z), "=f"(nb.w)
+        : "l"(np));
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
+        : "l"(reinterpret_cast<const char*>(np) + 32));
 #else
     const float4 na = np->a, nb = np->b, nc = np->c;
     const int c0 = np->c0, c1 = np->c1;
@@ -199,11 +209,9 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
     }
 }
 
-// One leaf (t.cur < 0, not DONE): its 1..8 triangles, then pop.
-template <class IntPtr, class FltPtr>
-ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
-                           unsigned* n_tris = nullptr) {
-    const int lr = ~t.cur;
+// The 1..8 triangles of one leaf reference against the ray; updates t.best only.
+ORB_HD void trav_leaf_test(TravState& t, const SceneView& s, int leaf, unsigned* n_tris = nullptr) {
+    const int lr = ~leaf;
     const int first = lr >> 3, count = (lr & 7) + 1;
     for (int i = 0; i < count; i++) {
         const float4* tp = s.tri + 3 * (size_t)(first + i);
@@ -216,6 +224,13 @@ ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
         float tt, u, v;
         if (tri_test(t0, t1, t2, t.o, t.d, 0.f, ORB_TMAX, tt, u, v)) hit_consider(t.best, tt, u, v, __float_as_int_hd(t0.w));
     }
+}
+
+// One leaf (t.cur < 0, not DONE): its triangles, then pop.
+template <class IntPtr, class FltPtr>
+ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
+                           unsigned* n_tris = nullptr) {
+    trav_leaf_test(t, s, t.cur, n_tris);
     t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
 }
 

@@ -168,6 +168,37 @@ def test_trace_hit_ids_bvh_vs_brute_force_and_oracle(renderer_factory):
     assert ties <= 2, ties
 
 
+@pytest.mark.parametrize("n_tris,leaf", [(1, 0), (3, 4), (5, 4), (2000, 1), (20000, 2), (200000, 8)])
+def test_sah_and_lbvh_builders_agree_with_brute_force(renderer_factory, n_tris, leaf):
+    """Both GPU builders (binned SAH, the default; Morton LBVH) against the brute-force closest hit, from
+    one triangle (root is a leaf) to 200 k, at several leaf sizes; frames rendered over the two trees
+    are bit-identical (the result does not depend on the hierarchy)."""
+    sc = scenes.scene_synthetic(n_tris=n_tris, n_quad_lights=2, width=48, height=32, patches=1 if n_tris < 200 else 8)
+    rng = np.random.default_rng(5)
+    n = 6000
+    org = (rng.uniform(-1, 1, (n, 3)) * 9).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) * 0.5 + 0.2
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:50, 0] = 0.0                      # axis-parallel components (infinite slab distances)
+    d[50:100, 2] = 0.0
+    frames = []
+    for builder in (api.BVH_SAH, api.BVH_LBVH):
+        r = renderer_factory(sc, max_leaf_tris=leaf, builder=builder)
+        p1, t1, u1, v1 = r.trace_rays(org, d, brute_force=False)
+        c = r.counters()
+        p2, t2, u2, v2 = r.trace_rays(org, d, brute_force=True)
+        assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
+        assert c["bvh_triangles"] == scenes.n_triangles(sc)
+        if n_tris >= 20000:
+            assert c["tris_tested"] < 0.05 * n * c["bvh_triangles"]
+        r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=2)
+        frames.append({k: r.download(k) for k in ("ltc", "sto_direct", "sto_no_vis", "position")})
+        frames[-1]["hit"] = r.hit_records()[0]
+    for k in frames[0]:
+        assert np.array_equal(frames[0][k], frames[1][k], equal_nan=True), k
+
+
 def test_ltc_gbuffer_pass_and_ratio_combine(renderer_factory):
     """BASELINE config 1 shape: saved G-buffer in, LTC pass + ratio arithmetic out."""
     g = np.load(os.path.join(P.G, "gbuffer48.npz"))

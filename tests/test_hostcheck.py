@@ -86,6 +86,9 @@ def test_bvh_traversal_equals_brute_force(hostcheck):
     org[:, 2] = np.abs(org[:, 2]) + 0.5
     d = rng.normal(size=(4000, 3)).astype(np.float32)
     d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:40, 0] = 0.0   # axis-parallel components: slab distances must stay finite
+    d[40:80, 2] = 0.0
+    d[80:100, 1] = -0.0
     p1, t1, u1, v1 = hostcheck.trace(org, d, brute=False)
     p2, t2, u2, v2 = hostcheck.trace(org, d, brute=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)

@@ -24,7 +24,7 @@ cam = np.asarray(sc["camera"]["pos"], np.float32)
 p = pos[ys, xs]
 d = p - cam
 d /= np.linalg.norm(d, axis=1, keepdims=True)
-out = {"max_leaf_tris": leaf, "counters": {k: r.counters()[k] for k in ("bvh_nodes", "bvh_triangles", "bvh_height")}}
+out = {"max_leaf_tris": leaf, "counters": {k: r.counters()[k] for k in ("bvh_nodes", "bvh_triangles", "bvh_height", "bvh_build_us")}}
 r.trace_rays(np.repeat(cam[None], len(d), 0), d)
 c = r.counters()
 out["camera_rays"] = {"n": len(d), "nodes_per_ray": c["nodes_visited"] / len(d), "tris_per_ray": c["tris_tested"] / len(d)}
