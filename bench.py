@@ -145,7 +145,8 @@ def workload_config(args, n):
             ("BASELINE configs[3]: same scene, PATH intended mode, %d bounces, progressive" % DEPTH),
             "width": W, "height": H, "triangles": N_TRIS, "tri_lights": 2 * N_QUADS, "shadow_spp": SPP,
             "max_depth": DEPTH if args.workload == "path" else 1, "lut": "8x8 (reference ltc_isotropic.h)",
-            "partition": "row bands x%d, BVH replicated, NCCL all-gather assembly" % n if n > 1 else "single GPU",
+            "partition": ("%d cost-balanced row bands, BVH replicated, NCCL all-gather of the packed denoise rows and of "
+                          "the finished frame" % n) if n > 1 else "single GPU",
             "l2": "working set per frame (13+ float4 frame buffers of 33 MB, 48 MB triangles, 64 MB BVH) exceeds the "
                   "126 MB L2; no explicit flush"}
 
@@ -189,6 +190,9 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: library chatter (NCCL prints its version there) goes to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
@@ -204,11 +208,14 @@ def run_ours(args):
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
 
-    def step(i):
+    def render(i):
         if ratio:
             T.render_ratio_frame(i, mode=api.INTENDED, shadow_spp=SPP)
         else:
             T.render_path_frame(i, mode=api.INTENDED, max_depth=DEPTH)
+
+    def step(i):
+        render(i)
         T.assemble(out_names)
 
     def barrier():
@@ -227,7 +234,18 @@ def run_ours(args):
         sampler = ClockSampler(local)
         sampler.start()
         for i in range(args.warmup):
-            step(i)
+            if world > 1:
+                # cut the row bands by cost: a model from the first frame's active pixels, then corrected by
+                # this rank's measured kernel time for its band (stage timers: the collectives and the
+                # waiting for slower neighbours are not in it) over the following warm-up frames
+                r.set_profiling(True)
+                r.stage_times()
+                step(i)
+                mine_ms = sum(t for t, _ in r.stage_times().values())
+                r.set_profiling(False)
+                T.rebalance(None if i == 0 else mine_ms)
+            else:
+                step(i)
         barrier()
         r.set_profiling(True)
         r.stage_times()
@@ -303,9 +321,13 @@ def run_ours(args):
                         "what": "orb_set_camera + orb_render_async(+denoise+combine) + orb_buffer_download_rows of the "
                                 "float4 result and the RGBA8 frame into pinned host memory"},
                 "gpu_launches": int(launches), "roofline": roofline, "passes": passes, "clocks": clocks}
+        if world > 1:
+            line["config"]["bands"] = [list(b) for b in T.bands]
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_sample(args.workload)
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(line), flush=True)
     r.close()
     if world > 1:
         dist.destroy_process_group()

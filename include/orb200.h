@@ -66,7 +66,9 @@ typedef enum OrbBufferId {
     ORB_BUF_STO_DIRECT_DN = 15, /* float4: denoised sto_direct  (stodirectDenoise.exr)             */
     ORB_BUF_STO_NO_VIS_DN = 16, /* float4: denoised sto_no_vis  (stoNoVisDenoise.exr)              */
     ORB_BUF_RATIO_FINAL = 17,  /* float4: ltc * (stoDirect / stoNoVis) (final_ratio_estimator.exr) */
-    ORB_BUF_COUNT = 18
+    ORB_BUF_DN_GUIDE = 18,     /* float4: denoise guide (n.xyz, camera distance or < 0 for lights / misses)      */
+    ORB_BUF_DN_VAL = 19,       /* float2 (8 B/px): packed (sto_direct.x, sto_no_vis.x), the filter's input      */
+    ORB_BUF_COUNT = 20
 } OrbBufferId;
 
 /* TriLight, cuda_include/common.cuh:64-72 -- 76 bytes, same field order. */
@@ -115,6 +117,8 @@ typedef struct OrbRenderConfig {
 } OrbRenderConfig;
 #define ORB_RENDER_FUSED_SHADOW 2 /* RATIO: trace the shadow rays inside one per-pixel kernel instead of the
                                      ray-stream kernels (kept for A/B measurement; same results) */
+#define ORB_RENDER_PATH_WAVEFRONT 4 /* PATH: one generate / trace / shade wavefront per bounce instead of the
+                                       persistent all-bounces kernel (kept for A/B measurement) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 
@@ -205,6 +209,14 @@ int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_ltc_gbuffer_pass(OrbContext* ctx, int32_t y0, int32_t y1);
 /* a-trous edge-avoiding filter: STO_DIRECT -> STO_DIRECT_DN, STO_NO_VIS -> STO_NO_VIS_DN */
 int orb_denoise(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1);
+/* The two halves of orb_denoise, for tile partitions: a band's owner packs ITS rows into ORB_BUF_DN_GUIDE /
+ * ORB_BUF_DN_VAL, the packed rows are exchanged between GPUs (24 B/px instead of re-rendering the filter's
+ * 2 * (2^iterations - 1) halo rows), and the filter then runs over the band. */
+int orb_denoise_pack(OrbContext* ctx, int32_t y0, int32_t y1);
+int orb_denoise_filter(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1);
+/* Active (non-light hit) pixels per row of the last rendered frame -> host_counts[height]; rows this context
+ * did not render report what its flags hold.  Used to balance row bands by cost. */
+int orb_row_active_counts(OrbContext* ctx, int32_t* host_counts);
 /* ltc_ratio_estimator.py:8: RATIO_FINAL = LTC * (STO_DIRECT[_DN] / STO_NO_VIS[_DN]) */
 int orb_ratio_combine(OrbContext* ctx, int32_t use_denoised, int32_t y0, int32_t y1);
 

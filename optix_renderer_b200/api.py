@@ -26,7 +26,7 @@ LITERAL, INTENDED = 0, 1
 BUFFERS = {
     "position": 0, "normal": 1, "uv": 2, "albedo": 3, "alpha": 4, "materialID": 5, "bounce0": 6, "bounce1": 7,
     "bounce2": 8, "ltc": 9, "sto_direct": 10, "sto_no_vis": 11, "accum": 12, "rgba8": 13, "hit": 14,
-    "sto_direct_dn": 15, "sto_no_vis_dn": 16, "ratio_final": 17,
+    "sto_direct_dn": 15, "sto_no_vis_dn": 16, "ratio_final": 17, "dn_guide": 18, "dn_val": 19,
 }
 
 _f = C.POINTER(C.c_float)
@@ -111,6 +111,9 @@ def load_library():
     L.orb_render_async.argtypes = [vp, C.POINTER(OrbRenderConfig)]
     L.orb_ltc_gbuffer_pass.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_denoise.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32]
+    L.orb_denoise_pack.argtypes = [vp, C.c_int32, C.c_int32]
+    L.orb_denoise_filter.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32]
+    L.orb_row_active_counts.argtypes = [vp, vp]
     L.orb_ratio_combine.argtypes = [vp, C.c_int32, C.c_int32, C.c_int32]
     L.orb_buffer_bytes.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.restype = C.c_size_t
@@ -230,17 +233,19 @@ class Renderer:
         self.W, self.H = int(W), int(H)
 
     # ---- launch (Viewer::render, viewer.hpp:553-568) ----
-    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True, fused_shadow=False):
+    def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True, fused_shadow=False,
+             path_wavefront=False):
         c = OrbRenderConfig()
-        c.flags = (0 if count_rays else 1) | (2 if fused_shadow else 0)  # ORB_RENDER_NO_COUNT, _FUSED_SHADOW
+        # ORB_RENDER_NO_COUNT, _FUSED_SHADOW, _PATH_WAVEFRONT
+        c.flags = (0 if count_rays else 1) | (2 if fused_shadow else 0) | (4 if path_wavefront else 0)
         c.renderer_type, c.accum_id, c.mode = int(renderer_type), int(accum_id), int(mode)
         c.shadow_spp, c.max_depth = int(shadow_spp), int(max_depth)
         c.y0, c.y1 = rows if rows else (0, 0)
         return c
 
     def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True,
-               count_rays=True, fused_shadow=False):
-        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays, fused_shadow)
+               count_rays=True, fused_shadow=False, path_wavefront=False):
+        c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays, fused_shadow, path_wavefront)
         self._ck((self.lib.orb_render if sync else self.lib.orb_render_async)(self._h, C.byref(c)))
 
     def ltc_gbuffer_pass(self, rows=None):
@@ -251,6 +256,23 @@ class Renderer:
         d = OrbDenoiseConfig(int(iterations), float(sigma_normal), float(sigma_position), float(sigma_colour))
         y0, y1 = rows if rows else (0, 0)
         self._ck(self.lib.orb_denoise(self._h, C.byref(d), y0, y1))
+
+    def denoise_pack(self, rows=None):
+        """First half of denoise(): this band's rows -> the packed guide / value buffers."""
+        y0, y1 = rows if rows else (0, 0)
+        self._ck(self.lib.orb_denoise_pack(self._h, y0, y1))
+
+    def denoise_filter(self, iterations=5, sigma_normal=32.0, sigma_position=0.25, sigma_colour=0.0, rows=None):
+        """Second half: the a-trous passes over rows; reads packed rows up to denoise_reach beyond them."""
+        d = OrbDenoiseConfig(int(iterations), float(sigma_normal), float(sigma_position), float(sigma_colour))
+        y0, y1 = rows if rows else (0, 0)
+        self._ck(self.lib.orb_denoise_filter(self._h, C.byref(d), y0, y1))
+
+    def row_active_counts(self):
+        """Active (non-light hit) pixels per row of the last frame, int32[H]."""
+        out = np.zeros(self.H, np.int32)
+        self._ck(self.lib.orb_row_active_counts(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
 
     def ratio_combine(self, use_denoised=False, rows=None):
         y0, y1 = rows if rows else (0, 0)
@@ -286,7 +308,7 @@ class Renderer:
         y0, y1 = rows if rows else (0, self.H)
         if out is None:
             out = (np.empty((y1 - y0, self.W), np.uint32) if name == "rgba8"
-                   else np.empty((y1 - y0, self.W, 4), np.float32))
+                   else np.empty((y1 - y0, self.W, 2 if name == "dn_val" else 4), np.float32))
         self._ck(self.lib.orb_buffer_download_rows(self._h, bid, out.ctypes.data_as(C.c_void_p), y0, y1))
         return out
 

@@ -674,6 +674,126 @@ k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce,
     }
 }
 
+// ---- persistent form of the whole bounce loop ----------------------------------------------------
+// The per-bounce wavefront above pays, for EVERY bounce, three launches, an 80-byte round trip of
+// the path state through HBM and -- worst -- the tail of the slowest ray: a few bounce rays skim the
+// terrain for a thousand node visits, so each traversal launch has a floor of ~0.18 ms no matter
+// how few paths are left (ncu launch list, profiles/r1j: bounces 4-7 take 0.18-0.19 ms each for
+// < 10 % of the rays).  Here a lane owns a PATH instead of a ray: when its ray ends it shades
+// (path_resolve) and starts the next bounce at once, and when its path ends it claims a new pixel
+// from the active-pixel queue.  One launch per frame, one tail per frame, no path state in HBM.
+// Shading is batched like the refill: lanes whose ray has ended wait until `refill_min` of them
+// have (or nobody can advance), so the divergent shading code runs with a fair number of lanes.
+template <bool LOCAL_STACK>
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int depth, unsigned* __restrict__ cursor,
+                  int refill_min, int node_min, int height) {
+    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
+    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
+    const unsigned n = f.cnt->queue_n;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned FULL = 0xffffffffu;
+    unsigned w_next = 0, w_end = 0;
+    TravState t;
+    t.cur = ORB_TRAVERSAL_DONE;
+    t.sp = 0;
+    int leaf = 0;
+    PathState st;
+    size_t ofs = 0;
+    int bounce = 0;
+    bool have_path = false, exhausted = false;
+    unsigned rays = 0;
+    PathBuffers none;
+    for (;;) {
+        const bool ended = t.cur == ORB_TRAVERSAL_DONE && leaf == 0;  // ray finished, or no path at all
+        const unsigned n_ended = __popc(__ballot_sync(FULL, ended && (have_path || !exhausted)));
+        const unsigned busy = __ballot_sync(FULL, !ended);
+        if (n_ended && ((int)n_ended >= refill_min || busy == 0u)) {
+            if (ended && have_path) {  // shade this bounce
+                const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+                Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+                rng_skip(rng, 2 + 5 * bounce);
+                const PathSample q = path_ray_setup(st, rng);  // same arithmetic as when the ray was made
+                float3 colour;
+                if (path_resolve(s, st, q, t.best, bounce == depth - 1, colour) == ORB_PATH_DONE) {
+                    st_stream(f.colour + ofs, make_float4(colour.x, colour.y, colour.z, 1.f));
+                    have_path = false;
+                } else {
+                    ++bounce;
+                }
+            }
+            // lanes without a path claim the next active pixels (chunks of the queue, one atomic per chunk)
+            const bool claim = ended && !have_path && !exhausted;
+            const unsigned want = __ballot_sync(FULL, claim);
+            if (want) {
+                const unsigned need = __popc(want);
+                const unsigned left = w_end - w_next;
+                unsigned base = w_next;
+                unsigned chunk = STREAM_CHUNK;
+                if (left < need) {
+                    if (lane == 0) {
+                        const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
+                        const unsigned rem = n > seen ? n - seen : 0u;
+                        const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
+                        chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
+                        base = atomicAdd(cursor, chunk);
+                    }
+                    base = __shfl_sync(FULL, base, 0);
+                    chunk = __shfl_sync(FULL, chunk, 0);
+                }
+                const unsigned rank = __popc(want & ((1u << lane) - 1u));
+                if (claim) {
+                    const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
+                    if (idx < n) {
+                        path_load_state<true>(f, cam_pos, none, idx, st, ofs);
+                        bounce = 0;
+                        have_path = true;
+                    } else {
+                        exhausted = true;
+                    }
+                }
+                if (left >= need) {
+                    w_next += need;
+                } else {
+                    w_next = base + (need - left);
+                    w_end = base + chunk;
+                }
+            }
+            if (ended && have_path) {  // next ray of this path
+                const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+                Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+                rng_skip(rng, 2 + 5 * bounce);
+                const PathSample q = path_ray_setup(st, rng);
+                trav_begin(t, s, q.origin, q.dir);
+                ++rays;
+            }
+        }
+        if (__ballot_sync(FULL, have_path) == 0u) break;
+#pragma unroll 1
+        for (int it = 0; it < 64; ++it) {  // node phase (speculative: one postponed leaf per lane)
+            if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
+            if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
+                leaf = t.cur;
+                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+            }
+            if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
+        }
+        if (leaf != 0) {  // leaf phase
+            trav_leaf_test(t, s, leaf);
+            leaf = 0;
+            if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
+                leaf = t.cur;
+                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(FULL, rays, o);
+    if (lane == 0 && rays) atomicAdd(&f.cnt->rays_bounce, (unsigned long long)rays);
+}
+
 __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
 
 // ---------------------------------------------------------------------------------------------
@@ -957,9 +1077,11 @@ struct OrbContext {
     int leaf_min = 12;
     int node_min = 16;
     int trace_variant = 1;  // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec)
+    int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
+    int path_node_min = 8;
+    int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // measured: 2.96 -> 2.51 ms for the 1080p shadow stage (more resident warps)
-    float4* dn_guide = nullptr;
-    float2* dn_val[2] = {nullptr, nullptr};
+    float2* dn_val_b = nullptr;  // ping-pong partner of ORB_BUF_DN_VAL
     float* unit_in = nullptr;
     float* unit_out = nullptr;
     Camera cam;
@@ -997,7 +1119,7 @@ struct StageTimer {
     }
 };
 
-static size_t buffer_elem_bytes(int id) { return id == ORB_BUF_RGBA8 ? 4 : 16; }
+static size_t buffer_elem_bytes(int id) { return id == ORB_BUF_RGBA8 ? 4 : (id == ORB_BUF_DN_VAL ? 8 : 16); }
 
 static void free_scene(OrbContext* c) {
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_prim_mesh); cudaFree(c->d_meshes);
@@ -1015,11 +1137,11 @@ static void free_frame(OrbContext* c) {
     for (int i = 0; i < ORB_BUF_COUNT; i++) { cudaFree(c->buf[i]); c->buf[i] = nullptr; }
     cudaFree(c->colour); cudaFree(c->flags); cudaFree(c->queue);
     for (int a = 0; a < 2; a++) for (int b = 0; b < 5; b++) { cudaFree(c->path_state[a][b]); c->path_state[a][b] = nullptr; }
-    cudaFree(c->dn_guide); cudaFree(c->dn_val[0]); cudaFree(c->dn_val[1]);
+    cudaFree(c->dn_val_b);
     cudaFree(c->stream_rays); cudaFree(c->stream_hits);
     c->stream_rays = c->stream_hits = nullptr;
     c->stream_cap = 0;
-    c->colour = nullptr; c->flags = nullptr; c->queue = nullptr; c->dn_guide = nullptr; c->dn_val[0] = c->dn_val[1] = nullptr;
+    c->colour = nullptr; c->flags = nullptr; c->queue = nullptr; c->dn_val_b = nullptr;
     c->W = c->H = 0;
 }
 
@@ -1108,6 +1230,9 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_LEAF_MIN")) c->leaf_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
+    if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
+    if (const char* e = getenv("ORB_PATH_SHADE_MIN")) c->path_shade_min = std::max(1, std::min(32, atoi(e)));
+    if (const char* e = getenv("ORB_PATH_NODE_MIN")) c->path_node_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
     return ORB_OK;
 }
@@ -1471,9 +1596,22 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         c->last_spp = spp;
     }
     if (renderer == ORB_PATH) {
-        int rc = ensure_path_state(c);
-        if (rc) return rc;
+        int rc = ORB_OK;
         const bool stream = mode == ORB_MODE_INTENDED && !(cfg->flags & ORB_RENDER_FUSED_SHADOW);
+        const bool persistent = stream && c->path_persistent && !(cfg->flags & ORB_RENDER_PATH_WAVEFRONT) &&
+                                c->local_stack && c->height <= LOCAL_STACK_MAX;
+        if (persistent) {
+            rc = ensure_stream(c, 1);  // the cursor
+            if (rc) return rc;
+            StageTimer tm(c, ORB_STAGE_PATH, 1);
+            CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
+            const int g = persistent_grid(c, k_path_persistent<true>, TRACE_BLOCK, 0);
+            k_path_persistent<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor,
+                                                              c->path_shade_min, c->path_node_min, c->height);
+            c->counters.kernel_launches++;
+        } else {
+        rc = ensure_path_state(c);
+        if (rc) return rc;
         StageTimer tm(c, ORB_STAGE_PATH, stream ? 4 * depth - 1 : 2 * depth - 1);
         PathBuffers pb[2];
         for (int a = 0; a < 2; a++)
@@ -1519,6 +1657,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                 c->counters.kernel_launches++;
             }
         }
+        }
     }
     {
         StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
@@ -1556,36 +1695,40 @@ int orb_ltc_gbuffer_pass(OrbContext* c, int32_t y0, int32_t y1) {
     return ORB_OK;
 }
 
-int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1) {
-    NEED(c && c->W > 0, "orb_denoise: orb_resize first");
-    NEED(c->have_cam, "orb_denoise: orb_set_camera first");
-    NEED(rows_ok(c, y0, y1), "orb_denoise: bad row range");
+// rows the a-trous pass `it` (step 2^it) of an `iters`-pass filter must WRITE beyond a band so that the
+// later passes find their taps: sum of 2 * 2^j over j > it; it = -1 gives the rows the packed input must cover
+static int denoise_reach(int iters, int it) { return 2 * ((1 << iters) - (1 << (it + 1))); }
+
+int orb_denoise_pack(OrbContext* c, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_denoise_pack: orb_resize first");
+    NEED(c->have_cam, "orb_denoise_pack: orb_set_camera first");
+    NEED(rows_ok(c, y0, y1), "orb_denoise_pack: bad row range");
+    CK(cudaSetDevice(c->device));
+    FrameView f = frame_view(c, y0, y1);
+    const size_t np = (size_t)(y1 - y0) * c->W;
+    const int gp = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
+    {
+        StageTimer tm(c, ORB_STAGE_DENOISE_PACK, 1);
+        k_denoise_pack<<<gp, 256, 0, c->stream>>>(f, c->cam.pos, (float4*)c->buf[ORB_BUF_DN_GUIDE], (float2*)c->buf[ORB_BUF_DN_VAL]);
+    }
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_denoise_filter: orb_resize first");
+    NEED(rows_ok(c, y0, y1), "orb_denoise_filter: bad row range");
     OrbDenoiseConfig d = {5, 32.f, 0.25f, 0.f};
     if (cfg) d = *cfg;
     if (d.iterations <= 0) d.iterations = 5;
     NEED(d.iterations <= 8, "orb_denoise: at most 8 iterations");
     CK(cudaSetDevice(c->device));
     const size_t n = (size_t)c->W * c->H;
-    if (!c->dn_guide) {
-        CK(cudaMalloc(&c->dn_guide, n * 16));
-        CK(cudaMalloc(&c->dn_val[0], n * 8));
-        CK(cudaMalloc(&c->dn_val[1], n * 8));
-    }
-    // Pass `it` (step 2^it) reads 2 * 2^it rows either side of the rows it writes, so for the band
-    // [y0, y1) pass `it` must write [y0 - R, y1 + R) with R = sum of 2 * 2^j over the LATER passes
-    // j > it, and the pack covers R of pass -1 = 2 * (2^iters - 1) rows (rows outside the band must
-    // hold valid G-buffer / sto data, e.g. rendered as a halo by the tile's owner).
-    auto reach = [&](int it) { return 2 * ((1 << d.iterations) - (1 << (it + 1))); };
-    const int p0 = std::max(0, y0 - reach(-1)), p1 = std::min(c->H, y1 + reach(-1));
-    FrameView all = frame_view(c, p0, p1);
+    if (!c->dn_val_b) CK(cudaMalloc(&c->dn_val_b, n * 8));
+    const float4* guide = (const float4*)c->buf[ORB_BUF_DN_GUIDE];
+    float2* val[2] = {(float2*)c->buf[ORB_BUF_DN_VAL], c->dn_val_b};
     FrameView f = frame_view(c, y0, y1);
-    const size_t np = (size_t)(p1 - p0) * c->W;
-    const int gp = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
-    {
-        StageTimer tm(c, ORB_STAGE_DENOISE_PACK, 1);
-        k_denoise_pack<<<gp, 256, 0, c->stream>>>(all, c->cam.pos, c->dn_guide, c->dn_val[0]);
-    }
-    c->counters.kernel_launches++;
     StageTimer tm_dn(c, ORB_STAGE_DENOISE, d.iterations);
     int cur = 0;
     for (int it = 0; it < d.iterations; it++) {
@@ -1595,20 +1738,64 @@ int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t 
         const float isc = d.sigma_colour > 0.f ? log2e / d.sigma_colour : 0.f;
         if (it == d.iterations - 1) {
             dim3 gb((c->W + 31) / 32, (y1 - y0 + 7) / 8);
-            k_denoise_atrous<true><<<gb, 256, 0, c->stream>>>(f, c->dn_guide, c->dn_val[cur], nullptr,
+            k_denoise_atrous<true><<<gb, 256, 0, c->stream>>>(f, guide, val[cur], nullptr,
                                                                (float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
                                                                (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN], step,
                                                                d.sigma_normal, isp, isc);
         } else {
-            FrameView part = frame_view(c, std::max(0, y0 - reach(it)), std::min(c->H, y1 + reach(it)));
+            const int r = denoise_reach(d.iterations, it);
+            FrameView part = frame_view(c, std::max(0, y0 - r), std::min(c->H, y1 + r));
             dim3 grid((c->W + 31) / 32, (part.y1 - part.y0 + 7) / 8);
-            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(part, c->dn_guide, c->dn_val[cur], c->dn_val[cur ^ 1],
-                                                                  nullptr, nullptr, step, d.sigma_normal, isp, isc);
+            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(part, guide, val[cur], val[cur ^ 1], nullptr, nullptr, step,
+                                                                  d.sigma_normal, isp, isc);
             cur ^= 1;
         }
         c->counters.kernel_launches++;
     }
+    if (d.iterations > 1 && ((d.iterations - 1) & 1)) {
+        // an odd number of ping-pong passes left pass 0's output in ORB_BUF_DN_VAL; nothing to restore:
+        // the packed input is rewritten by the next orb_denoise_pack
+    }
     CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+// pack + filter over rows [y0, y1): the packed input covers the band plus the filter's reach, so those rows
+// must hold valid G-buffer / sto data (a single-GPU frame, or halo rows rendered by the band's owner)
+int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1) {
+    NEED(c && c->W > 0, "orb_denoise: orb_resize first");
+    NEED(rows_ok(c, y0, y1), "orb_denoise: bad row range");
+    int iters = cfg && cfg->iterations > 0 ? cfg->iterations : 5;
+    NEED(iters <= 8, "orb_denoise: at most 8 iterations");
+    const int r = denoise_reach(iters, -1);
+    int rc = orb_denoise_pack(c, std::max(0, y0 - r), std::min(c->H, y1 + r));
+    if (rc) return rc;
+    return orb_denoise_filter(c, cfg, y0, y1);
+}
+
+// active (non-light hit) pixels of every row of the last frame, for cost-balanced tile partitions
+__global__ void k_row_active(FrameView f, int* __restrict__ counts) {
+    const int y = blockIdx.x;
+    int n = 0;
+    for (int x = threadIdx.x; x < f.W; x += blockDim.x) {
+        const uint32_t fl = f.flags[(size_t)y * f.W + x];
+        n += ((fl & FLAG_HIT) && !(fl & FLAG_LIGHT)) ? 1 : 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(&counts[y], n);
+}
+
+int orb_row_active_counts(OrbContext* c, int32_t* host_counts) {
+    NEED(c && c->W > 0 && host_counts, "orb_row_active_counts: bad argument");
+    CK(cudaSetDevice(c->device));
+    int* d = nullptr;
+    CK(cudaMalloc(&d, sizeof(int) * c->H));
+    CK(cudaMemsetAsync(d, 0, sizeof(int) * c->H, c->stream));
+    k_row_active<<<c->H, 128, 0, c->stream>>>(frame_view(c, 0, c->H), d);
+    c->counters.kernel_launches++;
+    CK(cudaMemcpyAsync(host_counts, d, sizeof(int) * c->H, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaFree(d));
     return ORB_OK;
 }
 

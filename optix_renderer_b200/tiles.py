@@ -4,18 +4,53 @@ The reference is single-GPU (owlContextCreate(nullptr, 1), include/viewer.hpp:17
 frame is split into contiguous row bands, one per rank; scene, BVH, lights and LUT are
 replicated; every pixel's RNG is keyed by its GLOBAL index and the GLOBAL frame size
 (cuda_include/lcg_random.cuh:54-62), so a band renders bit-identically to the same rows of a
-full frame.  Rendering needs no exchange.  The only collective is frame assembly: one
-all-gather of each rank's finished band (NCCL over NVLink on the GPU box; gloo in CPU tests).
-The denoise filter reaches 2*(2^iters - 1) rows beyond a band; the owner renders those halo
-rows redundantly (their rays are not counted) instead of exchanging them.
+full frame.  Rendering needs no exchange.
+
+Bands are BALANCED BY COST, not by row count: sky rows cost one cheap primary ray per pixel, rows
+full of geometry cost the LTC sum and four shadow rays per pixel on top (about 10x).  After a first
+frame every rank counts its active pixels per row, the counts are all-gathered, and all ranks cut
+the frame where the cumulative cost crosses k/N (same input, same cuts everywhere).
+
+Collectives (NCCL over NVLink on the GPU box; gloo in the CPU tests):
+  * denoise input: each rank packs ITS rows (guide float4 + value float2, 24 B/px) and sends the
+    2*(2^iters - 1) rows either side of a cut to the neighbours that filter them (point to point),
+    so nobody renders a halo twice;
+  * frame assembly: one all-gather of each rank's finished band per output buffer.
+Bands are uneven, so the gathers are lists of per-rank row views of the destination buffer.
 """
 import numpy as np
+
+ACTIVE_PIXEL_COST = 10.0  # cost of an active pixel relative to a primary ray (bench scene: 2.0 ns vs 0.19 ns)
 
 
 def row_bands(height, world_size):
     """Contiguous bands of ceil(H / N) rows; trailing ranks may get fewer (or zero) rows."""
     rows = -(-height // world_size)
     return [(min(r * rows, height), min((r + 1) * rows, height)) for r in range(world_size)]
+
+
+def balanced_bands(row_cost, world_size):
+    """Contiguous bands of (nearly) equal summed cost.  row_cost: per-row non-negative costs.
+    Deterministic in its input; every band of a frame with H >= N rows gets at least one row."""
+    c = np.asarray(row_cost, np.float64)
+    H = len(c)
+    if world_size <= 1:
+        return [(0, H)]
+    c = np.maximum(c, 0.0) + 1e-9
+    cum = np.concatenate([[0.0], np.cumsum(c)])
+    cuts = [0]
+    for k in range(1, world_size):
+        y = int(np.searchsorted(cum, cum[-1] * k / world_size, side="left"))
+        lo = min(cuts[-1] + 1, H)                # at least one row for the previous band ...
+        hi = max(H - (world_size - k), lo)      # ... and one for each band still to come
+        cuts.append(min(max(y, lo), hi))
+    cuts.append(H)
+    return [(cuts[i], cuts[i + 1]) for i in range(world_size)]
+
+
+def row_costs(active_per_row, width):
+    """Cost model of a row: one primary ray per pixel + ACTIVE_PIXEL_COST per active pixel."""
+    return float(width) + ACTIVE_PIXEL_COST * np.asarray(active_per_row, np.float64)
 
 
 def denoise_reach(iterations):
@@ -46,34 +81,45 @@ class _CudaView:
 
 
 def device_tensor(renderer, name):
-    """torch tensor aliasing one of the renderer's frame buffers ((H, W, 4) f32 or (H, W) i32)."""
+    """torch tensor aliasing one of the renderer's frame buffers: (H, W, 4) f32, (H, W, 2) f32 for
+    the packed denoise values, (H, W) i32 for RGBA8."""
     import torch
 
     ptr = renderer.device_ptr(name)
     if name == "rgba8":
         v = _CudaView(ptr, (renderer.H, renderer.W), "<i4")
     else:
-        v = _CudaView(ptr, (renderer.H, renderer.W, 4), "<f4")
+        v = _CudaView(ptr, (renderer.H, renderer.W, 2 if name == "dn_val" else 4), "<f4")
     return torch.as_tensor(v, device="cuda")
 
 
-def assemble(full, band, world_size, group=None):
-    """All-gather every rank's band of `full` (a (H, ...) tensor, rows [y0, y1) valid on the rank
-    that owns them) so that all ranks end with the whole frame.  Bands come from row_bands()."""
+def _contiguous_equal(bands, height):
+    return (len({b[1] - b[0] for b in bands}) == 1 and bands[0][0] == 0 and bands[-1][1] == height
+            and all(bands[i][1] == bands[i + 1][0] for i in range(len(bands) - 1)))
+
+
+def assemble(full, bands, rank, group=None):
+    """All-gather every rank's band of `full` (a (H, ...) tensor whose rows bands[rank] are valid on
+    this rank) so that all ranks end with the whole frame.  `bands`: the same list on every rank."""
+    import torch
     import torch.distributed as dist
 
-    H = full.shape[0]
-    bands = row_bands(H, world_size)
-    rows = bands[0][1] - bands[0][0]
-    y0, y1 = band
-    if H == rows * world_size:  # the common case (1080 / 8, 2160 / 8 ...): gather in place
-        dist.all_gather_into_tensor(full, full[y0:y1], group=group)
+    world = len(bands)
+    if world == 1:
         return full
-    import torch
-
+    y0, y1 = bands[rank]
+    if _contiguous_equal(bands, full.shape[0]):
+        dist.all_gather_into_tensor(full, full[y0:y1], group=group)  # equal bands: gather in place
+        return full
+    if dist.get_backend(group) == "nccl" and all(b[1] > b[0] for b in bands):
+        # uneven bands: the output list are row views of the destination itself (NCCL runs this as one
+        # group of broadcasts, no staging copy)
+        dist.all_gather([full[a:b] for a, b in bands], full[y0:y1], group=group)
+        return full
+    rows = max(max(b[1] - b[0] for b in bands), 1)  # gloo, or empty bands: pad to a common size
     mine = torch.zeros((rows,) + tuple(full.shape[1:]), dtype=full.dtype, device=full.device)
     mine[: y1 - y0] = full[y0:y1]
-    parts = [torch.empty_like(mine) for _ in range(world_size)]
+    parts = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(parts, mine, group=group)
     for (a, b), p in zip(bands, parts):
         if b > a:
@@ -81,32 +127,126 @@ def assemble(full, band, world_size, group=None):
     return full
 
 
-class TiledRenderer:
-    """One rank's share of a tile-partitioned frame: renders its band (+ denoise halo) with the
-    rank's Renderer and assembles finished buffers across ranks."""
+def _overlap(a, b):
+    lo, hi = max(a[0], b[0]), min(a[1], b[1])
+    return (lo, hi) if hi > lo else None
 
-    def __init__(self, renderer, rank, world_size, denoise_iterations=5):
+
+def halo_plan(bands, rank, height, iterations):
+    """Row ranges to exchange so that `rank` holds the rows its denoise pass reads: a list of
+    (peer, (y0, y1), 'send' | 'recv'), in an order both sides agree on."""
+    plan = []
+    mine = bands[rank]
+    my_halos = halo_bands(mine, height, iterations)
+    for q, bq in enumerate(bands):
+        if q == rank or bq[1] <= bq[0]:
+            continue
+        for h in my_halos:                       # rows of q's band that I read
+            o = _overlap(bq, h)
+            if o:
+                plan.append((q, o, "recv"))
+        if mine[1] > mine[0]:
+            for h in halo_bands(bq, height, iterations):  # rows of my band that q reads
+                o = _overlap(mine, h)
+                if o:
+                    plan.append((q, o, "send"))
+    return plan
+
+
+def exchange_halos(tensors, bands, rank, iterations, group=None):
+    """Point-to-point exchange of the denoise halo rows of every tensor in `tensors` ((H, ...) each):
+    at most 2*(2^iters - 1) rows per side instead of the whole frame."""
+    import torch.distributed as dist
+
+    H = tensors[0].shape[0]
+    plan = halo_plan(bands, rank, H, iterations)
+    ops = []
+    for peer, (a, b), kind in plan:
+        for t in tensors:
+            ops.append(dist.P2POp(dist.isend if kind == "send" else dist.irecv, t[a:b], peer, group))
+    if not ops:
+        return
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+
+
+class TiledRenderer:
+    """One rank's share of a tile-partitioned frame: renders its band with the rank's Renderer,
+    exchanges packed denoise rows, and assembles finished buffers across ranks."""
+
+    def __init__(self, renderer, rank, world_size, denoise_iterations=5, group=None):
         self.r = renderer
         self.rank, self.world = rank, world_size
         self.iters = denoise_iterations
-        self.band = row_bands(renderer.H, world_size)[rank]
-        self.halos = halo_bands(self.band, renderer.H, denoise_iterations) if world_size > 1 else []
+        self.group = group
+        self.bands = row_bands(renderer.H, world_size)
+        self.row_cost = None
+        self._views = {}
+
+    @property
+    def band(self):
+        return self.bands[self.rank]
+
+    def _t(self, name):
+        if name not in self._views:
+            self._views[name] = device_tensor(self.r, name)
+        return self._views[name]
+
+    def rebalance(self, measured_ms=None):
+        """Cut the bands by cost (all ranks must call).  First call: the model of row_costs() from the
+        active-pixel counts of the last frame.  With measured_ms (this rank's device time for its band
+        in the last frames) the model is corrected by feedback: every row of a band is scaled by
+        measured time / modelled cost of that band, then the frame is cut again."""
+        if self.world == 1:
+            return self.bands
+        import torch
+        import torch.distributed as dist
+
+        nccl = dist.get_backend(self.group) == "nccl"
+        assemble(self._t("accum"), self.bands, self.rank, self.group)  # progressive sums follow their rows
+        if self.row_cost is None or measured_ms is None:
+            counts = self.r.row_active_counts()
+            y0, y1 = self.band
+            mine = np.zeros(self.r.H, np.int32)
+            mine[y0:y1] = counts[y0:y1]  # only the rows this rank rendered are current
+            t = torch.from_numpy(mine)
+            t = t.cuda() if nccl else t
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            self.row_cost = row_costs(t.cpu().numpy(), self.r.W)
+        else:
+            t = torch.zeros(self.world, dtype=torch.float64)
+            t[self.rank] = float(measured_ms)
+            t = t.cuda() if nccl else t
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            ms = t.cpu().numpy()
+            cost = self.row_cost.copy()
+            for (y0, y1), m in zip(self.bands, ms):
+                if y1 > y0 and m > 0:
+                    cost[y0:y1] *= m / max(cost[y0:y1].sum(), 1e-30)
+            self.row_cost = cost
+        self.bands = balanced_bands(self.row_cost, self.world)
+        return self.bands
 
     def render_ratio_frame(self, accum_id, mode=1, shadow_spp=4, denoise=True):
-        """RATIO frame + denoise + combine for this rank's band; asynchronous on the renderer's stream."""
+        """RATIO frame + denoise + combine for this rank's band; asynchronous on the renderer's stream
+        (the collectives run on the current torch stream, which must be the renderer's)."""
         from . import api
 
         y0, y1 = self.band
-        if y1 <= y0:
-            return
         rows = None if self.world == 1 else (y0, y1)
-        self.r.render(api.RATIO, accum_id=accum_id, mode=mode, shadow_spp=shadow_spp, rows=rows, sync=False)
+        if y1 > y0:
+            self.r.render(api.RATIO, accum_id=accum_id, mode=mode, shadow_spp=shadow_spp, rows=rows, sync=False)
         if denoise:
-            for h in self.halos:
-                self.r.render(api.RATIO, accum_id=accum_id, mode=mode, shadow_spp=shadow_spp, rows=h, sync=False,
-                              count_rays=False)
-            self.r.denoise(iterations=self.iters, rows=rows)
-        self.r.ratio_combine(use_denoised=denoise, rows=rows)
+            if self.world == 1:
+                self.r.denoise(iterations=self.iters)
+            else:
+                if y1 > y0:
+                    self.r.denoise_pack(rows=rows)
+                exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
+                if y1 > y0:
+                    self.r.denoise_filter(iterations=self.iters, rows=rows)
+        if y1 > y0:
+            self.r.ratio_combine(use_denoised=denoise, rows=rows)
 
     def render_path_frame(self, accum_id, mode=1, max_depth=8):
         from . import api
@@ -117,8 +257,8 @@ class TiledRenderer:
         rows = None if self.world == 1 else (y0, y1)
         self.r.render(api.PATH, accum_id=accum_id, mode=mode, max_depth=max_depth, rows=rows, sync=False)
 
-    def assemble(self, names, group=None):
+    def assemble(self, names):
         if self.world == 1:
             return
         for n in names:
-            assemble(device_tensor(self.r, n), self.band, self.world, group)
+            assemble(self._t(n), self.bands, self.rank, self.group)

@@ -337,6 +337,27 @@ def test_ray_stream_equals_fused_shadow_kernel(renderer_factory):
         assert ca["rays_shadow"] == cb["rays_shadow"] == spp * cb["active_pixels"]
 
 
+def test_path_persistent_equals_wavefront(renderer_factory):
+    """PATH: the persistent all-bounces kernel (default) against the per-bounce ray-stream wavefront: the
+    same device functions in another schedule.  fma contraction may differ between the two kernels, so
+    compared like the fused form below."""
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
+    r = renderer_factory(sc)
+    for depth in (1, 3, 8):
+        r.render(api.PATH, accum_id=0, mode=1, max_depth=depth, path_wavefront=True)
+        a, ca = r.download("accum"), r.counters()
+        r.render(api.PATH, accum_id=0, mode=1, max_depth=depth)
+        b, cb = r.download("accum"), r.counters()
+        assert (np.isnan(a).any(-1) != np.isnan(b).any(-1)).sum() <= 4
+        m = np.isfinite(a).all(-1) & np.isfinite(b).all(-1)
+        d = (a[m] - b[m])[:, :3] / np.maximum(1.0, np.abs(a[m][:, :3]))
+        assert np.sqrt((d * d).mean()) <= 1e-3
+        assert (np.abs(d).max(-1) > 1e-4).mean() < 2e-3
+        assert abs(ca["rays_bounce"] - cb["rays_bounce"]) <= max(4, ca["rays_bounce"] // 500)
+        assert cb["rays_bounce"] >= cb["active_pixels"]
+        assert cb["kernel_launches"] - ca["kernel_launches"] == 3        # primary, all bounces, accumulate
+
+
 def test_path_stream_equals_fused_bounce_kernel(renderer_factory):
     """PATH: per-bounce ray streams vs the fused bounce kernel.  Same arithmetic, different fma
     contraction, so a handful of grazing bounce rays may end a path differently: compared by
@@ -345,7 +366,7 @@ def test_path_stream_equals_fused_bounce_kernel(renderer_factory):
     r = renderer_factory(sc)
     r.render(api.PATH, accum_id=0, mode=1, max_depth=8, fused_shadow=True)
     a, ca = r.download("accum"), r.counters()
-    r.render(api.PATH, accum_id=0, mode=1, max_depth=8, fused_shadow=False)
+    r.render(api.PATH, accum_id=0, mode=1, max_depth=8, fused_shadow=False, path_wavefront=True)
     b, cb = r.download("accum"), r.counters()
     assert (np.isnan(a).any(-1) != np.isnan(b).any(-1)).sum() <= 4
     m = np.isfinite(a).all(-1) & np.isfinite(b).all(-1)
@@ -354,3 +375,31 @@ def test_path_stream_equals_fused_bounce_kernel(renderer_factory):
     assert (np.abs(d).max(-1) > 1e-4).mean() < 2e-3
     assert abs(ca["rays_bounce"] - cb["rays_bounce"]) <= max(4, ca["rays_bounce"] // 500)
     assert cb["rays_bounce"] > cb["active_pixels"]
+
+
+def test_denoise_halves_and_row_counts(renderer_factory):
+    """orb_denoise == orb_denoise_pack + orb_denoise_filter; a band filtered from packed rows that were
+    written band by band (as ranks exchange them) equals the same rows of the full-frame filter; the
+    per-row active counts equal what the G-buffer says."""
+    sc = scenes.scene_cornell(96, 160)
+    r = renderer_factory(sc)
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    r.denoise(iterations=4)
+    want = {k: r.download(k) for k in ("sto_direct_dn", "sto_no_vis_dn")}
+    z = np.zeros((160, 96, 4), np.float32)
+    for k in want:
+        r.upload(k, z)
+    for rows in ((0, 50), (50, 51), (51, 160)):     # every "rank" packs its own rows
+        r.denoise_pack(rows=rows)
+    g, v = r.download("dn_guide"), r.download("dn_val")
+    assert g.shape == (160, 96, 4) and v.shape == (160, 96, 2)
+    assert np.array_equal(v[..., 0], r.download("sto_direct")[..., 0], equal_nan=True)
+    for rows in ((51, 160), (0, 50), (50, 51)):
+        for name, a in (("dn_guide", g), ("dn_val", v)):  # the filter's ping-pong overwrote dn_val: restore the gathered rows
+            r.upload(name, a)
+        r.denoise_filter(iterations=4, rows=rows)
+        for k in want:
+            assert np.array_equal(r.download(k, rows=rows), want[k][rows[0]:rows[1]], equal_nan=True), (k, rows)
+    mid = r.download("materialID")[..., 0]
+    prim, _, _ = r.hit_records()
+    assert np.array_equal(r.row_active_counts(), ((prim >= 0) & (mid != 0)).sum(1).astype(np.int32))

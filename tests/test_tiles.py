@@ -27,6 +27,25 @@ def test_row_bands_cover_the_frame():
     assert tiles.halo_bands((0, 135), 1080, 5) == [(135, 197)]
 
 
+def test_balanced_bands():
+    for H, n in ((1080, 8), (1080, 2), (37, 4), (8, 8), (5, 3)):
+        rng = np.random.default_rng(H + n)
+        cost = rng.uniform(0, 1, H) * (np.arange(H) < H // 2)      # all the work in the lower half
+        b = tiles.balanced_bands(cost, n)
+        assert len(b) == n and b[0][0] == 0 and b[-1][1] == H
+        assert all(b[i][1] == b[i + 1][0] for i in range(n - 1))
+        assert all(y1 > y0 for y0, y1 in b)                          # nobody is left without rows
+        if H >= 100:
+            sums = [cost[y0:y1].sum() for y0, y1 in b]
+            assert max(sums) <= cost.sum() / n + cost.max() * 2       # equal to within a row or two
+    # uniform cost -> equal bands
+    assert tiles.balanced_bands(np.ones(1080), 8) == tiles.row_bands(1080, 8)
+    # the cost model: a row of sky costs W, a row full of geometry (1 + ACTIVE_PIXEL_COST) W
+    c = tiles.row_costs([0, 1920], 1920)
+    assert c[0] == 1920 and c[1] == 1920 * (1 + tiles.ACTIVE_PIXEL_COST)
+    assert tiles.balanced_bands([1.0], 1) == [(0, 1)]
+
+
 def test_denoise_halo_is_sufficient(restatement):
     """Filtering a band from (band + halo) rows only gives the same pixels as filtering the frame."""
     W, H, iters = 40, 96, 3
@@ -66,19 +85,20 @@ def _worker(rank, world, port, W, H, out_dir):
         o = _oracle.Oracle("restatement")
         o.load_scene(sc)
         o.set_options(1, 4, 1)
-        band = tiles.row_bands(H, world)[rank]
+        bands = tiles.row_bands(H, world) if H < 8 else tiles.balanced_bands(np.arange(H) % 5 + 1.0, world)
+        band = bands[rank]
         part = o.render(W, H, _oracle.RATIO, 3, rows=band) if band[1] > band[0] else None
         res = {}
         for name in ("ltc", "sto_direct", "accum"):
             full = torch.zeros((H, W, 4), dtype=torch.float32)
             if part is not None:
                 full[band[0]:band[1]] = torch.from_numpy(part[name][band[0]:band[1]])
-            tiles.assemble(full, band, world)
+            tiles.assemble(full, bands, rank)
             res[name] = full.numpy()
         rg = torch.zeros((H, W), dtype=torch.int32)
         if part is not None:
             rg[band[0]:band[1]] = torch.from_numpy(part["rgba8"][band[0]:band[1]].view(np.int32))
-        tiles.assemble(rg, band, world)
+        tiles.assemble(rg, bands, rank)
         res["rgba8"] = rg.numpy()
         np.savez(os.path.join(out_dir, "rank%d.npz" % rank), **res)
     finally:
@@ -98,3 +118,49 @@ def test_assembly_over_gloo_equals_full_frame(tmp_path, world, W, H):
         for name in ("ltc", "sto_direct", "accum"):
             assert np.array_equal(got[name], full[name], equal_nan=True), (rank, name)
         assert np.array_equal(got["rgba8"].view(np.uint32), full["rgba8"])
+
+
+def test_halo_plan_is_symmetric():
+    for H, n, iters in ((1080, 8, 5), (96, 3, 3), (40, 4, 2), (200, 8, 5)):
+        bands = tiles.balanced_bands(np.arange(H) % 7 + 1.0, n)
+        plans = [tiles.halo_plan(bands, r, H, iters) for r in range(n)]
+        for r in range(n):
+            need = tiles.halo_bands(bands[r], H, iters)
+            got = sorted(o for _, o, k in plans[r] if k == "recv")
+            # the received pieces tile the halo exactly
+            assert sum(b - a for a, b in got) == sum(b - a for a, b in need)
+            for q, o, k in plans[r]:
+                other = "send" if k == "recv" else "recv"
+                assert (r, o, other) in plans[q]
+
+
+def _halo_worker(rank, world, port, H, iters, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        bands = tiles.balanced_bands(np.arange(H) % 5 + 1.0, world)
+        y0, y1 = bands[rank]
+        a = torch.full((H, 3, 4), -1.0)
+        b = torch.full((H, 3, 2), -1.0)
+        rows = torch.arange(H, dtype=torch.float32)
+        a[y0:y1] = rows[y0:y1, None, None]
+        b[y0:y1] = rows[y0:y1, None, None] * 2
+        tiles.exchange_halos([a, b], bands, rank, iters)
+        np.savez(os.path.join(out_dir, "halo%d.npz" % rank), a=a.numpy(), b=b.numpy(), bands=np.array(bands))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,H,iters", [(2, 40, 2), (3, 64, 3)])
+def test_halo_exchange_over_gloo(tmp_path, world, H, iters):
+    mp.spawn(_halo_worker, args=(world, _free_port(), H, iters, str(tmp_path)), nprocs=world, join=True)
+    reach = tiles.denoise_reach(iters)
+    for rank in range(world):
+        g = np.load(os.path.join(str(tmp_path), "halo%d.npz" % rank))
+        y0, y1 = g["bands"][rank]
+        lo, hi = max(0, y0 - reach), min(H, y1 + reach)
+        rows = np.arange(H, dtype=np.float32)
+        assert np.array_equal(g["a"][lo:hi, 0, 0], rows[lo:hi])       # band + halo present
+        assert np.array_equal(g["b"][lo:hi, 2, 1], rows[lo:hi] * 2)
+        assert (g["a"][:lo] == -1).all() and (g["a"][hi:] == -1).all()  # nothing else was sent
