@@ -119,6 +119,9 @@ typedef struct OrbRenderConfig {
                                      ray-stream kernels (kept for A/B measurement; same results) */
 #define ORB_RENDER_PATH_WAVEFRONT 4 /* PATH: one generate / trace / shade wavefront per bounce instead of the
                                        persistent all-bounces kernel (kept for A/B measurement) */
+#define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO: run the instrumented twin of the shadow-ray traversal kernel; node
+                                        records fetched / triangle records tested land in OrbCounters.nodes_visited
+                                        / tris_tested (same results, slower; bench.py's roofline uses it once) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 
@@ -151,14 +154,15 @@ typedef struct OrbCounters {
 typedef enum OrbStage {
     ORB_STAGE_PRIMARY = 0,      /* camera rays + closest hit + G-buffer write + queue compaction */
     ORB_STAGE_LTC = 1,          /* LTC area-light sum over the active-pixel queue                */
-    ORB_STAGE_SHADOW = 2,       /* ratio estimator shadow rays                                   */
+    ORB_STAGE_SHADOW = 2,       /* ratio estimator: shadow-ray generation + resolve (traversal: TRACE) */
     ORB_STAGE_PATH = 3,         /* all bounce kernels of a PATH frame                            */
     ORB_STAGE_ACCUMULATE = 4,   /* accum += colour, RGBA8                                        */
     ORB_STAGE_DENOISE_PACK = 5, /* guide / value packing                                         */
     ORB_STAGE_DENOISE = 6,      /* a-trous iterations                                            */
     ORB_STAGE_COMBINE = 7,      /* ratio combine                                                 */
     ORB_STAGE_LTC_GBUFFER = 8,  /* stand-alone LTC pass over a saved G-buffer                    */
-    ORB_STAGE_COUNT = 9
+    ORB_STAGE_TRACE = 9,        /* RATIO: the shadow-ray stream traversal kernel alone           */
+    ORB_STAGE_COUNT = 10
 } OrbStage;
 
 typedef struct OrbStageTimes {

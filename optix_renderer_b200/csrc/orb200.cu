@@ -368,11 +368,12 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
 // order; it only delays the pruning by best.t a little.  Against the batching form above this
 // keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
 // triangle test).
-template <bool LOCAL_STACK>
+template <bool LOCAL_STACK, bool COUNT = false>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
-                    int node_min, int height) {
+                    int node_min, int height, unsigned long long* __restrict__ stats = nullptr) {
+    unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
     int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
@@ -434,6 +435,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
         // node phase
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {
+            if (COUNT && t.cur >= 0) ++c_nodes;
             if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
             if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // postpone this leaf, keep walking
                 leaf = t.cur;
@@ -443,12 +445,22 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
         }
         // leaf phase
         if (leaf != 0) {
-            trav_leaf_test(t, s, leaf);
+            trav_leaf_test(t, s, leaf, COUNT ? &c_tris : nullptr);
             leaf = 0;
             if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
                 t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
             }
+        }
+    }
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) {
+            c_nodes += __shfl_xor_sync(FULL, c_nodes, o);
+            c_tris += __shfl_xor_sync(FULL, c_tris, o);
+        }
+        if (lane == 0) {
+            atomicAdd(stats, (unsigned long long)c_nodes);
+            atomicAdd(stats + 1, (unsigned long long)c_tris);
         }
     }
 }
@@ -1077,6 +1089,9 @@ struct OrbContext {
     int leaf_min = 12;
     int node_min = 16;
     int trace_variant = 1;  // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec)
+    cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int ltc_overlap = 0;  // measured: no gain (3.392 vs 3.394 ms per RATIO frame), kept as a knob
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
@@ -1106,15 +1121,17 @@ struct StageTimer {
         else cudaEventCreate(&e);
         return e;
     }
-    StageTimer(OrbContext* ctx, int stage, int launches) : c(ctx), on(ctx->profiling) {
+    cudaStream_t stream;
+    StageTimer(OrbContext* ctx, int stage, int launches, cudaStream_t on_stream = nullptr, bool enable = true)
+        : c(ctx), on(ctx->profiling && enable), stream(on_stream ? on_stream : ctx->stream) {
         if (!on) return;
         sp.stage = stage; sp.launches = launches;
         sp.e0 = get(c); sp.e1 = get(c);
-        cudaEventRecord(sp.e0, c->stream);
+        cudaEventRecord(sp.e0, stream);
     }
     ~StageTimer() {
         if (!on) return;
-        cudaEventRecord(sp.e1, c->stream);
+        cudaEventRecord(sp.e1, stream);
         c->spans.push_back(sp);
     }
 };
@@ -1231,6 +1248,10 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
     if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
+    if (const char* e = getenv("ORB_LTC_OVERLAP")) c->ltc_overlap = atoi(e);
+    CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     if (const char* e = getenv("ORB_PATH_SHADE_MIN")) c->path_shade_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_PATH_NODE_MIN")) c->path_node_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
@@ -1248,6 +1269,9 @@ void orb_destroy(OrbContext* c) {
     cudaFree(c->stream_cursor);
     cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->cnt); cudaFree(c->unit_in); cudaFree(c->unit_out);
     if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (c->aux_stream) { cudaStreamSynchronize(c->aux_stream); cudaStreamDestroy(c->aux_stream); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     delete c;
 }
 
@@ -1497,10 +1521,17 @@ static int ensure_stream(OrbContext* c, size_t n_rays) {
 }
 
 // closest hits of the rays in c->stream_rays -> c->stream_hits; the ray count is *n_items * mult on the device
-static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned mult) {
+static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned mult, bool count = false,
+                               bool timed = false) {
     cudaStream_t st = c->stream;
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
-    if (c->trace_variant == 1 && c->local_stack && c->height <= LOCAL_STACK_MAX) {
+    StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
+    if (count && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // instrumented twin of the default kernel
+        const int g = persistent_grid(c, k_trace_stream_spec<true, true>, TRACE_BLOCK, 0);
+        k_trace_stream_spec<true, true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
+                                                                   c->stream_cursor, c->refill_min, c->node_min,
+                                                                   c->height, &c->cnt->nodes_visited);
+    } else if (c->trace_variant == 1 && c->local_stack && c->height <= LOCAL_STACK_MAX) {
         const int g = persistent_grid(c, k_trace_stream_spec<true>, TRACE_BLOCK, 0);
         k_trace_stream_spec<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
                                                              c->stream_cursor, c->refill_min, c->node_min, c->height);
@@ -1558,18 +1589,24 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         if (count_rays) c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
     }
     const float4* colour_src = c->colour;
-    if (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) {
-        StageTimer tm(c, ORB_STAGE_LTC, 1);
+    // RATIO: the LTC sum (fp32-issue bound, no dependence on the shadow rays) is enqueued on a second
+    // stream AFTER the shadow-ray kernels, so its CTAs fill the SMs the persistent traversal kernel
+    // leaves idle while its last rays finish (floor of ~0.17 ms per traversal launch, profiles/r1k).
+    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & ORB_RENDER_FUSED_SHADOW);
+    auto launch_ltc = [&](cudaStream_t ls) {
+        StageTimer tm(c, ORB_STAGE_LTC, 1, ls);
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
         if (renderer == ORB_RATIO) {
             // light pixels already hold emit in `ltc` (k_primary), so `ltc` IS the frame colour
-            k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
             colour_src = f.ltc;
         } else {
-            k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.colour, nullptr);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.colour, nullptr);
         }
         c->counters.kernel_launches++;
-    }
+    };
+    if ((renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && !ltc_beside_shadow) launch_ltc(st);
+    if (ltc_beside_shadow) CK(cudaEventRecord(c->ev_fork, st));  // k_primary done: queue and G-buffers are final
     if (renderer == ORB_RATIO) {
         if (cfg->flags & ORB_RENDER_FUSED_SHADOW) {  // A/B: one thread per pixel, n rays in sequence
             StageTimer tm(c, ORB_STAGE_SHADOW, 1);
@@ -1580,15 +1617,23 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
             const size_t npx = (size_t)(y1 - y0) * c->W;
             int rc = ensure_stream(c, npx * (size_t)spp);
             if (rc) return rc;
-            StageTimer tm(c, ORB_STAGE_SHADOW, 3);
             const int n_lights = (int)c->h_lights.size();
             if (n_lights > 0) {
-                const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
-                k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
-                rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp);
+                {
+                    StageTimer tm(c, ORB_STAGE_SHADOW, 1);
+                    const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
+                    k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
+                    c->counters.kernel_launches++;
+                }
+                rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true);
                 if (rc) return rc;
-                c->counters.kernel_launches++;
             }
+            if (ltc_beside_shadow) {  // depends on k_primary only, but is SUBMITTED behind the traversal kernel
+                CK(cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+                launch_ltc(c->aux_stream);
+                CK(cudaEventRecord(c->ev_join, c->aux_stream));
+            }
+            StageTimer tm(c, ORB_STAGE_SHADOW, 1);
             const int gr = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);
             k_shadow_resolve<<<gr, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->stream_hits);
             c->counters.kernel_launches++;
@@ -1659,6 +1704,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
         }
     }
+    if (ltc_beside_shadow) CK(cudaStreamWaitEvent(st, c->ev_join, 0));
     {
         StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
         const size_t n = (size_t)(y1 - y0) * c->W;

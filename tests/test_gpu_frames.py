@@ -337,6 +337,30 @@ def test_ray_stream_equals_fused_shadow_kernel(renderer_factory):
         assert ca["rays_shadow"] == cb["rays_shadow"] == spp * cb["active_pixels"]
 
 
+def test_instrumented_traversal_counts(renderer_factory):
+    """ORB_RENDER_COUNT_TRAVERSAL: the instrumented twin of the shadow-ray kernel writes the same frame and
+    reports node / triangle fetch counts (bench.py's algorithmic bytes); the TRACE stage timer covers it."""
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
+    r = renderer_factory(sc)
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    a = {k: r.download(k) for k in ("sto_direct", "sto_no_vis", "ltc", "accum")}
+    c0 = r.counters()
+    assert c0["nodes_visited"] == 0 and c0["tris_tested"] == 0
+    r.set_profiling(True)
+    r.stage_times()
+    r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4, count_traversal=True)
+    st = r.stage_times()
+    r.set_profiling(False)
+    c1 = r.counters()
+    for k in a:
+        assert np.array_equal(a[k], r.download(k), equal_nan=True), k
+    rays = c1["rays_shadow"]
+    assert rays == 4 * c1["active_pixels"] > 0
+    assert c1["nodes_visited"] >= rays            # every ray fetches at least the root
+    assert 0 < c1["tris_tested"] < 64 * rays
+    assert st["trace"][1] == 1 and st["trace"][0] > 0 and st["shadow"][1] == 2
+
+
 def test_path_persistent_equals_wavefront(renderer_factory):
     """PATH: the persistent all-bounces kernel (default) against the per-bounce ray-stream wavefront: the
     same device functions in another schedule.  fma contraction may differ between the two kernels, so
