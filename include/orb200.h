@@ -66,7 +66,7 @@ typedef enum OrbBufferId {
     ORB_BUF_STO_DIRECT_DN = 15, /* float4: denoised sto_direct  (stodirectDenoise.exr)             */
     ORB_BUF_STO_NO_VIS_DN = 16, /* float4: denoised sto_no_vis  (stoNoVisDenoise.exr)              */
     ORB_BUF_RATIO_FINAL = 17,  /* float4: ltc * (stoDirect / stoNoVis) (final_ratio_estimator.exr) */
-    ORB_BUF_DN_GUIDE = 18,     /* float4: denoise guide (n.xyz, camera distance or < 0 for lights / misses)      */
+    ORB_BUF_DN_GUIDE = 18,     /* float4: denoise guide (n.xyz, camera distance; -1e30 on lights / misses)       */
     ORB_BUF_DN_VAL = 19,       /* float2 (8 B/px): packed (sto_direct.x, sto_no_vis.x), the filter's input      */
     ORB_BUF_COUNT = 20
 } OrbBufferId;

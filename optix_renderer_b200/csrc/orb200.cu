@@ -838,11 +838,12 @@ __global__ void k_accumulate(FrameView f, const float4* __restrict__ src, int ac
 // cuda_include/denoise/bilateral.cuh is an empty file).  CPU statement of the same
 // filter: oracle/restate.cpp ora_denoise().
 //   value  v(q) = (sto_direct.x, sto_no_vis.x)                       packed float2
-//   guide  g(q) = (n.xyz, depth = |p - cam|), depth < 0 for pixels with materialID == 0 or
-//                 n == 0 (lights, misses): passed through unfiltered and never used as a tap
+//   guide  g(q) = (n.xyz, depth = |p - cam|), depth = -1e30 for pixels with materialID == 0, n == 0
+//                 (lights, misses) or a non-finite guide: passed through unfiltered, never used as a tap
 //   weight w(q) = B3(dx) B3(dy) * max(0, n_c . n_q)^sigma_n * exp(-|d_c - d_q| / (sigma_p * step))
 //                 (* exp(-|v_c - v_q| / sigma_c) per image when sigma_c > 0); NaN taps are skipped
 // ---------------------------------------------------------------------------------------------
+#define DN_SKIP_DEPTH (-1e30f)  // guide.w of a pixel that is neither filtered nor used as a tap
 __global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__ guide, float2* __restrict__ val) {
     const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -850,55 +851,100 @@ __global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__
         const float4 nn = ld_stream(f.normal + ofs), pp = ld_stream(f.position + ofs);
         const float4 mm = ld_stream(f.material_id + ofs);
         const float4 a = ld_stream(f.sto_direct + ofs), b = ld_stream(f.sto_no_vis + ofs);
-        const bool skip = (nn.x == 0.f && nn.y == 0.f && nn.z == 0.f) || mm.x == 0.f;
-        const float depth = skip ? -1.f : length(v3(pp) - cam_pos);
-        guide[ofs] = make_float4(nn.x, nn.y, nn.z, depth);
-        val[ofs] = make_float2(a.x, b.x);
+        float depth = length(v3(pp) - cam_pos);
+        // lights, misses, and pixels whose guide is not finite (every weight would be NaN: the tap-skipping
+        // definition passes them through and never uses them as taps either).  The sentinel is so far from
+        // any depth that exp(-|dz| / (sigma_p step)) is exactly 0: the filter needs no per-tap test.
+        const bool skip = (nn.x == 0.f && nn.y == 0.f && nn.z == 0.f) || mm.x == 0.f ||
+                          !(fabsf(nn.x) + fabsf(nn.y) + fabsf(nn.z) < 1e18f) || !(depth < 1e18f);
+        guide[ofs] = make_float4(nn.x, nn.y, nn.z, skip ? DN_SKIP_DEPTH : depth);
+        val[ofs] = skip ? make_float2(0.f, 0.f) : make_float2(a.x, b.x);  // 0 * weight 0 stays 0 (emit may be inf)
     }
 }
 
-__constant__ float c_b3[5] = {1.f / 16.f, 1.f / 4.f, 3.f / 8.f, 1.f / 4.f, 1.f / 16.f};
+// MUFU lg2 / ex2 without the denormal fix-up code of __log2f / exp2f (a weight below 2^-126 is 0 either way)
+__device__ __forceinline__ float fast_lg2(float x) {
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ constexpr float b3_tap(int k) { return k == 0 ? 0.375f : ((k == 1 || k == -1) ? 0.25f : 0.0625f); }
 
-template <bool FINAL>
+// The 25 taps of one pixel.  INTERIOR: the whole block is further than 2*step from every frame edge, no
+// bounds tests.  COLOUR: sigma_c > 0.  STEP > 0: the tap distance as a compile-time constant (the column
+// offsets become immediates of the loads); 0: run-time `step`.  Skipped taps (guide sentinel: weight exactly
+// 0; NaN value) enter the sums as exact zeros, so the result is the one of the tap-skipping definition
+// (oracle/restate.cpp ora_denoise()).  The pass is issue-bound (25 taps x ~23 instructions against 32 B of
+// HBM traffic per pixel).
+template <bool COLOUR, bool INTERIOR, int STEP>
+__device__ __forceinline__ void atrous_taps(const float4* __restrict__ guide, const float2* __restrict__ vin, int W, int H,
+                                            int x, int y, int step_rt, float4 gc, float2 vc, float sigma_n,
+                                            float inv_sigma_p, float inv_sigma_c, float& sd, float& sn, float& wd,
+                                            float& wn) {
+    const int step = STEP > 0 ? STEP : step_rt;
+#pragma unroll
+    for (int j = -2; j <= 2; j++) {
+        const int yy = y + j * step;
+        if (!INTERIOR && (yy < 0 || yy >= H)) continue;
+        const int row = yy * W + x;  // 32-bit pixel offsets: orb_resize refuses frames of 2^31 pixels or more
+        const float4* grow = guide + row;
+        const float2* vrow = vin + row;
+#pragma unroll
+        for (int i = -2; i <= 2; i++) {
+            const int dx = i * step;
+            if (!INTERIOR && (x + dx < 0 || x + dx >= W)) continue;
+            const float4 g = __ldg(grow + dx);
+            const float2 v = __ldg(vrow + dx);
+            // nd^sigma_n * exp(-|dz| / (sigma_p step)) as ONE ex2 of a sum of logs
+            const float nd = fmaxf(0.f, gc.x * g.x + gc.y * g.y + gc.z * g.z);
+            const float ln = sigma_n > 0.f ? sigma_n * fast_lg2(nd) : 0.f;
+            const float w = (b3_tap(i) * b3_tap(j)) * fast_ex2(ln - fabsf(gc.w - g.w) * inv_sigma_p);
+            float w0 = w, w1 = w;
+            bool ok0 = v.x == v.x, ok1 = v.y == v.y;
+            if (COLOUR) {
+                w0 *= fast_ex2(-fabsf(vc.x - v.x) * inv_sigma_c);
+                w1 *= fast_ex2(-fabsf(vc.y - v.y) * inv_sigma_c);
+                ok0 = ok0 && w0 == w0;  // NaN centre value
+                ok1 = ok1 && w1 == w1;
+            }
+            w0 = ok0 ? w0 : 0.f;
+            w1 = ok1 ? w1 : 0.f;
+            sd += w0 * (ok0 ? v.x : 0.f);
+            wd += w0;
+            sn += w1 * (ok1 ? v.y : 0.f);
+            wn += w1;
+        }
+    }
+}
+
+template <bool FINAL, bool COLOUR, int STEP>
 __global__ void __launch_bounds__(256)
 k_denoise_atrous(FrameView f, const float4* __restrict__ guide, const float2* __restrict__ vin, float2* __restrict__ vout,
                  float4* __restrict__ out_d, float4* __restrict__ out_n, int step, float sigma_n, float inv_sigma_p,
                  float inv_sigma_c) {
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int y = f.y0 + blockIdx.y * 8 + (threadIdx.x >> 5);
+    const int bx = blockIdx.x * 32, by = f.y0 + blockIdx.y * 8;
+    const int x = bx + (threadIdx.x & 31);
+    const int y = by + (threadIdx.x >> 5);
     if (x >= f.W || y >= f.y1) return;
-    const size_t ofs = (size_t)y * f.W + x;
+    const int ofs = y * f.W + x;
     const float4 gc = __ldg(guide + ofs);
     const float2 vc = __ldg(vin + ofs);
     float2 r = vc;
     if (gc.w >= 0.f) {
         float sd = 0.f, sn = 0.f, wd = 0.f, wn = 0.f;
-#pragma unroll
-        for (int j = -2; j <= 2; j++) {
-            const int yy = y + j * step;
-            if (yy < 0 || yy >= f.H) continue;
-#pragma unroll
-            for (int i = -2; i <= 2; i++) {
-                const int xx = x + i * step;
-                if (xx < 0 || xx >= f.W) continue;
-                const size_t q = (size_t)yy * f.W + xx;
-                const float4 g = __ldg(guide + q);
-                if (g.w < 0.f) continue;
-                const float2 v = __ldg(vin + q);
-                // nd^sigma_n * exp(-|dz| / (sigma_p step)) as ONE exp2 of a sum of logs (MUFU lg2 + ex2:
-                // the libm powf/expf pair made this pass issue-bound at 8 % of the HBM rate)
-                const float nd = fmaxf(0.f, gc.x * g.x + gc.y * g.y + gc.z * g.z);
-                const float ln = sigma_n > 0.f ? sigma_n * __log2f(nd) : 0.f;
-                float w = c_b3[i + 2] * c_b3[j + 2] * exp2f(ln - fabsf(gc.w - g.w) * inv_sigma_p);
-                float w0 = w, w1 = w;
-                if (inv_sigma_c > 0.f) {
-                    w0 *= exp2f(-fabsf(vc.x - v.x) * inv_sigma_c);
-                    w1 *= exp2f(-fabsf(vc.y - v.y) * inv_sigma_c);
-                }
-                if (v.x == v.x && w0 == w0) { sd += w0 * v.x; wd += w0; }
-                if (v.y == v.y && w1 == w1) { sn += w1 * v.y; wn += w1; }
-            }
-        }
+        const int reach = 2 * (STEP > 0 ? STEP : step);
+        const bool interior = bx >= reach && bx + 31 + reach < f.W && by >= reach && by + 7 + reach < f.H;
+        if (interior)
+            atrous_taps<COLOUR, true, STEP>(guide, vin, f.W, f.H, x, y, step, gc, vc, sigma_n, inv_sigma_p, inv_sigma_c, sd,
+                                            sn, wd, wn);
+        else
+            atrous_taps<COLOUR, false, STEP>(guide, vin, f.W, f.H, x, y, step, gc, vc, sigma_n, inv_sigma_p, inv_sigma_c, sd,
+                                             sn, wd, wn);
         if (wd > 0.f) r.x = sd / wd;
         if (wn > 0.f) r.y = sn / wn;
     }
@@ -912,6 +958,20 @@ k_denoise_atrous(FrameView f, const float4* __restrict__ guide, const float2* __
         }
     } else {
         vout[ofs] = r;
+    }
+}
+
+typedef void (*AtrousKernel)(FrameView, const float4*, const float2*, float2*, float4*, float4*, int, float, float, float);
+template <bool FINAL>
+static AtrousKernel atrous_kernel(bool colour, int step) {
+    if (colour) return k_denoise_atrous<FINAL, true, 0>;
+    switch (step) {
+        case 1: return k_denoise_atrous<FINAL, false, 1>;
+        case 2: return k_denoise_atrous<FINAL, false, 2>;
+        case 4: return k_denoise_atrous<FINAL, false, 4>;
+        case 8: return k_denoise_atrous<FINAL, false, 8>;
+        case 16: return k_denoise_atrous<FINAL, false, 16>;
+        default: return k_denoise_atrous<FINAL, false, 0>;
     }
 }
 
@@ -1491,6 +1551,7 @@ int orb_set_camera(OrbContext* c, const float pos[3], const float d00[3], const 
 
 int orb_resize(OrbContext* c, int32_t W, int32_t H) {
     NEED(c && W > 0 && H > 0, "orb_resize: bad size");
+    NEED((size_t)W * (size_t)H < ((size_t)1 << 31), "orb_resize: frames are limited to 2^31 - 1 pixels (32-bit pixel offsets)");
     CK(cudaSetDevice(c->device));
     CK(cudaStreamSynchronize(c->stream));
     free_frame(c);
@@ -1769,6 +1830,7 @@ int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, i
     if (cfg) d = *cfg;
     if (d.iterations <= 0) d.iterations = 5;
     NEED(d.iterations <= 8, "orb_denoise: at most 8 iterations");
+    NEED(d.sigma_position > 0.f && d.sigma_position <= 1e12f, "orb_denoise: sigma_position must be in (0, 1e12]");
     CK(cudaSetDevice(c->device));
     const size_t n = (size_t)c->W * c->H;
     if (!c->dn_val_b) CK(cudaMalloc(&c->dn_val_b, n * 8));
@@ -1784,16 +1846,16 @@ int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, i
         const float isc = d.sigma_colour > 0.f ? log2e / d.sigma_colour : 0.f;
         if (it == d.iterations - 1) {
             dim3 gb((c->W + 31) / 32, (y1 - y0 + 7) / 8);
-            k_denoise_atrous<true><<<gb, 256, 0, c->stream>>>(f, guide, val[cur], nullptr,
-                                                               (float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
-                                                               (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN], step,
-                                                               d.sigma_normal, isp, isc);
+            AtrousKernel k = atrous_kernel<true>(isc > 0.f, step);
+            k<<<gb, 256, 0, c->stream>>>(f, guide, val[cur], nullptr, (float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
+                                         (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN], step, d.sigma_normal, isp, isc);
         } else {
             const int r = denoise_reach(d.iterations, it);
             FrameView part = frame_view(c, std::max(0, y0 - r), std::min(c->H, y1 + r));
             dim3 grid((c->W + 31) / 32, (part.y1 - part.y0 + 7) / 8);
-            k_denoise_atrous<false><<<grid, 256, 0, c->stream>>>(part, guide, val[cur], val[cur ^ 1], nullptr, nullptr, step,
-                                                                  d.sigma_normal, isp, isc);
+            AtrousKernel k = atrous_kernel<false>(isc > 0.f, step);
+            k<<<grid, 256, 0, c->stream>>>(part, guide, val[cur], val[cur ^ 1], nullptr, nullptr, step, d.sigma_normal, isp,
+                                           isc);
             cur ^= 1;
         }
         c->counters.kernel_launches++;

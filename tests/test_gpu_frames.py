@@ -248,6 +248,29 @@ def test_denoise_vs_definition(renderer_factory, restatement):
     with np.errstate(all="ignore"):
         want = r.download("ltc")[..., :3] * (gd[..., :3] / gn[..., :3])
     assert np.array_equal(r.download("ratio_final")[..., :3], want, equal_nan=True)
+    # NaN values are skipped as taps (and replaced where neighbours exist); a pixel with a NaN guide is passed
+    # through and never used as a tap -- same as the definition, where every weight it enters is NaN
+    rng = np.random.default_rng(5)
+    ok = np.argwhere(f["materialID"][..., 0] != 0)
+    pick = ok[rng.choice(len(ok), 12, replace=False)]
+    for k, (y, x) in enumerate(pick):
+        if k < 5:
+            f["sto_direct"][y, x, :3] = np.nan
+        elif k < 9:
+            f["sto_no_vis"][y, x, :3] = np.nan
+        else:
+            f["normal"][y, x, k % 3] = np.nan
+    for k in ("normal", "sto_direct", "sto_no_vis"):
+        r.upload(k, f[k])
+    for iters, sc_ in ((1, 0.0), (4, 0.0), (2, 0.5)):
+        r.denoise(iterations=iters, sigma_colour=sc_)
+        gd, gn = r.download("sto_direct_dn"), r.download("sto_no_vis_dn")
+        od, on = restatement.denoise(f["normal"], f["position"], f["materialID"], f["sto_direct"], f["sto_no_vis"],
+                                     sc["camera"]["pos"], iterations=iters, sigma_colour=sc_, nthreads=8)
+        for a, b in ((gd, od), (gn, on)):
+            assert np.array_equal(np.isnan(a[..., 0]), np.isnan(b[..., 0])), (iters, sc_)
+            m = np.isfinite(a) & np.isfinite(b)
+            np.testing.assert_allclose(a[m], b[m], rtol=2e-4, atol=1e-6)
 
 
 def test_edge_cases(renderer_factory):
@@ -417,7 +440,9 @@ def test_denoise_halves_and_row_counts(renderer_factory):
         r.denoise_pack(rows=rows)
     g, v = r.download("dn_guide"), r.download("dn_val")
     assert g.shape == (160, 96, 4) and v.shape == (160, 96, 2)
-    assert np.array_equal(v[..., 0], r.download("sto_direct")[..., 0], equal_nan=True)
+    use = g[..., 3] >= 0                               # lights / misses carry the skip sentinel and a zero value
+    assert np.array_equal(v[..., 0][use], r.download("sto_direct")[..., 0][use], equal_nan=True)
+    assert use.any() and (~use).any() and np.all(g[..., 3][~use] == np.float32(-1e30)) and not v[~use].any()
     for rows in ((51, 160), (0, 50), (50, 51)):
         for name, a in (("dn_guide", g), ("dn_val", v)):  # the filter's ping-pong overwrote dn_val: restore the gathered rows
             r.upload(name, a)

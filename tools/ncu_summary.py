@@ -26,7 +26,7 @@ def main():
     print("|---|" + "---|" * len(COLS))
     out = {}
     for d in data:
-        name = re.sub(r"\(.*", "", d[ix["Kernel Name"]])
+        name = re.sub(r"\(.*", "", d[ix["Kernel Name"]]).replace("void ", "")
         cells, rec = [], {}
         for key, label, scale in COLS:
             if key not in ix:
