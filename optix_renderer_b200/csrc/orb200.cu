@@ -524,6 +524,64 @@ k_shadow_resolve(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp
     }
 }
 
+// Same result, one thread per (active pixel, sample) for SPP = 2, 4 or 8: the SPP lanes of a pixel sit side
+// by side, so the dependent gathers of a sample (light record, hit record, the hit triangle's normals and
+// mesh record) of four times as many samples are in flight; lane 0 of the group then adds the samples in
+// rayGen's order (k = 0, 1, ...), which keeps the sums bit-identical to k_shadow_resolve.
+template <int SPP>
+__global__ void __launch_bounds__(256)
+k_shadow_resolve_lanes(SceneView s, FrameView f, float3 cam_pos, int frame_id, int mode, const float4* __restrict__ hits) {
+    const unsigned n = f.cnt->queue_n;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && s.n_lights > 0)
+        atomicAdd(&f.cnt->rays_shadow, (unsigned long long)n * (unsigned long long)SPP);
+    const unsigned total = n * (unsigned)SPP;
+    const unsigned rounded = (total + 31u) & ~31u;  // whole warps stay in the loop: the shuffles need every lane
+    for (unsigned r = blockIdx.x * blockDim.x + threadIdx.x; r < rounded; r += gridDim.x * blockDim.x) {
+        const bool live = r < total;
+        const unsigned i = r / (unsigned)SPP, k = r % (unsigned)SPP;
+        float3 d = v3(0.f), nv = v3(0.f);
+        size_t ofs = 0;
+        if (live) {
+            ofs = f.queue[i];
+            const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+            const float4 pp = __ldg(f.position + ofs), nn = __ldg(f.normal + ofs);
+            const float4 dd = __ldg(f.albedo + ofs), aa = __ldg(f.alpha + ofs);
+            Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
+            rng_skip(rng, 2 + 5 * (int)k);
+            const ShadowSample q = shadow_ray_setup(s, v3(pp), v3(nn), rng);
+            Hit h;
+            h.prim = -1;
+            h.t = INFINITY;
+            h.u = h.v = 0.f;
+            if (q.valid) {
+                const float4 hr = ld_stream(hits + r);
+                h.prim = __float_as_int(hr.x);
+                h.u = hr.y;
+                h.v = hr.z;
+                h.t = hr.w;
+            }
+            shadow_ray_resolve(s, q, h, cam_pos, v3(pp), v3(nn), v3(dd), aa.x, mode, d, nv);
+        }
+        float3 sd = d, sn = nv;
+#pragma unroll
+        for (int t = 1; t < SPP; t++) {
+            sd.x += __shfl_down_sync(0xffffffffu, d.x, t);
+            sd.y += __shfl_down_sync(0xffffffffu, d.y, t);
+            sd.z += __shfl_down_sync(0xffffffffu, d.z, t);
+            sn.x += __shfl_down_sync(0xffffffffu, nv.x, t);
+            sn.y += __shfl_down_sync(0xffffffffu, nv.y, t);
+            sn.z += __shfl_down_sync(0xffffffffu, nv.z, t);
+        }
+        if (live && k == 0) {
+            sd = sd / (float)SPP;
+            sn = sn / (float)SPP;
+            const float gd = (sd.x + sd.y + sd.z) / 3.f, gn = (sn.x + sn.y + sn.z) / 3.f;
+            st_stream(f.sto_direct + ofs, make_float4(gd, gd, gd, 1.f));
+            st_stream(f.sto_no_vis + ofs, make_float4(gn, gn, gn, 1.f));
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // k_path_bounce: one iteration of the bounce loop for every live path
 // ---------------------------------------------------------------------------------------------
@@ -1151,6 +1209,7 @@ struct OrbContext {
     int trace_variant = 1;  // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec)
     cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
     int ltc_overlap = 0;  // measured: no gain (3.392 vs 3.394 ms per RATIO frame), kept as a knob
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
@@ -1309,6 +1368,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
     if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
     if (const char* e = getenv("ORB_LTC_OVERLAP")) c->ltc_overlap = atoi(e);
+    if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -1696,7 +1756,15 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
             }
             StageTimer tm(c, ORB_STAGE_SHADOW, 1);
             const int gr = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);
-            k_shadow_resolve<<<gr, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->stream_hits);
+            const int gl = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
+            if (spp == 4 && c->resolve_lanes)
+                k_shadow_resolve_lanes<4><<<gl, 256, 0, st>>>(c->view, f, c->cam.pos, frame_id, mode, c->stream_hits);
+            else if (spp == 2 && c->resolve_lanes)
+                k_shadow_resolve_lanes<2><<<gl, 256, 0, st>>>(c->view, f, c->cam.pos, frame_id, mode, c->stream_hits);
+            else if (spp == 8 && c->resolve_lanes)
+                k_shadow_resolve_lanes<8><<<gl, 256, 0, st>>>(c->view, f, c->cam.pos, frame_id, mode, c->stream_hits);
+            else
+                k_shadow_resolve<<<gr, 128, 0, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->stream_hits);
             c->counters.kernel_launches++;
         }
         c->last_spp = spp;

@@ -360,6 +360,22 @@ def test_ray_stream_equals_fused_shadow_kernel(renderer_factory):
         assert ca["rays_shadow"] == cb["rays_shadow"] == spp * cb["active_pixels"]
 
 
+def test_resolve_per_sample_lanes_equal_per_pixel_kernel(renderer_factory, monkeypatch):
+    """k_shadow_resolve_lanes (one thread per sample, in-order sum over the pixel's lanes) is bit-identical to
+    the one-thread-per-pixel resolve kernel, for every lane-parallel spp; odd spp fall back to the latter."""
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=161, height=95)
+    a = renderer_factory(sc)
+    monkeypatch.setenv("ORB_RESOLVE_LANES", "0")
+    b = renderer_factory(sc)
+    monkeypatch.delenv("ORB_RESOLVE_LANES")
+    for spp in (2, 4, 8, 5):
+        for r in (a, b):
+            r.render(api.RATIO, accum_id=3, mode=1, shadow_spp=spp)
+        for k in ("sto_direct", "sto_no_vis"):
+            assert np.array_equal(a.download(k), b.download(k), equal_nan=True), (spp, k)
+        assert a.counters()["rays_shadow"] == b.counters()["rays_shadow"] == spp * a.counters()["active_pixels"]
+
+
 def test_instrumented_traversal_counts(renderer_factory):
     """ORB_RENDER_COUNT_TRAVERSAL: the instrumented twin of the shadow-ray kernel writes the same frame and
     reports node / triangle fetch counts (bench.py's algorithmic bytes); the TRACE stage timer covers it."""
