@@ -240,7 +240,9 @@ int orb_ratio_estimator_host(OrbContext* ctx, const float* ltc, const float* sto
 
 /* ---- ray casting over the committed scene (owl::traceRay semantics, tmin=0, tmax=1e30):
  * n rays, origin/direction as n*3 floats; outputs prim (global id, -1 miss), t, u, v.
- * brute_force != 0 tests every triangle instead of walking the BVH (hit-id parity checks). */
+ * brute_force: 0 = single-ray BVH2 traversal, 1 = every triangle (hit-id parity checks), 2 = the ray-stream
+ * kernel the RATIO / PATH frames use (compressed 8-wide BVH when built), instrumented: OrbCounters.nodes_visited /
+ * tris_tested. */
 int orb_trace_rays_host(OrbContext* ctx, const float* origin, const float* direction, size_t n, int32_t brute_force,
                         int32_t* prim, float* t, float* u, float* v);
 

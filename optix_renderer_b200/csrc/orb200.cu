@@ -28,6 +28,7 @@
 #include "../../include/orb200.h"
 #include "bvh_build.cuh"
 #include "bvh_sah.cuh"
+#include "bvh8.cuh"
 #include "pixel.cuh"
 
 using namespace orb;
@@ -368,7 +369,7 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
 // order; it only delays the pruning by best.t a little.  Against the batching form above this
 // keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
 // triangle test).
-template <bool LOCAL_STACK, bool COUNT = false>
+template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
@@ -432,24 +433,26 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             }
         }
         if (__ballot_sync(FULL, t.cur != ORB_TRAVERSAL_DONE || leaf != 0) == 0u) break;
-        // node phase
+        // node phase.  A lane is walking (an inner node, or culled stack entries still to drop: POP), holds a
+        // leaf, or is done; leaf references are the negative values above the two sentinels.
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {
             if (COUNT && t.cur >= 0) ++c_nodes;
-            if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
-            if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // postpone this leaf, keep walking
+            if (t.cur >= 0) trav_node_step<SKIP>(t, s, stk, stk_t, stride);
+            else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+            if (leaf == 0 && t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // postpone this leaf, keep walking
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
-            if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
+            if ((int)__popc(__ballot_sync(FULL, t.cur >= 0 || t.cur == ORB_TRAVERSAL_POP)) < node_min) break;
         }
         // leaf phase
         if (leaf != 0) {
             trav_leaf_test(t, s, leaf, COUNT ? &c_tris : nullptr);
             leaf = 0;
-            if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // a second leaf was waiting: it becomes the postponed one
+            if (t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
         }
     }
@@ -463,6 +466,110 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             atomicAdd(stats + 1, (unsigned long long)c_tris);
         }
     }
+}
+
+// The same ray stream through the compressed 8-wide BVH (bvh8.cuh): one wide_step() per live lane and
+// iteration -- open the nearest unopened node of the lane's current group (five 128-bit loads decide eight
+// subtrees), test the triangles of the leaves that were hit, pop.  Refill as above.
+template <bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_trace_stream_wide(Bvh8View w, int n_tris, const float4* __restrict__ rays, float4* __restrict__ hits,
+                    const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
+                    int node_min, unsigned long long* __restrict__ stats) {
+    uint32_t stk[2 * ORB_BVH8_STACK];
+    unsigned c_nodes = 0, c_tris = 0;
+    const unsigned n = *n_items * mult;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned FULL = 0xffffffffu;
+    unsigned w_next = 0, w_end = 0;
+    WideState t;
+    t.done = true;
+    t.sp = 0;
+    unsigned ray = FULL;
+    bool exhausted = false;
+    for (;;) {
+        const bool idle = t.done;
+        if (idle && ray != FULL) {
+            st_stream(hits + ray, make_float4(__int_as_float(t.best.prim), t.best.u, t.best.v, t.best.t));
+            ray = FULL;
+        }
+        const unsigned want = __ballot_sync(FULL, idle && !exhausted);
+        const unsigned busy = __ballot_sync(FULL, !idle);
+        if (want && ((int)__popc(want) >= refill_min || busy == 0u)) {
+            const unsigned need = __popc(want);
+            const unsigned left = w_end - w_next;
+            unsigned base = w_next;
+            unsigned chunk = STREAM_CHUNK;
+            if (left < need) {
+                if (lane == 0) {
+                    const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
+                    const unsigned rem = n > seen ? n - seen : 0u;
+                    const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
+                    chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
+                    base = atomicAdd(cursor, chunk);
+                }
+                base = __shfl_sync(FULL, base, 0);
+                chunk = __shfl_sync(FULL, chunk, 0);
+            }
+            const unsigned rank = __popc(want & ((1u << lane) - 1u));
+            if (idle && !exhausted) {
+                const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
+                if (idx < n) {
+                    const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
+                    ray = idx;
+                    wide_begin(t, n_tris, v3(ro), v3(rd));
+                } else {
+                    exhausted = true;
+                }
+            }
+            if (left >= need) {
+                w_next += need;
+            } else {
+                w_next = base + (need - left);
+                w_end = base + chunk;
+            }
+        }
+        if (__ballot_sync(FULL, !t.done) == 0u) break;
+#pragma unroll 1
+        for (int it = 0; it < 64; ++it) {
+            if (!t.done) wide_step(t, w, stk, 1, COUNT ? &c_nodes : nullptr, COUNT ? &c_tris : nullptr);
+            if ((int)__popc(__ballot_sync(FULL, !t.done)) < node_min) break;
+        }
+    }
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) {
+            c_nodes += __shfl_xor_sync(FULL, c_nodes, o);
+            c_tris += __shfl_xor_sync(FULL, c_tris, o);
+        }
+        if (lane == 0) {
+            atomicAdd(stats, (unsigned long long)c_nodes);
+            atomicAdd(stats + 1, (unsigned long long)c_tris);
+        }
+    }
+}
+
+__global__ void k_pack_rays(const float* __restrict__ o, const float* __restrict__ d, unsigned n, float4* __restrict__ rays) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) stream_put_ray(rays, i, v3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), v3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+}
+__global__ void k_unpack_hits(const float4* __restrict__ hits, unsigned n, int* __restrict__ prim, float* __restrict__ t,
+                              float* __restrict__ u, float* __restrict__ v) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = hits[i];
+    prim[i] = __float_as_int(h.x);
+    u[i] = h.y;
+    v[i] = h.z;
+    t[i] = h.w;
+}
+
+__global__ void k_gather_tris(const float4* __restrict__ src, const int* __restrict__ order, int n, float4* __restrict__ dst) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const float4* p = src + 3 * (size_t)order[k];
+    dst[3 * (size_t)k] = p[0];
+    dst[3 * (size_t)k + 1] = p[1];
+    dst[3 * (size_t)k + 2] = p[2];
 }
 
 // one thread per (active pixel, sample): the ray of ratio_based_shadow's light sample
@@ -1206,7 +1313,18 @@ struct OrbContext {
     int refill_min = 12;
     int leaf_min = 12;
     int node_min = 16;
-    int trace_variant = 1;  // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec)
+    // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec, default), 2: compressed 8-wide BVH
+    // (k_trace_stream_wide; measured 1.89 ms against 1.69 ms for the 5 M shadow rays of the bench frame: 14.5
+    // node steps of ~290 instructions per ray cost more issue slots than 35.9 BVH2 steps of ~70, and the
+    // kernel is issue-bound, not fetch-bound -- kept as an option, ORB_TRACE_VARIANT=2)
+    int trace_variant = 1;
+    float4* bvh8_nodes = nullptr;  // compressed 8-wide BVH (bvh8.cuh) for the ray-stream kernel; nullptr: not built
+    float4* bvh8_tri = nullptr;
+    int bvh8_height = 0, bvh8_n_nodes = 0;
+    int wide_node_min = 16;
+    // k_trace_stream_spec: culled stack entries dropped per main-loop iteration (0: drain in place).  Measured
+    // 1.689 / 1.732 / 1.697 / 1.686 ms for 0 / 1 / 2 / 4: the drain's divergence is not what bounds the kernel.
+    int pop_skip = 0;
     cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
@@ -1262,6 +1380,8 @@ static void free_scene(OrbContext* c) {
     for (void* p : c->d_tex) cudaFree(p);
     c->d_tex.clear();
     cudaFree(c->bvh.tri); cudaFree(c->bvh.nodes);
+    cudaFree(c->bvh8_nodes); cudaFree(c->bvh8_tri);
+    c->bvh8_nodes = c->bvh8_tri = nullptr;
     c->d_pos = c->d_nrm = c->d_uv = nullptr;
     c->d_prim_mesh = nullptr;
     c->d_meshes = nullptr;
@@ -1334,6 +1454,46 @@ static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem) {
     return per_sm * c->n_sm;
 }
 
+// The compressed 8-wide BVH of the ray-stream kernel: a second binned-SAH BVH2 with leaves of <= 3 triangles
+// (GPU), collapsed into 80-byte wide nodes on the host (bvh8_collapse, cold path: ~0.15 s per million
+// triangles), triangle records gathered into node order on the GPU.  Any failure leaves bvh8_nodes null and
+// the BVH2 kernels in charge.
+static int build_wide_bvh(OrbContext* c, int n) {
+    BvhBuildResult b3;
+    CK(build_bvh_sah(c->d_pos, n, 3, c->stream, b3));
+    c->counters.kernel_launches += b3.launches;
+    std::vector<BvhNode> h_nodes((size_t)std::max(b3.n_nodes, 1));
+    if (b3.n_nodes > 0)
+        CK(cudaMemcpyAsync(h_nodes.data(), b3.nodes, sizeof(BvhNode) * (size_t)b3.n_nodes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (b3.root_ref < 0)  // a single leaf: its box is the scene's
+        for (size_t i = 0; i < c->h_pos.size(); i++) {
+            lo[i % 3] = std::min(lo[i % 3], c->h_pos[i]);
+            hi[i % 3] = std::max(hi[i % 3], c->h_pos[i]);
+        }
+    Bvh8Host w;
+    const bool ok = bvh8_collapse(h_nodes.data(), b3.root_ref, lo, hi, w) && w.height <= ORB_BVH8_STACK &&
+                    (int)w.tri_order.size() == n;
+    if (ok) {
+        int* d_order = nullptr;
+        CK(cudaMalloc(&c->bvh8_nodes, sizeof(Bvh8Node) * w.nodes.size()));
+        CK(cudaMalloc(&c->bvh8_tri, 48 * (size_t)n));
+        CK(cudaMalloc(&d_order, 4 * (size_t)n));
+        CK(cudaMemcpyAsync(c->bvh8_nodes, w.nodes.data(), sizeof(Bvh8Node) * w.nodes.size(), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(d_order, w.tri_order.data(), 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        k_gather_tris<<<(n + 255) / 256, 256, 0, c->stream>>>(b3.tri, d_order, n, c->bvh8_tri);
+        c->counters.kernel_launches++;
+        CK(cudaStreamSynchronize(c->stream));
+        cudaFree(d_order);
+        c->bvh8_height = w.height;
+        c->bvh8_n_nodes = (int)w.nodes.size();
+    }
+    cudaFree(b3.tri);
+    cudaFree(b3.nodes);
+    return ORB_OK;
+}
+
 extern "C" {
 
 int orb_api_version(void) { return ORB_API_VERSION; }
@@ -1369,6 +1529,8 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
     if (const char* e = getenv("ORB_LTC_OVERLAP")) c->ltc_overlap = atoi(e);
     if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
+    if (const char* e = getenv("ORB_WIDE_NODE_MIN")) c->wide_node_min = atoi(e);
+    if (const char* e = getenv("ORB_POP_SKIP")) c->pop_skip = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -1570,6 +1732,10 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     CK(cudaEventRecord(eb0, c->stream));
     if (builder == ORB_BVH_LBVH) CK(build_bvh(c->d_pos, (int)n, max_leaf, c->stream, c->bvh));
     else CK(build_bvh_sah(c->d_pos, (int)n, max_leaf, c->stream, c->bvh));
+    if (c->trace_variant == 2 && n > 0) {
+        int rc8 = build_wide_bvh(c, (int)n);
+        if (rc8) return rc8;
+    }
     CK(cudaEventRecord(eb1, c->stream));
     CK(cudaEventSynchronize(eb1));
     float build_ms = 0.f;
@@ -1647,15 +1813,37 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
     cudaStream_t st = c->stream;
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
     StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
+    if (c->trace_variant == 2 && c->bvh8_nodes) {
+        Bvh8View w8;
+        w8.nodes = c->bvh8_nodes;
+        w8.tri = c->bvh8_tri;
+        if (count) {
+            const int g = persistent_grid(c, k_trace_stream_wide<true>, TRACE_BLOCK, 0);
+            k_trace_stream_wide<true><<<g, TRACE_BLOCK, 0, st>>>(w8, c->view.n_tris, c->stream_rays, c->stream_hits, n_items,
+                                                                 mult, c->stream_cursor, c->refill_min, c->wide_node_min,
+                                                                 &c->cnt->nodes_visited);
+        } else {
+            const int g = persistent_grid(c, k_trace_stream_wide<false>, TRACE_BLOCK, 0);
+            k_trace_stream_wide<false><<<g, TRACE_BLOCK, 0, st>>>(w8, c->view.n_tris, c->stream_rays, c->stream_hits, n_items,
+                                                                  mult, c->stream_cursor, c->refill_min, c->wide_node_min,
+                                                                  nullptr);
+        }
+        c->counters.kernel_launches++;
+        return ORB_OK;
+    }
     if (count && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // instrumented twin of the default kernel
         const int g = persistent_grid(c, k_trace_stream_spec<true, true>, TRACE_BLOCK, 0);
         k_trace_stream_spec<true, true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
                                                                    c->stream_cursor, c->refill_min, c->node_min,
                                                                    c->height, &c->cnt->nodes_visited);
     } else if (c->trace_variant == 1 && c->local_stack && c->height <= LOCAL_STACK_MAX) {
-        const int g = persistent_grid(c, k_trace_stream_spec<true>, TRACE_BLOCK, 0);
-        k_trace_stream_spec<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
-                                                             c->stream_cursor, c->refill_min, c->node_min, c->height);
+        auto k = k_trace_stream_spec<true, false, 0>;
+        if (c->pop_skip == 1) k = k_trace_stream_spec<true, false, 1>;
+        if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
+        if (c->pop_skip == 4) k = k_trace_stream_spec<true, false, 4>;
+        const int g = persistent_grid(c, k, TRACE_BLOCK, 0);
+        k<<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
+                                     c->node_min, c->height, nullptr);
     } else if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
         const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
         k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
@@ -2085,9 +2273,22 @@ int orb_trace_rays_host(OrbContext* c, const float* origin, const float* directi
     CK(cudaMemcpyAsync(d_d, direction, 12 * n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->cnt, 0, DEVCOUNTERS_FRAME_BYTES, c->stream));
     const int g = (int)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
-    k_trace_rays<<<g, TRACE_BLOCK, trace_smem(c), c->stream>>>(c->view, d_o, d_d, n, brute, d_p, d_t, d_t + n, d_t + 2 * n,
-                                                               c->height, c->cnt);
-    c->counters.kernel_launches++;
+    if (brute == 2) {  // through the ray-stream kernel the RATIO / PATH frames use (instrumented twin)
+        NEED(n < ((size_t)1 << 31), "orb_trace_rays_host: too many rays for the stream");
+        int rc = ensure_stream(c, n);
+        if (rc) return rc;
+        const unsigned nn = (unsigned)n;
+        CK(cudaMemcpyAsync(&c->cnt->queue_n, &nn, 4, cudaMemcpyHostToDevice, c->stream));
+        k_pack_rays<<<(nn + 255) / 256, 256, 0, c->stream>>>(d_o, d_d, nn, c->stream_rays);
+        rc = launch_trace_stream(c, &c->cnt->queue_n, 1u, true);
+        if (rc) return rc;
+        k_unpack_hits<<<(nn + 255) / 256, 256, 0, c->stream>>>(c->stream_hits, nn, d_p, d_t, d_t + n, d_t + 2 * n);
+        c->counters.kernel_launches += 2;
+    } else {
+        k_trace_rays<<<g, TRACE_BLOCK, trace_smem(c), c->stream>>>(c->view, d_o, d_d, n, brute, d_p, d_t, d_t + n, d_t + 2 * n,
+                                                                   c->height, c->cnt);
+        c->counters.kernel_launches++;
+    }
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(prim, d_p, 4 * n, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(t, d_t, 4 * n, cudaMemcpyDeviceToHost, c->stream));

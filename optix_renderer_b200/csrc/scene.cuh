@@ -134,10 +134,17 @@ ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, floa
 // the lowest primitive id), so any BVH and any order agree bit for bit.
 #define ORB_TRAVERSAL_DONE ((int)0x80000000)  // never a leaf reference: first + count < 2^28
 
-template <class IntPtr, class FltPtr>
+// ORB_TRAVERSAL_POP: "pop again" -- returned by the bounded pop below when MAX_SKIP culled entries were
+// dropped and the stack is not empty yet.  A ray that has found its hit still owns a stack full of
+// subtrees beyond it; draining them in an inner loop runs a few lanes alone for many iterations (ncu,
+// profiles/r1m: 16 % of the stream kernel's instructions at 2.8 - 8 active lanes).  The ray-stream kernels
+// drain MAX_SKIP entries per iteration of their main loop instead, beside the lanes that still walk nodes.
+#define ORB_TRAVERSAL_POP ((int)0x80000001)  // never a leaf reference either
+template <int MAX_SKIP = 0, class IntPtr, class FltPtr>
 ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& best) {
-    for (;;) {  // skip subtrees that start beyond the current closest hit
+    for (int k = 0;; ++k) {  // skip subtrees that start beyond the current closest hit
         if (sp == 0) return ORB_TRAVERSAL_DONE;
+        if (MAX_SKIP > 0 && k == MAX_SKIP) return ORB_TRAVERSAL_POP;
         --sp;
         if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) return stk[sp * stride];
     }
@@ -172,7 +179,7 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
 }
 
 // One inner node (t.cur >= 0): both child boxes of a 64-byte node, near child next, far pushed.
-template <class IntPtr, class FltPtr>
+template <int MAX_SKIP = 0, class IntPtr, class FltPtr>
 ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride) {
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
@@ -205,7 +212,7 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
     } else if (h1) {
         t.cur = c1;
     } else {
-        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+        t.cur = stack_pop<MAX_SKIP>(stk, stk_t, stride, t.sp, t.best);
     }
 }
 

@@ -192,6 +192,11 @@ def test_sah_and_lbvh_builders_agree_with_brute_force(renderer_factory, n_tris, 
         assert c["bvh_triangles"] == scenes.n_triangles(sc)
         if n_tris >= 20000:
             assert c["tris_tested"] < 0.05 * n * c["bvh_triangles"]
+        # the ray-stream kernel (compressed 8-wide BVH, bvh8.cuh) finds the same hits, bit for bit
+        p3, t3, u3, v3 = r.trace_rays(org, d, brute_force=2)
+        assert np.array_equal(p3, p2) and np.array_equal(t3, t2) and np.array_equal(u3, u2) and np.array_equal(v3, v2)
+        c3 = r.counters()
+        assert c3["tris_tested"] >= (p3 >= 0).sum()
         r.render(api.RATIO, accum_id=1, mode=1, shadow_spp=2)
         frames.append({k: r.download(k) for k in ("ltc", "sto_direct", "sto_no_vis", "position")})
         frames[-1]["hit"] = r.hit_records()[0]
@@ -374,6 +379,37 @@ def test_resolve_per_sample_lanes_equal_per_pixel_kernel(renderer_factory, monke
         for k in ("sto_direct", "sto_no_vis"):
             assert np.array_equal(a.download(k), b.download(k), equal_nan=True), (spp, k)
         assert a.counters()["rays_shadow"] == b.counters()["rays_shadow"] == spp * a.counters()["active_pixels"]
+
+
+def test_wide_bvh_stream_kernel(renderer_factory, monkeypatch):
+    """ORB_TRACE_VARIANT=2: the ray-stream kernel over the compressed 8-wide BVH (bvh8.cuh) returns the
+    brute-force hits bit for bit and renders the same RATIO / PATH-wavefront frames as the BVH2 kernels."""
+    sc = scenes.scene_synthetic(n_tris=60000, n_quad_lights=4, width=128, height=72)
+    a = renderer_factory(sc)
+    monkeypatch.setenv("ORB_TRACE_VARIANT", "2")
+    b = renderer_factory(sc)
+    monkeypatch.delenv("ORB_TRACE_VARIANT")
+    rng = np.random.default_rng(11)
+    n = 20000
+    org = (rng.uniform(-1, 1, (n, 3)) * 9).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) * 0.5 + 0.2
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:100, 1] = 0.0
+    want = b.trace_rays(org, d, brute_force=True)
+    got = b.trace_rays(org, d, brute_force=2)
+    wide_nodes = b.counters()["nodes_visited"]
+    for x, y in zip(got, want):
+        assert np.array_equal(x, y)
+    a.trace_rays(org, d, brute_force=2)
+    assert 0 < wide_nodes < a.counters()["nodes_visited"]     # fewer (wider) node steps than the BVH2 kernel
+    for r in (a, b):
+        r.render(api.RATIO, accum_id=2, mode=1, shadow_spp=4)
+    for k in ("sto_direct", "sto_no_vis", "ltc"):
+        assert np.array_equal(a.download(k), b.download(k), equal_nan=True), k
+    for r in (a, b):
+        r.render(api.PATH, accum_id=0, mode=1, max_depth=4, path_wavefront=True)
+    assert np.array_equal(a.download("accum"), b.download("accum"), equal_nan=True)
 
 
 def test_instrumented_traversal_counts(renderer_factory):

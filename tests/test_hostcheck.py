@@ -93,6 +93,27 @@ def test_bvh_traversal_equals_brute_force(hostcheck):
     p2, t2, u2, v2 = hostcheck.trace(org, d, brute=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
     assert (p1 >= 0).mean() > 0.2
+    # the compressed 8-wide BVH (bvh8.cuh: collapse + traversal) finds the same hits, bit for bit
+    nn, hh = hostcheck.wide_info()
+    assert nn > 100 and 2 <= hh <= 32
+    p3, t3, u3, v3 = hostcheck.trace(org, d, brute=2)
+    assert np.array_equal(p3, p2) and np.array_equal(t3, t2) and np.array_equal(u3, u2) and np.array_equal(v3, v2)
+
+
+@pytest.mark.parametrize("n_tris", [1, 2, 3, 4, 9, 100])
+def test_wide_bvh_small_scenes(hostcheck, n_tris):
+    sc = scenes.scene_synthetic(n_tris=n_tris, n_quad_lights=1, width=8, height=8)
+    hostcheck.load_scene(sc)
+    rng = np.random.default_rng(n_tris)
+    org = rng.uniform(-2, 2, (500, 3)).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) + 0.5
+    d = rng.normal(size=(500, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:20, 0] = 0.0
+    a = hostcheck.trace(org, d, brute=2)
+    b = hostcheck.trace(org, d, brute=True)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
 
 
 def test_ltc_gbuffer_pass(hostcheck, restatement):

@@ -58,7 +58,7 @@ def main():
     rows = blocks[which]
     hdr = rows[0]
     ix = {h: i for i, h in enumerate(hdr)}
-    lines = sass_lines(kernel)
+    lines = sass_lines(os.environ.get("MANGLED", kernel))
     base = int(rows[1][ix["Address"]], 16)
     agg = collections.defaultdict(lambda: [0, 0, 0, collections.Counter()])
     tot_inst = tot_thr = tot_samp = 0
