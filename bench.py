@@ -77,6 +77,10 @@ class ClockSampler(threading.Thread):
 
 # ALGORITHMIC bytes per stage, float4 AoS as at the boundary.
 def stage_bytes(stage, px, active, accum_id_gt0=True, trav=None):
+    if stage == "path":           # all bounces in one kernel: the traversal fetches (counted) + per path 64 B of G-buffer
+        if not trav:              # read and 16 B of colour written; no ray stream, no path state in HBM
+            return 0
+        return trav["nodes"] * 64 + trav["tris"] * 48 + active * 80
     if stage == "trace":          # nodes visited x 64 B + triangles tested x 48 B (counted by the
         if not trav:              # instrumented twin of the kernel) + the ray stream in (32 B) and hit records out (16 B)
             return 0
@@ -149,8 +153,8 @@ def workload_config(args, n):
             ("BASELINE configs[3]: same scene, PATH intended mode, %d bounces, progressive" % DEPTH),
             "width": W, "height": H, "triangles": N_TRIS, "tri_lights": 2 * N_QUADS, "shadow_spp": SPP,
             "max_depth": DEPTH if args.workload == "path" else 1, "lut": "8x8 (reference ltc_isotropic.h)",
-            "partition": ("%d cost-balanced row bands, BVH replicated, NCCL all-gather of the packed denoise rows and of "
-                          "the finished frame" % n) if n > 1 else "single GPU",
+            "partition": ("%d cost-balanced row bands, BVH replicated, point-to-point exchange of the packed denoise halo "
+                          "rows, NCCL all-gather of the finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
             "l2": "working set per frame (13+ float4 frame buffers of 33 MB, 48 MB triangles, 64 MB BVH) exceeds the "
                   "126 MB L2; no explicit flush"}
 
@@ -212,6 +216,8 @@ def run_ours(args):
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
 
+    SYNC_ASSEMBLE = bool(os.environ.get("ORB_BENCH_SYNC_ASSEMBLE"))  # A/B: gather in place on the render stream
+
     def render(i):
         if ratio:
             T.render_ratio_frame(i, mode=api.INTENDED, shadow_spp=SPP)
@@ -219,8 +225,13 @@ def run_ours(args):
             T.render_path_frame(i, mode=api.INTENDED, max_depth=DEPTH)
 
     def step(i):
+        # the finished band is handed to a side stream that all-gathers it while this stream renders the next
+        # frame; T.wait_assembled() (before the closing event / before a read) puts the last gather back in order
         render(i)
-        T.assemble(out_names)
+        if SYNC_ASSEMBLE:
+            T.assemble(out_names)
+        else:
+            T.assemble_async(out_names)
 
     def barrier():
         if world > 1:
@@ -239,6 +250,7 @@ def run_ours(args):
         sampler.start()
         for i in range(args.warmup):
             if world > 1:
+                T.wait_assembled()
                 # cut the row bands by cost: a model from the first frame's active pixels, then corrected by
                 # this rank's measured kernel time for its band (stage timers: the collectives and the
                 # waiting for slower neighbours are not in it) over the following warm-up frames
@@ -256,13 +268,18 @@ def run_ours(args):
         c0 = r.counters()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
+        if world > 1:
+            T.spans = {}
         ev0.record(stream)
         for i in range(args.steps):
             step(args.warmup + i)
+        T.wait_assembled()
         ev1.record(stream)
         barrier()
         ms = ev0.elapsed_time(ev1)
         st = r.stage_times()
+        coll_ms = T.span_ms() if world > 1 else {}
+        T.spans = None
         c1 = r.counters()
         r.set_profiling(False)
         ms = reduce(ms, dist.ReduceOp.MAX) if world > 1 else ms
@@ -275,24 +292,70 @@ def run_ours(args):
         # ---- end to end through the C-ABI with host buffers: camera in (host), frame out (pinned host) ----
         cam = sc["camera"]
         y0, y1 = (0, H)
-        host_f4 = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True).numpy()
-        host_u32 = torch.empty((H, W), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+        t_f4 = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+        t_u32 = torch.empty((H, W), dtype=torch.int32, pin_memory=True)
+        host_f4, host_u32 = t_f4.numpy(), t_u32.numpy().view(np.uint32)
         e_steps = max(3, min(args.steps, 30))
         barrier()
         t0 = time.perf_counter()
         for i in range(e_steps):
             r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
             step(args.warmup + args.steps + i)
-            if rank == 0:
-                r.download(out_names[0], rows=(y0, y1), out=host_f4)      # D2H, synchronises
+            if rank == 0 and world == 1:
+                r.download(out_names[0], rows=(y0, y1), out=host_f4)      # D2H through the C-ABI, synchronises
                 r.download("rgba8", rows=(y0, y1), out=host_u32)
+            elif rank == 0:                                               # the assembled frame lives in T.out
+                T.wait_assembled()
+                t_f4.copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
+                t_u32.copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
+                torch.cuda.current_stream().synchronize()
         barrier()
         e_ms = (time.perf_counter() - t0) * 1e3
         e_ms = reduce(e_ms, dist.ReduceOp.MAX) if world > 1 else e_ms
         e_value = (rays / args.steps) * e_steps / (e_ms * 1e-3) / 1e6
         clocks = sampler.summary()
         clocks["window"] = "warm-up + timed region + e2e loop (one continuous load)"
-        trav = None
+        same = None
+        if ratio and world > 1 and rank == 0:
+            # parity of the partitioned job: the frame assembled from N bands (halo rows exchanged, bands gathered)
+            # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
+            T.wait_assembled()
+            got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
+            last = args.warmup + args.steps + e_steps - 1
+            r.render(api.RATIO, accum_id=last, mode=api.INTENDED, shadow_spp=SPP, count_rays=False)
+            r.denoise(iterations=DN_ITERS)
+            r.ratio_combine(use_denoised=True)
+            torch.cuda.synchronize()
+            want = tiles.device_tensor(r, "ratio_final")
+            # compared on the pixels this frame WRITES: a pixel whose primary ray missed keeps whatever an earlier
+            # frame left in ltc / sto_* (the reference's rayGen writes nothing there either, deviceCode.cu:90-94,
+            # 118-143), and after the bands moved the ranks hold different histories for such silhouette pixels
+            nrm = tiles.device_tensor(r, "normal")
+            written = (nrm[..., :3] != 0).any(dim=2)
+            px_bad = (got.view(torch.int32) != want.view(torch.int32)).any(dim=2) & written
+            same = not bool(px_bad.any())
+            if not same:
+                rows_bad = torch.nonzero(px_bad.any(dim=1)).flatten().tolist()
+                print("bench.py: assembled frame differs from the single-GPU frame in %d pixels, rows %s ... %s; bands %s" %
+                      (int(px_bad.sum()), rows_bad[:12], rows_bad[-12:], T.bands), file=sys.stderr)
+        trav, one_quad = None, None
+        if ratio and world == 1:
+            # BASELINE's "HBM GB/s fraction on the LTC pass": the stand-alone LTC pass over the resident G-buffer
+            # with ONE quad light (2 TriLights, the only light count near the HBM roof); outside
+            # the timed region, 20 launches, working set 166 MB > L2
+            r.set_lights(sc["tri_lights"][:2])
+            r.stage_times()
+            for _ in range(3):
+                r.ltc_gbuffer_pass()
+            torch.cuda.synchronize()
+            r.set_profiling(True)
+            r.stage_times()
+            for _ in range(20):
+                r.ltc_gbuffer_pass()
+            torch.cuda.synchronize()
+            one_quad = r.stage_times()["ltc_gbuffer"][0] / 20
+            r.set_profiling(False)
+            r.set_lights(sc["tri_lights"])
         if ratio and world == 1:
             # one extra frame, outside every timed region, through the instrumented twin of the traversal kernel:
             # node / triangle records per shadow ray of THIS workload (the algorithmic bytes of the roofline)
@@ -300,6 +363,11 @@ def run_ours(args):
                      count_traversal=True)
             cc = r.counters()
             trav = {"nodes": cc["nodes_visited"], "tris": cc["tris_tested"], "rays": cc["rays_shadow"]}
+        if not ratio and world == 1:
+            r.render(api.PATH, accum_id=args.warmup + args.steps, mode=api.INTENDED, max_depth=DEPTH, count_rays=False,
+                     count_traversal=True)
+            cc = r.counters()
+            trav = {"nodes": cc["nodes_visited"], "tris": cc["tris_tested"], "rays": cc["rays_bounce"]}
 
     if rank == 0:
         px = W * H // world  # per rank (bands); stage times are rank 0's
@@ -335,6 +403,12 @@ def run_ours(args):
                             "ray.  Nearly all of them are served by L1/L2 (traffic = what reached DRAM), so the HBM "
                             "fraction says how far the kernel is from streaming its fetches, not that HBM limits it: "
                             "ncu shows it issue / L1-pipe bound (profiles/)"}
+        if one_quad:
+            b = px * 32 + active * 48  # normal read + ltc written everywhere; position, albedo, alpha where a surface was hit
+            line_ltc = {"tri_lights": 2, "ms": one_quad, "algorithmic_bytes": b, "gbs": b / (one_quad * 1e-3) / 1e9,
+                        "frac_of_hbm_peak": b / (one_quad * 1e-3) / 1e9 / peak,
+                        "what": "orb_ltc_gbuffer_pass over the frame's resident G-buffer, one quad light: 32 B per pixel + 48 B per "
+                                "surface pixel"}
         if trav:
             roofline["per_ray"] = {"nodes": trav["nodes"] / max(trav["rays"], 1), "tris": trav["tris"] / max(trav["rays"], 1),
                                    "rays_per_launch": trav["rays"]}
@@ -348,8 +422,12 @@ def run_ours(args):
                         "what": "orb_set_camera + orb_render_async(+denoise+combine) + orb_buffer_download_rows of the "
                                 "float4 result and the RGBA8 frame into pinned host memory"},
                 "gpu_launches": int(launches), "roofline": roofline, "passes": passes, "clocks": clocks}
+        if one_quad:
+            line["ltc_pass_one_quad"] = line_ltc
         if world > 1:
             line["config"]["bands"] = [list(b) for b in T.bands]
+            line["assembled_frame_equals_single_gpu_frame"] = same
+            line["collectives_ms_per_frame_rank0"] = {k: v / args.steps for k, v in coll_ms.items()}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_sample(args.workload)
         sys.stdout.flush()

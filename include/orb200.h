@@ -119,7 +119,7 @@ typedef struct OrbRenderConfig {
                                      ray-stream kernels (kept for A/B measurement; same results) */
 #define ORB_RENDER_PATH_WAVEFRONT 4 /* PATH: one generate / trace / shade wavefront per bounce instead of the
                                        persistent all-bounces kernel (kept for A/B measurement) */
-#define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO: run the instrumented twin of the shadow-ray traversal kernel; node
+#define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
                                         records fetched / triangle records tested land in OrbCounters.nodes_visited
                                         / tris_tested (same results, slower; bench.py's roofline uses it once) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows

@@ -861,10 +861,11 @@ k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce,
 // from the active-pixel queue.  One launch per frame, one tail per frame, no path state in HBM.
 // Shading is batched like the refill: lanes whose ray has ended wait until `refill_min` of them
 // have (or nobody can advance), so the divergent shading code runs with a fair number of lanes.
-template <bool LOCAL_STACK>
+template <bool LOCAL_STACK, bool COUNT = false>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int depth, unsigned* __restrict__ cursor,
                   int refill_min, int node_min, int height) {
+    unsigned c_nodes = 0, c_tris = 0;  // COUNT (ORB_RENDER_COUNT_TRAVERSAL): node / triangle records fetched by this lane
     int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
@@ -951,6 +952,7 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
         if (__ballot_sync(FULL, have_path) == 0u) break;
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {  // node phase (speculative: one postponed leaf per lane)
+            if (COUNT && t.cur >= 0) ++c_nodes;
             if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
             if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
                 leaf = t.cur;
@@ -959,7 +961,7 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
             if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
         }
         if (leaf != 0) {  // leaf phase
-            trav_leaf_test(t, s, leaf);
+            trav_leaf_test(t, s, leaf, COUNT ? &c_tris : nullptr);
             leaf = 0;
             if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
                 leaf = t.cur;
@@ -969,6 +971,16 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
     }
     for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(FULL, rays, o);
     if (lane == 0 && rays) atomicAdd(&f.cnt->rays_bounce, (unsigned long long)rays);
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) {
+            c_nodes += __shfl_xor_sync(FULL, c_nodes, o);
+            c_tris += __shfl_xor_sync(FULL, c_tris, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&f.cnt->nodes_visited, (unsigned long long)c_nodes);
+            atomicAdd(&f.cnt->tris_tested, (unsigned long long)c_tris);
+        }
+    }
 }
 
 __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
@@ -1967,9 +1979,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
             if (rc) return rc;
             StageTimer tm(c, ORB_STAGE_PATH, 1);
             CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
-            const int g = persistent_grid(c, k_path_persistent<true>, TRACE_BLOCK, 0);
-            k_path_persistent<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor,
-                                                              c->path_shade_min, c->path_node_min, c->height);
+            auto k = (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) ? k_path_persistent<true, true> : k_path_persistent<true, false>;
+            const int g = persistent_grid(c, k, TRACE_BLOCK, 0);
+            k<<<g, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor, c->path_shade_min,
+                                         c->path_node_min, c->height);
             c->counters.kernel_launches++;
         } else {
         rc = ensure_path_state(c);

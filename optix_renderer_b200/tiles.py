@@ -182,6 +182,10 @@ class TiledRenderer:
         self.bands = row_bands(renderer.H, world_size)
         self.row_cost = None
         self._views = {}
+        self.spans = None  # set to {} to collect CUDA-event spans of the collectives: name -> [(e0, e1), ...]
+        self.out = {}      # assemble_async(): name -> whole-frame tensor every rank ends up with
+        self._comm = None  # side stream the frame assembly runs on, beside the next frame's kernels
+        self._done = None
 
     @property
     def band(self):
@@ -191,6 +195,31 @@ class TiledRenderer:
         if name not in self._views:
             self._views[name] = device_tensor(self.r, name)
         return self._views[name]
+
+    def _span(self, name):
+        """Context manager: CUDA-event pair around a collective when self.spans is a dict."""
+        import contextlib
+
+        import torch
+
+        if self.spans is None:
+            return contextlib.nullcontext()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.spans.setdefault(name, []).append((e0, e1))
+
+        @contextlib.contextmanager
+        def cm():
+            e0.record()
+            yield
+            e1.record()
+        return cm()
+
+    def span_ms(self):
+        """Summed milliseconds per collective since spans were switched on (synchronises)."""
+        import torch
+
+        torch.cuda.synchronize()
+        return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in (self.spans or {}).items()}
 
     def rebalance(self, measured_ms=None):
         """Cut the bands by cost (all ranks must call).  First call: the model of row_costs() from the
@@ -242,7 +271,8 @@ class TiledRenderer:
             else:
                 if y1 > y0:
                     self.r.denoise_pack(rows=rows)
-                exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
+                with self._span("halo_exchange"):
+                    exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
                 if y1 > y0:
                     self.r.denoise_filter(iterations=self.iters, rows=rows)
         if y1 > y0:
@@ -257,8 +287,45 @@ class TiledRenderer:
         rows = None if self.world == 1 else (y0, y1)
         self.r.render(api.PATH, accum_id=accum_id, mode=mode, max_depth=max_depth, rows=rows, sync=False)
 
+    def assemble_async(self, names):
+        """Frame assembly off the critical path: this rank's finished band is copied into a whole-frame
+        tensor (self.out[name]) on the current stream, and the all-gather of those tensors runs on a side
+        stream while the current stream goes on with the next frame.  wait_assembled() orders the current
+        stream behind the last gather; self.out[name] is then the frame on every rank."""
+        if self.world == 1:
+            return
+        import torch
+
+        cur = torch.cuda.current_stream()
+        if self._comm is None:
+            self._comm = torch.cuda.Stream()
+        if self._done is not None:
+            cur.wait_event(self._done)  # the previous gather still reads / writes self.out
+        y0, y1 = self.band
+        for n in names:
+            v = self._t(n)
+            if n not in self.out:
+                self.out[n] = torch.empty_like(v)
+            if y1 > y0:
+                self.out[n][y0:y1].copy_(v[y0:y1])
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        with torch.cuda.stream(self._comm):
+            self._comm.wait_event(ready)
+            for n in names:
+                assemble(self.out[n], self.bands, self.rank, self.group)
+            self._done = torch.cuda.Event()
+            self._done.record(self._comm)
+
+    def wait_assembled(self):
+        if self._done is not None:
+            import torch
+
+            torch.cuda.current_stream().wait_event(self._done)
+
     def assemble(self, names):
         if self.world == 1:
             return
-        for n in names:
-            assemble(self._t(n), self.bands, self.rank, self.group)
+        with self._span("assemble"):
+            for n in names:
+                assemble(self._t(n), self.bands, self.rank, self.group)

@@ -434,6 +434,14 @@ def test_instrumented_traversal_counts(renderer_factory):
     assert c1["nodes_visited"] >= rays            # every ray fetches at least the root
     assert 0 < c1["tris_tested"] < 64 * rays
     assert st["trace"][1] == 1 and st["trace"][0] > 0 and st["shadow"][1] == 2
+    # the persistent path kernel has the same twin
+    r.render(api.PATH, accum_id=0, mode=1, max_depth=4)
+    want = r.download("accum")
+    assert r.counters()["nodes_visited"] == 0
+    r.render(api.PATH, accum_id=0, mode=1, max_depth=4, count_traversal=True)
+    c2 = r.counters()
+    assert np.array_equal(want, r.download("accum"), equal_nan=True)
+    assert c2["nodes_visited"] >= c2["rays_bounce"] > 0 and c2["tris_tested"] > 0
 
 
 def test_path_persistent_equals_wavefront(renderer_factory):

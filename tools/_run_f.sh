@@ -1,0 +1,14 @@
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+timeout 900 python bench.py > gpurun_out/r1n_bench_ratio.json 2> gpurun_out/r1n_bench_ratio.err; echo "ratio rc=$?"
+timeout 900 python bench.py --workload path > gpurun_out/r1n_bench_path.json 2> gpurun_out/r1n_bench_path.err; echo "path rc=$?"
+timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r1n_bench_ref.json 2> gpurun_out/r1n_bench_ref.err; echo "ref rc=$?"
+python - <<'PY'
+import json
+for n in ("ratio","path","ref"):
+    d=json.loads(open("gpurun_out/r1n_bench_%s.json"%n).read().strip().splitlines()[-1])
+    print(n, round(d["ms_per_step"],3), round(d["value"],2), "e2e", round(d["e2e"]["value"],2), d.get("gpu_launches"), d.get("clocks"))
+    if "passes" in d: print({k:(round(v["ms_per_frame"],3), round(v["frac_of_hbm_peak"] or 0,3)) for k,v in d["passes"].items()})
+    if "ltc_pass_one_quad" in d: print(d["ltc_pass_one_quad"])
+    if "roofline" in d: print({k:v for k,v in d["roofline"].items() if k!="note"})
+    if "cpu_baseline" in d: print(d["cpu_baseline"])
+PY
