@@ -248,7 +248,10 @@ def run_ours(args):
     with torch.cuda.stream(stream):
         sampler = ClockSampler(local)
         sampler.start()
-        for i in range(args.warmup):
+        T.floor_ms = float(os.environ.get("ORB_BAND_FLOOR_MS", "0.25" if ratio else "0.45"))
+        n_calib = int(os.environ.get("ORB_BAND_CALIB", "6")) if world > 1 else 0
+        base_id = args.warmup + n_calib  # accumId of the first timed frame
+        for i in range(args.warmup + n_calib):  # N > 1: n_calib extra untimed frames first, to settle the band cuts
             if world > 1:
                 T.wait_assembled()
                 # cut the row bands by cost: a model from the first frame's active pixels, then corrected by
@@ -272,7 +275,7 @@ def run_ours(args):
             T.spans = {}
         ev0.record(stream)
         for i in range(args.steps):
-            step(args.warmup + i)
+            step(base_id + i)
         T.wait_assembled()
         ev1.record(stream)
         barrier()
@@ -283,6 +286,12 @@ def run_ours(args):
         c1 = r.counters()
         r.set_profiling(False)
         ms = reduce(ms, dist.ReduceOp.MAX) if world > 1 else ms
+        rank_ms = None
+        if world > 1:  # every rank's own kernel time per frame (stage timers): how even the bands are
+            mine = torch.zeros(world, dtype=torch.float64, device="cuda")
+            mine[rank] = sum(t for t, _ in st.values()) / args.steps
+            dist.all_reduce(mine)
+            rank_ms = [round(x, 4) for x in mine.tolist()]
         d = {k: c1[k] - c0[k] for k in ("rays_primary", "rays_shadow_total", "rays_bounce_total", "kernel_launches",
                                          "active_pixels_total")}
         rays = reduce(d["rays_primary"] + d["rays_shadow_total"] + d["rays_bounce_total"], dist.ReduceOp.SUM if world > 1 else None)
@@ -300,7 +309,7 @@ def run_ours(args):
         t0 = time.perf_counter()
         for i in range(e_steps):
             r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
-            step(args.warmup + args.steps + i)
+            step(base_id + args.steps + i)
             if rank == 0 and world == 1:
                 r.download(out_names[0], rows=(y0, y1), out=host_f4)      # D2H through the C-ABI, synchronises
                 r.download("rgba8", rows=(y0, y1), out=host_u32)
@@ -321,7 +330,7 @@ def run_ours(args):
             # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
             T.wait_assembled()
             got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
-            last = args.warmup + args.steps + e_steps - 1
+            last = base_id + args.steps + e_steps - 1
             r.render(api.RATIO, accum_id=last, mode=api.INTENDED, shadow_spp=SPP, count_rays=False)
             r.denoise(iterations=DN_ITERS)
             r.ratio_combine(use_denoised=True)
@@ -359,12 +368,12 @@ def run_ours(args):
         if ratio and world == 1:
             # one extra frame, outside every timed region, through the instrumented twin of the traversal kernel:
             # node / triangle records per shadow ray of THIS workload (the algorithmic bytes of the roofline)
-            r.render(api.RATIO, accum_id=args.warmup + args.steps, mode=api.INTENDED, shadow_spp=SPP, count_rays=False,
+            r.render(api.RATIO, accum_id=base_id + args.steps, mode=api.INTENDED, shadow_spp=SPP, count_rays=False,
                      count_traversal=True)
             cc = r.counters()
             trav = {"nodes": cc["nodes_visited"], "tris": cc["tris_tested"], "rays": cc["rays_shadow"]}
         if not ratio and world == 1:
-            r.render(api.PATH, accum_id=args.warmup + args.steps, mode=api.INTENDED, max_depth=DEPTH, count_rays=False,
+            r.render(api.PATH, accum_id=base_id + args.steps, mode=api.INTENDED, max_depth=DEPTH, count_rays=False,
                      count_traversal=True)
             cc = r.counters()
             trav = {"nodes": cc["nodes_visited"], "tris": cc["tris_tested"], "rays": cc["rays_bounce"]}
@@ -427,6 +436,7 @@ def run_ours(args):
         if world > 1:
             line["config"]["bands"] = [list(b) for b in T.bands]
             line["assembled_frame_equals_single_gpu_frame"] = same
+            line["rank_kernel_ms_per_frame"] = rank_ms
             line["collectives_ms_per_frame_rank0"] = {k: v / args.steps for k, v in coll_ms.items()}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_sample(args.workload)

@@ -181,6 +181,7 @@ class TiledRenderer:
         self.group = group
         self.bands = row_bands(renderer.H, world_size)
         self.row_cost = None
+        self.floor_ms = 0.0  # fixed per-frame kernel time of a band of any height (see rebalance)
         self._views = {}
         self.spans = None  # set to {} to collect CUDA-event spans of the collectives: name -> [(e0, e1), ...]
         self.out = {}      # assemble_async(): name -> whole-frame tensor every rank ends up with
@@ -249,9 +250,11 @@ class TiledRenderer:
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             ms = t.cpu().numpy()
             cost = self.row_cost.copy()
+            # a band costs floor + sum of its rows: the kernels' fixed launch tails (FLOOR_MS, profiles/r1k_stage_floors)
+            # do not shrink with the band, so only the part above the floor is spread over the rows
             for (y0, y1), m in zip(self.bands, ms):
                 if y1 > y0 and m > 0:
-                    cost[y0:y1] *= m / max(cost[y0:y1].sum(), 1e-30)
+                    cost[y0:y1] *= max(m - self.floor_ms, 0.1 * m) / max(cost[y0:y1].sum(), 1e-30)
             self.row_cost = cost
         self.bands = balanced_bands(self.row_cost, self.world)
         return self.bands
