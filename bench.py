@@ -147,12 +147,19 @@ def run_reference(args):
 
 
 def workload_config(args, n):
-    return {"workload": ("BASELINE configs[2]: synthetic %d-triangle scene %dx%d, %d quad lights (%d TriLights), RATIO "
-                         "intended mode %d spp shadow rays + %d-pass a-trous denoise + ratio combine" %
-                         (N_TRIS, W, H, N_QUADS, 2 * N_QUADS, SPP, DN_ITERS)) if args.workload == "ratio" else
-            ("BASELINE configs[3]: same scene, PATH intended mode, %d bounces, progressive" % DEPTH),
+    if args.scene == "cfg5":
+        tag = "BASELINE configs[4] scene (4K, 10 M triangles, 64 quad lights), "
+    else:
+        tag = ""
+    if args.workload == "ratio":
+        desc = ("BASELINE configs[2]: synthetic %d-triangle scene %dx%d, %d quad lights (%d TriLights), RATIO intended mode "
+                "%d spp shadow rays + %d-pass a-trous denoise + ratio combine" % (N_TRIS, W, H, N_QUADS, 2 * N_QUADS, SPP, DN_ITERS))
+    else:
+        desc = "BASELINE configs[3]: same scene, PATH intended mode, %d bounces, progressive" % DEPTH
+    return {"workload": tag + desc,
             "width": W, "height": H, "triangles": N_TRIS, "tri_lights": 2 * N_QUADS, "shadow_spp": SPP,
-            "max_depth": DEPTH if args.workload == "path" else 1, "lut": "8x8 (reference ltc_isotropic.h)",
+            "max_depth": DEPTH if args.workload == "path" else 1,
+            "lut": "8x8 (reference ltc_isotropic.h)" if args.lut == 8 else "%dx%d (bilinear resampling of the reference table)" % (args.lut, args.lut),
             "partition": ("%d cost-balanced row bands, BVH replicated, point-to-point exchange of the packed denoise halo "
                           "rows, NCCL all-gather of the finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
             "l2": "working set per frame (13+ float4 frame buffers of 33 MB, 48 MB triangles, 64 MB BVH) exceeds the "
@@ -210,6 +217,8 @@ def run_ours(args):
     ratio = args.workload == "ratio"
 
     sc = scenes.scene_synthetic(N_TRIS, N_QUADS, W, H)
+    if args.lut != 8:
+        sc["lut"] = scenes.upsample_lut(sc["lut"], args.lut)
     r = api.Renderer(sc, device=local)
     stream = torch.cuda.Stream()
     r.set_stream(stream.cuda_stream)
@@ -456,7 +465,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="ratio", choices=["ratio", "path"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lut", type=int, default=8, help="LTC table size (8 = the reference's ltc_isotropic.h; 64 = north_star's)")
+    ap.add_argument("--scene", default="cfg3", choices=["cfg3", "cfg5"],
+                    help="cfg3: 1080p, 1 M triangles, 16 quad lights (default); cfg5: 4K, 10 M triangles, 64 quad lights")
     args = ap.parse_args()
+    global W, H, N_TRIS, N_QUADS
+    if args.scene == "cfg5":
+        W, H, N_TRIS, N_QUADS = 3840, 2160, 10_000_000, 64
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference(args)

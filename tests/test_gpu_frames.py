@@ -78,6 +78,20 @@ def test_frames_vs_oracle(renderer_factory, scene_fn, W, H, mode):
             assert rays == ref["rays"]                                      # exact
 
 
+def test_lut_64x64_vs_oracle(renderer_factory):
+    """A 64x64 LTC table (north_star; too large for the kernel's shared-memory copy: the global-memory path)
+    against the reference source with the same table."""
+    sc = scenes.scene_cornell(96, 80)
+    sc = dict(sc, lut=scenes.upsample_lut(sc["lut"], 64))
+    r = renderer_factory(sc)
+    o = best_oracle(1)
+    o.load_scene(sc)
+    assert o.set_options(1, 4, 1) == 0
+    for rt in (_oracle.LTC_BASELINE, _oracle.RATIO):
+        ref = o.render(96, 80, rt, 0, nthreads=8)
+        check_frame(gpu_frame(r, rt, 0, 1, 4, 1), ref, rt)
+
+
 def test_debug_aov_modes(renderer_factory):
     sc = scenes.scene_floor_blocker(48, 48)
     r = renderer_factory(sc)

@@ -62,6 +62,23 @@ def test_frames(hostcheck, scene_fn, W, H, mode):
             (a["rgba8"] != b["rgba8"]).mean() < 0.01  # 8-bit flips from last-ulp differences
 
 
+def test_lut_64x64(hostcheck):
+    """north_star names a 64x64 LTC table; the reference ships 8x8.  Any size goes through the same fetch
+    (fetchLtcMat, ltc_utils.cuh:10-23): the product against the reference source with a 64x64 table."""
+    sc = scenes.scene_cornell(40, 40)
+    sc = dict(sc, lut=scenes.upsample_lut(sc["lut"], 64))
+    hostcheck.load_scene(sc)
+    o = best_oracle(1)
+    o.load_scene(sc)
+    assert o.set_options(1, 4, 1) == 0
+    a = o.render(40, 40, _oracle.RATIO, 0)
+    b = hostcheck.render(40, 40, _oracle.RATIO, 0, mode=1, spp=4, depth=1)
+    rep = P.frame_report({k: b[k] for k in ("accum", "ltc", "sto_direct", "sto_no_vis", "position", "normal")},
+                         a, b["hit_prim"], a["hit_prim"])
+    assert rep["ltc"]["max_rel"] <= 1e-4 and rep["ltc"]["nan_mismatch"] == 0, rep["ltc"]
+    assert np.abs(a["ltc"][..., :3]).max() > 0
+
+
 def test_accumulation(hostcheck):
     sc = scenes.scene_floor_blocker(32, 32)
     hostcheck.load_scene(sc)
