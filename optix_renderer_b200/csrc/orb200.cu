@@ -369,14 +369,15 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
 // order; it only delays the pruning by best.t a little.  Against the batching form above this
 // keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
 // triangle test).
-template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0>
+template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, bool QSTACK = false>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
                     int node_min, int height, unsigned long long* __restrict__ stats = nullptr) {
     unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
-    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
+    unsigned long long q_stk[QSTACK ? LOCAL_STACK_MAX : 1];  // QSTACK: 64-bit entries, top entry in registers (scene.cuh)
+    int l_stk[LOCAL_STACK && !QSTACK ? LOCAL_STACK_MAX : 1];
+    float l_stk_t[LOCAL_STACK && !QSTACK ? LOCAL_STACK_MAX : 1];
     int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
     float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
     const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
@@ -438,11 +439,15 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {
             if (COUNT && t.cur >= 0) ++c_nodes;
-            if (t.cur >= 0) trav_node_step<SKIP>(t, s, stk, stk_t, stride);
-            else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+            if (QSTACK) {
+                if (t.cur >= 0) trav_node_step_q(t, s, q_stk);
+            } else {
+                if (t.cur >= 0) trav_node_step<SKIP>(t, s, stk, stk_t, stride);
+                else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+            }
             if (leaf == 0 && t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // postpone this leaf, keep walking
                 leaf = t.cur;
-                t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
             if ((int)__popc(__ballot_sync(FULL, t.cur >= 0 || t.cur == ORB_TRAVERSAL_POP)) < node_min) break;
         }
@@ -452,7 +457,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             leaf = 0;
             if (t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
-                t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
         }
     }
@@ -1334,6 +1339,9 @@ struct OrbContext {
     float4* bvh8_tri = nullptr;
     int bvh8_height = 0, bvh8_n_nodes = 0;
     int wide_node_min = 16;
+    // stream kernel: 64-bit stack entries with the top entry in registers (scene.cuh q forms).  Measured 1.735 ms
+    // against 1.696 ms: the earlier load does not pay for the extra register traffic.  Kept as a knob.
+    int q_stack = 0;
     // k_trace_stream_spec: culled stack entries dropped per main-loop iteration (0: drain in place).  Measured
     // 1.689 / 1.732 / 1.697 / 1.686 ms for 0 / 1 / 2 / 4: the drain's divergence is not what bounds the kernel.
     int pop_skip = 0;
@@ -1543,6 +1551,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
     if (const char* e = getenv("ORB_WIDE_NODE_MIN")) c->wide_node_min = atoi(e);
     if (const char* e = getenv("ORB_POP_SKIP")) c->pop_skip = atoi(e);
+    if (const char* e = getenv("ORB_Q_STACK")) c->q_stack = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -1853,6 +1862,7 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
         if (c->pop_skip == 1) k = k_trace_stream_spec<true, false, 1>;
         if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
         if (c->pop_skip == 4) k = k_trace_stream_spec<true, false, 4>;
+        if (c->q_stack) k = k_trace_stream_spec<true, false, 0, true>;
         const int g = persistent_grid(c, k, TRACE_BLOCK, 0);
         k<<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
                                      c->node_min, c->height, nullptr);

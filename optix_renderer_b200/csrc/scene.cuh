@@ -157,6 +157,8 @@ struct TravState {
     float3 o, d, inv, noi;  // noi = -o * inv
     Hit best;
     int cur, sp;
+    int top_ref;  // the "q" stack forms below keep the top entry here
+    float top_t;
 };
 
 ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
@@ -213,6 +215,70 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
         t.cur = c1;
     } else {
         t.cur = stack_pop<MAX_SKIP>(stk, stk_t, stride, t.sp, t.best);
+    }
+}
+
+// ---- "q" forms: 64-bit (reference, entry distance) stack entries, top entry in registers ---------------
+// The pop of the plain forms loads the entry it returns, so the next node fetch waits for a local-memory
+// load first (ncu profiles/r1m: 23 % of the stream kernel's stall samples sit on those loads).  Here the
+// entry a pop returns is already in registers and the load of the NEXT top is issued at once, a whole node
+// step before it is needed; an entry is one 64-bit word (one LDL / STL instead of two).
+// Invariant: entries 0 .. sp-2 are in `stk`, entry sp-1 is (top_ref, top_t).
+ORB_HD unsigned long long q_pack(int ref, float t) {
+    return ((unsigned long long)(unsigned)__float_as_int_hd(t) << 32) | (unsigned long long)(unsigned)ref;
+}
+ORB_HD void q_push(TravState& t, unsigned long long* stk, int ref, float tn) {
+    if (t.sp > 0) stk[t.sp - 1] = q_pack(t.top_ref, t.top_t);
+    t.top_ref = ref;
+    t.top_t = tn;
+    ++t.sp;
+}
+ORB_HD int q_pop(TravState& t, const unsigned long long* stk) {
+    for (;;) {  // skip subtrees that start beyond the current closest hit
+        if (t.sp == 0) return ORB_TRAVERSAL_DONE;
+        const int ref = t.top_ref;
+        const float tn = t.top_t;
+        --t.sp;
+        if (t.sp > 0) {
+            const unsigned long long e = stk[t.sp - 1];
+            t.top_ref = (int)(unsigned)(e & 0xffffffffull);
+            t.top_t = __int_as_float_hd((int)(unsigned)(e >> 32));
+        }
+        if (t.best.prim < 0 || !(tn > t.best.t)) return ref;
+    }
+}
+
+ORB_HD void trav_node_step_q(TravState& t, const SceneView& s, unsigned long long* stk) {
+    const BvhNode* np = s.nodes + t.cur;
+#ifdef __CUDA_ARCH__
+    float4 na, nb, nc;
+    int c0, c1, pad0, pad1;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(na.x), "=f"(na.y), "=f"(na.z), "=f"(na.w), "=f"(nb.x), "=f"(nb.y), "=f"(nb.z), "=f"(nb.w)
+        : "l"(np));
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
+        : "l"(reinterpret_cast<const char*>(np) + 32));
+    (void)pad0;
+    (void)pad1;
+#else
+    const float4 na = np->a, nb = np->b, nc = np->c;
+    const int c0 = np->c0, c1 = np->c1;
+#endif
+    const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
+    float tn0, tn1;
+    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
+    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
+    if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        q_push(t, stk, swap ? c0 : c1, swap ? tn0 : tn1);
+        t.cur = swap ? c1 : c0;
+    } else if (h0) {
+        t.cur = c0;
+    } else if (h1) {
+        t.cur = c1;
+    } else {
+        t.cur = q_pop(t, stk);
     }
 }
 
