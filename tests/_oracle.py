@@ -16,6 +16,10 @@ _PATHS = {
     "restatement": os.path.join(ROOT, "oracle", "liboracle.so"),
     "reference-literal": os.path.join(ROOT, "oracle", "_ref", "libref_literal.so"),
     "reference-intended": os.path.join(ROOT, "oracle", "_ref", "libref_intended.so"),
+    # the same reference TU compiled by nvcc for sm_100a: the literal megakernel ON THE GPU (oracle/ref_shim_gpu);
+    # scene / frame entry points only, whole frames only
+    "reference-gpu-literal": os.path.join(ROOT, "oracle", "_ref", "libref_gpu_literal.so"),
+    "reference-gpu-intended": os.path.join(ROOT, "oracle", "_ref", "libref_gpu_intended.so"),
 }
 
 BUFFER_NAMES = ["position", "normal", "uv", "albedo", "alpha", "materialID", "bounce0", "bounce1", "bounce2",
@@ -62,6 +66,11 @@ class Oracle:
         L.ora_set_options.argtypes = [C.c_int, C.c_int, C.c_int]
         L.ora_render.argtypes = [C.c_int] * 6 + [C.POINTER(OraBuffers), C.c_int]
         L.ora_render.restype = C.c_longlong
+        self.kind = L.ora_kind().decode()
+        self._keep = []
+        if self.kind.startswith("reference-gpu"):
+            L.ora_last_ms.restype = C.c_float
+            return
         L.ora_ltc_gbuffer.argtypes = [C.c_int, _f, _f, _f, _f, _f, _f, C.c_int]
         L.ora_u_rng.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, _u, _u, _f]
         L.ora_u_clip.argtypes = [C.c_int, _f]
@@ -85,6 +94,10 @@ class Oracle:
             L.ora_denoise.argtypes = [C.c_int, C.c_int, _f, _f, _f, _f, _f, _f, C.c_int, C.c_float, C.c_float,
                                       C.c_float, _f, _f, C.c_int]
         self._keep = []
+
+    def last_ms(self):
+        """reference-gpu kinds: CUDA-event time of the last render()'s megakernel."""
+        return float(self.lib.ora_last_ms())
 
     # ---- scene ----
     def reset(self):
