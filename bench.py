@@ -219,7 +219,7 @@ def run_ours(args):
     sc = scenes.scene_synthetic(N_TRIS, N_QUADS, W, H)
     if args.lut != 8:
         sc["lut"] = scenes.upsample_lut(sc["lut"], args.lut)
-    r = api.Renderer(sc, device=local)
+    r = api.Renderer(sc, device=local, quantise_lut=1)  # table fetched with the texture unit's weights, as the reference's tex2D
     stream = torch.cuda.Stream()
     r.set_stream(stream.cuda_stream)
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)

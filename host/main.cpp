@@ -39,6 +39,8 @@ static void usage() {
             "  --depth N            PATH bounces (default 8; literal mode fixes 1)\n"
             "  --denoise            RATIO: a-trous denoise of stoDirect/stoNoVis + ratio combine\n"
             "  --lut FILE.npy       LTC table (default: optix_renderer_b200/data/ltc_isotropic_8x8.npy)\n"
+            "  --exact-lut          fetch the table with exact fp32 bilinear weights instead of the texture unit's\n"
+            "                       1/256 weights (the reference reads it through tex2D, viewer.hpp:321-327)\n"
             "  --device D           CUDA device (default 0)\n"
             "  --dump-scene         print a JSON summary of the parsed scene and exit (no GPU needed)\n");
 }
@@ -121,6 +123,7 @@ int main(int argc, char** argv) {
     std::string scene_file, out_dir = "saves", lut_path, renderer_arg, mode_arg = "intended";
     int frames = -1, W = 0, H = 0, cam_i = 0, shadow_spp = 4, depth = 8, device = 0;
     bool denoise = false, only_dump = false;
+    int lut_quantise = 1;  // the texture unit's weight rule (measured on the B200, profiles/r1n_texture_unit.json)
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
         auto next = [&](const char* what) -> const char* {
@@ -142,6 +145,7 @@ int main(int argc, char** argv) {
         else if (a == "--depth") depth = atoi(next("--depth"));
         else if (a == "--denoise") denoise = true;
         else if (a == "--lut") lut_path = next("--lut");
+        else if (a == "--exact-lut") lut_quantise = 0;
         else if (a == "--device") device = atoi(next("--device"));
         else if (a == "--dump-scene") only_dump = true;
         else if (a == "-h" || a == "--help") { usage(); return 0; }
@@ -204,7 +208,7 @@ int main(int argc, char** argv) {
     }
     const std::vector<OrbTriLight> lights = build_tri_lights(scene);
     ORB_CHECK(orb_scene_set_lights(ctx, lights.data(), (int32_t)lights.size()));
-    ORB_CHECK(orb_scene_set_ltc_lut(ctx, m1.data(), m2.data(), m3.data(), lw, lh, 0));
+    ORB_CHECK(orb_scene_set_ltc_lut(ctx, m1.data(), m2.data(), m3.data(), lw, lh, lut_quantise));
     const auto t_build0 = std::chrono::steady_clock::now();
     ORB_CHECK(orb_scene_commit(ctx, nullptr));
     ORB_CHECK(orb_sync(ctx));

@@ -142,7 +142,7 @@ def test_host_dumps_equal_binding(host, tmp_path, renderer, frames):
         args.append("--denoise")
     o = subprocess.run(args, capture_output=True, text=True)
     assert o.returncode == 0, o.stderr
-    r = api.Renderer(sc)
+    r = api.Renderer(sc, quantise_lut=1)  # the host fetches the LTC table like the texture unit by default
     rt = {"ratio": api.RATIO, "path": api.PATH, "ltc_baseline": api.LTC_BASELINE}[renderer]
     for f in range(frames):
         r.render(rt, accum_id=f, mode=api.INTENDED, shadow_spp=4, max_depth=3)
