@@ -1339,6 +1339,9 @@ struct OrbContext {
     float4* bvh8_tri = nullptr;
     int bvh8_height = 0, bvh8_n_nodes = 0;
     int wide_node_min = 16;
+    // > 0: shrink the stream kernel's grid until every lane expects this many rays.  Measured on a 135-row band:
+    // 0.428 / 0.430 / 0.453 / 0.606 / 0.961 ms for 0 / 4 / 8 / 16 / 32 -- parallelism beats shorter tails.
+    int min_rays_per_lane = 0;
     // stream kernel: 64-bit stack entries with the top entry in registers (scene.cuh q forms).  Measured 1.735 ms
     // against 1.696 ms: the earlier load does not pay for the extra register traffic.  Kept as a knob.
     int q_stack = 0;
@@ -1552,6 +1555,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_WIDE_NODE_MIN")) c->wide_node_min = atoi(e);
     if (const char* e = getenv("ORB_POP_SKIP")) c->pop_skip = atoi(e);
     if (const char* e = getenv("ORB_Q_STACK")) c->q_stack = atoi(e);
+    if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -1830,7 +1834,7 @@ static int ensure_stream(OrbContext* c, size_t n_rays) {
 
 // closest hits of the rays in c->stream_rays -> c->stream_hits; the ray count is *n_items * mult on the device
 static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned mult, bool count = false,
-                               bool timed = false) {
+                               bool timed = false, size_t n_upper = 0) {
     cudaStream_t st = c->stream;
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
     StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
@@ -1863,7 +1867,12 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
         if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
         if (c->pop_skip == 4) k = k_trace_stream_spec<true, false, 4>;
         if (c->q_stack) k = k_trace_stream_spec<true, false, 0, true>;
-        const int g = persistent_grid(c, k, TRACE_BLOCK, 0);
+        int g = persistent_grid(c, k, TRACE_BLOCK, 0);
+        // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
+        // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.
+        if (c->min_rays_per_lane > 0 && n_upper > 0)
+            g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)TRACE_BLOCK * c->min_rays_per_lane - 1) /
+                                                     ((size_t)TRACE_BLOCK * c->min_rays_per_lane))));
         k<<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
                                      c->node_min, c->height, nullptr);
     } else if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
@@ -1956,7 +1965,8 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                     k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
                     c->counters.kernel_launches++;
                 }
-                rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true);
+                rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true,
+                                         npx * (size_t)spp);
                 if (rc) return rc;
             }
             if (ltc_beside_shadow) {  // depends on k_primary only, but is SUBMITTED behind the traversal kernel

@@ -7,7 +7,7 @@ from optix_renderer_b200 import api, scenes
 sc = scenes.scene_synthetic(1_000_000, 16, 1920, 1080)
 r = api.Renderer(sc)
 out = {}
-for rows in (1, 4, 16, 64, 256, 1080):
+for rows in ((135, 270) if os.environ.get("FLOOR_BANDS") else (1, 4, 16, 64, 256, 1080)):
     y0 = 300
     band = (y0, min(1080, y0 + rows)) if rows < 1080 else (0, 1080)
     for rt, name in ((api.RATIO, "ratio"), (api.PATH, "path")):
