@@ -39,6 +39,9 @@ static void usage() {
             "  --depth N            PATH bounces (default 8; literal mode fixes 1)\n"
             "  --denoise            RATIO: a-trous denoise of stoDirect/stoNoVis + ratio combine\n"
             "  --lut FILE.npy       LTC table (default: optix_renderer_b200/data/ltc_isotropic_8x8.npy)\n"
+            "  --exr                every .btc dump also as NAME.exr (what the reference's save.py produces)\n"
+            "  --save-state FILE    write the accumulation checkpoint (accum buffer + frame count) after the last frame\n"
+            "  --resume FILE        start from such a checkpoint: accumId continues where it stopped\n"
             "  --exact-lut          fetch the table with exact fp32 bilinear weights instead of the texture unit's\n"
             "                       1/256 weights (the reference reads it through tex2D, viewer.hpp:321-327)\n"
             "  --device D           CUDA device (default 0)\n"
@@ -54,12 +57,104 @@ static bool write_file(const std::string& path, const void* data, size_t bytes) 
 }
 
 // Viewer::savebuffer, viewer.hpp:695-713: the raw float4 buffer, every float divided by avg_factor
+// OpenEXR, scanline, uncompressed, three FLOAT channels: what the reference's save.py makes of a .btc dump
+// (reshape to rows of float4, flipud, drop w, imageio.imwrite(name.exr): save.py:9-12) and what
+// ltc_ratio_estimator.py:3-5 reads.  `rgba` is the float4 buffer, row 0 = bottom image row.
+static bool write_exr(const std::string& path, int W, int H, const float* rgba) {
+    std::vector<unsigned char> hd;
+    auto put = [&](const void* p, size_t n) { hd.insert(hd.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+    auto str = [&](const char* t) { put(t, strlen(t) + 1); };
+    auto i32 = [&](int32_t v) { put(&v, 4); };
+    auto f32 = [&](float v) { put(&v, 4); };
+    auto attr = [&](const char* name, const char* type, int32_t size) { str(name); str(type); i32(size); };
+    const unsigned char magic[4] = {0x76, 0x2f, 0x31, 0x01};
+    put(magic, 4);
+    i32(2);  // version 2, single-part scanline
+    attr("channels", "chlist", 3 * (2 + 16) + 1);
+    for (const char* c : {"B", "G", "R"}) {  // alphabetical, as the format requires
+        str(c);
+        i32(2);  // FLOAT
+        const unsigned char lin[4] = {0, 0, 0, 0};
+        put(lin, 4);
+        i32(1);
+        i32(1);
+    }
+    hd.push_back(0);
+    attr("compression", "compression", 1);
+    hd.push_back(0);
+    attr("dataWindow", "box2i", 16);
+    i32(0); i32(0); i32(W - 1); i32(H - 1);
+    attr("displayWindow", "box2i", 16);
+    i32(0); i32(0); i32(W - 1); i32(H - 1);
+    attr("lineOrder", "lineOrder", 1);
+    hd.push_back(0);
+    attr("pixelAspectRatio", "float", 4);
+    f32(1.f);
+    attr("screenWindowCenter", "v2f", 8);
+    f32(0.f); f32(0.f);
+    attr("screenWindowWidth", "float", 4);
+    f32(1.f);
+    hd.push_back(0);
+    const uint64_t line_bytes = 8 + (uint64_t)3 * W * 4;
+    uint64_t ofs = hd.size() + (uint64_t)8 * H;
+    for (int y = 0; y < H; y++, ofs += line_bytes) put(&ofs, 8);
+    FILE* fp = fopen(path.c_str(), "wb");
+    if (!fp) return false;
+    bool ok = fwrite(hd.data(), 1, hd.size(), fp) == hd.size();
+    std::vector<float> line((size_t)3 * W);
+    for (int y = 0; y < H && ok; y++) {
+        const float* src = rgba + 4 * (size_t)(H - 1 - y) * W;  // top image row first
+        for (int x = 0; x < W; x++) {
+            line[x] = src[4 * x + 2];
+            line[(size_t)W + x] = src[4 * x + 1];
+            line[(size_t)2 * W + x] = src[4 * x];
+        }
+        const int32_t head[2] = {y, (int32_t)(3 * W * 4)};
+        ok = fwrite(head, 4, 2, fp) == 2 && fwrite(line.data(), 4, line.size(), fp) == line.size();
+    }
+    return fclose(fp) == 0 && ok;
+}
+
+static bool g_write_exr = false;  // --exr: every .btc dump also as NAME.exr (save.py's output)
+static int g_W = 0, g_H = 0;      // frame size of the dumps
+
 static bool save_btc(OrbContext* ctx, int buffer_id, const std::string& path, int avg_factor, std::vector<float>& tmp) {
     const size_t bytes = orb_buffer_bytes(ctx, buffer_id);
     tmp.resize(bytes / 4);
     if (orb_buffer_download(ctx, buffer_id, tmp.data(), bytes)) return false;
     for (auto& x : tmp) x = x / (float)avg_factor;
-    return write_file(path, tmp.data(), bytes);
+    if (!write_file(path, tmp.data(), bytes)) return false;
+    if (g_write_exr) {
+        return write_exr(path.substr(0, path.rfind('.')) + ".exr", g_W, g_H, tmp.data());
+    }
+    return true;
+}
+
+// Accumulation checkpoint: the progressive sum and the number of frames in it (Viewer::accumId); --save-state
+// after the last frame, --resume before the first.
+struct StateHeader {
+    char magic[8];
+    int32_t W, H, frames, renderer;
+};
+static bool save_state(OrbContext* ctx, const std::string& path, int W, int H, int frames, int renderer) {
+    StateHeader h = {{'O', 'R', 'B', 'A', 'C', 'C', 'U', 'M'}, W, H, frames, renderer};
+    std::vector<float> acc((size_t)4 * W * H);
+    if (orb_buffer_download(ctx, ORB_BUF_ACCUM, acc.data(), acc.size() * 4)) return false;
+    FILE* fp = fopen(path.c_str(), "wb");
+    if (!fp) return false;
+    const bool ok = fwrite(&h, sizeof h, 1, fp) == 1 && fwrite(acc.data(), 4, acc.size(), fp) == acc.size();
+    return fclose(fp) == 0 && ok;
+}
+static int load_state(OrbContext* ctx, const std::string& path, int W, int H, int renderer) {  // frames done, or -1
+    FILE* fp = fopen(path.c_str(), "rb");
+    if (!fp) return -1;
+    StateHeader h;
+    std::vector<float> acc((size_t)4 * W * H);
+    const bool ok = fread(&h, sizeof h, 1, fp) == 1 && memcmp(h.magic, "ORBACCUM", 8) == 0 && h.W == W && h.H == H &&
+                    h.renderer == renderer && fread(acc.data(), 4, acc.size(), fp) == acc.size();
+    fclose(fp);
+    if (!ok || orb_buffer_upload(ctx, ORB_BUF_ACCUM, acc.data(), acc.size() * 4)) return -1;
+    return h.frames;
 }
 
 static bool save_ppm(OrbContext* ctx, int W, int H, const std::string& path) {
@@ -123,6 +218,7 @@ int main(int argc, char** argv) {
     std::string scene_file, out_dir = "saves", lut_path, renderer_arg, mode_arg = "intended";
     int frames = -1, W = 0, H = 0, cam_i = 0, shadow_spp = 4, depth = 8, device = 0;
     bool denoise = false, only_dump = false;
+    std::string save_state_path, resume_path;
     int lut_quantise = 1;  // the texture unit's weight rule (measured on the B200, profiles/r1n_texture_unit.json)
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
@@ -146,6 +242,18 @@ int main(int argc, char** argv) {
         else if (a == "--denoise") denoise = true;
         else if (a == "--lut") lut_path = next("--lut");
         else if (a == "--exact-lut") lut_quantise = 0;
+        else if (a == "--exr") g_write_exr = true;
+        else if (a == "--save-state") save_state_path = next("--save-state");
+        else if (a == "--resume") resume_path = next("--resume");
+        else if (a == "--selftest-exr") {  // writes a known image: tests/test_host.py reads it back
+            const char* path = next("--selftest-exr");
+            const int w = 7, h = 5;
+            std::vector<float> img((size_t)4 * w * h);
+            for (int y = 0; y < h; y++)
+                for (int x = 0; x < w; x++)
+                    for (int c = 0; c < 4; c++) img[4 * ((size_t)y * w + x) + c] = (float)(1000 * y + 10 * x + c) + 0.25f;
+            return write_exr(path, w, h, img.data()) ? 0 : 3;
+        }
         else if (a == "--device") device = atoi(next("--device"));
         else if (a == "--dump-scene") only_dump = true;
         else if (a == "-h" || a == "--help") { usage(); return 0; }
@@ -214,6 +322,8 @@ int main(int argc, char** argv) {
     ORB_CHECK(orb_sync(ctx));
     const double build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build0).count();
     ORB_CHECK(orb_resize(ctx, W, H));
+    g_W = W;
+    g_H = H;
     float pos[3], d00[3], du[3], dv[3];
     camera_vectors(scene.cameras[cam_i], W, H, pos, d00, du, dv);
     ORB_CHECK(orb_set_camera(ctx, pos, d00, du, dv));
@@ -227,8 +337,14 @@ int main(int argc, char** argv) {
     cfg.mode = mode_arg == "intended" ? 1 : 0;
     cfg.shadow_spp = shadow_spp;
     cfg.max_depth = depth;
+    int first_frame = 0;
+    if (!resume_path.empty()) {
+        first_frame = load_state(ctx, resume_path, W, H, renderer);
+        if (first_frame < 0) { fprintf(stderr, "orb_render: cannot resume from %s (size / renderer mismatch?)\n", resume_path.c_str()); return 1; }
+        fprintf(stderr, "resumed at accumId %d\n", first_frame);
+    }
     const auto t0 = std::chrono::steady_clock::now();
-    for (int f = 0; f < frames; f++) {
+    for (int f = first_frame; f < first_frame + frames; f++) {
         cfg.accum_id = f;
         ORB_CHECK(orb_render_async(ctx, &cfg));
     }
@@ -248,7 +364,11 @@ int main(int argc, char** argv) {
     mkdir(out_dir.c_str(), 0777);
     const std::string o = out_dir + "/";
     std::vector<float> tmp;
-    const int accum = frames;  // Viewer::accumId after `frames` calls of render()
+    const int accum = first_frame + frames;  // Viewer::accumId after that many calls of render()
+    if (!save_state_path.empty() && !save_state(ctx, save_state_path, W, H, accum, renderer)) {
+        fprintf(stderr, "orb_render: cannot write %s\n", save_state_path.c_str());
+        return 3;
+    }
     bool ok = true;
     if (renderer == ORB_RATIO) {
         ok &= save_btc(ctx, ORB_BUF_STO_DIRECT, o + "stoDirect.btc", 1, tmp);

@@ -129,6 +129,57 @@ def test_host_obj_features(host, tmp_path):
     assert green["vertex_hash"] == fnv1a(fan)
 
 
+def test_host_exr_writer(host, tmp_path):
+    """--exr writes what save.py makes of a .btc dump (flipud, RGB, float32): read back with OpenCV's EXR codec
+    (imageio, which the reference uses, is not installed)."""
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    cv2 = pytest.importorskip("cv2")
+    p = tmp_path / "t.exr"
+    assert subprocess.run([host, "--selftest-exr", str(p)]).returncode == 0
+    a = cv2.imread(str(p), cv2.IMREAD_UNCHANGED)
+    if a is None:
+        pytest.skip("this OpenCV build has no EXR codec")
+    h, w = 5, 7
+    y, x, c = np.meshgrid(np.arange(h), np.arange(w), np.arange(3), indexing="ij")
+    want = (1000 * (h - 1 - y) + 10 * x + c + 0.25).astype(np.float32)   # row 0 of the buffer is the bottom image row
+    assert a.dtype == np.float32 and np.array_equal(a[..., ::-1], want)
+
+
+@pytest.mark.gpu
+def test_host_checkpoint_resume_and_exr(host, tmp_path):
+    """2 frames + checkpoint + 3 more frames == 5 frames in one go, bit for bit (accum and accumId travel in the
+    checkpoint); the EXR dumps run through the reference's offline expression (ltc_ratio_estimator.py:8)."""
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    sc = scenes.scene_cornell(96, 64)
+    path = scenes.export_scene(sc, str(tmp_path))
+    a, b, ck = tmp_path / "a", tmp_path / "b", tmp_path / "state.bin"
+    run = lambda *x: subprocess.run([host, path, "--renderer", "path", "--depth", "3", *x], capture_output=True, text=True)
+    o = run("--out", str(a), "--frames", "5")
+    assert o.returncode == 0, o.stderr
+    o = run("--out", str(tmp_path / "b0"), "--frames", "2", "--save-state", str(ck))
+    assert o.returncode == 0, o.stderr
+    o = run("--out", str(b), "--frames", "3", "--resume", str(ck))
+    assert o.returncode == 0 and "resumed at accumId 2" in o.stderr, o.stderr
+    assert (a / "path.btc").read_bytes() == (b / "path.btc").read_bytes()
+    assert (a / "rendered_output.ppm").read_bytes() == (b / "rendered_output.ppm").read_bytes()
+    o = run("--out", str(b), "--frames", "1", "--resume", str(ck), "--size", "32x32")
+    assert o.returncode != 0 and "cannot resume" in o.stderr
+    # EXR dumps of a denoised RATIO run -> the reference's offline combine
+    cv2 = pytest.importorskip("cv2")
+    r = tmp_path / "r"
+    o = subprocess.run([host, path, "--renderer", "ratio", "--frames", "1", "--denoise", "--exr", "--out", str(r)],
+                       capture_output=True, text=True)
+    assert o.returncode == 0, o.stderr
+    rd = lambda n: cv2.imread(str(r / (n + ".exr")), cv2.IMREAD_UNCHANGED)
+    ltc, sd, sn, fin = rd("ltc"), rd("stodirectDenoise"), rd("stoNoVisDenoise"), rd("final_ratio_estimator")
+    if ltc is None:
+        pytest.skip("this OpenCV build has no EXR codec")
+    with np.errstate(all="ignore"):
+        assert np.array_equal(ltc * (sd / sn), fin, equal_nan=True)
+    btc = np.fromfile(str(r / "ltc.btc"), np.float32).reshape(64, 96, 4)
+    assert np.array_equal(np.flipud(btc)[..., :3], ltc[..., ::-1])          # save.py:9-11
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("renderer,frames", [("ratio", 2), ("path", 3), ("ltc_baseline", 1)])
 def test_host_dumps_equal_binding(host, tmp_path, renderer, frames):
