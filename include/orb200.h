@@ -122,6 +122,8 @@ typedef struct OrbRenderConfig {
 #define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
                                         records fetched / triangle records tested land in OrbCounters.nodes_visited
                                         / tris_tested (same results, slower; bench.py's roofline uses it once) */
+#define ORB_RENDER_DEFER_LTC 16 /* RATIO: primary + shadow rays only; orb_render_finish() runs the LTC sum and the
+                                   accumulation later (a tile partition overlaps them with its denoise halo exchange) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 
@@ -206,6 +208,8 @@ int orb_resize(OrbContext* ctx, int32_t width, int32_t height);
  * Blocking, like owlLaunch2D.  orb_render_async() enqueues on orb_stream() and returns. */
 int orb_render(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
+/* second half of a RATIO frame rendered with ORB_RENDER_DEFER_LTC (same cfg): LTC sum + accumulation; asynchronous */
+int orb_render_finish(OrbContext* ctx, const OrbRenderConfig* cfg);
 
 /* ---- stand-alone passes over RESIDENT frame buffers (rows [y0,y1), 0,0 = all) ---- */
 /* ltcDirectLighingBaseline over the G-buffer (position, normal, albedo, alpha) -> ORB_BUF_LTC;

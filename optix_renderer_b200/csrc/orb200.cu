@@ -1932,7 +1932,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     // RATIO: the LTC sum (fp32-issue bound, no dependence on the shadow rays) is enqueued on a second
     // stream AFTER the shadow-ray kernels, so its CTAs fill the SMs the persistent traversal kernel
     // leaves idle while its last rays finish (floor of ~0.17 ms per traversal launch, profiles/r1k).
-    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & ORB_RENDER_FUSED_SHADOW);
+    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & (ORB_RENDER_FUSED_SHADOW | ORB_RENDER_DEFER_LTC));
     auto launch_ltc = [&](cudaStream_t ls) {
         StageTimer tm(c, ORB_STAGE_LTC, 1, ls);
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
@@ -1945,7 +1945,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
         c->counters.kernel_launches++;
     };
-    if ((renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && !ltc_beside_shadow) launch_ltc(st);
+    // ORB_RENDER_DEFER_LTC (RATIO): stop after the shadow rays; orb_render_finish() runs the LTC sum and the
+    // accumulation later, e.g. while a tile partition's denoise halo is in flight
+    const bool defer_ltc = renderer == ORB_RATIO && (cfg->flags & ORB_RENDER_DEFER_LTC);
+    if ((renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && !ltc_beside_shadow && !defer_ltc) launch_ltc(st);
     if (ltc_beside_shadow) CK(cudaEventRecord(c->ev_fork, st));  // k_primary done: queue and G-buffers are final
     if (renderer == ORB_RATIO) {
         if (cfg->flags & ORB_RENDER_FUSED_SHADOW) {  // A/B: one thread per pixel, n rays in sequence
@@ -2055,11 +2058,40 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
     }
     if (ltc_beside_shadow) CK(cudaStreamWaitEvent(st, c->ev_join, 0));
-    {
+    if (!defer_ltc) {
         StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
         const size_t n = (size_t)(y1 - y0) * c->W;
         const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
         k_accumulate<<<g, 256, 0, st>>>(f, colour_src, cfg->accum_id, count_rays);
+        c->counters.kernel_launches++;
+    }
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+// Second half of a RATIO frame rendered with ORB_RENDER_DEFER_LTC: the LTC sum over the frame's active-pixel
+// queue and the accumulation, with the same config (rows, accumId).  Asynchronous.
+int orb_render_finish(OrbContext* c, const OrbRenderConfig* cfg) {
+    NEED(c && cfg, "orb_render_finish: NULL argument");
+    NEED(c->committed && c->W > 0 && c->have_cam && c->lut_w > 0, "orb_render_finish: no frame to finish");
+    NEED(cfg->renderer_type == ORB_RATIO && (cfg->flags & ORB_RENDER_DEFER_LTC),
+         "orb_render_finish: only after a RATIO orb_render with ORB_RENDER_DEFER_LTC");
+    int y0 = cfg->y0, y1 = cfg->y1;
+    NEED(rows_ok(c, y0, y1), "orb_render_finish: bad row range");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    FrameView f = frame_view(c, y0, y1);
+    {
+        StageTimer tm(c, ORB_STAGE_LTC, 1);
+        const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
+        k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+        c->counters.kernel_launches++;
+    }
+    {
+        StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
+        const size_t n = (size_t)(y1 - y0) * c->W;
+        const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
+        k_accumulate<<<g, 256, 0, st>>>(f, f.ltc, cfg->accum_id, (cfg->flags & ORB_RENDER_NO_COUNT) ? 0 : 1);
         c->counters.kernel_launches++;
     }
     CK(cudaGetLastError());
