@@ -226,6 +226,7 @@ def run_ours(args):
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
 
     SYNC_ASSEMBLE = bool(os.environ.get("ORB_BENCH_SYNC_ASSEMBLE"))  # A/B: gather in place on the render stream
+    SYNC_DOWNLOAD = os.environ.get("ORB_BENCH_SYNC_DOWNLOAD", "0") == "1"  # A/B: blocking read-back every frame
 
     def render(i):
         if ratio:
@@ -310,26 +311,50 @@ def run_ours(args):
         # ---- end to end through the C-ABI with host buffers: camera in (host), frame out (pinned host) ----
         cam = sc["camera"]
         y0, y1 = (0, H)
-        t_f4 = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
-        t_u32 = torch.empty((H, W), dtype=torch.int32, pin_memory=True)
+        t_f4 = torch.empty((2, H, W, 4), dtype=torch.float32, pin_memory=True)   # two host frames: a consumer reads one
+        t_u32 = torch.empty((2, H, W), dtype=torch.int32, pin_memory=True)       # while the next one lands
         host_f4, host_u32 = t_f4.numpy(), t_u32.numpy().view(np.uint32)
         e_steps = max(3, min(args.steps, 30))
-        barrier()
-        t0 = time.perf_counter()
-        for i in range(e_steps):
-            r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
-            step(base_id + args.steps + i)
-            if rank == 0 and world == 1:
-                r.download(out_names[0], rows=(y0, y1), out=host_f4)      # D2H through the C-ABI, synchronises
-                r.download("rgba8", rows=(y0, y1), out=host_u32)
-            elif rank == 0:                                               # the assembled frame lives in T.out
+
+        def e2e_loop(pipelined, id0, n):
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(n):
+                r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
+                step(id0 + i)
+                if rank == 0 and world == 1 and pipelined:
+                    # D2H through the C-ABI, every frame, overlapped with the next frame's kernels
+                    r.download_async(out_names[0], host_f4[i & 1], rows=(y0, y1))
+                    r.download_async("rgba8", host_u32[i & 1], rows=(y0, y1))
+                elif rank == 0 and world == 1:
+                    r.download(out_names[0], rows=(y0, y1), out=host_f4[i & 1])  # synchronises every frame
+                    r.download("rgba8", rows=(y0, y1), out=host_u32[i & 1])
+                elif rank == 0 and not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:
+                    # the assembled frame lives in T.out: read back behind the gather, beside the next frame
+                    T.read_back_async({out_names[0]: t_f4[i & 1], "rgba8": t_u32[i & 1]})
+                elif rank == 0:
+                    T.wait_assembled()
+                    t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
+                    t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
+                    torch.cuda.current_stream().synchronize()
+            if world > 1 and rank == 0:
                 T.wait_assembled()
-                t_f4.copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
-                t_u32.copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
                 torch.cuda.current_stream().synchronize()
-        barrier()
-        e_ms = (time.perf_counter() - t0) * 1e3
-        e_ms = reduce(e_ms, dist.ReduceOp.MAX) if world > 1 else e_ms
+                T.wait_read_back()  # the last frame is on the host when the clock stops
+            if world == 1 and pipelined:
+                r.sync()
+                r.download_wait()  # the last frame is on the host when the clock stops
+            barrier()
+            t = (time.perf_counter() - t0) * 1e3
+            return reduce(t, dist.ReduceOp.MAX) if world > 1 else t
+
+        PIPE = world == 1 and not SYNC_DOWNLOAD
+        serial_ms = e2e_loop(False, base_id + args.steps, e_steps) if PIPE else None
+        if PIPE:
+            e2e_loop(True, base_id + args.steps, 3)  # untimed: the read-back slots are allocated on first use
+        e_ms = e2e_loop(PIPE, base_id + args.steps + (e_steps if PIPE else 0), e_steps)
+        # the frame that arrived through the pipelined read-back is the frame the device holds
+        readback_ok = bool(np.array_equal(host_f4[(e_steps - 1) & 1], r.download(out_names[0]), equal_nan=True)) if PIPE else None
         e_value = (rays / args.steps) * e_steps / (e_ms * 1e-3) / 1e6
         clocks = sampler.summary()
         clocks["window"] = "warm-up + timed region + e2e loop (one continuous load)"
@@ -339,6 +364,8 @@ def run_ours(args):
             # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
             T.wait_assembled()
             got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
+            if not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:  # the frame as the host received it through the pipelined read-back
+                got = t_f4[(e_steps - 1) & 1].to("cuda")
             last = base_id + args.steps + e_steps - 1
             r.render(api.RATIO, accum_id=last, mode=api.INTENDED, shadow_spp=SPP, count_rays=False)
             r.denoise(iterations=DN_ITERS)
@@ -437,9 +464,18 @@ def run_ours(args):
                 "e2e": {"value": e_value, "unit": "Mrays/s", "ms_per_step": e_ms / e_steps,
                         "frames_per_s": e_steps / (e_ms * 1e-3), "h2d_bytes_per_step": 48 + 32,
                         "d2h_bytes_per_step": W * H * 20, "steps": e_steps,
-                        "what": "orb_set_camera + orb_render_async(+denoise+combine) + orb_buffer_download_rows of the "
-                                "float4 result and the RGBA8 frame into pinned host memory"},
+                        "what": "orb_set_camera + orb_render_async(+denoise+combine) + %s of the "
+                                "float4 result and the RGBA8 frame into pinned host memory, every frame"
+                                % ("orb_buffer_download_rows_async (read-back of frame i overlaps the kernels of frame i+1; "
+                                   "orb_download_wait inside the timed region)" if PIPE else
+                                   "orb_buffer_download_rows" if world == 1 else
+                                   "rank 0's copy of the assembled frame" + ("" if SYNC_ASSEMBLE or SYNC_DOWNLOAD else
+                                   " on a copy stream, behind the all-gather and beside the next frame's kernels; the "
+                                   "last copy is waited for inside the timed region"))},
                 "gpu_launches": int(launches), "roofline": roofline, "passes": passes, "clocks": clocks}
+        if PIPE:
+            line["e2e"]["serial_ms_per_step"] = serial_ms / e_steps  # the same loop with a blocking download per frame
+            line["e2e"]["readback_equals_device_frame"] = readback_ok
         if one_quad:
             line["ltc_pass_one_quad"] = line_ltc
         if world > 1:

@@ -233,6 +233,14 @@ size_t orb_buffer_bytes(OrbContext* ctx, int32_t buffer_id);
 void* orb_buffer_device_ptr(OrbContext* ctx, int32_t buffer_id);
 int orb_buffer_download(OrbContext* ctx, int32_t buffer_id, void* host_dst, size_t bytes);
 int orb_buffer_download_rows(OrbContext* ctx, int32_t buffer_id, void* host_dst, int32_t y0, int32_t y1);
+/* Pipelined read-back for an interactive loop (viewer.hpp:695-713 reads the frame back every frame): returns at
+ * once; the rows are snapshotted on the frame stream into one of two device slots per buffer and copied to
+ * host_dst on a copy stream while later frames render.  host_dst should be page-locked (a pageable destination
+ * makes the copy synchronous) and must stay valid until orb_download_wait, which blocks until every
+ * outstanding asynchronous download of this context has landed.  At most two downloads per buffer in flight
+ * keep distinct slots; a third waits for the first on the device. */
+int orb_buffer_download_rows_async(OrbContext* ctx, int32_t buffer_id, void* host_dst, int32_t y0, int32_t y1);
+int orb_download_wait(OrbContext* ctx);
 int orb_buffer_upload(OrbContext* ctx, int32_t buffer_id, const void* host_src, size_t bytes);
 int orb_get_counters(OrbContext* ctx, OrbCounters* out);
 

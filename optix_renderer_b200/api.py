@@ -123,6 +123,8 @@ def load_library():
     L.orb_buffer_device_ptr.restype = vp
     L.orb_buffer_download.argtypes = [vp, C.c_int32, vp, C.c_size_t]
     L.orb_buffer_download_rows.argtypes = [vp, C.c_int32, vp, C.c_int32, C.c_int32]
+    L.orb_buffer_download_rows_async.argtypes = [vp, C.c_int32, vp, C.c_int32, C.c_int32]
+    L.orb_download_wait.argtypes = [vp]
     L.orb_buffer_upload.argtypes = [vp, C.c_int32, vp, C.c_size_t]
     L.orb_get_counters.argtypes = [vp, C.POINTER(OrbCounters)]
     L.orb_ratio_estimator_host.argtypes = [vp, _f, _f, _f, _f, C.c_size_t]
@@ -320,6 +322,16 @@ class Renderer:
                    else np.empty((y1 - y0, self.W, 2 if name == "dn_val" else 4), np.float32))
         self._ck(self.lib.orb_buffer_download_rows(self._h, bid, out.ctypes.data_as(C.c_void_p), y0, y1))
         return out
+
+    def download_async(self, name, out, rows=None):
+        """Pipelined read-back (orb_buffer_download_rows_async): `out` is a page-locked array that must stay
+        alive and untouched until download_wait()."""
+        y0, y1 = rows if rows else (0, self.H)
+        self._ck(self.lib.orb_buffer_download_rows_async(self._h, BUFFERS[name], out.ctypes.data_as(C.c_void_p), y0, y1))
+        return out
+
+    def download_wait(self):
+        self._ck(self.lib.orb_download_wait(self._h))
 
     def upload(self, name, arr):
         a = np.ascontiguousarray(arr)

@@ -1349,6 +1349,13 @@ struct OrbContext {
     // 1.689 / 1.732 / 1.697 / 1.686 ms for 0 / 1 / 2 / 4: the drain's divergence is not what bounds the kernel.
     int pop_skip = 0;
     cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
+    // orb_buffer_download_rows_async: the frame stream snapshots the rows into a device slot (two per buffer), the
+    // copy stream moves the slot to the host while the next frame renders.
+    cudaStream_t copy_stream = nullptr;
+    struct DlSlot { void* dev = nullptr; size_t cap = 0; cudaEvent_t ready = nullptr, done = nullptr; };
+    DlSlot dl[ORB_BUF_COUNT][2];
+    int dl_next[ORB_BUF_COUNT] = {};
+    int dl_snapshot_kernel = 1;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
     int ltc_overlap = 0;  // measured: no gain (3.392 vs 3.394 ms per RATIO frame), kept as a knob
@@ -1556,6 +1563,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_POP_SKIP")) c->pop_skip = atoi(e);
     if (const char* e = getenv("ORB_Q_STACK")) c->q_stack = atoi(e);
     if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
+    if (const char* e = getenv("ORB_DL_SNAPSHOT_KERNEL")) c->dl_snapshot_kernel = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -1577,6 +1585,13 @@ void orb_destroy(OrbContext* c) {
     cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->cnt); cudaFree(c->unit_in); cudaFree(c->unit_out);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (c->aux_stream) { cudaStreamSynchronize(c->aux_stream); cudaStreamDestroy(c->aux_stream); }
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    for (auto& per_buf : c->dl)
+        for (auto& sl : per_buf) {
+            cudaFree(sl.dev);
+            if (sl.ready) cudaEventDestroy(sl.ready);
+            if (sl.done) cudaEventDestroy(sl.done);
+        }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     delete c;
@@ -2203,6 +2218,11 @@ int orb_denoise(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t 
 }
 
 // active (non-light hit) pixels of every row of the last frame, for cost-balanced tile partitions
+// orb_buffer_download_rows_async: rows -> device slot on the SMs, so the copy engines only carry the host copy
+__global__ void k_snapshot(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 __global__ void k_row_active(FrameView f, int* __restrict__ counts) {
     const int y = blockIdx.x;
     int n = 0;
@@ -2272,6 +2292,49 @@ int orb_buffer_download_rows(OrbContext* c, int32_t id, void* dst, int32_t y0, i
     const size_t row = (size_t)c->W * buffer_elem_bytes(id);
     CK(cudaMemcpyAsync(dst, (const char*)c->buf[id] + row * y0, row * (y1 - y0), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    return ORB_OK;
+}
+
+int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t y0, int32_t y1) {
+    NEED(c && dst && id >= 0 && id < ORB_BUF_COUNT, "orb_buffer_download_rows_async: bad argument");
+    NEED(rows_ok(c, y0, y1), "orb_buffer_download_rows_async: bad row range");
+    CK(cudaSetDevice(c->device));
+    if (!c->copy_stream) CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    const size_t row = (size_t)c->W * buffer_elem_bytes(id), bytes = row * (y1 - y0);
+    OrbContext::DlSlot& sl = c->dl[id][c->dl_next[id]];
+    c->dl_next[id] ^= 1;
+    if (!sl.ready) {
+        CK(cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
+    if (sl.cap < bytes) {
+        CK(cudaStreamSynchronize(c->copy_stream));
+        CK(cudaFree(sl.dev));
+        sl.dev = nullptr, sl.cap = 0;
+        CK(cudaMalloc(&sl.dev, bytes));
+        sl.cap = bytes;
+    } else {
+        CK(cudaStreamWaitEvent(c->stream, sl.done, 0));  // the slot's previous host copy has left it
+    }
+    if (c->dl_snapshot_kernel && bytes % 16 == 0 && (row * y0) % 16 == 0) {
+        const size_t n16 = bytes / 16;
+        k_snapshot<<<(unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)c->n_sm * 8), 256, 0, c->stream>>>(
+            (const uint4*)((const char*)c->buf[id] + row * y0), (uint4*)sl.dev, n16);
+        CK(cudaGetLastError());
+    } else {
+        CK(cudaMemcpyAsync(sl.dev, (const char*)c->buf[id] + row * y0, bytes, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    CK(cudaEventRecord(sl.ready, c->stream));
+    CK(cudaStreamWaitEvent(c->copy_stream, sl.ready, 0));
+    CK(cudaMemcpyAsync(dst, sl.dev, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaEventRecord(sl.done, c->copy_stream));
+    return ORB_OK;
+}
+
+int orb_download_wait(OrbContext* c) {
+    NEED(c, "orb_download_wait: ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    if (c->copy_stream) CK(cudaStreamSynchronize(c->copy_stream));
     return ORB_OK;
 }
 

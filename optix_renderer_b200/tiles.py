@@ -187,6 +187,8 @@ class TiledRenderer:
         self.out = {}      # assemble_async(): name -> whole-frame tensor every rank ends up with
         self._comm = None  # side stream the frame assembly runs on, beside the next frame's kernels
         self._done = None
+        self._copy = None  # stream the assembled frame is read back to the host on (read_back_async)
+        self._read = None
 
     @property
     def band(self):
@@ -307,6 +309,8 @@ class TiledRenderer:
             self._comm = torch.cuda.Stream()
         if self._done is not None:
             cur.wait_event(self._done)  # the previous gather still reads / writes self.out
+        if self._read is not None:
+            cur.wait_event(self._read)  # ... and so does its read-back to the host
         y0, y1 = self.band
         for n in names:
             v = self._t(n)
@@ -322,6 +326,27 @@ class TiledRenderer:
                 assemble(self.out[n], self.bands, self.rank, self.group)
             self._done = torch.cuda.Event()
             self._done.record(self._comm)
+
+    def read_back_async(self, host):
+        """After assemble_async: copy the assembled frame (self.out[name]) to page-locked host tensors
+        `host[name]` on a copy stream, behind the gather and beside the next frame's kernels.  The next
+        assemble_async waits for it on the device before it touches self.out; wait_read_back() blocks the
+        host until the frame has landed."""
+        import torch
+
+        if self._copy is None:
+            self._copy = torch.cuda.Stream()
+        with torch.cuda.stream(self._copy):
+            if self._done is not None:
+                self._copy.wait_event(self._done)
+            for n, t in host.items():
+                t.copy_(self.out[n], non_blocking=True)
+            self._read = torch.cuda.Event()
+            self._read.record(self._copy)
+
+    def wait_read_back(self):
+        if self._read is not None:
+            self._read.synchronize()
 
     def wait_assembled(self):
         if self._done is not None:

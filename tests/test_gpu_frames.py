@@ -447,6 +447,33 @@ def test_deferred_ltc_equals_one_call(renderer_factory):
         a._ck(a.lib.orb_render_finish(a._h, __import__("ctypes").byref(c)))
 
 
+def test_pipelined_download_equals_blocking_download(renderer_factory):
+    """orb_buffer_download_rows_async + orb_download_wait: frame i is read back while frames i+1.. render; each
+    host frame equals a blocking download taken right after the same frame, bit for bit (full frame and a band)."""
+    import torch
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
+    a, b = renderer_factory(sc), renderer_factory(sc)
+    n = 5
+    pin_f = torch.empty((n, 96, 160, 4), dtype=torch.float32, pin_memory=True).numpy()
+    pin_u = torch.empty((n, 96, 160), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+    pin_band = torch.empty((n, 30, 160, 4), dtype=torch.float32, pin_memory=True).numpy()
+    want = []
+    for i in range(n):
+        a.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4)
+        want.append((a.download("accum"), a.download("rgba8"), a.download("sto_direct", rows=(11, 41))))
+        b.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, sync=False)
+        b.download_async("accum", pin_f[i])
+        b.download_async("rgba8", pin_u[i])
+        b.download_async("sto_direct", pin_band[i], rows=(11, 41))
+    b.download_wait()
+    for i in range(n):
+        assert np.array_equal(pin_f[i], want[i][0], equal_nan=True), i
+        assert np.array_equal(pin_u[i], want[i][1]), i
+        assert np.array_equal(pin_band[i], want[i][2], equal_nan=True), i
+    with pytest.raises(api.OrbError):
+        b.download_async("accum", pin_f[0], rows=(5, 500))
+
+
 def test_instrumented_traversal_counts(renderer_factory):
     """ORB_RENDER_COUNT_TRAVERSAL: the instrumented twin of the shadow-ray kernel writes the same frame and
     reports node / triangle fetch counts (bench.py's algorithmic bytes); the TRACE stage timer covers it."""
