@@ -150,6 +150,7 @@ typedef struct OrbCounters {
     uint64_t rays_bounce_total;
     uint64_t active_pixels_total;
     uint64_t bvh_build_us; /* device time of the last orb_scene_commit's hierarchy build (CUDA events) */
+    uint64_t bvh_refit_us; /* device time of the last orb_scene_refit (CUDA events) */
 } OrbCounters;
 
 /* Stages of a frame, for orb_get_stage_times(): one entry per kernel family. */
@@ -198,6 +199,16 @@ int orb_scene_set_lights(OrbContext* ctx, const OrbTriLight* lights, int32_t n);
 int orb_scene_set_ltc_lut(OrbContext* ctx, const float* m1, const float* m2, const float* m3, int32_t w,
                           int32_t h, int32_t quantise_weights);
 int orb_scene_commit(OrbContext* ctx, const OrbBvhOptions* opt); /* builds the BVH on the GPU */
+/* Animated geometry (moving lights or meshes) on a COMMITTED scene.  The reference can only rebuild:
+ * owlTrianglesSetVertices + owlGroupBuildAccel of the GAS and the IAS again, viewer.hpp:494-517.
+ * orb_scene_update_mesh replaces the corner positions and normals of mesh `mesh_index` (the order
+ * of the orb_scene_add_mesh calls); arrays as in OrbMeshDesc, the triangle count must not change.
+ * orb_scene_refit then recomputes the triangle records and every BVH box on the GPU, topology
+ * unchanged; until it ran, orb_render* and orb_trace_rays_host fail with ORB_ERR_INVALID.
+ * TriLights that moved are passed again through orb_scene_set_lights. */
+int orb_scene_update_mesh(OrbContext* ctx, int32_t mesh_index, const float* vertex, const float* normal,
+                          int32_t n_vertices, const int32_t* index, int32_t n_triangles);
+int orb_scene_refit(OrbContext* ctx);
 
 /* ---- camera / frame ---- replaces owlParamsSet3f camera.*, viewer.hpp:647-650, and resize :571-612 */
 int orb_set_camera(OrbContext* ctx, const float pos[3], const float dir_00[3], const float dir_du[3],

@@ -68,7 +68,7 @@ class OrbCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_shadow", "rays_bounce", "kernel_launches",
                                           "nan_pixels", "bvh_nodes", "bvh_triangles", "bvh_height",
                                           "active_pixels", "nodes_visited", "tris_tested",
-                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total", "bvh_build_us")]
+                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total", "bvh_build_us", "bvh_refit_us")]
 
 
 STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "denoise", "combine", "ltc_gbuffer",
@@ -106,6 +106,8 @@ def load_library():
     L.orb_scene_set_lights.argtypes = [vp, _f, C.c_int32]
     L.orb_scene_set_ltc_lut.argtypes = [vp, _f, _f, _f, C.c_int32, C.c_int32, C.c_int32]
     L.orb_scene_commit.argtypes = [vp, C.POINTER(OrbBvhOptions)]
+    L.orb_scene_update_mesh.argtypes = [vp, C.c_int32, _f, _f, C.c_int32, _i, C.c_int32]
+    L.orb_scene_refit.argtypes = [vp]
     L.orb_set_camera.argtypes = [vp, _f, _f, _f, _f]
     L.orb_resize.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_render.argtypes = [vp, C.POINTER(OrbRenderConfig)]
@@ -215,6 +217,17 @@ class Renderer:
         o.max_leaf_tris = int(max_leaf_tris)
         o.builder = int(builder)
         self._ck(self.lib.orb_scene_commit(self._h, C.byref(o)))
+
+    def update_mesh(self, mesh_index, vtx, nrm, idx):
+        """New corner positions / normals for a mesh of the committed scene (same triangle count); call refit()."""
+        vtx, nrm = f32(vtx), f32(nrm)
+        idx = np.ascontiguousarray(idx, np.int32)
+        self._ck(self.lib.orb_scene_update_mesh(self._h, int(mesh_index), _fp(vtx), _fp(nrm), vtx.shape[0],
+                                                idx.ctypes.data_as(_i), idx.shape[0]))
+
+    def refit(self):
+        """Recompute triangle records and BVH boxes on the GPU, topology unchanged (viewer.hpp:506-517 rebuilds)."""
+        self._ck(self.lib.orb_scene_refit(self._h))
 
     def set_camera(self, pos, d00, du, dv):
         a = [f32(x) for x in (pos, d00, du, dv)]

@@ -22,6 +22,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -29,6 +31,7 @@
 #include "bvh_build.cuh"
 #include "bvh_sah.cuh"
 #include "bvh8.cuh"
+#include "bvh_refit.cuh"
 #include "pixel.cuh"
 
 using namespace orb;
@@ -1314,6 +1317,7 @@ struct OrbContext {
     BvhBuildResult bvh;
     SceneView view;
     bool committed = false;
+    bool geometry_dirty = false;  // orb_scene_update_mesh moved corners that orb_scene_refit has not seen yet
     int height = 1;  // stack entries per thread
     // frame
     int W = 0, H = 0;
@@ -1417,6 +1421,7 @@ static void free_scene(OrbContext* c) {
     c->d_meshes = nullptr;
     c->bvh = BvhBuildResult();
     c->committed = false;
+    c->geometry_dirty = false;
 }
 
 static void free_frame(OrbContext* c) {
@@ -1471,9 +1476,21 @@ static bool rows_ok(OrbContext* c, int& y0, int& y1) {
 
 static size_t trace_smem(OrbContext* c) { return (size_t)c->height * TRACE_BLOCK * 8; }
 
+// The attribute belongs to the (kernel, device) pair, not to a context: with two committed contexts on a
+// device, the one with the deeper BVH must keep its allowance, so the limit only ever grows.
 template <class K>
 static cudaError_t allow_smem(K kernel, size_t bytes) {
-    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, size_t> granted;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t& g = granted[std::make_pair((const void*)kernel, dev)];
+    if (bytes <= g) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) g = bytes;
+    return e;
 }
 
 // persistent grid: resident CTAs per SM x SM count
@@ -1804,6 +1821,61 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     return ORB_OK;
 }
 
+// ---- animated geometry: new corners for a mesh of the committed scene, then a refit ----------
+int orb_scene_update_mesh(OrbContext* c, int32_t mesh_index, const float* vertex, const float* normal, int32_t n_vertices,
+                          const int32_t* index, int32_t n_triangles) {
+    NEED(c, "orb_scene_update_mesh: ctx is NULL");
+    NEED(c->committed, "orb_scene_update_mesh: scene not committed");
+    NEED(mesh_index >= 0 && (size_t)mesh_index < c->meshes.size(), "orb_scene_update_mesh: no such mesh");
+    NEED(n_triangles == c->meshes[mesh_index].n_tris,
+         "orb_scene_update_mesh: triangle count differs from the mesh that was added (topology is fixed; rebuild with "
+         "orb_scene_clear + orb_scene_commit)");
+    if (n_triangles == 0) return ORB_OK;
+    NEED(vertex && normal && index && n_vertices > 0, "orb_scene_update_mesh: NULL array");
+    size_t base = 0;
+    for (int m = 0; m < mesh_index; m++) base += (size_t)c->meshes[m].n_tris;
+    std::vector<float> pos(9 * (size_t)n_triangles), nrm(9 * (size_t)n_triangles);
+    for (int t = 0; t < n_triangles; t++)
+        for (int k = 0; k < 3; k++) {
+            const int vi = index[3 * t + k];
+            NEED(vi >= 0 && vi < n_vertices, "orb_scene_update_mesh: index out of range");
+            for (int a = 0; a < 3; a++) {
+                pos[9 * (size_t)t + 3 * k + a] = vertex[3 * (size_t)vi + a];
+                nrm[9 * (size_t)t + 3 * k + a] = normal[3 * (size_t)vi + a];
+            }
+        }
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));  // frames in flight still read the old corners
+    c->geometry_dirty = true;
+    CK(cudaMemcpy(c->d_pos + 9 * base, pos.data(), 4 * pos.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->d_nrm + 9 * base, nrm.data(), 4 * nrm.size(), cudaMemcpyHostToDevice));
+    return ORB_OK;
+}
+
+int orb_scene_refit(OrbContext* c) {
+    NEED(c, "orb_scene_refit: ctx is NULL");
+    NEED(c->committed, "orb_scene_refit: scene not committed");
+    NEED(!(c->trace_variant == 2 && c->bvh8_nodes),
+         "orb_scene_refit: the compressed 8-wide BVH (ORB_TRACE_VARIANT=2) has no refit; rebuild the scene");
+    CK(cudaSetDevice(c->device));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, c->stream));
+    const int before = c->bvh.launches;
+    CK(refit_bvh(c->d_pos, (int)c->h_prim_mesh.size(), c->stream, c->bvh));
+    CK(cudaEventRecord(e1, c->stream));
+    CK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    c->counters.bvh_refit_us = (uint64_t)(ms * 1000.f);
+    c->counters.kernel_launches += (uint64_t)(c->bvh.launches - before);
+    c->geometry_dirty = false;
+    return ORB_OK;
+}
+
 // ---- camera / frame --------------------------------------------------------------------------
 int orb_set_camera(OrbContext* c, const float pos[3], const float d00[3], const float du[3], const float dv[3]) {
     NEED(c && pos && d00 && du && dv, "orb_set_camera: NULL argument");
@@ -1915,6 +1987,7 @@ static int ensure_path_state(OrbContext* c) {
 int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     NEED(c && cfg, "orb_render: NULL argument");
     NEED(c->committed, "orb_render: scene not committed");
+    NEED(!c->geometry_dirty, "orb_render: orb_scene_update_mesh without orb_scene_refit (the BVH is stale)");
     NEED(c->W > 0, "orb_render: orb_resize first");
     NEED(c->have_cam, "orb_render: orb_set_camera first");
     NEED(c->lut_w > 0 || (cfg->renderer_type != ORB_LTC_BASELINE && cfg->renderer_type != ORB_RATIO),
@@ -2392,6 +2465,7 @@ int orb_trace_rays_host(OrbContext* c, const float* origin, const float* directi
                         int32_t* prim, float* t, float* u, float* v) {
     NEED(c && origin && direction && prim && t && u && v, "orb_trace_rays_host: NULL argument");
     NEED(c->committed, "orb_trace_rays_host: scene not committed");
+    NEED(!c->geometry_dirty, "orb_trace_rays_host: orb_scene_update_mesh without orb_scene_refit (the BVH is stale)");
     if (n == 0) return ORB_OK;
     CK(cudaSetDevice(c->device));
     float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr;
