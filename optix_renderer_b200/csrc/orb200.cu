@@ -372,7 +372,7 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
 // order; it only delays the pruning by best.t a little.  Against the batching form above this
 // keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
 // triangle test).
-template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, bool QSTACK = false>
+template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, int QSTACK = 0>  // QSTACK 1: q forms, 2: p forms (scene.cuh)
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
@@ -443,14 +443,16 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
         for (int it = 0; it < 64; ++it) {
             if (COUNT && t.cur >= 0) ++c_nodes;
             if (QSTACK) {
-                if (t.cur >= 0) trav_node_step_q(t, s, q_stk);
+                if (QSTACK == 2) {
+                    if (t.cur >= 0) trav_node_step_p(t, s, q_stk);
+                } else if (t.cur >= 0) trav_node_step_q(t, s, q_stk);
             } else {
                 if (t.cur >= 0) trav_node_step<SKIP>(t, s, stk, stk_t, stride);
                 else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
             if (leaf == 0 && t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // postpone this leaf, keep walking
                 leaf = t.cur;
-                t.cur = QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = QSTACK == 2 ? p_pop(t, q_stk) : QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
             if ((int)__popc(__ballot_sync(FULL, t.cur >= 0 || t.cur == ORB_TRAVERSAL_POP)) < node_min) break;
         }
@@ -460,7 +462,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             leaf = 0;
             if (t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
-                t.cur = QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = QSTACK == 2 ? p_pop(t, q_stk) : QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
         }
     }
@@ -1953,7 +1955,8 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
         if (c->pop_skip == 1) k = k_trace_stream_spec<true, false, 1>;
         if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
         if (c->pop_skip == 4) k = k_trace_stream_spec<true, false, 4>;
-        if (c->q_stack) k = k_trace_stream_spec<true, false, 0, true>;
+        if (c->q_stack == 1) k = k_trace_stream_spec<true, false, 0, 1>;
+        if (c->q_stack == 2) k = k_trace_stream_spec<true, false, 0, 2>;
         int g = persistent_grid(c, k, TRACE_BLOCK, 0);
         // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
         // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.

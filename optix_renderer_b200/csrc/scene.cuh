@@ -248,6 +248,52 @@ ORB_HD int q_pop(TravState& t, const unsigned long long* stk) {
     }
 }
 
+// ---- "p" forms: the same 64-bit entries, all of them in memory (no register-held top): one STL.64 per push
+// and one LDL.64 per pop instead of two 32-bit accesses each -- the stack shares the L1 data pipe with the
+// node fetches, and with divergent stack depths every access of a lane is its own L1 wavefront.
+ORB_HD int p_pop(TravState& t, const unsigned long long* stk) {
+    for (;;) {
+        if (t.sp == 0) return ORB_TRAVERSAL_DONE;
+        const unsigned long long e = stk[--t.sp];
+        const float tn = __int_as_float_hd((int)(unsigned)(e >> 32));
+        if (t.best.prim < 0 || !(tn > t.best.t)) return (int)(unsigned)(e & 0xffffffffull);
+    }
+}
+
+ORB_HD void trav_node_step_p(TravState& t, const SceneView& s, unsigned long long* stk) {
+    const BvhNode* np = s.nodes + t.cur;
+#ifdef __CUDA_ARCH__
+    float4 na, nb, nc;
+    int c0, c1, pad0, pad1;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(na.x), "=f"(na.y), "=f"(na.z), "=f"(na.w), "=f"(nb.x), "=f"(nb.y), "=f"(nb.z), "=f"(nb.w)
+        : "l"(np));
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
+        : "l"(reinterpret_cast<const char*>(np) + 32));
+    (void)pad0;
+    (void)pad1;
+#else
+    const float4 na = np->a, nb = np->b, nc = np->c;
+    const int c0 = np->c0, c1 = np->c1;
+#endif
+    const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
+    float tn0, tn1;
+    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
+    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
+    if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        stk[t.sp++] = q_pack(swap ? c0 : c1, swap ? tn0 : tn1);
+        t.cur = swap ? c1 : c0;
+    } else if (h0) {
+        t.cur = c0;
+    } else if (h1) {
+        t.cur = c1;
+    } else {
+        t.cur = p_pop(t, stk);
+    }
+}
+
 ORB_HD void trav_node_step_q(TravState& t, const SceneView& s, unsigned long long* stk) {
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
