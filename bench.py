@@ -383,6 +383,25 @@ def run_ours(args):
                 rows_bad = torch.nonzero(px_bad.any(dim=1)).flatten().tolist()
                 print("bench.py: assembled frame differs from the single-GPU frame in %d pixels, rows %s ... %s; bands %s" %
                       (int(px_bad.sum()), rows_bad[:12], rows_bad[-12:], T.bands), file=sys.stderr)
+        if (not ratio) and world > 1:
+            # parity of the partitioned PATH job: frame accumId = 0 (accum = that frame's colour, no history, so the
+            # band cuts that moved during warm-up do not matter) rendered in N bands and gathered in place, against
+            # the same frame rendered whole by rank 0 -- bit for bit, outside every timed region
+            T.wait_assembled()
+            render(0)
+            T.assemble(out_names)
+            torch.cuda.synchronize()
+            if rank == 0:
+                got = tiles.device_tensor(r, "accum").clone()
+                r.render(api.PATH, accum_id=0, mode=api.INTENDED, max_depth=DEPTH, count_rays=False)
+                torch.cuda.synchronize()
+                want = tiles.device_tensor(r, "accum")
+                px_bad = (got.view(torch.int32) != want.view(torch.int32)).any(dim=2)
+                same = not bool(px_bad.any())
+                if not same:
+                    print("bench.py: assembled PATH frame differs from the single-GPU frame in %d pixels; bands %s" %
+                          (int(px_bad.sum()), T.bands), file=sys.stderr)
+            barrier()
         trav, one_quad = None, None
         if ratio and world == 1:
             # BASELINE's "HBM GB/s fraction on the LTC pass": the stand-alone LTC pass over the resident G-buffer
