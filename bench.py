@@ -315,6 +315,12 @@ def run_ours(args):
         t_u32 = torch.empty((2, H, W), dtype=torch.int32, pin_memory=True)       # while the next one lands
         host_f4, host_u32 = t_f4.numpy(), t_u32.numpy().view(np.uint32)
         e_steps = max(3, min(args.steps, 30))
+        # N > 1: every rank copies ITS band into one page-locked host frame shared by the ranks of the box (each
+        # over its own PCIe link) instead of rank 0 reading the whole assembled frame back alone
+        HOST_GATHER = world > 1 and not SYNC_ASSEMBLE and not SYNC_DOWNLOAD and os.environ.get("ORB_BENCH_HOST_GATHER", "1") == "1"
+        shared = None
+        if HOST_GATHER:
+            shared = tiles.SharedHostFrames(rank, world, {out_names[0]: ((H, W, 4), np.float32), "rgba8": ((H, W), np.uint32)})
 
         def e2e_loop(pipelined, id0, n):
             barrier()
@@ -329,6 +335,8 @@ def run_ours(args):
                 elif rank == 0 and world == 1:
                     r.download(out_names[0], rows=(y0, y1), out=host_f4[i & 1])  # synchronises every frame
                     r.download("rgba8", rows=(y0, y1), out=host_u32[i & 1])
+                elif HOST_GATHER:
+                    T.read_back_bands_async(shared, i & 1, out_names)
                 elif rank == 0 and not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:
                     # the assembled frame lives in T.out: read back behind the gather, beside the next frame
                     T.read_back_async({out_names[0]: t_f4[i & 1], "rgba8": t_u32[i & 1]})
@@ -337,7 +345,11 @@ def run_ours(args):
                     t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
                     t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
                     torch.cuda.current_stream().synchronize()
-            if world > 1 and rank == 0:
+            if HOST_GATHER:
+                T.wait_assembled()
+                torch.cuda.current_stream().synchronize()
+                T.wait_read_back_bands()  # every band of the last frame is on the host when the clock stops
+            elif world > 1 and rank == 0:
                 T.wait_assembled()
                 torch.cuda.current_stream().synchronize()
                 T.wait_read_back()  # the last frame is on the host when the clock stops
@@ -350,8 +362,8 @@ def run_ours(args):
 
         PIPE = world == 1 and not SYNC_DOWNLOAD
         serial_ms = e2e_loop(False, base_id + args.steps, e_steps) if PIPE else None
-        if PIPE:
-            e2e_loop(True, base_id + args.steps, 3)  # untimed: the read-back slots are allocated on first use
+        if PIPE or HOST_GATHER:
+            e2e_loop(PIPE, base_id + args.steps, 3)  # untimed: the read-back slots are allocated on first use
         e_ms = e2e_loop(PIPE, base_id + args.steps + (e_steps if PIPE else 0), e_steps)
         # the frame that arrived through the pipelined read-back is the frame the device holds
         readback_ok = bool(np.array_equal(host_f4[(e_steps - 1) & 1], r.download(out_names[0]), equal_nan=True)) if PIPE else None
@@ -364,7 +376,9 @@ def run_ours(args):
             # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
             T.wait_assembled()
             got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
-            if not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:  # the frame as the host received it through the pipelined read-back
+            if HOST_GATHER:  # the frame as the host received it: N bands, each copied by its own rank
+                got = torch.from_numpy(np.array(shared[out_names[0]][(e_steps - 1) & 1])).to("cuda")
+            elif not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:  # the frame as the host received it through the pipelined read-back
                 got = t_f4[(e_steps - 1) & 1].to("cuda")
             last = base_id + args.steps + e_steps - 1
             r.render(api.RATIO, accum_id=last, mode=api.INTENDED, shadow_spp=SPP, count_rays=False)
@@ -488,6 +502,10 @@ def run_ours(args):
                                 % ("orb_buffer_download_rows_async (read-back of frame i overlaps the kernels of frame i+1; "
                                    "orb_download_wait inside the timed region)" if PIPE else
                                    "orb_buffer_download_rows" if world == 1 else
+                                   "every rank's orb_buffer_download_rows_async of ITS band into one page-locked host "
+                                   "frame shared by the ranks of the box (tiles.SharedHostFrames; the device all-gather of "
+                                   "the frame runs beside it as in the device-timed loop; orb_download_wait on every rank "
+                                   "and a barrier inside the timed region)" if HOST_GATHER else
                                    "rank 0's copy of the assembled frame" + ("" if SYNC_ASSEMBLE or SYNC_DOWNLOAD else
                                    " on a copy stream, behind the all-gather and beside the next frame's kernels; the "
                                    "last copy is waited for inside the timed region"))},
@@ -498,6 +516,7 @@ def run_ours(args):
         if one_quad:
             line["ltc_pass_one_quad"] = line_ltc
         if world > 1:
+            line["e2e"]["host_gather"] = bool(HOST_GATHER)
             line["config"]["bands"] = [list(b) for b in T.bands]
             line["assembled_frame_equals_single_gpu_frame"] = same
             line["rank_kernel_ms_per_frame"] = rank_ms

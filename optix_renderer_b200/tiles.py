@@ -18,6 +18,8 @@ Collectives (NCCL over NVLink on the GPU box; gloo in the CPU tests):
   * frame assembly: one all-gather of each rank's finished band per output buffer.
 Bands are uneven, so the gathers are lists of per-rank row views of the destination buffer.
 """
+import os
+
 import numpy as np
 
 ACTIVE_PIXEL_COST = 10.0  # cost of an active pixel relative to a primary ray (bench scene: 2.0 ns vs 0.19 ns)
@@ -168,6 +170,63 @@ def exchange_halos(tensors, bands, rank, iterations, group=None):
         return
     for w in dist.batch_isend_irecv(ops):
         w.wait()
+
+
+class SharedHostFrames:
+    """Whole-frame host buffers shared by the ranks of one box: a /dev/shm file that every rank maps and
+    page-locks (cudaHostRegister).  Every rank then copies ITS band of a finished frame straight into the
+    frame over its own PCIe link (TiledRenderer.read_back_bands_async), instead of rank 0 reading the whole
+    assembled frame back alone: the host frame is complete after wait_read_back_bands().  The device-side
+    all-gather stays what puts the whole frame on every GPU; this is the host's copy of it.
+
+    spec: name -> (per-frame shape, numpy dtype); `slots` frames per name (a consumer reads one slot while
+    the next frame lands in the other).  pin=False maps without CUDA (CPU tests)."""
+
+    def __init__(self, rank, world_size, spec, slots=2, group=None, pin=True):
+        import torch.distributed as dist
+
+        self.rank, self.world, self.group = rank, world_size, group
+        self._pinned = []
+        sizes = {n: int(slots * np.prod(shape) * np.dtype(dt).itemsize) for n, (shape, dt) in spec.items()}
+        total = sum((b + 4095) // 4096 * 4096 for b in sizes.values())
+        box = [None]
+        if rank == 0:
+            box[0] = "/dev/shm/orb200_frames_%d_%x" % (os.getpid(), id(self) & 0xffffff)
+            with open(box[0], "wb") as fh:
+                fh.truncate(max(total, 4096))
+        if world_size > 1:
+            dist.broadcast_object_list(box, src=0, group=group)
+        self.path = box[0]
+        self._map = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(max(total, 4096),))
+        if world_size > 1:
+            dist.barrier(group=group)  # every rank holds its mapping: the name can go
+        if rank == 0:
+            os.unlink(self.path)
+        self.frames = {}
+        ofs = 0
+        for n, (shape, dt) in spec.items():
+            b = sizes[n]
+            self.frames[n] = self._map[ofs:ofs + b].view(dt).reshape((slots,) + tuple(shape))
+            ofs += (b + 4095) // 4096 * 4096
+        if pin:
+            import torch
+
+            rt = torch.cuda.cudart()
+            err = rt.cudaHostRegister(self._map.ctypes.data, self._map.nbytes, 0)
+            if int(err) != 0:
+                raise RuntimeError("cudaHostRegister of the shared host frames failed: %s" % (err,))
+            self._pinned.append(self._map.ctypes.data)
+
+    def __getitem__(self, name):
+        return self.frames[name]
+
+    def close(self):
+        if self._pinned:
+            import torch
+
+            for p in self._pinned:
+                torch.cuda.cudart().cudaHostUnregister(p)
+            self._pinned = []
 
 
 class TiledRenderer:
@@ -343,6 +402,24 @@ class TiledRenderer:
                 t.copy_(self.out[n], non_blocking=True)
             self._read = torch.cuda.Event()
             self._read.record(self._copy)
+
+    def read_back_bands_async(self, shared, slot, names):
+        """This rank's rows of the finished buffers `names` into the box-wide host frames `shared`
+        (SharedHostFrames), through the C-ABI's pipelined read-back (orb_buffer_download_rows_async: a device
+        snapshot on the render stream, the PCIe copy on the context's copy stream beside the next frame)."""
+        y0, y1 = self.band
+        if y1 <= y0:
+            return
+        for n in names:
+            self.r.download_async(n, shared[n][slot][y0:y1], rows=(y0, y1))
+
+    def wait_read_back_bands(self):
+        """Blocks until every rank's band has landed: the shared host frames are whole on return."""
+        self.r.download_wait()
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.barrier(group=self.group)
 
     def wait_read_back(self):
         if self._read is not None:

@@ -164,3 +164,41 @@ def test_halo_exchange_over_gloo(tmp_path, world, H, iters):
         assert np.array_equal(g["a"][lo:hi, 0, 0], rows[lo:hi])       # band + halo present
         assert np.array_equal(g["b"][lo:hi, 2, 1], rows[lo:hi] * 2)
         assert (g["a"][:lo] == -1).all() and (g["a"][hi:] == -1).all()  # nothing else was sent
+
+
+def _shared_worker(rank, world, port, W, H, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sh = tiles.SharedHostFrames(rank, world, {"ratio_final": ((H, W, 4), np.float32), "rgba8": ((H, W), np.uint32)},
+                                    pin=False)
+        bands = tiles.balanced_bands(np.arange(H) % 3 + 1.0, world)
+        y0, y1 = bands[rank]
+        for slot in (0, 1):
+            # what TiledRenderer.read_back_bands_async does through the C-ABI: this rank's rows, nobody else's
+            sh["ratio_final"][slot][y0:y1] = _pattern(H, W, slot)[y0:y1]
+            sh["rgba8"][slot][y0:y1] = (_pattern(H, W, slot)[..., 0] * 7).astype(np.uint32)[y0:y1]
+        dist.barrier()
+        if rank == 0:
+            assert not os.path.exists(sh.path)  # unlinked once every rank had mapped it
+            np.savez(os.path.join(out_dir, "shared.npz"), f=np.array(sh["ratio_final"]), g=np.array(sh["rgba8"]))
+        dist.barrier()
+        sh.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def _pattern(H, W, slot):
+    return (np.arange(H * W * 4, dtype=np.float32).reshape(H, W, 4) + 1000.0 * slot)
+
+
+@pytest.mark.parametrize("world,W,H", [(2, 16, 24), (3, 8, 10)])
+def test_shared_host_frames_over_gloo(tmp_path, world, W, H):
+    """N > 1 end-to-end read-back: every rank writes ITS band into one host frame mapped by all ranks of the box;
+    the frame rank 0 reads afterwards is whole, in both slots."""
+    mp.spawn(_shared_worker, args=(world, _free_port(), W, H, str(tmp_path)), nprocs=world, join=True)
+    got = np.load(os.path.join(str(tmp_path), "shared.npz"))
+    for slot in (0, 1):
+        assert np.array_equal(got["f"][slot], _pattern(H, W, slot))
+        assert np.array_equal(got["g"][slot], (_pattern(H, W, slot)[..., 0] * 7).astype(np.uint32))
