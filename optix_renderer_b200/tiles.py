@@ -191,12 +191,16 @@ class SharedHostFrames:
         total = sum((b + 4095) // 4096 * 4096 for b in sizes.values())
         box = [None]
         if rank == 0:
-            box[0] = "/dev/shm/orb200_frames_%d_%x" % (os.getpid(), id(self) & 0xffffff)
-            with open(box[0], "wb") as fh:
-                fh.truncate(max(total, 4096))
+            vfs = os.statvfs("/dev/shm")
+            if vfs.f_bavail * vfs.f_frsize >= total + (64 << 20):  # a short tmpfs would end in SIGBUS on first touch
+                box[0] = "/dev/shm/orb200_frames_%d_%x" % (os.getpid(), id(self) & 0xffffff)
+                with open(box[0], "wb") as fh:
+                    fh.truncate(max(total, 4096))
         if world_size > 1:
             dist.broadcast_object_list(box, src=0, group=group)
         self.path = box[0]
+        if self.path is None:  # the same answer on every rank
+            raise RuntimeError("SharedHostFrames: /dev/shm has less than %d MB free" % ((total >> 20) + 64))
         self._map = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(max(total, 4096),))
         if world_size > 1:
             dist.barrier(group=group)  # every rank holds its mapping: the name can go
@@ -212,10 +216,17 @@ class SharedHostFrames:
             import torch
 
             rt = torch.cuda.cudart()
-            err = rt.cudaHostRegister(self._map.ctypes.data, self._map.nbytes, 0)
-            if int(err) != 0:
-                raise RuntimeError("cudaHostRegister of the shared host frames failed: %s" % (err,))
-            self._pinned.append(self._map.ctypes.data)
+            err = int(rt.cudaHostRegister(self._map.ctypes.data, self._map.nbytes, 0))
+            if err == 0:
+                self._pinned.append(self._map.ctypes.data)
+            oks = [err == 0]
+            if world_size > 1:  # every rank pins or none does: the callers' fallback must be the same everywhere
+                oks = [None] * world_size
+                dist.all_gather_object(oks, err == 0, group=group)
+            if not all(oks):
+                self.close()
+                raise RuntimeError("SharedHostFrames: cudaHostRegister failed on ranks %s" %
+                                   [i for i, ok in enumerate(oks) if not ok])
 
     def __getitem__(self, name):
         return self.frames[name]
