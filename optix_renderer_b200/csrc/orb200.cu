@@ -12,6 +12,7 @@
 //   k_accumulate     colour + running sum -> accum, RGBA8, NaN count
 //   k_denoise_*      edge-avoiding a-trous on the packed (direct, no_vis) image
 //   k_ratio_combine  ltc * (direct / no_vis)
+//   k_refit_*        (bvh_refit.cuh) triangle records and BVH boxes after geometry moved, topology kept
 //
 // Queue kernels are persistent (grid = SMs x resident CTAs, grid-stride over a DEVICE-side
 // count), so a frame needs no host synchronisation.  No kernel is a dense contraction: there
