@@ -114,6 +114,21 @@ struct HostTracer {
             w8.tri = G.tri8.data();
             return trace_closest_wide(w8, G.view.n_tris, o, d, ws, 1);
         }
+        if (brute == 3 || brute == 4) {  // the 64-bit stack forms of the ray-stream kernel (ORB_Q_STACK = 1 / 2)
+            unsigned long long qs[128];
+            TravState t;
+            trav_begin(t, G.view, o, d);
+            while (t.cur != ORB_TRAVERSAL_DONE) {
+                if (t.cur >= 0) {
+                    if (brute == 3) trav_node_step_q(t, G.view, qs);
+                    else trav_node_step_p(t, G.view, qs);
+                } else {
+                    trav_leaf_test(t, G.view, t.cur);
+                    t.cur = brute == 3 ? q_pop(t, qs) : p_pop(t, qs);
+                }
+            }
+            return t.best;
+        }
         int stk[128];
         float stk_t[128];
         return trace_closest(G.view, o, d, stk, stk_t, 1);

@@ -110,6 +110,10 @@ def test_bvh_traversal_equals_brute_force(hostcheck):
     p2, t2, u2, v2 = hostcheck.trace(org, d, brute=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
     assert (p1 >= 0).mean() > 0.2
+    # the 64-bit stack forms of the stream kernel (scene.cuh q / p forms: ORB_Q_STACK = 1 / 2) walk to the same hits
+    for form in (3, 4):
+        pq, tq, uq, vq = hostcheck.trace(org, d, brute=form)
+        assert np.array_equal(pq, p2) and np.array_equal(tq, t2) and np.array_equal(uq, u2) and np.array_equal(vq, v2)
     # the compressed 8-wide BVH (bvh8.cuh: collapse + traversal) finds the same hits, bit for bit
     nn, hh = hostcheck.wide_info()
     assert nn > 100 and 2 <= hh <= 32
