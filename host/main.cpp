@@ -42,6 +42,8 @@ static void usage() {
             "  --exr                every .btc dump also as NAME.exr (what the reference's save.py produces)\n"
             "  --save-state FILE    write the accumulation checkpoint (accum buffer + frame count) after the last frame\n"
             "  --resume FILE        start from such a checkpoint: accumId continues where it stopped\n"
+            "  --move-lights X,Y,Z  translate every area light by (X,Y,Z) AFTER the scene was committed: the light meshes go\n"
+            "                       through orb_scene_update_mesh + orb_scene_refit (no rebuild), the TriLights are set again\n"
             "  --exact-lut          fetch the table with exact fp32 bilinear weights instead of the texture unit's\n"
             "                       1/256 weights (the reference reads it through tex2D, viewer.hpp:321-327)\n"
             "  --device D           CUDA device (default 0)\n"
@@ -219,6 +221,8 @@ int main(int argc, char** argv) {
     int frames = -1, W = 0, H = 0, cam_i = 0, shadow_spp = 4, depth = 8, device = 0;
     bool denoise = false, only_dump = false;
     std::string save_state_path, resume_path;
+    float move_lights[3] = {0.f, 0.f, 0.f};
+    bool have_move = false;
     int lut_quantise = 1;  // the texture unit's weight rule (measured on the B200, profiles/r1n_texture_unit.json)
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
@@ -245,6 +249,10 @@ int main(int argc, char** argv) {
         else if (a == "--exr") g_write_exr = true;
         else if (a == "--save-state") save_state_path = next("--save-state");
         else if (a == "--resume") resume_path = next("--resume");
+        else if (a == "--move-lights") {
+            if (sscanf(next("--move-lights"), "%f,%f,%f", &move_lights[0], &move_lights[1], &move_lights[2]) != 3) { usage(); return 1; }
+            have_move = true;
+        }
         else if (a == "--selftest-exr") {  // writes a known image: tests/test_host.py reads it back
             const char* path = next("--selftest-exr");
             const int w = 7, h = 5;
@@ -321,6 +329,21 @@ int main(int argc, char** argv) {
     ORB_CHECK(orb_scene_commit(ctx, nullptr));
     ORB_CHECK(orb_sync(ctx));
     const double build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build0).count();
+    if (have_move) {  // animated lights: the reference would rebuild both acceleration structures (viewer.hpp:494-517)
+        const auto t_refit0 = std::chrono::steady_clock::now();
+        for (size_t k = 0; k < scene.meshes.size(); k++) {
+            Mesh& m = scene.meshes[k];
+            if (!m.is_light) continue;
+            for (size_t i = 0; i < m.vertex.size(); i++) m.vertex[i] += move_lights[i % 3];
+            ORB_CHECK(orb_scene_update_mesh(ctx, (int32_t)k, m.vertex.data(), m.normal.data(), (int32_t)(m.vertex.size() / 3),
+                                            m.index.data(), (int32_t)(m.index.size() / 3)));
+        }
+        ORB_CHECK(orb_scene_refit(ctx));
+        const std::vector<OrbTriLight> moved = build_tri_lights(scene);
+        ORB_CHECK(orb_scene_set_lights(ctx, moved.data(), (int32_t)moved.size()));
+        fprintf(stderr, "lights moved by (%g, %g, %g): update + refit %.2f ms\n", move_lights[0], move_lights[1], move_lights[2],
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_refit0).count());
+    }
     ORB_CHECK(orb_resize(ctx, W, H));
     g_W = W;
     g_H = H;

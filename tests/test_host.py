@@ -229,3 +229,38 @@ def test_host_dumps_equal_binding(host, tmp_path, renderer, frames):
             final = ltc * (sd / sn)
         assert np.array_equal(final, np.flipud(btc("final_ratio_estimator"))[..., :3], equal_nan=True)
     r.close()
+
+
+@pytest.mark.gpu
+def test_host_move_lights_goes_through_refit(host, tmp_path):
+    """--move-lights: the host moves the light meshes of the COMMITTED scene (orb_scene_update_mesh +
+    orb_scene_refit + orb_scene_set_lights, no rebuild).  Its dumps equal, bit for bit, those of a scene that was
+    built with the lights already there."""
+    import copy
+
+    from optix_renderer_b200 import api
+
+    sc = scenes.scene_cornell(96, 64)
+    path = scenes.export_scene(sc, str(tmp_path))
+    out = tmp_path / "saves"
+    o = subprocess.run([host, path, "--out", str(out), "--renderer", "ratio", "--frames", "2", "--move-lights",
+                        "0.125,-0.25,0.0625"], capture_output=True, text=True)
+    assert o.returncode == 0, o.stderr
+    assert "update + refit" in o.stderr
+    mv = copy.deepcopy(sc)
+    for m in mv["meshes"]:
+        if m["is_light"]:
+            m["vtx"] = (m["vtx"] + np.array([0.125, -0.25, 0.0625], np.float32)).astype(np.float32)
+    mv["tri_lights"] = scenes.make_tri_lights(mv["meshes"])
+    r = api.Renderer(mv, quantise_lut=1)
+    for f in range(2):
+        r.render(api.RATIO, accum_id=f, mode=api.INTENDED, shadow_spp=4)
+    for fname, buf in (("stoDirect", "sto_direct"), ("stoNoVis", "sto_no_vis"), ("ltc", "ltc"),
+                       ("normal_screen_buffer", "normal"), ("materialID_screen_buffer", "materialID")):
+        got = np.fromfile(str(out / (fname + ".btc")), np.float32).reshape(64, 96, 4)
+        assert np.array_equal(got, r.download(buf), equal_nan=True), fname
+    still = api.Renderer(sc, quantise_lut=1)
+    still.render(api.RATIO, accum_id=1, mode=api.INTENDED, shadow_spp=4)
+    assert not np.array_equal(still.download("ltc"), r.download("ltc"), equal_nan=True)  # the lights did move
+    still.close()
+    r.close()
