@@ -51,6 +51,8 @@ class HostCheck:
         L.hc_commit.argtypes = [C.c_int]
         L.hc_set_camera.argtypes = [_f, _f, _f, _f]
         L.hc_trace.argtypes = [_f, _f, C.c_int, C.c_int, _i, _f, _f, _f]
+        L.hc_trace_counted.argtypes = [_f, _f, C.c_int, C.c_int, _i, _f, _f, _f, C.POINTER(C.c_ulonglong),
+                                       C.POINTER(C.c_ulonglong)]
         L.hc_render.argtypes = [C.c_int] * 7 + [C.POINTER(HcBuffers)]
         L.hc_render.restype = C.c_longlong
         L.hc_ltc_gbuffer.argtypes = [C.c_int, _f, _f, _f, _f, _f, _f]
@@ -127,6 +129,17 @@ class HostCheck:
         t, u, v = (np.zeros(n, np.float32) for _ in range(3))
         self.lib.hc_trace(_fp(org), _fp(dirs), n, int(brute), prim.ctypes.data_as(_i), _fp(t), _fp(u), _fp(v))
         return prim, t, u, v
+
+    def trace_counted(self, org, dirs, mode=0):
+        """(prim, t, u, v), node records fetched, triangles tested; mode 0 = fp32 nodes, 5 = 32-byte quantised nodes."""
+        org, dirs = f32(org).reshape(-1, 3), f32(dirs).reshape(-1, 3)
+        n = org.shape[0]
+        prim = np.zeros(n, np.int32)
+        t, u, v = (np.zeros(n, np.float32) for _ in range(3))
+        nn, nt = C.c_ulonglong(), C.c_ulonglong()
+        self.lib.hc_trace_counted(_fp(org), _fp(dirs), n, int(mode), prim.ctypes.data_as(_i), _fp(t), _fp(u), _fp(v),
+                                  C.byref(nn), C.byref(nt))
+        return (prim, t, u, v), nn.value, nt.value
 
     def ltc_gbuffer(self, position, normal, albedo, alpha, cam_pos):
         position, normal, albedo, alpha = f32(position), f32(normal), f32(albedo), f32(alpha)

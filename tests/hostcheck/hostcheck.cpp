@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../optix_renderer_b200/csrc/bvh8.cuh"
+#include "../../optix_renderer_b200/csrc/bvhq.cuh"
 #include "../../optix_renderer_b200/csrc/pixel.cuh"
 
 using namespace orb;
@@ -31,6 +32,8 @@ struct State {
     int root_ref = 0;
     Bvh8Host wide;             // collapsed from a second BVH2 with leaves of <= 3 triangles
     std::vector<float4> tri8;
+    std::vector<QNode> qnodes;  // bvhq.cuh: the same hierarchy on the 16-bit grid
+    QGrid qgrid;
     int wide_ok = 0;
     Camera cam;
     SceneView view;
@@ -103,6 +106,7 @@ void refresh() {
 
 struct HostTracer {
     mutable long long rays = 0;
+    mutable unsigned long long nodes = 0, tris = 0;  // modes 0 and 5: node records fetched / triangles tested
     int brute = 0;
     Hit operator()(float3 o, float3 d) const {
         rays++;
@@ -131,7 +135,15 @@ struct HostTracer {
         }
         int stk[128];
         float stk_t[128];
-        return trace_closest(G.view, o, d, stk, stk_t, 1);
+        unsigned nn = 0, nt = 0;
+        Hit h;
+        if (brute == 5 && G.root_ref >= 0 && !G.qnodes.empty())  // 32-byte quantised nodes (a leaf root has no nodes at all)
+            h = trace_closest_q(G.view, G.qnodes.data(), G.qgrid, o, d, stk, stk_t, 1, &nn, &nt);
+        else
+            h = trace_closest(G.view, o, d, stk, stk_t, 1, &nn, &nt);
+        nodes += nn;
+        tris += nt;
+        return h;
     }
 };
 }  // namespace
@@ -209,6 +221,12 @@ void hc_commit(int max_leaf) {
         G.tri[3 * (size_t)k + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.f);
         G.tri[3 * (size_t)k + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.f);
     }
+    G.qnodes.clear();
+    if (n && G.root_ref >= 0 && !G.nodes.empty()) {
+        G.qgrid = qgrid_from_root(G.nodes[G.root_ref]);
+        G.qnodes.resize(G.nodes.size());
+        for (size_t i = 0; i < G.nodes.size(); i++) G.qnodes[i] = q_encode(G.nodes[i], G.qgrid);
+    }
     // the wide BVH: a second BVH2 with leaves of <= 3 triangles, collapsed by the product's bvh8_collapse()
     G.wide_ok = 0;
     if (n) {
@@ -255,6 +273,22 @@ void hc_trace(const float* org, const float* dir, int n, int brute, int32_t* pri
         u[i] = h.u;
         v[i] = h.v;
     }
+}
+
+// hc_trace plus the traversal's fetch counts (modes 0 and 5)
+void hc_trace_counted(const float* org, const float* dir, int n, int mode, int32_t* prim, float* t, float* u, float* v,
+                      unsigned long long* nodes, unsigned long long* tris) {
+    HostTracer tr;
+    tr.brute = mode;
+    for (int i = 0; i < n; i++) {
+        const Hit h = tr(v3(org[3 * i], org[3 * i + 1], org[3 * i + 2]), v3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]));
+        prim[i] = h.prim;
+        t[i] = h.t;
+        u[i] = h.u;
+        v[i] = h.v;
+    }
+    *nodes = tr.nodes;
+    *tris = tr.tris;
 }
 
 // Same buffer set and order as OraBuffers (oracle/oracle_api.h).

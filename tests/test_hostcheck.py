@@ -144,3 +144,37 @@ def test_ltc_gbuffer_pass(hostcheck, restatement):
     out = hostcheck.ltc_gbuffer(g["position"], g["normal"], g["albedo"], g["alpha"], g["cam"])
     e = P.rel_err(out, g["ltc_gbuffer"])
     assert e.max() <= 1e-4
+
+
+@pytest.mark.parametrize("n_tris,leaf", [(5, 4), (60, 1), (3000, 4), (40000, 4)])
+def test_quantised_nodes_find_the_same_hits(hostcheck, n_tris, leaf):
+    """bvhq.cuh: 32-byte nodes (child boxes on a 16-bit grid, decoded inside the slab FMA) are conservative -- the
+    closest hits equal the brute-force ones bit for bit, also for axis-parallel rays and rays that start outside
+    the scene box -- and cost only a few per cent more node visits than the fp32 nodes they were encoded from."""
+    sc = scenes.scene_synthetic(n_tris=n_tris, n_quad_lights=2, width=16, height=16, patches=1 if n_tris < 200 else 4)
+    hostcheck.load_scene(sc, max_leaf=leaf)
+    rng = np.random.default_rng(100 + n_tris)
+    n = 6000
+    org = rng.uniform(-1, 1, (n, 3)).astype(np.float32) * np.float32(9)
+    org[:, 2] = np.abs(org[:, 2]) * np.float32(0.5) + np.float32(0.2)
+    org[:500] *= np.float32(8)                      # far outside the grid
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:60, 0] = 0.0
+    d[60:120, 2] = 0.0
+    d[120:160, 1] = -0.0
+    tgt = rng.uniform(-9, 9, (1500, 3)).astype(np.float32)   # rays aimed into the terrain from above and from the side
+    tgt[:, 2] = 0.0
+    d[1000:2500] = tgt - org[1000:2500]
+    d[1000:2500] /= np.linalg.norm(d[1000:2500], axis=1, keepdims=True)
+    want = hostcheck.trace(org, d, brute=True)
+    got32, nodes32, tris32 = hostcheck.trace_counted(org, d, mode=0)
+    gotq, nodesq, trisq = hostcheck.trace_counted(org, d, mode=5)
+    for a, b, c in zip(want, got32, gotq):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
+    assert (want[0] >= 0).mean() > 0.15
+    if n_tris >= 3000:
+        assert nodes32 > 0 and nodesq >= nodes32
+        assert nodesq <= 1.06 * nodes32, (nodesq, nodes32)
+        assert trisq <= 1.06 * tris32, (trisq, tris32)
+        print("quantised nodes: %d tris: node visits x%.4f, triangle tests x%.4f" % (n_tris, nodesq / nodes32, trisq / tris32))
