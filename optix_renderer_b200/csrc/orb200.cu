@@ -33,6 +33,7 @@
 #include "bvh_sah.cuh"
 #include "bvh8.cuh"
 #include "bvh_refit.cuh"
+#include "bvhq.cuh"
 #include "pixel.cuh"
 
 using namespace orb;
@@ -373,11 +374,14 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
 // order; it only delays the pruning by best.t a little.  Against the batching form above this
 // keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
 // triangle test).
-template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, int QSTACK = 0>  // QSTACK 1: q forms, 2: p forms (scene.cuh)
+// QN: the inner nodes are the 32-byte quantised ones of bvhq.cuh (`qn`, grid `qg`; ORB_TRACE_VARIANT=3) -- one
+// 256-bit load per node instead of two; same hits (the encoding is conservative).
+template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, int QSTACK = 0, bool QN = false>  // QSTACK 1: q forms, 2: p forms (scene.cuh)
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
-                    int node_min, int height, unsigned long long* __restrict__ stats = nullptr) {
+                    int node_min, int height, unsigned long long* __restrict__ stats = nullptr,
+                    const QNode* __restrict__ qn = nullptr, QGrid qg = QGrid()) {
     unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
     unsigned long long q_stk[QSTACK ? LOCAL_STACK_MAX : 1];  // QSTACK: 64-bit entries, top entry in registers (scene.cuh)
     int l_stk[LOCAL_STACK && !QSTACK ? LOCAL_STACK_MAX : 1];
@@ -425,7 +429,8 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
                 if (idx < n) {
                     const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
                     ray = idx;
-                    trav_begin(t, s, v3(ro), v3(rd));
+                    if (QN) trav_begin_q(t, s, qg, v3(ro), v3(rd));
+                    else trav_begin(t, s, v3(ro), v3(rd));
                 } else {
                     exhausted = true;
                 }
@@ -448,7 +453,10 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
                     if (t.cur >= 0) trav_node_step_p(t, s, q_stk);
                 } else if (t.cur >= 0) trav_node_step_q(t, s, q_stk);
             } else {
-                if (t.cur >= 0) trav_node_step<SKIP>(t, s, stk, stk_t, stride);
+                if (t.cur >= 0) {
+                    if (QN) trav_node_step_qn<SKIP>(t, qn, stk, stk_t, stride);
+                    else trav_node_step<SKIP>(t, s, stk, stk_t, stride);
+                }
                 else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
             }
             if (leaf == 0 && t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // postpone this leaf, keep walking
@@ -1320,6 +1328,8 @@ struct OrbContext {
     BvhBuildResult bvh;
     SceneView view;
     bool committed = false;
+    QNode* qnodes = nullptr;  // ORB_TRACE_VARIANT=3: the hierarchy's inner nodes on the 16-bit grid (bvhq.cuh)
+    QGrid qgrid;
     bool geometry_dirty = false;  // orb_scene_update_mesh moved corners that orb_scene_refit has not seen yet
     int height = 1;  // stack entries per thread
     // frame
@@ -1418,6 +1428,8 @@ static void free_scene(OrbContext* c) {
     c->d_tex.clear();
     cudaFree(c->bvh.tri); cudaFree(c->bvh.nodes);
     cudaFree(c->bvh8_nodes); cudaFree(c->bvh8_tri);
+    cudaFree(c->qnodes);
+    c->qnodes = nullptr;
     c->bvh8_nodes = c->bvh8_tri = nullptr;
     c->d_pos = c->d_nrm = c->d_uv = nullptr;
     c->d_prim_mesh = nullptr;
@@ -1541,6 +1553,25 @@ static int build_wide_bvh(OrbContext* c, int n) {
     }
     cudaFree(b3.tri);
     cudaFree(b3.nodes);
+    return ORB_OK;
+}
+
+__global__ void k_quantise_nodes(const BvhNode* __restrict__ nodes, int n, QGrid g, QNode* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = q_encode(nodes[i], g);
+}
+
+// ORB_TRACE_VARIANT=3: (re-)encode the inner nodes for the ray-stream kernel; after a build and after a refit.
+static int build_qnodes(OrbContext* c) {
+    if (c->trace_variant != 3 || c->bvh.n_nodes <= 0 || c->bvh.root_ref < 0) return ORB_OK;
+    BvhNode root;
+    CK(cudaMemcpyAsync(&root, c->bvh.nodes + c->bvh.root_ref, sizeof root, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->qgrid = qgrid_from_root(root);
+    if (!c->qnodes) CK(cudaMalloc(&c->qnodes, sizeof(QNode) * (size_t)c->bvh.n_nodes));
+    k_quantise_nodes<<<(c->bvh.n_nodes + 255) / 256, 256, 0, c->stream>>>(c->bvh.nodes, c->bvh.n_nodes, c->qgrid, c->qnodes);
+    CK(cudaGetLastError());
+    c->counters.kernel_launches++;
     return ORB_OK;
 }
 
@@ -1796,6 +1827,10 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
         int rc8 = build_wide_bvh(c, (int)n);
         if (rc8) return rc8;
     }
+    {
+        int rcq = build_qnodes(c);
+        if (rcq) return rcq;
+    }
     CK(cudaEventRecord(eb1, c->stream));
     CK(cudaEventSynchronize(eb1));
     float build_ms = 0.f;
@@ -1867,6 +1902,10 @@ int orb_scene_refit(OrbContext* c) {
     CK(cudaEventRecord(e0, c->stream));
     const int before = c->bvh.launches;
     CK(refit_bvh(c->d_pos, (int)c->h_prim_mesh.size(), c->stream, c->bvh));
+    {
+        int rcq = build_qnodes(c);
+        if (rcq) return rcq;
+    }
     CK(cudaEventRecord(e1, c->stream));
     CK(cudaEventSynchronize(e1));
     float ms = 0.f;
@@ -1946,12 +1985,24 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
         c->counters.kernel_launches++;
         return ORB_OK;
     }
-    if (count && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // instrumented twin of the default kernel
+    if (c->trace_variant == 3 && c->qnodes && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // 32-byte nodes
+        if (count) {
+            const int g = persistent_grid(c, k_trace_stream_spec<true, true, 0, 0, true>, TRACE_BLOCK, 0);
+            k_trace_stream_spec<true, true, 0, 0, true><<<g, TRACE_BLOCK, 0, st>>>(
+                c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min, c->node_min, c->height,
+                &c->cnt->nodes_visited, c->qnodes, c->qgrid);
+        } else {
+            const int g = persistent_grid(c, k_trace_stream_spec<true, false, 0, 0, true>, TRACE_BLOCK, 0);
+            k_trace_stream_spec<true, false, 0, 0, true><<<g, TRACE_BLOCK, 0, st>>>(
+                c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min, c->node_min, c->height,
+                nullptr, c->qnodes, c->qgrid);
+        }
+    } else if (count && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // instrumented twin of the default kernel
         const int g = persistent_grid(c, k_trace_stream_spec<true, true>, TRACE_BLOCK, 0);
         k_trace_stream_spec<true, true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
                                                                    c->stream_cursor, c->refill_min, c->node_min,
                                                                    c->height, &c->cnt->nodes_visited);
-    } else if (c->trace_variant == 1 && c->local_stack && c->height <= LOCAL_STACK_MAX) {
+    } else if ((c->trace_variant == 1 || c->trace_variant == 3) && c->local_stack && c->height <= LOCAL_STACK_MAX) {
         auto k = k_trace_stream_spec<true, false, 0>;
         if (c->pop_skip == 1) k = k_trace_stream_spec<true, false, 1>;
         if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
@@ -1965,7 +2016,7 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
             g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)TRACE_BLOCK * c->min_rays_per_lane - 1) /
                                                      ((size_t)TRACE_BLOCK * c->min_rays_per_lane))));
         k<<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
-                                     c->node_min, c->height, nullptr);
+                                     c->node_min, c->height, nullptr, (const QNode*)nullptr, QGrid());
     } else if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
         const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
         k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
