@@ -426,6 +426,41 @@ def test_wide_bvh_stream_kernel(renderer_factory, monkeypatch):
     assert np.array_equal(a.download("accum"), b.download("accum"), equal_nan=True)
 
 
+def test_quantised_node_stream_kernel(renderer_factory, monkeypatch):
+    """ORB_TRACE_VARIANT=3: the ray-stream kernel over the 32-byte nodes of bvhq.cuh (child boxes on a 16-bit grid,
+    conservative) returns the brute-force hits bit for bit, renders the same RATIO / PATH-wavefront frames as the
+    fp32-node kernel, and fetches about as many nodes."""
+    sc = scenes.scene_synthetic(n_tris=60000, n_quad_lights=4, width=128, height=72)
+    a = renderer_factory(sc)
+    monkeypatch.setenv("ORB_TRACE_VARIANT", "3")
+    b = renderer_factory(sc)
+    monkeypatch.delenv("ORB_TRACE_VARIANT")
+    rng = np.random.default_rng(12)
+    n = 20000
+    org = (rng.uniform(-1, 1, (n, 3)) * 9).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) * 0.5 + 0.2
+    org[:300] *= 6                      # outside the grid
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:100, 1] = 0.0
+    d[100:200, 2] = 0.0
+    want = b.trace_rays(org, d, brute_force=True)
+    got = b.trace_rays(org, d, brute_force=2)
+    q_nodes = b.counters()["nodes_visited"]
+    for x, y in zip(got, want):
+        assert np.array_equal(x, y)
+    a.trace_rays(org, d, brute_force=2)
+    f_nodes = a.counters()["nodes_visited"]
+    assert 0.95 * f_nodes < q_nodes < 1.05 * f_nodes, (q_nodes, f_nodes)
+    for r in (a, b):
+        r.render(api.RATIO, accum_id=2, mode=1, shadow_spp=4)
+    for k in ("sto_direct", "sto_no_vis", "ltc"):
+        assert np.array_equal(a.download(k), b.download(k), equal_nan=True), k
+    for r in (a, b):
+        r.render(api.PATH, accum_id=0, mode=1, max_depth=4, path_wavefront=True)
+    assert np.array_equal(a.download("accum"), b.download("accum"), equal_nan=True)
+
+
 def test_deferred_ltc_equals_one_call(renderer_factory):
     """ORB_RENDER_DEFER_LTC + orb_render_finish (the two halves a tile partition puts around its halo exchange)
     produce the frame of a single orb_render, bit for bit, over several accumulated frames and on a band."""
