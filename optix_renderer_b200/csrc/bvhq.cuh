@@ -8,7 +8,8 @@
 // in the GPU ray-stream kernel behind ORB_TRACE_VARIANT=3 (k_trace_stream_spec<.., QN = true>: one LDG.256 and
 // 12 more LOP3 per node).  Measured on the bench frame: trace stage 1.669 ms against 1.691 ms, 35.98 node
 // fetches per ray against 35.86 (profiles/r1q_qnodes_bench.json); hit-parity and refit tests pass under it
-// (tools/ab_qnodes.sh).  Not the default yet: the whole GPU suite has not run under it.
+// (tools/ab_qnodes.sh; tests/test_gpu_frames.py test_quantised_node_stream_kernel).  Not the default yet: the
+// whole GPU suite has not run under it.
 //
 // Same traversal as scene.cuh otherwise (owl::traceRay -> optixTrace replacement; call sites
 // cuda_src/deviceCode.cu:76, cuda_include/ratio/ratio.cuh:50, cuda_include/path/path.cuh:219).
