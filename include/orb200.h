@@ -115,8 +115,8 @@ typedef struct OrbRenderConfig {
     int32_t y0, y1;        /* rows [y0, y1) rendered by this context (tile partition); 0,0 = all */
     int32_t flags;         /* ORB_RENDER_* */
 } OrbRenderConfig;
-#define ORB_RENDER_FUSED_SHADOW 2 /* RATIO: trace the shadow rays inside one per-pixel kernel instead of the
-                                     ray-stream kernels (kept for A/B measurement; same results) */
+#define ORB_RENDER_FUSED_SHADOW 2 /* PATH: every bounce as one per-path kernel that traces its ray inline instead of
+                                     through the ray stream (the form literal mode uses; a cross-check in the tests) */
 #define ORB_RENDER_PATH_WAVEFRONT 4 /* PATH: one generate / trace / shade wavefront per bounce instead of the
                                        persistent all-bounces kernel (kept for A/B measurement) */
 #define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
@@ -264,7 +264,7 @@ int orb_ratio_estimator_host(OrbContext* ctx, const float* ltc, const float* sto
 /* ---- ray casting over the committed scene (owl::traceRay semantics, tmin=0, tmax=1e30):
  * n rays, origin/direction as n*3 floats; outputs prim (global id, -1 miss), t, u, v.
  * brute_force: 0 = single-ray BVH2 traversal, 1 = every triangle (hit-id parity checks), 2 = the ray-stream
- * kernel the RATIO / PATH frames use (compressed 8-wide BVH when built), instrumented: OrbCounters.nodes_visited /
+ * kernel the RATIO / PATH frames use, instrumented: OrbCounters.nodes_visited /
  * tris_tested. */
 int orb_trace_rays_host(OrbContext* ctx, const float* origin, const float* direction, size_t n, int32_t brute_force,
                         int32_t* prim, float* t, float* u, float* v);

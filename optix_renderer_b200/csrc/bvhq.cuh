@@ -94,14 +94,20 @@ ORB_HD float q_f_hi(uint32_t w) { return __int_as_float_hd((int)(0x4B000000u | (
 // trav_begin() for quantised nodes: t.inv / t.noi become the grid-space constants box_test() consumes.
 ORB_HD void trav_begin_q(TravState& t, const SceneView& s, const QGrid& g, float3 o, float3 d) {
     trav_begin(t, s, o, d);
-    const float3 inv = t.inv;
+    // trav_begin() substitutes +-1e30 for the reciprocal of a zero component; 2^23 * step * 1e30 overflows once
+    // the grid step exceeds ~40 (scene extent ~2.6e6), the slab distances become inf - inf and every node is
+    // rejected.  Clamp the reciprocal so the grid-space constants stay finite: the slab distances of such an
+    // axis remain far beyond any hit distance with the right sign, which is all the test needs.
+    const float lx = fminf(1e30f, 1e37f / (8388608.f * g.step.x)), ly = fminf(1e30f, 1e37f / (8388608.f * g.step.y)),
+                lz = fminf(1e30f, 1e37f / (8388608.f * g.step.z));
+    const float3 inv = v3(fmaxf(fminf(t.inv.x, lx), -lx), fmaxf(fminf(t.inv.y, ly), -ly), fmaxf(fminf(t.inv.z, lz), -lz));
     t.inv = v3(g.step.x * inv.x, g.step.y * inv.y, g.step.z * inv.z);
     t.noi = v3(xfma(-8388608.f, t.inv.x, (g.origin.x - o.x) * inv.x), xfma(-8388608.f, t.inv.y, (g.origin.y - o.y) * inv.y),
                xfma(-8388608.f, t.inv.z, (g.origin.z - o.z) * inv.z));
 }
 
 // One inner node of the quantised hierarchy; stack and order exactly as trav_node_step().
-template <int MAX_SKIP = 0, class IntPtr, class FltPtr>
+template <class IntPtr, class FltPtr>
 ORB_HD void trav_node_step_qn(TravState& t, const QNode* __restrict__ nodes, IntPtr stk, FltPtr stk_t, int stride) {
     const QNode* np = nodes + t.cur;
     uint32_t w0, w1, w2, w3, w4, w5;
@@ -129,7 +135,7 @@ ORB_HD void trav_node_step_qn(TravState& t, const QNode* __restrict__ nodes, Int
     } else if (h1) {
         t.cur = c1;
     } else {
-        t.cur = stack_pop<MAX_SKIP>(stk, stk_t, stride, t.sp, t.best);
+        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
     }
 }
 

@@ -7,8 +7,9 @@
 //                    six float4 G-buffers, per-pixel flags; non-light hit pixels are appended to
 //                    the ACTIVE-PIXEL QUEUE by warp ballot (one atomic per warp)
 //   k_ltc            queue -> LTC area-light sum (lights + LUT staged in shared memory)
-//   k_ratio_shadow   queue -> n closest-hit shadow rays per pixel -> sto_direct / sto_no_vis
-//   k_path_bounce    queue / path-state SoA -> one bounce, survivors re-compacted by ballot
+//   k_shadow_gen -> k_trace_stream_spec -> k_shadow_resolve   queue -> n closest-hit shadow rays per pixel as a
+//                    RAY STREAM traced by persistent warps that replace finished rays -> sto_direct / sto_no_vis
+//   k_path_persistent  queue -> all bounces of a PATH frame, a lane owns a path (k_path_bounce: literal mode)
 //   k_accumulate     colour + running sum -> accum, RGBA8, NaN count
 //   k_denoise_*      edge-avoiding a-trous on the packed (direct, no_vis) image
 //   k_ratio_combine  ltc * (direct / no_vis)
@@ -31,7 +32,6 @@
 #include "../../include/orb200.h"
 #include "bvh_build.cuh"
 #include "bvh_sah.cuh"
-#include "bvh8.cuh"
 #include "bvh_refit.cuh"
 #include "bvhq.cuh"
 #include "pixel.cuh"
@@ -222,47 +222,10 @@ k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_ratio_shadow: n light samples per active pixel, each one closest-hit ray
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, int mode, int height) {
-    int* stk = s_dyn + threadIdx.x;
-    float* stk_t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    unsigned rays = 0;
-    SmemTracer tr{s, stk, stk_t, &rays};
-    const unsigned n = f.cnt->queue_n;
-    const float nf = (float)spp;
-    for (unsigned i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
-        const size_t ofs = f.queue[i];
-        const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
-        const float4 pp = ld_stream(f.position + ofs), nn = ld_stream(f.normal + ofs);
-        const float4 dd = ld_stream(f.albedo + ofs), aa = ld_stream(f.alpha + ofs);
-        Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
-        rng_next(rng);  // the two jitter draws of the primary ray
-        rng_next(rng);
-        float3 sd = v3(0.f), sn = v3(0.f);
-        for (int k = 0; k < spp; k++) {
-            float3 d, nv;
-            ratio_shadow_sample(s, tr, cam_pos, v3(pp), v3(nn), v3(dd), aa.x, rng, mode, d, nv);
-            sd += d;
-            sn += nv;
-        }
-        sd = sd / nf;  // colors[k] /= n
-        sn = sn / nf;
-        const float gd = (sd.x + sd.y + sd.z) / 3.f, gn = (sn.x + sn.y + sn.z) / 3.f;
-        st_stream(f.sto_direct + ofs, make_float4(gd, gd, gd, 1.f));
-        st_stream(f.sto_no_vis + ofs, make_float4(gn, gn, gn, 1.f));
-    }
-    // one atomic per warp
-    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
-    if ((threadIdx.x & 31) == 0 && rays) atomicAdd(&f.cnt->rays_shadow, (unsigned long long)rays);
-}
-
-// ---------------------------------------------------------------------------------------------
-// Ray streams: generate -> k_trace_stream -> resolve.
+// Ray streams: generate -> k_trace_stream_spec -> resolve.
 //
-// ncu on the fused kernel above (profiles/r1a): incoherent shadow rays leave 8 of 32 lanes active
-// on average, because a warp runs until its LONGEST ray ends (2.3 lanes in the triangle block).
+// ncu on a one-thread-per-pixel shadow kernel (profiles/r1a): incoherent shadow rays leave 8 of 32 lanes
+// active on average, because a warp runs until its LONGEST ray ends (2.3 lanes in the triangle block).
 // The stream form stores rays (32 B) and hit records (16 B) in HBM and traverses them with
 // persistent warps that REPLACE finished rays: a lane whose ray ended writes its hit and, once
 // enough lanes are idle, the warp claims new rays from a global cursor (in chunks, one atomic per
@@ -270,23 +233,68 @@ k_ratio_shadow(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, 
 // is ~3 % of the kernel's time at the measured copy rate.
 // ---------------------------------------------------------------------------------------------
 #define STREAM_CHUNK 128u
-#define STREAM_BURST 8
 
 // (Tried and removed: longest-first scheduling by the ray's chord through the scene bounds, two
 // bins filled by warp-aggregated atomics.  It cost 0.07 ms of coherence on the shadow stage and
 // gained nothing: the per-launch floor was not late long rays but the chunk granularity, fixed by
-// the guided chunk sizes in k_trace_stream.)
+// the guided chunk sizes below.  Also removed after measurement, round 1: leaf batching without
+// speculation, a compressed 8-wide BVH, bounded pops, 64-bit stack entries -- DESIGN.md section 3.)
 __device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsigned id, float3 o, float3 d) {
     st_stream(rays + 2 * (size_t)id, make_float4(o.x, o.y, o.z, 0.f));
     st_stream(rays + 2 * (size_t)id + 1, make_float4(d.x, d.y, d.z, 0.f));
 }
 
-template <bool LOCAL_STACK>
+// A warp's claim on the shared work list [0, n): `need` idle lanes (ballot `want`) each get the next unclaimed
+// index; the warp's private range [w_next, w_end) is refilled from the global cursor by ONE atomic per chunk.
+// Guided self-scheduling: chunks shrink (128 -> 32) as the list runs dry, so a small launch or the end of a
+// large one is spread over all resident warps instead of being served 4 rounds deep by the few warps that
+// grabbed the last full chunks (ncu, PATH bounces 2-7: 0.4 ms each for a few 10k rays before this).
+// Returns this lane's index (only meaningful where its `want` bit is set); may be >= n (list exhausted).
+__device__ __forceinline__ unsigned warp_claim(unsigned want, unsigned lane, unsigned n, unsigned* __restrict__ cursor,
+                                               unsigned& w_next, unsigned& w_end) {
+    const unsigned FULL = 0xffffffffu;
+    const unsigned need = __popc(want);
+    const unsigned left = w_end - w_next;
+    unsigned base = w_next;
+    unsigned chunk = STREAM_CHUNK;
+    if (left < need) {  // uniform: claim another chunk, finish the old range first
+        if (lane == 0) {
+            const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
+            const unsigned rem = n > seen ? n - seen : 0u;
+            const unsigned warps = gridDim.x * (blockDim.x / 32);
+            chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
+            base = atomicAdd(cursor, chunk);
+        }
+        base = __shfl_sync(FULL, base, 0);
+        chunk = __shfl_sync(FULL, chunk, 0);
+    }
+    const unsigned rank = __popc(want & ((1u << lane) - 1u));
+    const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
+    if (left >= need) {
+        w_next += need;
+    } else {
+        w_next = base + (need - left);
+        w_end = base + chunk;
+    }
+    return idx;
+}
+
+// Speculative while-while traversal (after Aila & Laine): a lane that reaches a leaf POSTPONES it (one
+// slot) and keeps walking inner nodes; the warp leaves the node loop when fewer than `node_min` lanes can
+// still advance, and then every lane tests its postponed leaf together.  Postponing is legal because the
+// result does not depend on the visiting order; it only delays the pruning by best.t a little.  It keeps
+// lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the triangle test).
+// QN: the inner nodes are the 32-byte quantised ones of bvhq.cuh (`qn`, grid `qg`; ORB_TRACE_VARIANT=3) -- one
+// 256-bit load per node instead of two; same hits (the encoding is conservative).
+// LOCAL_STACK: traversal stack in thread-local memory (behind L1) -- no shared memory, so residency is limited
+// by registers only; false: per-lane columns of shared memory, for hierarchies deeper than LOCAL_STACK_MAX.
+template <bool LOCAL_STACK, bool COUNT = false, bool QN = false>
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits, const unsigned* __restrict__ n_items,
-               unsigned mult, unsigned* __restrict__ cursor, int refill_min, int leaf_min, int height) {
-    // Traversal stack: per-lane columns of shared memory (bank-conflict free, but 8 B x height x 128
-    // threads of shared memory per CTA caps residency), or thread-local memory behind L1.
+k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
+                    const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
+                    int node_min, int height, unsigned long long* __restrict__ stats = nullptr,
+                    const QNode* __restrict__ qn = nullptr, QGrid qg = QGrid()) {
+    unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
     int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
     int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
@@ -296,103 +304,6 @@ k_trace_stream(SceneView s, const float4* __restrict__ rays, float4* __restrict_
     const unsigned lane = threadIdx.x & 31u;
     const unsigned FULL = 0xffffffffu;
     unsigned w_next = 0, w_end = 0;  // the warp's claimed range of ray indices (uniform across lanes)
-    TravState t;
-    t.cur = ORB_TRAVERSAL_DONE;
-    t.sp = 0;
-    unsigned ray = FULL;
-    bool exhausted = false;
-    for (;;) {
-        const bool idle = t.cur == ORB_TRAVERSAL_DONE;
-        if (idle && ray != FULL) {
-            st_stream(hits + ray, make_float4(__int_as_float(t.best.prim), t.best.u, t.best.v, t.best.t));
-            ray = FULL;
-        }
-        const unsigned want = __ballot_sync(FULL, idle && !exhausted);
-        const unsigned busy = __ballot_sync(FULL, !idle);
-        if (want && ((int)__popc(want) >= refill_min || busy == 0u)) {
-            const unsigned need = __popc(want);
-            const unsigned left = w_end - w_next;
-            unsigned base = w_next;
-            unsigned chunk = STREAM_CHUNK;
-            if (left < need) {  // uniform: claim another chunk, finish the old range first
-                // Guided self-scheduling: chunks shrink (128 -> 32 rays) as the stream runs dry, so a
-                // small launch or the end of a large one is spread over all resident warps instead of
-                // being served 4 rounds deep by the few warps that grabbed the last full chunks
-                // (ncu, PATH bounces 2-7: 0.4 ms each for a few 10k rays before this).
-                if (lane == 0) {
-                    const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
-                    const unsigned rem = n > seen ? n - seen : 0u;
-                    const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
-                    chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
-                    base = atomicAdd(cursor, chunk);
-                }
-                base = __shfl_sync(FULL, base, 0);
-                chunk = __shfl_sync(FULL, chunk, 0);
-            }
-            const unsigned rank = __popc(want & ((1u << lane) - 1u));
-            if (idle && !exhausted) {
-                const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
-                if (idx < n) {
-                    const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
-                    ray = idx;
-                    trav_begin(t, s, v3(ro), v3(rd));
-                } else {
-                    exhausted = true;
-                }
-            }
-            if (left >= need) {
-                w_next += need;
-            } else {
-                w_next = base + (need - left);
-                w_end = base + chunk;
-            }
-        }
-        if (__ballot_sync(FULL, t.cur != ORB_TRAVERSAL_DONE) == 0u) break;
-        // A burst of single steps.  Lanes on an inner node advance every iteration; lanes that hold
-        // a LEAF wait until `leaf_min` of them do (or nobody has an inner node left) and then run
-        // the triangle tests together -- the while-while form left 10 of 32 lanes active in the
-        // node loop because each macro step lasted as long as its slowest lane (profiles/r1b).
-#pragma unroll 1
-        for (int it = 0; it < STREAM_BURST; ++it) {
-            if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
-            const bool at_leaf = t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE;
-            const unsigned leaves = __ballot_sync(FULL, at_leaf);
-            const unsigned inner = __ballot_sync(FULL, t.cur >= 0);
-            if (leaves && ((int)__popc(leaves) >= leaf_min || inner == 0u)) {
-                if (at_leaf) trav_leaf_step(t, s, stk, stk_t, stride);
-            } else if (inner == 0u) {
-                break;  // everyone is finished: go and refill
-            }
-        }
-    }
-}
-
-// Speculative form of the same kernel (after Aila & Laine's "speculative while-while"): a lane that
-// reaches a leaf POSTPONES it (one slot) and keeps walking inner nodes; the warp leaves the node
-// loop when fewer than `node_min` lanes can still advance, and then every lane tests its
-// postponed leaf together.  Postponing is legal because the result does not depend on the visiting
-// order; it only delays the pruning by best.t a little.  Against the batching form above this
-// keeps lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the
-// triangle test).
-// QN: the inner nodes are the 32-byte quantised ones of bvhq.cuh (`qn`, grid `qg`; ORB_TRACE_VARIANT=3) -- one
-// 256-bit load per node instead of two; same hits (the encoding is conservative).
-template <bool LOCAL_STACK, bool COUNT = false, int SKIP = 0, int QSTACK = 0, bool QN = false>  // QSTACK 1: q forms, 2: p forms (scene.cuh)
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
-                    const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
-                    int node_min, int height, unsigned long long* __restrict__ stats = nullptr,
-                    const QNode* __restrict__ qn = nullptr, QGrid qg = QGrid()) {
-    unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
-    unsigned long long q_stk[QSTACK ? LOCAL_STACK_MAX : 1];  // QSTACK: 64-bit entries, top entry in registers (scene.cuh)
-    int l_stk[LOCAL_STACK && !QSTACK ? LOCAL_STACK_MAX : 1];
-    float l_stk_t[LOCAL_STACK && !QSTACK ? LOCAL_STACK_MAX : 1];
-    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
-    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
-    const unsigned n = *n_items * mult;
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned FULL = 0xffffffffu;
-    unsigned w_next = 0, w_end = 0;
     TravState t;
     t.cur = ORB_TRAVERSAL_DONE;
     t.sp = 0;
@@ -408,24 +319,8 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
         const unsigned want = __ballot_sync(FULL, idle && !exhausted);
         const unsigned busy = __ballot_sync(FULL, !idle);
         if (want && ((int)__popc(want) >= refill_min || busy == 0u)) {
-            const unsigned need = __popc(want);
-            const unsigned left = w_end - w_next;
-            unsigned base = w_next;
-            unsigned chunk = STREAM_CHUNK;
-            if (left < need) {
-                if (lane == 0) {
-                    const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
-                    const unsigned rem = n > seen ? n - seen : 0u;
-                    const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
-                    chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
-                    base = atomicAdd(cursor, chunk);
-                }
-                base = __shfl_sync(FULL, base, 0);
-                chunk = __shfl_sync(FULL, chunk, 0);
-            }
-            const unsigned rank = __popc(want & ((1u << lane) - 1u));
+            const unsigned idx = warp_claim(want, lane, n, cursor, w_next, w_end);
             if (idle && !exhausted) {
-                const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
                 if (idx < n) {
                     const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
                     ray = idx;
@@ -435,124 +330,31 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
                     exhausted = true;
                 }
             }
-            if (left >= need) {
-                w_next += need;
-            } else {
-                w_next = base + (need - left);
-                w_end = base + chunk;
-            }
         }
         if (__ballot_sync(FULL, t.cur != ORB_TRAVERSAL_DONE || leaf != 0) == 0u) break;
-        // node phase.  A lane is walking (an inner node, or culled stack entries still to drop: POP), holds a
-        // leaf, or is done; leaf references are the negative values above the two sentinels.
+        // node phase.  A lane is walking an inner node, holds a leaf, or is done; leaf references are the
+        // negative values other than the DONE sentinel.
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {
             if (COUNT && t.cur >= 0) ++c_nodes;
-            if (QSTACK) {
-                if (QSTACK == 2) {
-                    if (t.cur >= 0) trav_node_step_p(t, s, q_stk);
-                } else if (t.cur >= 0) trav_node_step_q(t, s, q_stk);
-            } else {
-                if (t.cur >= 0) {
-                    if (QN) trav_node_step_qn<SKIP>(t, qn, stk, stk_t, stride);
-                    else trav_node_step<SKIP>(t, s, stk, stk_t, stride);
-                }
-                else if (SKIP > 0 && t.cur == ORB_TRAVERSAL_POP) t.cur = stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+            if (t.cur >= 0) {
+                if (QN) trav_node_step_qn(t, qn, stk, stk_t, stride);
+                else trav_node_step(t, s, stk, stk_t, stride);
             }
-            if (leaf == 0 && t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // postpone this leaf, keep walking
+            if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // postpone this leaf, keep walking
                 leaf = t.cur;
-                t.cur = QSTACK == 2 ? p_pop(t, q_stk) : QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
             }
-            if ((int)__popc(__ballot_sync(FULL, t.cur >= 0 || t.cur == ORB_TRAVERSAL_POP)) < node_min) break;
+            if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
         }
         // leaf phase
         if (leaf != 0) {
             trav_leaf_test(t, s, leaf, COUNT ? &c_tris : nullptr);
             leaf = 0;
-            if (t.cur < 0 && t.cur > ORB_TRAVERSAL_POP) {  // a second leaf was waiting: it becomes the postponed one
+            if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
-                t.cur = QSTACK == 2 ? p_pop(t, q_stk) : QSTACK ? q_pop(t, q_stk) : stack_pop<SKIP>(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
             }
-        }
-    }
-    if (COUNT) {
-        for (int o = 16; o; o >>= 1) {
-            c_nodes += __shfl_xor_sync(FULL, c_nodes, o);
-            c_tris += __shfl_xor_sync(FULL, c_tris, o);
-        }
-        if (lane == 0) {
-            atomicAdd(stats, (unsigned long long)c_nodes);
-            atomicAdd(stats + 1, (unsigned long long)c_tris);
-        }
-    }
-}
-
-// The same ray stream through the compressed 8-wide BVH (bvh8.cuh): one wide_step() per live lane and
-// iteration -- open the nearest unopened node of the lane's current group (five 128-bit loads decide eight
-// subtrees), test the triangles of the leaves that were hit, pop.  Refill as above.
-template <bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_stream_wide(Bvh8View w, int n_tris, const float4* __restrict__ rays, float4* __restrict__ hits,
-                    const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
-                    int node_min, unsigned long long* __restrict__ stats) {
-    uint32_t stk[2 * ORB_BVH8_STACK];
-    unsigned c_nodes = 0, c_tris = 0;
-    const unsigned n = *n_items * mult;
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned FULL = 0xffffffffu;
-    unsigned w_next = 0, w_end = 0;
-    WideState t;
-    t.done = true;
-    t.sp = 0;
-    unsigned ray = FULL;
-    bool exhausted = false;
-    for (;;) {
-        const bool idle = t.done;
-        if (idle && ray != FULL) {
-            st_stream(hits + ray, make_float4(__int_as_float(t.best.prim), t.best.u, t.best.v, t.best.t));
-            ray = FULL;
-        }
-        const unsigned want = __ballot_sync(FULL, idle && !exhausted);
-        const unsigned busy = __ballot_sync(FULL, !idle);
-        if (want && ((int)__popc(want) >= refill_min || busy == 0u)) {
-            const unsigned need = __popc(want);
-            const unsigned left = w_end - w_next;
-            unsigned base = w_next;
-            unsigned chunk = STREAM_CHUNK;
-            if (left < need) {
-                if (lane == 0) {
-                    const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
-                    const unsigned rem = n > seen ? n - seen : 0u;
-                    const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
-                    chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
-                    base = atomicAdd(cursor, chunk);
-                }
-                base = __shfl_sync(FULL, base, 0);
-                chunk = __shfl_sync(FULL, chunk, 0);
-            }
-            const unsigned rank = __popc(want & ((1u << lane) - 1u));
-            if (idle && !exhausted) {
-                const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
-                if (idx < n) {
-                    const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
-                    ray = idx;
-                    wide_begin(t, n_tris, v3(ro), v3(rd));
-                } else {
-                    exhausted = true;
-                }
-            }
-            if (left >= need) {
-                w_next += need;
-            } else {
-                w_next = base + (need - left);
-                w_end = base + chunk;
-            }
-        }
-        if (__ballot_sync(FULL, !t.done) == 0u) break;
-#pragma unroll 1
-        for (int it = 0; it < 64; ++it) {
-            if (!t.done) wide_step(t, w, stk, 1, COUNT ? &c_nodes : nullptr, COUNT ? &c_tris : nullptr);
-            if ((int)__popc(__ballot_sync(FULL, !t.done)) < node_min) break;
         }
     }
     if (COUNT) {
@@ -580,15 +382,6 @@ __global__ void k_unpack_hits(const float4* __restrict__ hits, unsigned n, int* 
     u[i] = h.y;
     v[i] = h.z;
     t[i] = h.w;
-}
-
-__global__ void k_gather_tris(const float4* __restrict__ src, const int* __restrict__ order, int n, float4* __restrict__ dst) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const float4* p = src + 3 * (size_t)order[k];
-    dst[3 * (size_t)k] = p[0];
-    dst[3 * (size_t)k + 1] = p[1];
-    dst[3 * (size_t)k + 2] = p[2];
 }
 
 // one thread per (active pixel, sample): the ray of ratio_based_shadow's light sample
@@ -1345,26 +1138,12 @@ struct OrbContext {
     size_t stream_cap = 0;
     unsigned* stream_cursor = nullptr;
     int refill_min = 12;
-    int leaf_min = 12;
     int node_min = 16;
-    // 0: leaf batching (k_trace_stream), 1: speculative (k_trace_stream_spec, default), 2: compressed 8-wide BVH
-    // (k_trace_stream_wide; measured 1.89 ms against 1.69 ms for the 5 M shadow rays of the bench frame: 14.5
-    // node steps of ~290 instructions per ray cost more issue slots than 35.9 BVH2 steps of ~70, and the
-    // kernel is issue-bound, not fetch-bound -- kept as an option, ORB_TRACE_VARIANT=2)
+    // ray-stream kernel: 1 = 64-byte fp32 nodes (default), 3 = 32-byte quantised nodes (bvhq.cuh; ORB_TRACE_VARIANT)
     int trace_variant = 1;
-    float4* bvh8_nodes = nullptr;  // compressed 8-wide BVH (bvh8.cuh) for the ray-stream kernel; nullptr: not built
-    float4* bvh8_tri = nullptr;
-    int bvh8_height = 0, bvh8_n_nodes = 0;
-    int wide_node_min = 16;
     // > 0: shrink the stream kernel's grid until every lane expects this many rays.  Measured on a 135-row band:
     // 0.428 / 0.430 / 0.453 / 0.606 / 0.961 ms for 0 / 4 / 8 / 16 / 32 -- parallelism beats shorter tails.
     int min_rays_per_lane = 0;
-    // stream kernel: 64-bit stack entries with the top entry in registers (scene.cuh q forms).  Measured 1.735 ms
-    // against 1.696 ms: the earlier load does not pay for the extra register traffic.  Kept as a knob.
-    int q_stack = 0;
-    // k_trace_stream_spec: culled stack entries dropped per main-loop iteration (0: drain in place).  Measured
-    // 1.689 / 1.732 / 1.697 / 1.686 ms for 0 / 1 / 2 / 4: the drain's divergence is not what bounds the kernel.
-    int pop_skip = 0;
     cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
     // orb_buffer_download_rows_async: the frame stream snapshots the rows into a device slot (two per buffer), the
     // copy stream moves the slot to the host while the next frame renders.
@@ -1427,10 +1206,8 @@ static void free_scene(OrbContext* c) {
     for (void* p : c->d_tex) cudaFree(p);
     c->d_tex.clear();
     cudaFree(c->bvh.tri); cudaFree(c->bvh.nodes);
-    cudaFree(c->bvh8_nodes); cudaFree(c->bvh8_tri);
     cudaFree(c->qnodes);
     c->qnodes = nullptr;
-    c->bvh8_nodes = c->bvh8_tri = nullptr;
     c->d_pos = c->d_nrm = c->d_uv = nullptr;
     c->d_prim_mesh = nullptr;
     c->d_meshes = nullptr;
@@ -1516,46 +1293,6 @@ static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem) {
     return per_sm * c->n_sm;
 }
 
-// The compressed 8-wide BVH of the ray-stream kernel: a second binned-SAH BVH2 with leaves of <= 3 triangles
-// (GPU), collapsed into 80-byte wide nodes on the host (bvh8_collapse, cold path: ~0.15 s per million
-// triangles), triangle records gathered into node order on the GPU.  Any failure leaves bvh8_nodes null and
-// the BVH2 kernels in charge.
-static int build_wide_bvh(OrbContext* c, int n) {
-    BvhBuildResult b3;
-    CK(build_bvh_sah(c->d_pos, n, 3, c->stream, b3));
-    c->counters.kernel_launches += b3.launches;
-    std::vector<BvhNode> h_nodes((size_t)std::max(b3.n_nodes, 1));
-    if (b3.n_nodes > 0)
-        CK(cudaMemcpyAsync(h_nodes.data(), b3.nodes, sizeof(BvhNode) * (size_t)b3.n_nodes, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    if (b3.root_ref < 0)  // a single leaf: its box is the scene's
-        for (size_t i = 0; i < c->h_pos.size(); i++) {
-            lo[i % 3] = std::min(lo[i % 3], c->h_pos[i]);
-            hi[i % 3] = std::max(hi[i % 3], c->h_pos[i]);
-        }
-    Bvh8Host w;
-    const bool ok = bvh8_collapse(h_nodes.data(), b3.root_ref, lo, hi, w) && w.height <= ORB_BVH8_STACK &&
-                    (int)w.tri_order.size() == n;
-    if (ok) {
-        int* d_order = nullptr;
-        CK(cudaMalloc(&c->bvh8_nodes, sizeof(Bvh8Node) * w.nodes.size()));
-        CK(cudaMalloc(&c->bvh8_tri, 48 * (size_t)n));
-        CK(cudaMalloc(&d_order, 4 * (size_t)n));
-        CK(cudaMemcpyAsync(c->bvh8_nodes, w.nodes.data(), sizeof(Bvh8Node) * w.nodes.size(), cudaMemcpyHostToDevice, c->stream));
-        CK(cudaMemcpyAsync(d_order, w.tri_order.data(), 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-        k_gather_tris<<<(n + 255) / 256, 256, 0, c->stream>>>(b3.tri, d_order, n, c->bvh8_tri);
-        c->counters.kernel_launches++;
-        CK(cudaStreamSynchronize(c->stream));
-        cudaFree(d_order);
-        c->bvh8_height = w.height;
-        c->bvh8_n_nodes = (int)w.nodes.size();
-    }
-    cudaFree(b3.tri);
-    cudaFree(b3.nodes);
-    return ORB_OK;
-}
-
 __global__ void k_quantise_nodes(const BvhNode* __restrict__ nodes, int n, QGrid g, QNode* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = q_encode(nodes[i], g);
@@ -1604,15 +1341,11 @@ int orb_create(int device, OrbContext** out) {
     memset(&c->view, 0, sizeof(c->view));
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
-    if (const char* e = getenv("ORB_LEAF_MIN")) c->leaf_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
     if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
     if (const char* e = getenv("ORB_LTC_OVERLAP")) c->ltc_overlap = atoi(e);
     if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
-    if (const char* e = getenv("ORB_WIDE_NODE_MIN")) c->wide_node_min = atoi(e);
-    if (const char* e = getenv("ORB_POP_SKIP")) c->pop_skip = atoi(e);
-    if (const char* e = getenv("ORB_Q_STACK")) c->q_stack = atoi(e);
     if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
     if (const char* e = getenv("ORB_DL_SNAPSHOT_KERNEL")) c->dl_snapshot_kernel = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
@@ -1823,10 +1556,6 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     CK(cudaEventRecord(eb0, c->stream));
     if (builder == ORB_BVH_LBVH) CK(build_bvh(c->d_pos, (int)n, max_leaf, c->stream, c->bvh));
     else CK(build_bvh_sah(c->d_pos, (int)n, max_leaf, c->stream, c->bvh));
-    if (c->trace_variant == 2 && n > 0) {
-        int rc8 = build_wide_bvh(c, (int)n);
-        if (rc8) return rc8;
-    }
     {
         int rcq = build_qnodes(c);
         if (rcq) return rcq;
@@ -1845,8 +1574,8 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     if (trace_smem(c) > 200 * 1024)
         return fail(ORB_ERR_INVALID, "orb_scene_commit: BVH too deep for the shared-memory traversal stack");
     CK(allow_smem(k_primary<false>, trace_smem(c)));
-    CK(allow_smem(k_ratio_shadow, trace_smem(c)));
-    CK(allow_smem(k_trace_stream<false>, trace_smem(c)));
+    CK(allow_smem(k_trace_stream_spec<false, false>, trace_smem(c)));
+    CK(allow_smem(k_trace_stream_spec<false, true>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<true>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<false>, trace_smem(c)));
     CK(allow_smem(k_trace_rays, trace_smem(c)));
@@ -1893,8 +1622,6 @@ int orb_scene_update_mesh(OrbContext* c, int32_t mesh_index, const float* vertex
 int orb_scene_refit(OrbContext* c) {
     NEED(c, "orb_scene_refit: ctx is NULL");
     NEED(c->committed, "orb_scene_refit: scene not committed");
-    NEED(!(c->trace_variant == 2 && c->bvh8_nodes),
-         "orb_scene_refit: the compressed 8-wide BVH (ORB_TRACE_VARIANT=2) has no refit; rebuild the scene");
     CK(cudaSetDevice(c->device));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
@@ -1967,66 +1694,23 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
     cudaStream_t st = c->stream;
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
     StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
-    if (c->trace_variant == 2 && c->bvh8_nodes) {
-        Bvh8View w8;
-        w8.nodes = c->bvh8_nodes;
-        w8.tri = c->bvh8_tri;
-        if (count) {
-            const int g = persistent_grid(c, k_trace_stream_wide<true>, TRACE_BLOCK, 0);
-            k_trace_stream_wide<true><<<g, TRACE_BLOCK, 0, st>>>(w8, c->view.n_tris, c->stream_rays, c->stream_hits, n_items,
-                                                                 mult, c->stream_cursor, c->refill_min, c->wide_node_min,
-                                                                 &c->cnt->nodes_visited);
-        } else {
-            const int g = persistent_grid(c, k_trace_stream_wide<false>, TRACE_BLOCK, 0);
-            k_trace_stream_wide<false><<<g, TRACE_BLOCK, 0, st>>>(w8, c->view.n_tris, c->stream_rays, c->stream_hits, n_items,
-                                                                  mult, c->stream_cursor, c->refill_min, c->wide_node_min,
-                                                                  nullptr);
-        }
-        c->counters.kernel_launches++;
-        return ORB_OK;
-    }
-    if (c->trace_variant == 3 && c->qnodes && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // 32-byte nodes
-        if (count) {
-            const int g = persistent_grid(c, k_trace_stream_spec<true, true, 0, 0, true>, TRACE_BLOCK, 0);
-            k_trace_stream_spec<true, true, 0, 0, true><<<g, TRACE_BLOCK, 0, st>>>(
-                c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min, c->node_min, c->height,
-                &c->cnt->nodes_visited, c->qnodes, c->qgrid);
-        } else {
-            const int g = persistent_grid(c, k_trace_stream_spec<true, false, 0, 0, true>, TRACE_BLOCK, 0);
-            k_trace_stream_spec<true, false, 0, 0, true><<<g, TRACE_BLOCK, 0, st>>>(
-                c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min, c->node_min, c->height,
-                nullptr, c->qnodes, c->qgrid);
-        }
-    } else if (count && c->local_stack && c->height <= LOCAL_STACK_MAX) {  // instrumented twin of the default kernel
-        const int g = persistent_grid(c, k_trace_stream_spec<true, true>, TRACE_BLOCK, 0);
-        k_trace_stream_spec<true, true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
-                                                                   c->stream_cursor, c->refill_min, c->node_min,
-                                                                   c->height, &c->cnt->nodes_visited);
-    } else if ((c->trace_variant == 1 || c->trace_variant == 3) && c->local_stack && c->height <= LOCAL_STACK_MAX) {
-        auto k = k_trace_stream_spec<true, false, 0>;
-        if (c->pop_skip == 1) k = k_trace_stream_spec<true, false, 1>;
-        if (c->pop_skip == 2) k = k_trace_stream_spec<true, false, 2>;
-        if (c->pop_skip == 4) k = k_trace_stream_spec<true, false, 4>;
-        if (c->q_stack == 1) k = k_trace_stream_spec<true, false, 0, 1>;
-        if (c->q_stack == 2) k = k_trace_stream_spec<true, false, 0, 2>;
-        int g = persistent_grid(c, k, TRACE_BLOCK, 0);
-        // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
-        // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.
-        if (c->min_rays_per_lane > 0 && n_upper > 0)
-            g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)TRACE_BLOCK * c->min_rays_per_lane - 1) /
-                                                     ((size_t)TRACE_BLOCK * c->min_rays_per_lane))));
-        k<<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
-                                     c->node_min, c->height, nullptr, (const QNode*)nullptr, QGrid());
-    } else if (c->local_stack && c->height <= LOCAL_STACK_MAX) {
-        const int g = persistent_grid(c, k_trace_stream<true>, TRACE_BLOCK, 0);
-        k_trace_stream<true><<<g, TRACE_BLOCK, 0, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
-                                                        c->stream_cursor, c->refill_min, c->leaf_min, c->height);
-    } else {
-        const size_t smem = trace_smem(c);
-        const int g = persistent_grid(c, k_trace_stream<false>, TRACE_BLOCK, smem);
-        k_trace_stream<false><<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult,
-                                                             c->stream_cursor, c->refill_min, c->leaf_min, c->height);
-    }
+    const bool local = c->local_stack && c->height <= LOCAL_STACK_MAX;
+    const size_t smem = local ? 0 : trace_smem(c);
+    const bool qn = c->trace_variant == 3 && c->qnodes && local;  // 32-byte nodes
+    typedef void (*Kernel)(SceneView, const float4*, float4*, const unsigned*, unsigned, unsigned*, int, int, int,
+                           unsigned long long*, const QNode*, QGrid);
+    Kernel k = qn ? (count ? k_trace_stream_spec<true, true, true> : k_trace_stream_spec<true, false, true>)
+               : local ? (count ? k_trace_stream_spec<true, true> : k_trace_stream_spec<true, false>)
+                       : (count ? k_trace_stream_spec<false, true> : k_trace_stream_spec<false, false>);
+    int g = persistent_grid(c, k, TRACE_BLOCK, smem);
+    // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
+    // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.
+    if (c->min_rays_per_lane > 0 && n_upper > 0)
+        g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)TRACE_BLOCK * c->min_rays_per_lane - 1) /
+                                                 ((size_t)TRACE_BLOCK * c->min_rays_per_lane))));
+    k<<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
+                                    c->node_min, c->height, count ? &c->cnt->nodes_visited : nullptr,
+                                    qn ? c->qnodes : (const QNode*)nullptr, qn ? c->qgrid : QGrid());
     c->counters.kernel_launches++;
     return ORB_OK;
 }
@@ -2075,7 +1759,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     // RATIO: the LTC sum (fp32-issue bound, no dependence on the shadow rays) is enqueued on a second
     // stream AFTER the shadow-ray kernels, so its CTAs fill the SMs the persistent traversal kernel
     // leaves idle while its last rays finish (floor of ~0.17 ms per traversal launch, profiles/r1k).
-    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & (ORB_RENDER_FUSED_SHADOW | ORB_RENDER_DEFER_LTC));
+    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & ORB_RENDER_DEFER_LTC);
     auto launch_ltc = [&](cudaStream_t ls) {
         StageTimer tm(c, ORB_STAGE_LTC, 1, ls);
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
@@ -2094,12 +1778,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     if ((renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && !ltc_beside_shadow && !defer_ltc) launch_ltc(st);
     if (ltc_beside_shadow) CK(cudaEventRecord(c->ev_fork, st));  // k_primary done: queue and G-buffers are final
     if (renderer == ORB_RATIO) {
-        if (cfg->flags & ORB_RENDER_FUSED_SHADOW) {  // A/B: one thread per pixel, n rays in sequence
-            StageTimer tm(c, ORB_STAGE_SHADOW, 1);
-            const int g = persistent_grid(c, k_ratio_shadow, TRACE_BLOCK, smem);
-            k_ratio_shadow<<<g, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam.pos, frame_id, spp, mode, c->height);
-            c->counters.kernel_launches++;
-        } else {
+        {
             const size_t npx = (size_t)(y1 - y0) * c->W;
             int rc = ensure_stream(c, npx * (size_t)spp);
             if (rc) return rc;

@@ -134,17 +134,10 @@ ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, floa
 // the lowest primitive id), so any BVH and any order agree bit for bit.
 #define ORB_TRAVERSAL_DONE ((int)0x80000000)  // never a leaf reference: first + count < 2^28
 
-// ORB_TRAVERSAL_POP: "pop again" -- returned by the bounded pop below when MAX_SKIP culled entries were
-// dropped and the stack is not empty yet.  A ray that has found its hit still owns a stack full of
-// subtrees beyond it; draining them in an inner loop runs a few lanes alone for many iterations (ncu,
-// profiles/r1m: 16 % of the stream kernel's instructions at 2.8 - 8 active lanes).  The ray-stream kernels
-// drain MAX_SKIP entries per iteration of their main loop instead, beside the lanes that still walk nodes.
-#define ORB_TRAVERSAL_POP ((int)0x80000001)  // never a leaf reference either
-template <int MAX_SKIP = 0, class IntPtr, class FltPtr>
+template <class IntPtr, class FltPtr>
 ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& best) {
-    for (int k = 0;; ++k) {  // skip subtrees that start beyond the current closest hit
+    for (;;) {  // skip subtrees that start beyond the current closest hit
         if (sp == 0) return ORB_TRAVERSAL_DONE;
-        if (MAX_SKIP > 0 && k == MAX_SKIP) return ORB_TRAVERSAL_POP;
         --sp;
         if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) return stk[sp * stride];
     }
@@ -157,8 +150,6 @@ struct TravState {
     float3 o, d, inv, noi;  // noi = -o * inv
     Hit best;
     int cur, sp;
-    int top_ref;  // the "q" stack forms below keep the top entry here
-    float top_t;
 };
 
 ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
@@ -181,7 +172,7 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
 }
 
 // One inner node (t.cur >= 0): both child boxes of a 64-byte node, near child next, far pushed.
-template <int MAX_SKIP = 0, class IntPtr, class FltPtr>
+template <class IntPtr, class FltPtr>
 ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride) {
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
@@ -214,117 +205,7 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
     } else if (h1) {
         t.cur = c1;
     } else {
-        t.cur = stack_pop<MAX_SKIP>(stk, stk_t, stride, t.sp, t.best);
-    }
-}
-
-// ---- "q" forms: 64-bit (reference, entry distance) stack entries, top entry in registers ---------------
-// The pop of the plain forms loads the entry it returns, so the next node fetch waits for a local-memory
-// load first (ncu profiles/r1m: 23 % of the stream kernel's stall samples sit on those loads).  Here the
-// entry a pop returns is already in registers and the load of the NEXT top is issued at once, a whole node
-// step before it is needed; an entry is one 64-bit word (one LDL / STL instead of two).
-// Invariant: entries 0 .. sp-2 are in `stk`, entry sp-1 is (top_ref, top_t).
-ORB_HD unsigned long long q_pack(int ref, float t) {
-    return ((unsigned long long)(unsigned)__float_as_int_hd(t) << 32) | (unsigned long long)(unsigned)ref;
-}
-ORB_HD void q_push(TravState& t, unsigned long long* stk, int ref, float tn) {
-    if (t.sp > 0) stk[t.sp - 1] = q_pack(t.top_ref, t.top_t);
-    t.top_ref = ref;
-    t.top_t = tn;
-    ++t.sp;
-}
-ORB_HD int q_pop(TravState& t, const unsigned long long* stk) {
-    for (;;) {  // skip subtrees that start beyond the current closest hit
-        if (t.sp == 0) return ORB_TRAVERSAL_DONE;
-        const int ref = t.top_ref;
-        const float tn = t.top_t;
-        --t.sp;
-        if (t.sp > 0) {
-            const unsigned long long e = stk[t.sp - 1];
-            t.top_ref = (int)(unsigned)(e & 0xffffffffull);
-            t.top_t = __int_as_float_hd((int)(unsigned)(e >> 32));
-        }
-        if (t.best.prim < 0 || !(tn > t.best.t)) return ref;
-    }
-}
-
-// ---- "p" forms: the same 64-bit entries, all of them in memory (no register-held top): one STL.64 per push
-// and one LDL.64 per pop instead of two 32-bit accesses each -- the stack shares the L1 data pipe with the
-// node fetches, and with divergent stack depths every access of a lane is its own L1 wavefront.
-ORB_HD int p_pop(TravState& t, const unsigned long long* stk) {
-    for (;;) {
-        if (t.sp == 0) return ORB_TRAVERSAL_DONE;
-        const unsigned long long e = stk[--t.sp];
-        const float tn = __int_as_float_hd((int)(unsigned)(e >> 32));
-        if (t.best.prim < 0 || !(tn > t.best.t)) return (int)(unsigned)(e & 0xffffffffull);
-    }
-}
-
-ORB_HD void trav_node_step_p(TravState& t, const SceneView& s, unsigned long long* stk) {
-    const BvhNode* np = s.nodes + t.cur;
-#ifdef __CUDA_ARCH__
-    float4 na, nb, nc;
-    int c0, c1, pad0, pad1;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(na.x), "=f"(na.y), "=f"(na.z), "=f"(na.w), "=f"(nb.x), "=f"(nb.y), "=f"(nb.z), "=f"(nb.w)
-        : "l"(np));
-    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
-        : "l"(reinterpret_cast<const char*>(np) + 32));
-    (void)pad0;
-    (void)pad1;
-#else
-    const float4 na = np->a, nb = np->b, nc = np->c;
-    const int c0 = np->c0, c1 = np->c1;
-#endif
-    const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
-    float tn0, tn1;
-    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
-    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
-    if (h0 && h1) {
-        const bool swap = tn1 < tn0;
-        stk[t.sp++] = q_pack(swap ? c0 : c1, swap ? tn0 : tn1);
-        t.cur = swap ? c1 : c0;
-    } else if (h0) {
-        t.cur = c0;
-    } else if (h1) {
-        t.cur = c1;
-    } else {
-        t.cur = p_pop(t, stk);
-    }
-}
-
-ORB_HD void trav_node_step_q(TravState& t, const SceneView& s, unsigned long long* stk) {
-    const BvhNode* np = s.nodes + t.cur;
-#ifdef __CUDA_ARCH__
-    float4 na, nb, nc;
-    int c0, c1, pad0, pad1;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(na.x), "=f"(na.y), "=f"(na.z), "=f"(na.w), "=f"(nb.x), "=f"(nb.y), "=f"(nb.z), "=f"(nb.w)
-        : "l"(np));
-    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
-        : "l"(reinterpret_cast<const char*>(np) + 32));
-    (void)pad0;
-    (void)pad1;
-#else
-    const float4 na = np->a, nb = np->b, nc = np->c;
-    const int c0 = np->c0, c1 = np->c1;
-#endif
-    const float lim = t.best.prim < 0 ? ORB_TMAX : t.best.t;
-    float tn0, tn1;
-    const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
-    const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
-    if (h0 && h1) {
-        const bool swap = tn1 < tn0;
-        q_push(t, stk, swap ? c0 : c1, swap ? tn0 : tn1);
-        t.cur = swap ? c1 : c0;
-    } else if (h0) {
-        t.cur = c0;
-    } else if (h1) {
-        t.cur = c1;
-    } else {
-        t.cur = q_pop(t, stk);
+        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
     }
 }
 

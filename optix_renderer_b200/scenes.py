@@ -142,6 +142,34 @@ def scene_floor_blocker(width=64, height=64):
     return finish([floor, blocker, light], cam, width, height)
 
 
+def checker_texture(w, h, seed=3):
+    """(h, w, 4) uint8 RGBA: every texel a different colour (a wrong texel pick changes the albedo), with texels at
+    both ends of the unorm8 range so the /255 scale is visible, and an alpha channel that must be ignored."""
+    rng = np.random.default_rng(seed)
+    t = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    t[0, 0] = (0, 255, 1, 7)
+    t[-1, -1] = (255, 0, 254, 200)
+    return t
+
+
+def scene_textured(width=48, height=40):
+    """The floor / blocker / light scene with RGBA8 diffuse textures (hit_miss.cuh:39-43; nearest, clamp,
+    include/viewer.hpp:436-447): the floor's texture coordinates run from -1.3 to 2.4, so abs(fmodf(uv, 1))
+    wraps, mirrors the negative part and lands on texel borders; the blocker carries a 3x2 texture."""
+    up = (0, 0, 1)
+    fp, fn, fuv = quad_tris((-2, -2, 0), (2, -2, 0), (2, 2, 0), (-2, 2, 0), up)
+    fuv = (fuv * F(3.7) - F(1.3)).astype(F)
+    floor = make_mesh(fp, fn, fuv, diffuse=(.8, .6, .4), alpha=.3, material_id=1, tex=checker_texture(8, 4, 3))
+    bp, bn, buv = quad_tris((-.3, -.3, .5), (.3, -.3, .5), (.3, .3, .5), (-.3, .3, .5), up)
+    blocker = make_mesh(bp, bn, buv, diffuse=(.2, .7, .2), alpha=.5, material_id=2, tex=checker_texture(3, 2, 4))
+    wall = quad_mesh((-2, 2, 0), (2, 2, 0), (2, 2, 1.5), (-2, 2, 1.5), (0, -1, 0), diffuse=(.5, .5, .7), alpha=.7,
+                     material_id=3)  # untextured beside textured meshes
+    light = quad_mesh((-.5, -.5, 1), (-.5, .5, 1), (.5, .5, 1), (.5, -.5, 1), (0, 0, -1), diffuse=(0, 0, 0),
+                      alpha=1., emit=(10, 10, 10), is_light=True, material_id=0)
+    cam = camera_from_lookat((3, -3, 2.5), (0, 0, .3), (0, 0, 1), .66, width, height)
+    return finish([floor, blocker, wall, light], cam, width, height)
+
+
 def _box_meshes(lo, hi, rot_deg, **kw):
     """Axis-aligned box [lo,hi] rotated about the y axis through its centre: 5 visible faces + bottom."""
     lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)

@@ -65,6 +65,13 @@ long long ora_render(int W, int H, int rendererType, int accumId, int y0, int y1
 void ora_ltc_gbuffer(int n, const float* position, const float* normal, const float* albedo,
                      const float* alpha, const float* cam_pos, float* out, int nthreads);
 
+/* liboracle.so ONLY -- classification aid of the parity tests, not a reference function: per pixel of a saved
+ * G-buffer, the distance of the LTC evaluation to its nearest sign decision (wo_local.z < 0, the back-face test,
+ * the above-horizon bit of every clip vertex).  out[n]; +inf on miss pixels.  Pixels below ~1e-4 are where a
+ * last-ulp difference moves the evaluation to another case of clipPolygon's table ("case flips"). */
+void ora_ltc_margin(int n, const float* position, const float* normal, const float* alpha, const float* cam_pos,
+                    float* out, int nthreads);
+
 /* ---- unit entry points (known-answer tests) ---- */
 void ora_u_rng(int frame_id, uint32_t px, uint32_t py, uint32_t W, uint32_t H, int n, uint32_t* state0,
                uint32_t* raw, float* flt); /* state0 = seed; raw[n] from lcg_random; flt[n] CONTINUES with lcg_randomf */

@@ -357,6 +357,42 @@ V3 ltc_direct(const Surf& si) {
     return color;
 }
 
+// Classification aid for the parity tests (not a reference function): how close the pixel's LTC evaluation comes
+// to one of its SIGN DECISIONS -- wo_local.z < 0 (deviceCode.cu:27), the back-face test (ltc_utils.cuh:58-60), the
+// above-horizon bit of every vertex fed to the two clips (polygon_utils.cuh:27-31).  A pixel whose margin is below
+// ~1e-4 takes, or sits next to, another branch of the 25-case table when a direction differs in the last ulps
+// (libdevice vs glibc, fma contraction, the texture unit's weights): a "case flip" pixel in north_star's terms.
+float ltc_decision_margin(const Surf& si) {
+    const V3 wo_local = normalize(apply_mat(si.to_local, si.wo));
+    float m = fabsf(wo_local.z);
+    if (wo_local.z < 0.f) return m;
+    const float theta = acosf(wo_local.z);
+    M3 ltc_mat;
+    float amplitude = 1.f;
+    fetch_ltc(si.alpha, theta, ltc_mat, amplitude);
+    const M3 ltc_inv = inverse(ltc_mat);
+    M3 iso;
+    iso.r[0] = normalize(mk(wo_local.x, wo_local.y, 0.f));
+    iso.r[2] = mk(0.f, 0.f, 1.f);
+    iso.r[1] = normalize(cross(iso.r[2], iso.r[0]));
+    for (size_t l = 0; l < S.lights.size(); l++) {
+        const Light& L = S.lights[l];
+        V3 a = normalize(L.v1 - si.p), b = normalize(L.v2 - si.p), c = normalize(L.v3 - si.p);
+        const float bf = dot(-normalize(a + b + c), L.normal);
+        m = fminf(m, fabsf(bf));
+        if (bf < 0.f) continue;
+        a = normalize(apply_mat(iso, normalize(apply_mat(si.to_local, a))));
+        b = normalize(apply_mat(iso, normalize(apply_mat(si.to_local, b))));
+        c = normalize(apply_mat(iso, normalize(apply_mat(si.to_local, c))));
+        m = fminf(m, fminf(fabsf(a.z), fminf(fabsf(b.z), fabsf(c.z))));
+        if (!(a.z > 0.f || b.z > 0.f || c.z > 0.f)) continue;  // the diffuse clip returned 0: the second clip does nothing
+        const V3 ta = normalize(apply_mat(ltc_inv, a)), tb = normalize(apply_mat(ltc_inv, b)),
+                 tc = normalize(apply_mat(ltc_inv, c));
+        m = fminf(m, fminf(fabsf(ta.z), fminf(fabsf(tb.z), fabsf(tc.z))));
+    }
+    return m;
+}
+
 }  // namespace
 
 // ================================================================================================
@@ -909,6 +945,28 @@ void ora_ltc_gbuffer(int n, const float* position, const float* normal, const fl
                 col = ltc_direct(si);
             }
             put4(out, (size_t)i, col.x, col.y, col.z, 1.f);
+        }
+    });
+}
+
+// ltc_decision_margin() over a saved G-buffer of n pixels; out[n] floats, +inf for miss pixels (normal == 0).
+void ora_ltc_margin(int n, const float* position, const float* normal, const float* alpha, const float* cam_pos,
+                    float* out, int nthreads) {
+    const int chunk = 1024;
+    parallel_rows(0, (n + chunk - 1) / chunk, nthreads, [&](int c) {
+        const int e = std::min(n, (c + 1) * chunk);
+        for (int i = c * chunk; i < e; i++) {
+            const V3 nrm = mk(normal + 4 * (size_t)i);
+            out[i] = INFINITY;
+            if (nrm.x == 0.f && nrm.y == 0.f && nrm.z == 0.f) continue;
+            Surf si;
+            si.hit = true;
+            si.p = mk(position + 4 * (size_t)i);
+            si.n_geom = nrm;
+            si.alpha = alpha[4 * (size_t)i];
+            si.wo = normalize(mk(cam_pos) - si.p);
+            onb(si.n_geom, si.to_local, si.to_world);
+            out[i] = ltc_decision_margin(si);
         }
     });
 }

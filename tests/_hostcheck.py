@@ -116,12 +116,6 @@ class HostCheck:
         out["rays"] = self.lib.hc_render(W, H, int(renderer), int(accum_id), int(mode), int(spp), int(depth), C.byref(b))
         return out
 
-    def wide_info(self):
-        n, h = C.c_int(), C.c_int()
-        ok = self.lib.hc_wide_info(C.byref(n), C.byref(h))
-        assert ok, "bvh8_collapse failed"
-        return n.value, h.value
-
     def trace(self, org, dirs, brute=False):
         org, dirs = f32(org).reshape(-1, 3), f32(dirs).reshape(-1, 3)
         n = org.shape[0]

@@ -91,6 +91,7 @@ class Oracle:
         L.ora_ratio_combine.argtypes = [C.c_longlong, _f, _f, _f, _f]
         self.kind = L.ora_kind().decode()
         if self.kind == "restatement":
+            L.ora_ltc_margin.argtypes = [C.c_int, _f, _f, _f, _f, _f, C.c_int]
             L.ora_denoise.argtypes = [C.c_int, C.c_int, _f, _f, _f, _f, _f, _f, C.c_int, C.c_float, C.c_float,
                                       C.c_float, _f, _f, C.c_int]
         self._keep = []
@@ -171,6 +172,16 @@ class Oracle:
         out = np.zeros_like(position)
         c = f32(cam_pos)
         self.lib.ora_ltc_gbuffer(n, _fp(position), _fp(normal), _fp(albedo), _fp(alpha), _fp(c), _fp(out), nthreads)
+        return out
+
+    def ltc_margin(self, position, normal, alpha, cam_pos, nthreads=1):
+        """liboracle.so only: distance of every pixel's LTC evaluation to its nearest sign decision (see
+        oracle_api.h); the scene's lights and LUT must be loaded."""
+        position, normal, alpha = f32(position), f32(normal), f32(alpha)
+        n = position.size // 4
+        out = np.zeros(position.shape[:-1], np.float32)
+        c = f32(cam_pos)
+        self.lib.ora_ltc_margin(n, _fp(position), _fp(normal), _fp(alpha), _fp(c), _fp(out), nthreads)
         return out
 
     def ratio_combine(self, ltc, sd, snv):

@@ -112,3 +112,47 @@ def frame_report(got, ref, hit_got, hit_ref):
                   "rmse": float(np.sqrt((d * d).mean())) if d.size else 0.0,
                   "nan_mismatch": int((nan_g != nan_r)[same].sum()), "nan_ref": int(nan_r.sum())}
     return out
+
+
+# ---- classification of the pixels that differ (north_star: "edge ties ... are counted and reported") -------------
+def classify_hit_mismatches(got, ref, cam_pos, edge_tol=1e-4):
+    """Split the pixels whose primary hit id differs into
+      tie    both sides hit, at the same point in space (|dp| <= 16 ulp of the hit distance): two triangles share
+             the edge / the point the ray passes through and the closest-t comparison went the other way;
+      edge   the hit of at least one side lies within `edge_tol` (barycentric) of a triangle edge: the ray grazes a
+             silhouette edge and a last-ulp difference of the ray direction (fma contraction of the camera ray)
+             moves it on or off the triangle -- what is behind is then hit instead;
+      other  anything else: a real difference.  Tests fail on these.
+    got / ref need hit_prim (H, W), hit_uv (H, W, 2) and position (H, W, 4)."""
+    gp, rp = got["hit_prim"], ref["hit_prim"]
+    bad = gp != rp
+    out = {"mismatch": int(bad.sum()), "tie": 0, "edge": 0, "other": 0}
+    if not bad.any():
+        return out
+    cam = np.asarray(cam_pos, np.float64)
+    pg = np.asarray(got["position"], np.float64)[bad][:, :3]
+    pr = np.asarray(ref["position"], np.float64)[bad][:, :3]
+    both = (gp[bad] >= 0) & (rp[bad] >= 0)
+    t = np.maximum(1.0, np.linalg.norm(pr - cam, axis=1))
+    tie = both & (np.abs(pg - pr).max(axis=1) <= 16 * np.finfo(np.float32).eps * t)
+
+    def near_edge(uv, prim):
+        u, v = uv[..., 0].astype(np.float64), uv[..., 1].astype(np.float64)
+        return (prim >= 0) & (np.minimum(np.minimum(u, v), 1.0 - u - v) <= edge_tol)
+
+    edge = ~tie & (near_edge(got["hit_uv"][bad], gp[bad]) | near_edge(ref["hit_uv"][bad], rp[bad]))
+    out["tie"], out["edge"] = int(tie.sum()), int(edge.sum())
+    out["other"] = out["mismatch"] - out["tie"] - out["edge"]
+    return out
+
+
+def classify_ltc_outliers(err, margin, same_hit, tol=1e-4, near=1e-3):
+    """Pixels whose LTC radiance is outside `tol` (relative), split by the distance of their evaluation to its
+    nearest sign decision (oracle ora_ltc_margin: wo_local.z, back-face test, above-horizon bits of the clip):
+      flip   margin <= near -- the pixel takes, or sits beside, another case of clipPolygon's table;
+      other  margin >  near -- a real difference.  Tests fail on these."""
+    bad = same_hit & (err > tol)
+    flip = bad & (margin <= near)
+    return {"pixels": int(same_hit.sum()), "outside_tol": int(bad.sum()), "flip": int(flip.sum()),
+            "other": int((bad & ~flip).sum()),
+            "margin_quartiles_of_outliers": [float(x) for x in np.quantile(margin[bad], [0.25, 0.5, 0.75, 1.0])] if bad.any() else []}

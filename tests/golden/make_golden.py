@@ -140,4 +140,5 @@ if __name__ == "__main__":
     print("wrote units")
     frames(scenes.scene_floor_blocker, "frames_floor32", 32, 32)
     frames(scenes.scene_cornell, "frames_cornell24", 24, 24)
+    frames(scenes.scene_textured, "frames_textured24", 24, 24)  # RGBA8 diffuse textures (hit_miss.cuh:39-43)
     ltc_gbuffer_case()

@@ -12,7 +12,6 @@
 #include <cstring>
 #include <vector>
 
-#include "../../optix_renderer_b200/csrc/bvh8.cuh"
 #include "../../optix_renderer_b200/csrc/bvhq.cuh"
 #include "../../optix_renderer_b200/csrc/pixel.cuh"
 
@@ -30,11 +29,8 @@ struct State {
     std::vector<float4> tri;
     std::vector<BvhNode> nodes;
     int root_ref = 0;
-    Bvh8Host wide;             // collapsed from a second BVH2 with leaves of <= 3 triangles
-    std::vector<float4> tri8;
     std::vector<QNode> qnodes;  // bvhq.cuh: the same hierarchy on the 16-bit grid
     QGrid qgrid;
-    int wide_ok = 0;
     Camera cam;
     SceneView view;
 } G;
@@ -111,28 +107,6 @@ struct HostTracer {
     Hit operator()(float3 o, float3 d) const {
         rays++;
         if (brute == 1) return trace_brute(G.view, o, d);
-        if (brute == 2) {  // the compressed 8-wide BVH
-            uint32_t ws[2 * ORB_BVH8_STACK];
-            Bvh8View w8;
-            w8.nodes = reinterpret_cast<const float4*>(G.wide.nodes.data());
-            w8.tri = G.tri8.data();
-            return trace_closest_wide(w8, G.view.n_tris, o, d, ws, 1);
-        }
-        if (brute == 3 || brute == 4) {  // the 64-bit stack forms of the ray-stream kernel (ORB_Q_STACK = 1 / 2)
-            unsigned long long qs[128];
-            TravState t;
-            trav_begin(t, G.view, o, d);
-            while (t.cur != ORB_TRAVERSAL_DONE) {
-                if (t.cur >= 0) {
-                    if (brute == 3) trav_node_step_q(t, G.view, qs);
-                    else trav_node_step_p(t, G.view, qs);
-                } else {
-                    trav_leaf_test(t, G.view, t.cur);
-                    t.cur = brute == 3 ? q_pop(t, qs) : p_pop(t, qs);
-                }
-            }
-            return t.best;
-        }
         int stk[128];
         float stk_t[128];
         unsigned nn = 0, nt = 0;
@@ -227,33 +201,7 @@ void hc_commit(int max_leaf) {
         G.qnodes.resize(G.nodes.size());
         for (size_t i = 0; i < G.nodes.size(); i++) G.qnodes[i] = q_encode(G.nodes[i], G.qgrid);
     }
-    // the wide BVH: a second BVH2 with leaves of <= 3 triangles, collapsed by the product's bvh8_collapse()
-    G.wide_ok = 0;
-    if (n) {
-        std::vector<BvhNode> keep;
-        keep.swap(G.nodes);
-        std::vector<int> idx3(n);
-        for (int i = 0; i < n; i++) idx3[i] = i;
-        const int root3 = build_rec(idx3, 0, n, 3);
-        const Box all = bounds(idx3, 0, n);
-        G.wide_ok = bvh8_collapse(G.nodes.data(), root3, all.lo, all.hi, G.wide) && G.wide.height <= ORB_BVH8_STACK;
-        G.nodes.swap(keep);
-        G.tri8.resize(3 * (size_t)n);
-        for (int k = 0; k < n && G.wide_ok; k++) {
-            const int g = idx3[G.wide.tri_order[k]];
-            const float* p = &G.pos[9 * (size_t)g];
-            G.tri8[3 * (size_t)k] = make_float4(p[0], p[1], p[2], __int_as_float_hd(g));
-            G.tri8[3 * (size_t)k + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.f);
-            G.tri8[3 * (size_t)k + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.f);
-        }
-    }
     refresh();
-}
-
-int hc_wide_info(int* n_nodes, int* height) {
-    *n_nodes = (int)G.wide.nodes.size();
-    *height = G.wide.height;
-    return G.wide_ok;
 }
 
 void hc_set_camera(const float* pos, const float* d00, const float* du, const float* dv) {

@@ -38,7 +38,8 @@ def test_rng_skip_equals_sequential_draws(hc):
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-@pytest.mark.parametrize("scene_fn,W,H", [(scenes.scene_floor_blocker, 48, 40), (scenes.scene_cornell, 40, 40)])
+@pytest.mark.parametrize("scene_fn,W,H", [(scenes.scene_floor_blocker, 48, 40), (scenes.scene_cornell, 40, 40),
+                                          (scenes.scene_textured, 48, 40)])
 def test_frames(hostcheck, scene_fn, W, H, mode):
     sc = scene_fn(W, H)
     hostcheck.load_scene(sc)
@@ -49,10 +50,12 @@ def test_frames(hostcheck, scene_fn, W, H, mode):
     for rt in (_oracle.LTC_BASELINE, _oracle.RATIO, _oracle.PATH, _oracle.NORMALS, _oracle.MATERIAL_ID):
         a = o.render(W, H, rt, 0)
         b = hostcheck.render(W, H, rt, 0, mode=mode, spp=4, depth=depth)
-        rep = P.frame_report({k: b[k] for k in ("accum", "ltc", "sto_direct", "sto_no_vis", "position", "normal")},
+        rep = P.frame_report({k: b[k] for k in ("accum", "ltc", "sto_direct", "sto_no_vis", "position", "normal", "albedo", "uv")},
                              a, b["hit_prim"], a["hit_prim"])
         assert rep["hit_mismatch"] == 0
         assert a["rays"] == b["rays"]
+        for k in ("albedo", "uv"):  # the texel pick (hit_miss.cuh:39-43) and uv.z = diffuse.z (deviceCode.cu:167): exact
+            assert np.array_equal(a[k], b[k]), (rt, k)
         for k in ("accum", "ltc", "position", "normal"):
             assert rep[k]["max_rel"] <= 1e-4, (rt, k, rep[k])
             assert rep[k]["nan_mismatch"] == 0
@@ -110,31 +113,6 @@ def test_bvh_traversal_equals_brute_force(hostcheck):
     p2, t2, u2, v2 = hostcheck.trace(org, d, brute=True)
     assert np.array_equal(p1, p2) and np.array_equal(t1, t2) and np.array_equal(u1, u2) and np.array_equal(v1, v2)
     assert (p1 >= 0).mean() > 0.2
-    # the 64-bit stack forms of the stream kernel (scene.cuh q / p forms: ORB_Q_STACK = 1 / 2) walk to the same hits
-    for form in (3, 4):
-        pq, tq, uq, vq = hostcheck.trace(org, d, brute=form)
-        assert np.array_equal(pq, p2) and np.array_equal(tq, t2) and np.array_equal(uq, u2) and np.array_equal(vq, v2)
-    # the compressed 8-wide BVH (bvh8.cuh: collapse + traversal) finds the same hits, bit for bit
-    nn, hh = hostcheck.wide_info()
-    assert nn > 100 and 2 <= hh <= 32
-    p3, t3, u3, v3 = hostcheck.trace(org, d, brute=2)
-    assert np.array_equal(p3, p2) and np.array_equal(t3, t2) and np.array_equal(u3, u2) and np.array_equal(v3, v2)
-
-
-@pytest.mark.parametrize("n_tris", [1, 2, 3, 4, 9, 100])
-def test_wide_bvh_small_scenes(hostcheck, n_tris):
-    sc = scenes.scene_synthetic(n_tris=n_tris, n_quad_lights=1, width=8, height=8)
-    hostcheck.load_scene(sc)
-    rng = np.random.default_rng(n_tris)
-    org = rng.uniform(-2, 2, (500, 3)).astype(np.float32)
-    org[:, 2] = np.abs(org[:, 2]) + 0.5
-    d = rng.normal(size=(500, 3)).astype(np.float32)
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    d[:20, 0] = 0.0
-    a = hostcheck.trace(org, d, brute=2)
-    b = hostcheck.trace(org, d, brute=True)
-    for x, y in zip(a, b):
-        assert np.array_equal(x, y)
 
 
 def test_ltc_gbuffer_pass(hostcheck, restatement):
@@ -178,3 +156,33 @@ def test_quantised_nodes_find_the_same_hits(hostcheck, n_tris, leaf):
         assert nodesq <= 1.06 * nodes32, (nodesq, nodes32)
         assert trisq <= 1.06 * tris32, (trisq, tris32)
         print("quantised nodes: %d tris: node visits x%.4f, triangle tests x%.4f" % (n_tris, nodesq / nodes32, trisq / tris32))
+
+
+def test_quantised_nodes_large_extent_axis_parallel_rays(hostcheck):
+    """bvhq.cuh with a grid step far above 40 (scene extent 1e7): rays with exactly-zero direction components
+    must not lose every node to an inf - inf in the grid-space slab constants (trav_begin_q clamps the
+    substituted reciprocal).  Hits equal brute force and the fp32-node traversal."""
+    import copy
+    sc = copy.deepcopy(scenes.scene_synthetic(n_tris=3000, n_quad_lights=2, width=16, height=16, patches=4))
+    k = np.float32(5e5)
+    for m in sc["meshes"]:
+        m["vtx"] = (m["vtx"] * k).astype(np.float32)
+    hostcheck.load_scene(sc)
+    rng = np.random.default_rng(77)
+    n = 3000
+    org = (rng.uniform(-1, 1, (n, 3)) * 9).astype(np.float32)
+    org[:, 2] = np.abs(org[:, 2]) * np.float32(0.5) + np.float32(1.5)
+    org *= k
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d[:, 2] = -np.abs(d[:, 2])
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:800] = (0, 0, -1)              # straight down: two exactly-zero components
+    d[800:1200, 0] = 0.0
+    d[1200:1600, 1] = -0.0
+    d[800:1600] /= np.linalg.norm(d[800:1600], axis=1, keepdims=True)
+    want = hostcheck.trace(org, d, brute=True)
+    got32, _, _ = hostcheck.trace_counted(org, d, mode=0)
+    gotq, _, _ = hostcheck.trace_counted(org, d, mode=5)
+    assert (want[0][:800] >= 0).mean() > 0.9          # the vertical rays do hit the terrain
+    for a, b, c in zip(want, got32, gotq):
+        assert np.array_equal(a, b) and np.array_equal(a, c)

@@ -117,7 +117,8 @@ def test_small_units_golden(ora, units):
 
 
 @pytest.mark.parametrize("name,fn,W", [("frames_floor32", scenes.scene_floor_blocker, 32),
-                                       ("frames_cornell24", scenes.scene_cornell, 24)])
+                                       ("frames_cornell24", scenes.scene_cornell, 24),
+                                       ("frames_textured24", scenes.scene_textured, 24)])
 def test_frames_golden(restatement, name, fn, W):
     g = np.load(os.path.join(G, name + ".npz"))
     restatement.load_scene(fn(W, W))

@@ -1,6 +1,6 @@
 """Per-source-line instruction and stall totals of one kernel in an .ncu-rep (run here, no GPU).
 
-    python tools/ncu_lines.py gpurun_out/x.ncu-rep k_trace_stream [launch-index] [top-n]
+    python tools/ncu_lines.py gpurun_out/x.ncu-rep|x_src_<kernel>.csv k_trace_stream [launch-index] [top-n]
 
 ncu's CSV source page is per SASS instruction without line numbers; nvdisasm -g of the cubin inside
 liborb200.so has the same instruction sequence with //## File/line markers.  The two are joined by
@@ -15,7 +15,7 @@ import sys
 import tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB = os.path.join(ROOT, "optix_renderer_b200", "liborb200.so")
+LIB = os.environ.get("ORB_LIB", os.path.join(ROOT, "optix_renderer_b200", "liborb200.so"))  # the build that was profiled
 
 
 def sass_lines(kernel):
@@ -45,8 +45,11 @@ def main():
     rep, kernel = sys.argv[1], sys.argv[2]
     which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel],
-                         capture_output=True, text=True).stdout
+    if rep.endswith(".csv"):  # the source page exported on the GPU box (tools/ncu_full.sh)
+        raw = open(rep).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel],
+                             capture_output=True, text=True).stdout
     # several launches: blocks start with a "Kernel Name" row
     blocks, cur = [], None
     for row in csv.reader(io.StringIO(raw)):
