@@ -122,8 +122,6 @@ typedef struct OrbRenderConfig {
 #define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
                                         records fetched / triangle records tested land in OrbCounters.nodes_visited
                                         / tris_tested (same results, slower; bench.py's roofline uses it once) */
-#define ORB_RENDER_DEFER_LTC 16 /* RATIO: primary + shadow rays only; orb_render_finish() runs the LTC sum and the
-                                   accumulation later (a tile partition overlaps them with its denoise halo exchange) */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 
@@ -219,8 +217,15 @@ int orb_resize(OrbContext* ctx, int32_t width, int32_t height);
  * Blocking, like owlLaunch2D.  orb_render_async() enqueues on orb_stream() and returns. */
 int orb_render(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
-/* second half of a RATIO frame rendered with ORB_RENDER_DEFER_LTC (same cfg): LTC sum + accumulation; asynchronous */
-int orb_render_finish(OrbContext* ctx, const OrbRenderConfig* cfg);
+/* Frames in flight: 1 (default) or 2.  With 2, consecutive orb_render_async calls alternate between two sets of frame
+ * buffers and two streams, so the kernels of frame i+1 run beside the tail of frame i's persistent traversal kernels
+ * (the reference renders strictly one frame at a time: owlLaunch2D blocks, viewer.hpp:565).  ORB_BUF_ACCUM and
+ * ORB_BUF_RGBA8 are shared and accumulate in call order; every other buffer exists once per slot.  All calls that
+ * follow an orb_render_async -- denoise, combine, downloads, orb_buffer_device_ptr, orb_stream -- refer to THAT
+ * frame's slot until the next orb_render_async; orb_sync waits for every frame in flight.  Re-allocates the frame. */
+int orb_set_frame_slots(OrbContext* ctx, int32_t n_slots);
+int32_t orb_frame_slot(OrbContext* ctx);  /* slot of the frame the calls currently refer to */
+int32_t orb_frame_slots(OrbContext* ctx);
 
 /* ---- stand-alone passes over RESIDENT frame buffers (rows [y0,y1), 0,0 = all) ---- */
 /* ltcDirectLighingBaseline over the G-buffer (position, normal, albedo, alpha) -> ORB_BUF_LTC;

@@ -112,7 +112,9 @@ def load_library():
     L.orb_resize.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_render.argtypes = [vp, C.POINTER(OrbRenderConfig)]
     L.orb_render_async.argtypes = [vp, C.POINTER(OrbRenderConfig)]
-    L.orb_render_finish.argtypes = [vp, C.POINTER(OrbRenderConfig)]
+    L.orb_set_frame_slots.argtypes = [vp, C.c_int32]
+    L.orb_frame_slot.argtypes = [vp]
+    L.orb_frame_slots.argtypes = [vp]
     L.orb_ltc_gbuffer_pass.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_denoise.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32]
     L.orb_denoise_pack.argtypes = [vp, C.c_int32, C.c_int32]
@@ -251,26 +253,35 @@ class Renderer:
 
     # ---- launch (Viewer::render, viewer.hpp:553-568) ----
     def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True, fused_shadow=False,
-             path_wavefront=False, count_traversal=False, defer_ltc=False):
+             path_wavefront=False, count_traversal=False):
         c = OrbRenderConfig()
         # ORB_RENDER_NO_COUNT, _FUSED_SHADOW, _PATH_WAVEFRONT, _COUNT_TRAVERSAL
         c.flags = ((0 if count_rays else 1) | (2 if fused_shadow else 0) | (4 if path_wavefront else 0)
-                   | (8 if count_traversal else 0) | (16 if defer_ltc else 0))
+                   | (8 if count_traversal else 0))
         c.renderer_type, c.accum_id, c.mode = int(renderer_type), int(accum_id), int(mode)
         c.shadow_spp, c.max_depth = int(shadow_spp), int(max_depth)
         c.y0, c.y1 = rows if rows else (0, 0)
         return c
 
     def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True,
-               count_rays=True, fused_shadow=False, path_wavefront=False, count_traversal=False, defer_ltc=False):
+               count_rays=True, fused_shadow=False, path_wavefront=False, count_traversal=False):
         c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays, fused_shadow, path_wavefront,
-                      count_traversal, defer_ltc)
+                      count_traversal)
         self._ck((self.lib.orb_render if sync else self.lib.orb_render_async)(self._h, C.byref(c)))
 
-    def render_finish(self, accum_id=0, mode=LITERAL, shadow_spp=4, rows=None, count_rays=True):
-        """LTC sum + accumulation of a RATIO frame rendered with defer_ltc=True (same arguments); asynchronous."""
-        c = self._cfg(RATIO, accum_id, mode, shadow_spp, 1, rows, count_rays, defer_ltc=True)
-        self._ck(self.lib.orb_render_finish(self._h, C.byref(c)))
+    def set_frame_slots(self, n):
+        """1 (default) or 2 frames in flight: with 2, consecutive render() calls alternate between two sets of frame
+        buffers and two streams (accum / RGBA8 shared, accumulated in call order); everything called after a render()
+        -- denoise, combine, download, device_ptr, stream -- refers to THAT frame until the next render()."""
+        self._ck(self.lib.orb_set_frame_slots(self._h, int(n)))
+
+    @property
+    def frame_slot(self):
+        return int(self.lib.orb_frame_slot(self._h))
+
+    @property
+    def frame_slots(self):
+        return int(self.lib.orb_frame_slots(self._h))
 
     def ltc_gbuffer_pass(self, rows=None):
         y0, y1 = rows if rows else (0, 0)

@@ -225,18 +225,20 @@ __global__ void k_emit(int n, int max_leaf, float pad, const int2* __restrict__ 
 }
 
 __global__ void k_tri_records(const float* __restrict__ pos, const unsigned* __restrict__ sorted, int n,
-                              float4* __restrict__ tri) {
+                              float4* __restrict__ tri, float2* __restrict__ tri_b) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const unsigned g = sorted[k];
-    const float* p = pos + 9 * (size_t)g;
-    tri[3 * (size_t)k + 0] = make_float4(p[0], p[1], p[2], __int_as_float((int)g));
-    tri[3 * (size_t)k + 1] = make_float4(__fsub_rn(p[3], p[0]), __fsub_rn(p[4], p[1]), __fsub_rn(p[5], p[2]), 0.f);
-    tri[3 * (size_t)k + 2] = make_float4(__fsub_rn(p[6], p[0]), __fsub_rn(p[7], p[1]), __fsub_rn(p[8], p[2]), 0.f);
+    float a[8], b[2];
+    tri_record(a, b, pos + 9 * (size_t)g, (int)g);
+    tri[2 * (size_t)k + 0] = make_float4(a[0], a[1], a[2], a[3]);
+    tri[2 * (size_t)k + 1] = make_float4(a[4], a[5], a[6], a[7]);
+    tri_b[k] = make_float2(b[0], b[1]);
 }
 
 struct BvhBuildResult {
-    float4* tri = nullptr;
+    float4* tri = nullptr;    // 32 B per triangle (scene.cuh tri_record)
+    float2* tri_b = nullptr;  // 8 B per triangle
     BvhNode* nodes = nullptr;
     int root_ref = 0;
     int height = 0;
@@ -270,7 +272,8 @@ inline cudaError_t build_bvh(const float* d_pos, int n, int max_leaf, cudaStream
     ORB_CU(cudaMalloc(&keys_s, 8 * (size_t)n));
     ORB_CU(cudaMalloc(&vals, 4 * (size_t)n));
     ORB_CU(cudaMalloc(&vals_s, 4 * (size_t)n));
-    ORB_CU(cudaMalloc(&out.tri, sizeof(float4) * 3 * (size_t)n));
+    ORB_CU(cudaMalloc(&out.tri, sizeof(float4) * 2 * (size_t)n));
+    ORB_CU(cudaMalloc(&out.tri_b, sizeof(float2) * (size_t)n));
     const unsigned box_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     ORB_CU(cudaMemcpyAsync(scene_box, box_init, sizeof(box_init), cudaMemcpyHostToDevice, st));
     k_prim_bounds<<<G, B, 0, st>>>(d_pos, n, plo, phi, scene_box);
@@ -279,7 +282,7 @@ inline cudaError_t build_bvh(const float* d_pos, int n, int max_leaf, cudaStream
     ORB_CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_s, vals, vals_s, n, 0, 63, st));
     ORB_CU(cudaMalloc(&cub_tmp, tmp_bytes ? tmp_bytes : 16));
     ORB_CU(cub::DeviceRadixSort::SortPairs(cub_tmp, tmp_bytes, keys, keys_s, vals, vals_s, n, 0, 63, st));
-    k_tri_records<<<G, B, 0, st>>>(d_pos, vals_s, n, out.tri);
+    k_tri_records<<<G, B, 0, st>>>(d_pos, vals_s, n, out.tri, out.tri_b);
     out.launches = 4;
     unsigned box_h[6];
     ORB_CU(cudaMemcpyAsync(box_h, scene_box, sizeof(box_h), cudaMemcpyDeviceToHost, st));

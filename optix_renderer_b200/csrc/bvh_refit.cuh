@@ -20,15 +20,18 @@
 
 namespace orb {
 
-__global__ void k_refit_tris(const float* __restrict__ pos, int n, float4* __restrict__ tri, unsigned* __restrict__ scene_box) {
+__global__ void k_refit_tris(const float* __restrict__ pos, int n, float4* __restrict__ tri, float2* __restrict__ tri_b,
+                             unsigned* __restrict__ scene_box) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (k < n) {
-        const int g = __float_as_int(tri[3 * (size_t)k].w);
+        const int g = __float_as_int(tri[2 * (size_t)k].w);
         const float* p = pos + 9 * (size_t)g;
-        tri[3 * (size_t)k + 0] = make_float4(p[0], p[1], p[2], __int_as_float(g));
-        tri[3 * (size_t)k + 1] = make_float4(__fsub_rn(p[3], p[0]), __fsub_rn(p[4], p[1]), __fsub_rn(p[5], p[2]), 0.f);
-        tri[3 * (size_t)k + 2] = make_float4(__fsub_rn(p[6], p[0]), __fsub_rn(p[7], p[1]), __fsub_rn(p[8], p[2]), 0.f);
+        float a[8], b[2];
+        tri_record(a, b, p, g);
+        tri[2 * (size_t)k + 0] = make_float4(a[0], a[1], a[2], a[3]);
+        tri[2 * (size_t)k + 1] = make_float4(a[4], a[5], a[6], a[7]);
+        tri_b[k] = make_float2(b[0], b[1]);
 #pragma unroll
         for (int a = 0; a < 3; a++) {
             lo[a] = fminf(fminf(p[a], p[3 + a]), p[6 + a]);
@@ -76,7 +79,7 @@ __device__ __forceinline__ void refit_child_box(int ref, const float4* __restric
     lo = v3(INFINITY);
     hi = v3(-INFINITY);
     for (int k = first; k < first + count; k++) {
-        const int g = __float_as_int(tri[3 * (size_t)k].w);
+        const int g = __float_as_int(tri[2 * (size_t)k].w);
         const float* p = pos + 9 * (size_t)g;
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -137,7 +140,7 @@ inline cudaError_t refit_bvh(const float* d_pos, int n, cudaStream_t st, BvhBuil
     ORB_CU(cudaMalloc(&scene_box, 6 * sizeof(unsigned)));
     ORB_CU(cudaMemsetAsync(scene_box, 0xff, 3 * sizeof(unsigned), st));  // mins start at the largest key
     ORB_CU(cudaMemsetAsync(scene_box + 3, 0, 3 * sizeof(unsigned), st));
-    k_refit_tris<<<G, B, 0, st>>>(d_pos, n, bvh.tri, scene_box);
+    k_refit_tris<<<G, B, 0, st>>>(d_pos, n, bvh.tri, bvh.tri_b, scene_box);
     bvh.launches++;
     const int nn = bvh.n_nodes;
     if (nn > 0 && bvh.root_ref >= 0) {

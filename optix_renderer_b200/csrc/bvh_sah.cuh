@@ -321,7 +321,8 @@ inline cudaError_t build_bvh_sah(const float* d_pos, int n, int max_leaf, cudaSt
     ORB_CU(cudaMalloc(&node_b, 4 * (size_t)n));
     ORB_CU(cudaMalloc(&id_a, 4 * (size_t)n));
     ORB_CU(cudaMalloc(&id_b, 4 * (size_t)n));
-    ORB_CU(cudaMalloc(&out.tri, sizeof(float4) * 3 * (size_t)n));
+    ORB_CU(cudaMalloc(&out.tri, sizeof(float4) * 2 * (size_t)n));
+    ORB_CU(cudaMalloc(&out.tri_b, sizeof(float2) * (size_t)n));
     const unsigned box_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     ORB_CU(cudaMemcpyAsync(scene_box, box_init, sizeof(box_init), cudaMemcpyHostToDevice, st));
     k_prim_bounds<<<G, B, 0, st>>>(d_pos, n, plo, phi, scene_box);
@@ -338,7 +339,7 @@ inline cudaError_t build_bvh_sah(const float* d_pos, int n, int max_leaf, cudaSt
     unsigned box_h[6];
     ORB_CU(cudaMemcpyAsync(box_h, scene_box, sizeof(box_h), cudaMemcpyDeviceToHost, st));
     if (n <= max_leaf) {
-        k_tri_records<<<G, B, 0, st>>>(d_pos, id_a, n, out.tri);
+        k_tri_records<<<G, B, 0, st>>>(d_pos, id_a, n, out.tri, out.tri_b);
         out.launches++;
         out.root_ref = leaf_ref(0, n);
         out.height = 0;
@@ -392,7 +393,7 @@ inline cudaError_t build_bvh_sah(const float* d_pos, int n, int max_leaf, cudaSt
         const float pad = ext * 1e-5f;
         ORB_CU(cudaMalloc(&out.nodes, sizeof(BvhNode) * (size_t)n_nodes));
         k_sah_emit<<<(n_nodes + 255) / 256, 256, 0, st>>>(n_nodes, pad, nd, out.nodes);
-        k_tri_records<<<G, B, 0, st>>>(d_pos, id_a, n, out.tri);
+        k_tri_records<<<G, B, 0, st>>>(d_pos, id_a, n, out.tri, out.tri_b);
         out.launches += 2;
         ORB_CU(cudaStreamSynchronize(st));
         out.root_ref = 0;

@@ -107,8 +107,8 @@ ORB_HD void trav_begin_q(TravState& t, const SceneView& s, const QGrid& g, float
 }
 
 // One inner node of the quantised hierarchy; stack and order exactly as trav_node_step().
-template <class IntPtr, class FltPtr>
-ORB_HD void trav_node_step_qn(TravState& t, const QNode* __restrict__ nodes, IntPtr stk, FltPtr stk_t, int stride) {
+template <class Stack>
+ORB_HD void trav_node_step_qn(TravState& t, const QNode* __restrict__ nodes, Stack& st) {
     const QNode* np = nodes + t.cur;
     uint32_t w0, w1, w2, w3, w4, w5;
     int c0, c1;
@@ -124,35 +124,28 @@ ORB_HD void trav_node_step_qn(TravState& t, const QNode* __restrict__ nodes, Int
     float tn0, tn1;
     const bool h0 = box_test(q_f_lo(w0), q_f_hi(w0), q_f_lo(w1), q_f_hi(w1), q_f_lo(w2), q_f_hi(w2), t.noi, t.inv, lim, tn0);
     const bool h1 = box_test(q_f_lo(w3), q_f_hi(w3), q_f_lo(w4), q_f_hi(w4), q_f_lo(w5), q_f_hi(w5), t.noi, t.inv, lim, tn1);
-    if (h0 && h1) {
-        const bool swap = tn1 < tn0;
-        stk[t.sp * stride] = swap ? c0 : c1;
-        stk_t[t.sp * stride] = swap ? tn0 : tn1;
-        ++t.sp;
-        t.cur = swap ? c1 : c0;
-    } else if (h0) {
-        t.cur = c0;
-    } else if (h1) {
-        t.cur = c1;
-    } else {
-        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
-    }
+    trav_descend(t, st, h0, h1, tn0, tn1, c0, c1);
 }
 
-template <class IntPtr, class FltPtr>
-ORB_HD Hit trace_closest_q(const SceneView& s, const QNode* nodes, const QGrid& g, float3 o, float3 d, IntPtr stk,
-                           FltPtr stk_t, int stride, unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+template <class Stack>
+ORB_HD Hit trace_closest_q(const SceneView& s, const QNode* nodes, const QGrid& g, float3 o, float3 d, Stack& st,
+                           unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
     TravState t;
     trav_begin_q(t, s, g, o, d);
     while (t.cur != ORB_TRAVERSAL_DONE) {
         while (t.cur >= 0) {
             if (n_nodes) ++*n_nodes;
-            trav_node_step_qn(t, nodes, stk, stk_t, stride);
+            trav_node_step_qn(t, nodes, st);
         }
         if (t.cur == ORB_TRAVERSAL_DONE) break;
-        trav_leaf_step(t, s, stk, stk_t, stride, n_tris);
+        trav_leaf_step(t, s, st, n_tris);
     }
     return t.best;
+}
+ORB_HD Hit trace_closest_q(const SceneView& s, const QNode* nodes, const QGrid& g, float3 o, float3 d, int* stk,
+                           float* stk_t, int stride, unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+    StridedStack st{stk, stk_t, stride};
+    return trace_closest_q(s, nodes, g, o, d, st, n_nodes, n_tris);
 }
 
 }  // namespace orb

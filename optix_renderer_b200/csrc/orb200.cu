@@ -35,6 +35,7 @@
 #include "bvh_refit.cuh"
 #include "bvhq.cuh"
 #include "pixel.cuh"
+#include "halo.cuh"
 
 using namespace orb;
 
@@ -86,11 +87,26 @@ struct FrameView {
 
 #define TRACE_BLOCK 128
 
-// shared-memory traversal stack, one column per thread: entry e of thread t at [e * TRACE_BLOCK + t]
-// (any mix of stack depths inside a warp is bank-conflict free)
+// Dynamic shared memory of the traversal kernels: the per-lane stack columns (scene.cuh HybridStack / StridedStack).
 extern __shared__ int s_dyn[];
 
-struct SmemTracer {
+// SD (template parameter of every traversal kernel) selects the stack:
+//   SD > 0   HybridStack: SD entries per lane in shared memory (SD * 8 * TRACE_BLOCK bytes per CTA), the rest local
+//   SD == 0  thread-local memory only (no shared memory)
+//   SD == -1 StridedStack: full-height shared-memory columns, for hierarchies deeper than ORB_LOCAL_STACK_MAX
+template <int SD> struct StackOf { typedef HybridStack<SD, TRACE_BLOCK> type; };
+template <> struct StackOf<-1> { typedef StridedStack type; };
+template <int SD>
+__device__ __forceinline__ void stack_init(HybridStack<SD, TRACE_BLOCK>& st, int) {
+    st.s = reinterpret_cast<unsigned long long*>(s_dyn) + threadIdx.x;
+}
+__device__ __forceinline__ void stack_init(StridedStack& st, int height) {
+    st.r = s_dyn + threadIdx.x;
+    st.t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
+    st.stride = TRACE_BLOCK;
+}
+
+struct SmemTracer {  // single-ray closest hit through full-height shared-memory columns (cold paths: literal / fused PATH)
     const SceneView& s;
     int* stk;
     float* stk_t;
@@ -105,19 +121,12 @@ struct SmemTracer {
 // k_primary
 // ---------------------------------------------------------------------------------------------
 // A warp covers an 8x4 pixel tile (coherent rays, 128-byte row segments on the float4 stores);
-// a 128-thread block covers 16x8.  LOCAL_STACK: traversal stack in thread-local memory (behind L1)
-// instead of shared-memory columns -- no shared memory, so residency is limited by registers only
-// (ncu profiles/r1c: 28 % warps active and 30 % of the samples waiting on the node fetch with the
-// shared-memory stack).
-#define LOCAL_STACK_MAX 64
-template <bool LOCAL_STACK>
+// a 128-thread block covers 16x8.  QN: inner nodes are the 32-byte quantised ones (bvhq.cuh).
+template <int SD, bool QN>
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int height) {
-    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
-    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    const int stk_stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
+k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int height, const QNode* __restrict__ qn, QGrid qg) {
+    typename StackOf<SD>::type st;
+    stack_init(st, height);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = f.y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -128,7 +137,7 @@ k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int 
         ofs = (size_t)py * f.W + px;
         float3 o, d;
         primary_ray(cam, frame_id, px, py, f.W, f.H, o, d);
-        const Hit h = trace_closest(s, o, d, stk, stk_t, stk_stride);
+        const Hit h = QN ? trace_closest_q(s, qn, qg, o, d, st) : trace_closest(s, o, d, st);
         const Surface si = shade_hit(s, h.prim, h.u, h.v);
         st_stream(f.hit + ofs, make_float4(__int_as_float(h.prim), h.u, h.v, h.t));
         st_stream(f.position + ofs, make_float4(si.p.x, si.p.y, si.p.z, 1.f));
@@ -286,20 +295,19 @@ __device__ __forceinline__ unsigned warp_claim(unsigned want, unsigned lane, uns
 // lanes busy in BOTH phases (profiles/r1c: 19.5 of 32 lanes in the node step, 9.8 in the triangle test).
 // QN: the inner nodes are the 32-byte quantised ones of bvhq.cuh (`qn`, grid `qg`; ORB_TRACE_VARIANT=3) -- one
 // 256-bit load per node instead of two; same hits (the encoding is conservative).
-// LOCAL_STACK: traversal stack in thread-local memory (behind L1) -- no shared memory, so residency is limited
-// by registers only; false: per-lane columns of shared memory, for hierarchies deeper than LOCAL_STACK_MAX.
-template <bool LOCAL_STACK, bool COUNT = false, bool QN = false>
-__global__ void __launch_bounds__(TRACE_BLOCK)
+// SD: where the traversal stack lives (StackOf above).
+#ifndef ORB_TRACE_MINB
+#define ORB_TRACE_MINB 9  // resident CTAs per SM the register allocation of the stream kernel aims at (56 registers)
+#endif
+template <int SD, bool COUNT = false, bool QN = false>
+__global__ void __launch_bounds__(TRACE_BLOCK, ORB_TRACE_MINB)
 k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __restrict__ hits,
                     const unsigned* __restrict__ n_items, unsigned mult, unsigned* __restrict__ cursor, int refill_min,
                     int node_min, int height, unsigned long long* __restrict__ stats = nullptr,
                     const QNode* __restrict__ qn = nullptr, QGrid qg = QGrid()) {
     unsigned c_nodes = 0, c_tris = 0;  // COUNT: node records fetched / triangle records tested by this lane
-    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
-    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
+    typename StackOf<SD>::type st;
+    stack_init(st, height);
     const unsigned n = *n_items * mult;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned FULL = 0xffffffffu;
@@ -338,12 +346,12 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
         for (int it = 0; it < 64; ++it) {
             if (COUNT && t.cur >= 0) ++c_nodes;
             if (t.cur >= 0) {
-                if (QN) trav_node_step_qn(t, qn, stk, stk_t, stride);
-                else trav_node_step(t, s, stk, stk_t, stride);
+                if (QN) trav_node_step_qn(t, qn, st);
+                else trav_node_step(t, s, st);
             }
             if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // postpone this leaf, keep walking
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(st, t.sp, t.best);
             }
             if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
         }
@@ -353,7 +361,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             leaf = 0;
             if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {  // a second leaf was waiting: it becomes the postponed one
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(st, t.sp, t.best);
             }
         }
     }
@@ -673,16 +681,13 @@ k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce,
 // from the active-pixel queue.  One launch per frame, one tail per frame, no path state in HBM.
 // Shading is batched like the refill: lanes whose ray has ended wait until `refill_min` of them
 // have (or nobody can advance), so the divergent shading code runs with a fair number of lanes.
-template <bool LOCAL_STACK, bool COUNT = false>
+template <int SD, bool COUNT = false, bool QN = false>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int depth, unsigned* __restrict__ cursor,
-                  int refill_min, int node_min, int height) {
+                  int refill_min, int node_min, int height, const QNode* __restrict__ qn, QGrid qg) {
     unsigned c_nodes = 0, c_tris = 0;  // COUNT (ORB_RENDER_COUNT_TRAVERSAL): node / triangle records fetched by this lane
-    int l_stk[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    float l_stk_t[LOCAL_STACK ? LOCAL_STACK_MAX : 1];
-    int* stk = LOCAL_STACK ? l_stk : s_dyn + threadIdx.x;
-    float* stk_t = LOCAL_STACK ? l_stk_t : reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    const int stride = LOCAL_STACK ? 1 : TRACE_BLOCK;
+    typename StackOf<SD>::type stk;
+    stack_init(stk, height);
     const unsigned n = f.cnt->queue_n;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned FULL = 0xffffffffu;
@@ -692,6 +697,11 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
     t.sp = 0;
     int leaf = 0;
     PathState st;
+    // what the shading of a bounce needs from the moment its ray was made (path_ray_setup): the two local
+    // directions and the pdf -- 7 registers carried across the traversal instead of re-deriving the basis, the five
+    // draws and the BSDF sample a second time per bounce (orb200.cu:912-918 against :962-967)
+    float3 q_wi = v3(0.f), q_wo = v3(0.f);
+    float q_pdf = 0.f;
     size_t ofs = 0;
     int bounce = 0;
     bool have_path = false, exhausted = false;
@@ -703,10 +713,10 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
         const unsigned busy = __ballot_sync(FULL, !ended);
         if (n_ended && ((int)n_ended >= refill_min || busy == 0u)) {
             if (ended && have_path) {  // shade this bounce
-                const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
-                Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
-                rng_skip(rng, 2 + 5 * bounce);
-                const PathSample q = path_ray_setup(st, rng);  // same arithmetic as when the ray was made
+                PathSample q;
+                q.wi_local = q_wi;
+                q.wo_local = q_wo;
+                q.bsdf_pdf = q_pdf;
                 float3 colour;
                 if (path_resolve(s, st, q, t.best, bounce == depth - 1, colour) == ORB_PATH_DONE) {
                     st_stream(f.colour + ofs, make_float4(colour.x, colour.y, colour.z, 1.f));
@@ -719,24 +729,8 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
             const bool claim = ended && !have_path && !exhausted;
             const unsigned want = __ballot_sync(FULL, claim);
             if (want) {
-                const unsigned need = __popc(want);
-                const unsigned left = w_end - w_next;
-                unsigned base = w_next;
-                unsigned chunk = STREAM_CHUNK;
-                if (left < need) {
-                    if (lane == 0) {
-                        const unsigned seen = *reinterpret_cast<volatile unsigned*>(cursor);
-                        const unsigned rem = n > seen ? n - seen : 0u;
-                        const unsigned warps = gridDim.x * (TRACE_BLOCK / 32);
-                        chunk = min(STREAM_CHUNK, max(32u, (rem / (2u * warps)) & ~31u));
-                        base = atomicAdd(cursor, chunk);
-                    }
-                    base = __shfl_sync(FULL, base, 0);
-                    chunk = __shfl_sync(FULL, chunk, 0);
-                }
-                const unsigned rank = __popc(want & ((1u << lane) - 1u));
+                const unsigned idx = warp_claim(want, lane, n, cursor, w_next, w_end);
                 if (claim) {
-                    const unsigned idx = left >= need ? w_next + rank : (rank < left ? w_next + rank : base + (rank - left));
                     if (idx < n) {
                         path_load_state<true>(f, cam_pos, none, idx, st, ofs);
                         bounce = 0;
@@ -745,19 +739,17 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
                         exhausted = true;
                     }
                 }
-                if (left >= need) {
-                    w_next += need;
-                } else {
-                    w_next = base + (need - left);
-                    w_end = base + chunk;
-                }
             }
             if (ended && have_path) {  // next ray of this path
                 const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
                 Rng rng = rng_seed(frame_id, (uint32_t)px, (uint32_t)py, (uint32_t)f.W);
                 rng_skip(rng, 2 + 5 * bounce);
                 const PathSample q = path_ray_setup(st, rng);
-                trav_begin(t, s, q.origin, q.dir);
+                q_wi = q.wi_local;
+                q_wo = q.wo_local;
+                q_pdf = q.bsdf_pdf;
+                if (QN) trav_begin_q(t, s, qg, q.origin, q.dir);
+                else trav_begin(t, s, q.origin, q.dir);
                 ++rays;
             }
         }
@@ -765,10 +757,13 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
 #pragma unroll 1
         for (int it = 0; it < 64; ++it) {  // node phase (speculative: one postponed leaf per lane)
             if (COUNT && t.cur >= 0) ++c_nodes;
-            if (t.cur >= 0) trav_node_step(t, s, stk, stk_t, stride);
+            if (t.cur >= 0) {
+                if (QN) trav_node_step_qn(t, qn, stk);
+                else trav_node_step(t, s, stk);
+            }
             if (leaf == 0 && t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(stk, t.sp, t.best);
             }
             if ((int)__popc(__ballot_sync(FULL, t.cur >= 0)) < node_min) break;
         }
@@ -777,7 +772,7 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
             leaf = 0;
             if (t.cur < 0 && t.cur != ORB_TRAVERSAL_DONE) {
                 leaf = t.cur;
-                t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+                t.cur = stack_pop(stk, t.sp, t.best);
             }
         }
     }
@@ -1099,11 +1094,45 @@ struct HostMesh {
     std::vector<uint8_t> tex;
 };
 
-struct OrbContext {
-    int device = 0;
+// Everything ONE FRAME IN FLIGHT owns.  A context has 1 (default) or 2 of these (orb_set_frame_slots): with two,
+// orb_render_async alternates between them, each on its own stream, so the kernels of frame i+1 fill the SMs that
+// the persistent traversal kernel of frame i leaves idle while its last rays finish (the fixed tail of every stage,
+// profiles/r1k_stage_floors.json: what limits a narrow band of a tile partition) and the issue slots it leaves
+// empty while it waits on node fetches.  Frames are independent except for the running sum: `accum` and RGBA8 are
+// SHARED between the slots and frame i+1's k_accumulate is ordered behind everything frame i's slot has enqueued.
+struct DlSlot { void* dev = nullptr; size_t cap = 0; cudaEvent_t ready = nullptr, done = nullptr; };
+struct FrameSlot {
     cudaStream_t stream = nullptr;
     bool own_stream = true;
+    void* buf[ORB_BUF_COUNT] = {nullptr};  // ORB_BUF_ACCUM / ORB_BUF_RGBA8: the same pointers in every slot
+    float4* colour = nullptr;
+    uint32_t* flags = nullptr;
+    uint32_t* queue = nullptr;
+    DevCounters* cnt = nullptr;
+    float4* path_state[2][5] = {{nullptr}};
+    float4* stream_rays = nullptr;   // 2 float4 per ray
+    float4* stream_hits = nullptr;   // 1 float4 per ray
+    size_t stream_cap = 0;
+    unsigned* stream_cursor = nullptr;
+    float2* dn_val_b = nullptr;  // ping-pong partner of ORB_BUF_DN_VAL
+    // orb_buffer_download_rows_async: the frame stream snapshots the rows into a device slot (two per buffer), the
+    // copy stream moves the slot to the host while the next frame renders.
+    DlSlot dl[ORB_BUF_COUNT][2];
+    int dl_next[ORB_BUF_COUNT] = {};
+    cudaEvent_t ev_order = nullptr;  // "everything enqueued on this slot so far" for the other slot's k_accumulate
+    int last_spp = 0;
+    bool rendered = false;           // a frame has been enqueued on this slot since the last resize
+    uint32_t halo_epoch = 0;         // frames whose packed denoise rows this slot has pushed to its peers (halo.cuh)
+};
+#define ORB_MAX_SLOTS 2
+
+// The context IS its active slot (the FrameSlot base: c->stream, c->buf, ... are the active frame's); the other
+// slot is parked in `parked` and swapped in by select_slot().
+struct OrbContext : FrameSlot {
+    int device = 0;
     int n_sm = 148;
+    int n_slots = 1, cur_slot = 0;
+    FrameSlot parked[ORB_MAX_SLOTS];
     // scene staging (host)
     std::vector<float> h_pos, h_nrm, h_uv;
     std::vector<int> h_prim_mesh;
@@ -1121,57 +1150,49 @@ struct OrbContext {
     BvhBuildResult bvh;
     SceneView view;
     bool committed = false;
-    QNode* qnodes = nullptr;  // ORB_TRACE_VARIANT=3: the hierarchy's inner nodes on the 16-bit grid (bvhq.cuh)
+    QNode* qnodes = nullptr;  // the hierarchy's inner nodes as 32-byte records on a 16-bit grid (bvhq.cuh)
     QGrid qgrid;
     bool geometry_dirty = false;  // orb_scene_update_mesh moved corners that orb_scene_refit has not seen yet
     int height = 1;  // stack entries per thread
     // frame
     int W = 0, H = 0;
-    void* buf[ORB_BUF_COUNT] = {nullptr};
-    float4* colour = nullptr;
-    uint32_t* flags = nullptr;
-    uint32_t* queue = nullptr;
-    DevCounters* cnt = nullptr;
-    float4* path_state[2][5] = {{nullptr}};
-    float4* stream_rays = nullptr;   // 2 float4 per ray
-    float4* stream_hits = nullptr;   // 1 float4 per ray
-    size_t stream_cap = 0;
-    unsigned* stream_cursor = nullptr;
     int refill_min = 12;
     int node_min = 16;
-    // ray-stream kernel: 1 = 64-byte fp32 nodes (default), 3 = 32-byte quantised nodes (bvhq.cuh; ORB_TRACE_VARIANT)
-    int trace_variant = 1;
+    // traversal kernels: 3 = 32-byte quantised inner nodes (bvhq.cuh; default), 1 = the 64-byte fp32 nodes (ORB_TRACE_VARIANT)
+    int trace_variant = 3;
     // > 0: shrink the stream kernel's grid until every lane expects this many rays.  Measured on a 135-row band:
     // 0.428 / 0.430 / 0.453 / 0.606 / 0.961 ms for 0 / 4 / 8 / 16 / 32 -- parallelism beats shorter tails.
     int min_rays_per_lane = 0;
-    cudaStream_t aux_stream = nullptr;  // RATIO: the LTC sum runs here, beside the shadow-ray kernels
-    // orb_buffer_download_rows_async: the frame stream snapshots the rows into a device slot (two per buffer), the
-    // copy stream moves the slot to the host while the next frame renders.
+    // persistent kernels: resident CTAs per SM the traversal kernels may take, 0 = all that fit.  With two frames
+    // in flight a full persistent grid would keep the other frame's CTAs out until it exits (ORB_TRACE_CTAS_PER_SM).
+    int trace_ctas_per_sm = 0;
     cudaStream_t copy_stream = nullptr;
-    struct DlSlot { void* dev = nullptr; size_t cap = 0; cudaEvent_t ready = nullptr, done = nullptr; };
-    DlSlot dl[ORB_BUF_COUNT][2];
-    int dl_next[ORB_BUF_COUNT] = {};
     int dl_snapshot_kernel = 1;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
-    int ltc_overlap = 0;  // measured: no gain (3.392 vs 3.394 ms per RATIO frame), kept as a knob
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
-    int local_stack = 1;  // measured: 2.96 -> 2.51 ms for the 1080p shadow stage (more resident warps)
-    float2* dn_val_b = nullptr;  // ping-pong partner of ORB_BUF_DN_VAL
+    int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
+    int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
     float* unit_out = nullptr;
     Camera cam;
     bool have_cam = false;
     OrbCounters counters;
-    int last_spp = 0;
     // per-stage timing (orb_set_profiling)
     bool profiling = false;
     struct StageSpan { int stage; int launches; cudaEvent_t e0, e1; };
     std::vector<StageSpan> spans;          // recorded since the last orb_get_stage_times
     std::vector<cudaEvent_t> free_events;  // recycled
+    HaloLinks halo;                        // peer-mapped denoise buffers of the other ranks of a tile partition (halo.cuh)
 };
+
+static void select_slot(OrbContext* c, int k) {
+    if (k == c->cur_slot) return;
+    c->parked[c->cur_slot] = *static_cast<FrameSlot*>(c);
+    *static_cast<FrameSlot*>(c) = c->parked[k];
+    c->cur_slot = k;
+}
 
 // RAII span: records an event pair around the launches of one stage when profiling is on
 struct StageTimer {
@@ -1205,7 +1226,7 @@ static void free_scene(OrbContext* c) {
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_prim_mesh); cudaFree(c->d_meshes);
     for (void* p : c->d_tex) cudaFree(p);
     c->d_tex.clear();
-    cudaFree(c->bvh.tri); cudaFree(c->bvh.nodes);
+    cudaFree(c->bvh.tri); cudaFree(c->bvh.tri_b); cudaFree(c->bvh.nodes);
     cudaFree(c->qnodes);
     c->qnodes = nullptr;
     c->d_pos = c->d_nrm = c->d_uv = nullptr;
@@ -1216,21 +1237,83 @@ static void free_scene(OrbContext* c) {
     c->geometry_dirty = false;
 }
 
+static size_t buffer_elem_bytes(int id);
+
+static void free_slot_frame(FrameSlot& f, bool owns_shared) {
+    for (int i = 0; i < ORB_BUF_COUNT; i++) {
+        if (owns_shared || (i != ORB_BUF_ACCUM && i != ORB_BUF_RGBA8)) cudaFree(f.buf[i]);
+        f.buf[i] = nullptr;
+    }
+    cudaFree(f.colour); cudaFree(f.flags); cudaFree(f.queue);
+    for (int a = 0; a < 2; a++) for (int b = 0; b < 5; b++) { cudaFree(f.path_state[a][b]); f.path_state[a][b] = nullptr; }
+    cudaFree(f.dn_val_b);
+    cudaFree(f.stream_rays); cudaFree(f.stream_hits);
+    f.stream_rays = f.stream_hits = nullptr;
+    f.stream_cap = 0;
+    f.colour = nullptr; f.flags = nullptr; f.queue = nullptr; f.dn_val_b = nullptr;
+    f.rendered = false;
+}
+
 static void free_frame(OrbContext* c) {
-    for (int i = 0; i < ORB_BUF_COUNT; i++) { cudaFree(c->buf[i]); c->buf[i] = nullptr; }
-    cudaFree(c->colour); cudaFree(c->flags); cudaFree(c->queue);
-    for (int a = 0; a < 2; a++) for (int b = 0; b < 5; b++) { cudaFree(c->path_state[a][b]); c->path_state[a][b] = nullptr; }
-    cudaFree(c->dn_val_b);
-    cudaFree(c->stream_rays); cudaFree(c->stream_hits);
-    c->stream_rays = c->stream_hits = nullptr;
-    c->stream_cap = 0;
-    c->colour = nullptr; c->flags = nullptr; c->queue = nullptr; c->dn_val_b = nullptr;
+    select_slot(c, 0);
+    free_slot_frame(*c, true);
+    for (int k = 1; k < ORB_MAX_SLOTS; k++) free_slot_frame(c->parked[k], false);
     c->W = c->H = 0;
+}
+
+// stream and counters of a slot (everything of a slot that does not depend on the frame size)
+static int init_slot(FrameSlot& f) {
+    if (!f.stream) {
+        CK(cudaStreamCreateWithFlags(&f.stream, cudaStreamNonBlocking));
+        f.own_stream = true;
+    }
+    if (!f.cnt) {
+        CK(cudaMalloc(&f.cnt, sizeof(DevCounters)));
+        CK(cudaMemset(f.cnt, 0, sizeof(DevCounters)));
+    }
+    return ORB_OK;
+}
+
+static void destroy_slot(FrameSlot& f) {
+    if (f.stream) cudaStreamSynchronize(f.stream);
+    cudaFree(f.stream_cursor);
+    cudaFree(f.cnt);
+    f.stream_cursor = nullptr;
+    f.cnt = nullptr;
+    for (auto& per_buf : f.dl)
+        for (auto& sl : per_buf) {
+            cudaFree(sl.dev);
+            if (sl.ready) cudaEventDestroy(sl.ready);
+            if (sl.done) cudaEventDestroy(sl.done);
+            sl = DlSlot();
+        }
+    if (f.ev_order) cudaEventDestroy(f.ev_order);
+    f.ev_order = nullptr;
+    if (f.own_stream && f.stream) cudaStreamDestroy(f.stream);
+    f.stream = nullptr;
+}
+
+// frame buffers of one slot; slot 0 owns the shared accum / RGBA8
+static int alloc_slot_frame(FrameSlot& f, const FrameSlot* shared_from, int W, int H) {
+    const size_t n = (size_t)W * H;
+    for (int i = 0; i < ORB_BUF_COUNT; i++) {
+        if (shared_from && (i == ORB_BUF_ACCUM || i == ORB_BUF_RGBA8)) {
+            f.buf[i] = shared_from->buf[i];
+            continue;
+        }
+        CK(cudaMalloc(&f.buf[i], n * buffer_elem_bytes(i)));
+        CK(cudaMemset(f.buf[i], 0, n * buffer_elem_bytes(i)));
+    }
+    CK(cudaMalloc(&f.colour, n * 16)); CK(cudaMemset(f.colour, 0, n * 16));
+    CK(cudaMalloc(&f.flags, n * 4)); CK(cudaMemset(f.flags, 0, n * 4));
+    CK(cudaMalloc(&f.queue, n * 4));
+    return ORB_OK;
 }
 
 static void refresh_view(OrbContext* c) {
     SceneView& v = c->view;
     v.tri = c->bvh.tri;
+    v.tri_b = c->bvh.tri_b;
     v.nodes = c->bvh.nodes;
     v.root_ref = c->bvh.root_ref;
     v.n_tris = (int)c->h_prim_mesh.size();
@@ -1285,22 +1368,55 @@ static cudaError_t allow_smem(K kernel, size_t bytes) {
     return e;
 }
 
-// persistent grid: resident CTAs per SM x SM count
+// persistent grid: resident CTAs per SM x SM count (`cap` > 0 limits the CTAs per SM: room for another frame's kernels)
 template <class K>
-static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem) {
+static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem, int cap = 0) {
     int per_sm = 1;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    if (cap > 0) per_sm = std::min(per_sm, cap);
     return per_sm * c->n_sm;
 }
+
+// ---- which instantiation of a traversal kernel a context launches --------------------------------------------
+// stack form (template parameter SD of the kernels) and the dynamic shared memory it needs
+static int stack_mode(OrbContext* c) { return (c->local_stack && c->height <= ORB_LOCAL_STACK_MAX) ? c->stack_smem : -1; }
+static size_t stack_bytes(OrbContext* c, int sd) { return sd < 0 ? trace_smem(c) : (size_t)sd * 8 * TRACE_BLOCK; }
+// 32-byte quantised inner nodes (default) or the 64-byte fp32 ones (ORB_TRACE_VARIANT=1)
+static bool use_qnodes(OrbContext* c) { return c->trace_variant == 3 && c->qnodes != nullptr; }
+
+typedef void (*StreamKernel)(SceneView, const float4*, float4*, const unsigned*, unsigned, unsigned*, int, int, int,
+                             unsigned long long*, const QNode*, QGrid);
+typedef void (*PrimaryKernel)(SceneView, FrameView, Camera, int, int, int, const QNode*, QGrid);
+typedef void (*PathKernel)(SceneView, FrameView, float3, int, int, unsigned*, int, int, int, const QNode*, QGrid);
+template <int SD> static StreamKernel stream_kernel_sd(bool count, bool qn) {
+    return qn ? (count ? k_trace_stream_spec<SD, true, true> : k_trace_stream_spec<SD, false, true>)
+              : (count ? k_trace_stream_spec<SD, true, false> : k_trace_stream_spec<SD, false, false>);
+}
+template <int SD> static PathKernel path_kernel_sd(bool count, bool qn) {
+    return qn ? (count ? k_path_persistent<SD, true, true> : k_path_persistent<SD, false, true>)
+              : (count ? k_path_persistent<SD, true, false> : k_path_persistent<SD, false, false>);
+}
+template <int SD> static PrimaryKernel primary_kernel_sd(bool qn) { return qn ? k_primary<SD, true> : k_primary<SD, false>; }
+#define ORB_SD_SWITCH(sd, F, ...)                \
+    switch (sd) {                                \
+        case 0: return F<0>(__VA_ARGS__);        \
+        case 8: return F<8>(__VA_ARGS__);        \
+        case 12: return F<12>(__VA_ARGS__);      \
+        case 16: return F<16>(__VA_ARGS__);      \
+        default: return F<-1>(__VA_ARGS__);      \
+    }
+static StreamKernel stream_kernel(int sd, bool count, bool qn) { ORB_SD_SWITCH(sd, stream_kernel_sd, count, qn) }
+static PathKernel path_kernel(int sd, bool count, bool qn) { ORB_SD_SWITCH(sd, path_kernel_sd, count, qn) }
+static PrimaryKernel primary_kernel(int sd, bool qn) { ORB_SD_SWITCH(sd, primary_kernel_sd, qn) }
 
 __global__ void k_quantise_nodes(const BvhNode* __restrict__ nodes, int n, QGrid g, QNode* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = q_encode(nodes[i], g);
 }
 
-// ORB_TRACE_VARIANT=3: (re-)encode the inner nodes for the ray-stream kernel; after a build and after a refit.
+// (re-)encode the inner nodes as the 32-byte records the traversal kernels read; after a build and after a refit.
 static int build_qnodes(OrbContext* c) {
-    if (c->trace_variant != 3 || c->bvh.n_nodes <= 0 || c->bvh.root_ref < 0) return ORB_OK;
+    if (c->bvh.n_nodes <= 0 || c->bvh.root_ref < 0) return ORB_OK;
     BvhNode root;
     CK(cudaMemcpyAsync(&root, c->bvh.nodes + c->bvh.root_ref, sizeof root, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -1332,25 +1448,24 @@ int orb_create(int device, OrbContext** out) {
     OrbContext* c = new OrbContext();
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
-    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CK(cudaMalloc(&c->cnt, sizeof(DevCounters)));
-    CK(cudaMemset(c->cnt, 0, sizeof(DevCounters)));
+    {
+        int rc = init_slot(*c);
+        if (rc) return rc;
+    }
     CK(cudaMalloc(&c->unit_in, 64 * sizeof(float)));
     CK(cudaMalloc(&c->unit_out, 4096 * sizeof(float)));
     memset(&c->counters, 0, sizeof(c->counters));
     memset(&c->view, 0, sizeof(c->view));
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
+    if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
+    if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
     if (const char* e = getenv("ORB_PATH_PERSISTENT")) c->path_persistent = atoi(e);
-    if (const char* e = getenv("ORB_LTC_OVERLAP")) c->ltc_overlap = atoi(e);
     if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
     if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
     if (const char* e = getenv("ORB_DL_SNAPSHOT_KERNEL")) c->dl_snapshot_kernel = atoi(e);
-    CK(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
-    CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     if (const char* e = getenv("ORB_PATH_SHADE_MIN")) c->path_shade_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_PATH_NODE_MIN")) c->path_node_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
@@ -1360,26 +1475,46 @@ int orb_create(int device, OrbContext** out) {
 void orb_destroy(OrbContext* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    select_slot(c, 0);
     cudaStreamSynchronize(c->stream);
+    for (int k = 1; k < ORB_MAX_SLOTS; k++)
+        if (c->parked[k].stream) cudaStreamSynchronize(c->parked[k].stream);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    halo_disconnect(c->halo);
     free_scene(c);
     free_frame(c);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto e : c->free_events) cudaEventDestroy(e);
-    cudaFree(c->stream_cursor);
-    cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->cnt); cudaFree(c->unit_in); cudaFree(c->unit_out);
-    if (c->own_stream) cudaStreamDestroy(c->stream);
-    if (c->aux_stream) { cudaStreamSynchronize(c->aux_stream); cudaStreamDestroy(c->aux_stream); }
-    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
-    for (auto& per_buf : c->dl)
-        for (auto& sl : per_buf) {
-            cudaFree(sl.dev);
-            if (sl.ready) cudaEventDestroy(sl.ready);
-            if (sl.done) cudaEventDestroy(sl.done);
-        }
-    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    cudaFree(c->d_lights); cudaFree(c->d_lut); cudaFree(c->unit_in); cudaFree(c->unit_out);
+    destroy_slot(*c);
+    for (int k = 1; k < ORB_MAX_SLOTS; k++) destroy_slot(c->parked[k]);
     delete c;
 }
+
+// Frames in flight (1 or 2).  With 2, consecutive orb_render_async calls alternate between two sets of frame buffers
+// and two streams; `accum` / RGBA8 stay shared and accumulate in call order.  Re-allocates the frame buffers.
+int orb_set_frame_slots(OrbContext* c, int32_t n) {
+    NEED(c && n >= 1 && n <= ORB_MAX_SLOTS, "orb_set_frame_slots: 1 or 2 slots");
+    CK(cudaSetDevice(c->device));
+    int rc = orb_sync(c);
+    if (rc) return rc;
+    NEED(c->halo.n_peers == 0, "orb_set_frame_slots: disconnect the halo peers first (their buffers are re-allocated)");
+    const int W = c->W, H = c->H;
+    free_frame(c);  // back on slot 0
+    for (int k = 1; k < ORB_MAX_SLOTS; k++) {
+        if (k < n) {
+            rc = init_slot(c->parked[k]);
+            if (rc) return rc;
+        } else {
+            destroy_slot(c->parked[k]);
+        }
+    }
+    c->n_slots = n;
+    return W > 0 ? orb_resize(c, W, H) : ORB_OK;
+}
+
+int32_t orb_frame_slot(OrbContext* c) { return c ? c->cur_slot : -1; }
+int32_t orb_frame_slots(OrbContext* c) { return c ? c->n_slots : 0; }
 
 void* orb_stream(OrbContext* c) { return c ? (void*)c->stream : nullptr; }
 
@@ -1393,10 +1528,12 @@ int orb_set_stream(OrbContext* c, void* stream) {
     return ORB_OK;
 }
 
-int orb_sync(OrbContext* c) {
+int orb_sync(OrbContext* c) {  // every frame in flight
     NEED(c, "orb_sync: ctx is NULL");
     CK(cudaSetDevice(c->device));
     CK(cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < c->n_slots; k++)
+        if (k != c->cur_slot && c->parked[k].stream) CK(cudaStreamSynchronize(c->parked[k].stream));
     return ORB_OK;
 }
 
@@ -1408,8 +1545,10 @@ int orb_set_profiling(OrbContext* c, int enable) {
 
 int orb_get_stage_times(OrbContext* c, OrbStageTimes* out) {
     NEED(c && out, "orb_get_stage_times: NULL argument");
-    CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
+    {
+        int rc = orb_sync(c);
+        if (rc) return rc;
+    }
     memset(out, 0, sizeof(*out));
     for (auto& sp : c->spans) {
         float ms = 0.f;
@@ -1573,9 +1712,6 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     c->height = c->bvh.height + 2;
     if (trace_smem(c) > 200 * 1024)
         return fail(ORB_ERR_INVALID, "orb_scene_commit: BVH too deep for the shared-memory traversal stack");
-    CK(allow_smem(k_primary<false>, trace_smem(c)));
-    CK(allow_smem(k_trace_stream_spec<false, false>, trace_smem(c)));
-    CK(allow_smem(k_trace_stream_spec<false, true>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<true>, trace_smem(c)));
     CK(allow_smem(k_path_bounce<false>, trace_smem(c)));
     CK(allow_smem(k_trace_rays, trace_smem(c)));
@@ -1660,16 +1796,20 @@ int orb_resize(OrbContext* c, int32_t W, int32_t H) {
     NEED(c && W > 0 && H > 0, "orb_resize: bad size");
     NEED((size_t)W * (size_t)H < ((size_t)1 << 31), "orb_resize: frames are limited to 2^31 - 1 pixels (32-bit pixel offsets)");
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
-    free_frame(c);
-    const size_t n = (size_t)W * H;
-    for (int i = 0; i < ORB_BUF_COUNT; i++) {
-        CK(cudaMalloc(&c->buf[i], n * buffer_elem_bytes(i)));
-        CK(cudaMemset(c->buf[i], 0, n * buffer_elem_bytes(i)));
+    {
+        int rc = orb_sync(c);
+        if (rc) return rc;
     }
-    CK(cudaMalloc(&c->colour, n * 16)); CK(cudaMemset(c->colour, 0, n * 16));
-    CK(cudaMalloc(&c->flags, n * 4)); CK(cudaMemset(c->flags, 0, n * 4));
-    CK(cudaMalloc(&c->queue, n * 4));
+    NEED(c->halo.n_peers == 0, "orb_resize: disconnect the halo peers first (their buffers are re-allocated)");
+    free_frame(c);  // leaves slot 0 active
+    {
+        int rc = alloc_slot_frame(*c, nullptr, W, H);
+        if (rc) return rc;
+        for (int k = 1; k < c->n_slots; k++) {
+            rc = alloc_slot_frame(c->parked[k], c, W, H);
+            if (rc) return rc;
+        }
+    }
     c->W = W; c->H = H;
     return ORB_OK;
 }
@@ -1694,15 +1834,12 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
     cudaStream_t st = c->stream;
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
     StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
-    const bool local = c->local_stack && c->height <= LOCAL_STACK_MAX;
-    const size_t smem = local ? 0 : trace_smem(c);
-    const bool qn = c->trace_variant == 3 && c->qnodes && local;  // 32-byte nodes
-    typedef void (*Kernel)(SceneView, const float4*, float4*, const unsigned*, unsigned, unsigned*, int, int, int,
-                           unsigned long long*, const QNode*, QGrid);
-    Kernel k = qn ? (count ? k_trace_stream_spec<true, true, true> : k_trace_stream_spec<true, false, true>)
-               : local ? (count ? k_trace_stream_spec<true, true> : k_trace_stream_spec<true, false>)
-                       : (count ? k_trace_stream_spec<false, true> : k_trace_stream_spec<false, false>);
-    int g = persistent_grid(c, k, TRACE_BLOCK, smem);
+    const int sd = stack_mode(c);
+    const size_t smem = stack_bytes(c, sd);
+    const bool qn = use_qnodes(c);
+    StreamKernel k = stream_kernel(sd, count, qn);
+    if (smem > 48 * 1024) CK(allow_smem(k, smem));
+    int g = persistent_grid(c, k, TRACE_BLOCK, smem, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
     // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
     // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.
     if (c->min_rays_per_lane > 0 && n_upper > 0)
@@ -1723,6 +1860,18 @@ static int ensure_path_state(OrbContext* c) {
     return ORB_OK;
 }
 
+// Two frame slots: `accum` and RGBA8 are shared, so this frame's k_accumulate (on the active slot's stream) is ordered
+// behind EVERYTHING the previous frame's slot has enqueued so far -- its own k_accumulate, and whatever read the shared
+// buffers after it (snapshots of orb_buffer_download_rows_async, a caller's copies on that slot's stream).
+static int order_behind_other_slot(OrbContext* c, int prev_slot, bool prev_rendered) {
+    if (c->n_slots < 2 || prev_slot == c->cur_slot || !prev_rendered) return ORB_OK;
+    FrameSlot& p = c->parked[prev_slot];
+    if (!p.ev_order) CK(cudaEventCreateWithFlags(&p.ev_order, cudaEventDisableTiming));
+    CK(cudaEventRecord(p.ev_order, p.stream));
+    CK(cudaStreamWaitEvent(c->stream, p.ev_order, 0));
+    return ORB_OK;
+}
+
 int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     NEED(c && cfg, "orb_render: NULL argument");
     NEED(c->committed, "orb_render: scene not committed");
@@ -1739,6 +1888,12 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     const int spp = mode == 0 ? 4 : (cfg->shadow_spp > 0 ? cfg->shadow_spp : 4);      // deviceCode.cu:128
     const int depth = mode == 0 ? 1 : (cfg->max_depth > 0 ? cfg->max_depth : 1);      // deviceCode.cu:151
     CK(cudaSetDevice(c->device));
+    // two frames in flight: this frame takes the other slot (its own buffers and stream); everything the caller
+    // enqueues next (denoise, combine, downloads, orb_stream()) refers to it until the next orb_render_async
+    const int prev_slot = c->cur_slot;
+    const bool prev_rendered = c->rendered;
+    if (c->n_slots > 1) select_slot(c, (c->cur_slot + 1) % c->n_slots);
+    c->rendered = true;
     cudaStream_t st = c->stream;
     FrameView f = frame_view(c, y0, y1);
     const int frame_id = cfg->accum_id + 10007;  // deviceCode.cu:65
@@ -1748,18 +1903,17 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     {
         StageTimer tm(c, ORB_STAGE_PRIMARY, 1);
         dim3 grid((c->W + 15) / 16, (y1 - y0 + 7) / 8);
-        if (c->local_stack && c->height <= LOCAL_STACK_MAX)
-            k_primary<true><<<grid, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
-        else
-            k_primary<false><<<grid, TRACE_BLOCK, smem, st>>>(c->view, f, c->cam, frame_id, renderer, c->height);
+        const int sd = stack_mode(c);
+        const size_t sm = stack_bytes(c, sd);
+        const bool qn = use_qnodes(c);
+        PrimaryKernel k = primary_kernel(sd, qn);
+        if (sm > 48 * 1024) CK(allow_smem(k, sm));
+        k<<<grid, TRACE_BLOCK, sm, st>>>(c->view, f, c->cam, frame_id, renderer, c->height, qn ? c->qnodes : (const QNode*)nullptr,
+                                         qn ? c->qgrid : QGrid());
         c->counters.kernel_launches++;
         if (count_rays) c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
     }
     const float4* colour_src = c->colour;
-    // RATIO: the LTC sum (fp32-issue bound, no dependence on the shadow rays) is enqueued on a second
-    // stream AFTER the shadow-ray kernels, so its CTAs fill the SMs the persistent traversal kernel
-    // leaves idle while its last rays finish (floor of ~0.17 ms per traversal launch, profiles/r1k).
-    const bool ltc_beside_shadow = renderer == ORB_RATIO && c->ltc_overlap && !(cfg->flags & ORB_RENDER_DEFER_LTC);
     auto launch_ltc = [&](cudaStream_t ls) {
         StageTimer tm(c, ORB_STAGE_LTC, 1, ls);
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
@@ -1772,11 +1926,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
         c->counters.kernel_launches++;
     };
-    // ORB_RENDER_DEFER_LTC (RATIO): stop after the shadow rays; orb_render_finish() runs the LTC sum and the
-    // accumulation later, e.g. while a tile partition's denoise halo is in flight
-    const bool defer_ltc = renderer == ORB_RATIO && (cfg->flags & ORB_RENDER_DEFER_LTC);
-    if ((renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && !ltc_beside_shadow && !defer_ltc) launch_ltc(st);
-    if (ltc_beside_shadow) CK(cudaEventRecord(c->ev_fork, st));  // k_primary done: queue and G-buffers are final
+    if (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) launch_ltc(st);
     if (renderer == ORB_RATIO) {
         {
             const size_t npx = (size_t)(y1 - y0) * c->W;
@@ -1793,11 +1943,6 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                 rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true,
                                          npx * (size_t)spp);
                 if (rc) return rc;
-            }
-            if (ltc_beside_shadow) {  // depends on k_primary only, but is SUBMITTED behind the traversal kernel
-                CK(cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
-                launch_ltc(c->aux_stream);
-                CK(cudaEventRecord(c->ev_join, c->aux_stream));
             }
             StageTimer tm(c, ORB_STAGE_SHADOW, 1);
             const int gr = (int)std::min<size_t>((npx + 127) / 128, (size_t)c->n_sm * 8);
@@ -1817,17 +1962,21 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     if (renderer == ORB_PATH) {
         int rc = ORB_OK;
         const bool stream = mode == ORB_MODE_INTENDED && !(cfg->flags & ORB_RENDER_FUSED_SHADOW);
-        const bool persistent = stream && c->path_persistent && !(cfg->flags & ORB_RENDER_PATH_WAVEFRONT) &&
-                                c->local_stack && c->height <= LOCAL_STACK_MAX;
+        const bool persistent = stream && c->path_persistent && !(cfg->flags & ORB_RENDER_PATH_WAVEFRONT);
         if (persistent) {
             rc = ensure_stream(c, 1);  // the cursor
             if (rc) return rc;
             StageTimer tm(c, ORB_STAGE_PATH, 1);
             CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
-            auto k = (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) ? k_path_persistent<true, true> : k_path_persistent<true, false>;
-            const int g = persistent_grid(c, k, TRACE_BLOCK, 0);
-            k<<<g, TRACE_BLOCK, 0, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor, c->path_shade_min,
-                                         c->path_node_min, c->height);
+            const int sd = stack_mode(c);
+            const size_t sm = stack_bytes(c, sd);
+            const bool qn = use_qnodes(c);
+            PathKernel k = path_kernel(sd, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, qn);
+            if (sm > 48 * 1024) CK(allow_smem(k, sm));
+            const int g = persistent_grid(c, k, TRACE_BLOCK, sm, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
+            k<<<g, TRACE_BLOCK, sm, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor, c->path_shade_min,
+                                          c->path_node_min, c->height, qn ? c->qnodes : (const QNode*)nullptr,
+                                          qn ? c->qgrid : QGrid());
             c->counters.kernel_launches++;
         } else {
         rc = ensure_path_state(c);
@@ -1879,41 +2028,13 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         }
         }
     }
-    if (ltc_beside_shadow) CK(cudaStreamWaitEvent(st, c->ev_join, 0));
-    if (!defer_ltc) {
+    {
+        int rc = order_behind_other_slot(c, prev_slot, prev_rendered);
+        if (rc) return rc;
         StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
         const size_t n = (size_t)(y1 - y0) * c->W;
         const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
         k_accumulate<<<g, 256, 0, st>>>(f, colour_src, cfg->accum_id, count_rays);
-        c->counters.kernel_launches++;
-    }
-    CK(cudaGetLastError());
-    return ORB_OK;
-}
-
-// Second half of a RATIO frame rendered with ORB_RENDER_DEFER_LTC: the LTC sum over the frame's active-pixel
-// queue and the accumulation, with the same config (rows, accumId).  Asynchronous.
-int orb_render_finish(OrbContext* c, const OrbRenderConfig* cfg) {
-    NEED(c && cfg, "orb_render_finish: NULL argument");
-    NEED(c->committed && c->W > 0 && c->have_cam && c->lut_w > 0, "orb_render_finish: no frame to finish");
-    NEED(cfg->renderer_type == ORB_RATIO && (cfg->flags & ORB_RENDER_DEFER_LTC),
-         "orb_render_finish: only after a RATIO orb_render with ORB_RENDER_DEFER_LTC");
-    int y0 = cfg->y0, y1 = cfg->y1;
-    NEED(rows_ok(c, y0, y1), "orb_render_finish: bad row range");
-    CK(cudaSetDevice(c->device));
-    cudaStream_t st = c->stream;
-    FrameView f = frame_view(c, y0, y1);
-    {
-        StageTimer tm(c, ORB_STAGE_LTC, 1);
-        const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
-        k_ltc<true><<<g, LTC_BLOCK, 0, st>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
-        c->counters.kernel_launches++;
-    }
-    {
-        StageTimer tm(c, ORB_STAGE_ACCUMULATE, 1);
-        const size_t n = (size_t)(y1 - y0) * c->W;
-        const int g = (int)std::min<size_t>((n + 255) / 256, (size_t)c->n_sm * 8);
-        k_accumulate<<<g, 256, 0, st>>>(f, f.ltc, cfg->accum_id, (cfg->flags & ORB_RENDER_NO_COUNT) ? 0 : 1);
         c->counters.kernel_launches++;
     }
     CK(cudaGetLastError());
@@ -2108,7 +2229,7 @@ int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t
     CK(cudaSetDevice(c->device));
     if (!c->copy_stream) CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     const size_t row = (size_t)c->W * buffer_elem_bytes(id), bytes = row * (y1 - y0);
-    OrbContext::DlSlot& sl = c->dl[id][c->dl_next[id]];
+    DlSlot& sl = c->dl[id][c->dl_next[id]];
     c->dl_next[id] ^= 1;
     if (!sl.ready) {
         CK(cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
@@ -2171,6 +2292,15 @@ int orb_get_counters(OrbContext* c, OrbCounters* out) {
     out->rays_shadow_total = d.tot_shadow;
     out->rays_bounce_total = d.tot_bounce;
     out->active_pixels_total = d.tot_active;
+    for (int k = 0; k < c->n_slots; k++) {  // the running totals are kept per slot
+        if (k == c->cur_slot || !c->parked[k].cnt) continue;
+        DevCounters o;
+        CK(cudaMemcpyAsync(&o, c->parked[k].cnt, sizeof(o), cudaMemcpyDeviceToHost, c->parked[k].stream));
+        CK(cudaStreamSynchronize(c->parked[k].stream));
+        out->rays_shadow_total += o.tot_shadow;
+        out->rays_bounce_total += o.tot_bounce;
+        out->active_pixels_total += o.tot_active;
+    }
     return ORB_OK;
 }
 

@@ -10,11 +10,12 @@
 //   barycentricInterpolate, cuda_include/utils.cuh:10-29
 //
 // HBM layout (all arrays 16-byte aligned, built once per scene, replicated per GPU):
-//   tri      3 x float4 per triangle in BVH-leaf order: (v0.xyz, global prim id), (e1.xyz, 0),
-//            (e2.xyz, 0) with e1 = v1 - v0, e2 = v2 - v0 rounded in fp32 -- the operands the
-//            checker's Moeller-Trumbore forms at test time.  48 B, three 128-bit loads.
+//   tri, tri_b   per triangle in BVH-leaf order: 32 bytes (v0.xyz, global prim id | e1.xyz, e2.x) + 8 bytes
+//            (e2.y, e2.z), with e1 = v1 - v0, e2 = v2 - v0 rounded in fp32 -- the operands the checker's
+//            Moeller-Trumbore forms at test time.  One 256-bit and one 64-bit load per lane.
 //   nodes    64-byte BVH2 nodes, each holding BOTH child boxes and both child references, so
-//            one node fetch (four 128-bit loads, one 64-B sector pair) decides two subtrees.
+//            one node fetch (two 256-bit loads) decides two subtrees; the traversal kernels read the
+//            32-byte quantised copy of them (bvhq.cuh), the builders and the refit these.
 //   pos/nrm/uv  per-global-primitive corner attributes, un-indexed like the reference's meshes
 //            (src/Model.cpp:186-201): 9 + 9 + 6 floats, gathered only at the closest hit.
 //   prim_mesh, meshes   global prim -> mesh record (TriangleMeshData without the pointers).
@@ -49,7 +50,8 @@ struct MeshRec {  // TriangleMeshData, cuda_include/common.cuh:130-151, minus po
 };
 
 struct SceneView {
-    const float4* tri;
+    const float4* tri;    // 2 x float4 per triangle: (v0.xyz, prim id) (e1.xyz, e2.x)
+    const float2* tri_b;  // (e2.y, e2.z)
     const BvhNode* nodes;
     int root_ref;  // child-style reference of the root; 0 triangles -> n_tris == 0
     int n_tris;
@@ -69,6 +71,31 @@ struct Hit {
 };
 
 #define ORB_TMAX 1e30f  // owl::RayT default tmax; tmin = 0
+
+// Triangle record k as the three operands of tri_test(): (v0, prim id), (e1, -), (e2, -).
+ORB_HD void tri_record(float* a8, float* b2, const float* p9, int prim) {  // writer side: builders, refit, CPU checks
+    a8[0] = p9[0], a8[1] = p9[1], a8[2] = p9[2], a8[3] = __int_as_float_hd(prim);
+    a8[4] = xsub(p9[3], p9[0]), a8[5] = xsub(p9[4], p9[1]), a8[6] = xsub(p9[5], p9[2]);
+    a8[7] = xsub(p9[6], p9[0]);
+    b2[0] = xsub(p9[7], p9[1]), b2[1] = xsub(p9[8], p9[2]);
+}
+ORB_HD void tri_fetch(const SceneView& s, int k, float4& t0, float4& t1, float4& t2) {
+#ifdef __CUDA_ARCH__
+    float e2x;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(t0.x), "=f"(t0.y), "=f"(t0.z), "=f"(t0.w), "=f"(t1.x), "=f"(t1.y), "=f"(t1.z), "=f"(e2x)
+        : "l"(s.tri + 2 * (size_t)k));
+    const float2 b = __ldg(s.tri_b + k);
+#else
+    const float4 a0 = s.tri[2 * (size_t)k], a1 = s.tri[2 * (size_t)k + 1];
+    const float2 b = s.tri_b[k];
+    const float e2x = a1.w;
+    t0 = a0;
+    t1 = a1;
+#endif
+    t1.w = 0.f;
+    t2 = make_float4(e2x, b.x, b.y, 0.f);
+}
 
 // Moeller-Trumbore exactly as oracle/trace_cpu.h tri_test(): every rounding step is explicit.
 ORB_HD bool tri_test(float4 t0, float4 t1, float4 t2, float3 o, float3 d, float tmin, float tmax, float& t, float& u,
@@ -128,24 +155,72 @@ ORB_HD bool box_test(float lox, float loy, float loz, float hix, float hiy, floa
 // until it holds a leaf (or is finished) and only then does the warp run the triangle tests, so
 // the expensive Moeller-Trumbore block executes with most lanes active instead of the two or
 // three that happened to reach a leaf in the same iteration (ncu, profiles/r1a: 2.3 active lanes
-// in the leaf block of the if-if form).  STACK entries live where the caller put them
-// (`stk`/`stk_t` index stride `stride`): shared memory interleaved per lane in the kernels, a
-// plain array on the CPU.  The result does not depend on the visiting order (closest t, ties to
-// the lowest primitive id), so any BVH and any order agree bit for bit.
+// in the leaf block of the if-if form).  The result does not depend on the visiting order (closest t,
+// ties to the lowest primitive id), so any BVH and any order agree bit for bit.
 #define ORB_TRAVERSAL_DONE ((int)0x80000000)  // never a leaf reference: first + count < 2^28
 
-template <class IntPtr, class FltPtr>
-ORB_HD int stack_pop(IntPtr stk, FltPtr stk_t, int stride, int& sp, const Hit& best) {
-    for (;;) {  // skip subtrees that start beyond the current closest hit
+// ---- traversal stacks: entry = (child reference, entry distance of its box) --------------------------------
+// StridedStack: two arrays indexed [i * stride] -- plain arrays on the CPU, thread-local arrays (stride 1), or
+// per-lane columns of shared memory (entry e of thread t at [e * BLOCK + t]: any mix of stack depths inside a
+// warp is bank-conflict free).
+struct StridedStack {
+    int* r;
+    float* t;
+    int stride;
+    ORB_HD void put(int i, int ref, float tn) const {
+        r[i * stride] = ref;
+        t[i * stride] = tn;
+    }
+    ORB_HD float dist(int i) const { return t[i * stride]; }
+    ORB_HD int ref(int i) const { return r[i * stride]; }
+};
+
+// HybridStack: the D entries nearest the root in SHARED memory (one 64-bit word per entry, columns as above),
+// deeper ones in thread-local memory.  Why (ncu --set full of the round-1 kernel, profiles/r2b): the ray-stream
+// kernel is bound by the L1 data pipe -- 402 M wavefronts per 5 M-ray launch = 82 % of one wavefront per cycle
+// and SM -- because every lane's access is its own wavefront: two per node (64-byte node = 2 x LDG.256), three
+// per triangle (3 x LDG.128), and the thread-local stack costs one per DISTINCT stack depth in the warp for each
+// of its four accesses per push / pop (incoherent rays: nearly one per lane).  The local stack also takes ~4 KB
+// of L1 per warp (147 KB per SM at 36 warps) from the node data.  A shared-memory column is ONE wavefront per
+// warp and instruction whatever the depths, and leaves L1 to the nodes.  (A full-height shared stack was
+// measured slower in round 1: 27 KB per CTA cut the resident warps.  D entries cost D KB per 128-thread CTA.)
+#define ORB_LOCAL_STACK_MAX 64
+template <int D, int BLOCK>
+struct HybridStack {
+    unsigned long long* s;  // this thread's column: entry e at s[e * BLOCK]
+    unsigned long long l[ORB_LOCAL_STACK_MAX - D];
+    ORB_HD static unsigned long long pack(int ref, float tn) {
+        return ((unsigned long long)(unsigned)__float_as_int_hd(tn) << 32) | (unsigned long long)(unsigned)ref;
+    }
+    ORB_HD void put(int i, int ref, float tn) {
+        if (i < D) s[i * BLOCK] = pack(ref, tn);
+        else l[i - D] = pack(ref, tn);
+    }
+    ORB_HD unsigned long long get(int i) const { return i < D ? s[i * BLOCK] : l[i - D]; }
+};
+
+// pop: skip subtrees that start beyond the current closest hit
+template <class Stack>
+ORB_HD int stack_pop(const Stack& st, int& sp, const Hit& best) {
+    for (;;) {
         if (sp == 0) return ORB_TRAVERSAL_DONE;
         --sp;
-        if (best.prim < 0 || !(stk_t[sp * stride] > best.t)) return stk[sp * stride];
+        if (best.prim < 0 || !(st.dist(sp) > best.t)) return st.ref(sp);
+    }
+}
+template <int D, int BLOCK>
+ORB_HD int stack_pop(const HybridStack<D, BLOCK>& st, int& sp, const Hit& best) {
+    for (;;) {
+        if (sp == 0) return ORB_TRAVERSAL_DONE;
+        --sp;
+        const unsigned long long e = st.get(sp);  // one 64-bit load: distance and reference together
+        if (best.prim < 0 || !(__int_as_float_hd((int)(unsigned)(e >> 32)) > best.t)) return (int)(unsigned)(e & 0xffffffffull);
     }
 }
 
 // Traversal state of one ray; a "macro step" walks inner nodes until a leaf is reached, tests
 // that leaf, and pops.  trace_closest() runs macro steps to completion; the ray-stream kernel
-// (orb200.cu k_trace_stream) interleaves them with refills so finished lanes get new rays.
+// (orb200.cu k_trace_stream_spec) interleaves them with refills so finished lanes get new rays.
 struct TravState {
     float3 o, d, inv, noi;  // noi = -o * inv
     Hit best;
@@ -171,13 +246,30 @@ ORB_HD void trav_begin(TravState& t, const SceneView& s, float3 o, float3 d) {
     t.cur = (s.n_tris == 0 || chk != chk) ? ORB_TRAVERSAL_DONE : s.root_ref;
 }
 
-// One inner node (t.cur >= 0): both child boxes of a 64-byte node, near child next, far pushed.
-template <class IntPtr, class FltPtr>
-ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride) {
+// After both child boxes of a node were tested: near child next, far child pushed, or pop.
+template <class Stack>
+ORB_HD void trav_descend(TravState& t, Stack& st, bool h0, bool h1, float tn0, float tn1, int c0, int c1) {
+    if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        st.put(t.sp, swap ? c0 : c1, swap ? tn0 : tn1);
+        ++t.sp;
+        t.cur = swap ? c1 : c0;
+    } else if (h0) {
+        t.cur = c0;
+    } else if (h1) {
+        t.cur = c1;
+    } else {
+        t.cur = stack_pop(st, t.sp, t.best);
+    }
+}
+
+// One inner node (t.cur >= 0): both child boxes of a 64-byte node.
+template <class Stack>
+ORB_HD void trav_node_step(TravState& t, const SceneView& s, Stack& st) {
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
-    // two 256-bit loads (sm_100: LDG.E.256) instead of four 128-bit ones: the node fetch is the
-    // kernel's L1 bottleneck (ncu profiles/r1c: l1tex 81 % busy), every lane reading its own node
+    // two 256-bit loads (sm_100: LDG.E.256) instead of four 128-bit ones: every lane reads its own node and
+    // every load instruction of a lane is its own L1 wavefront
     float4 na, nb, nc;
     int c0, c1, pad0, pad1;
     asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -186,6 +278,8 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
     asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(nc.x), "=f"(nc.y), "=f"(nc.z), "=f"(nc.w), "=r"(c0), "=r"(c1), "=r"(pad0), "=r"(pad1)
         : "l"(reinterpret_cast<const char*>(np) + 32));
+    (void)pad0;
+    (void)pad1;
 #else
     const float4 na = np->a, nb = np->b, nc = np->c;
     const int c0 = np->c0, c1 = np->c1;
@@ -194,32 +288,18 @@ ORB_HD void trav_node_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr 
     float tn0, tn1;
     const bool h0 = box_test(na.x, na.y, na.z, na.w, nb.x, nb.y, t.noi, t.inv, lim, tn0);
     const bool h1 = box_test(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, t.noi, t.inv, lim, tn1);
-    if (h0 && h1) {
-        const bool swap = tn1 < tn0;
-        stk[t.sp * stride] = swap ? c0 : c1;
-        stk_t[t.sp * stride] = swap ? tn0 : tn1;
-        ++t.sp;
-        t.cur = swap ? c1 : c0;
-    } else if (h0) {
-        t.cur = c0;
-    } else if (h1) {
-        t.cur = c1;
-    } else {
-        t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
-    }
+    trav_descend(t, st, h0, h1, tn0, tn1, c0, c1);
 }
 
-// The 1..8 triangles of one leaf reference against the ray; updates t.best only.
+// The 1..8 triangles of one leaf reference against the ray; updates t.best only.  A triangle record is one
+// 32-byte word of `tri` (v0.xyz, prim id | e1.xyz, e2.x) and one 8-byte word of `tri_b` (e2.y, e2.z): two loads
+// per lane instead of the three 16-byte ones of a 48-byte record, 40 bytes of cache footprint instead of 48.
 ORB_HD void trav_leaf_test(TravState& t, const SceneView& s, int leaf, unsigned* n_tris = nullptr) {
     const int lr = ~leaf;
     const int first = lr >> 3, count = (lr & 7) + 1;
     for (int i = 0; i < count; i++) {
-        const float4* tp = s.tri + 3 * (size_t)(first + i);
-#ifdef __CUDA_ARCH__
-        const float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-#else
-        const float4 t0 = tp[0], t1 = tp[1], t2 = tp[2];
-#endif
+        float4 t0, t1, t2;
+        tri_fetch(s, first + i, t0, t1, t2);
         if (n_tris) ++*n_tris;
         float tt, u, v;
         if (tri_test(t0, t1, t2, t.o, t.d, 0.f, ORB_TMAX, tt, u, v)) hit_consider(t.best, tt, u, v, __float_as_int_hd(t0.w));
@@ -227,31 +307,31 @@ ORB_HD void trav_leaf_test(TravState& t, const SceneView& s, int leaf, unsigned*
 }
 
 // One leaf (t.cur < 0, not DONE): its triangles, then pop.
-template <class IntPtr, class FltPtr>
-ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
-                           unsigned* n_tris = nullptr) {
+template <class Stack>
+ORB_HD void trav_leaf_step(TravState& t, const SceneView& s, Stack& st, unsigned* n_tris = nullptr) {
     trav_leaf_test(t, s, t.cur, n_tris);
-    t.cur = stack_pop(stk, stk_t, stride, t.sp, t.best);
+    t.cur = stack_pop(st, t.sp, t.best);
 }
 
-template <class IntPtr, class FltPtr>
-ORB_HD void trav_macro_step(TravState& t, const SceneView& s, IntPtr stk, FltPtr stk_t, int stride,
-                            unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
-    while (t.cur >= 0) {
-        if (n_nodes) ++*n_nodes;
-        trav_node_step(t, s, stk, stk_t, stride);
-    }
-    if (t.cur == ORB_TRAVERSAL_DONE) return;
-    trav_leaf_step(t, s, stk, stk_t, stride, n_tris);
-}
-
-template <class IntPtr, class FltPtr>
-ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, IntPtr stk, FltPtr stk_t, int stride,
-                         unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+template <class Stack>
+ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, Stack& st, unsigned* n_nodes = nullptr,
+                         unsigned* n_tris = nullptr) {
     TravState t;
     trav_begin(t, s, o, d);
-    while (t.cur != ORB_TRAVERSAL_DONE) trav_macro_step(t, s, stk, stk_t, stride, n_nodes, n_tris);
+    while (t.cur != ORB_TRAVERSAL_DONE) {
+        while (t.cur >= 0) {
+            if (n_nodes) ++*n_nodes;
+            trav_node_step(t, s, st);
+        }
+        if (t.cur == ORB_TRAVERSAL_DONE) break;
+        trav_leaf_step(t, s, st, n_tris);
+    }
     return t.best;
+}
+ORB_HD Hit trace_closest(const SceneView& s, float3 o, float3 d, int* stk, float* stk_t, int stride,
+                         unsigned* n_nodes = nullptr, unsigned* n_tris = nullptr) {
+    StridedStack st{stk, stk_t, stride};
+    return trace_closest(s, o, d, st, n_nodes, n_tris);
 }
 
 // Brute force over every triangle record: the GPU-side reference for hit-id parity tests.
@@ -261,9 +341,10 @@ ORB_HD Hit trace_brute(const SceneView& s, float3 o, float3 d) {
     best.u = best.v = 0.f;
     best.prim = -1;
     for (int i = 0; i < s.n_tris; i++) {
-        const float4* tp = s.tri + 3 * (size_t)i;
+        float4 t0, t1, t2;
+        tri_fetch(s, i, t0, t1, t2);
         float t, u, v;
-        if (tri_test(tp[0], tp[1], tp[2], o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(tp[0].w));
+        if (tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, t, u, v)) hit_consider(best, t, u, v, __float_as_int_hd(t0.w));
     }
     return best;
 }

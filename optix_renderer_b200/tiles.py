@@ -333,10 +333,7 @@ class TiledRenderer:
 
     def render_ratio_frame(self, accum_id, mode=1, shadow_spp=4, denoise=True):
         """RATIO frame + denoise + combine for this rank's band; asynchronous on the renderer's stream
-        (the collectives run on the current torch stream, which must be the renderer's).
-        (Running the halo exchange on a side stream beside the LTC sum -- ORB_RENDER_DEFER_LTC +
-        orb_render_finish -- was measured at N = 4: 1.27 ms against 1.25 ms.  What the exchange costs is the
-        wait for the neighbour, which no overlap hides; the plain order stays.)"""
+        (the collectives run on the current torch stream, which must be the renderer's)."""
         from . import api
 
         y0, y1 = self.band

@@ -31,7 +31,7 @@ using owl::common::vec3f;
 
 // ---- device-side scene ------------------------------------------------------------------------------
 struct GpuScene {
-    orb::SceneView view;  // tri, nodes, root_ref, n_tris are used by the traversal; the rest stays null
+    orb::SceneView view;  // tri, tri_b, nodes, root_ref, n_tris are used by the traversal; the rest stays null
     const TriangleMeshData* meshes;
     const int* primMesh;
     const int* primLocal;
@@ -159,6 +159,7 @@ void free_all() {
     S.arrays.clear();
     S.owned.clear();
     cudaFree(S.bvh.tri);
+    cudaFree(S.bvh.tri_b);
     cudaFree(S.bvh.nodes);
     S.bvh = orb::BvhBuildResult();
     for (auto& b : S.buf) { cudaFree(b); b = nullptr; }
@@ -246,6 +247,7 @@ void ora_commit(int /*use_bvh*/) {
     if (n) CKR(orb::build_bvh_sah(d_pos, n, 4, 0, S.bvh));
     memset((void*)&S.gs.view, 0, sizeof(S.gs.view));
     S.gs.view.tri = S.bvh.tri;
+    S.gs.view.tri_b = S.bvh.tri_b;
     S.gs.view.nodes = S.bvh.nodes;
     S.gs.view.root_ref = S.bvh.root_ref;
     S.gs.view.n_tris = n;

@@ -27,6 +27,7 @@ struct State {
     std::vector<float4> lut;
     int lut_w = 0, lut_h = 0, lut_q = 0;
     std::vector<float4> tri;
+    std::vector<float2> tri_b;
     std::vector<BvhNode> nodes;
     int root_ref = 0;
     std::vector<QNode> qnodes;  // bvhq.cuh: the same hierarchy on the 16-bit grid
@@ -84,9 +85,10 @@ int build_rec(std::vector<int>& idx, int first, int count, int max_leaf) {
 void refresh() {
     SceneView& v = G.view;
     v.tri = G.tri.data();
+    v.tri_b = G.tri_b.data();
     v.nodes = G.nodes.data();
     v.root_ref = G.root_ref;
-    v.n_tris = (int)G.tri.size() / 3;
+    v.n_tris = (int)G.tri_b.size();
     v.pos = G.pos.data();
     v.nrm = G.nrm.data();
     v.uv = G.uv.data();
@@ -107,9 +109,20 @@ struct HostTracer {
     Hit operator()(float3 o, float3 d) const {
         rays++;
         if (brute == 1) return trace_brute(G.view, o, d);
+        unsigned nn = 0, nt = 0;
+        if (brute == 6 || brute == 7) {  // the hybrid stack of the GPU kernels: first 3 entries in a "shared" column, rest local
+            unsigned long long col[3];
+            HybridStack<3, 1> hs;
+            hs.s = col;
+            const Hit hh = (brute == 7 && G.root_ref >= 0 && !G.qnodes.empty())
+                               ? trace_closest_q(G.view, G.qnodes.data(), G.qgrid, o, d, hs, &nn, &nt)
+                               : trace_closest(G.view, o, d, hs, &nn, &nt);
+            nodes += nn;
+            tris += nt;
+            return hh;
+        }
         int stk[128];
         float stk_t[128];
-        unsigned nn = 0, nt = 0;
         Hit h;
         if (brute == 5 && G.root_ref >= 0 && !G.qnodes.empty())  // 32-byte quantised nodes (a leaf root has no nodes at all)
             h = trace_closest_q(G.view, G.qnodes.data(), G.qgrid, o, d, stk, stk_t, 1, &nn, &nt);
@@ -188,12 +201,14 @@ void hc_commit(int max_leaf) {
     for (int i = 0; i < n; i++) idx[i] = i;
     G.nodes.clear();
     G.root_ref = n ? build_rec(idx, 0, n, max_leaf > 0 ? max_leaf : 4) : 0;
-    G.tri.resize(3 * (size_t)n);
+    G.tri.resize(2 * (size_t)n);
+    G.tri_b.resize((size_t)n);
     for (int k = 0; k < n; k++) {
-        const float* p = &G.pos[9 * (size_t)idx[k]];
-        G.tri[3 * (size_t)k] = make_float4(p[0], p[1], p[2], __int_as_float_hd(idx[k]));
-        G.tri[3 * (size_t)k + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.f);
-        G.tri[3 * (size_t)k + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.f);
+        float a[8], b[2];
+        tri_record(a, b, &G.pos[9 * (size_t)idx[k]], idx[k]);  // the product's own record writer (scene.cuh)
+        G.tri[2 * (size_t)k] = make_float4(a[0], a[1], a[2], a[3]);
+        G.tri[2 * (size_t)k + 1] = make_float4(a[4], a[5], a[6], a[7]);
+        G.tri_b[k] = make_float2(b[0], b[1]);
     }
     G.qnodes.clear();
     if (n && G.root_ref >= 0 && !G.nodes.empty()) {

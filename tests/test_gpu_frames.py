@@ -441,27 +441,6 @@ def test_quantised_node_stream_kernel(renderer_factory, monkeypatch):
     assert np.array_equal(a.download("accum"), b.download("accum"), equal_nan=True)
 
 
-def test_deferred_ltc_equals_one_call(renderer_factory):
-    """ORB_RENDER_DEFER_LTC + orb_render_finish (the two halves a tile partition puts around its halo exchange)
-    produce the frame of a single orb_render, bit for bit, over several accumulated frames and on a band."""
-    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
-    a, b = renderer_factory(sc), renderer_factory(sc)
-    for rows in (None, (20, 70)):
-        for i in range(3):
-            a.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, rows=rows)
-            b.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, rows=rows, defer_ltc=True)
-            b.denoise_pack(rows=rows)
-            b.render_finish(accum_id=i, mode=1, shadow_spp=4, rows=rows)
-            b.sync()
-        for k in ("ltc", "sto_direct", "sto_no_vis", "accum", "rgba8", "position"):
-            assert np.array_equal(a.download(k), b.download(k), equal_nan=True), (rows, k)
-        assert a.counters()["rays_shadow_total"] == b.counters()["rays_shadow_total"]
-    with pytest.raises(api.OrbError):
-        a.lib.orb_render_finish  # bound
-        c = a._cfg(api.PATH, 0, 1, 4, 1, None, defer_ltc=True)
-        a._ck(a.lib.orb_render_finish(a._h, __import__("ctypes").byref(c)))
-
-
 def test_pipelined_download_equals_blocking_download(renderer_factory):
     """orb_buffer_download_rows_async + orb_download_wait: frame i is read back while frames i+1.. render; each
     host frame equals a blocking download taken right after the same frame, bit for bit (full frame and a band)."""

@@ -150,6 +150,13 @@ def test_quantised_nodes_find_the_same_hits(hostcheck, n_tris, leaf):
     gotq, nodesq, trisq = hostcheck.trace_counted(org, d, mode=5)
     for a, b, c in zip(want, got32, gotq):
         assert np.array_equal(a, b) and np.array_equal(a, c)
+    # the hybrid stack of the GPU traversal kernels (first entries in a shared-memory column, deeper ones in local
+    # memory; here 3 + local) walks both hierarchies to the same hits with the same number of node visits
+    goth, nodesh, _ = hostcheck.trace_counted(org, d, mode=6)
+    gothq, nodeshq, _ = hostcheck.trace_counted(org, d, mode=7)
+    for a, b, c in zip(want, goth, gothq):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
+    assert nodesh == nodes32 and nodeshq == nodesq
     assert (want[0] >= 0).mean() > 0.15
     if n_tris >= 3000:
         assert nodes32 > 0 and nodesq >= nodes32
