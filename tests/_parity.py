@@ -115,13 +115,35 @@ def frame_report(got, ref, hit_got, hit_ref):
 
 
 # ---- classification of the pixels that differ (north_star: "edge ties ... are counted and reported") -------------
-def classify_hit_mismatches(got, ref, cam_pos, edge_tol=1e-4):
+def _prim_vertices(scene, prim):
+    """(3, 3) float64 corner positions of global primitive `prim` (meshes in scene order, orb200.h)."""
+    for m in scene["meshes"]:
+        n = m["idx"].shape[0]
+        if prim < n:
+            return np.asarray(m["vtx"], np.float64)[m["idx"][prim]]
+        prim -= n
+    raise IndexError(prim)
+
+
+def _ray_segment_angle(c, d, p, q):
+    """Smallest angle (radians, small-angle form) under which the segment [p, q] is seen from the ray c + s d."""
+    e, w = q - p, c - p
+    b, cc, dd, f = d @ e, e @ e, d @ w, e @ w
+    den = cc - b * b
+    u = 0.0 if den <= 1e-300 else min(1.0, max(0.0, (f - b * dd) / den))
+    s = b * u - dd
+    return float(np.linalg.norm(w + s * d - u * e) / max(s, 1e-12))
+
+
+def classify_hit_mismatches(got, ref, cam_pos, scene=None, edge_tol=1e-4, angle_tol=2e-6):
     """Split the pixels whose primary hit id differs into
       tie    both sides hit, at the same point in space (|dp| <= 16 ulp of the hit distance): two triangles share
              the edge / the point the ray passes through and the closest-t comparison went the other way;
-      edge   the hit of at least one side lies within `edge_tol` (barycentric) of a triangle edge: the ray grazes a
-             silhouette edge and a last-ulp difference of the ray direction (fma contraction of the camera ray)
-             moves it on or off the triangle -- what is behind is then hit instead;
+      edge   the ray grazes the boundary of the NEARER of the two triangles -- the one the other side missed: seen
+             from the camera it passes within `angle_tol` radians (1/300 of a 1080p pixel, a few ulp of a direction
+             component) of one of its edges, so a last-ulp difference of the camera ray (fma contraction) moves it on
+             or off the triangle and what lies behind is hit instead.  Without `scene` (no vertices): the hit lies
+             within `edge_tol` (barycentric) of an edge on either side;
       other  anything else: a real difference.  Tests fail on these.
     got / ref need hit_prim (H, W), hit_uv (H, W, 2) and position (H, W, 4)."""
     gp, rp = got["hit_prim"], ref["hit_prim"]
@@ -132,17 +154,30 @@ def classify_hit_mismatches(got, ref, cam_pos, edge_tol=1e-4):
     cam = np.asarray(cam_pos, np.float64)
     pg = np.asarray(got["position"], np.float64)[bad][:, :3]
     pr = np.asarray(ref["position"], np.float64)[bad][:, :3]
-    both = (gp[bad] >= 0) & (rp[bad] >= 0)
-    t = np.maximum(1.0, np.linalg.norm(pr - cam, axis=1))
-    tie = both & (np.abs(pg - pr).max(axis=1) <= 16 * np.finfo(np.float32).eps * t)
-
-    def near_edge(uv, prim):
-        u, v = uv[..., 0].astype(np.float64), uv[..., 1].astype(np.float64)
-        return (prim >= 0) & (np.minimum(np.minimum(u, v), 1.0 - u - v) <= edge_tol)
-
-    edge = ~tie & (near_edge(got["hit_uv"][bad], gp[bad]) | near_edge(ref["hit_uv"][bad], rp[bad]))
-    out["tie"], out["edge"] = int(tie.sum()), int(edge.sum())
-    out["other"] = out["mismatch"] - out["tie"] - out["edge"]
+    g, r = gp[bad], rp[bad]
+    ug, ur = got["hit_uv"][bad].astype(np.float64), ref["hit_uv"][bad].astype(np.float64)
+    eps = float(np.finfo(np.float32).eps)
+    worst = 0.0
+    for k in range(len(g)):
+        tg = np.linalg.norm(pg[k] - cam) if g[k] >= 0 else np.inf
+        tr = np.linalg.norm(pr[k] - cam) if r[k] >= 0 else np.inf
+        if g[k] >= 0 and r[k] >= 0 and np.abs(pg[k] - pr[k]).max() <= 16 * eps * max(1.0, tr):
+            out["tie"] += 1
+            continue
+        near_prim, near_p = (g[k], pg[k]) if tg <= tr else (r[k], pr[k])
+        if scene is not None:
+            d = (near_p - cam) / np.linalg.norm(near_p - cam)
+            v = _prim_vertices(scene, int(near_prim))
+            ang = min(_ray_segment_angle(cam, d, v[i], v[(i + 1) % 3]) for i in range(3))
+            worst = max(worst, ang)
+            is_edge = ang <= angle_tol
+        else:
+            def near(uv, prim):
+                return prim >= 0 and min(uv[0], uv[1], 1.0 - uv[0] - uv[1]) <= edge_tol
+            is_edge = near(ug[k], g[k]) or near(ur[k], r[k])
+        out["edge" if is_edge else "other"] += 1
+    if scene is not None:
+        out["max_edge_angle_rad"] = worst
     return out
 
 

@@ -102,7 +102,7 @@ def test_cfg2_cornell_1024_one_shadow_sample(renderer_factory):
         c = r.counters()
         rep = check_frame(got, ref, _oracle.RATIO, strict_hits=False)
         assert W * H + c["rays_shadow"] == ref["rays"] and c["rays_shadow"] == c["active_pixels"]   # 1 spp, exact
-        hits = P.classify_hit_mismatches(got, ref, sc["camera"]["pos"])
+        hits = P.classify_hit_mismatches(got, ref, sc["camera"]["pos"], scene=sc)
         assert hits["other"] == 0, hits
         print("cfg2 frame %d:" % i, hits, {k: rep[k]["frac_le_1e-4"] for k in ("ltc", "accum")},
               {k: rep[k]["rmse"] for k in ("sto_direct", "sto_no_vis")})

@@ -94,7 +94,7 @@ def classified(got, ref, sc, rt, lights_lut_oracle=None, tag=""):
     <= 1e-4 relative": every pixel outside those bars is classified (tests/_parity.py) and anything that is neither
     a tie / grazed edge nor a clip case flip fails the test."""
     cam = sc["camera"]["pos"]
-    hits = P.classify_hit_mismatches(got, ref, cam)
+    hits = P.classify_hit_mismatches(got, ref, cam, scene=sc)
     out = {"hits": hits}
     assert hits["other"] == 0, (tag, hits)
     if rt in (_oracle.LTC_BASELINE, _oracle.RATIO):
