@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define ORB_API_VERSION 1
+#define ORB_API_VERSION 2
 
 typedef enum OrbStatus {
     ORB_OK = 0,
@@ -163,7 +163,8 @@ typedef enum OrbStage {
     ORB_STAGE_COMBINE = 7,      /* ratio combine                                                 */
     ORB_STAGE_LTC_GBUFFER = 8,  /* stand-alone LTC pass over a saved G-buffer                    */
     ORB_STAGE_TRACE = 9,        /* RATIO: the shadow-ray stream traversal kernel alone           */
-    ORB_STAGE_COUNT = 10
+    ORB_STAGE_HALO = 10,        /* tile partition: flag kernels of the hand-off (time = waiting for the peers) */
+    ORB_STAGE_COUNT = 11
 } OrbStage;
 
 typedef struct OrbStageTimes {
@@ -238,6 +239,27 @@ int orb_denoise(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_
  * 2 * (2^iterations - 1) halo rows), and the filter then runs over the band. */
 int orb_denoise_pack(OrbContext* ctx, int32_t y0, int32_t y1);
 int orb_denoise_filter(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1);
+/* ---- tile hand-off of a row-band partition (one context per GPU; the reference has one GPU, viewer.hpp:177) ----
+ * Each rank maps its peers' packed denoise buffers once; orb_denoise_band then packs a band and STORES the rows its
+ * neighbours' filters read straight into their buffers over NVLink from inside the pack kernel, ordered by epoch
+ * flags (no NCCL call, no host synchronisation).  Set-up per (peer, frame slot): the owner calls orb_halo_local,
+ * hands the three pointers over -- as they are to a context of the same process, through orb_ipc_export /
+ * orb_ipc_open to another process -- and the peer calls orb_halo_connect with them.  Every rank must connect every
+ * other rank and call orb_denoise_band exactly once per frame (y0 == y1 for an empty band). */
+typedef struct OrbHaloSend {
+    int32_t peer_rank; /* rank whose filter reads these rows */
+    int32_t y0, y1;    /* rows of THIS band, [y0, y1) */
+} OrbHaloSend;
+int orb_halo_local(OrbContext* ctx, int32_t slot, void** guide_dev, void** val_dev, void** flags_dev);
+int orb_ipc_export(OrbContext* ctx, void* dev_ptr, unsigned char handle[64]);
+int orb_ipc_open(OrbContext* ctx, const unsigned char handle[64], void** dev_ptr_out);
+int orb_ipc_close(OrbContext* ctx, void* dev_ptr);
+int orb_halo_connect(OrbContext* ctx, int32_t my_rank, int32_t peer_rank, int32_t slot, void* guide_dev, void* val_dev,
+                     void* flags_dev);
+int orb_halo_disconnect(OrbContext* ctx);
+int orb_halo_status(OrbContext* ctx, int32_t* status); /* 0 = ok; > 0 = a flag wait timed out (peer lost) */
+int orb_denoise_band(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1, const OrbHaloSend* sends,
+                     int32_t n_sends, const int32_t* recv_ranks, int32_t n_recv);
 /* Active (non-light hit) pixels per row of the last rendered frame -> host_counts[height]; rows this context
  * did not render report what its flags hold.  Used to balance row bands by cost. */
 int orb_row_active_counts(OrbContext* ctx, int32_t* host_counts);

@@ -64,6 +64,10 @@ class OrbDenoiseConfig(C.Structure):
                 ("sigma_colour", C.c_float)]
 
 
+class OrbHaloSend(C.Structure):
+    _fields_ = [("peer_rank", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32)]
+
+
 class OrbCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_shadow", "rays_bounce", "kernel_launches",
                                           "nan_pixels", "bvh_nodes", "bvh_triangles", "bvh_height",
@@ -72,11 +76,11 @@ class OrbCounters(C.Structure):
 
 
 STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "denoise", "combine", "ltc_gbuffer",
-          "trace"]
+          "trace", "halo"]
 
 
 class OrbStageTimes(C.Structure):
-    _fields_ = [("ms", C.c_double * 10), ("launches", C.c_uint64 * 10)]
+    _fields_ = [("ms", C.c_double * 11), ("launches", C.c_uint64 * 11)]
 
 
 _lib = None
@@ -120,6 +124,15 @@ def load_library():
     L.orb_denoise_pack.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_denoise_filter.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32]
     L.orb_row_active_counts.argtypes = [vp, vp]
+    L.orb_halo_local.argtypes = [vp, C.c_int32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.orb_ipc_export.argtypes = [vp, vp, C.c_char_p]
+    L.orb_ipc_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    L.orb_ipc_close.argtypes = [vp, vp]
+    L.orb_halo_connect.argtypes = [vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp]
+    L.orb_halo_disconnect.argtypes = [vp]
+    L.orb_halo_status.argtypes = [vp, C.POINTER(C.c_int32)]
+    L.orb_denoise_band.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32, C.POINTER(OrbHaloSend), C.c_int32,
+                                   _i, C.c_int32]
     L.orb_ratio_combine.argtypes = [vp, C.c_int32, C.c_int32, C.c_int32]
     L.orb_buffer_bytes.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.restype = C.c_size_t
@@ -302,6 +315,46 @@ class Renderer:
         d = OrbDenoiseConfig(int(iterations), float(sigma_normal), float(sigma_position), float(sigma_colour))
         y0, y1 = rows if rows else (0, 0)
         self._ck(self.lib.orb_denoise_filter(self._h, C.byref(d), y0, y1))
+
+    # ---- tile hand-off between the ranks of a row-band partition (include/orb200.h, csrc/halo.cuh) ----
+    def halo_local(self, slot=0):
+        """Device pointers (guide, val, control block) a peer needs to push its rows into this context's `slot`."""
+        g, v, f = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.orb_halo_local(self._h, int(slot), C.byref(g), C.byref(v), C.byref(f)))
+        return g.value, v.value, f.value
+
+    def ipc_export(self, ptr):
+        h = C.create_string_buffer(64)
+        self._ck(self.lib.orb_ipc_export(self._h, C.c_void_p(ptr), h))
+        return h.raw
+
+    def ipc_open(self, handle):
+        out = C.c_void_p()
+        self._ck(self.lib.orb_ipc_open(self._h, C.create_string_buffer(bytes(handle), 64), C.byref(out)))
+        return out.value
+
+    def ipc_close(self, ptr):
+        self._ck(self.lib.orb_ipc_close(self._h, C.c_void_p(ptr)))
+
+    def halo_connect(self, my_rank, peer_rank, slot, guide, val, flags):
+        self._ck(self.lib.orb_halo_connect(self._h, int(my_rank), int(peer_rank), int(slot), C.c_void_p(guide), C.c_void_p(val),
+                                           C.c_void_p(flags)))
+
+    def halo_disconnect(self):
+        self._ck(self.lib.orb_halo_disconnect(self._h))
+
+    def halo_status(self):
+        s = C.c_int32()
+        self._ck(self.lib.orb_halo_status(self._h, C.byref(s)))
+        return int(s.value)
+
+    def denoise_band(self, rows, sends=(), recv_ranks=(), iterations=5, sigma_normal=32.0, sigma_position=0.25, sigma_colour=0.0):
+        """Denoise of this rank's band with the hand-off fused in: pack (+ peer stores of the rows in `sends` =
+        [(peer_rank, y0, y1), ...]), flags, filter once the rows of `recv_ranks` have arrived.  Asynchronous."""
+        d = OrbDenoiseConfig(int(iterations), float(sigma_normal), float(sigma_position), float(sigma_colour))
+        sa = (OrbHaloSend * max(len(sends), 1))(*[OrbHaloSend(int(p), int(a), int(b)) for p, a, b in sends])
+        ra = (C.c_int32 * max(len(recv_ranks), 1))(*[int(x) for x in recv_ranks])
+        self._ck(self.lib.orb_denoise_band(self._h, C.byref(d), int(rows[0]), int(rows[1]), sa, len(sends), ra, len(recv_ranks)))
 
     def row_active_counts(self):
         """Active (non-light hit) pixels per row of the last frame, int32[H]."""

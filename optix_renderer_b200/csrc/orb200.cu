@@ -828,7 +828,10 @@ __global__ void k_accumulate(FrameView f, const float4* __restrict__ src, int ac
 //                 (* exp(-|v_c - v_q| / sigma_c) per image when sigma_c > 0); NaN taps are skipped
 // ---------------------------------------------------------------------------------------------
 #define DN_SKIP_DEPTH (-1e30f)  // guide.w of a pixel that is neither filtered nor used as a tap
-__global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__ guide, float2* __restrict__ val) {
+// HaloSendList (halo.cuh): the rows of this band that other ranks' filters read are stored a second time, straight
+// into those ranks' buffers over NVLink (peer-mapped pointers) -- the tile hand-off is part of the pack kernel.
+__global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__ guide, float2* __restrict__ val,
+                               HaloSendList sends) {
     const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const size_t ofs = first + i;
@@ -841,8 +844,19 @@ __global__ void k_denoise_pack(FrameView f, float3 cam_pos, float4* __restrict__
         // any depth that exp(-|dz| / (sigma_p step)) is exactly 0: the filter needs no per-tap test.
         const bool skip = (nn.x == 0.f && nn.y == 0.f && nn.z == 0.f) || mm.x == 0.f ||
                           !(fabsf(nn.x) + fabsf(nn.y) + fabsf(nn.z) < 1e18f) || !(depth < 1e18f);
-        guide[ofs] = make_float4(nn.x, nn.y, nn.z, skip ? DN_SKIP_DEPTH : depth);
-        val[ofs] = skip ? make_float2(0.f, 0.f) : make_float2(a.x, b.x);  // 0 * weight 0 stays 0 (emit may be inf)
+        const float4 g = make_float4(nn.x, nn.y, nn.z, skip ? DN_SKIP_DEPTH : depth);
+        const float2 v = skip ? make_float2(0.f, 0.f) : make_float2(a.x, b.x);  // 0 * weight 0 stays 0 (emit may be inf)
+        guide[ofs] = g;
+        val[ofs] = v;
+        if (sends.n) {
+            const int y = (int)(ofs / (size_t)f.W);
+#pragma unroll
+            for (int k = 0; k < ORB_HALO_MAX_SENDS; k++)
+                if (k < sends.n && y >= sends.s[k].y0 && y < sends.s[k].y1) {
+                    sends.s[k].guide[ofs] = g;
+                    sends.s[k].val[ofs] = v;
+                }
+        }
     }
 }
 
@@ -1481,6 +1495,7 @@ void orb_destroy(OrbContext* c) {
         if (c->parked[k].stream) cudaStreamSynchronize(c->parked[k].stream);
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
     halo_disconnect(c->halo);
+    cudaFree(c->halo.flags);
     free_scene(c);
     free_frame(c);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
@@ -2080,7 +2095,9 @@ int orb_denoise_pack(OrbContext* c, int32_t y0, int32_t y1) {
     const int gp = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
     {
         StageTimer tm(c, ORB_STAGE_DENOISE_PACK, 1);
-        k_denoise_pack<<<gp, 256, 0, c->stream>>>(f, c->cam.pos, (float4*)c->buf[ORB_BUF_DN_GUIDE], (float2*)c->buf[ORB_BUF_DN_VAL]);
+        HaloSendList none;
+        none.n = 0;
+        k_denoise_pack<<<gp, 256, 0, c->stream>>>(f, c->cam.pos, (float4*)c->buf[ORB_BUF_DN_GUIDE], (float2*)c->buf[ORB_BUF_DN_VAL], none);
     }
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
@@ -2128,6 +2145,215 @@ int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, i
         // an odd number of ping-pong passes left pass 0's output in ORB_BUF_DN_VAL; nothing to restore:
         // the packed input is rewritten by the next orb_denoise_pack
     }
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
+// ---- tile hand-off between the ranks of a row-band partition (halo.cuh) ---------------------------------------
+// CUDA loads kernels lazily, and a first-time load can wait for running kernels to finish.  A flag-wait kernel of
+// the hand-off runs until ANOTHER stream's kernels have run, so every kernel a frame may launch behind it has to be
+// resident before the first wait is enqueued (CUDA programming guide, "Lazy Loading": concurrent kernels).
+__global__ void k_snapshot(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n);
+static int preload_frame_kernels() {
+    cudaFuncAttributes a;
+    const int sds[5] = {-1, 0, 8, 12, 16};
+    for (int sd : sds)
+        for (int q = 0; q < 2; q++) {
+            CK(cudaFuncGetAttributes(&a, primary_kernel(sd, q != 0)));
+            for (int cnt = 0; cnt < 2; cnt++) {
+                CK(cudaFuncGetAttributes(&a, stream_kernel(sd, cnt != 0, q != 0)));
+                CK(cudaFuncGetAttributes(&a, path_kernel(sd, cnt != 0, q != 0)));
+            }
+        }
+    const int steps[6] = {0, 1, 2, 4, 8, 16};
+    for (int st : steps) {
+        CK(cudaFuncGetAttributes(&a, atrous_kernel<true>(false, st)));
+        CK(cudaFuncGetAttributes(&a, atrous_kernel<false>(false, st)));
+    }
+    CK(cudaFuncGetAttributes(&a, atrous_kernel<true>(true, 0)));
+    CK(cudaFuncGetAttributes(&a, atrous_kernel<false>(true, 0)));
+    CK(cudaFuncGetAttributes(&a, k_ltc<true>));
+    CK(cudaFuncGetAttributes(&a, k_ltc<false>));
+    CK(cudaFuncGetAttributes(&a, k_shadow_gen));
+    CK(cudaFuncGetAttributes(&a, k_shadow_resolve));
+    CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<2>));
+    CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<4>));
+    CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<8>));
+    CK(cudaFuncGetAttributes(&a, k_path_bounce<true>));
+    CK(cudaFuncGetAttributes(&a, k_path_bounce<false>));
+    CK(cudaFuncGetAttributes(&a, k_path_gen<true>));
+    CK(cudaFuncGetAttributes(&a, k_path_gen<false>));
+    CK(cudaFuncGetAttributes(&a, k_path_shade<true>));
+    CK(cudaFuncGetAttributes(&a, k_path_shade<false>));
+    CK(cudaFuncGetAttributes(&a, k_reset_slot));
+    CK(cudaFuncGetAttributes(&a, k_accumulate));
+    CK(cudaFuncGetAttributes(&a, k_denoise_pack));
+    CK(cudaFuncGetAttributes(&a, k_ratio_combine));
+    CK(cudaFuncGetAttributes(&a, k_snapshot));
+    CK(cudaFuncGetAttributes(&a, k_halo_signal));
+    CK(cudaFuncGetAttributes(&a, k_halo_wait));
+    return ORB_OK;
+}
+
+static FrameSlot& slot_ref(OrbContext* c, int k) { return k == c->cur_slot ? *static_cast<FrameSlot*>(c) : c->parked[k]; }
+
+// Device pointers a peer needs to push its rows here: this context's ORB_BUF_DN_GUIDE / ORB_BUF_DN_VAL of `slot` and
+// its control block.  Same process: pass them to the peer's orb_halo_connect; other process: through orb_ipc_export.
+int orb_halo_local(OrbContext* c, int32_t slot, void** guide, void** val, void** flags) {
+    NEED(c && guide && val && flags, "orb_halo_local: NULL argument");
+    NEED(c->W > 0, "orb_halo_local: orb_resize first");
+    NEED(slot >= 0 && slot < c->n_slots, "orb_halo_local: no such frame slot");
+    CK(cudaSetDevice(c->device));
+    if (!c->halo.flags) {
+        int rc = preload_frame_kernels();
+        if (rc) return rc;
+        CK(cudaMalloc(&c->halo.flags, ORB_HALO_BLOCK_BYTES));
+        CK(cudaMemset(c->halo.flags, 0, ORB_HALO_BLOCK_BYTES));
+    }
+    FrameSlot& f = slot_ref(c, slot);
+    *guide = f.buf[ORB_BUF_DN_GUIDE];
+    *val = f.buf[ORB_BUF_DN_VAL];
+    *flags = c->halo.flags;
+    return ORB_OK;
+}
+
+// cudaIpc handles (64 bytes) for the pointers above; the opening side gets a pointer valid in ITS process.
+int orb_ipc_export(OrbContext* c, void* dev_ptr, unsigned char handle[64]) {
+    NEED(c && dev_ptr && handle, "orb_ipc_export: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
+    CK(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, dev_ptr));
+    memcpy(handle, &h, 64);
+    return ORB_OK;
+}
+int orb_ipc_open(OrbContext* c, const unsigned char handle[64], void** out) {
+    NEED(c && handle && out, "orb_ipc_open: NULL argument");
+    CK(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    CK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return ORB_OK;
+}
+int orb_ipc_close(OrbContext* c, void* ptr) {
+    NEED(c && ptr, "orb_ipc_close: NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaIpcCloseMemHandle(ptr));
+    return ORB_OK;
+}
+
+// Register peer `peer_rank`'s buffers of `slot` (pointers valid in this process: orb_halo_local of a context in the
+// same process, or orb_ipc_open of an exported handle).  my_rank = this context's index in the partition.
+int orb_halo_connect(OrbContext* c, int32_t my_rank, int32_t peer_rank, int32_t slot, void* guide, void* val, void* flags) {
+    NEED(c && guide && val && flags, "orb_halo_connect: NULL argument");
+    NEED(my_rank >= 0 && my_rank < ORB_HALO_MAX_PEERS && peer_rank >= 0 && peer_rank < ORB_HALO_MAX_PEERS && peer_rank != my_rank,
+         "orb_halo_connect: ranks must be distinct and below 8");
+    NEED(slot >= 0 && slot < c->n_slots, "orb_halo_connect: no such frame slot");
+    HaloLinks& h = c->halo;
+    NEED(h.flags, "orb_halo_connect: orb_halo_local first (it allocates this context's control block)");
+    NEED(h.n_peers == 0 || h.my_rank == my_rank, "orb_halo_connect: my_rank changed");
+    h.my_rank = my_rank;
+    int i = 0;
+    while (i < h.n_peers && h.peer[i].rank != peer_rank) i++;
+    if (i == h.n_peers) {
+        NEED(h.n_peers < ORB_HALO_MAX_PEERS, "orb_halo_connect: too many peers");
+        h.peer[h.n_peers++].rank = peer_rank;
+    }
+    h.peer[i].guide[slot] = (float4*)guide;
+    h.peer[i].val[slot] = (float2*)val;
+    h.peer[i].flags = (uint32_t*)flags;
+    return ORB_OK;
+}
+
+int orb_halo_disconnect(OrbContext* c) {
+    NEED(c, "orb_halo_disconnect: ctx is NULL");
+    int rc = orb_sync(c);
+    if (rc) return rc;
+    halo_disconnect(c->halo);
+    if (c->halo.flags) CK(cudaMemset(c->halo.flags, 0, ORB_HALO_WORDS * 4));
+    for (int k = 0; k < ORB_MAX_SLOTS; k++) slot_ref(c, k).halo_epoch = 0;
+    return ORB_OK;
+}
+
+// 0 = every wait so far was answered; k > 0 = a wait gave up after its timeout (k - 1 = index in its flag list)
+int orb_halo_status(OrbContext* c, int32_t* status) {
+    NEED(c && status, "orb_halo_status: NULL argument");
+    *status = 0;
+    if (!c->halo.flags) return ORB_OK;
+    int rc = orb_sync(c);
+    if (rc) return rc;
+    uint32_t e = 0;
+    CK(cudaMemcpy(&e, c->halo.flags + ORB_HALO_ERR, 4, cudaMemcpyDeviceToHost));
+    *status = (int32_t)e;
+    return ORB_OK;
+}
+
+// The denoise of one band of a partitioned frame, hand-off included (asynchronous, on the frame's stream):
+//   wait until every peer has consumed what this slot pushed two frames ago -> pack rows [y0, y1) and store the rows
+//   listed in `sends` (peer rank, row range: what that rank's filter reads of this band) into the peers' buffers ->
+//   publish READY to all peers -> wait for READY from `recv_ranks` (the ranks whose rows this band's filter reads)
+//   -> filter -> publish CONSUMED to all peers.
+// A rank with an empty band passes y0 == y1 (no kernels but the flags).  All ranks call this once per frame.
+int orb_denoise_band(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, int32_t y1, const OrbHaloSend* sends,
+                     int32_t n_sends, const int32_t* recv_ranks, int32_t n_recv) {
+    NEED(c && c->W > 0, "orb_denoise_band: orb_resize first");
+    NEED(c->have_cam, "orb_denoise_band: orb_set_camera first");
+    NEED(y0 >= 0 && y1 <= c->H && y0 <= y1, "orb_denoise_band: bad row range");
+    NEED(n_sends >= 0 && n_sends <= ORB_HALO_MAX_SENDS && (n_sends == 0 || sends), "orb_denoise_band: at most 4 sends");
+    NEED(n_recv >= 0 && n_recv <= ORB_HALO_MAX_PEERS && (n_recv == 0 || recv_ranks), "orb_denoise_band: bad receive list");
+    HaloLinks& h = c->halo;
+    NEED(h.flags && h.n_peers > 0, "orb_denoise_band: no peers connected (orb_halo_connect)");
+    CK(cudaSetDevice(c->device));
+    const int slot = c->cur_slot;
+    const uint32_t epoch = ++c->halo_epoch;
+    const long long timeout = 4000000000ll;  // ~2 s of SM clock
+    HaloFlagList to_ready, to_consumed, from_consumed, from_ready;
+    to_ready.n = to_consumed.n = from_consumed.n = from_ready.n = 0;
+    HaloSendList sl;
+    sl.n = 0;
+    for (int i = 0; i < h.n_peers; i++) {
+        NEED(h.peer[i].guide[slot] && h.peer[i].val[slot], "orb_denoise_band: a peer has no buffers for this frame slot");
+        to_ready.p[to_ready.n++] = h.peer[i].flags + ORB_HALO_READY(slot, h.my_rank);
+        to_consumed.p[to_consumed.n++] = h.peer[i].flags + ORB_HALO_CONSUMED(slot, h.my_rank);
+        from_consumed.p[from_consumed.n++] = h.flags + ORB_HALO_CONSUMED(slot, h.peer[i].rank);
+    }
+    for (int k = 0; k < n_sends; k++) {
+        int i = 0;
+        while (i < h.n_peers && h.peer[i].rank != sends[k].peer_rank) i++;
+        NEED(i < h.n_peers, "orb_denoise_band: send to a rank that is not connected");
+        NEED(sends[k].y0 >= y0 && sends[k].y1 <= y1 && sends[k].y0 <= sends[k].y1, "orb_denoise_band: send rows outside the band");
+        if (sends[k].y1 > sends[k].y0) sl.s[sl.n++] = HaloSend{h.peer[i].guide[slot], h.peer[i].val[slot], sends[k].y0, sends[k].y1};
+    }
+    for (int k = 0; k < n_recv; k++) {
+        NEED(recv_ranks[k] >= 0 && recv_ranks[k] < ORB_HALO_MAX_PEERS && recv_ranks[k] != h.my_rank, "orb_denoise_band: bad receive rank");
+        from_ready.p[from_ready.n++] = h.flags + ORB_HALO_READY(slot, recv_ranks[k]);
+    }
+    cudaStream_t st = c->stream;
+    {
+        StageTimer tm(c, ORB_STAGE_HALO, 2);
+        if (epoch > 1) k_halo_wait<<<1, 32, 0, st>>>(from_consumed, epoch - 1, h.flags + ORB_HALO_ERR, timeout);
+    }
+    if (y1 > y0) {
+        FrameView f = frame_view(c, y0, y1);
+        const size_t np = (size_t)(y1 - y0) * c->W;
+        const int gp = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
+        StageTimer tm(c, ORB_STAGE_DENOISE_PACK, 1);
+        k_denoise_pack<<<gp, 256, 0, st>>>(f, c->cam.pos, (float4*)c->buf[ORB_BUF_DN_GUIDE], (float2*)c->buf[ORB_BUF_DN_VAL], sl);
+        c->counters.kernel_launches++;
+    }
+    {
+        StageTimer tm(c, ORB_STAGE_HALO, 2);
+        k_halo_signal<<<1, 32, 0, st>>>(to_ready, epoch);
+        if (from_ready.n) k_halo_wait<<<1, 32, 0, st>>>(from_ready, epoch, h.flags + ORB_HALO_ERR, timeout);
+        c->counters.kernel_launches += 2;
+    }
+    CK(cudaGetLastError());
+    if (y1 > y0) {
+        int rc = orb_denoise_filter(c, cfg, y0, y1);
+        if (rc) return rc;
+    }
+    k_halo_signal<<<1, 32, 0, st>>>(to_consumed, epoch);
+    c->counters.kernel_launches++;
     CK(cudaGetLastError());
     return ORB_OK;
 }

@@ -11,10 +11,12 @@ full of geometry cost the LTC sum and four shadow rays per pixel on top (about 1
 frame every rank counts its active pixels per row, the counts are all-gathered, and all ranks cut
 the frame where the cumulative cost crosses k/N (same input, same cuts everywhere).
 
-Collectives (NCCL over NVLink on the GPU box; gloo in the CPU tests):
-  * denoise input: each rank packs ITS rows (guide float4 + value float2, 24 B/px) and sends the
-    2*(2^iters - 1) rows either side of a cut to the neighbours that filter them (point to point),
-    so nobody renders a halo twice;
+Exchanges (NVLink on the GPU box; gloo in the CPU tests):
+  * denoise input: each rank packs ITS rows (guide float4 + value float2, 24 B/px) and the
+    2*(2^iters - 1) rows either side of a cut reach the neighbours that filter them, so nobody renders a
+    halo twice.  After connect_halo() the pack kernel itself stores those rows into the neighbours'
+    buffers through peer-mapped pointers (csrc/halo.cuh: cudaIpc handles exchanged once, epoch flags, no
+    NCCL call on the frame's critical path); without it they go point to point through torch.distributed;
   * frame assembly: one all-gather of each rank's finished band per output buffer.
 Bands are uneven, so the gathers are lists of per-rank row views of the destination buffer.
 """
@@ -253,6 +255,10 @@ class TiledRenderer:
         self.row_cost = None
         self.floor_ms = 0.0  # fixed per-frame kernel time of a band of any height (see rebalance)
         self._views = {}
+        self._streams = {}
+        self._ipc = []        # peer mappings opened by connect_halo()
+        self.halo = False     # True: the denoise halo is handed over by peer stores inside the pack kernel
+        self._plan_key, self._plan = None, None
         self.spans = None  # set to {} to collect CUDA-event spans of the collectives: name -> [(e0, e1), ...]
         self.out = {}      # assemble_async(): name -> whole-frame tensor every rank ends up with
         self._comm = None  # side stream the frame assembly runs on, beside the next frame's kernels
@@ -265,9 +271,71 @@ class TiledRenderer:
         return self.bands[self.rank]
 
     def _t(self, name):
-        if name not in self._views:
-            self._views[name] = device_tensor(self.r, name)
-        return self._views[name]
+        """torch view of the ACTIVE frame slot's buffer (the slot of the last render())."""
+        key = (name, self.r.frame_slot)
+        if key not in self._views:
+            self._views[key] = device_tensor(self.r, name)
+        return self._views[key]
+
+    def slot_stream(self):
+        """torch handle of the stream the active frame slot's kernels run on (the library's own stream)."""
+        import torch
+
+        k = self.r.frame_slot
+        if k not in self._streams:
+            self._streams[k] = torch.cuda.ExternalStream(self.r.stream())
+        return self._streams[k]
+
+    def connect_halo(self):
+        """Map every other rank's packed denoise buffers and control block into this process (cudaIpc handles
+        through one all_gather_object) so that render_ratio_frame() hands its halo rows over with peer stores
+        from inside the pack kernel.  All ranks must call it, after set_frame_slots / resize."""
+        if self.world == 1:
+            return False
+        import torch.distributed as dist
+
+        mine = []
+        for k in range(self.r.frame_slots):
+            g, v, f = self.r.halo_local(k)
+            mine.append((self.r.ipc_export(g), self.r.ipc_export(v)))
+        mine.append(self.r.ipc_export(self.r.halo_local(0)[2]))
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        for q, theirs in enumerate(everyone):
+            if q == self.rank:
+                continue
+            flags = self.r.ipc_open(theirs[-1])
+            self._ipc.append(flags)
+            for k, (hg, hv) in enumerate(theirs[:-1]):
+                g, v = self.r.ipc_open(hg), self.r.ipc_open(hv)
+                self._ipc += [g, v]
+                self.r.halo_connect(self.rank, q, k, g, v, flags)
+        dist.barrier(group=self.group)
+        self.halo = True
+        return True
+
+    def disconnect_halo(self):
+        if not self.halo:
+            return
+        import torch.distributed as dist
+
+        self.r.sync()
+        dist.barrier(group=self.group)  # nobody may still be pushing into a mapping that is about to go
+        self.r.halo_disconnect()
+        for p in self._ipc:
+            self.r.ipc_close(p)
+        self._ipc = []
+        self.halo = False
+
+    def _band_plan(self):
+        """(sends, recv_ranks) of this rank's band for orb_denoise_band, from the plan both sides agree on."""
+        key = tuple(self.bands)
+        if self._plan_key != key:
+            plan = halo_plan(self.bands, self.rank, self.r.H, self.iters)
+            self._plan = ([(q, a, b) for q, (a, b), kind in plan if kind == "send"],
+                          sorted({q for q, _, kind in plan if kind == "recv"}))
+            self._plan_key = key
+        return self._plan
 
     def _span(self, name):
         """Context manager: CUDA-event pair around a collective when self.spans is a dict."""
@@ -305,7 +373,13 @@ class TiledRenderer:
         import torch.distributed as dist
 
         nccl = dist.get_backend(self.group) == "nccl"
-        assemble(self._t("accum"), self.bands, self.rank, self.group)  # progressive sums follow their rows
+        self.r.sync()  # every frame in flight has left the shared accum and the peers' halo rows
+        if nccl:
+            with torch.cuda.stream(self.slot_stream()):
+                assemble(self._t("accum"), self.bands, self.rank, self.group)  # progressive sums follow their rows
+            self.slot_stream().synchronize()
+        else:
+            assemble(self._t("accum"), self.bands, self.rank, self.group)
         if self.row_cost is None or measured_ms is None:
             counts = self.r.row_active_counts()
             y0, y1 = self.band
@@ -332,8 +406,8 @@ class TiledRenderer:
         return self.bands
 
     def render_ratio_frame(self, accum_id, mode=1, shadow_spp=4, denoise=True):
-        """RATIO frame + denoise + combine for this rank's band; asynchronous on the renderer's stream
-        (the collectives run on the current torch stream, which must be the renderer's)."""
+        """RATIO frame + denoise + combine for this rank's band; asynchronous on the stream of the frame slot the
+        render takes (torch-side exchanges are issued on that same stream, slot_stream())."""
         from . import api
 
         y0, y1 = self.band
@@ -343,13 +417,19 @@ class TiledRenderer:
         if denoise:
             if self.world == 1:
                 self.r.denoise(iterations=self.iters)
+            elif self.halo:
+                sends, recv = self._band_plan()
+                self.r.denoise_band((y0, max(y0, y1)), sends, recv, iterations=self.iters)  # every rank, every frame
             else:
-                if y1 > y0:
-                    self.r.denoise_pack(rows=rows)
-                with self._span("halo_exchange"):
-                    exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
-                if y1 > y0:
-                    self.r.denoise_filter(iterations=self.iters, rows=rows)
+                import torch
+
+                with torch.cuda.stream(self.slot_stream()):
+                    if y1 > y0:
+                        self.r.denoise_pack(rows=rows)
+                    with self._span("halo_exchange"):
+                        exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
+                    if y1 > y0:
+                        self.r.denoise_filter(iterations=self.iters, rows=rows)
         if y1 > y0:
             self.r.ratio_combine(use_denoised=denoise, rows=rows)
 
@@ -371,7 +451,7 @@ class TiledRenderer:
             return
         import torch
 
-        cur = torch.cuda.current_stream()
+        cur = self.slot_stream()
         if self._comm is None:
             self._comm = torch.cuda.Stream()
         if self._done is not None:
@@ -379,12 +459,13 @@ class TiledRenderer:
         if self._read is not None:
             cur.wait_event(self._read)  # ... and so does its read-back to the host
         y0, y1 = self.band
-        for n in names:
-            v = self._t(n)
-            if n not in self.out:
-                self.out[n] = torch.empty_like(v)
-            if y1 > y0:
-                self.out[n][y0:y1].copy_(v[y0:y1])
+        with torch.cuda.stream(cur):
+            for n in names:
+                v = self._t(n)
+                if n not in self.out:
+                    self.out[n] = torch.empty_like(v)
+                if y1 > y0:
+                    self.out[n][y0:y1].copy_(v[y0:y1])
         ready = torch.cuda.Event()
         ready.record(cur)
         with torch.cuda.stream(self._comm):
@@ -433,15 +514,17 @@ class TiledRenderer:
         if self._read is not None:
             self._read.synchronize()
 
-    def wait_assembled(self):
+    def wait_assembled(self, stream=None):
+        """Orders `stream` (default: the active frame slot's) behind the last gather."""
         if self._done is not None:
-            import torch
-
-            torch.cuda.current_stream().wait_event(self._done)
+            (stream or self.slot_stream()).wait_event(self._done)
 
     def assemble(self, names):
         if self.world == 1:
             return
-        with self._span("assemble"):
-            for n in names:
-                assemble(self._t(n), self.bands, self.rank, self.group)
+        import torch
+
+        with torch.cuda.stream(self.slot_stream()):
+            with self._span("assemble"):
+                for n in names:
+                    assemble(self._t(n), self.bands, self.rank, self.group)

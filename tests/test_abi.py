@@ -22,7 +22,7 @@ def test_header_symbols_exported():
     assert len(names) >= 40
     for n in names:
         assert hasattr(lib, n), "liborb200.so does not export " + n
-    assert lib.orb_api_version() == 1
+    assert lib.orb_api_version() == 2
 
 
 def test_struct_layouts_match_header():

@@ -649,3 +649,93 @@ def test_refit_after_moving_meshes(renderer_factory, builder, n_tris):
     got = r.trace_rays(org, d)
     for a, b in zip(got, want):
         assert np.array_equal(a, b)
+
+
+def test_two_frame_slots_equal_one(renderer_factory):
+    """orb_set_frame_slots(2): consecutive frames alternate between two buffer sets and two streams; accum / RGBA8 are
+    shared and ordered.  Frames, the running sum and the ray totals equal those of a one-slot context bit for bit,
+    for RATIO (+ denoise + combine on the frame's slot) and PATH, with pipelined read-backs of every frame."""
+    import torch
+    sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
+    a, b = renderer_factory(sc), renderer_factory(sc)
+    b.set_frame_slots(2)
+    assert b.frame_slots == 2 and a.frame_slots == 1
+    n = 6
+    pin = torch.empty((n, 96, 160, 4), dtype=torch.float32, pin_memory=True).numpy()
+    pin_u = torch.empty((n, 96, 160), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+    want = []
+    for i in range(n):
+        a.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4)
+        a.denoise(iterations=3)
+        a.ratio_combine(use_denoised=True)
+        want.append((a.download("ratio_final"), a.download("rgba8"), a.download("accum")))
+        b.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, sync=False)
+        assert b.frame_slot == (i + 1) % 2
+        b.denoise(iterations=3)
+        b.ratio_combine(use_denoised=True)
+        b.download_async("ratio_final", pin[i])
+        b.download_async("rgba8", pin_u[i])
+    b.sync()
+    b.download_wait()
+    for i in range(n):
+        assert np.array_equal(pin[i], want[i][0], equal_nan=True), i
+        assert np.array_equal(pin_u[i], want[i][1]), i
+    assert np.array_equal(b.download("accum"), want[-1][2], equal_nan=True)
+    ca, cb = a.counters(), b.counters()
+    for k in ("rays_primary", "rays_shadow_total", "active_pixels_total"):
+        assert ca[k] == cb[k], k
+    for i in range(4):
+        a.render(api.PATH, accum_id=i, mode=1, max_depth=5)
+        b.render(api.PATH, accum_id=i, mode=1, max_depth=5, sync=False)
+    b.sync()
+    assert np.array_equal(a.download("accum"), b.download("accum"), equal_nan=True)
+    assert a.counters()["rays_bounce_total"] == b.counters()["rays_bounce_total"]
+    b.set_frame_slots(1)      # back to one slot: buffers re-allocated, frames still right
+    b.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    a.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    assert np.array_equal(a.download("sto_direct"), b.download("sto_direct"), equal_nan=True)
+
+
+@pytest.mark.parametrize("slots", [1, 2])
+def test_band_handoff_through_peer_stores(renderer_factory, slots):
+    """The fused tile hand-off (csrc/halo.cuh, orb_denoise_band): three contexts of ONE process play the ranks of a
+    row-band partition -- bands of 50 / 8 / 102 rows, the middle one narrower than the filter's reach so its
+    neighbours' halos span two peers -- each packing its band and storing the rows the others' filters read straight
+    into their buffers, ordered by epoch flags only.  Denoised bands equal the same rows of a whole-frame denoise bit
+    for bit over several frames (both frame slots in use), and no flag wait times out."""
+    from optix_renderer_b200 import tiles
+    W, H, iters = 96, 160, 4
+    sc = scenes.scene_cornell(W, H)
+    bands = [(0, 50), (50, 58), (58, 160)]
+    ranks = [renderer_factory(sc) for _ in bands]
+    for r in ranks:
+        r.set_frame_slots(slots)
+    ptrs = [[r.halo_local(k) for k in range(slots)] for r in ranks]
+    for i, ri in enumerate(ranks):
+        for j in range(len(ranks)):
+            if i != j:
+                for k in range(slots):
+                    ri.halo_connect(i, j, k, *ptrs[j][k])
+    whole = renderer_factory(sc)
+    for frame in range(5):
+        whole.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4)
+        whole.denoise(iterations=iters)
+        want = {k: whole.download(k) for k in ("sto_direct_dn", "sto_no_vis_dn")}
+        for i, r in enumerate(ranks):
+            r.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4, rows=bands[i], sync=False)
+            plan = tiles.halo_plan(bands, i, H, iters)
+            sends = [(q, a, b) for q, (a, b), kind in plan if kind == "send"]
+            recv = sorted({q for q, _, kind in plan if kind == "recv"})
+            assert sends and recv
+            r.denoise_band(bands[i], sends, recv, iterations=iters)
+        for i, r in enumerate(ranks):
+            for k in want:
+                assert np.array_equal(r.download(k, rows=bands[i]), want[k][bands[i][0]:bands[i][1]], equal_nan=True), (frame, i, k)
+    for r in ranks:
+        assert r.halo_status() == 0
+    with pytest.raises(api.OrbError, match="not connected"):
+        ranks[0].denoise_band(bands[0], [(5, 10, 20)], [])
+    for r in ranks:
+        r.halo_disconnect()
+    with pytest.raises(api.OrbError, match="no peers"):
+        ranks[0].denoise_band(bands[0], [], [])
