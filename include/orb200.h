@@ -227,6 +227,7 @@ int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_set_frame_slots(OrbContext* ctx, int32_t n_slots);
 int32_t orb_frame_slot(OrbContext* ctx);  /* slot of the frame the calls currently refer to */
 int32_t orb_frame_slots(OrbContext* ctx);
+void* orb_slot_stream(OrbContext* ctx, int32_t slot); /* cudaStream_t of a frame slot (to order a caller's stream behind it) */
 
 /* ---- stand-alone passes over RESIDENT frame buffers (rows [y0,y1), 0,0 = all) ---- */
 /* ltcDirectLighingBaseline over the G-buffer (position, normal, albedo, alpha) -> ORB_BUF_LTC;

@@ -119,6 +119,8 @@ def load_library():
     L.orb_set_frame_slots.argtypes = [vp, C.c_int32]
     L.orb_frame_slot.argtypes = [vp]
     L.orb_frame_slots.argtypes = [vp]
+    L.orb_slot_stream.argtypes = [vp, C.c_int32]
+    L.orb_slot_stream.restype = vp
     L.orb_ltc_gbuffer_pass.argtypes = [vp, C.c_int32, C.c_int32]
     L.orb_denoise.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32]
     L.orb_denoise_pack.argtypes = [vp, C.c_int32, C.c_int32]
@@ -295,6 +297,10 @@ class Renderer:
     @property
     def frame_slots(self):
         return int(self.lib.orb_frame_slots(self._h))
+
+    def slot_stream(self, k):
+        """cudaStream_t (as int) of frame slot k."""
+        return self.lib.orb_slot_stream(self._h, int(k))
 
     def ltc_gbuffer_pass(self, rows=None):
         y0, y1 = rows if rows else (0, 0)

@@ -1187,6 +1187,7 @@ struct OrbContext : FrameSlot {
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
+    int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
     int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
     float* unit_out = nullptr;
@@ -1442,6 +1443,35 @@ static int build_qnodes(OrbContext* c) {
     return ORB_OK;
 }
 
+// ORB_L2_PERSIST_MB: an access-policy window over the node array on every frame stream -- node lines are kept in
+// the persisting part of L2 while the ray stream and the frame buffers pass through the rest.
+static int apply_l2_window(OrbContext* c) {
+    if (c->l2_persist_mb <= 0 || c->bvh.n_nodes <= 0) return ORB_OK;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, c->device));
+    const bool qn = use_qnodes(c);
+    const void* base = qn ? (const void*)c->qnodes : (const void*)c->bvh.nodes;
+    size_t bytes = (size_t)c->bvh.n_nodes * (qn ? sizeof(QNode) : sizeof(BvhNode));
+    size_t want = std::min<size_t>((size_t)c->l2_persist_mb << 20, (size_t)prop.persistingL2CacheMaxSize);
+    if (want == 0) return ORB_OK;
+    CK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want));
+    bytes = std::min<size_t>(bytes, (size_t)prop.accessPolicyMaxWindowSize);
+    cudaStreamAttrValue a;
+    memset(&a, 0, sizeof a);
+    a.accessPolicyWindow.base_ptr = const_cast<void*>(base);
+    a.accessPolicyWindow.num_bytes = bytes;
+    a.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)bytes);
+    a.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    a.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    for (int k = 0; k < c->n_slots; k++) {
+        cudaStream_t st = k == c->cur_slot ? c->stream : c->parked[k].stream;
+        if (st) CK(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &a));
+    }
+    fprintf(stderr, "orb200: L2 window %.1f MB over the nodes (persisting L2 %.1f MB, hit ratio %.2f)\n", bytes / 1048576.0,
+            want / 1048576.0, a.accessPolicyWindow.hitRatio);
+    return ORB_OK;
+}
+
 extern "C" {
 
 int orb_api_version(void) { return ORB_API_VERSION; }
@@ -1473,6 +1503,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
+    if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
@@ -1529,6 +1560,10 @@ int orb_set_frame_slots(OrbContext* c, int32_t n) {
 }
 
 int32_t orb_frame_slot(OrbContext* c) { return c ? c->cur_slot : -1; }
+void* orb_slot_stream(OrbContext* c, int32_t k) {
+    if (!c || k < 0 || k >= c->n_slots) return nullptr;
+    return (void*)(k == c->cur_slot ? c->stream : c->parked[k].stream);
+}
 int32_t orb_frame_slots(OrbContext* c) { return c ? c->n_slots : 0; }
 
 void* orb_stream(OrbContext* c) { return c ? (void*)c->stream : nullptr; }
@@ -1731,6 +1766,10 @@ int orb_scene_commit(OrbContext* c, const OrbBvhOptions* opt) {
     CK(allow_smem(k_path_bounce<false>, trace_smem(c)));
     CK(allow_smem(k_trace_rays, trace_smem(c)));
     c->committed = true;
+    {
+        int rcw = apply_l2_window(c);
+        if (rcw) return rcw;
+    }
     // host staging is no longer needed
     std::vector<float>().swap(c->h_pos);
     std::vector<float>().swap(c->h_nrm);

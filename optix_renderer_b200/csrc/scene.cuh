@@ -82,9 +82,15 @@ ORB_HD void tri_record(float* a8, float* b2, const float* p9, int prim) {  // wr
 ORB_HD void tri_fetch(const SceneView& s, int k, float4& t0, float4& t1, float4& t2) {
 #ifdef __CUDA_ARCH__
     float e2x;
+#if defined(ORB_TRI_FETCH) && ORB_TRI_FETCH == 1  // A/B: two 128-bit loads instead of one 256-bit load
+    t0 = __ldg(s.tri + 2 * (size_t)k);
+    t1 = __ldg(s.tri + 2 * (size_t)k + 1);
+    e2x = t1.w;
+#else
     asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(t0.x), "=f"(t0.y), "=f"(t0.z), "=f"(t0.w), "=f"(t1.x), "=f"(t1.y), "=f"(t1.z), "=f"(e2x)
         : "l"(s.tri + 2 * (size_t)k));
+#endif
     const float2 b = __ldg(s.tri_b + k);
 #else
     const float4 a0 = s.tri[2 * (size_t)k], a1 = s.tri[2 * (size_t)k + 1];

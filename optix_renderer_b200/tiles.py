@@ -281,10 +281,25 @@ class TiledRenderer:
         """torch handle of the stream the active frame slot's kernels run on (the library's own stream)."""
         import torch
 
-        k = self.r.frame_slot
+        return self.stream_of(self.r.frame_slot)
+
+    def stream_of(self, k):
+        import torch
+
         if k not in self._streams:
-            self._streams[k] = torch.cuda.ExternalStream(self.r.stream())
+            self._streams[k] = torch.cuda.ExternalStream(self.r.slot_stream(k))
         return self._streams[k]
+
+    def join(self, stream):
+        """Orders `stream` behind everything enqueued so far on every frame slot and behind the last assembly."""
+        import torch
+
+        for k in range(self.r.frame_slots):
+            e = torch.cuda.Event()
+            e.record(self.stream_of(k))
+            stream.wait_event(e)
+        if self._done is not None:
+            stream.wait_event(self._done)
 
     def connect_halo(self):
         """Map every other rank's packed denoise buffers and control block into this process (cudaIpc handles

@@ -668,7 +668,7 @@ def test_two_frame_slots_equal_one(renderer_factory):
         a.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4)
         a.denoise(iterations=3)
         a.ratio_combine(use_denoised=True)
-        want.append((a.download("ratio_final"), a.download("rgba8"), a.download("accum")))
+        want.append((a.download("ratio_final"), a.download("rgba8"), a.download("accum"), (a.download("normal")[..., :3] != 0).any(-1)))
         b.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, sync=False)
         assert b.frame_slot == (i + 1) % 2
         b.denoise(iterations=3)
@@ -678,7 +678,11 @@ def test_two_frame_slots_equal_one(renderer_factory):
     b.sync()
     b.download_wait()
     for i in range(n):
-        assert np.array_equal(pin[i], want[i][0], equal_nan=True), i
+        # compared on the pixels frame i WRITES: a pixel whose primary ray misses keeps what an earlier frame of the
+        # same buffer set left in ltc / sto_* (as in the reference, deviceCode.cu:90-94) -- frame i-1 with one slot,
+        # frame i-2 with two
+        w = want[i][3]
+        assert np.array_equal(pin[i][w], want[i][0][w], equal_nan=True), i
         assert np.array_equal(pin_u[i], want[i][1]), i
     assert np.array_equal(b.download("accum"), want[-1][2], equal_nan=True)
     ca, cb = a.counters(), b.counters()
@@ -721,6 +725,7 @@ def test_band_handoff_through_peer_stores(renderer_factory, slots):
         whole.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4)
         whole.denoise(iterations=iters)
         want = {k: whole.download(k) for k in ("sto_direct_dn", "sto_no_vis_dn")}
+        wrote = (whole.download("normal")[..., :3] != 0).any(-1)   # miss pixels keep an earlier frame's values (per buffer set)
         for i, r in enumerate(ranks):
             r.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4, rows=bands[i], sync=False)
             plan = tiles.halo_plan(bands, i, H, iters)
@@ -730,7 +735,8 @@ def test_band_handoff_through_peer_stores(renderer_factory, slots):
             r.denoise_band(bands[i], sends, recv, iterations=iters)
         for i, r in enumerate(ranks):
             for k in want:
-                assert np.array_equal(r.download(k, rows=bands[i]), want[k][bands[i][0]:bands[i][1]], equal_nan=True), (frame, i, k)
+                m = wrote[bands[i][0]:bands[i][1]]
+                assert np.array_equal(r.download(k, rows=bands[i])[m], want[k][bands[i][0]:bands[i][1]][m], equal_nan=True), (frame, i, k)
     for r in ranks:
         assert r.halo_status() == 0
     with pytest.raises(api.OrbError, match="not connected"):
