@@ -160,9 +160,12 @@ def workload_config(args, n):
             "width": W, "height": H, "triangles": N_TRIS, "tri_lights": 2 * N_QUADS, "shadow_spp": SPP,
             "max_depth": DEPTH if args.workload == "path" else 1,
             "lut": "8x8 (reference ltc_isotropic.h)" if args.lut == 8 else "%dx%d (bilinear resampling of the reference table)" % (args.lut, args.lut),
-            "partition": ("%d cost-balanced row bands, BVH replicated, point-to-point exchange of the packed denoise halo "
-                          "rows, NCCL all-gather of the finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
-            "l2": "working set per frame (13+ float4 frame buffers of 33 MB, 48 MB triangles, 64 MB BVH) exceeds the "
+            "partition": ("%d cost-balanced row bands, BVH replicated, packed denoise halo rows stored into the neighbours' "
+                          "buffers by the pack kernel (peer-mapped memory over NVLink, epoch flags), NCCL all-gather of the "
+                          "finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
+            "frames_in_flight": "2 per GPU (orb_set_frame_slots): frame i+1's kernels run beside frame i's traversal tail; "
+                                "accum / RGBA8 shared and accumulated in order",
+            "l2": "working set per frame (2 x 13+ float4 frame buffers of 33 MB, 40 MB triangles, 37 MB BVH) exceeds the "
                   "126 MB L2; no explicit flush"}
 
 
@@ -220,9 +223,11 @@ def run_ours(args):
     if args.lut != 8:
         sc["lut"] = scenes.upsample_lut(sc["lut"], args.lut)
     r = api.Renderer(sc, device=local, quantise_lut=1)  # table fetched with the texture unit's weights, as the reference's tex2D
-    stream = torch.cuda.Stream()
-    r.set_stream(stream.cuda_stream)
+    SLOTS = max(1, min(2, int(os.environ.get("ORB_BENCH_SLOTS", "2"))))  # frames in flight per GPU (orb_set_frame_slots)
+    r.set_frame_slots(SLOTS)
+    stream = torch.cuda.Stream()  # carries the timing events; ordered behind the frame slots' own streams by T.join()
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
+    HALO = world > 1 and ratio and os.environ.get("ORB_BENCH_HALO", "1") == "1" and T.connect_halo()
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
 
     SYNC_ASSEMBLE = bool(os.environ.get("ORB_BENCH_SYNC_ASSEMBLE"))  # A/B: gather in place on the render stream
@@ -236,7 +241,7 @@ def run_ours(args):
 
     def step(i):
         # the finished band is handed to a side stream that all-gathers it while this stream renders the next
-        # frame; T.wait_assembled() (before the closing event / before a read) puts the last gather back in order
+        # frame; T.join(stream) (before the closing event / before a read) orders `stream` behind the last gather
         render(i)
         if SYNC_ASSEMBLE:
             T.assemble(out_names)
@@ -244,6 +249,7 @@ def run_ours(args):
             T.assemble_async(out_names)
 
     def barrier():
+        r.sync()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -263,43 +269,51 @@ def run_ours(args):
         base_id = args.warmup + n_calib  # accumId of the first timed frame
         for i in range(args.warmup + n_calib):  # N > 1: n_calib extra untimed frames first, to settle the band cuts
             if world > 1:
-                T.wait_assembled()
                 # cut the row bands by cost: a model from the first frame's active pixels, then corrected by
                 # this rank's measured kernel time for its band (stage timers: the collectives and the
                 # waiting for slower neighbours are not in it) over the following warm-up frames
                 r.set_profiling(True)
                 r.stage_times()
                 step(i)
-                mine_ms = sum(t for t, _ in r.stage_times().values())
+                mine_ms = sum(t for k, (t, _) in r.stage_times().items() if k != "halo")
                 r.set_profiling(False)
                 T.rebalance(None if i == 0 else mine_ms)
             else:
                 step(i)
         barrier()
-        r.set_profiling(True)
-        r.stage_times()
         c0 = r.counters()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
-        if world > 1:
-            T.spans = {}
-        ev0.record(stream)
+        ev0.record(stream)          # every stream is idle: the clock starts here
         for i in range(args.steps):
             step(base_id + i)
-        T.wait_assembled()
+        T.join(stream)              # behind both frame slots and the last assembly
         ev1.record(stream)
         barrier()
         ms = ev0.elapsed_time(ev1)
+        c1 = r.counters()
+        # per-stage CUDA-event times, OUTSIDE the timed region: the same frames one at a time (a sync after each), so
+        # the stages of two frames in flight do not overlap inside each other's event pairs
+        P_FRAMES = max(3, min(10, args.steps))
+        r.set_profiling(True)
+        r.stage_times()
+        if world > 1:
+            T.spans = {}
+        for i in range(P_FRAMES):
+            step(base_id + args.steps + i)
+            r.sync()
         st = r.stage_times()
         coll_ms = T.span_ms() if world > 1 else {}
         T.spans = None
-        c1 = r.counters()
         r.set_profiling(False)
+        st = {k: (t * args.steps / P_FRAMES, n * args.steps / P_FRAMES) for k, (t, n) in st.items()}  # per `steps` frames, as below
+        coll_ms = {k: v * args.steps / P_FRAMES for k, v in coll_ms.items()}
+        base_id += P_FRAMES
         ms = reduce(ms, dist.ReduceOp.MAX) if world > 1 else ms
         rank_ms = None
         if world > 1:  # every rank's own kernel time per frame (stage timers): how even the bands are
             mine = torch.zeros(world, dtype=torch.float64, device="cuda")
-            mine[rank] = sum(t for t, _ in st.values()) / args.steps
+            mine[rank] = sum(t for k, (t, _) in st.items() if k != "halo") / args.steps  # halo = waiting for the peers' flags
             dist.all_reduce(mine)
             rank_ms = [round(x, 4) for x in mine.tolist()]
         d = {k: c1[k] - c0[k] for k in ("rays_primary", "rays_shadow_total", "rays_bounce_total", "kernel_launches",
@@ -346,17 +360,18 @@ def run_ours(args):
                     # the assembled frame lives in T.out: read back behind the gather, beside the next frame
                     T.read_back_async({out_names[0]: t_f4[i & 1], "rgba8": t_u32[i & 1]})
                 elif rank == 0:
-                    T.wait_assembled()
+                    T.join(stream)
+                    stream.synchronize()
                     t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
                     t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
                     torch.cuda.current_stream().synchronize()
             if HOST_GATHER:
-                T.wait_assembled()
-                torch.cuda.current_stream().synchronize()
+                T.join(stream)
+                stream.synchronize()
                 T.wait_read_back_bands()  # every band of the last frame is on the host when the clock stops
             elif world > 1 and rank == 0:
-                T.wait_assembled()
-                torch.cuda.current_stream().synchronize()
+                T.join(stream)
+                stream.synchronize()
                 T.wait_read_back()  # the last frame is on the host when the clock stops
             if world == 1 and pipelined:
                 r.sync()
@@ -379,7 +394,8 @@ def run_ours(args):
         if ratio and world > 1 and rank == 0:
             # parity of the partitioned job: the frame assembled from N bands (halo rows exchanged, bands gathered)
             # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
-            T.wait_assembled()
+            T.join(stream)
+            stream.synchronize()
             got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
             if HOST_GATHER:  # the frame as the host received it: N bands, each copied by its own rank
                 got = torch.from_numpy(np.array(shared[out_names[0]][(e_steps - 1) & 1])).to("cuda")
@@ -406,7 +422,8 @@ def run_ours(args):
             # parity of the partitioned PATH job: frame accumId = 0 (accum = that frame's colour, no history, so the
             # band cuts that moved during warm-up do not matter) rendered in N bands and gathered in place, against
             # the same frame rendered whole by rank 0 -- bit for bit, outside every timed region
-            T.wait_assembled()
+            T.join(stream)
+            stream.synchronize()
             render(0)
             T.assemble(out_names)
             torch.cuda.synchronize()
@@ -470,22 +487,50 @@ def run_ours(args):
         n_top = tp["launches_per_frame"]
         kernel_of = {"trace": "k_trace_stream_spec", "path": "k_path_persistent", "ltc": "k_ltc", "primary": "k_primary",
                      "denoise": "k_denoise_atrous"}
-        traffic, traffic_src = None, None
-        tj = os.path.join(ROOT, "profiles", "roofline_traffic.json")  # dram bytes per launch from the ncu --set full capture
-        if os.path.exists(tj):
-            e = json.load(open(tj)).get(kernel_of.get(top, top))
-            if e and world == 1:
-                traffic, traffic_src = e["dram_bytes_per_launch"], e["source"]
-        roofline = {"kernel": kernel_of.get(top, top), "stage": top, "bound": "hbm", "achieved": tp["gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": tp["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src,
-                    "peak_source": peak_src, "avg_launch_ms": tp["ms_per_frame"] / n_top,
-                    "algorithmic_bytes_per_launch": tp["algorithmic_bytes"] / n_top,
-                    "share_of_step": tp["ms_per_frame"] / (ms / args.steps),
-                    "note": "algorithmic bytes of the traversal kernel = node records fetched x 64 B + triangle records "
-                            "tested x 48 B (counted by the instrumented kernel on this workload) + 48 B of stream per "
-                            "ray.  Nearly all of them are served by L1/L2 (traffic = what reached DRAM), so the HBM "
-                            "fraction says how far the kernel is from streaming its fetches, not that HBM limits it: "
-                            "ncu shows it issue / L1-pipe bound (profiles/)"}
+        # ---- roofline of the dominant kernel --------------------------------------------------------------------
+        # The traversal kernels are not HBM-bound (their fetches are served by L1 / L2): the roofs they are under are
+        # the SM's issue slots and the L1 data pipe (one wavefront per cycle and SM).  Numerators come from the
+        # committed `ncu --set full` capture of this same workload (profiles/roofline_traffic.json, written by
+        # tools/ncu_summary.py --json: warp instructions, L1 wavefronts and DRAM bytes per launch -- the workload is
+        # deterministic), denominators from THIS run: the kernel's CUDA-event time and the SM clock sampled under load.
+        kname = kernel_of.get(top, top)
+        n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+        clk_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        dur_s = tp["ms_per_frame"] / n_top * 1e-3
+        cap = None
+        tj = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tj) and world == 1 and args.scene == "cfg3":
+            cap = json.load(open(tj)).get(kname)
+        roofline = {"kernel": kname, "stage": top, "avg_launch_ms": dur_s * 1e3,
+                    "share_of_step_serial": tp["ms_per_frame"] / sum(v["ms_per_frame"] for v in passes.values()),
+                    "sm_clock_mhz": clk_hz / 1e6, "sms": n_sm,
+                    "fetched_bytes_per_launch": tp["algorithmic_bytes"] / n_top if tp["algorithmic_bytes"] else None,
+                    "fetched_gbs": tp["gbs"], "hbm_peak_gbs": peak, "peak_source": peak_src}
+        if cap and cap.get("warp_inst") and top in ("trace", "path", "primary"):
+            issue_rate, issue_peak = cap["warp_inst"] / dur_s, n_sm * 4 * clk_hz
+            l1_rate, l1_peak = (cap.get("l1_wavefronts") or 0) / dur_s, n_sm * clk_hz
+            l1_bound = l1_rate / l1_peak > issue_rate / issue_peak
+            roofline.update({
+                "bound": "l1-wavefronts" if l1_bound else "issue",
+                "achieved": (l1_rate if l1_bound else issue_rate) / 1e9, "peak": (l1_peak if l1_bound else issue_peak) / 1e9,
+                "unit": "G wavefronts/s" if l1_bound else "G warp-instructions/s",
+                "frac": (l1_rate / l1_peak) if l1_bound else (issue_rate / issue_peak),
+                "issue_frac": issue_rate / issue_peak, "l1_wavefront_frac": l1_rate / l1_peak if l1_rate else None,
+                "lanes_per_inst": cap.get("threads_per_inst"), "traffic": cap.get("dram_bytes_per_launch"),
+                "hbm_frac": cap["dram_bytes_per_launch"] / dur_s / 1e9 / peak if cap.get("dram_bytes_per_launch") else None,
+                "counts_source": cap.get("source"),
+                "note": "issue roof = SMs x 4 schedulers x SM clock; L1 roof = SMs x 1 wavefront per cycle x SM clock; "
+                        "instruction / wavefront / DRAM-byte counts per launch from the committed ncu capture of this "
+                        "workload, duration and clock measured in this run.  fetched_* = node and triangle records "
+                        "fetched (counted by the instrumented twin) -- served by L1 / L2, not an HBM figure"})
+        elif top in ("trace", "path", "primary"):
+            roofline.update({"bound": "issue", "achieved": None, "peak": n_sm * 4 * clk_hz / 1e9, "unit": "G warp-instructions/s",
+                             "frac": None, "traffic": None,
+                             "note": "no ncu capture of this kernel on this partition / scene under profiles/roofline_traffic.json: "
+                                     "counts unknown (the capture is the single-GPU full frame of configs[2] / configs[3])"})
+        else:  # a streaming pass on top: HBM roof, algorithmic bytes over its own time
+            roofline.update({"bound": "hbm", "achieved": tp["gbs"], "peak": peak, "unit": "GB/s", "frac": tp["frac_of_hbm_peak"],
+                             "traffic": cap.get("dram_bytes_per_launch") if cap else None})
         if one_quad:
             b = px * 32 + active * 48  # normal read + ltc written everywhere; position, albedo, alpha where a surface was hit
             line_ltc = {"tri_lights": 2, "ms": one_quad, "algorithmic_bytes": b, "gbs": b / (one_quad * 1e-3) / 1e9,
@@ -514,7 +559,11 @@ def run_ours(args):
                                    "rank 0's copy of the assembled frame" + ("" if SYNC_ASSEMBLE or SYNC_DOWNLOAD else
                                    " on a copy stream, behind the all-gather and beside the next frame's kernels; the "
                                    "last copy is waited for inside the timed region"))},
-                "gpu_launches": int(launches), "roofline": roofline, "passes": passes, "clocks": clocks}
+                "gpu_launches": int(launches), "frames_in_flight": SLOTS, "roofline": roofline, "passes": passes,
+                "passes_note": "per-stage CUDA-event times of %d extra frames run ONE AT A TIME after the timed region "
+                               "(with %d frames in flight the stages of consecutive frames overlap, so their sum "
+                               "exceeds ms_per_step)" % (P_FRAMES, SLOTS),
+                "clocks": clocks}
         if PIPE:
             line["e2e"]["serial_ms_per_step"] = serial_ms / e_steps  # the same loop with a blocking download per frame
             line["e2e"]["readback_equals_device_frame"] = readback_ok
@@ -526,6 +575,8 @@ def run_ours(args):
             line["assembled_frame_equals_single_gpu_frame"] = same
             line["rank_kernel_ms_per_frame"] = rank_ms
             line["collectives_ms_per_frame_rank0"] = {k: v / args.steps for k, v in coll_ms.items()}
+            line["halo"] = ("peer stores inside k_denoise_pack + epoch flags (orb_denoise_band); status %d" % r.halo_status()) if HALO \
+                else ("torch.distributed point-to-point" if ratio else None)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_sample(args.workload)
         sys.stdout.flush()

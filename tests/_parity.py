@@ -176,6 +176,9 @@ def classify_hit_mismatches(got, ref, cam_pos, scene=None, edge_tol=1e-4, angle_
                 return prim >= 0 and min(uv[0], uv[1], 1.0 - uv[0] - uv[1]) <= edge_tol
             is_edge = near(ug[k], g[k]) or near(ur[k], r[k])
         out["edge" if is_edge else "other"] += 1
+        if not is_edge:
+            out.setdefault("others", []).append({"got": int(g[k]), "ref": int(r[k]), "t_got": float(tg), "t_ref": float(tr),
+                                                 "edge_angle_rad": float(ang) if scene is not None else None})
     if scene is not None:
         out["max_edge_angle_rad"] = worst
     return out
