@@ -353,8 +353,8 @@ bool load_obj(const std::string& obj_file, std::vector<Mesh>& out, std::string* 
                 std::string tp = mt.map_kd;
                 for (auto& ch : tp)
                     if (ch == '\\') ch = '/';
-                if (!load_ppm_rgba8(base + tp, m.tex, m.tex_w, m.tex_h) && !warned[tp]++)
-                    fprintf(stderr, "Could not load texture from %s (binary PPM only)\n", (base + tp).c_str());
+                if (!load_image_rgba8(base + tp, m.tex, m.tex_w, m.tex_h) && !warned[tp]++)
+                    fprintf(stderr, "Could not load texture from %s (PNG, TGA and binary PPM are read)\n", (base + tp).c_str());
             }
             out.push_back(std::move(m));
         }

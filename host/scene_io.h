@@ -59,5 +59,8 @@ bool load_ltc_lut_npy(const std::string& path, std::vector<float>& m1, std::vect
                       int& w, int& h, std::string* err);
 // binary PPM (P6) reader for map_Kd textures; other formats are reported and ignored
 bool load_ppm_rgba8(const std::string& path, std::vector<uint8_t>& rgba, int& w, int& h);
+// map_Kd files as the reference's stb_image call reads them (src/Model.cpp:81-128): PNG, TGA, binary PPM -> RGBA8,
+// bottom row first (image_io.cpp)
+bool load_image_rgba8(const std::string& path, std::vector<uint8_t>& rgba, int& w, int& h);
 
 }  // namespace orbhost

@@ -20,7 +20,7 @@
 //    unit's 1.8 fixed-point weight quantisation selectable.
 //  * Double promotions of the reference (double PI) are kept where they happen once per pixel
 //    (LUT coordinate, basis); the per-edge `0.5*(1/sqrt(max(1-x*x,1e-7)))` runs in fp32 --
-//    measured effect on the final colour < 1e-6 relative (tests/test_ltc_gpu.py).
+//    measured effect on the final colour < 1e-6 relative (tests/test_hostcheck.py::test_frames, tests/test_gpu_frames.py).
 #pragma once
 #include "vec.cuh"
 
@@ -67,7 +67,24 @@ ORB_HD float m9_get(const M9& m, int r, int c) {
             if (i == r && j == c) v = m.a[i][j];
     return v;
 }
-ORB_HD Mat3 mat3_inverse(const Mat3& in) {
+// The isotropic LTC tables (include/ltc/ltc_isotropic.h:4-8) only populate m00, m02, m11, m20, m22 -- and a bilinear
+// fetch keeps exact zeros -- so the matrix splits into the (x, z) 2x2 block and the y scale: a cofactor inverse of a
+// dozen instructions instead of the select-heavy full-pivot elimination below (~250).  Agrees with the elimination to
+// a few ulp (golden `minv` units, tests/_parity.py check_scalar_units).  Any other matrix takes the general path.
+ORB_HD bool mat3_is_xz_block(const Mat3& m) { return m.r0.y == 0.f && m.r1.x == 0.f && m.r1.z == 0.f && m.r2.y == 0.f; }
+ORB_HD Mat3 mat3_inverse_xz_block(const Mat3& m) {
+    const float inv_det = 1.f / (m.r0.x * m.r2.z - m.r0.z * m.r2.x);
+    Mat3 r;
+    r.r0 = v3(m.r2.z * inv_det, 0.f, -m.r0.z * inv_det);
+    r.r1 = v3(0.f, 1.f / m.r1.y, 0.f);
+    r.r2 = v3(-m.r2.x * inv_det, 0.f, m.r0.x * inv_det);
+    return r;
+}
+
+ORB_HD Mat3 mat3_inverse_general(const Mat3& in);
+ORB_HD Mat3 mat3_inverse(const Mat3& in) { return mat3_is_xz_block(in) ? mat3_inverse_xz_block(in) : mat3_inverse_general(in); }
+
+ORB_HD Mat3 mat3_inverse_general(const Mat3& in) {
     M9 m;
     m.a[0][0] = in.r0.x; m.a[0][1] = in.r0.y; m.a[0][2] = in.r0.z;
     m.a[1][0] = in.r1.x; m.a[1][1] = in.r1.y; m.a[1][2] = in.r1.z;
@@ -299,7 +316,13 @@ struct LtcFrame {
     Mat3 minv;         // inverse of the fetched LTC matrix
     float amplitude;
     bool valid;        // false: wo_local.z < 0 -> colour 0 (deviceCode.cu:27-28)
+    bool xz_block;     // minv has the isotropic sparsity: five multiply-adds per vertex instead of nine
 };
+
+ORB_HD float3 apply_minv(const LtcFrame& f, float3 v) {
+    if (f.xz_block) return v3(f.minv.r0.x * v.x + f.minv.r0.z * v.z, f.minv.r1.y * v.y, f.minv.r2.x * v.x + f.minv.r2.z * v.z);
+    return apply(f.minv, v);
+}
 
 // Everything ltcDirectLighingBaseline does before its light loop.  wo_local as rayGen computes
 // it (deviceCode.cu:84); the function re-normalises it like the reference (:26).
@@ -313,6 +336,7 @@ ORB_HD void ltc_setup(LtcFrame& f, const LtcLut& lut, float3 p, float3 diffuse, 
     const float theta = acosf(wl.z);  // sphericalTheta, utils.cuh:202
     Mat3 m;
     lut.fetch(alpha, theta, m, f.amplitude);
+    f.xz_block = mat3_is_xz_block(m);
     f.minv = mat3_inverse(m);
     const float3 x = normalize(v3(wl.x, wl.y, 0.f));
     const float3 z = v3(0.f, 0.f, 1.f);
@@ -341,8 +365,7 @@ ORB_HD float3 integrate_tri_light(const LtcFrame& f, float3 lv1, float3 lv2, flo
     const float diffuse_shading = clipped_form_factor(a, b, c, false, n_diff);
     float ggx_shading = 0.f;
     if (n_diff != 0) {
-        const float3 ta = normalize(apply(f.minv, a)), tb = normalize(apply(f.minv, b)),
-                     tc = normalize(apply(f.minv, c));
+        const float3 ta = normalize(apply_minv(f, a)), tb = normalize(apply_minv(f, b)), tc = normalize(apply_minv(f, c));
         int n_ggx;
         ggx_shading = clipped_form_factor(ta, tb, tc, n_diff == 4, n_ggx);
     }

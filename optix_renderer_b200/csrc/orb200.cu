@@ -248,9 +248,14 @@ k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4
 // gained nothing: the per-launch floor was not late long rays but the chunk granularity, fixed by
 // the guided chunk sizes below.  Also removed after measurement, round 1: leaf batching without
 // speculation, a compressed 8-wide BVH, bounded pops, 64-bit stack entries -- DESIGN.md section 3.)
+// Ray `pos` of the stream; its hit record goes to hits[slot] (o.w carries the slot, so a generator may ORDER the
+// stream for coherence -- k_shadow_gen_sorted -- without the consumers of the hits knowing).
+__device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsigned pos, float3 o, float3 d, unsigned slot) {
+    st_stream(rays + 2 * (size_t)pos, make_float4(o.x, o.y, o.z, __uint_as_float(slot)));
+    st_stream(rays + 2 * (size_t)pos + 1, make_float4(d.x, d.y, d.z, 0.f));
+}
 __device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsigned id, float3 o, float3 d) {
-    st_stream(rays + 2 * (size_t)id, make_float4(o.x, o.y, o.z, 0.f));
-    st_stream(rays + 2 * (size_t)id + 1, make_float4(d.x, d.y, d.z, 0.f));
+    stream_put_ray(rays, id, o, d, id);
 }
 
 // A warp's claim on the shared work list [0, n): `need` idle lanes (ballot `want`) each get the next unclaimed
@@ -331,7 +336,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
             if (idle && !exhausted) {
                 if (idx < n) {
                     const float4 ro = ld_stream(rays + 2 * (size_t)idx), rd = ld_stream(rays + 2 * (size_t)idx + 1);
-                    ray = idx;
+                    ray = __float_as_uint(ro.w);  // where this ray's hit record goes
                     if (QN) trav_begin_q(t, s, qg, v3(ro), v3(rd));
                     else trav_begin(t, s, v3(ro), v3(rd));
                 } else {
@@ -405,6 +410,72 @@ k_shadow_gen(SceneView s, FrameView f, int frame_id, int spp, float4* __restrict
         rng_skip(rng, 2 + 5 * (int)k);  // two jitter draws, five per earlier sample
         const ShadowSample q = shadow_ray_setup(s, v3(pp), v3(nn), rng);
         stream_put_ray(rays, r, q.origin, q.L);
+    }
+}
+
+// The same rays, ORDERED for the traversal: the queue is cut into chunks of SORT_CHUNK_PX active pixels (a strip of
+// neighbouring 8x4 tiles, in the order k_primary's warps appended them), and inside a chunk the rays are grouped by
+// the TriLight they aim at.  A warp of the stream kernel then holds rays with nearby origins AND nearby targets:
+// lanes walk the same nodes for most of the way down, so their node fetches share L1 wavefronts (the stream kernel is
+// bound by the L1 data pipe: every divergent lane access is its own wavefront, profiles/r2e) and fewer lanes idle
+// while others finish.  (Round 1 binned by light over the WHOLE frame and lost 16 %: origin coherence matters more;
+// here it is kept.)  One CTA per chunk: light index of every ray (the sample's fifth draw) -> shared histogram ->
+// exclusive scan -> scatter.  Hit records still land at hits[pixel * spp + sample]: the resolve kernels are unchanged.
+#define SORT_CHUNK_PX 1024
+#define SORT_MAX_LIGHTS 256
+__global__ void __launch_bounds__(256)
+k_shadow_gen_sorted(SceneView s, FrameView f, int frame_id, int spp, float4* __restrict__ rays, unsigned chunk_px) {
+    __shared__ unsigned hist[SORT_MAX_LIGHTS];
+    __shared__ unsigned warp_tot[8];
+    const unsigned n_px = f.cnt->queue_n;
+    const unsigned n_chunks = (n_px + chunk_px - 1) / chunk_px;
+    for (unsigned chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const unsigned px0 = chunk * chunk_px, px1 = min(px0 + chunk_px, n_px);
+        const unsigned r0 = px0 * (unsigned)spp, n_rays = (px1 - px0) * (unsigned)spp;
+        for (unsigned b = threadIdx.x; b < SORT_MAX_LIGHTS; b += blockDim.x) hist[b] = 0;
+        __syncthreads();
+        // pass 1: the light each ray selects (ratio.cuh:27-33: fifth draw of the sample, int(rand * (numTriLights - 1)))
+        for (unsigned j = threadIdx.x; j < n_rays; j += blockDim.x) {
+            const unsigned r = r0 + j, i = r / (unsigned)spp, k = r - i * (unsigned)spp;
+            const size_t ofs = f.queue[i];
+            Rng rng = rng_seed(frame_id, (uint32_t)(ofs % (size_t)f.W), (uint32_t)(ofs / (size_t)f.W), (uint32_t)f.W);
+            rng_skip(rng, 2 + 5 * (int)k + 4);
+            const float sel = rng_nextf(rng);
+            const int idx = imin(imax((int)(sel * (float)(s.n_lights - 1)), 0), s.n_lights - 1);
+            atomicAdd(&hist[idx & (SORT_MAX_LIGHTS - 1)], 1u);
+        }
+        __syncthreads();
+        // exclusive scan of the 256 bins by 256 threads
+        {
+            const unsigned v = hist[threadIdx.x];
+            unsigned x = v;
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+                if ((threadIdx.x & 31) >= (unsigned)o) x += y;
+            }
+            if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = x;
+            __syncthreads();
+            unsigned base = 0;
+            for (unsigned w = 0; w < (threadIdx.x >> 5); w++) base += warp_tot[w];
+            hist[threadIdx.x] = base + x - v;
+        }
+        __syncthreads();
+        // pass 2: the ray itself, written at its group's next free position
+        for (unsigned j = threadIdx.x; j < n_rays; j += blockDim.x) {
+            const unsigned r = r0 + j, i = r / (unsigned)spp, k = r - i * (unsigned)spp;
+            const size_t ofs = f.queue[i];
+            const float4 pp = __ldg(f.position + ofs), nn = __ldg(f.normal + ofs);
+            Rng rng = rng_seed(frame_id, (uint32_t)(ofs % (size_t)f.W), (uint32_t)(ofs / (size_t)f.W), (uint32_t)f.W);
+            rng_skip(rng, 2 + 5 * (int)k);
+            Rng rsel = rng;
+            rng_skip(rsel, 4);
+            const float sel = rng_nextf(rsel);
+            const int idx = imin(imax((int)(sel * (float)(s.n_lights - 1)), 0), s.n_lights - 1);
+            const ShadowSample q = shadow_ray_setup(s, v3(pp), v3(nn), rng);
+            const unsigned pos = r0 + atomicAdd(&hist[idx & (SORT_MAX_LIGHTS - 1)], 1u);
+            stream_put_ray(rays, pos, q.origin, q.L, r);
+        }
+        __syncthreads();
     }
 }
 
@@ -1133,12 +1204,15 @@ struct FrameSlot {
     // copy stream moves the slot to the host while the next frame renders.
     DlSlot dl[ORB_BUF_COUNT][2];
     int dl_next[ORB_BUF_COUNT] = {};
+    cudaEvent_t pending_dl[8] = {};  // in-place read-backs of this slot's buffers the slot's next frame has to wait for
+    int n_pending_dl = 0;
     cudaEvent_t ev_order = nullptr;  // "everything enqueued on this slot so far" for the other slot's k_accumulate
     int last_spp = 0;
     bool rendered = false;           // a frame has been enqueued on this slot since the last resize
     uint32_t halo_epoch = 0;         // frames whose packed denoise rows this slot has pushed to its peers (halo.cuh)
 };
 #define ORB_MAX_SLOTS 2
+#define ORB_MAX_PENDING_DL 8
 
 // The context IS its active slot (the FrameSlot base: c->stream, c->buf, ... are the active frame's); the other
 // slot is parked in `parked` and swapped in by select_slot().
@@ -1172,8 +1246,10 @@ struct OrbContext : FrameSlot {
     int W = 0, H = 0;
     int refill_min = 12;
     int node_min = 16;
-    // traversal kernels: 3 = 32-byte quantised inner nodes (bvhq.cuh; default), 1 = the 64-byte fp32 nodes (ORB_TRACE_VARIANT)
-    int trace_variant = 3;
+    // traversal kernels: 1 = 64-byte fp32 nodes (default), 3 = the 32-byte quantised nodes of bvhq.cuh (ORB_TRACE_VARIANT).
+    // Measured with the hybrid stack (profiles/r2c_ab_trace.jsonl): trace stage 1.626 ms against 1.726 ms, primary 0.412 against
+    // 0.457 -- the decode (12 LOP3 / PRMT per node) and 4 more registers cost more than the second 256-bit load.
+    int trace_variant = 1;
     // > 0: shrink the stream kernel's grid until every lane expects this many rays.  Measured on a 135-row band:
     // 0.428 / 0.430 / 0.453 / 0.606 / 0.961 ms for 0 / 4 / 8 / 16 / 32 -- parallelism beats shorter tails.
     int min_rays_per_lane = 0;
@@ -1187,6 +1263,8 @@ struct OrbContext : FrameSlot {
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
+    int sort_chunk_px = SORT_CHUNK_PX;  // active pixels per chunk of the ordering (ORB_SORT_CHUNK)
+    int sort_rays = 1;      // RATIO: order the shadow-ray stream by (queue chunk, light) for the traversal (ORB_SORT_RAYS)
     int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
     int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
@@ -1396,7 +1474,7 @@ static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem, int 
 // stack form (template parameter SD of the kernels) and the dynamic shared memory it needs
 static int stack_mode(OrbContext* c) { return (c->local_stack && c->height <= ORB_LOCAL_STACK_MAX) ? c->stack_smem : -1; }
 static size_t stack_bytes(OrbContext* c, int sd) { return sd < 0 ? trace_smem(c) : (size_t)sd * 8 * TRACE_BLOCK; }
-// 32-byte quantised inner nodes (default) or the 64-byte fp32 ones (ORB_TRACE_VARIANT=1)
+// the 64-byte fp32 nodes (default) or the 32-byte quantised ones (ORB_TRACE_VARIANT=3)
 static bool use_qnodes(OrbContext* c) { return c->trace_variant == 3 && c->qnodes != nullptr; }
 
 typedef void (*StreamKernel)(SceneView, const float4*, float4*, const unsigned*, unsigned, unsigned*, int, int, int,
@@ -1503,6 +1581,8 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
+    if (const char* e = getenv("ORB_SORT_RAYS")) c->sort_rays = atoi(e);
+    if (const char* e = getenv("ORB_SORT_CHUNK")) c->sort_chunk_px = std::max(32, atoi(e));
     if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
@@ -1949,6 +2029,8 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
     if (c->n_slots > 1) select_slot(c, (c->cur_slot + 1) % c->n_slots);
     c->rendered = true;
     cudaStream_t st = c->stream;
+    for (int i = 0; i < c->n_pending_dl; i++) CK(cudaStreamWaitEvent(st, c->pending_dl[i], 0));  // in-place read-backs of this slot
+    c->n_pending_dl = 0;
     FrameView f = frame_view(c, y0, y1);
     const int frame_id = cfg->accum_id + 10007;  // deviceCode.cu:65
     const size_t smem = trace_smem(c);
@@ -1991,7 +2073,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                 {
                     StageTimer tm(c, ORB_STAGE_SHADOW, 1);
                     const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
-                    k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
+                    if (c->sort_rays && n_lights > 1)
+                        k_shadow_gen_sorted<<<c->n_sm * 4, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays, (unsigned)c->sort_chunk_px);
+                    else
+                        k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
                     c->counters.kernel_launches++;
                 }
                 rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true,
@@ -2214,6 +2299,7 @@ static int preload_frame_kernels() {
     CK(cudaFuncGetAttributes(&a, k_ltc<true>));
     CK(cudaFuncGetAttributes(&a, k_ltc<false>));
     CK(cudaFuncGetAttributes(&a, k_shadow_gen));
+    CK(cudaFuncGetAttributes(&a, k_shadow_gen_sorted));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<2>));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<4>));
@@ -2500,6 +2586,21 @@ int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t
         CK(cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
+    const bool shared = id == ORB_BUF_ACCUM || id == ORB_BUF_RGBA8;
+    if (c->n_slots > 1 && !shared) {
+        // Two frame slots: this buffer belongs to the frame's slot and is not written again before the NEXT frame on
+        // the slot (two frames later), so the copy stream reads it in place -- no snapshot.  (A snapshot KERNEL would
+        // queue for SMs behind the other slot's persistent traversal kernel and hold back everything enqueued on this
+        // slot after it: measured, PATH e2e 2.97 ms against 1.99 ms device time.)  The slot's next render waits for
+        // the copy (pending_dl), which by then has long finished.
+        CK(cudaEventRecord(sl.ready, c->stream));
+        CK(cudaStreamWaitEvent(c->copy_stream, sl.ready, 0));
+        CK(cudaMemcpyAsync(dst, (const char*)c->buf[id] + row * y0, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+        CK(cudaEventRecord(sl.done, c->copy_stream));
+        if (c->n_pending_dl < ORB_MAX_PENDING_DL) c->pending_dl[c->n_pending_dl++] = sl.done;
+        else CK(cudaStreamWaitEvent(c->stream, sl.done, 0));
+        return ORB_OK;
+    }
     if (sl.cap < bytes) {
         CK(cudaStreamSynchronize(c->copy_stream));
         CK(cudaFree(sl.dev));
@@ -2509,7 +2610,9 @@ int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t
     } else {
         CK(cudaStreamWaitEvent(c->stream, sl.done, 0));  // the slot's previous host copy has left it
     }
-    if (c->dl_snapshot_kernel && bytes % 16 == 0 && (row * y0) % 16 == 0) {
+    // one slot: a kernel snapshots the rows (the copy engines only carry the host copy); two slots, shared accum /
+    // RGBA8: a copy-engine snapshot, which needs no SM while the other slot's persistent kernels hold them all
+    if (c->dl_snapshot_kernel && c->n_slots == 1 && bytes % 16 == 0 && (row * y0) % 16 == 0) {
         const size_t n16 = bytes / 16;
         k_snapshot<<<(unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)c->n_sm * 8), 256, 0, c->stream>>>(
             (const uint4*)((const char*)c->buf[id] + row * y0), (uint4*)sl.dev, n16);
