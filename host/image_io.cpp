@@ -17,6 +17,7 @@
 
 #include "scene_io.h"
 
+namespace orbhost {
 namespace {
 
 bool slurp(const std::string& path, std::string& out) {
@@ -190,3 +191,5 @@ bool load_image_rgba8(const std::string& path, std::vector<uint8_t>& rgba, int& 
     if (ext == ".tga") return load_tga(s, rgba, w, h);
     return false;
 }
+
+}  // namespace orbhost

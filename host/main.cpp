@@ -195,10 +195,10 @@ static void dump_scene(const Scene& sc, int W, int H, int cam_i) {
     for (size_t i = 0; i < sc.meshes.size(); i++) {
         const Mesh& m = sc.meshes[i];
         printf("%s{\"triangles\": %zu, \"material_id\": %u, \"is_light\": %s, \"diffuse\": [%.9g, %.9g, %.9g], \"alpha\": %.9g, "
-               "\"emit\": [%.9g, %.9g, %.9g], \"tex\": [%d, %d], \"vertex_hash\": \"%016llx\", \"normal_hash\": \"%016llx\", "
-               "\"texcoord_hash\": \"%016llx\"}",
+               "\"emit\": [%.9g, %.9g, %.9g], \"tex\": [%d, %d], \"tex_hash\": \"%016llx\", \"vertex_hash\": \"%016llx\", "
+               "\"normal_hash\": \"%016llx\", \"texcoord_hash\": \"%016llx\"}",
                i ? ", " : "", m.index.size() / 3, m.material_id, m.is_light ? "true" : "false", m.diffuse[0], m.diffuse[1],
-               m.diffuse[2], m.alpha, m.emit[0], m.emit[1], m.emit[2], m.tex_w, m.tex_h,
+               m.diffuse[2], m.alpha, m.emit[0], m.emit[1], m.emit[2], m.tex_w, m.tex_h, fnv1a(m.tex.data(), m.tex.size()),
                fnv1a(m.vertex.data(), m.vertex.size() * 4), fnv1a(m.normal.data(), m.normal.size() * 4),
                fnv1a(m.texcoord.data(), m.texcoord.size() * 4));
     }

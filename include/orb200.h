@@ -122,6 +122,10 @@ typedef struct OrbRenderConfig {
 #define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
                                         records fetched / triangle records tested land in OrbCounters.nodes_visited
                                         / tris_tested (same results, slower; bench.py's roofline uses it once) */
+#define ORB_RENDER_CHECKED 32 /* count what north_star wants reported with a frame: OrbCounters.hit_ties (primary hits with a
+                                 second triangle within 4 ulp of the closest distance: the reported id follows the tie rule)
+                                 and OrbCounters.ltc_near_decision (LTC / RATIO pixels within 1e-4 of a clip / back-face /
+                                 horizon decision, the "case flip" candidates).  One extra kernel; same frame. */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
                                  a tile owner renders redundantly for the denoise filter) */
 
@@ -149,6 +153,8 @@ typedef struct OrbCounters {
     uint64_t active_pixels_total;
     uint64_t bvh_build_us; /* device time of the last orb_scene_commit's hierarchy build (CUDA events) */
     uint64_t bvh_refit_us; /* device time of the last orb_scene_refit (CUDA events) */
+    uint64_t hit_ties;          /* last frame rendered with ORB_RENDER_CHECKED, else 0 */
+    uint64_t ltc_near_decision; /* last frame rendered with ORB_RENDER_CHECKED, else 0 */
 } OrbCounters;
 
 /* Stages of a frame, for orb_get_stage_times(): one entry per kernel family. */

@@ -72,7 +72,8 @@ class OrbCounters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays_primary", "rays_shadow", "rays_bounce", "kernel_launches",
                                           "nan_pixels", "bvh_nodes", "bvh_triangles", "bvh_height",
                                           "active_pixels", "nodes_visited", "tris_tested",
-                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total", "bvh_build_us", "bvh_refit_us")]
+                                          "rays_shadow_total", "rays_bounce_total", "active_pixels_total", "bvh_build_us", "bvh_refit_us",
+                                          "hit_ties", "ltc_near_decision")]
 
 
 STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "denoise", "combine", "ltc_gbuffer",
@@ -268,20 +269,20 @@ class Renderer:
 
     # ---- launch (Viewer::render, viewer.hpp:553-568) ----
     def _cfg(self, renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays=True, fused_shadow=False,
-             path_wavefront=False, count_traversal=False):
+             path_wavefront=False, count_traversal=False, checked=False):
         c = OrbRenderConfig()
         # ORB_RENDER_NO_COUNT, _FUSED_SHADOW, _PATH_WAVEFRONT, _COUNT_TRAVERSAL
         c.flags = ((0 if count_rays else 1) | (2 if fused_shadow else 0) | (4 if path_wavefront else 0)
-                   | (8 if count_traversal else 0))
+                   | (8 if count_traversal else 0) | (32 if checked else 0))
         c.renderer_type, c.accum_id, c.mode = int(renderer_type), int(accum_id), int(mode)
         c.shadow_spp, c.max_depth = int(shadow_spp), int(max_depth)
         c.y0, c.y1 = rows if rows else (0, 0)
         return c
 
     def render(self, renderer_type, accum_id=0, mode=LITERAL, shadow_spp=4, max_depth=1, rows=None, sync=True,
-               count_rays=True, fused_shadow=False, path_wavefront=False, count_traversal=False):
+               count_rays=True, fused_shadow=False, path_wavefront=False, count_traversal=False, checked=False):
         c = self._cfg(renderer_type, accum_id, mode, shadow_spp, max_depth, rows, count_rays, fused_shadow, path_wavefront,
-                      count_traversal)
+                      count_traversal, checked)
         self._ck((self.lib.orb_render if sync else self.lib.orb_render_async)(self._h, C.byref(c)))
 
     def set_frame_slots(self, n):

@@ -372,6 +372,31 @@ ORB_HD float3 integrate_tri_light(const LtcFrame& f, float3 lv1, float3 lv2, flo
     return (f.diffuse * lemit * diffuse_shading) + (f.amplitude * lemit * ggx_shading);
 }
 
+// Distance of a pixel's LTC evaluation to its nearest SIGN DECISION: wo_local.z < 0 (deviceCode.cu:27), the
+// back-face test (ltc_utils.cuh:58-60), the above-horizon bit of every vertex fed to the two clips
+// (polygon_utils.cuh:27-31).  A pixel below ~1e-4 takes another case of clipPolygon's 25-case table when a direction
+// differs in its last ulps between two implementations: north_star's "case flip" pixels, counted by a checked render
+// (ORB_RENDER_CHECKED -> OrbCounters.ltc_near_decision).
+ORB_HD float ltc_decision_margin(const LtcFrame& f, float wl_z, const TriLight* lights, int n_lights) {
+    float m = fabsf(wl_z);
+    if (!f.valid) return m;
+    for (int l = 0; l < n_lights; l++) {
+        const TriLight& L = lights[l];
+        float3 a = normalize(L.v1 - f.p), b = normalize(L.v2 - f.p), c = normalize(L.v3 - f.p);
+        const float bf = -dot(normalize(a + b + c), L.normal);
+        m = fminf(m, fabsf(bf));
+        if (bf < 0.f) continue;
+        a = apply(f.world_to_iso, a);
+        b = apply(f.world_to_iso, b);
+        c = apply(f.world_to_iso, c);
+        m = fminf(m, fminf(fabsf(a.z), fminf(fabsf(b.z), fabsf(c.z))));
+        if (!(a.z > 0.f || b.z > 0.f || c.z > 0.f)) continue;
+        const float3 ta = normalize(apply_minv(f, a)), tb = normalize(apply_minv(f, b)), tc = normalize(apply_minv(f, c));
+        m = fminf(m, fminf(fabsf(ta.z), fminf(fabsf(tb.z), fabsf(tc.z))));
+    }
+    return m;
+}
+
 // The light loop.  `lights` normally points to shared memory (all lanes read the same light:
 // a broadcast).
 ORB_HD float3 ltc_direct(const LtcFrame& f, const TriLight* lights, int n_lights) {

@@ -70,6 +70,7 @@ struct DevCounters {
     unsigned nan_pixels;
     unsigned long long rays_shadow, rays_bounce;
     unsigned long long nodes_visited, tris_tested;  // filled by the instrumented trace only
+    unsigned hit_ties, ltc_near_decision;           // filled by a checked render only (k_check_frame)
     // ---- everything above is cleared at the start of a frame; the totals below are not ----
     unsigned long long tot_shadow, tot_bounce, tot_active;
 };
@@ -248,8 +249,8 @@ k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4
 // gained nothing: the per-launch floor was not late long rays but the chunk granularity, fixed by
 // the guided chunk sizes below.  Also removed after measurement, round 1: leaf batching without
 // speculation, a compressed 8-wide BVH, bounded pops, 64-bit stack entries -- DESIGN.md section 3.)
-// Ray `pos` of the stream; its hit record goes to hits[slot] (o.w carries the slot, so a generator may ORDER the
-// stream for coherence -- k_shadow_gen_sorted -- without the consumers of the hits knowing).
+// Ray `pos` of the stream; its hit record goes to hits[slot] (o.w carries the slot, so a generator may order the
+// stream as it likes without the consumers of the hits knowing).
 __device__ __forceinline__ void stream_put_ray(float4* __restrict__ rays, unsigned pos, float3 o, float3 d, unsigned slot) {
     st_stream(rays + 2 * (size_t)pos, make_float4(o.x, o.y, o.z, __uint_as_float(slot)));
     st_stream(rays + 2 * (size_t)pos + 1, make_float4(d.x, d.y, d.z, 0.f));
@@ -413,72 +414,11 @@ k_shadow_gen(SceneView s, FrameView f, int frame_id, int spp, float4* __restrict
     }
 }
 
-// The same rays, ORDERED for the traversal: the queue is cut into chunks of SORT_CHUNK_PX active pixels (a strip of
-// neighbouring 8x4 tiles, in the order k_primary's warps appended them), and inside a chunk the rays are grouped by
-// the TriLight they aim at.  A warp of the stream kernel then holds rays with nearby origins AND nearby targets:
-// lanes walk the same nodes for most of the way down, so their node fetches share L1 wavefronts (the stream kernel is
-// bound by the L1 data pipe: every divergent lane access is its own wavefront, profiles/r2e) and fewer lanes idle
-// while others finish.  (Round 1 binned by light over the WHOLE frame and lost 16 %: origin coherence matters more;
-// here it is kept.)  One CTA per chunk: light index of every ray (the sample's fifth draw) -> shared histogram ->
-// exclusive scan -> scatter.  Hit records still land at hits[pixel * spp + sample]: the resolve kernels are unchanged.
-#define SORT_CHUNK_PX 1024
-#define SORT_MAX_LIGHTS 256
-__global__ void __launch_bounds__(256)
-k_shadow_gen_sorted(SceneView s, FrameView f, int frame_id, int spp, float4* __restrict__ rays, unsigned chunk_px) {
-    __shared__ unsigned hist[SORT_MAX_LIGHTS];
-    __shared__ unsigned warp_tot[8];
-    const unsigned n_px = f.cnt->queue_n;
-    const unsigned n_chunks = (n_px + chunk_px - 1) / chunk_px;
-    for (unsigned chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-        const unsigned px0 = chunk * chunk_px, px1 = min(px0 + chunk_px, n_px);
-        const unsigned r0 = px0 * (unsigned)spp, n_rays = (px1 - px0) * (unsigned)spp;
-        for (unsigned b = threadIdx.x; b < SORT_MAX_LIGHTS; b += blockDim.x) hist[b] = 0;
-        __syncthreads();
-        // pass 1: the light each ray selects (ratio.cuh:27-33: fifth draw of the sample, int(rand * (numTriLights - 1)))
-        for (unsigned j = threadIdx.x; j < n_rays; j += blockDim.x) {
-            const unsigned r = r0 + j, i = r / (unsigned)spp, k = r - i * (unsigned)spp;
-            const size_t ofs = f.queue[i];
-            Rng rng = rng_seed(frame_id, (uint32_t)(ofs % (size_t)f.W), (uint32_t)(ofs / (size_t)f.W), (uint32_t)f.W);
-            rng_skip(rng, 2 + 5 * (int)k + 4);
-            const float sel = rng_nextf(rng);
-            const int idx = imin(imax((int)(sel * (float)(s.n_lights - 1)), 0), s.n_lights - 1);
-            atomicAdd(&hist[idx & (SORT_MAX_LIGHTS - 1)], 1u);
-        }
-        __syncthreads();
-        // exclusive scan of the 256 bins by 256 threads
-        {
-            const unsigned v = hist[threadIdx.x];
-            unsigned x = v;
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
-                if ((threadIdx.x & 31) >= (unsigned)o) x += y;
-            }
-            if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = x;
-            __syncthreads();
-            unsigned base = 0;
-            for (unsigned w = 0; w < (threadIdx.x >> 5); w++) base += warp_tot[w];
-            hist[threadIdx.x] = base + x - v;
-        }
-        __syncthreads();
-        // pass 2: the ray itself, written at its group's next free position
-        for (unsigned j = threadIdx.x; j < n_rays; j += blockDim.x) {
-            const unsigned r = r0 + j, i = r / (unsigned)spp, k = r - i * (unsigned)spp;
-            const size_t ofs = f.queue[i];
-            const float4 pp = __ldg(f.position + ofs), nn = __ldg(f.normal + ofs);
-            Rng rng = rng_seed(frame_id, (uint32_t)(ofs % (size_t)f.W), (uint32_t)(ofs / (size_t)f.W), (uint32_t)f.W);
-            rng_skip(rng, 2 + 5 * (int)k);
-            Rng rsel = rng;
-            rng_skip(rsel, 4);
-            const float sel = rng_nextf(rsel);
-            const int idx = imin(imax((int)(sel * (float)(s.n_lights - 1)), 0), s.n_lights - 1);
-            const ShadowSample q = shadow_ray_setup(s, v3(pp), v3(nn), rng);
-            const unsigned pos = r0 + atomicAdd(&hist[idx & (SORT_MAX_LIGHTS - 1)], 1u);
-            stream_put_ray(rays, pos, q.origin, q.L, r);
-        }
-        __syncthreads();
-    }
-}
-
+// (Measured and removed, round 2: ordering the stream by (chunk of the queue, selected light) so that a warp holds rays
+// with nearby origins AND a common target -- trace stage 1.74 ms against 1.61 ms for every chunk size from 256 to
+// 16 k pixels, plus 0.09 ms of sorting (profiles/r2f_ab_sort.jsonl).  The four samples of a pixel sit in adjacent
+// lanes here and start from the SAME point; most node visits of a shadow ray lie next to its origin, so that
+// sharing is worth more than a common target.  Round 1's frame-wide binning by light lost 16 % for the same reason.)
 // one thread per active pixel: the n samples in order (sum, / n, grey mean) as rayGen does
 __global__ void __launch_bounds__(128)
 k_shadow_resolve(SceneView s, FrameView f, float3 cam_pos, int frame_id, int spp, int mode,
@@ -862,6 +802,80 @@ k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int de
 }
 
 __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
+
+// ---------------------------------------------------------------------------------------------
+// k_check_frame (ORB_RENDER_CHECKED): what north_star wants "counted and reported"
+//   hit_ties           pixels whose primary ray hits a SECOND triangle within 4 ulp of the closest hit's distance: the
+//                      id the frame reports there is decided by the tie rule (lowest primitive id), and another
+//                      ray/triangle test or traversal order (OptiX: not in the repository) may report the other one
+//   ltc_near_decision  active pixels whose LTC evaluation is within 1e-4 of a sign decision (ltc_decision_margin)
+// One thread per pixel, single-ray traversal restricted to the t window; runs after k_primary, outside any timing.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_check_frame(SceneView s, FrameView f, Camera cam, int frame_id, int with_ltc) {
+    const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
+    unsigned ties = 0, near = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t ofs = first + i;
+        const float4 h = f.hit[ofs];
+        const int prim = __float_as_int(h.x);
+        if (prim < 0) continue;
+        const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
+        float3 o, d;
+        primary_ray(cam, frame_id, px, py, f.W, f.H, o, d);
+        const float lo = h.w * (1.f - 4.f * 1.1920929e-7f), hi = h.w * (1.f + 4.f * 1.1920929e-7f);
+        // walk every subtree whose box the ray enters before `hi`; count triangles other than `prim` hit in [lo, hi]
+        int stk[ORB_LOCAL_STACK_MAX];
+        int sp = 0, cur = s.root_ref;
+        TravState t;
+        trav_begin(t, s, o, d);
+        bool tie = false;
+        while (!tie) {
+            if (cur >= 0) {
+                const BvhNode nd = s.nodes[cur];
+                float tn0, tn1;
+                const bool h0 = box_test(nd.a.x, nd.a.y, nd.a.z, nd.a.w, nd.b.x, nd.b.y, t.noi, t.inv, hi, tn0);
+                const bool h1 = box_test(nd.b.z, nd.b.w, nd.c.x, nd.c.y, nd.c.z, nd.c.w, t.noi, t.inv, hi, tn1);
+                if (h0 && h1) {
+                    if (sp < ORB_LOCAL_STACK_MAX) stk[sp++] = nd.c1;
+                    cur = nd.c0;
+                    continue;
+                }
+                if (h0) { cur = nd.c0; continue; }
+                if (h1) { cur = nd.c1; continue; }
+            } else if (cur != ORB_TRAVERSAL_DONE) {
+                const int lr = ~cur, k0 = lr >> 3, cnt = (lr & 7) + 1;
+                for (int k = 0; k < cnt; k++) {
+                    float4 t0, t1, t2;
+                    tri_fetch(s, k0 + k, t0, t1, t2);
+                    float tt, u, v;
+                    if (__float_as_int(t0.w) != prim && tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, tt, u, v) && tt >= lo && tt <= hi)
+                        tie = true;
+                }
+            }
+            if (sp == 0) break;
+            cur = stk[--sp];
+        }
+        ties += tie ? 1u : 0u;
+        if (with_ltc && (f.flags[ofs] & FLAG_HIT) && !(f.flags[ofs] & FLAG_LIGHT)) {
+            const float4 pp = f.position[ofs], nn = f.normal[ofs], aa = f.alpha[ofs];
+            const float3 wo = normalize(cam.pos - v3(pp));
+            const Mat3 to_local = onb_rows(v3(nn));
+            LtcFrame fr;
+            ltc_setup(fr, s.lut, v3(pp), v3(0.f), aa.x, to_local, wo);
+            const float wl_z = normalize(apply(to_local, wo)).z;
+            near += ltc_decision_margin(fr, wl_z, s.lights, s.n_lights) <= 1e-4f ? 1u : 0u;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ties += __shfl_xor_sync(0xffffffffu, ties, o);
+        near += __shfl_xor_sync(0xffffffffu, near, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (ties) atomicAdd(&f.cnt->hit_ties, ties);
+        if (near) atomicAdd(&f.cnt->ltc_near_decision, near);
+    }
+}
 
 // ---------------------------------------------------------------------------------------------
 // k_accumulate: deviceCode.cu:158-161,172-174
@@ -1263,8 +1277,6 @@ struct OrbContext : FrameSlot {
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
-    int sort_chunk_px = SORT_CHUNK_PX;  // active pixels per chunk of the ordering (ORB_SORT_CHUNK)
-    int sort_rays = 1;      // RATIO: order the shadow-ray stream by (queue chunk, light) for the traversal (ORB_SORT_RAYS)
     int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
     int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
@@ -1581,8 +1593,6 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
-    if (const char* e = getenv("ORB_SORT_RAYS")) c->sort_rays = atoi(e);
-    if (const char* e = getenv("ORB_SORT_CHUNK")) c->sort_chunk_px = std::max(32, atoi(e));
     if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
@@ -2049,6 +2059,13 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         c->counters.kernel_launches++;
         if (count_rays) c->counters.rays_primary += (uint64_t)(y1 - y0) * c->W;
     }
+    if (cfg->flags & ORB_RENDER_CHECKED) {  // ties of the primary hits, LTC pixels next to a clip decision -> OrbCounters
+        const size_t npx = (size_t)(y1 - y0) * c->W;
+        const int with_ltc = (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && c->lut_w > 0;
+        k_check_frame<<<(unsigned)std::min<size_t>((npx + TRACE_BLOCK - 1) / TRACE_BLOCK, (size_t)c->n_sm * 16), TRACE_BLOCK, 0, st>>>(
+            c->view, f, c->cam, frame_id, with_ltc);
+        c->counters.kernel_launches++;
+    }
     const float4* colour_src = c->colour;
     auto launch_ltc = [&](cudaStream_t ls) {
         StageTimer tm(c, ORB_STAGE_LTC, 1, ls);
@@ -2073,10 +2090,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
                 {
                     StageTimer tm(c, ORB_STAGE_SHADOW, 1);
                     const int gg = (int)std::min<size_t>((npx * spp + 255) / 256, (size_t)c->n_sm * 8);
-                    if (c->sort_rays && n_lights > 1)
-                        k_shadow_gen_sorted<<<c->n_sm * 4, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays, (unsigned)c->sort_chunk_px);
-                    else
-                        k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
+                    k_shadow_gen<<<gg, 256, 0, st>>>(c->view, f, frame_id, spp, c->stream_rays);
                     c->counters.kernel_launches++;
                 }
                 rc = launch_trace_stream(c, &c->cnt->queue_n, (unsigned)spp, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, true,
@@ -2299,7 +2313,6 @@ static int preload_frame_kernels() {
     CK(cudaFuncGetAttributes(&a, k_ltc<true>));
     CK(cudaFuncGetAttributes(&a, k_ltc<false>));
     CK(cudaFuncGetAttributes(&a, k_shadow_gen));
-    CK(cudaFuncGetAttributes(&a, k_shadow_gen_sorted));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<2>));
     CK(cudaFuncGetAttributes(&a, k_shadow_resolve_lanes<4>));
@@ -2656,6 +2669,8 @@ int orb_get_counters(OrbContext* c, OrbCounters* out) {
     out->active_pixels = d.queue_n;
     out->nodes_visited = d.nodes_visited;
     out->tris_tested = d.tris_tested;
+    out->hit_ties = d.hit_ties;
+    out->ltc_near_decision = d.ltc_near_decision;
     out->bvh_height = (uint64_t)c->bvh.height;
     out->rays_shadow_total = d.tot_shadow;
     out->rays_bounce_total = d.tot_bounce;

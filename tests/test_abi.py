@@ -28,7 +28,7 @@ def test_header_symbols_exported():
 def test_struct_layouts_match_header():
     assert ctypes.sizeof(api.OrbRenderConfig) == 32
     assert ctypes.sizeof(api.OrbDenoiseConfig) == 16
-    assert ctypes.sizeof(api.OrbCounters) == 128
+    assert ctypes.sizeof(api.OrbCounters) == 144
     assert ctypes.sizeof(api.OrbBvhOptions) == 16
     assert api.OrbMeshDesc.index.offset == 32 and api.OrbMeshDesc.diffuse.offset == 44
 

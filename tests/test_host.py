@@ -129,6 +129,92 @@ def test_host_obj_features(host, tmp_path):
     assert green["vertex_hash"] == fnv1a(fan)
 
 
+def _png(path, arr, ctype, depth=8, palette=None, trns=None):
+    """Minimal PNG writer (zlib + CRC), filter type chosen per row to exercise all five."""
+    import struct, zlib
+    h, w = arr.shape[:2]
+    raw = bytearray()
+    a = np.ascontiguousarray(arr).reshape(h, -1).astype(np.uint8)
+    bpp = max(1, a.shape[1] // w)
+    prev = np.zeros(a.shape[1], np.int32)
+    for y in range(h):
+        cur = a[y].astype(np.int32)
+        ft = y % 5
+        left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])
+        ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])
+        if ft == 0:
+            enc = cur
+        elif ft == 1:
+            enc = cur - left
+        elif ft == 2:
+            enc = cur - prev
+        elif ft == 3:
+            enc = cur - ((left + prev) >> 1)
+        else:
+            p = left + prev - ul
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - ul)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
+            enc = cur - pred
+        raw += bytes([ft]) + bytes((enc & 255).astype(np.uint8).tolist())
+        prev = cur
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d) & 0xffffffff)
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 0))
+    if palette is not None:
+        out += chunk(b"PLTE", bytes(np.asarray(palette, np.uint8).ravel().tolist()))
+    if trns is not None:
+        out += chunk(b"tRNS", bytes(trns))
+    comp = zlib.compress(bytes(raw))
+    out += chunk(b"IDAT", comp[:len(comp) // 2]) + chunk(b"IDAT", comp[len(comp) // 2:]) + chunk(b"IEND", b"")
+    open(path, "wb").write(out)
+
+
+def test_host_texture_formats(host, tmp_path):
+    """map_Kd through PNG (RGB, RGBA, grey, palette + tRNS; all five row filters, split IDAT) and TGA (raw and RLE):
+    the texels the host hands to orb_scene_add_mesh are the file's, as RGBA8 with the BOTTOM row first -- what the
+    reference gets from stbi_load(..., STBI_rgb_alpha) plus its y mirror (src/Model.cpp:81-128)."""
+    rng = np.random.default_rng(9)
+    w, h = 7, 6
+    rgb = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    rgba = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    grey = rng.integers(0, 256, (h, w, 1), dtype=np.uint8)
+    pal = rng.integers(0, 256, (5, 3), dtype=np.uint8)
+    idx = rng.integers(0, 5, (h, w, 1), dtype=np.uint8)
+    cases = {}
+    _png(tmp_path / "rgb.png", rgb, 2)
+    cases["rgb.png"] = np.concatenate([rgb, np.full((h, w, 1), 255, np.uint8)], -1)
+    _png(tmp_path / "rgba.png", rgba, 6)
+    cases["rgba.png"] = rgba
+    _png(tmp_path / "grey.png", grey, 0)
+    cases["grey.png"] = np.concatenate([grey, grey, grey, np.full((h, w, 1), 255, np.uint8)], -1)
+    _png(tmp_path / "pal.png", idx, 3, palette=pal, trns=[10, 20, 30])
+    a = np.array([10, 20, 30, 255, 255], np.uint8)[idx[..., 0]][..., None]
+    cases["pal.png"] = np.concatenate([pal[idx[..., 0]], a], -1)
+    bgr = rgb[::-1, :, ::-1]  # TGA: bottom-up rows, BGR
+    (tmp_path / "raw.tga").write_bytes(bytes([0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, w, 0, h, 0, 24, 0]) + bgr.tobytes())
+    cases["raw.tga"] = cases["rgb.png"]
+    rle = bytearray()
+    for row in bgr.reshape(h, w, 3):
+        rle += bytes([128 | 1]) + row[0].tobytes()          # a run of 2 x the first pixel ...
+        rle += bytes([w - 3]) + row[2:].tobytes()           # ... then w - 2 literal pixels
+    (tmp_path / "rle.tga").write_bytes(bytes([0, 0, 10, 0, 0, 0, 0, 0, 0, 0, 0, 0, w, 0, h, 0, 24, 0]) + bytes(rle))
+    t = rgb.copy()
+    t[:, 1] = t[:, 0]
+    cases["rle.tga"] = np.concatenate([t, np.full((h, w, 1), 255, np.uint8)], -1)
+    for name, want in cases.items():
+        (tmp_path / "a.mtl").write_text("newmtl m\nKd 1 0 0\nNs 0.5\nmap_Kd %s\n" % name)
+        (tmp_path / "a.obj").write_text("mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nusemtl m\nf 1/1/1 2/1/1 3/1/1\n")
+        (tmp_path / "s.json").write_text(json.dumps({
+            "spp": 1, "width": 8, "height": 8, "renderers": [9],
+            "cameras": [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 0.66}],
+            "surface_geometry": "a.obj", "area_lights": "a.obj"}))
+        rc, d, err = dump(host, str(tmp_path / "s.json"))
+        assert rc == 0, err
+        m = d["meshes"][0]
+        assert m["tex"] == [w, h], (name, err)
+        assert m["tex_hash"] == fnv1a(want[::-1]), name      # bottom row first
+
+
 def test_host_exr_writer(host, tmp_path):
     """--exr writes what save.py makes of a .btc dump (flipud, RGB, float32): read back with OpenCV's EXR codec
     (imageio, which the reference uses, is not installed)."""
