@@ -223,7 +223,7 @@ def run_ours(args):
     if args.lut != 8:
         sc["lut"] = scenes.upsample_lut(sc["lut"], args.lut)
     r = api.Renderer(sc, device=local, quantise_lut=1)  # table fetched with the texture unit's weights, as the reference's tex2D
-    SLOTS = max(1, min(2, int(os.environ.get("ORB_BENCH_SLOTS", "2"))))  # frames in flight per GPU (orb_set_frame_slots)
+    SLOTS = max(1, min(4, int(os.environ.get("ORB_BENCH_SLOTS", "2"))))  # frames in flight per GPU (orb_set_frame_slots)
     r.set_frame_slots(SLOTS)
     stream = torch.cuda.Stream()  # carries the timing events; ordered behind the frame slots' own streams by T.join()
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
@@ -285,8 +285,10 @@ def run_ours(args):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         ev0.record(stream)          # every stream is idle: the clock starts here
+        t_host = time.perf_counter()
         for i in range(args.steps):
             step(base_id + i)
+        host_ms = (time.perf_counter() - t_host) * 1e3 / args.steps  # host time to ENQUEUE a frame (no device wait in it)
         T.join(stream)              # behind both frame slots and the last assembly
         ev1.record(stream)
         barrier()
@@ -559,7 +561,7 @@ def run_ours(args):
                                    "rank 0's copy of the assembled frame" + ("" if SYNC_ASSEMBLE or SYNC_DOWNLOAD else
                                    " on a copy stream, behind the all-gather and beside the next frame's kernels; the "
                                    "last copy is waited for inside the timed region"))},
-                "gpu_launches": int(launches), "frames_in_flight": SLOTS, "roofline": roofline, "passes": passes,
+                "gpu_launches": int(launches), "frames_in_flight": SLOTS, "host_enqueue_ms_per_step": host_ms, "roofline": roofline, "passes": passes,
                 "passes_note": "per-stage CUDA-event times of %d extra frames run ONE AT A TIME after the timed region "
                                "(with %d frames in flight the stages of consecutive frames overlap, so their sum "
                                "exceeds ms_per_step)" % (P_FRAMES, SLOTS),

@@ -122,8 +122,8 @@ typedef struct OrbRenderConfig {
 #define ORB_RENDER_COUNT_TRAVERSAL 8 /* RATIO / PATH: run the instrumented twin of the shadow-ray / path kernel; node
                                         records fetched / triangle records tested land in OrbCounters.nodes_visited
                                         / tris_tested (same results, slower; bench.py's roofline uses it once) */
-#define ORB_RENDER_CHECKED 32 /* count what north_star wants reported with a frame: OrbCounters.hit_ties (primary hits with a
-                                 second triangle within 4 ulp of the closest distance: the reported id follows the tie rule)
+#define ORB_RENDER_CHECKED 32 /* count what north_star wants reported with a frame: OrbCounters.hit_ties (primary hits within
+                                 1e-5, barycentric, of an edge of their triangle: another test may report the neighbour)
                                  and OrbCounters.ltc_near_decision (LTC / RATIO pixels within 1e-4 of a clip / back-face /
                                  horizon decision, the "case flip" candidates).  One extra kernel; same frame. */
 #define ORB_RENDER_NO_COUNT 1 /* rays of this launch are not added to the *_total counters (halo rows
@@ -224,8 +224,8 @@ int orb_resize(OrbContext* ctx, int32_t width, int32_t height);
  * Blocking, like owlLaunch2D.  orb_render_async() enqueues on orb_stream() and returns. */
 int orb_render(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
-/* Frames in flight: 1 (default) or 2.  With 2, consecutive orb_render_async calls alternate between two sets of frame
- * buffers and two streams, so the kernels of frame i+1 run beside the tail of frame i's persistent traversal kernels
+/* Frames in flight: 1 (default) to 4.  With n > 1, consecutive orb_render_async calls cycle through n sets of frame
+ * buffers and n streams, so the kernels of frame i+1 run beside the tail of frame i's persistent traversal kernels
  * (the reference renders strictly one frame at a time: owlLaunch2D blocks, viewer.hpp:565).  ORB_BUF_ACCUM and
  * ORB_BUF_RGBA8 are shared and accumulate in call order; every other buffer exists once per slot.  All calls that
  * follow an orb_render_async -- denoise, combine, downloads, orb_buffer_device_ptr, orb_stream -- refer to THAT

@@ -24,7 +24,7 @@
 namespace orb {
 
 #define ORB_HALO_MAX_PEERS 8
-#define ORB_HALO_MAX_SLOTS 2
+#define ORB_HALO_MAX_SLOTS 4
 #define ORB_HALO_MAX_SENDS 4  // row ranges one pack launch pushes (a band narrower than the filter's reach has > 2)
 
 // control block layout (uint32 words): [0] error flag, then ready[slot][rank], then consumed[slot][rank]
@@ -36,8 +36,8 @@ namespace orb {
 
 struct HaloPeer {
     int rank = -1;
-    float4* guide[ORB_HALO_MAX_SLOTS] = {nullptr, nullptr};  // the peer's ORB_BUF_DN_GUIDE, mapped here
-    float2* val[ORB_HALO_MAX_SLOTS] = {nullptr, nullptr};    // the peer's ORB_BUF_DN_VAL
+    float4* guide[ORB_HALO_MAX_SLOTS] = {nullptr};  // the peer's ORB_BUF_DN_GUIDE, mapped here
+    float2* val[ORB_HALO_MAX_SLOTS] = {nullptr};    // the peer's ORB_BUF_DN_VAL
     uint32_t* flags = nullptr;                                // the peer's control block
 };
 

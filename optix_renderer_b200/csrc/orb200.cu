@@ -805,57 +805,22 @@ __global__ void k_reset_slot(DevCounters* c, int slot) { c->path_n[slot] = 0; }
 
 // ---------------------------------------------------------------------------------------------
 // k_check_frame (ORB_RENDER_CHECKED): what north_star wants "counted and reported"
-//   hit_ties           pixels whose primary ray hits a SECOND triangle within 4 ulp of the closest hit's distance: the
-//                      id the frame reports there is decided by the tie rule (lowest primitive id), and another
-//                      ray/triangle test or traversal order (OptiX: not in the repository) may report the other one
+//   hit_ties           pixels whose primary hit lies within 1e-5 (barycentric) of an edge of its triangle: the ray
+//                      passes through the seam between two triangles within the rounding of the ray/triangle test, and
+//                      another test or traversal order (OptiX: not in the repository) may report the neighbour's id
 //   ltc_near_decision  active pixels whose LTC evaluation is within 1e-4 of a sign decision (ltc_decision_margin)
-// One thread per pixel, single-ray traversal restricted to the t window; runs after k_primary, outside any timing.
+// One thread per pixel over the frame's hit records and G-buffer; runs after k_primary, outside any timing.
 // ---------------------------------------------------------------------------------------------
+#define ORB_EDGE_TIE_EPS 1e-5f
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_check_frame(SceneView s, FrameView f, Camera cam, int frame_id, int with_ltc) {
+k_check_frame(SceneView s, FrameView f, Camera cam, int with_ltc) {
     const size_t first = (size_t)f.y0 * f.W, n = (size_t)(f.y1 - f.y0) * f.W;
     unsigned ties = 0, near = 0;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const size_t ofs = first + i;
         const float4 h = f.hit[ofs];
-        const int prim = __float_as_int(h.x);
-        if (prim < 0) continue;
-        const int px = (int)(ofs % (size_t)f.W), py = (int)(ofs / (size_t)f.W);
-        float3 o, d;
-        primary_ray(cam, frame_id, px, py, f.W, f.H, o, d);
-        const float lo = h.w * (1.f - 4.f * 1.1920929e-7f), hi = h.w * (1.f + 4.f * 1.1920929e-7f);
-        // walk every subtree whose box the ray enters before `hi`; count triangles other than `prim` hit in [lo, hi]
-        int stk[ORB_LOCAL_STACK_MAX];
-        int sp = 0, cur = s.root_ref;
-        TravState t;
-        trav_begin(t, s, o, d);
-        bool tie = false;
-        while (!tie) {
-            if (cur >= 0) {
-                const BvhNode nd = s.nodes[cur];
-                float tn0, tn1;
-                const bool h0 = box_test(nd.a.x, nd.a.y, nd.a.z, nd.a.w, nd.b.x, nd.b.y, t.noi, t.inv, hi, tn0);
-                const bool h1 = box_test(nd.b.z, nd.b.w, nd.c.x, nd.c.y, nd.c.z, nd.c.w, t.noi, t.inv, hi, tn1);
-                if (h0 && h1) {
-                    if (sp < ORB_LOCAL_STACK_MAX) stk[sp++] = nd.c1;
-                    cur = nd.c0;
-                    continue;
-                }
-                if (h0) { cur = nd.c0; continue; }
-                if (h1) { cur = nd.c1; continue; }
-            } else if (cur != ORB_TRAVERSAL_DONE) {
-                const int lr = ~cur, k0 = lr >> 3, cnt = (lr & 7) + 1;
-                for (int k = 0; k < cnt; k++) {
-                    float4 t0, t1, t2;
-                    tri_fetch(s, k0 + k, t0, t1, t2);
-                    float tt, u, v;
-                    if (__float_as_int(t0.w) != prim && tri_test(t0, t1, t2, o, d, 0.f, ORB_TMAX, tt, u, v) && tt >= lo && tt <= hi)
-                        tie = true;
-                }
-            }
-            if (sp == 0) break;
-            cur = stk[--sp];
-        }
+        if (__float_as_int(h.x) < 0) continue;
+        const bool tie = fminf(fminf(h.y, h.z), 1.f - h.y - h.z) <= ORB_EDGE_TIE_EPS;
         ties += tie ? 1u : 0u;
         if (with_ltc && (f.flags[ofs] & FLAG_HIT) && !(f.flags[ofs] & FLAG_LIGHT)) {
             const float4 pp = f.position[ofs], nn = f.normal[ofs], aa = f.alpha[ofs];
@@ -1193,8 +1158,8 @@ struct HostMesh {
     std::vector<uint8_t> tex;
 };
 
-// Everything ONE FRAME IN FLIGHT owns.  A context has 1 (default) or 2 of these (orb_set_frame_slots): with two,
-// orb_render_async alternates between them, each on its own stream, so the kernels of frame i+1 fill the SMs that
+// Everything ONE FRAME IN FLIGHT owns.  A context has 1 (default) to 4 of these (orb_set_frame_slots): with several,
+// orb_render_async cycles through them, each on its own stream, so the kernels of frame i+1 fill the SMs that
 // the persistent traversal kernel of frame i leaves idle while its last rays finish (the fixed tail of every stage,
 // profiles/r1k_stage_floors.json: what limits a narrow band of a tile partition) and the issue slots it leaves
 // empty while it waits on node fetches.  Frames are independent except for the running sum: `accum` and RGBA8 are
@@ -1225,7 +1190,7 @@ struct FrameSlot {
     bool rendered = false;           // a frame has been enqueued on this slot since the last resize
     uint32_t halo_epoch = 0;         // frames whose packed denoise rows this slot has pushed to its peers (halo.cuh)
 };
-#define ORB_MAX_SLOTS 2
+#define ORB_MAX_SLOTS 4
 #define ORB_MAX_PENDING_DL 8
 
 // The context IS its active slot (the FrameSlot base: c->stream, c->buf, ... are the active frame's); the other
@@ -1627,10 +1592,10 @@ void orb_destroy(OrbContext* c) {
     delete c;
 }
 
-// Frames in flight (1 or 2).  With 2, consecutive orb_render_async calls alternate between two sets of frame buffers
-// and two streams; `accum` / RGBA8 stay shared and accumulate in call order.  Re-allocates the frame buffers.
+// Frames in flight (1 to 4).  With n > 1, consecutive orb_render_async calls cycle through n sets of frame buffers
+// and n streams; `accum` / RGBA8 stay shared and accumulate in call order.  Re-allocates the frame buffers.
 int orb_set_frame_slots(OrbContext* c, int32_t n) {
-    NEED(c && n >= 1 && n <= ORB_MAX_SLOTS, "orb_set_frame_slots: 1 or 2 slots");
+    NEED(c && n >= 1 && n <= ORB_MAX_SLOTS, "orb_set_frame_slots: 1 to 4 slots");
     CK(cudaSetDevice(c->device));
     int rc = orb_sync(c);
     if (rc) return rc;
@@ -2063,7 +2028,7 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         const size_t npx = (size_t)(y1 - y0) * c->W;
         const int with_ltc = (renderer == ORB_LTC_BASELINE || renderer == ORB_RATIO) && c->lut_w > 0;
         k_check_frame<<<(unsigned)std::min<size_t>((npx + TRACE_BLOCK - 1) / TRACE_BLOCK, (size_t)c->n_sm * 16), TRACE_BLOCK, 0, st>>>(
-            c->view, f, c->cam, frame_id, with_ltc);
+            c->view, f, c->cam, with_ltc);
         c->counters.kernel_launches++;
     }
     const float4* colour_src = c->colour;
