@@ -359,13 +359,13 @@ def run_ours(args):
                 elif HOST_GATHER:
                     T.read_back_bands_async(shared, i & 1, out_names)
                 elif rank == 0 and not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:
-                    # the assembled frame lives in T.out: read back behind the gather, beside the next frame
+                    # the gathered frame: read back behind the gather, beside the next frame
                     T.read_back_async({out_names[0]: t_f4[i & 1], "rgba8": t_u32[i & 1]})
                 elif rank == 0:
                     T.join(stream)
                     stream.synchronize()
-                    t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.out[out_names[0]])
-                    t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.out["rgba8"])
+                    t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.assembled(out_names[0]))
+                    t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.assembled("rgba8"))
                     torch.cuda.current_stream().synchronize()
             if HOST_GATHER:
                 T.join(stream)
@@ -398,7 +398,7 @@ def run_ours(args):
             # against the same frame rendered whole by this rank alone -- bit for bit, outside every timed region
             T.join(stream)
             stream.synchronize()
-            got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.out["ratio_final"]).clone()
+            got = (tiles.device_tensor(r, "ratio_final") if SYNC_ASSEMBLE else T.assembled("ratio_final")).clone()
             if HOST_GATHER:  # the frame as the host received it: N bands, each copied by its own rank
                 got = torch.from_numpy(np.array(shared[out_names[0]][(e_steps - 1) & 1])).to("cuda")
             elif not SYNC_ASSEMBLE and not SYNC_DOWNLOAD:  # the frame as the host received it through the pipelined read-back

@@ -196,16 +196,21 @@ k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int 
 
 template <bool FROM_QUEUE>
 __global__ void __launch_bounds__(LTC_BLOCK)
-k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4* __restrict__ out2) {
+k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4* __restrict__ out2, int pair_quads) {
     __shared__ TriLight sh_lights[LTC_SMEM_LIGHTS];
     __shared__ float4 sh_lut[LTC_SMEM_LUT_TEXELS];
     const bool lights_sm = s.n_lights <= LTC_SMEM_LIGHTS;
     const int lut_texels = 3 * s.lut.w * s.lut.h;
     const bool lut_sm = lut_texels <= LTC_SMEM_LUT_TEXELS;
+    __shared__ unsigned char sh_quad[LTC_SMEM_LIGHTS];  // light l and l + 1 are the halves of one quad (ltc.cuh)
     if (lights_sm) {
         const float* src = reinterpret_cast<const float*>(s.lights);
         float* dst = reinterpret_cast<float*>(sh_lights);
         for (int i = threadIdx.x; i < s.n_lights * 19; i += LTC_BLOCK) dst[i] = src[i];
+        __syncthreads();
+        // pairs are looked for at even positions only, so a pair never overlaps the next one
+        for (int l = threadIdx.x; l < s.n_lights; l += LTC_BLOCK)
+            sh_quad[l] = (pair_quads && !(l & 1) && l + 1 < s.n_lights && lights_form_quad(sh_lights[l], sh_lights[l + 1])) ? 1 : 0;
     }
     if (lut_sm)
         for (int i = threadIdx.x; i < lut_texels; i += LTC_BLOCK) sh_lut[i] = s.lut.data[i];
@@ -223,7 +228,7 @@ k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4
             const float4 pp = ld_stream(f.position + ofs);
             const float4 dd = ld_stream(f.albedo + ofs);
             const float4 aa = ld_stream(f.alpha + ofs);
-            c = ltc_pixel(lut, lights, s.n_lights, cam_pos, v3(pp), v3(nn), v3(dd), aa.x);
+            c = ltc_pixel(lut, lights, s.n_lights, cam_pos, v3(pp), v3(nn), v3(dd), aa.x, lights_sm ? sh_quad : nullptr);
         }
         const float4 o = make_float4(c.x, c.y, c.z, 1.f);
         st_stream(out + ofs, o);
@@ -1242,6 +1247,7 @@ struct OrbContext : FrameSlot {
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
+    int ltc_pair_quads = 1;  // k_ltc: two TriLights that are the halves of a quad share their unclipped case (ORB_LTC_PAIR_QUADS)
     int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
     int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
@@ -1558,6 +1564,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
+    if (const char* e = getenv("ORB_LTC_PAIR_QUADS")) c->ltc_pair_quads = atoi(e);
     if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
@@ -2037,10 +2044,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
         if (renderer == ORB_RATIO) {
             // light pixels already hold emit in `ltc` (k_primary), so `ltc` IS the frame colour
-            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.ltc, nullptr, c->ltc_pair_quads);
             colour_src = f.ltc;
         } else {
-            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.colour, nullptr);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.colour, nullptr, c->ltc_pair_quads);
         }
         c->counters.kernel_launches++;
     };
@@ -2177,7 +2184,7 @@ int orb_ltc_gbuffer_pass(OrbContext* c, int32_t y0, int32_t y1) {
     const int g = persistent_grid(c, k_ltc<false>, LTC_BLOCK, 0);
     {
         StageTimer tm(c, ORB_STAGE_LTC_GBUFFER, 1);
-        k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
+        k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr, c->ltc_pair_quads);
     }
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
