@@ -53,8 +53,10 @@ def main():
             if name in best and best[name][0] >= ms:
                 continue
             wav = raw(d, "l1tex__data_pipe_lsu_wavefronts.sum")
-            if wav is None and "l1tex__data_pipe_lsu_wavefronts.avg" in ix:
-                wav = raw(d, "l1tex__data_pipe_lsu_wavefronts.avg") * (raw(d, "launch__sm_count") or 148)
+            if wav is None:  # the raw page carries it as a per-SM average under a section prefix
+                key = next((h for h in hdr if h.endswith("l1tex__data_pipe_lsu_wavefronts.avg")), None)
+                n_l1 = (raw(d, "l1tex__cycles_elapsed.sum") or 0) / (raw(d, "l1tex__cycles_elapsed.avg") or 1)
+                wav = raw(d, key) * round(n_l1) if key and n_l1 else None
             rd = to_bytes(raw(d, "dram__bytes_read.sum"), units[ix["dram__bytes_read.sum"]])
             wr = to_bytes(raw(d, "dram__bytes_write.sum"), units[ix["dram__bytes_write.sum"]])
             best[name] = (ms, {"dram_bytes_per_launch": rd + wr, "ms_under_ncu": ms, "warp_inst": raw(d, "smsp__inst_executed.sum"),
