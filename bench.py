@@ -311,6 +311,21 @@ def run_ours(args):
         st = {k: (t * args.steps / P_FRAMES, n * args.steps / P_FRAMES) for k, (t, n) in st.items()}  # per `steps` frames, as below
         coll_ms = {k: v * args.steps / P_FRAMES for k, v in coll_ms.items()}
         base_id += P_FRAMES
+        if os.environ.get("ORB_BENCH_TIMELINE"):
+            # a timeline of a few frames AS THEY RUN in the timed loop (frames in flight overlap): every stage's
+            # CUDA-event start / end on rank 0, relative to the first -- where the overlap happens and where it does not
+            r.set_profiling(True)
+            r.stage_times()
+            for i in range(6):
+                step(base_id + i)
+            spans = r.stage_spans()
+            r.stage_times()
+            r.set_profiling(False)
+            base_id += 6
+            if rank == 0:
+                with open(os.environ["ORB_BENCH_TIMELINE"], "w") as fh:
+                    json.dump({"n_gpus": world, "slots": SLOTS, "workload": args.workload, "bands": [list(b) for b in T.bands],
+                               "spans": [[n, k, round(a, 4), round(b, 4)] for n, k, a, b in spans]}, fh)
         ms = reduce(ms, dist.ReduceOp.MAX) if world > 1 else ms
         rank_ms = None
         if world > 1:  # every rank's own kernel time per frame (stage timers): how even the bands are
@@ -343,10 +358,14 @@ def run_ours(args):
                     print("bench.py: %s; e2e falls back to rank 0's read-back of the assembled frame" % e, file=sys.stderr)
                 HOST_GATHER = False
 
+        e2e_host = [None]
+
         def e2e_loop(pipelined, id0, n):
             barrier()
             t0 = time.perf_counter()
             for i in range(n):
+                if i == n - 1:
+                    e2e_host[0] = (time.perf_counter() - t0) * 1e3 / max(n - 1, 1)  # host time per frame of the enqueue loop
                 r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
                 step(id0 + i)
                 if rank == 0 and world == 1 and pipelined:
@@ -548,7 +567,7 @@ def run_ours(args):
                 "data": "synthetic", "config": workload_config(args, world), "rays_per_frame": rays / args.steps,
                 "e2e": {"value": e_value, "unit": "Mrays/s", "ms_per_step": e_ms / e_steps,
                         "frames_per_s": e_steps / (e_ms * 1e-3), "h2d_bytes_per_step": 48 + 32,
-                        "d2h_bytes_per_step": W * H * 20, "steps": e_steps,
+                        "d2h_bytes_per_step": W * H * 20, "steps": e_steps, "host_enqueue_ms_per_step": e2e_host[0],
                         "what": "orb_set_camera + orb_render_async(+denoise+combine) + %s of the "
                                 "float4 result and the RGBA8 frame into pinned host memory, every frame"
                                 % ("orb_buffer_download_rows_async (read-back of frame i overlaps the kernels of frame i+1; "

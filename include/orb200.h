@@ -178,6 +178,11 @@ typedef struct OrbStageTimes {
     uint64_t launches[ORB_STAGE_COUNT]; /* kernels launched in the stage                  */
 } OrbStageTimes;
 
+typedef struct OrbStageSpan {
+    int32_t stage, slot; /* OrbStage, frame slot */
+    float t0_ms, t1_ms;  /* CUDA-event times relative to the first recorded span */
+} OrbStageSpan;
+
 typedef struct OrbContext OrbContext;
 
 /* ---- context ---- replaces owlContextCreate/ModuleCreate, viewer.hpp:177-178 */
@@ -194,6 +199,8 @@ int orb_sync(OrbContext* ctx);
  * resets them.  New in this library (the reference has no timing code at all). */
 int orb_set_profiling(OrbContext* ctx, int enable);
 int orb_get_stage_times(OrbContext* ctx, OrbStageTimes* out);
+/* the spans recorded since the last orb_get_stage_times, as a timeline (several frame slots overlap); synchronises */
+int orb_get_stage_spans(OrbContext* ctx, OrbStageSpan* out, int32_t max, int32_t* n);
 
 /* ---- scene ---- replaces owlGeom*, owlTriangles*, owlGroupBuildAccel, viewer.hpp:375-517 */
 int orb_scene_clear(OrbContext* ctx);

@@ -80,6 +80,10 @@ STAGES = ["primary", "ltc", "shadow", "path", "accumulate", "denoise_pack", "den
           "trace", "halo"]
 
 
+class OrbStageSpan(C.Structure):
+    _fields_ = [("stage", C.c_int32), ("slot", C.c_int32), ("t0_ms", C.c_float), ("t1_ms", C.c_float)]
+
+
 class OrbStageTimes(C.Structure):
     _fields_ = [("ms", C.c_double * 11), ("launches", C.c_uint64 * 11)]
 
@@ -106,6 +110,7 @@ def load_library():
     L.orb_sync.argtypes = [vp]
     L.orb_set_profiling.argtypes = [vp, C.c_int]
     L.orb_get_stage_times.argtypes = [vp, C.POINTER(OrbStageTimes)]
+    L.orb_get_stage_spans.argtypes = [vp, C.POINTER(OrbStageSpan), C.c_int32, C.POINTER(C.c_int32)]
     L.orb_scene_clear.argtypes = [vp]
     L.orb_scene_add_mesh.argtypes = [vp, C.POINTER(OrbMeshDesc)]
     L.orb_scene_set_lights.argtypes = [vp, _f, C.c_int32]
@@ -384,6 +389,13 @@ class Renderer:
 
     def set_profiling(self, enable=True):
         self._ck(self.lib.orb_set_profiling(self._h, int(enable)))
+
+    def stage_spans(self, max_spans=4096):
+        """[(stage name, slot, t0_ms, t1_ms), ...] recorded since the last stage_times(): a timeline (synchronises)."""
+        a = (OrbStageSpan * max_spans)()
+        n = C.c_int32()
+        self._ck(self.lib.orb_get_stage_spans(self._h, a, max_spans, C.byref(n)))
+        return [(STAGES[a[i].stage], a[i].slot, a[i].t0_ms, a[i].t1_ms) for i in range(min(n.value, max_spans))]
 
     def stage_times(self):
         """{stage: (summed ms, kernel launches)} since the previous call (synchronises)."""

@@ -697,8 +697,11 @@ k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce,
 // from the active-pixel queue.  One launch per frame, one tail per frame, no path state in HBM.
 // Shading is batched like the refill: lanes whose ray has ended wait until `refill_min` of them
 // have (or nobody can advance), so the divergent shading code runs with a fair number of lanes.
+#ifndef ORB_PATH_MINB
+#define ORB_PATH_MINB 5  // resident CTAs per SM the register allocation of the path kernel aims at
+#endif
 template <int SD, bool COUNT = false, bool QN = false>
-__global__ void __launch_bounds__(TRACE_BLOCK)
+__global__ void __launch_bounds__(TRACE_BLOCK, ORB_PATH_MINB)
 k_path_persistent(SceneView s, FrameView f, float3 cam_pos, int frame_id, int depth, unsigned* __restrict__ cursor,
                   int refill_min, int node_min, int height, const QNode* __restrict__ qn, QGrid qg) {
     unsigned c_nodes = 0, c_tris = 0;  // COUNT (ORB_RENDER_COUNT_TRAVERSAL): node / triangle records fetched by this lane
@@ -1242,6 +1245,7 @@ struct OrbContext : FrameSlot {
     int trace_ctas_per_sm = 0;
     cudaStream_t copy_stream = nullptr;
     int dl_snapshot_kernel = 1;
+    int dl_inplace = 1;  // several frame slots: read per-slot buffers back in place (ORB_DL_INPLACE)
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
@@ -1257,7 +1261,7 @@ struct OrbContext : FrameSlot {
     OrbCounters counters;
     // per-stage timing (orb_set_profiling)
     bool profiling = false;
-    struct StageSpan { int stage; int launches; cudaEvent_t e0, e1; };
+    struct StageSpan { int stage; int launches; cudaEvent_t e0, e1; int slot; };
     std::vector<StageSpan> spans;          // recorded since the last orb_get_stage_times
     std::vector<cudaEvent_t> free_events;  // recycled
     HaloLinks halo;                        // peer-mapped denoise buffers of the other ranks of a tile partition (halo.cuh)
@@ -1285,7 +1289,7 @@ struct StageTimer {
     StageTimer(OrbContext* ctx, int stage, int launches, cudaStream_t on_stream = nullptr, bool enable = true)
         : c(ctx), on(ctx->profiling && enable), stream(on_stream ? on_stream : ctx->stream) {
         if (!on) return;
-        sp.stage = stage; sp.launches = launches;
+        sp.stage = stage; sp.launches = launches; sp.slot = ctx->cur_slot;
         sp.e0 = get(c); sp.e1 = get(c);
         cudaEventRecord(sp.e0, stream);
     }
@@ -1573,6 +1577,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_RESOLVE_LANES")) c->resolve_lanes = atoi(e);
     if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
     if (const char* e = getenv("ORB_DL_SNAPSHOT_KERNEL")) c->dl_snapshot_kernel = atoi(e);
+    if (const char* e = getenv("ORB_DL_INPLACE")) c->dl_inplace = atoi(e);
     if (const char* e = getenv("ORB_PATH_SHADE_MIN")) c->path_shade_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_PATH_NODE_MIN")) c->path_node_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
@@ -1652,6 +1657,28 @@ int orb_sync(OrbContext* c) {  // every frame in flight
 int orb_set_profiling(OrbContext* c, int enable) {
     NEED(c, "orb_set_profiling: ctx is NULL");
     c->profiling = enable != 0;
+    return ORB_OK;
+}
+
+// The recorded spans themselves (a timeline of the frames in flight), times in ms relative to the first span's start;
+// does not clear them (orb_get_stage_times does).  Returns the number of spans through *n (at most `max` are written).
+int orb_get_stage_spans(OrbContext* c, OrbStageSpan* out, int32_t max, int32_t* n) {
+    NEED(c && n && (out || max == 0), "orb_get_stage_spans: NULL argument");
+    {
+        int rc = orb_sync(c);
+        if (rc) return rc;
+    }
+    *n = (int32_t)c->spans.size();
+    for (int i = 0; i < (int)c->spans.size() && i < max; i++) {
+        const auto& sp = c->spans[i];
+        float a = 0.f, b = 0.f;
+        CK(cudaEventElapsedTime(&a, c->spans[0].e0, sp.e0));
+        CK(cudaEventElapsedTime(&b, c->spans[0].e0, sp.e1));
+        out[i].stage = sp.stage;
+        out[i].slot = sp.slot;
+        out[i].t0_ms = a;
+        out[i].t1_ms = b;
+    }
     return ORB_OK;
 }
 
@@ -2572,7 +2599,7 @@ int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t
         CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
     }
     const bool shared = id == ORB_BUF_ACCUM || id == ORB_BUF_RGBA8;
-    if (c->n_slots > 1 && !shared) {
+    if (c->n_slots > 1 && !shared && c->dl_inplace) {
         // Two frame slots: this buffer belongs to the frame's slot and is not written again before the NEXT frame on
         // the slot (two frames later), so the copy stream reads it in place -- no snapshot.  (A snapshot KERNEL would
         // queue for SMs behind the other slot's persistent traversal kernel and hold back everything enqueued on this
