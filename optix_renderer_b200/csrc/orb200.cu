@@ -92,19 +92,20 @@ struct FrameView {
 extern __shared__ int s_dyn[];
 
 // SD (template parameter of every traversal kernel) selects the stack:
-//   SD > 0   HybridStack: SD entries per lane in shared memory (SD * 8 * TRACE_BLOCK bytes per CTA), the rest local
+//   SD > 0   HybridStack: SD entries per lane in shared memory (SD * 8 bytes per thread), the rest local
 //   SD == 0  thread-local memory only (no shared memory)
 //   SD == -1 StridedStack: full-height shared-memory columns, for hierarchies deeper than ORB_LOCAL_STACK_MAX
-template <int SD> struct StackOf { typedef HybridStack<SD, TRACE_BLOCK> type; };
+template <int SD> struct StackOf { typedef HybridStack<SD> type; };
 template <> struct StackOf<-1> { typedef StridedStack type; };
 template <int SD>
-__device__ __forceinline__ void stack_init(HybridStack<SD, TRACE_BLOCK>& st, int) {
+__device__ __forceinline__ void stack_init(HybridStack<SD>& st, int) {
     st.s = reinterpret_cast<unsigned long long*>(s_dyn) + threadIdx.x;
+    st.stride = (int)blockDim.x;
 }
 __device__ __forceinline__ void stack_init(StridedStack& st, int height) {
     st.r = s_dyn + threadIdx.x;
-    st.t = reinterpret_cast<float*>(s_dyn + height * TRACE_BLOCK) + threadIdx.x;
-    st.stride = TRACE_BLOCK;
+    st.t = reinterpret_cast<float*>(s_dyn + height * blockDim.x) + threadIdx.x;
+    st.stride = (int)blockDim.x;
 }
 
 struct SmemTracer {  // single-ray closest hit through full-height shared-memory columns (cold paths: literal / fused PATH)
@@ -1245,7 +1246,7 @@ struct OrbContext : FrameSlot {
     int trace_ctas_per_sm = 0;
     cudaStream_t copy_stream = nullptr;
     int dl_snapshot_kernel = 1;
-    int dl_inplace = 1;  // several frame slots: read per-slot buffers back in place (ORB_DL_INPLACE)
+    int dl_inplace = 0;  // several frame slots: 1 = read per-slot buffers back in place instead of through a copy-engine snapshot (ORB_DL_INPLACE)
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
@@ -1253,6 +1254,10 @@ struct OrbContext : FrameSlot {
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
     int ltc_pair_quads = 1;  // k_ltc: two TriLights that are the halves of a quad share their unclipped case (ORB_LTC_PAIR_QUADS)
     int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
+    // threads per CTA of the persistent traversal kernels (32 / 64 / 128, ORB_STREAM_BLOCK).  A CTA keeps its registers and
+    // shared memory until its LAST warp has finished: with frames in flight, small CTAs hand the SM to the other
+    // frame's kernels warp by warp while a traversal kernel's last rays run
+    int stream_block = 128;
     int stack_smem = 12;  // HybridStack: stack entries per lane held in shared memory (0, 8, 12 or 16; ORB_STACK_SMEM)
     float* unit_in = nullptr;
     float* unit_out = nullptr;
@@ -1460,7 +1465,7 @@ static int persistent_grid(OrbContext* c, K kernel, int block, size_t smem, int 
 // ---- which instantiation of a traversal kernel a context launches --------------------------------------------
 // stack form (template parameter SD of the kernels) and the dynamic shared memory it needs
 static int stack_mode(OrbContext* c) { return (c->local_stack && c->height <= ORB_LOCAL_STACK_MAX) ? c->stack_smem : -1; }
-static size_t stack_bytes(OrbContext* c, int sd) { return sd < 0 ? trace_smem(c) : (size_t)sd * 8 * TRACE_BLOCK; }
+static size_t stack_bytes(OrbContext* c, int sd, int block = TRACE_BLOCK) { return sd < 0 ? (size_t)c->height * block * 8 : (size_t)sd * 8 * block; }
 // the 64-byte fp32 nodes (default) or the 32-byte quantised ones (ORB_TRACE_VARIANT=3)
 static bool use_qnodes(OrbContext* c) { return c->trace_variant == 3 && c->qnodes != nullptr; }
 
@@ -1570,6 +1575,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
     if (const char* e = getenv("ORB_LTC_PAIR_QUADS")) c->ltc_pair_quads = atoi(e);
     if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
+    if (const char* e = getenv("ORB_STREAM_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128) c->stream_block = v; }
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_NODE_MIN")) c->node_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_TRACE_VARIANT")) c->trace_variant = atoi(e);
@@ -1978,17 +1984,18 @@ static int launch_trace_stream(OrbContext* c, const unsigned* n_items, unsigned 
     CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
     StageTimer tm(c, ORB_STAGE_TRACE, 1, nullptr, timed);
     const int sd = stack_mode(c);
-    const size_t smem = stack_bytes(c, sd);
+    const int block = c->stream_block;
+    const size_t smem = stack_bytes(c, sd, block);
     const bool qn = use_qnodes(c);
     StreamKernel k = stream_kernel(sd, count, qn);
     if (smem > 48 * 1024) CK(allow_smem(k, smem));
-    int g = persistent_grid(c, k, TRACE_BLOCK, smem, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
+    int g = persistent_grid(c, k, block, smem, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
     // a short stream (a narrow band of a tile partition) on a full persistent grid is mostly tail: every lane
     // gets a handful of rays and idles while the slowest ray of its warp finishes.  Fewer CTAs, more rays each.
     if (c->min_rays_per_lane > 0 && n_upper > 0)
-        g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)TRACE_BLOCK * c->min_rays_per_lane - 1) /
-                                                 ((size_t)TRACE_BLOCK * c->min_rays_per_lane))));
-    k<<<g, TRACE_BLOCK, smem, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
+        g = std::max(c->n_sm, std::min(g, (int)((n_upper + (size_t)block * c->min_rays_per_lane - 1) /
+                                                 ((size_t)block * c->min_rays_per_lane))));
+    k<<<g, block, smem, st>>>(c->view, c->stream_rays, c->stream_hits, n_items, mult, c->stream_cursor, c->refill_min,
                                     c->node_min, c->height, count ? &c->cnt->nodes_visited : nullptr,
                                     qn ? c->qnodes : (const QNode*)nullptr, qn ? c->qgrid : QGrid());
     c->counters.kernel_launches++;
@@ -2121,12 +2128,13 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
             StageTimer tm(c, ORB_STAGE_PATH, 1);
             CK(cudaMemsetAsync(c->stream_cursor, 0, 4, st));
             const int sd = stack_mode(c);
-            const size_t sm = stack_bytes(c, sd);
+            const int block = c->stream_block;
+            const size_t sm = stack_bytes(c, sd, block);
             const bool qn = use_qnodes(c);
             PathKernel k = path_kernel(sd, (cfg->flags & ORB_RENDER_COUNT_TRAVERSAL) != 0, qn);
             if (sm > 48 * 1024) CK(allow_smem(k, sm));
-            const int g = persistent_grid(c, k, TRACE_BLOCK, sm, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
-            k<<<g, TRACE_BLOCK, sm, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor, c->path_shade_min,
+            const int g = persistent_grid(c, k, block, sm, c->n_slots > 1 ? c->trace_ctas_per_sm : 0);
+            k<<<g, block, sm, st>>>(c->view, f, c->cam.pos, frame_id, depth, c->stream_cursor, c->path_shade_min,
                                           c->path_node_min, c->height, qn ? c->qnodes : (const QNode*)nullptr,
                                           qn ? c->qgrid : QGrid());
             c->counters.kernel_launches++;

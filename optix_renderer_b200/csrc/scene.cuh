@@ -189,20 +189,21 @@ struct StridedStack {
 // of its four accesses per push / pop (incoherent rays: nearly one per lane).  The local stack also takes ~4 KB
 // of L1 per warp (147 KB per SM at 36 warps) from the node data.  A shared-memory column is ONE wavefront per
 // warp and instruction whatever the depths, and leaves L1 to the nodes.  (A full-height shared stack was
-// measured slower in round 1: 27 KB per CTA cut the resident warps.  D entries cost D KB per 128-thread CTA.)
+// measured slower in round 1: 27 KB per CTA cut the resident warps.  D entries cost 8 D bytes per thread.)
 #define ORB_LOCAL_STACK_MAX 64
-template <int D, int BLOCK>
+template <int D>
 struct HybridStack {
-    unsigned long long* s;  // this thread's column: entry e at s[e * BLOCK]
+    unsigned long long* s;  // this thread's column: entry e at s[e * stride]
+    int stride;             // threads per CTA (columns side by side); 1 for a private array
     unsigned long long l[ORB_LOCAL_STACK_MAX - D];
     ORB_HD static unsigned long long pack(int ref, float tn) {
         return ((unsigned long long)(unsigned)__float_as_int_hd(tn) << 32) | (unsigned long long)(unsigned)ref;
     }
     ORB_HD void put(int i, int ref, float tn) {
-        if (i < D) s[i * BLOCK] = pack(ref, tn);
+        if (i < D) s[i * stride] = pack(ref, tn);
         else l[i - D] = pack(ref, tn);
     }
-    ORB_HD unsigned long long get(int i) const { return i < D ? s[i * BLOCK] : l[i - D]; }
+    ORB_HD unsigned long long get(int i) const { return i < D ? s[i * stride] : l[i - D]; }
 };
 
 // pop: skip subtrees that start beyond the current closest hit
@@ -214,8 +215,8 @@ ORB_HD int stack_pop(const Stack& st, int& sp, const Hit& best) {
         if (best.prim < 0 || !(st.dist(sp) > best.t)) return st.ref(sp);
     }
 }
-template <int D, int BLOCK>
-ORB_HD int stack_pop(const HybridStack<D, BLOCK>& st, int& sp, const Hit& best) {
+template <int D>
+ORB_HD int stack_pop(const HybridStack<D>& st, int& sp, const Hit& best) {
     for (;;) {
         if (sp == 0) return ORB_TRAVERSAL_DONE;
         --sp;

@@ -113,8 +113,9 @@ struct HostTracer {
         unsigned nn = 0, nt = 0;
         if (brute == 6 || brute == 7) {  // the hybrid stack of the GPU kernels: first 3 entries in a "shared" column, rest local
             unsigned long long col[3];
-            HybridStack<3, 1> hs;
+            HybridStack<3> hs;
             hs.s = col;
+            hs.stride = 1;
             const Hit hh = (brute == 7 && G.root_ref >= 0 && !G.qnodes.empty())
                                ? trace_closest_q(G.view, G.qnodes.data(), G.qgrid, o, d, hs, &nn, &nt)
                                : trace_closest(G.view, o, d, hs, &nn, &nt);
