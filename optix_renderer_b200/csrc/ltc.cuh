@@ -397,58 +397,18 @@ ORB_HD float ltc_decision_margin(const LtcFrame& f, float wl_z, const TriLight* 
     return m;
 }
 
-// ---- two TriLights that are the halves of one quad -------------------------------------------------------------
-// The reference's lights are the triangles of light MESHES (include/viewer.hpp:236-265), and a quad arrives as the fan
-// (a, b, c), (a, c, d) -- tinyobj's triangulation (src/Model.cpp:150-158), scenes.quad_tris here.  When both halves
-// take the unclipped case in both domains (every vertex above the horizon: the common case for a light overhead) the
-// two closed edge sums share the diagonal, and ca + ac cancel EXACTLY (edge_integral(p, q) = -edge_integral(q, p) in
-// floating point: the cross term changes sign, theta/sin(theta) depends on the dot product only).  So
-//     |ab + bc + ca| + |ac + cd + da|  =  |ab + bc + cd + da|
-// up to the order of four additions (< 1e-6 relative; both halves have the same orientation): four vertices are
-// normalised and transformed instead of six and four edge integrals evaluated instead of six, per domain.  Any
-// other case -- a back-facing half, a vertex below either horizon -- returns false and the caller integrates the
-// two triangles one by one exactly as before.
-ORB_HD bool lights_form_quad(const TriLight& A, const TriLight& B) {
-    return B.v1.x == A.v1.x && B.v1.y == A.v1.y && B.v1.z == A.v1.z && B.v2.x == A.v3.x && B.v2.y == A.v3.y && B.v2.z == A.v3.z &&
-           B.normal.x == A.normal.x && B.normal.y == A.normal.y && B.normal.z == A.normal.z && B.emit.x == A.emit.x &&
-           B.emit.y == A.emit.y && B.emit.z == A.emit.z;
-}
-
-ORB_HD bool integrate_quad_unclipped(const LtcFrame& f, const TriLight& A, const TriLight& B, float3& colour) {
-    float3 a = normalize(A.v1 - f.p), b = normalize(A.v2 - f.p), c = normalize(A.v3 - f.p), d = normalize(B.v3 - f.p);
-    if (dot(a + b + c, A.normal) > 0.f || dot(a + c + d, A.normal) > 0.f) return false;  // a back-facing half
-    a = apply(f.world_to_iso, a);
-    b = apply(f.world_to_iso, b);
-    c = apply(f.world_to_iso, c);
-    d = apply(f.world_to_iso, d);
-    if (!(a.z > 0.f && b.z > 0.f && c.z > 0.f && d.z > 0.f)) return false;
-    const float3 ta = normalize(apply_minv(f, a)), tb = normalize(apply_minv(f, b)), tc = normalize(apply_minv(f, c)),
-                 td = normalize(apply_minv(f, d));
-    if (!(ta.z > 0.f && tb.z > 0.f && tc.z > 0.f && td.z > 0.f)) return false;
-    float sd = edge_integral(a, b);
-    sd += edge_integral(b, c);
-    sd += edge_integral(c, d);
-    sd += edge_integral(d, a);
-    float sg = edge_integral(ta, tb);
-    sg += edge_integral(tb, tc);
-    sg += edge_integral(tc, td);
-    sg += edge_integral(td, ta);
-    colour += (f.diffuse * A.emit * fabsf(sd)) + (f.amplitude * A.emit * fabsf(sg));
-    return true;
-}
-
+// (Measured and removed, round 2: evaluating two TriLights that are the halves of one quad -- the fan (a, b, c),
+// (a, c, d) -- as ONE four-edge polygon in their common unclipped case.  The diagonal's two edge integrals cancel
+// exactly, so four vertices and four edges per domain instead of six and six; but k_ltc went 0.533 -> 0.589 ms at 32
+// lights (profiles/r2l_ab_ltc.jsonl): the fast path and its fall-back double the loop body, lanes of a warp split
+// between them, and the kernel was instruction-fetch sensitive already in round 1.)
 // The light loop.  `lights` normally points to shared memory (all lanes read the same light: a broadcast).
-// `quad` (optional, one byte per light): light l and l + 1 are the halves of a quad (lights_form_quad).
-ORB_HD float3 ltc_direct(const LtcFrame& f, const TriLight* lights, int n_lights, const unsigned char* quad = nullptr) {
+ORB_HD float3 ltc_direct(const LtcFrame& f, const TriLight* lights, int n_lights) {
     float3 colour = v3(0.f);
     if (!f.valid) return colour;
 #pragma unroll 1
     for (int l = 0; l < n_lights; l++) {
         const TriLight& L = lights[l];
-        if (quad && quad[l] && integrate_quad_unclipped(f, L, lights[l + 1], colour)) {
-            ++l;  // both halves done
-            continue;
-        }
         colour += integrate_tri_light(f, L.v1, L.v2, L.v3, L.normal, L.emit);
     }
     return colour;

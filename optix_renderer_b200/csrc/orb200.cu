@@ -197,21 +197,16 @@ k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int 
 
 template <bool FROM_QUEUE>
 __global__ void __launch_bounds__(LTC_BLOCK)
-k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4* __restrict__ out2, int pair_quads) {
+k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4* __restrict__ out2) {
     __shared__ TriLight sh_lights[LTC_SMEM_LIGHTS];
     __shared__ float4 sh_lut[LTC_SMEM_LUT_TEXELS];
     const bool lights_sm = s.n_lights <= LTC_SMEM_LIGHTS;
     const int lut_texels = 3 * s.lut.w * s.lut.h;
     const bool lut_sm = lut_texels <= LTC_SMEM_LUT_TEXELS;
-    __shared__ unsigned char sh_quad[LTC_SMEM_LIGHTS];  // light l and l + 1 are the halves of one quad (ltc.cuh)
     if (lights_sm) {
         const float* src = reinterpret_cast<const float*>(s.lights);
         float* dst = reinterpret_cast<float*>(sh_lights);
         for (int i = threadIdx.x; i < s.n_lights * 19; i += LTC_BLOCK) dst[i] = src[i];
-        __syncthreads();
-        // pairs are looked for at even positions only, so a pair never overlaps the next one
-        for (int l = threadIdx.x; l < s.n_lights; l += LTC_BLOCK)
-            sh_quad[l] = (pair_quads && !(l & 1) && l + 1 < s.n_lights && lights_form_quad(sh_lights[l], sh_lights[l + 1])) ? 1 : 0;
     }
     if (lut_sm)
         for (int i = threadIdx.x; i < lut_texels; i += LTC_BLOCK) sh_lut[i] = s.lut.data[i];
@@ -229,7 +224,7 @@ k_ltc(SceneView s, FrameView f, float3 cam_pos, float4* __restrict__ out, float4
             const float4 pp = ld_stream(f.position + ofs);
             const float4 dd = ld_stream(f.albedo + ofs);
             const float4 aa = ld_stream(f.alpha + ofs);
-            c = ltc_pixel(lut, lights, s.n_lights, cam_pos, v3(pp), v3(nn), v3(dd), aa.x, lights_sm ? sh_quad : nullptr);
+            c = ltc_pixel(lut, lights, s.n_lights, cam_pos, v3(pp), v3(nn), v3(dd), aa.x);
         }
         const float4 o = make_float4(c.x, c.y, c.z, 1.f);
         st_stream(out + ofs, o);
@@ -699,7 +694,10 @@ k_path_shade(SceneView s, FrameView f, float3 cam_pos, int frame_id, int bounce,
 // Shading is batched like the refill: lanes whose ray has ended wait until `refill_min` of them
 // have (or nobody can advance), so the divergent shading code runs with a fair number of lanes.
 #ifndef ORB_PATH_MINB
-#define ORB_PATH_MINB 5  // resident CTAs per SM the register allocation of the path kernel aims at
+// resident CTAs per SM the register allocation of the path kernel aims at.  Measured (profiles/r2l_ab_pmb.jsonl), PATH frame /
+// 135-row band: 5 CTAs (95 registers, no spills) 1.899 / 0.812 ms, 6 (80) 1.842 / 0.842, 7 (72, 142 B spilled) 1.759 / 0.833,
+// 8 (64, 222 B spilled) 1.740 / 0.863: the kernel is latency-bound, 28 warps beat 20 despite the spills.
+#define ORB_PATH_MINB 7
 #endif
 template <int SD, bool COUNT = false, bool QN = false>
 __global__ void __launch_bounds__(TRACE_BLOCK, ORB_PATH_MINB)
@@ -1252,7 +1250,6 @@ struct OrbContext : FrameSlot {
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
     int local_stack = 1;  // 0: full-height shared-memory stacks everywhere (round 1: 2.96 vs 2.51 ms for the 1080p shadow stage)
-    int ltc_pair_quads = 1;  // k_ltc: two TriLights that are the halves of a quad share their unclipped case (ORB_LTC_PAIR_QUADS)
     int l2_persist_mb = 0;  // > 0: pin the BVH nodes in a persisting-L2 window of this many MB (ORB_L2_PERSIST_MB)
     // threads per CTA of the persistent traversal kernels (32 / 64 / 128, ORB_STREAM_BLOCK).  A CTA keeps its registers and
     // shared memory until its LAST warp has finished: with frames in flight, small CTAs hand the SM to the other
@@ -1573,7 +1570,6 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_REFILL_MIN")) c->refill_min = std::max(1, std::min(32, atoi(e)));  // tuning knobs
     if (const char* e = getenv("ORB_LOCAL_STACK")) c->local_stack = atoi(e);
     if (const char* e = getenv("ORB_STACK_SMEM")) { const int v = atoi(e); if (v == 0 || v == 8 || v == 12 || v == 16) c->stack_smem = v; }
-    if (const char* e = getenv("ORB_LTC_PAIR_QUADS")) c->ltc_pair_quads = atoi(e);
     if (const char* e = getenv("ORB_L2_PERSIST_MB")) c->l2_persist_mb = std::max(0, atoi(e));
     if (const char* e = getenv("ORB_STREAM_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128) c->stream_block = v; }
     if (const char* e = getenv("ORB_TRACE_CTAS_PER_SM")) c->trace_ctas_per_sm = std::max(0, atoi(e));
@@ -2078,10 +2074,10 @@ int orb_render_async(OrbContext* c, const OrbRenderConfig* cfg) {
         const int g = persistent_grid(c, k_ltc<true>, LTC_BLOCK, 0);
         if (renderer == ORB_RATIO) {
             // light pixels already hold emit in `ltc` (k_primary), so `ltc` IS the frame colour
-            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.ltc, nullptr, c->ltc_pair_quads);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
             colour_src = f.ltc;
         } else {
-            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.colour, nullptr, c->ltc_pair_quads);
+            k_ltc<true><<<g, LTC_BLOCK, 0, ls>>>(c->view, f, c->cam.pos, f.colour, nullptr);
         }
         c->counters.kernel_launches++;
     };
@@ -2219,7 +2215,7 @@ int orb_ltc_gbuffer_pass(OrbContext* c, int32_t y0, int32_t y1) {
     const int g = persistent_grid(c, k_ltc<false>, LTC_BLOCK, 0);
     {
         StageTimer tm(c, ORB_STAGE_LTC_GBUFFER, 1);
-        k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr, c->ltc_pair_quads);
+        k_ltc<false><<<g, LTC_BLOCK, 0, c->stream>>>(c->view, f, c->cam.pos, f.ltc, nullptr);
     }
     c->counters.kernel_launches++;
     CK(cudaGetLastError());

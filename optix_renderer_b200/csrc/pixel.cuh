@@ -38,12 +38,12 @@ ORB_HD void primary_ray(const Camera& cam, int frame_id, int px, int py, int W, 
 
 // si.wo / to_local / wo_local as rayGen sets them (deviceCode.cu:80-84), then the LTC sum.
 ORB_HD float3 ltc_pixel(const LtcLut& lut, const TriLight* lights, int n_lights, float3 cam_pos, float3 p, float3 n,
-                        float3 diffuse, float alpha, const unsigned char* quad = nullptr) {
+                        float3 diffuse, float alpha) {
     const float3 wo = normalize(cam_pos - p);
     const Mat3 to_local = onb_rows(n);
     LtcFrame f;
     ltc_setup(f, lut, p, diffuse, alpha, to_local, wo);
-    return ltc_direct(f, lights, n_lights, quad);
+    return ltc_direct(f, lights, n_lights);
 }
 
 // One call of ratio_based_shadow(si, rng, 1): five draws, one closest-hit "shadow" ray.  Split

@@ -24,7 +24,6 @@ struct State {
     std::vector<MeshRec> meshes;
     std::vector<std::vector<uint8_t>> tex;
     std::vector<TriLight> lights;
-    std::vector<unsigned char> quad;  // lights l, l + 1 are the halves of a quad (ltc.cuh lights_form_quad), as k_ltc flags them
     std::vector<float4> lut;
     int lut_w = 0, lut_h = 0, lut_q = 0;
     std::vector<float4> tri;
@@ -180,8 +179,6 @@ void hc_add_mesh(const float* vtx, const float* nrm, const float* uv, int nVtx, 
 void hc_set_lights(const float* l19, int n) {
     G.lights.resize(n);
     if (n) memcpy((void*)G.lights.data(), l19, sizeof(TriLight) * (size_t)n);
-    G.quad.assign((size_t)n + 1, 0);
-    for (int l = 0; l + 1 < n; l += 2) G.quad[l] = lights_form_quad(G.lights[l], G.lights[l + 1]) ? 1 : 0;
     refresh();
 }
 
@@ -312,7 +309,7 @@ long long hc_render(int W, int H, int renderer, int accum_id, int mode, int spp,
                     put(b->sto_no_vis, o, c.x, c.y, c.z);
                 }
             } else if (renderer == 7 || renderer == 8) {
-                c = ltc_pixel(G.view.lut, G.view.lights, G.view.n_lights, G.cam.pos, si.p, si.n, si.diffuse, si.alpha, G.quad.data());
+                c = ltc_pixel(G.view.lut, G.view.lights, G.view.n_lights, G.cam.pos, si.p, si.n, si.diffuse, si.alpha);
                 if (renderer == 8) {
                     put(b->ltc, o, c.x, c.y, c.z);
                     Rng rng = rng_seed(frame_id, px, py, W);
