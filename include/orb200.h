@@ -310,6 +310,20 @@ int orb_ratio_estimator_host(OrbContext* ctx, const float* ltc, const float* sto
 int orb_trace_rays_host(OrbContext* ctx, const float* origin, const float* direction, size_t n, int32_t brute_force,
                         int32_t* prim, float* t, float* u, float* v);
 
+/* ---- allocation-free ray casting.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops).
+ * Same rays -> closest hits as orb_trace_rays_host(brute_force = 2) (the ray-stream kernel the RATIO / PATH
+ * frames use), but origin / direction (n*3 floats) and prim / t / u / v (n each) are DEVICE pointers the caller
+ * owns, and the kernel's scratch (ray stream, hit records, claim cursor) lives in one file-scope device array
+ * of 256 + 48 * ORB_NO_ALLOC_MAX_RAYS bytes (3 MiB) that every GPU loading the library holds until exit.
+ * Calls cudaMalloc / cudaFree / no allocating routine; n > ORB_NO_ALLOC_MAX_RAYS is refused with
+ * ORB_ERR_INVALID.  Enqueues three kernels on orb_stream() and returns (orb_sync() or the caller's own
+ * stream ordering before reading the outputs).  Every call on a device shares the scratch array: calls that
+ * overlap on the GPU (two contexts, two streams) race -- serialise them. */
+#define ORB_NO_ALLOC_MAX_RAYS 65536u
+int orb_trace_rays_no_alloc(OrbContext* ctx, const float* d_origin, const float* d_direction, uint32_t n,
+                            int32_t* d_prim, float* d_t, float* d_u, float* d_v);
+
 /* ---- known-answer entry points: run ONE device function in a one-thread kernel ---- */
 int orb_unit_rng(OrbContext* ctx, int frame_id, uint32_t px, uint32_t py, uint32_t W, int n, uint32_t* state0,
                  uint32_t* raw, float* flt);

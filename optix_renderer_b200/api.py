@@ -47,6 +47,7 @@ class OrbMeshDesc(C.Structure):
 
 
 BVH_SAH, BVH_LBVH = 0, 1
+NO_ALLOC_MAX_RAYS = 65536  # ORB_NO_ALLOC_MAX_RAYS (include/orb200.h)
 
 
 class OrbBvhOptions(C.Structure):
@@ -154,6 +155,7 @@ def load_library():
     L.orb_get_counters.argtypes = [vp, C.POINTER(OrbCounters)]
     L.orb_ratio_estimator_host.argtypes = [vp, _f, _f, _f, _f, C.c_size_t]
     L.orb_trace_rays_host.argtypes = [vp, _f, _f, C.c_size_t, C.c_int32, _i, _f, _f, _f]
+    L.orb_trace_rays_no_alloc.argtypes = [vp, vp, vp, C.c_uint32, vp, vp, vp, vp]
     L.orb_unit_rng.argtypes = [vp, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, _u, _u, _f]
     L.orb_unit_clip.argtypes = [vp, _f, C.c_int, _i, _f]
     L.orb_unit_integrate_edge.argtypes = [vp, _f, _f, _f]
@@ -464,6 +466,11 @@ class Renderer:
         self._ck(self.lib.orb_trace_rays_host(self._h, _fp(o), _fp(d), n, int(brute_force), prim.ctypes.data_as(_i),
                                               _fp(t), _fp(u), _fp(v)))
         return prim, t, u, v
+
+    def trace_rays_no_alloc(self, d_origin, d_direction, n, d_prim, d_t, d_u, d_v):
+        """orb_trace_rays_no_alloc: DEVICE pointers (ints) in and out, scratch in the library's static device array,
+        no allocation; enqueued on stream() -- sync() before reading the outputs.  n <= NO_ALLOC_MAX_RAYS."""
+        self._ck(self.lib.orb_trace_rays_no_alloc(self._h, d_origin, d_direction, int(n), d_prim, d_t, d_u, d_v))
 
     # ---- known-answer entry points ----
     def u_rng(self, frame, px, py, W, n):

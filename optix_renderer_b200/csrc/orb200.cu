@@ -2751,6 +2751,82 @@ int orb_trace_rays_host(OrbContext* c, const float* origin, const float* directi
     return ORB_OK;
 }
 
+// ---- allocation-free ray casting -------------------------------------------------------------
+// orb_trace_rays_no_alloc(): the ray-stream kernel (k_trace_stream_spec) with its scratch -- the packed ray
+// stream (32 B / ray), the hit records (16 B / ray), the claim cursor and the device-side ray count -- in ONE
+// file-scope device array instead of cudaMalloc'd buffers, for callers that may not allocate (CUDA graph
+// capture, serving loops).  The array is a fixed ORB_NO_ALLOC_SCRATCH_BYTES on every GPU that loads the
+// library, until exit.  Every call on a device shares it: calls that overlap on the GPU race.
+#define NOALLOC_HDR_BYTES 256u  // [0] claim cursor, [16] ray count (both cleared / set by k_noalloc_pack)
+#define ORB_NO_ALLOC_SCRATCH_BYTES (NOALLOC_HDR_BYTES + (size_t)ORB_NO_ALLOC_MAX_RAYS * 48u)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[ORB_NO_ALLOC_SCRATCH_BYTES];
+
+// `g_noalloc_scratch` in HOST code is only a handle for the symbol, not a device address; the address is asked of
+// the runtime once per device (with that device current) and cached.
+static int noalloc_scratch(int device, unsigned char** out) {
+    static std::mutex mu;
+    static unsigned char* base[64] = {};
+    NEED(device >= 0 && device < 64, "orb_trace_rays_no_alloc: device index out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!base[device]) {
+        unsigned char* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        NEED(p != nullptr && ((uintptr_t)p & 255u) == 0, "orb_trace_rays_no_alloc: scratch symbol has no aligned device address");
+        base[device] = p;
+    }
+    *out = base[device];
+    return ORB_OK;
+}
+
+// rays into the scratch stream; thread 0 resets what must start at zero (the claim cursor) and publishes the count
+__global__ void k_noalloc_pack(const float* __restrict__ o, const float* __restrict__ d, unsigned n, unsigned char* __restrict__ scratch) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        reinterpret_cast<unsigned*>(scratch)[0] = 0u;
+        reinterpret_cast<unsigned*>(scratch)[4] = n;
+    }
+    float4* rays = reinterpret_cast<float4*>(scratch + NOALLOC_HDR_BYTES);
+    if (i < n) stream_put_ray(rays, i, v3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), v3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+}
+
+int orb_trace_rays_no_alloc(OrbContext* c, const float* d_origin, const float* d_direction, uint32_t n, int32_t* d_prim,
+                            float* d_t, float* d_u, float* d_v) {
+    NEED(c && d_origin && d_direction && d_prim && d_t && d_u && d_v, "orb_trace_rays_no_alloc: NULL argument");
+    NEED(c->committed, "orb_trace_rays_no_alloc: scene not committed");
+    NEED(!c->geometry_dirty, "orb_trace_rays_no_alloc: orb_scene_update_mesh without orb_scene_refit (the BVH is stale)");
+    if (n > ORB_NO_ALLOC_MAX_RAYS) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "orb_trace_rays_no_alloc: %u rays exceed the fixed scratch (ORB_NO_ALLOC_MAX_RAYS = %u)", n,
+                 (unsigned)ORB_NO_ALLOC_MAX_RAYS);
+        return fail(ORB_ERR_INVALID, msg);
+    }
+    if (n == 0) return ORB_OK;
+    CK(cudaSetDevice(c->device));
+    unsigned char* scratch = nullptr;
+    int rc = noalloc_scratch(c->device, &scratch);
+    if (rc) return rc;
+    unsigned* cursor = reinterpret_cast<unsigned*>(scratch);
+    const unsigned* count = cursor + 4;
+    float4* rays = reinterpret_cast<float4*>(scratch + NOALLOC_HDR_BYTES);
+    float4* hits = rays + 2 * (size_t)ORB_NO_ALLOC_MAX_RAYS;
+    cudaStream_t st = c->stream;
+    k_noalloc_pack<<<(n + 255) / 256, 256, 0, st>>>(d_origin, d_direction, n, scratch);
+    const int sd = stack_mode(c);
+    const int block = c->stream_block;
+    const size_t smem = stack_bytes(c, sd, block);
+    const bool qn = use_qnodes(c);
+    StreamKernel k = stream_kernel(sd, false, qn);
+    if (smem > 48 * 1024) CK(allow_smem(k, smem));
+    int g = persistent_grid(c, k, block, smem, 0);
+    g = std::max(1, std::min(g, (int)((n + (unsigned)block - 1) / (unsigned)block)));
+    k<<<g, block, smem, st>>>(c->view, rays, hits, count, 1u, cursor, c->refill_min, c->node_min, c->height, nullptr,
+                              qn ? c->qnodes : (const QNode*)nullptr, qn ? c->qgrid : QGrid());
+    k_unpack_hits<<<(n + 255) / 256, 256, 0, st>>>(hits, n, d_prim, d_t, d_u, d_v);
+    c->counters.kernel_launches += 3;
+    CK(cudaGetLastError());
+    return ORB_OK;
+}
+
 // ---- known-answer entry points ---------------------------------------------------------------
 static int run_unit(OrbContext* c, int op, const float* in, int n_in, float* out, int n_out) {
     NEED(c, "orb_unit: ctx is NULL");
