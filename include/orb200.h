@@ -278,6 +278,10 @@ int orb_denoise_band(OrbContext* ctx, const OrbDenoiseConfig* cfg, int32_t y0, i
  * did not render report what its flags hold.  Used to balance row bands by cost. */
 int orb_row_active_counts(OrbContext* ctx, int32_t* host_counts);
 /* ltc_ratio_estimator.py:8: RATIO_FINAL = LTC * (STO_DIRECT[_DN] / STO_NO_VIS[_DN]) */
+/* orb_set_fused_combine(1): the filter's final pass (orb_denoise / orb_denoise_filter / orb_denoise_band) also writes
+ * RATIO_FINAL = LTC * (STO_DIRECT_DN / STO_NO_VIS_DN) over the rows it filters -- the same values, bit for bit, as a
+ * following orb_ratio_combine(use_denoised = 1), which the caller then leaves out (one launch and 48 B/px of reads). */
+int orb_set_fused_combine(OrbContext* ctx, int32_t enable);
 int orb_ratio_combine(OrbContext* ctx, int32_t use_denoised, int32_t y0, int32_t y1);
 
 /* ---- buffers ---- replaces owlBufferGetPointer + cudaMemcpy, viewer.hpp:695-713 */

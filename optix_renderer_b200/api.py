@@ -143,6 +143,7 @@ def load_library():
     L.orb_denoise_band.argtypes = [vp, C.POINTER(OrbDenoiseConfig), C.c_int32, C.c_int32, C.POINTER(OrbHaloSend), C.c_int32,
                                    _i, C.c_int32]
     L.orb_ratio_combine.argtypes = [vp, C.c_int32, C.c_int32, C.c_int32]
+    L.orb_set_fused_combine.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.restype = C.c_size_t
     L.orb_buffer_device_ptr.argtypes = [vp, C.c_int32]
@@ -375,6 +376,10 @@ class Renderer:
         out = np.zeros(self.H, np.int32)
         self._ck(self.lib.orb_row_active_counts(self._h, out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def set_fused_combine(self, enable=True):
+        """The filter's final pass also writes ratio_final (= ratio_combine(use_denoised=True), which is then left out)."""
+        self._ck(self.lib.orb_set_fused_combine(self._h, int(bool(enable))))
 
     def ratio_combine(self, use_denoised=False, rows=None):
         y0, y1 = rows if rows else (0, 0)

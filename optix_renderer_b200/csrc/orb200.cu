@@ -928,7 +928,9 @@ __device__ __forceinline__ float fast_ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
-__device__ __forceinline__ constexpr float b3_tap(int k) { return k == 0 ? 0.375f : ((k == 1 || k == -1) ? 0.25f : 0.0625f); }
+// log2 of the B3 tap weights (3/8, 1/4, 1/16): the tap's B3(dx) B3(dy) enters the weight's exponent as a constant
+__device__ __forceinline__ constexpr double b3_lg2_1(int k) { return k == 0 ? -1.4150374992788437 : ((k == 1 || k == -1) ? -2.0 : -4.0); }
+__device__ __forceinline__ constexpr float b3_lg2(int i, int j) { return (float)(b3_lg2_1(i) + b3_lg2_1(j)); }
 
 // The 25 taps of one pixel.  INTERIOR: the whole block is further than 2*step from every frame edge, no
 // bounds tests.  COLOUR: sigma_c > 0.  STEP > 0: the tap distance as a compile-time constant (the column
@@ -955,10 +957,10 @@ __device__ __forceinline__ void atrous_taps(const float4* __restrict__ guide, co
             if (!INTERIOR && (x + dx < 0 || x + dx >= W)) continue;
             const float4 g = __ldg(grow + dx);
             const float2 v = __ldg(vrow + dx);
-            // nd^sigma_n * exp(-|dz| / (sigma_p step)) as ONE ex2 of a sum of logs
+            // B3 B3 * nd^sigma_n * exp(-|dz| / (sigma_p step)) as ONE ex2 of a sum of logs
             const float nd = fmaxf(0.f, gc.x * g.x + gc.y * g.y + gc.z * g.z);
-            const float ln = sigma_n > 0.f ? sigma_n * fast_lg2(nd) : 0.f;
-            const float w = (b3_tap(i) * b3_tap(j)) * fast_ex2(ln - fabsf(gc.w - g.w) * inv_sigma_p);
+            const float ln = sigma_n > 0.f ? fmaf(sigma_n, fast_lg2(nd), b3_lg2(i, j)) : b3_lg2(i, j);
+            const float w = fast_ex2(fmaf(-fabsf(gc.w - g.w), inv_sigma_p, ln));
             float w0 = w, w1 = w;
             bool ok0 = v.x == v.x, ok1 = v.y == v.y;
             if (COLOUR) {
@@ -1013,6 +1015,153 @@ k_denoise_atrous(FrameView f, const float4* __restrict__ guide, const float2* __
         }
     } else {
         vout[ofs] = r;
+    }
+}
+
+// Four pixels per thread, `step` rows apart: pixel k's tap rows are y + (k - 2 .. k + 2) step, so the four share
+// eight rows of taps -- 40 tap loads for 100 tap evaluations instead of 100.  The one-pixel kernel sits at the L1
+// data pipe's roof as much as at the issue roof (6 wavefronts and 23 instructions per tap and warp, 4 schedulers
+// on one pipe); this form needs 2.4 wavefronts per evaluation.  A NaN value is skipped as a tap of ITS image only:
+// the test runs once per LOADED tap (value -> 0, mask -> 0), not once per evaluation, and an evaluation is four
+// multiply-adds (two sums, two masked weight sums) -- the same products and sums in the same order as
+// atrous_taps, so the two kernels agree bit for bit (test_atrous_four_pixels_per_thread_equals_one_pixel_kernel).
+// sigma_n > 0 and no colour term (the host launches k_denoise_atrous otherwise).  ratio_out != nullptr (FINAL): the
+// pass also writes RATIO_FINAL = ltc * (direct / no_vis), the k_ratio_combine of the denoised pair.
+// Rows of a CTA: step <= 8: 32 consecutive rows (8 / step groups of 4 step rows); step >= 16: the rows
+// by + ty + k step of a 4 step-row span, step / 8 CTAs per span.
+template <bool FINAL, int STEP, bool INTERIOR>
+__device__ __forceinline__ void atrous4_body(const FrameView& f, const float4* __restrict__ guide, const float2* __restrict__ vin,
+                                             float2* __restrict__ vout, float4* __restrict__ out_d, float4* __restrict__ out_n,
+                                             const float4* __restrict__ ltc, float4* __restrict__ ratio_out, int s, int x,
+                                             int base, float sigma_n, float inv_sigma_p) {
+    const int W = f.W, H = f.H;
+    float4 gc[4];
+    float2 vc[4];
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int y = base + k * s;
+        gc[k] = make_float4(0.f, 0.f, 0.f, DN_SKIP_DEPTH);
+        vc[k] = make_float2(0.f, 0.f);
+        if (y < f.y1) {
+            gc[k] = __ldg(guide + y * W + x);
+            vc[k] = __ldg(vin + y * W + x);
+        }
+        any = any || gc[k].w >= 0.f;
+    }
+    float sd[4] = {0.f, 0.f, 0.f, 0.f}, sn[4] = {0.f, 0.f, 0.f, 0.f}, wd[4] = {0.f, 0.f, 0.f, 0.f}, wn[4] = {0.f, 0.f, 0.f, 0.f};
+    if (any) {
+#pragma unroll
+        for (int m = 0; m < 8; m++) {
+            const int yy = base + (m - 2) * s;
+            const bool rowok = INTERIOR || (yy >= 0 && yy < H);
+            const float4* grow = guide + yy * W + x;
+            const float2* vrow = vin + yy * W + x;
+#pragma unroll
+            for (int i = -2; i <= 2; i++) {
+                const int dx = i * s;
+                // a tap outside the frame: the skip sentinel and a zero value enter every sum as exact zeros
+                float4 g = make_float4(0.f, 0.f, 0.f, DN_SKIP_DEPTH);
+                float2 v = make_float2(0.f, 0.f);
+                if (INTERIOR || (rowok && x + dx >= 0 && x + dx < W)) {
+                    g = __ldg(grow + dx);
+                    v = __ldg(vrow + dx);
+                }
+                const float m0 = v.x == v.x ? 1.f : 0.f, m1 = v.y == v.y ? 1.f : 0.f;
+                v.x = v.x == v.x ? v.x : 0.f;
+                v.y = v.y == v.y ? v.y : 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int j = m - k - 2;
+                    if (j < -2 || j > 2) continue;
+                    const float nd = fmaxf(0.f, gc[k].x * g.x + gc[k].y * g.y + gc[k].z * g.z);
+                    const float w = fast_ex2(fmaf(-fabsf(gc[k].w - g.w), inv_sigma_p, fmaf(sigma_n, fast_lg2(nd), b3_lg2(i, j))));
+                    sd[k] = fmaf(w, v.x, sd[k]);
+                    sn[k] = fmaf(w, v.y, sn[k]);
+                    wd[k] = fmaf(w, m0, wd[k]);
+                    wn[k] = fmaf(w, m1, wn[k]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int y = base + k * s;
+        if (y >= f.y1) continue;
+        const int ofs = y * W + x;
+        float2 r = vc[k];
+        const bool act = gc[k].w >= 0.f;
+        if (act) {
+            if (wd[k] > 0.f) r.x = sd[k] / wd[k];
+            if (wn[k] > 0.f) r.y = sn[k] / wn[k];
+        }
+        if (FINAL) {
+            float4 od, on;
+            if (act) {
+                od = make_float4(r.x, r.x, r.x, 1.f);
+                on = make_float4(r.y, r.y, r.y, 1.f);
+            } else {  // lights / misses: the unfiltered float4 (emit on light pixels, deviceCode.cu:121-123)
+                od = f.sto_direct[ofs];
+                on = f.sto_no_vis[ofs];
+            }
+            out_d[ofs] = od;
+            out_n[ofs] = on;
+            if (ratio_out) {
+                const float4 l = ld_stream(ltc + ofs);
+                st_stream(ratio_out + ofs, make_float4(l.x * (od.x / on.x), l.y * (od.y / on.y), l.z * (od.z / on.z), 1.f));
+            }
+        } else {
+            vout[ofs] = r;
+        }
+    }
+}
+
+#ifndef ORB_ATROUS4_MINB
+#define ORB_ATROUS4_MINB 3
+#endif
+template <bool FINAL, int STEP>
+__global__ void __launch_bounds__(256, ORB_ATROUS4_MINB)
+k_denoise_atrous4(FrameView f, const float4* __restrict__ guide, const float2* __restrict__ vin, float2* __restrict__ vout,
+                  float4* __restrict__ out_d, float4* __restrict__ out_n, const float4* __restrict__ ltc,
+                  float4* __restrict__ ratio_out, int step_rt, float sigma_n, float inv_sigma_p) {
+    const int s = STEP > 0 ? STEP : step_rt;
+    const int ty = threadIdx.x >> 5;
+    const int bx = blockIdx.x * 32;
+    const int x = bx + (threadIdx.x & 31);
+    int by, base, last;  // the CTA's first row, this thread's first row, the CTA's last row
+    if (s <= 8) {
+        by = f.y0 + blockIdx.y * 32;
+        base = by + (ty / s) * 4 * s + (ty % s);
+        last = by + 31;
+    } else {
+        const int per_span = s >= 8 ? s >> 3 : 1;
+        by = f.y0 + ((int)blockIdx.y / per_span) * 4 * s + ((int)blockIdx.y % per_span) * 8;
+        base = by + ty;
+        last = by + 7 + 3 * s;
+    }
+    if (x >= f.W || base >= f.y1) return;
+    const int reach = 2 * s;
+    const bool interior = bx >= reach && bx + 31 + reach < f.W && by >= reach && last + reach < f.H;
+    if (interior)
+        atrous4_body<FINAL, STEP, true>(f, guide, vin, vout, out_d, out_n, ltc, ratio_out, s, x, base, sigma_n, inv_sigma_p);
+    else
+        atrous4_body<FINAL, STEP, false>(f, guide, vin, vout, out_d, out_n, ltc, ratio_out, s, x, base, sigma_n, inv_sigma_p);
+}
+static dim3 atrous4_grid(int W, int rows, int step) {
+    if (step <= 8) return dim3((W + 31) / 32, (rows + 31) / 32);
+    return dim3((W + 31) / 32, ((rows + 4 * step - 1) / (4 * step)) * (step / 8));
+}
+typedef void (*Atrous4Kernel)(FrameView, const float4*, const float2*, float2*, float4*, float4*, const float4*, float4*, int,
+                              float, float);
+template <bool FINAL>
+static Atrous4Kernel atrous4_kernel(int step) {
+    switch (step) {
+        case 1: return k_denoise_atrous4<FINAL, 1>;
+        case 2: return k_denoise_atrous4<FINAL, 2>;
+        case 4: return k_denoise_atrous4<FINAL, 4>;
+        case 8: return k_denoise_atrous4<FINAL, 8>;
+        case 16: return k_denoise_atrous4<FINAL, 16>;
+        default: return k_denoise_atrous4<FINAL, 0>;
     }
 }
 
@@ -1246,6 +1395,8 @@ struct OrbContext : FrameSlot {
     int dl_snapshot_kernel = 1;
     int dl_inplace = 0;  // several frame slots: 1 = read per-slot buffers back in place instead of through a copy-engine snapshot (ORB_DL_INPLACE)
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
+    int atrous4 = 1;         // a-trous passes as k_denoise_atrous4 (four pixels per thread); 0 = one pixel per thread (ORB_ATROUS4)
+    int fused_combine = 0;   // the final a-trous pass also writes RATIO_FINAL (orb_set_fused_combine)
     int path_shade_min = 20;  // k_path_persistent: lanes with an ended ray before the warp shades / refills
     int path_node_min = 8;
     int path_persistent = 1;  // PATH intended mode: one persistent kernel for all bounces (0: per-bounce ray streams)
@@ -1580,6 +1731,7 @@ int orb_create(int device, OrbContext** out) {
     if (const char* e = getenv("ORB_MIN_RAYS_PER_LANE")) c->min_rays_per_lane = atoi(e);
     if (const char* e = getenv("ORB_DL_SNAPSHOT_KERNEL")) c->dl_snapshot_kernel = atoi(e);
     if (const char* e = getenv("ORB_DL_INPLACE")) c->dl_inplace = atoi(e);
+    if (const char* e = getenv("ORB_ATROUS4")) c->atrous4 = atoi(e);
     if (const char* e = getenv("ORB_PATH_SHADE_MIN")) c->path_shade_min = std::max(1, std::min(32, atoi(e)));
     if (const char* e = getenv("ORB_PATH_NODE_MIN")) c->path_node_min = std::max(1, std::min(32, atoi(e)));
     *out = c;
@@ -2266,7 +2418,22 @@ int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, i
         const float log2e = 1.4426950408889634f;  // the kernel evaluates exp(x) as exp2(x log2 e)
         const float isp = log2e / (d.sigma_position * (float)step);
         const float isc = d.sigma_colour > 0.f ? log2e / d.sigma_colour : 0.f;
-        if (it == d.iterations - 1) {
+        const bool four = c->atrous4 && isc == 0.f && d.sigma_normal > 0.f;
+        if (four && it == d.iterations - 1) {
+            Atrous4Kernel k = atrous4_kernel<true>(step);
+            k<<<atrous4_grid(c->W, y1 - y0, step), 256, 0, c->stream>>>(
+                f, guide, val[cur], nullptr, (float4*)c->buf[ORB_BUF_STO_DIRECT_DN], (float4*)c->buf[ORB_BUF_STO_NO_VIS_DN],
+                (const float4*)c->buf[ORB_BUF_LTC], c->fused_combine ? (float4*)c->buf[ORB_BUF_RATIO_FINAL] : nullptr, step,
+                d.sigma_normal, isp);
+        } else if (four) {
+            const int r = denoise_reach(d.iterations, it);
+            FrameView part = frame_view(c, std::max(0, y0 - r), std::min(c->H, y1 + r));
+            Atrous4Kernel k = atrous4_kernel<false>(step);
+            k<<<atrous4_grid(c->W, part.y1 - part.y0, step), 256, 0, c->stream>>>(part, guide, val[cur], val[cur ^ 1], nullptr,
+                                                                                  nullptr, nullptr, nullptr, step,
+                                                                                  d.sigma_normal, isp);
+            cur ^= 1;
+        } else if (it == d.iterations - 1) {
             dim3 gb((c->W + 31) / 32, (y1 - y0 + 7) / 8);
             AtrousKernel k = atrous_kernel<true>(isc > 0.f, step);
             k<<<gb, 256, 0, c->stream>>>(f, guide, val[cur], nullptr, (float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
@@ -2281,6 +2448,14 @@ int orb_denoise_filter(OrbContext* c, const OrbDenoiseConfig* cfg, int32_t y0, i
             cur ^= 1;
         }
         c->counters.kernel_launches++;
+        if (c->fused_combine && !four && it == d.iterations - 1) {  // same contract without the fused kernel
+            const size_t first = (size_t)y0 * c->W, np = (size_t)(y1 - y0) * c->W;
+            const int g = (int)std::min<size_t>((np + 255) / 256, (size_t)c->n_sm * 8);
+            k_ratio_combine<<<g, 256, 0, c->stream>>>((const float4*)c->buf[ORB_BUF_LTC], (const float4*)c->buf[ORB_BUF_STO_DIRECT_DN],
+                                                      (const float4*)c->buf[ORB_BUF_STO_NO_VIS_DN],
+                                                      (float4*)c->buf[ORB_BUF_RATIO_FINAL], first, np);
+            c->counters.kernel_launches++;
+        }
     }
     if (d.iterations > 1 && ((d.iterations - 1) & 1)) {
         // an odd number of ping-pong passes left pass 0's output in ORB_BUF_DN_VAL; nothing to restore:
@@ -2310,6 +2485,10 @@ static int preload_frame_kernels() {
     for (int st : steps) {
         CK(cudaFuncGetAttributes(&a, atrous_kernel<true>(false, st)));
         CK(cudaFuncGetAttributes(&a, atrous_kernel<false>(false, st)));
+    }
+    for (int st : steps) {
+        CK(cudaFuncGetAttributes(&a, atrous4_kernel<true>(st)));
+        CK(cudaFuncGetAttributes(&a, atrous4_kernel<false>(st)));
     }
     CK(cudaFuncGetAttributes(&a, atrous_kernel<true>(true, 0)));
     CK(cudaFuncGetAttributes(&a, atrous_kernel<false>(true, 0)));
@@ -2540,6 +2719,12 @@ int orb_row_active_counts(OrbContext* c, int32_t* host_counts) {
     CK(cudaMemcpyAsync(host_counts, d, sizeof(int) * c->H, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaFree(d));
+    return ORB_OK;
+}
+
+int orb_set_fused_combine(OrbContext* c, int32_t enable) {
+    NEED(c, "orb_set_fused_combine: ctx is NULL");
+    c->fused_combine = enable ? 1 : 0;
     return ORB_OK;
 }
 

@@ -258,6 +258,9 @@ class TiledRenderer:
         self._streams = {}
         self._ipc = []        # peer mappings opened by connect_halo()
         self.halo = False     # True: the denoise halo is handed over by peer stores inside the pack kernel
+        # the filter's final pass writes ratio_final too (orb_set_fused_combine); ORB_FUSED_COMBINE=0: separate kernel
+        self.fused_combine = os.environ.get("ORB_FUSED_COMBINE", "1") != "0"
+        renderer.set_fused_combine(self.fused_combine)
         self._plan_key, self._plan = None, None
         self.spans = None  # set to {} to collect CUDA-event spans of the collectives: name -> [(e0, e1), ...]
         self._stage_key, self._stage_in, self._stage_all, self._stage_meta, self._done_bands = None, None, None, {}, None
@@ -445,7 +448,7 @@ class TiledRenderer:
                         exchange_halos([self._t("dn_guide"), self._t("dn_val")], self.bands, self.rank, self.iters, self.group)
                     if y1 > y0:
                         self.r.denoise_filter(iterations=self.iters, rows=rows)
-        if y1 > y0:
+        if y1 > y0 and not (denoise and self.fused_combine):
             self.r.ratio_combine(use_denoised=denoise, rows=rows)
 
     def render_path_frame(self, accum_id, mode=1, max_depth=8):

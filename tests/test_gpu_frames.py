@@ -540,6 +540,44 @@ def test_path_stream_equals_fused_bounce_kernel(renderer_factory):
     assert cb["rays_bounce"] > cb["active_pixels"]
 
 
+@pytest.mark.parametrize("W,H", [(96, 64), (203, 157)])
+def test_atrous_four_pixels_per_thread_equals_one_pixel_kernel(renderer_factory, monkeypatch, W, H):
+    """k_denoise_atrous4 (four pixels per thread sharing tap rows, shared weight sum, NaN fall-back) against the
+    one-pixel kernel (ORB_ATROUS4=0): bit for bit -- every pass count up to 8 (run-time steps 32 .. 128), frames that are
+    not a multiple of the CTA tile, bands, NaN values and guides; and the combine fused into the final pass."""
+    sc = scenes.scene_cornell(W, H)
+    a = renderer_factory(sc)
+    monkeypatch.setenv("ORB_ATROUS4", "0")
+    b = renderer_factory(sc)
+    monkeypatch.delenv("ORB_ATROUS4")
+    a.set_fused_combine(True)
+    names = ("sto_direct_dn", "sto_no_vis_dn", "ratio_final")
+    for r in (a, b):
+        r.render(api.RATIO, accum_id=0, mode=1, shadow_spp=4)
+    f = {k: a.download(k) for k in ("normal", "sto_direct", "sto_no_vis", "materialID")}
+    rng = np.random.default_rng(9)
+    for with_nan in (False, True):
+        if with_nan:
+            ok = np.argwhere(f["materialID"][..., 0] != 0)
+            for k, (y, x) in enumerate(ok[rng.choice(len(ok), 40, replace=False)]):
+                f[("sto_direct", "sto_no_vis", "normal")[k % 3]][y, x, :3] = np.nan if k % 5 else np.inf
+            for r in (a, b):
+                for k in ("normal", "sto_direct", "sto_no_vis"):
+                    r.upload(k, f[k])
+        for iters in (1, 2, 3, 5, 8):
+            for rows in (None, (0, 37), (37, 38), (38, H)):
+                for r in (a, b):
+                    z = np.zeros((H, W, 4), np.float32)
+                    for k in names:
+                        r.upload(k, z)
+                    r.denoise_pack()
+                    r.denoise_filter(iterations=iters, rows=rows)
+                b.ratio_combine(use_denoised=True, rows=rows)
+                for k in names:
+                    assert np.array_equal(a.download(k), b.download(k), equal_nan=True), (k, iters, rows, with_nan)
+    assert a.counters()["kernel_launches"] < b.counters()["kernel_launches"]
+
+
 def test_denoise_halves_and_row_counts(renderer_factory):
     """orb_denoise == orb_denoise_pack + orb_denoise_filter; a band filtered from packed rows that were
     written band by band (as ranks exchange them) equals the same rows of the full-frame filter; the

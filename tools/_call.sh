@@ -1,5 +1,13 @@
 mkdir -p gpurun_out
-python -c "import __graft_entry__ as g; g.build_library()" 2>&1 | tail -2
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -x 2>&1 | tail -15 > gpurun_out/r2m_noalloc_alone.log; tail -3 gpurun_out/r2m_noalloc_alone.log
-timeout 1800 python -m pytest tests -m gpu -q -x --durations=15 2>&1 | tail -40 > gpurun_out/r2m_pytest.log; tail -25 gpurun_out/r2m_pytest.log
-timeout 600 python bench.py > gpurun_out/r2m_bench_ratio.json 2> gpurun_out/r2m_bench_ratio.err; tail -c 3000 gpurun_out/r2m_bench_ratio.json
+timeout 900 python -m pytest tests/test_gpu_frames.py -m gpu -q -x -k "atrous or denoise or two_frame_slots or band_handoff" 2>&1 | tail -5
+ORB200_LIB=$PWD/optix_renderer_b200/liborb200_mb3.so timeout 600 python bench.py --steps 60 --no-cpu-baseline > gpurun_out/r2n_ratio_mb3.json 2> gpurun_out/r2n_ratio_mb3.err
+timeout 600 python bench.py --steps 60 --no-cpu-baseline > gpurun_out/r2n_ratio_mb4.json 2> gpurun_out/r2n_ratio_mb4.err
+python - <<'PY'
+import json, glob
+for f in sorted(glob.glob("gpurun_out/r2n_ratio_mb*.json")):
+    try:
+        d = json.loads(open(f).read().strip().splitlines()[-1])
+        print(f, round(d["ms_per_step"], 3), "e2e", round(d["e2e"]["ms_per_step"], 3), {k: round(v["ms_per_frame"], 4) for k, v in d["passes"].items()})
+    except Exception as e:
+        print(f, "ERR", e)
+PY
