@@ -163,9 +163,10 @@ def workload_config(args, n):
             "partition": ("%d cost-balanced row bands, BVH replicated, packed denoise halo rows stored into the neighbours' "
                           "buffers by the pack kernel (peer-mapped memory over NVLink, epoch flags), NCCL all-gather of the "
                           "finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
-            "frames_in_flight": "2 per GPU (orb_set_frame_slots): frame i+1's kernels run beside frame i's traversal tail; "
-                                "accum / RGBA8 shared and accumulated in order",
-            "l2": "working set per frame (2 x 13+ float4 frame buffers of 33 MB, 40 MB triangles, 37 MB BVH) exceeds the "
+            "frames_in_flight": "several per GPU (orb_set_frame_slots; the count is this line's frames_in_flight key): the "
+                                "next frames' kernels run beside a frame's traversal tail; accum / RGBA8 shared and "
+                                "accumulated in order",
+            "l2": "working set per frame (13+ float4 frame buffers of 33 MB per frame in flight, 40 MB triangles, 37 MB BVH) exceeds the "
                   "126 MB L2; no explicit flush"}
 
 
@@ -223,8 +224,20 @@ def run_ours(args):
     if args.lut != 8:
         sc["lut"] = scenes.upsample_lut(sc["lut"], args.lut)
     r = api.Renderer(sc, device=local, quantise_lut=1)  # table fetched with the texture unit's weights, as the reference's tex2D
-    SLOTS = max(1, min(4, int(os.environ.get("ORB_BENCH_SLOTS", "2"))))  # frames in flight per GPU (orb_set_frame_slots)
+    # frames in flight per GPU (orb_set_frame_slots) and the persistent kernels' share of an SM.  Measured on one GPU
+    # rendering the band an N-way partition gives a rank (tools/ab_band.py, profiles/r2o_ab_band*.jsonl), ms per frame
+    # RATIO / PATH:            2 slots, no cap    4 slots, 4 CTAs    6 slots
+    #   whole frame            2.717 / 1.880      2.611 / 1.948*     2.600 / 1.802 (cap 4)        * cap 6
+    #   270 rows (N = 4)       1.103 / 1.056      0.993 / 0.843      0.979 / 0.827 (cap 3)
+    #   135 rows (N = 8)       0.669 / 0.737      0.538 / 0.527      0.521 / 0.466 (cap 2)
+    # A persistent kernel on a full grid keeps the other frames' CTAs off the SMs until its last ray ends, and a band's
+    # kernel is mostly tail: more frames in flight, each with a smaller share of every SM.
+    SLOTS = max(1, min(8, int(os.environ.get("ORB_BENCH_SLOTS", "6"))))
+    # 8 GPUs (profiles/r2q_n8_*.json): 6 slots cap 2 / cap 3 / 8 slots cap 2 = 0.672 / 0.638 / 0.694 ms per RATIO frame
+    CTA_CAP = int(os.environ.get("ORB_BENCH_CTA_CAP", "4" if world == 1 else "3"))
     r.set_frame_slots(SLOTS)
+    if "ORB_TRACE_CTAS_PER_SM" not in os.environ:
+        r.set_persistent_ctas_per_sm(CTA_CAP)
     stream = torch.cuda.Stream()  # carries the timing events; ordered behind the frame slots' own streams by T.join()
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
     HALO = world > 1 and ratio and os.environ.get("ORB_BENCH_HALO", "1") == "1" and T.connect_halo()
@@ -266,8 +279,15 @@ def run_ours(args):
         sampler.start()
         T.floor_ms = float(os.environ.get("ORB_BAND_FLOOR_MS", "0.25" if ratio else "0.45"))
         n_calib = int(os.environ.get("ORB_BAND_CALIB", "6")) if world > 1 else 0
-        base_id = args.warmup + n_calib  # accumId of the first timed frame
-        for i in range(args.warmup + n_calib):  # N > 1: n_calib extra untimed frames first, to settle the band cuts
+        # N > 1: after the last re-cut every frame slot renders one more untimed frame, so that whatever is sized by the
+        # band (ray streams, staging) is re-allocated before the clock starts (a cudaFree / cudaMalloc costs ~10 ms
+        # beside 7 peers' mapped memory)
+        n_settle = SLOTS if world > 1 else 0
+        base_id = args.warmup + n_calib + n_settle  # accumId of the first timed frame
+        for i in range(args.warmup + n_calib + n_settle):  # N > 1: n_calib extra untimed frames first, to settle the band cuts
+            if i >= args.warmup + n_calib:
+                step(i)
+                continue
             if world > 1:
                 # cut the row bands by cost: a model from the first frame's active pixels, then corrected by
                 # this rank's measured kernel time for its band (stage timers: the collectives and the
@@ -359,15 +379,28 @@ def run_ours(args):
                 HOST_GATHER = False
 
         e2e_host = [None]
+        e2e_host_parts = {"set_camera": 0.0, "render": 0.0, "assemble": 0.0, "read_back": 0.0, "final_wait": 0.0, "frames": 0}
 
         def e2e_loop(pipelined, id0, n):
             barrier()
             t0 = time.perf_counter()
+            hb = e2e_host_parts
+            for k in hb:
+                hb[k] = 0  # the last (timed) loop's numbers are the ones reported
             for i in range(n):
                 if i == n - 1:
                     e2e_host[0] = (time.perf_counter() - t0) * 1e3 / max(n - 1, 1)  # host time per frame of the enqueue loop
+                ta = time.perf_counter()
                 r.set_camera(cam["pos"], cam["d00"], cam["du"], cam["dv"])  # host -> library (launch parameters)
-                step(id0 + i)
+                tb = time.perf_counter()
+                render(id0 + i)
+                tc = time.perf_counter()
+                if SYNC_ASSEMBLE:
+                    T.assemble(out_names)
+                else:
+                    T.assemble_async(out_names)
+                td = time.perf_counter()
+                hb["set_camera"] += tb - ta; hb["render"] += tc - tb; hb["assemble"] += td - tc; hb["frames"] += 1
                 if rank == 0 and world == 1 and pipelined:
                     # D2H through the C-ABI, every frame, overlapped with the next frame's kernels
                     r.download_async(out_names[0], host_f4[i & 1], rows=(y0, y1))
@@ -386,10 +419,13 @@ def run_ours(args):
                     t_f4[i & 1].copy_(tiles.device_tensor(r, out_names[0]) if SYNC_ASSEMBLE else T.assembled(out_names[0]))
                     t_u32[i & 1].copy_(tiles.device_tensor(r, "rgba8") if SYNC_ASSEMBLE else T.assembled("rgba8"))
                     torch.cuda.current_stream().synchronize()
+                hb["read_back"] += time.perf_counter() - td
             if HOST_GATHER:
                 T.join(stream)
                 stream.synchronize()
+                tw = time.perf_counter()
                 T.wait_read_back_bands()  # every band of the last frame is on the host when the clock stops
+                hb["final_wait"] = (time.perf_counter() - tw) * hb["frames"]  # reported per frame like the others: x frames here
             elif world > 1 and rank == 0:
                 T.join(stream)
                 stream.synchronize()
@@ -404,7 +440,9 @@ def run_ours(args):
         PIPE = world == 1 and not SYNC_DOWNLOAD
         serial_ms = e2e_loop(False, base_id + args.steps, e_steps) if PIPE else None
         if PIPE or HOST_GATHER:
-            e2e_loop(PIPE, base_id + args.steps, 3)  # untimed: the read-back slots are allocated on first use
+            # untimed: the read-back staging is allocated on first use -- two staging buffers per output and frame slot,
+            # so 2 x SLOTS frames touch them all (a cudaMalloc / cudaFree inside the timed loop costs milliseconds at N = 8)
+            e2e_loop(PIPE, base_id + args.steps, max(3, 2 * SLOTS))
         e_ms = e2e_loop(PIPE, base_id + args.steps + (e_steps if PIPE else 0), e_steps)
         # the frame that arrived through the pipelined read-back is the frame the device holds
         readback_ok = bool(np.array_equal(host_f4[(e_steps - 1) & 1], r.download(out_names[0]), equal_nan=True)) if PIPE else None
@@ -568,6 +606,8 @@ def run_ours(args):
                 "e2e": {"value": e_value, "unit": "Mrays/s", "ms_per_step": e_ms / e_steps,
                         "frames_per_s": e_steps / (e_ms * 1e-3), "h2d_bytes_per_step": 48 + 32,
                         "d2h_bytes_per_step": W * H * 20, "steps": e_steps, "host_enqueue_ms_per_step": e2e_host[0],
+                        "host_ms_per_step_by_call": {k: round(v * 1e3 / max(1, e2e_host_parts["frames"]), 4)
+                                                     for k, v in e2e_host_parts.items() if k != "frames"},
                         "what": "orb_set_camera + orb_render_async(+denoise+combine) + %s of the "
                                 "float4 result and the RGBA8 frame into pinned host memory, every frame"
                                 % ("orb_buffer_download_rows_async (read-back of frame i overlaps the kernels of frame i+1; "

@@ -231,13 +231,17 @@ int orb_resize(OrbContext* ctx, int32_t width, int32_t height);
  * Blocking, like owlLaunch2D.  orb_render_async() enqueues on orb_stream() and returns. */
 int orb_render(OrbContext* ctx, const OrbRenderConfig* cfg);
 int orb_render_async(OrbContext* ctx, const OrbRenderConfig* cfg);
-/* Frames in flight: 1 (default) to 4.  With n > 1, consecutive orb_render_async calls cycle through n sets of frame
+/* Frames in flight: 1 (default) to 8.  With n > 1, consecutive orb_render_async calls cycle through n sets of frame
  * buffers and n streams, so the kernels of frame i+1 run beside the tail of frame i's persistent traversal kernels
  * (the reference renders strictly one frame at a time: owlLaunch2D blocks, viewer.hpp:565).  ORB_BUF_ACCUM and
  * ORB_BUF_RGBA8 are shared and accumulate in call order; every other buffer exists once per slot.  All calls that
  * follow an orb_render_async -- denoise, combine, downloads, orb_buffer_device_ptr, orb_stream -- refer to THAT
  * frame's slot until the next orb_render_async; orb_sync waits for every frame in flight.  Re-allocates the frame. */
 int orb_set_frame_slots(OrbContext* ctx, int32_t n_slots);
+/* With several frame slots: resident CTAs per SM the persistent traversal kernels (ray stream, PATH) may take, 0 = all
+ * that fit (default).  A full persistent grid keeps the other frames' kernels off the SMs until its last ray ends; on
+ * the narrow bands of a tile partition (few rays per lane) a cap of 2 - 4 with 4 - 6 slots is 20 - 35 % faster. */
+int orb_set_persistent_ctas_per_sm(OrbContext* ctx, int32_t n);
 int32_t orb_frame_slot(OrbContext* ctx);  /* slot of the frame the calls currently refer to */
 int32_t orb_frame_slots(OrbContext* ctx);
 void* orb_slot_stream(OrbContext* ctx, int32_t slot); /* cudaStream_t of a frame slot (to order a caller's stream behind it) */

@@ -144,6 +144,7 @@ def load_library():
                                    _i, C.c_int32]
     L.orb_ratio_combine.argtypes = [vp, C.c_int32, C.c_int32, C.c_int32]
     L.orb_set_fused_combine.argtypes = [vp, C.c_int32]
+    L.orb_set_persistent_ctas_per_sm.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.argtypes = [vp, C.c_int32]
     L.orb_buffer_bytes.restype = C.c_size_t
     L.orb_buffer_device_ptr.argtypes = [vp, C.c_int32]
@@ -376,6 +377,10 @@ class Renderer:
         out = np.zeros(self.H, np.int32)
         self._ck(self.lib.orb_row_active_counts(self._h, out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def set_persistent_ctas_per_sm(self, n):
+        """Frame slots > 1: CTAs per SM the persistent traversal kernels may take (0 = all that fit)."""
+        self._ck(self.lib.orb_set_persistent_ctas_per_sm(self._h, int(n)))
 
     def set_fused_combine(self, enable=True):
         """The filter's final pass also writes ratio_final (= ratio_combine(use_denoised=True), which is then left out)."""

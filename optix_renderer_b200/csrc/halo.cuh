@@ -24,7 +24,7 @@
 namespace orb {
 
 #define ORB_HALO_MAX_PEERS 8
-#define ORB_HALO_MAX_SLOTS 4
+#define ORB_HALO_MAX_SLOTS 8
 #define ORB_HALO_MAX_SENDS 4  // row ranges one pack launch pushes (a band narrower than the filter's reach has > 2)
 
 // control block layout (uint32 words): [0] error flag, then ready[slot][rank], then consumed[slot][rank]

@@ -24,6 +24,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <map>
 #include <mutex>
 #include <string>
@@ -1346,7 +1347,7 @@ struct FrameSlot {
     bool rendered = false;           // a frame has been enqueued on this slot since the last resize
     uint32_t halo_epoch = 0;         // frames whose packed denoise rows this slot has pushed to its peers (halo.cuh)
 };
-#define ORB_MAX_SLOTS 4
+#define ORB_MAX_SLOTS 8
 #define ORB_MAX_PENDING_DL 8
 
 // The context IS its active slot (the FrameSlot base: c->stream, c->buf, ... are the active frame's); the other
@@ -1738,8 +1739,10 @@ int orb_create(int device, OrbContext** out) {
     return ORB_OK;
 }
 
+static void dl_trace_report();
 void orb_destroy(OrbContext* c) {
     if (!c) return;
+    dl_trace_report();
     cudaSetDevice(c->device);
     select_slot(c, 0);
     cudaStreamSynchronize(c->stream);
@@ -1761,7 +1764,7 @@ void orb_destroy(OrbContext* c) {
 // Frames in flight (1 to 4).  With n > 1, consecutive orb_render_async calls cycle through n sets of frame buffers
 // and n streams; `accum` / RGBA8 stay shared and accumulate in call order.  Re-allocates the frame buffers.
 int orb_set_frame_slots(OrbContext* c, int32_t n) {
-    NEED(c && n >= 1 && n <= ORB_MAX_SLOTS, "orb_set_frame_slots: 1 to 4 slots");
+    NEED(c && n >= 1 && n <= ORB_MAX_SLOTS, "orb_set_frame_slots: 1 to 8 slots");
     CK(cudaSetDevice(c->device));
     int rc = orb_sync(c);
     if (rc) return rc;
@@ -2119,9 +2122,12 @@ static int ensure_stream(OrbContext* c, size_t n_rays) {
     cudaFree(c->stream_hits);
     c->stream_rays = c->stream_hits = nullptr;
     c->stream_cap = 0;
-    CK(cudaMalloc(&c->stream_rays, n_rays * 32));
-    CK(cudaMalloc(&c->stream_hits, n_rays * 16));
-    c->stream_cap = n_rays;
+    // growth with headroom: the bands of a tile partition move by a few rows when they are re-balanced, and a
+    // cudaFree / cudaMalloc pair synchronises the device (milliseconds beside peers' mapped memory)
+    const size_t cap = std::min(n_rays + n_rays / 4, std::max(n_rays, (size_t)c->W * c->H * 8));
+    CK(cudaMalloc(&c->stream_rays, cap * 32));
+    CK(cudaMalloc(&c->stream_hits, cap * 16));
+    c->stream_cap = cap;
     return ORB_OK;
 }
 
@@ -2722,6 +2728,12 @@ int orb_row_active_counts(OrbContext* c, int32_t* host_counts) {
     return ORB_OK;
 }
 
+int orb_set_persistent_ctas_per_sm(OrbContext* c, int32_t n) {
+    NEED(c && n >= 0, "orb_set_persistent_ctas_per_sm: bad argument");
+    c->trace_ctas_per_sm = n;
+    return ORB_OK;
+}
+
 int orb_set_fused_combine(OrbContext* c, int32_t enable) {
     NEED(c, "orb_set_fused_combine: ctx is NULL");
     c->fused_combine = enable ? 1 : 0;
@@ -2775,8 +2787,29 @@ int orb_buffer_download_rows(OrbContext* c, int32_t id, void* dst, int32_t y0, i
     return ORB_OK;
 }
 
+// ORB_DL_TRACE=1: host time spent in each CUDA call of orb_buffer_download_rows_async, printed by orb_destroy
+static double g_dl_trace[8];
+static long g_dl_calls;
+static int g_dl_trace_on = -1;
+struct DlTrace {
+    int k;
+    std::chrono::steady_clock::time_point t0;
+    explicit DlTrace(int kk) : k(kk), t0(std::chrono::steady_clock::now()) {}
+    ~DlTrace() {
+        if (g_dl_trace_on > 0) g_dl_trace[k] += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+};
+static void dl_trace_report() {
+    if (g_dl_trace_on > 0 && g_dl_calls)
+        fprintf(stderr, "ORB_DL_TRACE: %ld calls; ms per call: event-wait %.4f  snapshot %.4f  record+wait %.4f  d2h %.4f  record %.4f  realloc %.4f\n",
+                g_dl_calls, g_dl_trace[0] / g_dl_calls, g_dl_trace[1] / g_dl_calls, g_dl_trace[2] / g_dl_calls,
+                g_dl_trace[3] / g_dl_calls, g_dl_trace[4] / g_dl_calls, g_dl_trace[5] / g_dl_calls);
+}
+
 int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t y0, int32_t y1) {
     NEED(c && dst && id >= 0 && id < ORB_BUF_COUNT, "orb_buffer_download_rows_async: bad argument");
+    if (g_dl_trace_on < 0) g_dl_trace_on = getenv("ORB_DL_TRACE") ? 1 : 0;
+    g_dl_calls++;
     NEED(rows_ok(c, y0, y1), "orb_buffer_download_rows_async: bad row range");
     CK(cudaSetDevice(c->device));
     if (!c->copy_stream) CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
@@ -2803,27 +2836,38 @@ int orb_buffer_download_rows_async(OrbContext* c, int32_t id, void* dst, int32_t
         return ORB_OK;
     }
     if (sl.cap < bytes) {
+        DlTrace t(5);
         CK(cudaStreamSynchronize(c->copy_stream));
         CK(cudaFree(sl.dev));
         sl.dev = nullptr, sl.cap = 0;
         CK(cudaMalloc(&sl.dev, bytes));
         sl.cap = bytes;
     } else {
+        DlTrace t(0);
         CK(cudaStreamWaitEvent(c->stream, sl.done, 0));  // the slot's previous host copy has left it
     }
     // one slot: a kernel snapshots the rows (the copy engines only carry the host copy); two slots, shared accum /
     // RGBA8: a copy-engine snapshot, which needs no SM while the other slot's persistent kernels hold them all
     if (c->dl_snapshot_kernel && c->n_slots == 1 && bytes % 16 == 0 && (row * y0) % 16 == 0) {
+        DlTrace t(1);
         const size_t n16 = bytes / 16;
         k_snapshot<<<(unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)c->n_sm * 8), 256, 0, c->stream>>>(
             (const uint4*)((const char*)c->buf[id] + row * y0), (uint4*)sl.dev, n16);
         CK(cudaGetLastError());
     } else {
+        DlTrace t(1);
         CK(cudaMemcpyAsync(sl.dev, (const char*)c->buf[id] + row * y0, bytes, cudaMemcpyDeviceToDevice, c->stream));
     }
-    CK(cudaEventRecord(sl.ready, c->stream));
-    CK(cudaStreamWaitEvent(c->copy_stream, sl.ready, 0));
-    CK(cudaMemcpyAsync(dst, sl.dev, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    {
+        DlTrace t(2);
+        CK(cudaEventRecord(sl.ready, c->stream));
+        CK(cudaStreamWaitEvent(c->copy_stream, sl.ready, 0));
+    }
+    {
+        DlTrace t(3);
+        CK(cudaMemcpyAsync(dst, sl.dev, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    DlTrace t(4);
     CK(cudaEventRecord(sl.done, c->copy_stream));
     return ORB_OK;
 }

@@ -689,16 +689,19 @@ def test_refit_after_moving_meshes(renderer_factory, builder, n_tris):
         assert np.array_equal(a, b)
 
 
-def test_two_frame_slots_equal_one(renderer_factory):
-    """orb_set_frame_slots(2): consecutive frames alternate between two buffer sets and two streams; accum / RGBA8 are
+@pytest.mark.parametrize("slots,cap", [(2, 0), (6, 3)])
+def test_two_frame_slots_equal_one(renderer_factory, slots, cap):
+    """orb_set_frame_slots(n): consecutive frames cycle through n buffer sets and n streams (with an optional cap on the
+    persistent kernels' CTAs per SM, orb_set_persistent_ctas_per_sm); accum / RGBA8 are
     shared and ordered.  Frames, the running sum and the ray totals equal those of a one-slot context bit for bit,
     for RATIO (+ denoise + combine on the frame's slot) and PATH, with pipelined read-backs of every frame."""
     import torch
     sc = scenes.scene_synthetic(n_tris=50000, n_quad_lights=5, width=160, height=96)
     a, b = renderer_factory(sc), renderer_factory(sc)
-    b.set_frame_slots(2)
-    assert b.frame_slots == 2 and a.frame_slots == 1
-    n = 6
+    b.set_frame_slots(slots)
+    b.set_persistent_ctas_per_sm(cap)
+    assert b.frame_slots == slots and a.frame_slots == 1
+    n = 6 if slots == 2 else 14
     pin = torch.empty((n, 96, 160, 4), dtype=torch.float32, pin_memory=True).numpy()
     pin_u = torch.empty((n, 96, 160), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
     want = []
@@ -708,7 +711,7 @@ def test_two_frame_slots_equal_one(renderer_factory):
         a.ratio_combine(use_denoised=True)
         want.append((a.download("ratio_final"), a.download("rgba8"), a.download("accum"), (a.download("normal")[..., :3] != 0).any(-1)))
         b.render(api.RATIO, accum_id=i, mode=1, shadow_spp=4, sync=False)
-        assert b.frame_slot == (i + 1) % 2
+        assert b.frame_slot == (i + 1) % slots
         b.denoise(iterations=3)
         b.ratio_combine(use_denoised=True)
         b.download_async("ratio_final", pin[i])
@@ -739,7 +742,7 @@ def test_two_frame_slots_equal_one(renderer_factory):
     assert np.array_equal(a.download("sto_direct")[w], b.download("sto_direct")[w], equal_nan=True)
 
 
-@pytest.mark.parametrize("slots", [1, 2])
+@pytest.mark.parametrize("slots", [1, 2, 6])
 def test_band_handoff_through_peer_stores(renderer_factory, slots):
     """The fused tile hand-off (csrc/halo.cuh, orb_denoise_band): three contexts of ONE process play the ranks of a
     row-band partition -- bands of 50 / 8 / 102 rows, the middle one narrower than the filter's reach so its

@@ -16,11 +16,13 @@ for spec in (sys.argv[1:] or [""]):
         k, v = kv.split("=")
         if k == "SLOTS":
             slots = int(v)
+        elif k == "BAND":  # BAND=y0:y1 (default: the 135 rows an 8-way partition gives one rank)
+            band = tuple(int(x) for x in v.split(":"))
         else:
             os.environ[k] = v
     r = api.Renderer(sc, quantise_lut=1)
     r.set_frame_slots(slots)
-    out = {"knobs": spec, "slots": slots, "lib": os.environ.get("ORB200_LIB", "default")[-14:]}
+    out = {"knobs": spec, "slots": slots, "band": list(band), "lib": os.environ.get("ORB200_LIB", "default")[-14:]}
     for wl in ("ratio", "path"):
         def frame(i):
             if wl == "ratio":
