@@ -193,6 +193,7 @@ class Renderer:
         self._ck(self.lib.orb_create(int(device), C.byref(h)))
         self._h = h
         self.W = self.H = 0
+        self._dl_keep = []
         if scene is not None:
             self.load_scene(scene, quantise_lut, max_leaf_tris, builder)
 
@@ -435,11 +436,20 @@ class Renderer:
         """Pipelined read-back (orb_buffer_download_rows_async): `out` is a page-locked array that must stay
         alive and untouched until download_wait()."""
         y0, y1 = rows if rows else (0, self.H)
+        elem = 4 if name == "rgba8" else (8 if name == "dn_val" else 16)
+        need = (y1 - y0) * self.W * elem
+        if not (isinstance(out, np.ndarray) and out.flags.c_contiguous and out.flags.writeable and out.nbytes == need):
+            # the copy stream writes `need` bytes at out's address asynchronously: a strided view or a short array
+            # would be overrun silently
+            raise OrbError("download_async: `out` must be a writable C-contiguous array of exactly %d bytes "
+                           "(rows %d..%d of %s)" % (need, y0, y1, name))
         self._ck(self.lib.orb_buffer_download_rows_async(self._h, BUFFERS[name], out.ctypes.data_as(C.c_void_p), y0, y1))
+        self._dl_keep.append(out)  # alive until download_wait()
         return out
 
     def download_wait(self):
         self._ck(self.lib.orb_download_wait(self._h))
+        self._dl_keep = []
 
     def upload(self, name, arr):
         a = np.ascontiguousarray(arr)

@@ -252,6 +252,19 @@ struct BvhBuildResult {
         if (e_ != cudaSuccess) return e_; \
     } while (0)
 
+// Scratch arrays of a build / refit: freed when the function returns, on the error paths of ORB_CU too.
+struct DevFreeOnExit {
+    void** v[40];
+    int n = 0;
+    void add(void* pp) { if (n < 40) v[n++] = static_cast<void**>(pp); }
+    ~DevFreeOnExit() {
+        for (int i = 0; i < n; i++) {
+            cudaFree(*v[i]);
+            *v[i] = nullptr;
+        }
+    }
+};
+
 // d_pos: 9 floats per global primitive, already on the device.  Synchronises the stream once.
 inline cudaError_t build_bvh(const float* d_pos, int n, int max_leaf, cudaStream_t st, BvhBuildResult& out) {
     out = BvhBuildResult();
@@ -264,6 +277,11 @@ inline cudaError_t build_bvh(const float* d_pos, int n, int max_leaf, cudaStream
     int2 *child = nullptr, *range = nullptr;
     int *node_parent = nullptr, *leaf_parent = nullptr, *height = nullptr;
     void* cub_tmp = nullptr;
+    DevFreeOnExit scratch;
+    for (void* pp : {(void*)&plo, (void*)&phi, (void*)&nlo, (void*)&nhi, (void*)&scene_box, (void*)&vals, (void*)&vals_s,
+                     (void*)&flag, (void*)&keys, (void*)&keys_s, (void*)&child, (void*)&range, (void*)&node_parent,
+                     (void*)&leaf_parent, (void*)&height, (void*)&cub_tmp})
+        scratch.add(pp);
     const size_t ni = (size_t)(n > 1 ? n - 1 : 1);
     ORB_CU(cudaMalloc(&plo, sizeof(float4) * n));
     ORB_CU(cudaMalloc(&phi, sizeof(float4) * n));
@@ -317,9 +335,6 @@ inline cudaError_t build_bvh(const float* d_pos, int n, int max_leaf, cudaStream
         out.n_nodes = n - 1;
     }
     ORB_CU(cudaGetLastError());
-    cudaFree(plo); cudaFree(phi); cudaFree(scene_box); cudaFree(keys); cudaFree(keys_s); cudaFree(vals);
-    cudaFree(vals_s); cudaFree(cub_tmp); cudaFree(child); cudaFree(range); cudaFree(node_parent);
-    cudaFree(leaf_parent); cudaFree(height); cudaFree(flag); cudaFree(nlo); cudaFree(nhi);
     return cudaSuccess;
 }
 

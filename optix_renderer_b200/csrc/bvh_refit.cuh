@@ -137,6 +137,8 @@ inline cudaError_t refit_bvh(const float* d_pos, int n, cudaStream_t st, BvhBuil
     int* parent = nullptr;
     unsigned* arrivals = nullptr;
     float4 *sub_lo = nullptr, *sub_hi = nullptr;
+    DevFreeOnExit scratch;
+    for (void* pp : {(void*)&scene_box, (void*)&parent, (void*)&arrivals, (void*)&sub_lo, (void*)&sub_hi}) scratch.add(pp);
     ORB_CU(cudaMalloc(&scene_box, 6 * sizeof(unsigned)));
     ORB_CU(cudaMemsetAsync(scene_box, 0xff, 3 * sizeof(unsigned), st));  // mins start at the largest key
     ORB_CU(cudaMemsetAsync(scene_box + 3, 0, 3 * sizeof(unsigned), st));
@@ -157,7 +159,6 @@ inline cudaError_t refit_bvh(const float* d_pos, int n, cudaStream_t st, BvhBuil
     }
     ORB_CU(cudaStreamSynchronize(st));
     ORB_CU(cudaGetLastError());
-    cudaFree(scene_box); cudaFree(parent); cudaFree(arrivals); cudaFree(sub_lo); cudaFree(sub_hi);
     return cudaSuccess;
 }
 

@@ -312,6 +312,11 @@ inline cudaError_t build_bvh_sah(const float* d_pos, int n, int max_leaf, cudaSt
     SahBin* bins = nullptr;
     int* counters = nullptr;
     void* cub_tmp = nullptr;
+    DevFreeOnExit scratch;
+    for (void* pp : {(void*)&plo, (void*)&phi, (void*)&scene_box, (void*)&node_a, (void*)&node_b, (void*)&id_a, (void*)&id_b,
+                     (void*)&keys, (void*)&keys_s, (void*)&nd.lo, (void*)&nd.hi, (void*)&nd.count, (void*)&nd.first,
+                     (void*)&nd.left, (void*)&nd.split, (void*)&nd.slot, (void*)&bins, (void*)&counters, (void*)&cub_tmp})
+        scratch.add(pp);
     ORB_CU(cudaMalloc(&plo, sizeof(float4) * n));
     ORB_CU(cudaMalloc(&phi, sizeof(float4) * n));
     ORB_CU(cudaMalloc(&scene_box, 6 * sizeof(unsigned)));
@@ -401,10 +406,6 @@ inline cudaError_t build_bvh_sah(const float* d_pos, int n, int max_leaf, cudaSt
         out.n_nodes = n_nodes;
     }
     ORB_CU(cudaGetLastError());
-    cudaFree(plo); cudaFree(phi); cudaFree(scene_box); cudaFree(keys); cudaFree(keys_s); cudaFree(node_a);
-    cudaFree(node_b); cudaFree(id_a); cudaFree(id_b); cudaFree(cub_tmp); cudaFree(nd.lo); cudaFree(nd.hi);
-    cudaFree(nd.count); cudaFree(nd.first); cudaFree(nd.left); cudaFree(nd.split); cudaFree(nd.slot);
-    cudaFree(bins); cudaFree(counters);
     return cudaSuccess;
 }
 

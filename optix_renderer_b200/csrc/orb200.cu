@@ -185,6 +185,7 @@ k_primary(SceneView s, FrameView f, Camera cam, int frame_id, int renderer, int 
         unsigned base = 0;
         if (lane == 0) base = atomicAdd(&f.cnt->queue_n, (unsigned)__popc(m));
         base = __shfl_sync(0xffffffffu, base, 0);
+        ORB_DEVICE_ASSERT(!active || base + __popc(m & ((1u << lane) - 1u)) < (unsigned)((f.y1 - f.y0) * f.W));
         if (active) f.queue[base + __popc(m & ((1u << lane) - 1u))] = (uint32_t)ofs;
     }
 }
@@ -329,6 +330,7 @@ k_trace_stream_spec(SceneView s, const float4* __restrict__ rays, float4* __rest
     for (;;) {
         const bool idle = t.cur == ORB_TRAVERSAL_DONE && leaf == 0;
         if (idle && ray != FULL) {
+            ORB_DEVICE_ASSERT(ray < n);  // the slot a generator wrote into the ray record
             st_stream(hits + ray, make_float4(__int_as_float(t.best.prim), t.best.u, t.best.v, t.best.t));
             ray = FULL;
         }
@@ -1065,6 +1067,7 @@ __device__ __forceinline__ void atrous4_body(const FrameView& f, const float4* _
                 float4 g = make_float4(0.f, 0.f, 0.f, DN_SKIP_DEPTH);
                 float2 v = make_float2(0.f, 0.f);
                 if (INTERIOR || (rowok && x + dx >= 0 && x + dx < W)) {
+                    ORB_DEVICE_ASSERT(yy >= 0 && yy < H && x + dx >= 0 && x + dx < W);
                     g = __ldg(grow + dx);
                     v = __ldg(vrow + dx);
                 }
@@ -1551,6 +1554,7 @@ static void refresh_view(OrbContext* c) {
     v.nodes = c->bvh.nodes;
     v.root_ref = c->bvh.root_ref;
     v.n_tris = (int)c->h_prim_mesh.size();
+    v.n_nodes = c->bvh.n_nodes;
     v.pos = c->d_pos;
     v.nrm = c->d_nrm;
     v.uv = c->d_uv;
@@ -2059,9 +2063,16 @@ int orb_scene_refit(OrbContext* c) {
     NEED(c, "orb_scene_refit: ctx is NULL");
     NEED(c->committed, "orb_scene_refit: scene not committed");
     CK(cudaSetDevice(c->device));
-    cudaEvent_t e0, e1;
-    CK(cudaEventCreate(&e0));
-    CK(cudaEventCreate(&e1));
+    struct EventPair {  // destroyed on every return path
+        cudaEvent_t a = nullptr, b = nullptr;
+        ~EventPair() {
+            if (a) cudaEventDestroy(a);
+            if (b) cudaEventDestroy(b);
+        }
+    } ev;
+    CK(cudaEventCreate(&ev.a));
+    CK(cudaEventCreate(&ev.b));
+    cudaEvent_t e0 = ev.a, e1 = ev.b;
     CK(cudaEventRecord(e0, c->stream));
     const int before = c->bvh.launches;
     CK(refit_bvh(c->d_pos, (int)c->h_prim_mesh.size(), c->stream, c->bvh));
@@ -2073,8 +2084,6 @@ int orb_scene_refit(OrbContext* c) {
     CK(cudaEventSynchronize(e1));
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     c->counters.bvh_refit_us = (uint64_t)(ms * 1000.f);
     c->counters.kernel_launches += (uint64_t)(c->bvh.launches - before);
     c->geometry_dirty = false;

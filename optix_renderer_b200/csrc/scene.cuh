@@ -55,6 +55,7 @@ struct SceneView {
     const BvhNode* nodes;
     int root_ref;  // child-style reference of the root; 0 triangles -> n_tris == 0
     int n_tris;
+    int n_nodes;   // inner nodes (ORB_CHECKS: bound of every node reference)
     const float* pos;
     const float* nrm;
     const float* uv;
@@ -80,6 +81,7 @@ ORB_HD void tri_record(float* a8, float* b2, const float* p9, int prim) {  // wr
     b2[0] = xsub(p9[7], p9[1]), b2[1] = xsub(p9[8], p9[2]);
 }
 ORB_HD void tri_fetch(const SceneView& s, int k, float4& t0, float4& t1, float4& t2) {
+    ORB_DEVICE_ASSERT(k >= 0 && k < s.n_tris);
 #ifdef __CUDA_ARCH__
     float e2x;
 #if defined(ORB_TRI_FETCH) && ORB_TRI_FETCH == 1  // A/B: two 128-bit loads instead of one 256-bit load
@@ -200,10 +202,14 @@ struct HybridStack {
         return ((unsigned long long)(unsigned)__float_as_int_hd(tn) << 32) | (unsigned long long)(unsigned)ref;
     }
     ORB_HD void put(int i, int ref, float tn) {
+        ORB_DEVICE_ASSERT(i >= 0 && i < ORB_LOCAL_STACK_MAX);
         if (i < D) s[i * stride] = pack(ref, tn);
         else l[i - D] = pack(ref, tn);
     }
-    ORB_HD unsigned long long get(int i) const { return i < D ? s[i * stride] : l[i - D]; }
+    ORB_HD unsigned long long get(int i) const {
+        ORB_DEVICE_ASSERT(i >= 0 && i < ORB_LOCAL_STACK_MAX);
+        return i < D ? s[i * stride] : l[i - D];
+    }
 };
 
 // pop: skip subtrees that start beyond the current closest hit
@@ -273,6 +279,7 @@ ORB_HD void trav_descend(TravState& t, Stack& st, bool h0, bool h1, float tn0, f
 // One inner node (t.cur >= 0): both child boxes of a 64-byte node.
 template <class Stack>
 ORB_HD void trav_node_step(TravState& t, const SceneView& s, Stack& st) {
+    ORB_DEVICE_ASSERT(t.cur >= 0 && t.cur < s.n_nodes);
     const BvhNode* np = s.nodes + t.cur;
 #ifdef __CUDA_ARCH__
     // two 256-bit loads (sm_100: LDG.E.256) instead of four 128-bit ones: every lane reads its own node and

@@ -11,6 +11,18 @@
 #include <stdint.h>
 #include <string.h>
 
+// ORB_CHECKS build (tools/build_checked.sh -> liborb200_chk.so): device-side assertions on every index the kernels
+// form from claimed work items, stack depths, node / triangle references and tap coordinates.  compute-sanitizer is
+// not available on this pool (profiles/r2m_sanitizer_closed.txt); the GPU suite run against the checked library is
+// the bounds evidence instead.  A failed assertion prints file:line and turns the next CUDA call into
+// cudaErrorAssert, so the test that triggered it fails.
+#if defined(ORB_CHECKS) && defined(__CUDA_ARCH__)
+#include <assert.h>
+#define ORB_DEVICE_ASSERT(c) assert(c)
+#else
+#define ORB_DEVICE_ASSERT(c) ((void)0)
+#endif
+
 #define ORB_PI_D 3.141592653589793238  // include/common.h:4 -- a DOUBLE literal in the reference
 #define ORB_PI_F ((float)ORB_PI_D)
 #define ORB_EPS 1e-5f  // cuda_include/frostbite.cuh:8

@@ -194,10 +194,21 @@ class SharedHostFrames:
         box = [None]
         if rank == 0:
             vfs = os.statvfs("/dev/shm")
-            if vfs.f_bavail * vfs.f_frsize >= total + (64 << 20):  # a short tmpfs would end in SIGBUS on first touch
-                box[0] = "/dev/shm/orb200_frames_%d_%x" % (os.getpid(), id(self) & 0xffffff)
-                with open(box[0], "wb") as fh:
-                    fh.truncate(max(total, 4096))
+            if vfs.f_bavail * vfs.f_frsize >= total + (64 << 20):
+                # private to this user, never an existing file, and the pages RESERVED now: a sparse file on a short
+                # tmpfs would end in SIGBUS on first touch (or a partial cudaHostRegister) long after this check
+                name = "/dev/shm/orb200_frames_%d_%s" % (os.getpid(), os.urandom(8).hex())
+                try:
+                    fd = os.open(name, os.O_RDWR | os.O_CREAT | os.O_EXCL, 0o600)
+                    try:
+                        os.posix_fallocate(fd, 0, max(total, 4096))
+                        box[0] = name
+                    except OSError:  # ENOSPC: the same None answer on every rank below
+                        os.unlink(name)
+                    finally:
+                        os.close(fd)
+                except OSError:
+                    pass
         if world_size > 1:
             dist.broadcast_object_list(box, src=0, group=group)
         self.path = box[0]
@@ -234,12 +245,32 @@ class SharedHostFrames:
         return self.frames[name]
 
     def close(self):
+        """Unpins and unmaps.  Views handed out by [] must not be used afterwards."""
         if self._pinned:
             import torch
 
             for p in self._pinned:
                 torch.cuda.cudart().cudaHostUnregister(p)
             self._pinned = []
+        self.frames = {}
+        m, self._map = getattr(self, "_map", None), None
+        if m is not None and getattr(m, "_mmap", None) is not None:
+            try:
+                m._mmap.close()
+            except (BufferError, ValueError):  # a caller still holds a view: the mapping goes with its last reference
+                pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class TiledRenderer:

@@ -37,6 +37,31 @@ _ensure_built()
 import _oracle  # noqa: E402
 
 
+# oracle/_ref (the reference's own device source compiled here) is git-ignored: on a fresh clone without
+# /root/reference the strongest checker silently drops out.  Which kind each test got is printed in the session
+# summary, and ORB_REQUIRE_REF=1 turns every such skip / fall-back into a failure.
+_ORACLE_KINDS_USED = {}
+
+
+def _note(kind):
+    _ORACLE_KINDS_USED[kind] = _ORACLE_KINDS_USED.get(kind, 0) + 1
+
+
+def _ref_or_skip(kind):
+    if not _oracle.available(kind):
+        if os.environ.get("ORB_REQUIRE_REF") == "1":
+            pytest.fail("ORB_REQUIRE_REF=1 and oracle/_ref (%s) is not built" % kind)
+        _note("skipped: " + kind)
+        pytest.skip("oracle/_ref not built (reference absent)")
+    _note(kind)
+    return _oracle.Oracle(kind)
+
+
+def pytest_terminal_summary(terminalreporter):
+    if _ORACLE_KINDS_USED:
+        terminalreporter.write_line("oracle kinds used: " + ", ".join("%s x%d" % kv for kv in sorted(_ORACLE_KINDS_USED.items())))
+
+
 @pytest.fixture(scope="session")
 def restatement():
     return _oracle.Oracle("restatement")
@@ -44,22 +69,23 @@ def restatement():
 
 @pytest.fixture(scope="session")
 def ref_literal():
-    if not _oracle.available("reference-literal"):
-        pytest.skip("oracle/_ref not built (reference absent)")
-    return _oracle.Oracle("reference-literal")
+    return _ref_or_skip("reference-literal")
 
 
 @pytest.fixture(scope="session")
 def ref_intended():
-    if not _oracle.available("reference-intended"):
-        pytest.skip("oracle/_ref not built (reference absent)")
-    return _oracle.Oracle("reference-intended")
+    return _ref_or_skip("reference-intended")
 
 
 def best_oracle(mode):
     """The strongest checker available: the compiled reference TU, else the restatement."""
     kind = "reference-intended" if mode == 1 else "reference-literal"
-    return _oracle.Oracle(kind if _oracle.available(kind) else "restatement")
+    if not _oracle.available(kind):
+        if os.environ.get("ORB_REQUIRE_REF") == "1":
+            pytest.fail("ORB_REQUIRE_REF=1 and oracle/_ref (%s) is not built" % kind)
+        kind = "restatement"
+    _note(kind)
+    return _oracle.Oracle(kind)
 
 
 @pytest.fixture(scope="session")
