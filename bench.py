@@ -217,6 +217,18 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # The only collective of the job is the per-frame all-gather of the finished bands (20 - 40 MB), beside the next
+        # frames' kernels.  An NCCL kernel is a rendezvous: its CTAs spin until the peers' kernels arrive, and the
+        # ranks of a 6-deep frame pipeline drift apart -- with NCCL's default channel count the spinning CTAs took
+        # 0.2 - 0.4 ms per frame from the render kernels at N = 2 (1.36 ms without the gather, 1.72 - 1.78 with).
+        # Two channels move 40 MB per frame many times over.
+        # (one channel is too few: 1.87 ms, the ring of staging blocks backs up).  N = 8 gathers more bytes per frame
+        # (bands padded to the tallest) and keeps NCCL's own choice: not measured otherwise.
+        # N = 4: 0.927 ms per RATIO frame with 4 channels against 0.986 with NCCL's default (profiles/r2w_n4_*.json).
+        nch = os.environ.get("ORB_BENCH_NCCL_CHANNELS", "2" if world == 2 else ("4" if world <= 4 else ""))
+        if nch:
+            os.environ.setdefault("NCCL_MAX_NCHANNELS", nch)
+            os.environ.setdefault("NCCL_MIN_NCHANNELS", "1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ratio = args.workload == "ratio"
 
@@ -243,6 +255,7 @@ def run_ours(args):
     HALO = world > 1 and ratio and os.environ.get("ORB_BENCH_HALO", "1") == "1" and T.connect_halo()
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
 
+    NO_ASSEMBLE = os.environ.get("ORB_BENCH_NO_ASSEMBLE") == "1"
     SYNC_ASSEMBLE = bool(os.environ.get("ORB_BENCH_SYNC_ASSEMBLE"))  # A/B: gather in place on the render stream
     SYNC_DOWNLOAD = os.environ.get("ORB_BENCH_SYNC_DOWNLOAD", "0") == "1"  # A/B: blocking read-back every frame
 
@@ -256,6 +269,8 @@ def run_ours(args):
         # the finished band is handed to a side stream that all-gathers it while this stream renders the next
         # frame; T.join(stream) (before the closing event / before a read) orders `stream` behind the last gather
         render(i)
+        if NO_ASSEMBLE:  # diagnostic only (ORB_BENCH_NO_ASSEMBLE=1): what the frame assembly costs the pipeline
+            return
         if SYNC_ASSEMBLE:
             T.assemble(out_names)
         else:
@@ -317,6 +332,10 @@ def run_ours(args):
         # per-stage CUDA-event times, OUTSIDE the timed region: the same frames one at a time (a sync after each), so
         # the stages of two frames in flight do not overlap inside each other's event pairs
         P_FRAMES = max(3, min(10, args.steps))
+        # ... and with the persistent kernels' CTA cap lifted: the cap leaves room for the OTHER frames in flight; a
+        # kernel timed alone (the roofline's duration) runs on the whole SM
+        if "ORB_TRACE_CTAS_PER_SM" not in os.environ:
+            r.set_persistent_ctas_per_sm(0)
         r.set_profiling(True)
         r.stage_times()
         if world > 1:
@@ -328,6 +347,8 @@ def run_ours(args):
         coll_ms = T.span_ms() if world > 1 else {}
         T.spans = None
         r.set_profiling(False)
+        if "ORB_TRACE_CTAS_PER_SM" not in os.environ:
+            r.set_persistent_ctas_per_sm(CTA_CAP)
         st = {k: (t * args.steps / P_FRAMES, n * args.steps / P_FRAMES) for k, (t, n) in st.items()}  # per `steps` frames, as below
         coll_ms = {k: v * args.steps / P_FRAMES for k, v in coll_ms.items()}
         base_id += P_FRAMES
@@ -621,7 +642,7 @@ def run_ours(args):
                                    " on a copy stream, behind the all-gather and beside the next frame's kernels; the "
                                    "last copy is waited for inside the timed region"))},
                 "gpu_launches": int(launches), "frames_in_flight": SLOTS, "host_enqueue_ms_per_step": host_ms, "roofline": roofline, "passes": passes,
-                "passes_note": "per-stage CUDA-event times of %d extra frames run ONE AT A TIME after the timed region "
+                "persistent_ctas_per_sm": CTA_CAP, "passes_note": "per-stage CUDA-event times of %d extra frames run ONE AT A TIME (CTA cap lifted) after the timed region "
                                "(with %d frames in flight the stages of consecutive frames overlap, so their sum "
                                "exceeds ms_per_step)" % (P_FRAMES, SLOTS),
                 "clocks": clocks}
