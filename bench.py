@@ -161,8 +161,9 @@ def workload_config(args, n):
             "max_depth": DEPTH if args.workload == "path" else 1,
             "lut": "8x8 (reference ltc_isotropic.h)" if args.lut == 8 else "%dx%d (bilinear resampling of the reference table)" % (args.lut, args.lut),
             "partition": ("%d cost-balanced row bands, BVH replicated, packed denoise halo rows stored into the neighbours' "
-                          "buffers by the pack kernel (peer-mapped memory over NVLink, epoch flags), NCCL all-gather of the "
-                          "finished bands on a side stream beside the next frame" % n) if n > 1 else "single GPU",
+                          "buffers by the pack kernel (peer-mapped memory over NVLink, epoch flags), finished bands copied into every "
+                          "GPU's frame beside the next frames (one-sided copy-engine transfers, or an NCCL all-gather: this "
+                          "line's assembly key)" % n) if n > 1 else "single GPU",
             "frames_in_flight": "several per GPU (orb_set_frame_slots; the count is this line's frames_in_flight key): the "
                                 "next frames' kernels run beside a frame's traversal tail; accum / RGBA8 shared and "
                                 "accumulated in order",
@@ -254,6 +255,13 @@ def run_ours(args):
     T = tiles.TiledRenderer(r, rank, world, DN_ITERS)
     HALO = world > 1 and ratio and os.environ.get("ORB_BENCH_HALO", "1") == "1" and T.connect_halo()
     out_names = ["ratio_final", "rgba8"] if ratio else ["accum", "rgba8"]
+    # frame assembly: one-sided copies of the finished band into every peer's frame (orb_copy_rows_to_peer: copy engines,
+    # no rendezvous) instead of an NCCL all-gather; ORB_BENCH_PEER_ASSEMBLE=0 or a failed mapping keeps the all-gather
+    # (only with the e2e loop's per-rank host gather: a read-back of the ASSEMBLED frame right behind a frame would need
+    # a cross-rank wait for the peers' copies, which the all-gather gives and one-sided copies do not)
+    PEER_ASM = (world > 1 and os.environ.get("ORB_BENCH_PEER_ASSEMBLE", "1") == "1"
+                and not os.environ.get("ORB_BENCH_SYNC_ASSEMBLE") and os.environ.get("ORB_BENCH_SYNC_DOWNLOAD", "0") != "1"
+                and os.environ.get("ORB_BENCH_HOST_GATHER", "1") == "1" and T.connect_assembly(out_names))
 
     NO_ASSEMBLE = os.environ.get("ORB_BENCH_NO_ASSEMBLE") == "1"
     SYNC_ASSEMBLE = bool(os.environ.get("ORB_BENCH_SYNC_ASSEMBLE"))  # A/B: gather in place on the render stream
@@ -278,6 +286,7 @@ def run_ours(args):
 
     def barrier():
         r.sync()
+        torch.cuda.synchronize()  # this rank's copies into its peers' frames have landed before anyone passes the barrier
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -398,6 +407,8 @@ def run_ours(args):
                 if rank == 0:
                     print("bench.py: %s; e2e falls back to rank 0's read-back of the assembled frame" % e, file=sys.stderr)
                 HOST_GATHER = False
+                PEER_ASM = False
+                T._peer_asm, T._peer_names = None, ()  # rank 0 reads the gathered frame back: the all-gather again
 
         e2e_host = [None]
         e2e_host_parts = {"set_camera": 0.0, "render": 0.0, "assemble": 0.0, "read_back": 0.0, "final_wait": 0.0, "frames": 0}
@@ -655,6 +666,8 @@ def run_ours(args):
             line["e2e"]["host_gather"] = bool(HOST_GATHER)
             line["config"]["bands"] = [list(b) for b in T.bands]
             line["assembled_frame_equals_single_gpu_frame"] = same
+            line["assembly"] = ("orb_copy_rows_to_peer: every rank's band into every peer's frame by the copy engines over "
+                                "NVLink, no rendezvous") if PEER_ASM else "NCCL all_gather_into_tensor on a side stream"
             line["rank_kernel_ms_per_frame"] = rank_ms
             line["collectives_ms_per_frame_rank0"] = {k: v / args.steps for k, v in coll_ms.items()}
             line["halo"] = ("peer stores inside k_denoise_pack + epoch flags (orb_denoise_band); status %d" % r.halo_status()) if HALO \

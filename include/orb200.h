@@ -291,6 +291,17 @@ int orb_ratio_combine(OrbContext* ctx, int32_t use_denoised, int32_t y0, int32_t
 /* ---- buffers ---- replaces owlBufferGetPointer + cudaMemcpy, viewer.hpp:695-713 */
 size_t orb_buffer_bytes(OrbContext* ctx, int32_t buffer_id);
 void* orb_buffer_device_ptr(OrbContext* ctx, int32_t buffer_id);
+/* Buffer `buffer_id` of frame slot `slot` (ORB_BUF_ACCUM / ORB_BUF_RGBA8 are one buffer for every slot). */
+void* orb_slot_buffer_device_ptr(OrbContext* ctx, int32_t slot, int32_t buffer_id);
+/* One-sided frame assembly of a row-band partition (the reference has one GPU, viewer.hpp:177): rows [y0, y1) of the
+ * ACTIVE slot's buffer are copied into the same rows of a peer's buffer -- peer_buffer = that peer's
+ * orb_slot_buffer_device_ptr for the same slot and id, as it is (a context of this process) or through orb_ipc_export /
+ * orb_ipc_open (another process) -- by the copy engines over NVLink, on a stream of its own behind everything the
+ * slot has enqueued: no kernel, no rendezvous between ranks.  last != 0 closes the frame's batch of copies: the slot's
+ * stream waits for them, so orb_sync() covers them and later frames do not overwrite rows still being read.  After
+ * every rank's copies (a cross-rank barrier behind orb_sync) every rank's buffer holds the whole frame.  Pointers
+ * obtained before an orb_resize / orb_set_frame_slots of the peer are stale. */
+int orb_copy_rows_to_peer(OrbContext* ctx, int32_t buffer_id, void* peer_buffer, int32_t y0, int32_t y1, int32_t last);
 int orb_buffer_download(OrbContext* ctx, int32_t buffer_id, void* host_dst, size_t bytes);
 int orb_buffer_download_rows(OrbContext* ctx, int32_t buffer_id, void* host_dst, int32_t y0, int32_t y1);
 /* Pipelined read-back for an interactive loop (viewer.hpp:695-713 reads the frame back every frame): returns at

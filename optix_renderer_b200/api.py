@@ -149,6 +149,9 @@ def load_library():
     L.orb_buffer_bytes.restype = C.c_size_t
     L.orb_buffer_device_ptr.argtypes = [vp, C.c_int32]
     L.orb_buffer_device_ptr.restype = vp
+    L.orb_slot_buffer_device_ptr.argtypes = [vp, C.c_int32, C.c_int32]
+    L.orb_slot_buffer_device_ptr.restype = vp
+    L.orb_copy_rows_to_peer.argtypes = [vp, C.c_int32, vp, C.c_int32, C.c_int32, C.c_int32]
     L.orb_buffer_download.argtypes = [vp, C.c_int32, vp, C.c_size_t]
     L.orb_buffer_download_rows.argtypes = [vp, C.c_int32, vp, C.c_int32, C.c_int32]
     L.orb_buffer_download_rows_async.argtypes = [vp, C.c_int32, vp, C.c_int32, C.c_int32]
@@ -422,6 +425,15 @@ class Renderer:
 
     def buffer_bytes(self, name):
         return self.lib.orb_buffer_bytes(self._h, BUFFERS[name])
+
+    def slot_buffer_ptr(self, slot, name):
+        """Device pointer of buffer `name` of frame slot `slot` (accum / rgba8: one buffer for every slot)."""
+        return self.lib.orb_slot_buffer_device_ptr(self._h, int(slot), BUFFERS[name])
+
+    def copy_rows_to_peer(self, name, peer_ptr, rows, last=False):
+        """orb_copy_rows_to_peer: rows of the active slot's buffer into the same rows of a peer's buffer (copy engines,
+        behind the slot's kernels); last=True closes the frame's batch."""
+        self._ck(self.lib.orb_copy_rows_to_peer(self._h, BUFFERS[name], peer_ptr, int(rows[0]), int(rows[1]), int(bool(last))))
 
     def download(self, name, rows=None, out=None):
         bid = BUFFERS[name]

@@ -1346,6 +1346,8 @@ struct FrameSlot {
     cudaEvent_t pending_dl[8] = {};  // in-place read-backs of this slot's buffers the slot's next frame has to wait for
     int n_pending_dl = 0;
     cudaEvent_t ev_order = nullptr;  // "everything enqueued on this slot so far" for the other slot's k_accumulate
+    cudaEvent_t ev_peer_ready = nullptr, ev_peer_done = nullptr;  // orb_copy_rows_to_peer: the frame is finished / its copies have left
+    bool peer_batch_open = false;
     int last_spp = 0;
     bool rendered = false;           // a frame has been enqueued on this slot since the last resize
     uint32_t halo_epoch = 0;         // frames whose packed denoise rows this slot has pushed to its peers (halo.cuh)
@@ -1396,6 +1398,7 @@ struct OrbContext : FrameSlot {
     // in flight a full persistent grid would keep the other frame's CTAs out until it exits (ORB_TRACE_CTAS_PER_SM).
     int trace_ctas_per_sm = 0;
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t peer_stream = nullptr;  // orb_copy_rows_to_peer: copy-engine transfers of finished bands into the peers' frames
     int dl_snapshot_kernel = 1;
     int dl_inplace = 0;  // several frame slots: 1 = read per-slot buffers back in place instead of through a copy-engine snapshot (ORB_DL_INPLACE)
     int resolve_lanes = 1;  // RATIO resolve: one thread per (pixel, sample) for spp 2 / 4 / 8
@@ -1526,6 +1529,10 @@ static void destroy_slot(FrameSlot& f) {
         }
     if (f.ev_order) cudaEventDestroy(f.ev_order);
     f.ev_order = nullptr;
+    if (f.ev_peer_ready) cudaEventDestroy(f.ev_peer_ready);
+    if (f.ev_peer_done) cudaEventDestroy(f.ev_peer_done);
+    f.ev_peer_ready = f.ev_peer_done = nullptr;
+    f.peer_batch_open = false;
     if (f.own_stream && f.stream) cudaStreamDestroy(f.stream);
     f.stream = nullptr;
 }
@@ -1753,6 +1760,7 @@ void orb_destroy(OrbContext* c) {
     for (int k = 1; k < ORB_MAX_SLOTS; k++)
         if (c->parked[k].stream) cudaStreamSynchronize(c->parked[k].stream);
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->peer_stream) { cudaStreamSynchronize(c->peer_stream); cudaStreamDestroy(c->peer_stream); }
     halo_disconnect(c->halo);
     cudaFree(c->halo.flags);
     free_scene(c);
@@ -2775,6 +2783,44 @@ size_t orb_buffer_bytes(OrbContext* c, int32_t id) {
 void* orb_buffer_device_ptr(OrbContext* c, int32_t id) {
     if (!c || id < 0 || id >= ORB_BUF_COUNT) return nullptr;
     return c->buf[id];
+}
+
+void* orb_slot_buffer_device_ptr(OrbContext* c, int32_t slot, int32_t id) {
+    if (!c || id < 0 || id >= ORB_BUF_COUNT || slot < 0 || slot >= c->n_slots) return nullptr;
+    return slot_ref(c, slot).buf[id];
+}
+
+// One-sided frame assembly of a row-band partition: rows [y0, y1) of the active slot's buffer go into the same rows of
+// a PEER's buffer (a pointer valid in this process: another context's orb_slot_buffer_device_ptr, or orb_ipc_open of
+// its exported handle) -- cudaMemcpyAsync over NVLink on the context's peer-copy stream, behind everything the slot
+// has enqueued.  No kernel and no rendezvous: an NCCL all-gather is a kernel whose CTAs spin until every peer's
+// kernel has arrived, and the ranks of a deep frame pipeline are frames apart (bench.py: 0.2 - 0.4 ms per frame at
+// N = 2).  `last` closes the frame's batch: the slot's stream then waits for the copies, so the slot's next frame and
+// (through the accumulate ordering) the next frame's writes to the shared ACCUM / RGBA8 rows come after them.
+int orb_copy_rows_to_peer(OrbContext* c, int32_t id, void* peer_buffer, int32_t y0, int32_t y1, int32_t last) {
+    NEED(c && peer_buffer && id >= 0 && id < ORB_BUF_COUNT, "orb_copy_rows_to_peer: bad argument");
+    NEED(c->W > 0 && y0 >= 0 && y0 <= y1 && y1 <= c->H, "orb_copy_rows_to_peer: bad row range");
+    CK(cudaSetDevice(c->device));
+    if (!c->peer_stream) CK(cudaStreamCreateWithFlags(&c->peer_stream, cudaStreamNonBlocking));
+    if (!c->ev_peer_ready) {
+        CK(cudaEventCreateWithFlags(&c->ev_peer_ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->ev_peer_done, cudaEventDisableTiming));
+    }
+    if (!c->peer_batch_open) {
+        CK(cudaEventRecord(c->ev_peer_ready, c->stream));
+        CK(cudaStreamWaitEvent(c->peer_stream, c->ev_peer_ready, 0));
+        c->peer_batch_open = true;
+    }
+    const size_t row = (size_t)c->W * buffer_elem_bytes(id);
+    if (y1 > y0)
+        CK(cudaMemcpyAsync((char*)peer_buffer + row * y0, (const char*)c->buf[id] + row * y0, row * (size_t)(y1 - y0),
+                           cudaMemcpyDefault, c->peer_stream));
+    if (last) {
+        CK(cudaEventRecord(c->ev_peer_done, c->peer_stream));
+        CK(cudaStreamWaitEvent(c->stream, c->ev_peer_done, 0));
+        c->peer_batch_open = false;
+    }
+    return ORB_OK;
 }
 
 int orb_buffer_download(OrbContext* c, int32_t id, void* dst, size_t bytes) {

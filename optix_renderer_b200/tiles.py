@@ -297,6 +297,7 @@ class TiledRenderer:
         self._stage_key, self._stage_in, self._stage_all, self._stage_meta, self._done_bands = None, None, None, {}, None
         self._comm = None  # side stream the frame assembly runs on, beside the next frame's kernels
         self._ring, self._ring_i, self._cur_ent = [], -1, None
+        self._peer_asm, self._peer_names = None, ()  # connect_assembly(): (peer, slot, name) -> mapped pointer
         self._done = None
         self._copy = None  # stream the assembled frame is read back to the host on (read_back_async)
         self._read = None
@@ -364,6 +365,45 @@ class TiledRenderer:
         self.halo = True
         return True
 
+    def connect_assembly(self, names):
+        """One-sided frame assembly (orb_copy_rows_to_peer): map every other rank's buffers `names` of every frame slot
+        into this process, so that assemble_async() copies this rank's finished band straight into the peers' frames
+        with the copy engines -- no NCCL kernel, no rendezvous.  All ranks must call it, after set_frame_slots /
+        resize.  Returns False (and assemble_async keeps the NCCL all-gather) if any rank failed to map a peer."""
+        if self.world == 1:
+            return False
+        import torch.distributed as dist
+
+        slots = self.r.frame_slots
+        mine, seen = {}, {}
+        for k in range(slots):
+            for n in names:
+                ptr = self.r.slot_buffer_ptr(k, n)
+                if ptr not in seen:  # accum / rgba8 are one buffer for every slot: one handle, opened once
+                    seen[ptr] = self.r.ipc_export(ptr)
+                mine[(k, n)] = seen[ptr]
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        table, ok = {}, True
+        try:
+            for q, theirs in enumerate(everyone):
+                if q == self.rank:
+                    continue
+                opened = {}
+                for (k, n), h in sorted(theirs.items()):
+                    if h not in opened:
+                        opened[h] = self.r.ipc_open(h)
+                        self._ipc.append(opened[h])
+                    table[(q, k, n)] = opened[h]
+        except Exception:  # noqa: BLE001 -- any failure: every rank falls back together
+            ok = False
+        oks = [None] * self.world
+        dist.all_gather_object(oks, ok, group=self.group)
+        if not all(oks):
+            return False
+        self._peer_asm, self._peer_names = table, tuple(names)
+        return True
+
     def disconnect_halo(self):
         if not self.halo:
             return
@@ -375,6 +415,7 @@ class TiledRenderer:
         for p in self._ipc:
             self.r.ipc_close(p)
         self._ipc = []
+        self._peer_asm, self._peer_names = None, ()  # its mappings were in the same list
         self.halo = False
 
     def _band_plan(self):
@@ -505,6 +546,19 @@ class TiledRenderer:
         import torch
         import torch.distributed as dist
 
+        if self._peer_asm is not None and tuple(names) == self._peer_names:
+            # one-sided: this rank's band into every peer's frame of the same slot, by the copy engines, behind the
+            # slot's kernels.  join() / orb_sync cover the copies (the slot's stream waits for them); the frame is
+            # whole on every rank once all ranks have synchronised (a barrier).
+            y0, y1 = self.band
+            k = self.r.frame_slot
+            if y1 > y0:
+                ops = [(n, self._peer_asm[(q, k, n)]) for q in range(self.world) if q != self.rank for n in names]
+                for i, (n, ptr) in enumerate(ops):
+                    self.r.copy_rows_to_peer(n, ptr, (y0, y1), last=(i == len(ops) - 1))
+            self._done = None
+            self._done_bands = list(self.bands)
+            return
         cur = self.slot_stream()
         if self._comm is None:
             # high priority: the gather's CTAs go ahead of the queued CTAs of the frames in flight, whose persistent
@@ -559,6 +613,11 @@ class TiledRenderer:
         import torch
 
         st = stream or self.slot_stream()
+        if self._peer_asm is not None and name in self._peer_names:
+            # the peers stored their bands into this rank's own buffer of the frame's slot (valid once every rank has
+            # synchronised behind its copies)
+            with torch.cuda.stream(st):
+                return self._t(name).clone()
         o, rb, dt, shp = self._stage_meta[name]
         with torch.cuda.stream(st):
             if self._done is not None:

@@ -789,6 +789,53 @@ def test_band_handoff_through_peer_stores(renderer_factory, slots):
         ranks[0].denoise_band(bands[0], [], [])
 
 
+def test_one_sided_frame_assembly(renderer_factory):
+    """orb_copy_rows_to_peer: three contexts of ONE process play the ranks of a row-band partition with two frame slots;
+    every rank copies its finished band of ratio_final (per slot) and rgba8 (shared by the slots) into the other two
+    ranks' buffers.  After a sync every rank holds the whole frame: equal to the frame one context renders whole,
+    bit for bit, for several frames in a row."""
+    W, H, slots = 96, 120, 2
+    sc = scenes.scene_cornell(W, H)
+    bands = [(0, 50), (50, 58), (58, 120)]
+    ranks = [renderer_factory(sc) for _ in bands]
+    for r in ranks:
+        r.set_frame_slots(slots)
+        r.set_fused_combine(True)
+    whole = renderer_factory(sc)
+    for frame in range(5):
+        whole.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4)
+        whole.denoise(iterations=2)
+        whole.ratio_combine(use_denoised=True)
+        want = whole.download("ratio_final")
+        want_u = whole.download("rgba8")
+        wrote = (whole.download("normal")[..., :3] != 0).any(-1)
+        for i, r in enumerate(ranks):
+            r.render(api.RATIO, accum_id=frame, mode=1, shadow_spp=4, rows=bands[i], sync=False)
+        for i, r in enumerate(ranks):   # the packed rows of every band first: a band's filter reads its neighbours' rows
+            r.denoise_pack(rows=bands[i])
+        packed = [(r.download("dn_guide"), r.download("dn_val")) for r in ranks]
+        for i, r in enumerate(ranks):
+            g, v = packed[i][0].copy(), packed[i][1].copy()
+            for j, (a, b) in enumerate(bands):
+                g[a:b], v[a:b] = packed[j][0][a:b], packed[j][1][a:b]
+            r.upload("dn_guide", g)
+            r.upload("dn_val", v)
+            r.denoise_filter(iterations=2, rows=bands[i])
+            k = r.frame_slot
+            ops = [(n, ranks[j].slot_buffer_ptr(k, n)) for j in range(len(ranks)) if j != i for n in ("ratio_final", "rgba8")]
+            for q, (n, ptr) in enumerate(ops):
+                r.copy_rows_to_peer(n, ptr, bands[i], last=(q == len(ops) - 1))
+        for r in ranks:
+            r.sync()
+        for i, r in enumerate(ranks):
+            assert r.frame_slot == (frame + 1) % slots
+            got = r.download("ratio_final")
+            assert np.array_equal(got[wrote], want[wrote], equal_nan=True), (frame, i)
+            assert np.array_equal(r.download("rgba8"), want_u), (frame, i)
+    with pytest.raises(api.OrbError, match="bad row range"):
+        ranks[0].copy_rows_to_peer("ratio_final", ranks[1].slot_buffer_ptr(0, "ratio_final"), (10, H + 1))
+
+
 def test_checked_render_counts_ties_and_near_decisions(renderer_factory, restatement):
     """ORB_RENDER_CHECKED: OrbCounters.hit_ties = primary hits within 1e-5 (barycentric) of a triangle edge -- the
     pixels where another ray/triangle test may report the neighbouring triangle -- and OrbCounters.ltc_near_decision
