@@ -1,6 +1,6 @@
 // image_io.cpp -- texture files for `map_Kd`: what the reference reads through stb_image
 // (src/Model.cpp:81-128: stbi_load(..., STBI_rgb_alpha), then mirrored along y) -- PNG (all colour types, 8 / 16 bit,
-// non-interlaced; zlib inflates the IDAT stream), TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
+// non-interlaced; zlib inflates the IDAT stream), baseline JPEG, TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
 // Output: RGBA8, BOTTOM row first (the reference's mirror), as orb_scene_add_mesh takes it.
 // Own code: stb_image is a third-party library the reference vendors; only its observable result is matched
 // (grey -> (g,g,g,255), palette + tRNS -> RGBA, 16-bit samples keep their high byte).
@@ -178,6 +178,400 @@ bool load_tga(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) 
     return true;
 }
 
+
+// ---- JPEG: baseline / extended sequential Huffman (SOF0 / SOF1), 8-bit, grey or YCbCr (RGB when an Adobe marker says
+// so), any sampling factors, restart intervals.  Progressive and arithmetic-coded files are refused (the caller
+// prints what is read).  A JPEG's texels are not defined bit for bit by the format: what the reference gets is what
+// ITS decoder makes of the file, so the three places where decoders differ follow stb_image's choices -- a 12-bit
+// fixed-point "islow" inverse DCT (two extra bits kept between the passes), triangle-filtered chroma upsampling for
+// 2x1 / 1x2 / 2x2 sampling (replication otherwise), and a 20-bit fixed-point YCbCr -> RGB.
+struct JpegHuff {
+    uint8_t size[257];
+    uint16_t code[256];
+    uint8_t value[256];
+    int maxcode[18];  // left-aligned to 16 bits, exclusive
+    int delta[17];
+    int n = 0;
+    bool build(const unsigned char* counts, const unsigned char* vals) {
+        int k = 0;
+        for (int len = 1; len <= 16; len++)
+            for (int i = 0; i < counts[len - 1]; i++) {
+                if (k >= 256) return false;
+                size[k++] = (uint8_t)len;
+            }
+        size[k] = 0;
+        n = k;
+        memcpy(value, vals, (size_t)k);
+        int c = 0;
+        k = 0;
+        for (int len = 1; len <= 16; len++) {
+            delta[len] = k - c;
+            if (size[k] == len) {
+                while (size[k] == len) code[k++] = (uint16_t)c++;
+                if (c - 1 >= (1 << len)) return false;
+            }
+            maxcode[len] = c << (16 - len);
+            c <<= 1;
+        }
+        maxcode[17] = 0x7fffffff;
+        return true;
+    }
+};
+
+struct JpegBits {
+    const unsigned char* d;
+    size_t p, end;
+    uint32_t acc = 0;
+    int n = 0;
+    bool hit_marker = false;
+    void fill() {
+        while (n <= 24) {
+            int b = 0;
+            if (!hit_marker && p < end) {
+                b = d[p];
+                if (b == 0xff) {
+                    const int m = p + 1 < end ? d[p + 1] : 0xd9;
+                    if (m == 0) p += 2;           // stuffed zero
+                    else { hit_marker = true; b = 0; }  // a marker ends the entropy segment: feed zeros
+                } else {
+                    p++;
+                }
+            }
+            acc |= (uint32_t)b << (24 - n);
+            n += 8;
+        }
+    }
+    int get(int k) {  // k bits, MSB first
+        if (k == 0) return 0;
+        if (n < k) fill();
+        const int v = (int)(acc >> (32 - k));
+        acc <<= k;
+        n -= k;
+        return v;
+    }
+    int decode(const JpegHuff& h) {
+        if (n < 16) fill();
+        const int top = (int)(acc >> 16);
+        int len = 1;
+        while (len <= 16 && top >= h.maxcode[len]) len++;
+        if (len > 16) return -1;
+        const int c = (top >> (16 - len)) + h.delta[len];
+        if (c < 0 || c >= h.n) return -1;
+        acc <<= len;
+        n -= len;
+        return h.value[c];
+    }
+    static int extend(int v, int bits) { return bits && v < (1 << (bits - 1)) ? v - (1 << bits) + 1 : v; }
+    void reset() { acc = 0; n = 0; hit_marker = false; }
+};
+
+// one dimension of the inverse DCT on eight values `s`, 12-bit constants; even part in x[0..3], odd part in t[0..3]
+inline void jpeg_idct_1d(const int* s, int stride, int x[4], int t[4]) {
+    auto F = [](double v) { return (int)(v * 4096 + 0.5); };
+    int p2 = s[2 * stride], p3 = s[6 * stride];
+    int p1 = (p2 + p3) * F(0.5411961);
+    const int e2 = p1 + p3 * F(-1.847759065), e3 = p1 + p2 * F(0.765366865);
+    p2 = s[0];
+    p3 = s[4 * stride];
+    const int e0 = (p2 + p3) * 4096, e1 = (p2 - p3) * 4096;
+    x[0] = e0 + e3;
+    x[3] = e0 - e3;
+    x[1] = e1 + e2;
+    x[2] = e1 - e2;
+    int t0 = s[7 * stride], t1 = s[5 * stride], t2 = s[3 * stride], t3 = s[1 * stride];
+    p3 = t0 + t2;
+    int p4 = t1 + t3;
+    p1 = t0 + t3;
+    p2 = t1 + t2;
+    const int p5 = (p3 + p4) * F(1.175875602);
+    t0 *= F(0.298631336);
+    t1 *= F(2.053119869);
+    t2 *= F(3.072711026);
+    t3 *= F(1.501321110);
+    p1 = p5 + p1 * F(-0.899976223);
+    p2 = p5 + p2 * F(-2.562915447);
+    p3 *= F(-1.961570560);
+    p4 *= F(-0.390180644);
+    t[3] = t3 + p1 + p4;
+    t[2] = t2 + p2 + p3;
+    t[1] = t1 + p2 + p4;
+    t[0] = t0 + p1 + p3;
+}
+
+inline uint8_t clamp8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+
+void jpeg_idct_block(const short* coef, uint8_t* out, int out_stride) {
+    int mid[64];
+    for (int c = 0; c < 8; c++) {  // columns
+        const short* d = coef + c;
+        int col[8];
+        bool ac = false;
+        for (int r = 0; r < 8; r++) {
+            col[r] = d[8 * r];
+            ac = ac || (r && col[r]);
+        }
+        if (!ac) {
+            for (int r = 0; r < 8; r++) mid[8 * r + c] = col[0] * 4;
+            continue;
+        }
+        int x[4], t[4];
+        jpeg_idct_1d(col, 1, x, t);
+        for (int k = 0; k < 4; k++) {
+            const int e = x[k] + 512;
+            mid[8 * k + c] = (e + t[3 - k]) >> 10;
+            mid[8 * (7 - k) + c] = (e - t[3 - k]) >> 10;
+        }
+    }
+    for (int r = 0; r < 8; r++) {  // rows; +128 and the rounding of the final >> 17 folded into the even part
+        int x[4], t[4];
+        jpeg_idct_1d(mid + 8 * r, 1, x, t);
+        uint8_t* o = out + (size_t)r * out_stride;
+        for (int k = 0; k < 4; k++) {
+            const int e = x[k] + 65536 + (128 << 17);
+            o[k] = clamp8((e + t[3 - k]) >> 17);
+            o[7 - k] = clamp8((e - t[3 - k]) >> 17);
+        }
+    }
+}
+
+bool load_jpeg(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) {
+    static const unsigned char zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                             41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                             30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+    const unsigned char* d = (const unsigned char*)s.data();
+    const size_t n = s.size();
+    if (n < 4 || d[0] != 0xff || d[1] != 0xd8) return false;
+    struct Comp {
+        int id = 0, hs = 1, vs = 1, tq = 0, td = 0, ta = 0, dc = 0;
+        int bw = 0, bh = 0;  // blocks across / down, padded to whole MCUs
+        int cw = 0, ch = 0;  // true size in samples
+        std::vector<uint8_t> px;
+    } comp[3];
+    uint16_t qt[4][64] = {};
+    bool have_qt[4] = {};
+    JpegHuff hdc[4], hac[4];
+    bool have_dc[4] = {}, have_ac[4] = {};
+    int ncomp = 0, restart = 0, adobe_transform = -1;
+    int hmax = 1, vmax = 1, mcux = 0, mcuy = 0;
+    bool have_frame = false;
+    size_t p = 2;
+    w = h = 0;
+    while (p + 4 <= n) {
+        if (d[p] != 0xff) return false;
+        while (p < n && d[p] == 0xff) p++;  // fill bytes
+        if (p >= n) return false;
+        const int m = d[p++];
+        if (m == 0xd9) break;
+        if (m == 0x01 || (m >= 0xd0 && m <= 0xd7)) continue;
+        if (p + 2 > n) return false;
+        const size_t len = ((size_t)d[p] << 8) | d[p + 1];
+        if (len < 2 || p + len > n) return false;
+        const unsigned char* b = d + p + 2;
+        const size_t bl = len - 2;
+        if (m == 0xdb) {  // DQT
+            size_t o = 0;
+            while (o < bl) {
+                const int pq = b[o] >> 4, t = b[o] & 15;
+                o++;
+                if (t > 3 || o + (pq ? 128 : 64) > bl) return false;
+                for (int i = 0; i < 64; i++, o += pq ? 2 : 1) qt[t][zigzag[i]] = pq ? (uint16_t)((b[o] << 8) | b[o + 1]) : b[o];
+                have_qt[t] = true;
+            }
+        } else if (m == 0xc4) {  // DHT
+            size_t o = 0;
+            while (o + 17 <= bl) {
+                const int tc = b[o] >> 4, t = b[o] & 15;
+                if (tc > 1 || t > 3) return false;
+                int total = 0;
+                for (int i = 0; i < 16; i++) total += b[o + 1 + i];
+                if (total > 256 || o + 17 + (size_t)total > bl) return false;
+                JpegHuff& hf = tc ? hac[t] : hdc[t];
+                if (!hf.build(b + o + 1, b + o + 17)) return false;
+                (tc ? have_ac : have_dc)[t] = true;
+                o += 17 + (size_t)total;
+            }
+        } else if (m == 0xc0 || m == 0xc1) {  // SOF0 / SOF1
+            if (bl < 6 || b[0] != 8) return false;
+            h = (b[1] << 8) | b[2];
+            w = (b[3] << 8) | b[4];
+            ncomp = b[5];
+            if ((ncomp != 1 && ncomp != 3) || w <= 0 || h <= 0 || bl < 6 + 3 * (size_t)ncomp) return false;
+            for (int i = 0; i < ncomp; i++) {
+                comp[i].id = b[6 + 3 * i];
+                comp[i].hs = b[7 + 3 * i] >> 4;
+                comp[i].vs = b[7 + 3 * i] & 15;
+                comp[i].tq = b[8 + 3 * i];
+                if (comp[i].hs < 1 || comp[i].hs > 4 || comp[i].vs < 1 || comp[i].vs > 4 || comp[i].tq > 3) return false;
+                hmax = comp[i].hs > hmax ? comp[i].hs : hmax;
+                vmax = comp[i].vs > vmax ? comp[i].vs : vmax;
+            }
+            have_frame = true;
+        } else if (m == 0xc2 || (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc)) {
+            return false;  // progressive, lossless, arithmetic coding
+        } else if (m == 0xdd) {
+            if (bl < 2) return false;
+            restart = (b[0] << 8) | b[1];
+        } else if (m == 0xee && bl >= 12 && !memcmp(b, "Adobe", 5)) {
+            adobe_transform = b[11];
+        } else if (m == 0xda) {  // SOS: one interleaved scan over all components
+            if (!have_frame || bl < 1 || b[0] != ncomp || bl < 1 + 2 * (size_t)ncomp + 3) return false;
+            for (int i = 0; i < ncomp; i++) {
+                int k = 0;
+                while (k < ncomp && comp[k].id != b[1 + 2 * i]) k++;
+                if (k != i) return false;  // scan order = frame order (what every encoder writes)
+                comp[i].td = b[2 + 2 * i] >> 4;
+                comp[i].ta = b[2 + 2 * i] & 15;
+                if (comp[i].td > 3 || comp[i].ta > 3 || !have_dc[comp[i].td] || !have_ac[comp[i].ta] || !have_qt[comp[i].tq]) return false;
+            }
+            mcux = (w + 8 * hmax - 1) / (8 * hmax);
+            mcuy = (h + 8 * vmax - 1) / (8 * vmax);
+            for (int i = 0; i < ncomp; i++) {
+                Comp& c = comp[i];
+                if (ncomp == 1) c.hs = c.vs = 1;  // a single-component scan is not interleaved: 8x8 blocks in raster order
+                c.bw = mcux * c.hs;
+                c.bh = mcuy * c.vs;
+                c.cw = (w * c.hs + hmax - 1) / hmax;
+                c.ch = (h * c.vs + vmax - 1) / vmax;
+                c.px.assign((size_t)64 * c.bw * c.bh, 0);
+                c.dc = 0;
+            }
+            if (ncomp == 1) {
+                hmax = vmax = 1;
+                mcux = (w + 7) / 8;
+                mcuy = (h + 7) / 8;
+                comp[0].bw = mcux;
+                comp[0].bh = mcuy;
+                comp[0].cw = w;
+                comp[0].ch = h;
+                comp[0].px.assign((size_t)64 * mcux * mcuy, 0);
+            }
+            JpegBits br{d, p + len, n};
+            int todo = restart;
+            for (int my = 0; my < mcuy; my++)
+                for (int mx = 0; mx < mcux; mx++) {
+                    for (int i = 0; i < ncomp; i++) {
+                        Comp& c = comp[i];
+                        for (int by = 0; by < c.vs; by++)
+                            for (int bx = 0; bx < c.hs; bx++) {
+                                short coef[64] = {};
+                                const int tdc = br.decode(hdc[c.td]);
+                                if (tdc < 0 || tdc > 15) return false;
+                                c.dc += JpegBits::extend(br.get(tdc), tdc);
+                                coef[0] = (short)(c.dc * qt[c.tq][0]);
+                                for (int k = 1; k < 64;) {
+                                    const int rs = br.decode(hac[c.ta]);
+                                    if (rs < 0) return false;
+                                    const int run = rs >> 4, sz = rs & 15;
+                                    if (sz == 0) {
+                                        if (run != 15) break;  // end of block
+                                        k += 16;
+                                        continue;
+                                    }
+                                    k += run;
+                                    if (k > 63) return false;
+                                    coef[zigzag[k]] = (short)(JpegBits::extend(br.get(sz), sz) * qt[c.tq][zigzag[k]]);
+                                    k++;
+                                }
+                                const size_t stride = (size_t)8 * c.bw;
+                                jpeg_idct_block(coef, &c.px[((size_t)(my * c.vs + by) * 8) * stride + (size_t)(mx * c.hs + bx) * 8], (int)stride);
+                            }
+                    }
+                    if (restart && --todo == 0 && !(my == mcuy - 1 && mx == mcux - 1)) {
+                        // the next marker must be RSTn: byte-align, skip it, reset the predictors
+                        size_t q = br.p;
+                        while (q + 1 < n && !(d[q] == 0xff && d[q + 1] >= 0xd0 && d[q + 1] <= 0xd7)) q++;
+                        if (q + 1 >= n) return false;
+                        br.p = q + 2;
+                        br.reset();
+                        for (int i = 0; i < ncomp; i++) comp[i].dc = 0;
+                        todo = restart;
+                    }
+                }
+            // ---- samples -> RGBA rows (top-down), written bottom row first
+            rgba.assign((size_t)4 * w * h, 255);
+            std::vector<uint8_t> line[3], row((size_t)4 * w);
+            for (int i = 0; i < ncomp; i++) line[i].assign((size_t)(comp[i].bw * 8) * (hmax / 1) + 16, 0);
+            const bool to_rgb = ncomp == 3 && adobe_transform != 0;
+            for (int y = 0; y < h; y++) {
+                const uint8_t* src[3] = {nullptr, nullptr, nullptr};
+                for (int i = 0; i < ncomp; i++) {
+                    const Comp& c = comp[i];
+                    const size_t stride = (size_t)8 * c.bw;
+                    const int fh = hmax / c.hs, fv = vmax / c.vs;  // upsampling factors (whole numbers for every real file)
+                    if (hmax % c.hs || vmax % c.vs) return false;
+                    const int wl = (w + fh - 1) / fh;  // low-resolution samples across
+                    int near = y / fv, far = near;
+                    if (fv == 2) far = (y & 1) ? near + 1 : near - 1;
+                    near = near < 0 ? 0 : (near > c.ch - 1 ? c.ch - 1 : near);
+                    far = far < 0 ? 0 : (far > c.ch - 1 ? c.ch - 1 : far);
+                    const uint8_t* a = &c.px[(size_t)near * stride];
+                    const uint8_t* f = &c.px[(size_t)far * stride];
+                    uint8_t* o = line[i].data();
+                    if (fh == 1 && fv == 1) {
+                        src[i] = a;
+                        continue;
+                    } else if (fh == 1 && fv == 2) {
+                        for (int x = 0; x < wl; x++) o[x] = (uint8_t)((3 * a[x] + f[x] + 2) >> 2);
+                    } else if (fh == 2 && fv == 1) {
+                        if (wl == 1) {
+                            o[0] = o[1] = a[0];
+                        } else {
+                            o[0] = a[0];
+                            o[1] = (uint8_t)((a[0] * 3 + a[1] + 2) >> 2);
+                            int x = 1;
+                            for (; x < wl - 1; x++) {
+                                const int t = 3 * a[x] + 2;
+                                o[2 * x] = (uint8_t)((t + a[x - 1]) >> 2);
+                                o[2 * x + 1] = (uint8_t)((t + a[x + 1]) >> 2);
+                            }
+                            o[2 * x] = (uint8_t)((a[wl - 2] * 3 + a[wl - 1] + 2) >> 2);
+                            o[2 * x + 1] = a[wl - 1];
+                        }
+                    } else if (fh == 2 && fv == 2) {
+                        int t1 = 3 * a[0] + f[0];
+                        if (wl == 1) {
+                            o[0] = o[1] = (uint8_t)((t1 + 2) >> 2);
+                        } else {
+                            o[0] = (uint8_t)((t1 + 2) >> 2);
+                            for (int x = 1; x < wl; x++) {
+                                const int t0 = t1;
+                                t1 = 3 * a[x] + f[x];
+                                o[2 * x - 1] = (uint8_t)((3 * t0 + t1 + 8) >> 4);
+                                o[2 * x] = (uint8_t)((3 * t1 + t0 + 8) >> 4);
+                            }
+                            o[2 * wl - 1] = (uint8_t)((t1 + 2) >> 2);
+                        }
+                    } else {  // any other ratio: nearest sample
+                        for (int x = 0; x < wl; x++)
+                            for (int k = 0; k < fh; k++) o[x * fh + k] = a[x];
+                    }
+                    src[i] = o;
+                }
+                for (int x = 0; x < w; x++) {
+                    uint8_t* o = &row[4 * (size_t)x];
+                    if (ncomp == 1) {
+                        o[0] = o[1] = o[2] = src[0][x];
+                    } else if (!to_rgb) {
+                        o[0] = src[0][x], o[1] = src[1][x], o[2] = src[2][x];
+                    } else {
+                        auto FX = [](double v) { return ((int)(v * 4096.0 + 0.5)) << 8; };
+                        const int yf = (src[0][x] << 20) + (1 << 19), cb = src[1][x] - 128, cr = src[2][x] - 128;
+                        const int r = yf + cr * FX(1.40200);
+                        const int g = yf + cr * -FX(0.71414) + (int)((unsigned)(cb * -FX(0.34414)) & 0xffff0000u);
+                        const int bl2 = yf + cb * FX(1.77200);
+                        o[0] = clamp8(r >> 20), o[1] = clamp8(g >> 20), o[2] = clamp8(bl2 >> 20);
+                    }
+                    o[3] = 255;
+                }
+                put_flipped(rgba, w, h, y, row.data());
+            }
+            return true;
+        }
+        p += len;
+    }
+    return false;
+}
+
 }  // namespace
 
 // RGBA8, bottom row first.  Formats by content (PNG signature, "P6"), TGA by its extension (it has no signature).
@@ -186,6 +580,7 @@ bool load_image_rgba8(const std::string& path, std::vector<uint8_t>& rgba, int& 
     if (!slurp(path, s) || s.size() < 4) return false;
     if ((unsigned char)s[0] == 0x89 && s[1] == 'P') return load_png(s, rgba, w, h);
     if (s[0] == 'P' && s[1] == '6') return load_ppm_rgba8(path, rgba, w, h);
+    if ((unsigned char)s[0] == 0xff && (unsigned char)s[1] == 0xd8) return load_jpeg(s, rgba, w, h);
     std::string ext = path.size() >= 4 ? path.substr(path.size() - 4) : "";
     for (auto& c : ext) c = (char)tolower((unsigned char)c);
     if (ext == ".tga") return load_tga(s, rgba, w, h);

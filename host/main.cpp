@@ -47,7 +47,8 @@ static void usage() {
             "  --exact-lut          fetch the table with exact fp32 bilinear weights instead of the texture unit's\n"
             "                       1/256 weights (the reference reads it through tex2D, viewer.hpp:321-327)\n"
             "  --device D           CUDA device (default 0)\n"
-            "  --dump-scene         print a JSON summary of the parsed scene and exit (no GPU needed)\n");
+            "  --dump-scene         print a JSON summary of the parsed scene and exit (no GPU needed)\n"
+            "  --dump-texels        --dump-scene plus the texels of small textures (<= 4096) as hex RGBA8\n");
 }
 
 static bool write_file(const std::string& path, const void* data, size_t bytes) {
@@ -185,7 +186,7 @@ static unsigned long long fnv1a(const void* p, size_t n, unsigned long long h = 
     return h;
 }
 
-static void dump_scene(const Scene& sc, int W, int H, int cam_i) {
+static void dump_scene(const Scene& sc, int W, int H, int cam_i, bool texels = false) {
     const std::vector<OrbTriLight> lights = build_tri_lights(sc);
     float pos[3], d00[3], du[3], dv[3];
     camera_vectors(sc.cameras[cam_i], W, H, pos, d00, du, dv);
@@ -196,11 +197,17 @@ static void dump_scene(const Scene& sc, int W, int H, int cam_i) {
         const Mesh& m = sc.meshes[i];
         printf("%s{\"triangles\": %zu, \"material_id\": %u, \"is_light\": %s, \"diffuse\": [%.9g, %.9g, %.9g], \"alpha\": %.9g, "
                "\"emit\": [%.9g, %.9g, %.9g], \"tex\": [%d, %d], \"tex_hash\": \"%016llx\", \"vertex_hash\": \"%016llx\", "
-               "\"normal_hash\": \"%016llx\", \"texcoord_hash\": \"%016llx\"}",
+               "\"normal_hash\": \"%016llx\", \"texcoord_hash\": \"%016llx\"",
                i ? ", " : "", m.index.size() / 3, m.material_id, m.is_light ? "true" : "false", m.diffuse[0], m.diffuse[1],
                m.diffuse[2], m.alpha, m.emit[0], m.emit[1], m.emit[2], m.tex_w, m.tex_h, fnv1a(m.tex.data(), m.tex.size()),
                fnv1a(m.vertex.data(), m.vertex.size() * 4), fnv1a(m.normal.data(), m.normal.size() * 4),
                fnv1a(m.texcoord.data(), m.texcoord.size() * 4));
+        if (texels && !m.tex.empty() && m.tex.size() <= 4 * 4096) {  // --dump-texels: small textures as hex RGBA8, bottom row first
+            printf(", \"texels\": \"");
+            for (unsigned char b : m.tex) printf("%02x", b);
+            printf("\"");
+        }
+        printf("}");
     }
     printf("], \"n_tri_lights\": %zu, \"tri_lights_hash\": \"%016llx\", \"camera\": {\"pos\": [%.9g, %.9g, %.9g], "
            "\"d00\": [%.9g, %.9g, %.9g], \"du\": [%.9g, %.9g, %.9g], \"dv\": [%.9g, %.9g, %.9g]}}\n",
@@ -219,7 +226,7 @@ static void dump_scene(const Scene& sc, int W, int H, int cam_i) {
 int main(int argc, char** argv) {
     std::string scene_file, out_dir = "saves", lut_path, renderer_arg, mode_arg = "intended";
     int frames = -1, W = 0, H = 0, cam_i = 0, shadow_spp = 4, depth = 8, device = 0;
-    bool denoise = false, only_dump = false;
+    bool denoise = false, only_dump = false, dump_texels = false;
     std::string save_state_path, resume_path;
     float move_lights[3] = {0.f, 0.f, 0.f};
     bool have_move = false;
@@ -264,6 +271,7 @@ int main(int argc, char** argv) {
         }
         else if (a == "--device") device = atoi(next("--device"));
         else if (a == "--dump-scene") only_dump = true;
+        else if (a == "--dump-texels") only_dump = dump_texels = true;
         else if (a == "-h" || a == "--help") { usage(); return 0; }
         else if (!a.empty() && a[0] != '-' && scene_file.empty()) scene_file = a;
         else { fprintf(stderr, "orb_render: unknown argument %s\n", a.c_str()); usage(); return 1; }
@@ -280,7 +288,7 @@ int main(int argc, char** argv) {
     }
     if (W == 0) { W = scene.width; H = scene.height; }
     if (cam_i < 0 || cam_i >= (int)scene.cameras.size()) { fprintf(stderr, "orb_render: no camera %d\n", cam_i); return 1; }
-    if (only_dump) { dump_scene(scene, W, H, cam_i); return 0; }
+    if (only_dump) { dump_scene(scene, W, H, cam_i, dump_texels); return 0; }
 
     int renderer = scene.renderers.empty() ? ORB_PATH : scene.renderers[0];
     if (!renderer_arg.empty()) {
