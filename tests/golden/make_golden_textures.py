@@ -4,7 +4,7 @@ steps (src/Model.cpp:99-118: stbi_load(..., STBI_rgb_alpha), then the mirror alo
 oracle/_ref/stb_decode (oracle/Makefile target ref_stb).  host/image_io.cpp is pinned against these bit for bit
 (tests/test_host.py::test_host_textures_equal_the_reference_decoder).
 
-Run in the build container (needs /root/reference and Pillow to WRITE the test files; the test itself needs neither):
+Run in the build container (needs /root/reference, and Pillow / OpenCV to WRITE the test files; the test itself needs neither):
     make -C oracle ref_stb && python tests/golden/make_golden_textures.py
 """
 import io
@@ -63,12 +63,14 @@ def main():
     jpeg("noise_420", rng.integers(0, 256, (24, 40, 3), dtype=np.uint8), quality=95, subsampling=2)  # clamping, large AC
     jpeg("grey_33x20", smooth(rng, 20, 33, 1)[..., 0], quality=90)
     jpeg("grey_9x9_rst", smooth(rng, 9, 9, 1)[..., 0], quality=60, restart_marker_blocks=1)
-    # 4:4:0 (luma 1x2) and 4:1:1 (luma 4x1): Pillow writes them from a "keep" of a re-encoded file only through its
-    # named modes; 4:1:1 is not offered, so the generic (replicating) path is pinned by the 1x2 file alone
-    try:
-        jpeg("c_440_20x30", smooth(rng, 30, 20, 3), quality=85, subsampling="4:4:0")
-    except (TypeError, ValueError, KeyError):
-        pass
+    # 4:4:0 (luma 1x2: the vertical-only filter) and 4:1:1 (luma 4x1: the replicating path) through OpenCV's encoder
+    import cv2
+
+    for tag, flag, (w, h) in (("440", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_440, (20, 30)), ("411", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_411, (41, 18)),
+                              ("440", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_440, (5, 9)), ("411", cv2.IMWRITE_JPEG_SAMPLING_FACTOR_411, (7, 3))):
+        ok, buf = cv2.imencode(".jpg", smooth(rng, h, w, 3), [cv2.IMWRITE_JPEG_QUALITY, 85, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, flag])
+        assert ok
+        files["cv_%s_%dx%d.jpg" % (tag, w, h)] = buf.tobytes()
     b = io.BytesIO()
     Image.fromarray(smooth(rng, 11, 13, 3)).save(b, format="PNG")
     files["rgb_13x11.png"] = b.getvalue()

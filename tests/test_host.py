@@ -232,7 +232,7 @@ def test_host_exr_writer(host, tmp_path):
 
 
 def test_host_textures_equal_the_reference_decoder(host, tmp_path):
-    """map_Kd through JPEG (4:4:4 / 4:2:2 / 4:2:0 / 4:4:0, grey, optimised Huffman tables, restart intervals, 1x1 and
+    """map_Kd through JPEG (4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1, grey, optimised Huffman tables, restart intervals, 1x1 and
     odd sizes), PNG and TGA: the texels the host hands to orb_scene_add_mesh equal, BIT FOR BIT, what the reference gets
     from the same file -- its vendored stb_image.h behind loadTexture's stbi_load + y mirror (src/Model.cpp:99-118),
     recorded in tests/golden/textures.npz by tests/golden/make_golden_textures.py.  A JPEG's texels are decoder
