@@ -202,3 +202,105 @@ def test_shared_host_frames_over_gloo(tmp_path, world, W, H):
     for slot in (0, 1):
         assert np.array_equal(got["f"][slot], _pattern(H, W, slot))
         assert np.array_equal(got["g"][slot], (_pattern(H, W, slot)[..., 0] * 7).astype(np.uint32))
+
+
+class _FakeRenderer:
+    """The part of api.Renderer that TiledRenderer's one-sided frame assembly uses, with file-backed arrays as the
+    "device" buffers: ipc_export hands out the file's path, ipc_open maps it, copy_rows_to_peer copies rows."""
+
+    def __init__(self, out_dir, rank, W, H, slots):
+        self.W, self.H, self.frame_slots, self.frame_slot = W, H, slots, 0
+        self.rank, self.dir = rank, out_dir
+        self._reg = {}          # "pointer" -> (path, array)
+        self._next = 0x1000
+        self._bufs = {}
+        self.copies = []        # (name, rows, last) in call order
+        for k in range(slots):
+            self._bufs[(k, "ratio_final")] = self._alloc("r%d_ratio_%d" % (rank, k), (H, W, 4), np.float32)
+        shared = self._alloc("r%d_rgba8" % rank, (H, W), np.uint32)   # one buffer for every slot
+        for k in range(slots):
+            self._bufs[(k, "rgba8")] = shared
+
+    def _alloc(self, tag, shape, dt):
+        path = os.path.join(self.dir, tag + ".bin")
+        a = np.lib.format.open_memmap(path, mode="w+", dtype=dt, shape=shape)
+        ptr = self._next
+        self._next += 0x1000
+        self._reg[ptr] = (path, a)
+        return ptr
+
+    def set_fused_combine(self, on):
+        pass
+
+    def slot_buffer_ptr(self, k, name):
+        return self._bufs[(k, name)]
+
+    def array(self, k, name):
+        return self._reg[self._bufs[(k, name)]][1]
+
+    def ipc_export(self, ptr):
+        return self._reg[ptr][0].encode().ljust(64, b"\0")[:64] if len(self._reg[ptr][0]) <= 64 else self._reg[ptr][0].encode()
+
+    def ipc_open(self, handle):
+        path = bytes(handle).rstrip(b"\0").decode()
+        assert all(path != p for p, _ in self._reg.values()), "a handle was opened twice (or is this rank's own)"
+        ptr = self._next
+        self._next += 0x1000
+        self._reg[ptr] = (path, np.load(path, mmap_mode="r+"))
+        return ptr
+
+    def copy_rows_to_peer(self, name, ptr, rows, last=False):
+        y0, y1 = rows
+        dst = self._reg[ptr][1]
+        dst[y0:y1] = self.array(self.frame_slot, name)[y0:y1]
+        dst.flush()
+        self.copies.append((name, (y0, y1), bool(last)))
+
+
+def _pat2(H, W, frame):
+    return np.arange(H * W, dtype=np.float32).reshape(H, W) + 1000.0 * frame
+
+
+def _peer_asm_worker(rank, world, port, W, H, slots, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        r = _FakeRenderer(out_dir, rank, W, H, slots)
+        T = tiles.TiledRenderer(r, rank, world)
+        T.bands = tiles.balanced_bands(np.arange(H) % 7 + 1.0, world)
+        names = ["ratio_final", "rgba8"]
+        assert T.connect_assembly(names)
+        res = {}
+        for frame in range(slots + 1):                       # every slot, and the first one a second time
+            r.frame_slot = (frame + 1) % slots
+            y0, y1 = T.band
+            r.array(r.frame_slot, "ratio_final")[y0:y1] = _pat2(H, W, frame)[y0:y1, :, None] + np.arange(4, dtype=np.float32)
+            r.array(r.frame_slot, "rgba8")[y0:y1] = _pat2(H, W, frame)[y0:y1].astype(np.uint32) + 7
+            n0 = len(r.copies)
+            T.assemble_async(names)
+            mine = r.copies[n0:]
+            assert len(mine) == 2 * (world - 1) and [c[2] for c in mine] == [False] * (len(mine) - 1) + [True]
+            assert all(c[1] == (y0, y1) for c in mine)
+            dist.barrier()                                   # every rank's copies have landed
+            res["ratio_%d" % frame] = np.array(r.array(r.frame_slot, "ratio_final"))
+            res["rgba8_%d" % frame] = np.array(r.array(r.frame_slot, "rgba8"))
+            dist.barrier()                                   # nobody writes the next frame before everyone has read
+        np.savez(os.path.join(out_dir, "rank%d.npz" % rank), **res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,W,H,slots", [(2, 12, 40, 2), (3, 8, 33, 3)])
+def test_one_sided_assembly_protocol_over_gloo(tmp_path, world, W, H, slots):
+    """TiledRenderer.connect_assembly / assemble_async (the orb_copy_rows_to_peer path) with a file-backed stand-in for
+    the C-ABI: every rank maps every peer's buffers once (the buffer shared by the slots through ONE handle), sends its
+    band to every peer with `last` on the final copy only, and after a barrier every rank holds the whole frame in
+    the buffers of the frame's slot -- for every slot."""
+    mp.spawn(_peer_asm_worker, args=(world, _free_port(), W, H, slots, str(tmp_path)), nprocs=world, join=True)
+    for rank in range(world):
+        got = np.load(os.path.join(str(tmp_path), "rank%d.npz" % rank))
+        for frame in range(slots + 1):
+            want = _pat2(H, W, frame)
+            assert np.array_equal(got["ratio_%d" % frame], want[:, :, None] + np.arange(4, dtype=np.float32)), (rank, frame)
+            assert np.array_equal(got["rgba8_%d" % frame], want.astype(np.uint32) + 7), (rank, frame)
