@@ -1,3 +1,6 @@
+# NOTE (round 2): compute-sanitizer is CLOSED on this pool (profiles/r2m_sanitizer_closed.txt is what it prints); the bounds
+# evidence of this repository is tools/check_bounds_gpu.sh (the GPU suite against a -DORB_CHECKS build).  Kept for pools where
+# the tool runs.
 # usage: tools/sanitize_gpu.sh [label]  -- compute-sanitizer over the kernels with shared cursors, warp-aggregated atomics,
 # shared-memory stacks and cross-stream flags: memcheck (out-of-bounds / misaligned accesses, leaks of
 # device memory at exit are not the point), racecheck (shared-memory hazards: the HybridStack columns, k_ltc's staging)
