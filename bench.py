@@ -137,7 +137,7 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "ms_per_full_frame_extrapolated": dt / args.steps * 1e3 * H / rows,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, 1),
+            "config": workload_config(args, args.gpus),  # the job's config as the GPU arm states it for this N
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores,
                              "kind": "reference" if kind.startswith("reference") else "port", "sample": sample},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -664,7 +664,7 @@ def run_ours(args):
             line["ltc_pass_one_quad"] = line_ltc
         if world > 1:
             line["e2e"]["host_gather"] = bool(HOST_GATHER)
-            line["config"]["bands"] = [list(b) for b in T.bands]
+            line["bands"] = [list(b) for b in T.bands]  # beside config, so both arms print the same config at every N
             line["assembled_frame_equals_single_gpu_frame"] = same
             line["assembly"] = ("orb_copy_rows_to_peer: every rank's band into every peer's frame by the copy engines over "
                                 "NVLink, no rendezvous") if PEER_ASM else "NCCL all_gather_into_tensor on a side stream"

@@ -4,7 +4,7 @@ for wl in ratio path; do
   python - <<PY
 import json
 s=open("gpurun_out/cfg5_${wl}_n$N.json").read().strip().splitlines()
-d=json.loads(s[-1]); print(d.get("collectives_ms_per_frame_rank0"), d.get("assembled_frame_equals_single_gpu_frame"), d.get("rank_kernel_ms_per_frame")); print("$wl", d["n_gpus"], round(d["ms_per_step"],3), round(d["value"],1), round(d["e2e"]["value"],1), d["config"].get("bands"), {k:round(v["ms_per_frame"],3) for k,v in d["passes"].items()})
+d=json.loads(s[-1]); print(d.get("collectives_ms_per_frame_rank0"), d.get("assembled_frame_equals_single_gpu_frame"), d.get("rank_kernel_ms_per_frame")); print("$wl", d["n_gpus"], round(d["ms_per_step"],3), round(d["value"],1), round(d["e2e"]["value"],1), (d.get("bands") or d["config"].get("bands")), {k:round(v["ms_per_frame"],3) for k,v in d["passes"].items()})
 PY
   grep -v "OMP_NUM_THREADS\|^\*\*\*\|^$" gpurun_out/cfg5_${wl}_n$N.err | tail -4
 done
