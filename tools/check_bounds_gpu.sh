@@ -7,7 +7,8 @@
 # Build here (no GPU needed):  tools/check_bounds_gpu.sh build
 L=${1:-r2}
 CHK=optix_renderer_b200/liborb200_chk.so
-if [ "$L" = build ] || [ ! -f $CHK ]; then
+STALE=$(find optix_renderer_b200/csrc include -newer $CHK 2>/dev/null | head -1)
+if [ "$L" = build ] || [ ! -f $CHK ] || [ -n "$STALE" ]; then
   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared -DORB_CHECKS \
        -o $CHK optix_renderer_b200/csrc/orb200.cu || exit 1
   [ "$L" = build ] && exit 0
