@@ -1,6 +1,6 @@
 // image_io.cpp -- texture files for `map_Kd`: what the reference reads through stb_image
 // (src/Model.cpp:81-128: stbi_load(..., STBI_rgb_alpha), then mirrored along y) -- PNG (all colour types, 8 / 16 bit,
-// non-interlaced; zlib inflates the IDAT stream), baseline JPEG, TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
+// non-interlaced; zlib inflates the IDAT stream), JPEG (baseline and progressive Huffman), TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
 // Output: RGBA8, BOTTOM row first (the reference's mirror), as orb_scene_add_mesh takes it.
 // Own code: stb_image is a third-party library the reference vendors; only its observable result is matched
 // (grey -> (g,g,g,255), palette + tRNS -> RGBA, 16-bit samples keep their high byte).
@@ -179,9 +179,9 @@ bool load_tga(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) 
 }
 
 
-// ---- JPEG: baseline / extended sequential Huffman (SOF0 / SOF1), 8-bit, grey or YCbCr (RGB when an Adobe marker says
-// so), any sampling factors, restart intervals.  Progressive and arithmetic-coded files are refused (the caller
-// prints what is read).  A JPEG's texels are not defined bit for bit by the format: what the reference gets is what
+// ---- JPEG: baseline / extended sequential (SOF0 / SOF1) and progressive (SOF2) Huffman, 8-bit, grey or YCbCr (RGB when
+// an Adobe marker says so), any sampling factors, interleaved or one scan per component, restart intervals.
+// Arithmetic-coded, lossless and hierarchical files are refused (the caller prints what is read).  A JPEG's texels are not defined bit for bit by the format: what the reference gets is what
 // ITS decoder makes of the file, so the three places where decoders differ follow stb_image's choices -- a 12-bit
 // fixed-point "islow" inverse DCT (two extra bits kept between the passes), triangle-filtered chroma upsampling for
 // 2x1 / 1x2 / 2x2 sampling (replication otherwise), and a 20-bit fixed-point YCbCr -> RGB.
@@ -334,17 +334,15 @@ void jpeg_idct_block(const short* coef, uint8_t* out, int out_stride) {
     }
 }
 
-bool load_jpeg(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) {
-    static const unsigned char zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
-                                             41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
-                                             30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
-    const unsigned char* d = (const unsigned char*)s.data();
-    const size_t n = s.size();
-    if (n < 4 || d[0] != 0xff || d[1] != 0xd8) return false;
+// One JPEG file.  Every scan decodes into per-component coefficient planes (64 shorts per 8x8 block); dequantisation
+// and the inverse DCT run once, at the end -- which is what lets progressive files (SOF2: spectral selection and
+// successive approximation over many scans) and baseline files with one scan per component share the code.
+struct JpegDecoder {
     struct Comp {
         int id = 0, hs = 1, vs = 1, tq = 0, td = 0, ta = 0, dc = 0;
         int bw = 0, bh = 0;  // blocks across / down, padded to whole MCUs
         int cw = 0, ch = 0;  // true size in samples
+        std::vector<short> coef;
         std::vector<uint8_t> px;
     } comp[3];
     uint16_t qt[4][64] = {};
@@ -353,223 +351,397 @@ bool load_jpeg(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h)
     bool have_dc[4] = {}, have_ac[4] = {};
     int ncomp = 0, restart = 0, adobe_transform = -1;
     int hmax = 1, vmax = 1, mcux = 0, mcuy = 0;
-    bool have_frame = false;
-    size_t p = 2;
-    w = h = 0;
-    while (p + 4 <= n) {
-        if (d[p] != 0xff) return false;
-        while (p < n && d[p] == 0xff) p++;  // fill bytes
-        if (p >= n) return false;
-        const int m = d[p++];
-        if (m == 0xd9) break;
-        if (m == 0x01 || (m >= 0xd0 && m <= 0xd7)) continue;
-        if (p + 2 > n) return false;
-        const size_t len = ((size_t)d[p] << 8) | d[p + 1];
-        if (len < 2 || p + len > n) return false;
-        const unsigned char* b = d + p + 2;
-        const size_t bl = len - 2;
-        if (m == 0xdb) {  // DQT
-            size_t o = 0;
-            while (o < bl) {
-                const int pq = b[o] >> 4, t = b[o] & 15;
-                o++;
-                if (t > 3 || o + (pq ? 128 : 64) > bl) return false;
-                for (int i = 0; i < 64; i++, o += pq ? 2 : 1) qt[t][zigzag[i]] = pq ? (uint16_t)((b[o] << 8) | b[o + 1]) : b[o];
-                have_qt[t] = true;
+    int w = 0, h = 0;
+    bool have_frame = false, progressive = false;
+    // the current scan
+    int scan_n = 0, order[3] = {0, 0, 0}, ss = 0, se = 63, ah = 0, al = 0, eob_run = 0;
+
+    static const unsigned char* zigzag() {
+        static const unsigned char z[64 + 15] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                                 41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                                 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63,
+                                                 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};  // a corrupt run stays inside
+        return z;
+    }
+
+    bool block_sequential(JpegBits& br, Comp& c, short* blk) {  // a whole block of a baseline scan
+        const int t = br.decode(hdc[c.td]);
+        if (t < 0 || t > 15) return false;
+        c.dc += JpegBits::extend(br.get(t), t);
+        blk[0] = (short)c.dc;
+        const unsigned char* z = zigzag();
+        for (int k = 1; k < 64;) {
+            const int rs = br.decode(hac[c.ta]);
+            if (rs < 0) return false;
+            const int run = rs >> 4, sz = rs & 15;
+            if (sz == 0) {
+                if (run != 15) break;  // end of block
+                k += 16;
+                continue;
             }
-        } else if (m == 0xc4) {  // DHT
-            size_t o = 0;
-            while (o + 17 <= bl) {
-                const int tc = b[o] >> 4, t = b[o] & 15;
-                if (tc > 1 || t > 3) return false;
-                int total = 0;
-                for (int i = 0; i < 16; i++) total += b[o + 1 + i];
-                if (total > 256 || o + 17 + (size_t)total > bl) return false;
-                JpegHuff& hf = tc ? hac[t] : hdc[t];
-                if (!hf.build(b + o + 1, b + o + 17)) return false;
-                (tc ? have_ac : have_dc)[t] = true;
-                o += 17 + (size_t)total;
+            k += run;
+            if (k > 63) return false;
+            blk[z[k++]] = (short)JpegBits::extend(br.get(sz), sz);
+        }
+        return true;
+    }
+
+    bool block_dc_progressive(JpegBits& br, Comp& c, short* blk) {
+        if (ah == 0) {  // first pass: the difference, scaled by the point transform
+            const int t = br.decode(hdc[c.td]);
+            if (t < 0 || t > 15) return false;
+            c.dc += JpegBits::extend(br.get(t), t);
+            blk[0] = (short)(c.dc * (1 << al));
+        } else if (br.get(1)) {  // refinement: one more bit
+            blk[0] = (short)(blk[0] + (1 << al));
+        }
+        return true;
+    }
+
+    bool block_ac_progressive(JpegBits& br, Comp& c, short* blk) {
+        const unsigned char* z = zigzag();
+        if (ah == 0) {  // first pass of a band of coefficients
+            if (eob_run) {
+                --eob_run;
+                return true;
             }
-        } else if (m == 0xc0 || m == 0xc1) {  // SOF0 / SOF1
-            if (bl < 6 || b[0] != 8) return false;
-            h = (b[1] << 8) | b[2];
-            w = (b[3] << 8) | b[4];
-            ncomp = b[5];
-            if ((ncomp != 1 && ncomp != 3) || w <= 0 || h <= 0 || bl < 6 + 3 * (size_t)ncomp) return false;
-            for (int i = 0; i < ncomp; i++) {
-                comp[i].id = b[6 + 3 * i];
-                comp[i].hs = b[7 + 3 * i] >> 4;
-                comp[i].vs = b[7 + 3 * i] & 15;
-                comp[i].tq = b[8 + 3 * i];
-                if (comp[i].hs < 1 || comp[i].hs > 4 || comp[i].vs < 1 || comp[i].vs > 4 || comp[i].tq > 3) return false;
-                hmax = comp[i].hs > hmax ? comp[i].hs : hmax;
-                vmax = comp[i].vs > vmax ? comp[i].vs : vmax;
-            }
-            have_frame = true;
-        } else if (m == 0xc2 || (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc)) {
-            return false;  // progressive, lossless, arithmetic coding
-        } else if (m == 0xdd) {
-            if (bl < 2) return false;
-            restart = (b[0] << 8) | b[1];
-        } else if (m == 0xee && bl >= 12 && !memcmp(b, "Adobe", 5)) {
-            adobe_transform = b[11];
-        } else if (m == 0xda) {  // SOS: one interleaved scan over all components
-            if (!have_frame || bl < 1 || b[0] != ncomp || bl < 1 + 2 * (size_t)ncomp + 3) return false;
-            for (int i = 0; i < ncomp; i++) {
-                int k = 0;
-                while (k < ncomp && comp[k].id != b[1 + 2 * i]) k++;
-                if (k != i) return false;  // scan order = frame order (what every encoder writes)
-                comp[i].td = b[2 + 2 * i] >> 4;
-                comp[i].ta = b[2 + 2 * i] & 15;
-                if (comp[i].td > 3 || comp[i].ta > 3 || !have_dc[comp[i].td] || !have_ac[comp[i].ta] || !have_qt[comp[i].tq]) return false;
-            }
-            mcux = (w + 8 * hmax - 1) / (8 * hmax);
-            mcuy = (h + 8 * vmax - 1) / (8 * vmax);
-            for (int i = 0; i < ncomp; i++) {
-                Comp& c = comp[i];
-                if (ncomp == 1) c.hs = c.vs = 1;  // a single-component scan is not interleaved: 8x8 blocks in raster order
-                c.bw = mcux * c.hs;
-                c.bh = mcuy * c.vs;
-                c.cw = (w * c.hs + hmax - 1) / hmax;
-                c.ch = (h * c.vs + vmax - 1) / vmax;
-                c.px.assign((size_t)64 * c.bw * c.bh, 0);
-                c.dc = 0;
-            }
-            if (ncomp == 1) {
-                hmax = vmax = 1;
-                mcux = (w + 7) / 8;
-                mcuy = (h + 7) / 8;
-                comp[0].bw = mcux;
-                comp[0].bh = mcuy;
-                comp[0].cw = w;
-                comp[0].ch = h;
-                comp[0].px.assign((size_t)64 * mcux * mcuy, 0);
-            }
-            JpegBits br{d, p + len, n};
-            int todo = restart;
-            for (int my = 0; my < mcuy; my++)
-                for (int mx = 0; mx < mcux; mx++) {
-                    for (int i = 0; i < ncomp; i++) {
-                        Comp& c = comp[i];
-                        for (int by = 0; by < c.vs; by++)
-                            for (int bx = 0; bx < c.hs; bx++) {
-                                short coef[64] = {};
-                                const int tdc = br.decode(hdc[c.td]);
-                                if (tdc < 0 || tdc > 15) return false;
-                                c.dc += JpegBits::extend(br.get(tdc), tdc);
-                                coef[0] = (short)(c.dc * qt[c.tq][0]);
-                                for (int k = 1; k < 64;) {
-                                    const int rs = br.decode(hac[c.ta]);
-                                    if (rs < 0) return false;
-                                    const int run = rs >> 4, sz = rs & 15;
-                                    if (sz == 0) {
-                                        if (run != 15) break;  // end of block
-                                        k += 16;
-                                        continue;
-                                    }
-                                    k += run;
-                                    if (k > 63) return false;
-                                    coef[zigzag[k]] = (short)(JpegBits::extend(br.get(sz), sz) * qt[c.tq][zigzag[k]]);
-                                    k++;
-                                }
-                                const size_t stride = (size_t)8 * c.bw;
-                                jpeg_idct_block(coef, &c.px[((size_t)(my * c.vs + by) * 8) * stride + (size_t)(mx * c.hs + bx) * 8], (int)stride);
-                            }
+            int k = ss;
+            do {
+                const int rs = br.decode(hac[c.ta]);
+                if (rs < 0) return false;
+                const int sz = rs & 15, r = rs >> 4;
+                if (sz == 0) {
+                    if (r < 15) {
+                        eob_run = 1 << r;
+                        if (r) eob_run += br.get(r);
+                        --eob_run;
+                        break;
                     }
-                    if (restart && --todo == 0 && !(my == mcuy - 1 && mx == mcux - 1)) {
-                        // the next marker must be RSTn: byte-align, skip it, reset the predictors
-                        size_t q = br.p;
-                        while (q + 1 < n && !(d[q] == 0xff && d[q + 1] >= 0xd0 && d[q + 1] <= 0xd7)) q++;
-                        if (q + 1 >= n) return false;
-                        br.p = q + 2;
-                        br.reset();
-                        for (int i = 0; i < ncomp; i++) comp[i].dc = 0;
-                        todo = restart;
-                    }
+                    k += 16;
+                } else {
+                    k += r;
+                    if (k > 63) return false;
+                    blk[z[k++]] = (short)(JpegBits::extend(br.get(sz), sz) * (1 << al));
                 }
-            // ---- samples -> RGBA rows (top-down), written bottom row first
-            rgba.assign((size_t)4 * w * h, 255);
-            std::vector<uint8_t> line[3], row((size_t)4 * w);
-            for (int i = 0; i < ncomp; i++) line[i].assign((size_t)(comp[i].bw * 8) * (hmax / 1) + 16, 0);
-            const bool to_rgb = ncomp == 3 && adobe_transform != 0;
-            for (int y = 0; y < h; y++) {
-                const uint8_t* src[3] = {nullptr, nullptr, nullptr};
-                for (int i = 0; i < ncomp; i++) {
-                    const Comp& c = comp[i];
-                    const size_t stride = (size_t)8 * c.bw;
-                    const int fh = hmax / c.hs, fv = vmax / c.vs;  // upsampling factors (whole numbers for every real file)
-                    if (hmax % c.hs || vmax % c.vs) return false;
-                    const int wl = (w + fh - 1) / fh;  // low-resolution samples across
-                    int near = y / fv, far = near;
-                    if (fv == 2) far = (y & 1) ? near + 1 : near - 1;
-                    near = near < 0 ? 0 : (near > c.ch - 1 ? c.ch - 1 : near);
-                    far = far < 0 ? 0 : (far > c.ch - 1 ? c.ch - 1 : far);
-                    const uint8_t* a = &c.px[(size_t)near * stride];
-                    const uint8_t* f = &c.px[(size_t)far * stride];
-                    uint8_t* o = line[i].data();
-                    if (fh == 1 && fv == 1) {
-                        src[i] = a;
-                        continue;
-                    } else if (fh == 1 && fv == 2) {
-                        for (int x = 0; x < wl; x++) o[x] = (uint8_t)((3 * a[x] + f[x] + 2) >> 2);
-                    } else if (fh == 2 && fv == 1) {
-                        if (wl == 1) {
-                            o[0] = o[1] = a[0];
-                        } else {
-                            o[0] = a[0];
-                            o[1] = (uint8_t)((a[0] * 3 + a[1] + 2) >> 2);
-                            int x = 1;
-                            for (; x < wl - 1; x++) {
-                                const int t = 3 * a[x] + 2;
-                                o[2 * x] = (uint8_t)((t + a[x - 1]) >> 2);
-                                o[2 * x + 1] = (uint8_t)((t + a[x + 1]) >> 2);
-                            }
-                            o[2 * x] = (uint8_t)((a[wl - 2] * 3 + a[wl - 1] + 2) >> 2);
-                            o[2 * x + 1] = a[wl - 1];
-                        }
-                    } else if (fh == 2 && fv == 2) {
-                        int t1 = 3 * a[0] + f[0];
-                        if (wl == 1) {
-                            o[0] = o[1] = (uint8_t)((t1 + 2) >> 2);
-                        } else {
-                            o[0] = (uint8_t)((t1 + 2) >> 2);
-                            for (int x = 1; x < wl; x++) {
-                                const int t0 = t1;
-                                t1 = 3 * a[x] + f[x];
-                                o[2 * x - 1] = (uint8_t)((3 * t0 + t1 + 8) >> 4);
-                                o[2 * x] = (uint8_t)((3 * t1 + t0 + 8) >> 4);
-                            }
-                            o[2 * wl - 1] = (uint8_t)((t1 + 2) >> 2);
-                        }
-                    } else {  // any other ratio: nearest sample
-                        for (int x = 0; x < wl; x++)
-                            for (int k = 0; k < fh; k++) o[x * fh + k] = a[x];
-                    }
-                    src[i] = o;
-                }
-                for (int x = 0; x < w; x++) {
-                    uint8_t* o = &row[4 * (size_t)x];
-                    if (ncomp == 1) {
-                        o[0] = o[1] = o[2] = src[0][x];
-                    } else if (!to_rgb) {
-                        o[0] = src[0][x], o[1] = src[1][x], o[2] = src[2][x];
-                    } else {
-                        auto FX = [](double v) { return ((int)(v * 4096.0 + 0.5)) << 8; };
-                        const int yf = (src[0][x] << 20) + (1 << 19), cb = src[1][x] - 128, cr = src[2][x] - 128;
-                        const int r = yf + cr * FX(1.40200);
-                        const int g = yf + cr * -FX(0.71414) + (int)((unsigned)(cb * -FX(0.34414)) & 0xffff0000u);
-                        const int bl2 = yf + cb * FX(1.77200);
-                        o[0] = clamp8(r >> 20), o[1] = clamp8(g >> 20), o[2] = clamp8(bl2 >> 20);
-                    }
-                    o[3] = 255;
-                }
-                put_flipped(rgba, w, h, y, row.data());
+            } while (k <= se);
+            return true;
+        }
+        const short bit = (short)(1 << al);  // refinement: one more bit of the non-zero coefficients, new +-1s between them
+        auto refine = [&](short* q) {
+            if (br.get(1) && (*q & bit) == 0) *q = (short)(*q > 0 ? *q + bit : *q - bit);
+        };
+        if (eob_run) {
+            --eob_run;
+            for (int k = ss; k <= se; k++) {
+                short* q = &blk[z[k]];
+                if (*q != 0) refine(q);
             }
             return true;
         }
-        p += len;
+        int k = ss;
+        do {
+            const int rs = br.decode(hac[c.ta]);
+            if (rs < 0) return false;
+            int sz = rs & 15, r = rs >> 4;
+            if (sz == 0) {
+                if (r < 15) {
+                    eob_run = (1 << r) - 1;
+                    if (r) eob_run += br.get(r);
+                    r = 64;  // nothing new in the rest of this block
+                }
+            } else {
+                if (sz != 1) return false;
+                sz = br.get(1) ? bit : -bit;
+            }
+            while (k <= se) {
+                short* q = &blk[z[k++]];
+                if (*q != 0) {
+                    refine(q);
+                } else {
+                    if (r == 0) {
+                        *q = (short)sz;
+                        break;
+                    }
+                    --r;
+                }
+            }
+        } while (k <= se);
+        return true;
     }
-    return false;
+
+    bool block(JpegBits& br, Comp& c, int bx, int by) {
+        short* blk = &c.coef[((size_t)by * c.bw + bx) * 64];
+        if (!progressive) return block_sequential(br, c, blk);
+        return ss == 0 ? block_dc_progressive(br, c, blk) : block_ac_progressive(br, c, blk);
+    }
+
+    // the entropy-coded segment after an SOS header that ended at `start`; returns the offset of the next marker
+    bool scan(const unsigned char* d, size_t n, size_t start, size_t& next) {
+        JpegBits br{d, start, n};
+        for (int i = 0; i < scan_n; i++) comp[order[i]].dc = 0;
+        eob_run = 0;
+        int todo = restart;
+        auto at_restart = [&](bool last) {
+            if (!restart || --todo != 0 || last) return true;
+            size_t q = br.p;  // the next marker must be RSTn: byte-align, skip it, reset the predictors
+            while (q + 1 < n && !(d[q] == 0xff && d[q + 1] >= 0xd0 && d[q + 1] <= 0xd7)) {
+                if (d[q] == 0xff && d[q + 1] != 0 && d[q + 1] != 0xff) return false;  // another marker: the scan is short
+                q++;
+            }
+            if (q + 1 >= n) return false;
+            br.p = q + 2;
+            br.reset();
+            for (int i = 0; i < scan_n; i++) comp[order[i]].dc = 0;
+            eob_run = 0;
+            todo = restart;
+            return true;
+        };
+        if (scan_n == 1) {  // one component: its blocks in raster order, only those that hold image samples
+            Comp& c = comp[order[0]];
+            const int nx = (c.cw + 7) >> 3, ny = (c.ch + 7) >> 3;
+            for (int by = 0; by < ny; by++)
+                for (int bx = 0; bx < nx; bx++) {
+                    if (!block(br, c, bx, by)) return false;
+                    if (!at_restart(by == ny - 1 && bx == nx - 1)) return false;
+                }
+        } else {  // interleaved: MCU by MCU, hs x vs blocks of every component of the scan
+            if (progressive && ss != 0) return false;
+            for (int my = 0; my < mcuy; my++)
+                for (int mx = 0; mx < mcux; mx++) {
+                    for (int i = 0; i < scan_n; i++) {
+                        Comp& c = comp[order[i]];
+                        for (int y = 0; y < c.vs; y++)
+                            for (int x = 0; x < c.hs; x++)
+                                if (!block(br, c, mx * c.hs + x, my * c.vs + y)) return false;
+                    }
+                    if (!at_restart(my == mcuy - 1 && mx == mcux - 1)) return false;
+                }
+        }
+        size_t q = br.p;  // the marker that ended the segment (the bit reader never reads past one)
+        while (q + 1 < n && !(d[q] == 0xff && d[q + 1] != 0 && d[q + 1] != 0xff && !(d[q + 1] >= 0xd0 && d[q + 1] <= 0xd7))) q++;
+        next = q;
+        return true;
+    }
+
+    bool parse(const unsigned char* d, size_t n) {
+        if (n < 4 || d[0] != 0xff || d[1] != 0xd8) return false;
+        const unsigned char* z = zigzag();
+        size_t p = 2;
+        bool any_scan = false;
+        while (p + 2 <= n) {
+            if (d[p] != 0xff) return false;
+            while (p < n && d[p] == 0xff) p++;  // fill bytes
+            if (p >= n) break;
+            const int m = d[p++];
+            if (m == 0xd9) break;
+            if (m == 0x01 || (m >= 0xd0 && m <= 0xd7)) continue;
+            if (p + 2 > n) return false;
+            const size_t len = ((size_t)d[p] << 8) | d[p + 1];
+            if (len < 2 || p + len > n) return false;
+            const unsigned char* b = d + p + 2;
+            const size_t bl = len - 2;
+            if (m == 0xdb) {  // DQT
+                size_t o = 0;
+                while (o < bl) {
+                    const int pq = b[o] >> 4, t = b[o] & 15;
+                    o++;
+                    if (t > 3 || o + (pq ? 128 : 64) > bl) return false;
+                    for (int i = 0; i < 64; i++, o += pq ? 2 : 1) qt[t][z[i]] = pq ? (uint16_t)((b[o] << 8) | b[o + 1]) : b[o];
+                    have_qt[t] = true;
+                }
+            } else if (m == 0xc4) {  // DHT
+                size_t o = 0;
+                while (o + 17 <= bl) {
+                    const int tc = b[o] >> 4, t = b[o] & 15;
+                    if (tc > 1 || t > 3) return false;
+                    int total = 0;
+                    for (int i = 0; i < 16; i++) total += b[o + 1 + i];
+                    if (total > 256 || o + 17 + (size_t)total > bl) return false;
+                    JpegHuff& hf = tc ? hac[t] : hdc[t];
+                    if (!hf.build(b + o + 1, b + o + 17)) return false;
+                    (tc ? have_ac : have_dc)[t] = true;
+                    o += 17 + (size_t)total;
+                }
+            } else if (m == 0xc0 || m == 0xc1 || m == 0xc2) {  // SOF0 / SOF1 / SOF2
+                if (have_frame || bl < 6 || b[0] != 8) return false;
+                progressive = m == 0xc2;
+                h = (b[1] << 8) | b[2];
+                w = (b[3] << 8) | b[4];
+                ncomp = b[5];
+                if ((ncomp != 1 && ncomp != 3) || w <= 0 || h <= 0 || bl < 6 + 3 * (size_t)ncomp) return false;
+                for (int i = 0; i < ncomp; i++) {
+                    comp[i].id = b[6 + 3 * i];
+                    comp[i].hs = b[7 + 3 * i] >> 4;
+                    comp[i].vs = b[7 + 3 * i] & 15;
+                    comp[i].tq = b[8 + 3 * i];
+                    if (comp[i].hs < 1 || comp[i].hs > 4 || comp[i].vs < 1 || comp[i].vs > 4 || comp[i].tq > 3) return false;
+                }
+                if (ncomp == 1) comp[0].hs = comp[0].vs = 1;  // a lone component is never interleaved: plain 8x8 blocks
+                for (int i = 0; i < ncomp; i++) {
+                    hmax = comp[i].hs > hmax ? comp[i].hs : hmax;
+                    vmax = comp[i].vs > vmax ? comp[i].vs : vmax;
+                }
+                mcux = (w + 8 * hmax - 1) / (8 * hmax);
+                mcuy = (h + 8 * vmax - 1) / (8 * vmax);
+                for (int i = 0; i < ncomp; i++) {
+                    Comp& c = comp[i];
+                    if (hmax % c.hs || vmax % c.vs) return false;  // whole-number upsampling factors (every real file)
+                    c.bw = mcux * c.hs;
+                    c.bh = mcuy * c.vs;
+                    c.cw = (w * c.hs + hmax - 1) / hmax;
+                    c.ch = (h * c.vs + vmax - 1) / vmax;
+                    c.coef.assign((size_t)64 * c.bw * c.bh, 0);
+                }
+                have_frame = true;
+            } else if (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) {
+                return false;  // lossless, hierarchical, arithmetic coding
+            } else if (m == 0xdd) {
+                if (bl < 2) return false;
+                restart = (b[0] << 8) | b[1];
+            } else if (m == 0xee && bl >= 12 && !memcmp(b, "Adobe", 5)) {
+                adobe_transform = b[11];
+            } else if (m == 0xda) {  // SOS
+                if (!have_frame || bl < 1) return false;
+                scan_n = b[0];
+                if (scan_n < 1 || scan_n > ncomp || bl < 1 + 2 * (size_t)scan_n + 3) return false;
+                for (int i = 0; i < scan_n; i++) {
+                    int k = 0;
+                    while (k < ncomp && comp[k].id != b[1 + 2 * i]) k++;
+                    if (k == ncomp) return false;
+                    order[i] = k;
+                    comp[k].td = b[2 + 2 * i] >> 4;
+                    comp[k].ta = b[2 + 2 * i] & 15;
+                    if (comp[k].td > 3 || comp[k].ta > 3) return false;
+                }
+                ss = b[1 + 2 * scan_n];
+                se = b[2 + 2 * scan_n];
+                ah = b[3 + 2 * scan_n] >> 4;
+                al = b[3 + 2 * scan_n] & 15;
+                if (progressive) {
+                    if (ss > 63 || se > 63 || ss > se || ah > 13 || al > 13) return false;
+                } else {
+                    if (ss != 0 || ah != 0 || al != 0) return false;
+                    se = 63;
+                }
+                for (int i = 0; i < scan_n; i++) {
+                    const Comp& c = comp[order[i]];
+                    const bool need_dc = !progressive || (ss == 0 && ah == 0), need_ac = !progressive || ss != 0;
+                    if ((need_dc && !have_dc[c.td]) || (need_ac && !have_ac[c.ta])) return false;
+                }
+                size_t next = 0;
+                if (!scan(d, n, p + len, next)) return false;
+                any_scan = true;
+                p = next;
+                continue;
+            }
+            p += len;
+        }
+        return have_frame && any_scan;
+    }
+
+    // coefficient planes -> sample planes (dequantise in 16 bits, as the coefficients are held)
+    bool finish() {
+        for (int i = 0; i < ncomp; i++) {
+            Comp& c = comp[i];
+            if (!have_qt[c.tq]) return false;
+            c.px.assign((size_t)64 * c.bw * c.bh, 0);
+            const size_t stride = (size_t)8 * c.bw;
+            const int nx = progressive || ncomp == 1 ? (c.cw + 7) >> 3 : c.bw, ny = progressive || ncomp == 1 ? (c.ch + 7) >> 3 : c.bh;
+            for (int by = 0; by < ny; by++)
+                for (int bx = 0; bx < nx; bx++) {
+                    short* blk = &c.coef[((size_t)by * c.bw + bx) * 64];
+                    for (int k = 0; k < 64; k++) blk[k] = (short)(blk[k] * qt[c.tq][k]);
+                    jpeg_idct_block(blk, &c.px[((size_t)by * 8) * stride + (size_t)bx * 8], (int)stride);
+                }
+        }
+        return true;
+    }
+};
+
+bool load_jpeg(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) {
+    JpegDecoder J;
+    if (!J.parse((const unsigned char*)s.data(), s.size()) || !J.finish()) return false;
+    w = J.w;
+    h = J.h;
+    const int ncomp = J.ncomp, hmax = J.hmax, vmax = J.vmax;
+    // ---- samples -> RGBA rows (top-down), written bottom row first
+    rgba.assign((size_t)4 * w * h, 255);
+    std::vector<uint8_t> line[3], row((size_t)4 * w);
+    for (int i = 0; i < ncomp; i++) line[i].assign((size_t)(J.comp[i].bw * 8) * hmax + 16, 0);
+    const bool to_rgb = ncomp == 3 && J.adobe_transform != 0;
+    for (int y = 0; y < h; y++) {
+        const uint8_t* src[3] = {nullptr, nullptr, nullptr};
+        for (int i = 0; i < ncomp; i++) {
+            const JpegDecoder::Comp& c = J.comp[i];
+            const size_t stride = (size_t)8 * c.bw;
+            const int fh = hmax / c.hs, fv = vmax / c.vs;  // upsampling factors
+            const int wl = (w + fh - 1) / fh;               // low-resolution samples across
+            int near = y / fv, far = near;
+            if (fv == 2) far = (y & 1) ? near + 1 : near - 1;
+            near = near < 0 ? 0 : (near > c.ch - 1 ? c.ch - 1 : near);
+            far = far < 0 ? 0 : (far > c.ch - 1 ? c.ch - 1 : far);
+            const uint8_t* a = &c.px[(size_t)near * stride];
+            const uint8_t* f = &c.px[(size_t)far * stride];
+            uint8_t* o = line[i].data();
+            if (fh == 1 && fv == 1) {
+                src[i] = a;
+                continue;
+            } else if (fh == 1 && fv == 2) {
+                for (int x = 0; x < wl; x++) o[x] = (uint8_t)((3 * a[x] + f[x] + 2) >> 2);
+            } else if (fh == 2 && fv == 1) {
+                if (wl == 1) {
+                    o[0] = o[1] = a[0];
+                } else {
+                    o[0] = a[0];
+                    o[1] = (uint8_t)((a[0] * 3 + a[1] + 2) >> 2);
+                    int x = 1;
+                    for (; x < wl - 1; x++) {
+                        const int t = 3 * a[x] + 2;
+                        o[2 * x] = (uint8_t)((t + a[x - 1]) >> 2);
+                        o[2 * x + 1] = (uint8_t)((t + a[x + 1]) >> 2);
+                    }
+                    o[2 * x] = (uint8_t)((a[wl - 2] * 3 + a[wl - 1] + 2) >> 2);  // the reference decoder's last column, as it is
+                    o[2 * x + 1] = a[wl - 1];
+                }
+            } else if (fh == 2 && fv == 2) {
+                int t1 = 3 * a[0] + f[0];
+                if (wl == 1) {
+                    o[0] = o[1] = (uint8_t)((t1 + 2) >> 2);
+                } else {
+                    o[0] = (uint8_t)((t1 + 2) >> 2);
+                    for (int x = 1; x < wl; x++) {
+                        const int t0 = t1;
+                        t1 = 3 * a[x] + f[x];
+                        o[2 * x - 1] = (uint8_t)((3 * t0 + t1 + 8) >> 4);
+                        o[2 * x] = (uint8_t)((3 * t1 + t0 + 8) >> 4);
+                    }
+                    o[2 * wl - 1] = (uint8_t)((t1 + 2) >> 2);
+                }
+            } else {  // any other ratio: nearest sample
+                for (int x = 0; x < wl; x++)
+                    for (int k = 0; k < fh; k++) o[x * fh + k] = a[x];
+            }
+            src[i] = o;
+        }
+        for (int x = 0; x < w; x++) {
+            uint8_t* o = &row[4 * (size_t)x];
+            if (ncomp == 1) {
+                o[0] = o[1] = o[2] = src[0][x];
+            } else if (!to_rgb) {
+                o[0] = src[0][x], o[1] = src[1][x], o[2] = src[2][x];
+            } else {
+                auto FX = [](double v) { return ((int)(v * 4096.0 + 0.5)) << 8; };
+                const int yf = (src[0][x] << 20) + (1 << 19), cb = src[1][x] - 128, cr = src[2][x] - 128;
+                const int r = yf + cr * FX(1.40200);
+                const int g = yf + cr * -FX(0.71414) + (int)((unsigned)(cb * -FX(0.34414)) & 0xffff0000u);
+                const int bl2 = yf + cb * FX(1.77200);
+                o[0] = clamp8(r >> 20), o[1] = clamp8(g >> 20), o[2] = clamp8(bl2 >> 20);
+            }
+            o[3] = 255;
+        }
+        put_flipped(rgba, w, h, y, row.data());
+    }
+    return true;
 }
 
 }  // namespace

@@ -1,4 +1,4 @@
-"""Generate tests/golden/textures.npz: image files (JPEG in every sampling layout, PNG, TGA) and the RGBA8 texels the
+"""Generate tests/golden/textures.npz: image files (baseline and progressive JPEG in every sampling layout, PNG, TGA) and the RGBA8 texels the
 REFERENCE gets from each -- its own vendored decoder (/root/reference/include/stb/stb_image.h) behind loadTexture's two
 steps (src/Model.cpp:99-118: stbi_load(..., STBI_rgb_alpha), then the mirror along y), compiled where it lies as
 oracle/_ref/stb_decode (oracle/Makefile target ref_stb).  host/image_io.cpp is pinned against these bit for bit
@@ -71,6 +71,22 @@ def main():
         ok, buf = cv2.imencode(".jpg", smooth(rng, h, w, 3), [cv2.IMWRITE_JPEG_QUALITY, 85, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, flag])
         assert ok
         files["cv_%s_%dx%d.jpg" % (tag, w, h)] = buf.tobytes()
+    # progressive (SOF2): spectral selection + successive approximation, DC scans interleaved, AC scans per component
+    k = 0
+    for (w, h) in ((16, 16), (37, 23), (50, 41), (1, 1), (9, 3)):
+        for sub, tag in ((0, "444"), (1, "422"), (2, "420")):
+            for kw, t2 in (({}, "std"), ({"optimize": True}, "opt"), ({"restart_marker_blocks": 2}, "rst")):
+                if (w, h) in ((1, 1), (9, 3)) and t2 != "std":
+                    continue
+                jpeg("p%d_%dx%d_%s_%s" % (k, w, h, tag, t2), smooth(rng, h, w, 3), quality=(92, 75, 40)[k % 3], subsampling=sub,
+                     progressive=True, **kw)
+                k += 1
+    jpeg("p_noise_420", rng.integers(0, 256, (24, 40, 3), dtype=np.uint8), quality=95, subsampling=2, progressive=True)
+    jpeg("p_grey_33x20", smooth(rng, 20, 33, 1)[..., 0], quality=90, progressive=True)
+    ok, buf = cv2.imencode(".jpg", smooth(rng, 21, 30, 3), [cv2.IMWRITE_JPEG_QUALITY, 80, cv2.IMWRITE_JPEG_PROGRESSIVE, 1,
+                                                            cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_440])
+    assert ok
+    files["p_cv_440_30x21.jpg"] = buf.tobytes()
     b = io.BytesIO()
     Image.fromarray(smooth(rng, 11, 13, 3)).save(b, format="PNG")
     files["rgb_13x11.png"] = b.getvalue()

@@ -232,15 +232,15 @@ def test_host_exr_writer(host, tmp_path):
 
 
 def test_host_textures_equal_the_reference_decoder(host, tmp_path):
-    """map_Kd through JPEG (4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1, grey, optimised Huffman tables, restart intervals, 1x1 and
-    odd sizes), PNG and TGA: the texels the host hands to orb_scene_add_mesh equal, BIT FOR BIT, what the reference gets
+    """map_Kd through JPEG (baseline AND progressive; 4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1, grey, optimised Huffman tables,
+    restart intervals, 1x1 and odd sizes), PNG and TGA: the texels the host hands to orb_scene_add_mesh equal, BIT FOR BIT, what the reference gets
     from the same file -- its vendored stb_image.h behind loadTexture's stbi_load + y mirror (src/Model.cpp:99-118),
     recorded in tests/golden/textures.npz by tests/golden/make_golden_textures.py.  A JPEG's texels are decoder
     defined (IDCT rounding, chroma upsampling filter, fixed-point colour conversion): host/image_io.cpp follows the
-    reference's decoder in all three.  Progressive JPEGs are refused with a message, not mis-decoded."""
+    reference's decoder in all three."""
     g = np.load(os.path.join(ROOT, "tests", "golden", "textures.npz"))
     names = [str(n) for n in g["names"]]
-    assert len(names) >= 40 and sum(n.endswith(".jpg") for n in names) >= 35
+    assert len(names) >= 80 and sum(n.startswith("p") for n in names) >= 30
     (tmp_path / "a.obj").write_text("mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nusemtl m\nf 1/1/1 2/1/1 3/1/1\n")
     (tmp_path / "s.json").write_text(json.dumps({
         "spp": 1, "width": 8, "height": 8, "renderers": [9],
@@ -256,15 +256,21 @@ def test_host_textures_equal_the_reference_decoder(host, tmp_path):
         assert m["tex"] == [want.shape[1], want.shape[0]], (name, err)
         got = np.frombuffer(bytes.fromhex(m["texels"]), np.uint8).reshape(want.shape)
         assert np.array_equal(got, want), (name, int(np.abs(got.astype(int) - want.astype(int)).max()))
-    # progressive: refused (the scene renders with the material's Kd and a message), never decoded wrongly
-    prog = bytearray(g["file_%d" % names.index(next(n for n in names if n.endswith("444_std.jpg")))].tobytes())
-    k = prog.find(b"\xff\xc0")
+    # arithmetic coding (SOF9): refused -- the scene renders with the material's Kd and a message -- never mis-decoded
+    bad = bytearray(g["file_%d" % names.index(next(n for n in names if n.endswith("444_std.jpg") and n.startswith("c")))].tobytes())
+    k = bad.find(b"\xff\xc0")
     assert k > 0
-    prog[k + 1] = 0xC2
-    (tmp_path / "p.jpg").write_bytes(bytes(prog))
-    (tmp_path / "a.mtl").write_text("newmtl m\nKd 1 0 0\nNs 0.5\nmap_Kd p.jpg\n")
+    bad[k + 1] = 0xC9
+    (tmp_path / "ari.jpg").write_bytes(bytes(bad))
+    (tmp_path / "a.mtl").write_text("newmtl m\nKd 1 0 0\nNs 0.5\nmap_Kd ari.jpg\n")
     rc, d, err = dump(host, str(tmp_path / "s.json"), "--dump-texels")
     assert rc == 0 and d["meshes"][0]["tex"] == [0, 0] and "Could not load texture" in err
+    # a truncated file: refused or decoded to SOMETHING of the right size, never a crash
+    for cut in (200, len(bad) // 2):
+        (tmp_path / "cut.jpg").write_bytes(g["file_%d" % names.index("noise_420.jpg")].tobytes()[:cut])
+        (tmp_path / "a.mtl").write_text("newmtl m\nKd 1 0 0\nNs 0.5\nmap_Kd cut.jpg\n")
+        rc, d, err = dump(host, str(tmp_path / "s.json"), "--dump-texels")
+        assert rc == 0 and d["meshes"][0]["tex"] in ([0, 0], [40, 24])
 
 
 @pytest.mark.gpu
