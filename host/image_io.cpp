@@ -1,6 +1,6 @@
 // image_io.cpp -- texture files for `map_Kd`: what the reference reads through stb_image
-// (src/Model.cpp:81-128: stbi_load(..., STBI_rgb_alpha), then mirrored along y) -- PNG (all colour types, 8 / 16 bit,
-// non-interlaced; zlib inflates the IDAT stream), JPEG (baseline and progressive Huffman), TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
+// (src/Model.cpp:81-128: stbi_load(..., STBI_rgb_alpha), then mirrored along y) -- PNG (all colour types and bit depths,
+// Adam7 interlace; zlib inflates the IDAT stream), JPEG (baseline and progressive Huffman), TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
 // Output: RGBA8, BOTTOM row first (the reference's mirror), as orb_scene_add_mesh takes it.
 // Own code: stb_image is a third-party library the reference vendors; only its observable result is matched
 // (grey -> (g,g,g,255), palette + tRNS -> RGBA, 16-bit samples keep their high byte).
@@ -72,112 +72,193 @@ bool load_png(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) 
         }
         p += 12 + (size_t)len;
     }
-    if (!have_hdr || w <= 0 || h <= 0 || (size_t)w * h > ((size_t)1 << 28) || interlace != 0) return false;
+    if (!have_hdr || w <= 0 || h <= 0 || (size_t)w * h > ((size_t)1 << 28) || interlace > 1) return false;
     if (depth != 8 && depth != 16 && !(ctype == 3 || ctype == 0)) return false;
     if (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16) return false;
     const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
     if (!channels || (ctype == 3 && plte.size() < 3)) return false;
     const int bpp_bits = channels * depth;
-    const size_t stride = ((size_t)w * bpp_bits + 7) / 8, bpp = (size_t)(bpp_bits + 7) / 8;
-    std::vector<unsigned char> raw((stride + 1) * (size_t)h);
+    const size_t bpp = (size_t)(bpp_bits + 7) / 8;
+    // one pass (the whole image) or the seven passes of Adam7: pass k holds the pixels (x0 + i dx, y0 + j dy)
+    static const int ax0[7] = {0, 4, 0, 2, 0, 1, 0}, ay0[7] = {0, 0, 4, 0, 2, 0, 1};
+    static const int adx[7] = {8, 8, 4, 4, 2, 2, 1}, ady[7] = {8, 8, 8, 4, 4, 2, 2};
+    const int n_pass = interlace ? 7 : 1;
+    int pw[7], ph[7];
+    size_t total = 0;
+    for (int k = 0; k < n_pass; k++) {
+        pw[k] = interlace ? (w - ax0[k] + adx[k] - 1) / adx[k] : w;
+        ph[k] = interlace ? (h - ay0[k] + ady[k] - 1) / ady[k] : h;
+        if (pw[k] > 0 && ph[k] > 0) total += (((size_t)pw[k] * bpp_bits + 7) / 8 + 1) * (size_t)ph[k];
+    }
+    std::vector<unsigned char> raw(total);
     uLongf raw_len = (uLongf)raw.size();
     if (uncompress(raw.data(), &raw_len, idat.data(), (uLong)idat.size()) != Z_OK || raw_len != raw.size()) return false;
     rgba.assign((size_t)4 * w * h, 255);
-    std::vector<unsigned char> prev(stride, 0), cur(stride);
-    std::vector<uint8_t> out_row((size_t)4 * w);
-    for (int y = 0; y < h; y++) {
-        const unsigned char* in = &raw[(stride + 1) * (size_t)y];
-        const int filter = in[0];
-        for (size_t i = 0; i < stride; i++) {
-            const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
-            int v = in[1 + i];
-            switch (filter) {
-                case 0: break;
-                case 1: v += a; break;
-                case 2: v += b; break;
-                case 3: v += (a + b) >> 1; break;
-                case 4: v += paeth(a, b, c); break;
-                default: return false;
+    size_t off = 0;
+    for (int k = 0; k < n_pass; k++) {
+        if (pw[k] <= 0 || ph[k] <= 0) continue;
+        const size_t stride = ((size_t)pw[k] * bpp_bits + 7) / 8;
+        const int x0 = interlace ? ax0[k] : 0, y0 = interlace ? ay0[k] : 0, dx = interlace ? adx[k] : 1, dy = interlace ? ady[k] : 1;
+        std::vector<unsigned char> prev(stride, 0), cur(stride);
+        for (int y = 0; y < ph[k]; y++) {
+            const unsigned char* in = &raw[off];
+            off += stride + 1;
+            const int filter = in[0];
+            for (size_t i = 0; i < stride; i++) {
+                const int a = i >= bpp ? cur[i - bpp] : 0, b = prev[i], c = i >= bpp ? prev[i - bpp] : 0;
+                int v = in[1 + i];
+                switch (filter) {
+                    case 0: break;
+                    case 1: v += a; break;
+                    case 2: v += b; break;
+                    case 3: v += (a + b) >> 1; break;
+                    case 4: v += paeth(a, b, c); break;
+                    default: return false;
+                }
+                cur[i] = (unsigned char)v;
             }
-            cur[i] = (unsigned char)v;
-        }
-        for (int x = 0; x < w; x++) {
-            uint8_t* o = &out_row[4 * (size_t)x];
-            auto sample = [&](int ch) -> int {  // 8-bit value of channel ch of pixel x (16-bit: the high byte)
-                if (depth == 8) return cur[(size_t)x * channels + ch];
-                if (depth == 16) return cur[((size_t)x * channels + ch) * 2];
-                const int bit = x * depth, v = (cur[bit >> 3] >> (8 - depth - (bit & 7))) & ((1 << depth) - 1);
-                return ctype == 3 ? v : v * 255 / ((1 << depth) - 1);
-            };
-            if (ctype == 3) {
-                const size_t k = (size_t)sample(0);
-                if (3 * k + 2 >= plte.size()) return false;
-                o[0] = plte[3 * k], o[1] = plte[3 * k + 1], o[2] = plte[3 * k + 2];
-                o[3] = k < trns.size() ? trns[k] : 255;
-            } else if (ctype == 0 || ctype == 4) {
-                o[0] = o[1] = o[2] = (uint8_t)sample(0);
-                o[3] = ctype == 4 ? (uint8_t)sample(1) : 255;
-                if (ctype == 0 && trns.size() >= 2 && depth == 8 && o[0] == trns[1]) o[3] = 0;
-            } else {
-                o[0] = (uint8_t)sample(0), o[1] = (uint8_t)sample(1), o[2] = (uint8_t)sample(2);
-                o[3] = ctype == 6 ? (uint8_t)sample(3) : 255;
-                if (ctype == 2 && trns.size() >= 6 && depth == 8 && o[0] == trns[1] && o[1] == trns[3] && o[2] == trns[5]) o[3] = 0;
+            const int Y = y0 + y * dy;
+            for (int x = 0; x < pw[k]; x++) {
+                uint8_t* o = &rgba[4 * ((size_t)(h - 1 - Y) * w + (size_t)(x0 + x * dx))];  // bottom row first
+                auto sample = [&](int ch) -> int {  // 8-bit value of channel ch of pixel x (16-bit: the high byte)
+                    if (depth == 8) return cur[(size_t)x * channels + ch];
+                    if (depth == 16) return cur[((size_t)x * channels + ch) * 2];
+                    const int bit = x * depth, v = (cur[bit >> 3] >> (8 - depth - (bit & 7))) & ((1 << depth) - 1);
+                    return ctype == 3 ? v : v * 255 / ((1 << depth) - 1);
+                };
+                if (ctype == 3) {
+                    const size_t q = (size_t)sample(0);
+                    if (3 * q + 2 >= plte.size()) return false;
+                    o[0] = plte[3 * q], o[1] = plte[3 * q + 1], o[2] = plte[3 * q + 2];
+                    o[3] = q < trns.size() ? trns[q] : 255;
+                } else if (ctype == 0 || ctype == 4) {
+                    o[0] = o[1] = o[2] = (uint8_t)sample(0);
+                    o[3] = ctype == 4 ? (uint8_t)sample(1) : 255;
+                    if (ctype == 0 && trns.size() >= 2) {  // the one transparent grey level: compared at full depth
+                        if (depth == 16) {
+                            if (cur[(size_t)x * 2] == trns[0] && cur[(size_t)x * 2 + 1] == trns[1]) o[3] = 0;
+                        } else if (o[0] == (uint8_t)(trns[1] * (depth == 8 ? 1 : 255 / ((1 << depth) - 1)))) {
+                            o[3] = 0;
+                        }
+                    }
+                } else {
+                    o[0] = (uint8_t)sample(0), o[1] = (uint8_t)sample(1), o[2] = (uint8_t)sample(2);
+                    o[3] = ctype == 6 ? (uint8_t)sample(3) : 255;
+                    if (ctype == 2 && trns.size() >= 6) {  // the one transparent colour
+                        if (depth == 16) {
+                            if (!memcmp(&cur[(size_t)x * 6], trns.data(), 6)) o[3] = 0;
+                        } else if (o[0] == trns[1] && o[1] == trns[3] && o[2] == trns[5]) {
+                            o[3] = 0;
+                        }
+                    }
+                }
             }
+            prev.swap(cur);
         }
-        put_flipped(rgba, w, h, y, out_row.data());
-        prev.swap(cur);
     }
     return true;
 }
 
+// TGA: true colour (15 / 16 / 24 / 32 bit), grey (8 bit, or 16 = grey + alpha) and colour-mapped (8- or 16-bit indices into
+// a 15 / 16 / 24 / 32-bit palette), raw or run-length encoded, bottom-up or top-down.  16-bit colours are 5-5-5
+// (c * 255 / 31 per channel); an index past the palette reads entry 0.
 bool load_tga(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) {
     if (s.size() < 18) return false;
     const unsigned char* d = (const unsigned char*)s.data();
-    const int id_len = d[0], cmap = d[1], type = d[2], bits = d[16], desc = d[17];
+    const int id_len = d[0], indexed = d[1], bits = d[16], desc = d[17];
+    int type = d[2];
+    const int pal_start = d[3] | (d[4] << 8), pal_len = d[5] | (d[6] << 8), pal_bits = d[7];
     w = d[12] | (d[13] << 8);
     h = d[14] | (d[15] << 8);
-    if (cmap != 0 || w <= 0 || h <= 0) return false;
-    const bool rle = type == 10 || type == 11, grey = type == 3 || type == 11;
-    if (!(type == 2 || type == 3 || rle)) return false;
-    if (!((grey && bits == 8) || (!grey && (bits == 24 || bits == 32)))) return false;
-    const int bpp = bits / 8;
+    if (w <= 0 || h <= 0 || indexed > 1) return false;
+    const bool rle = type >= 8;
+    if (rle) type -= 8;
+    if (!(type == 1 || type == 2 || type == 3) || (type == 1) != (indexed == 1)) return false;
+    // components of a colour of `b` bits: 1 grey, 2 grey + alpha, 3 / 4 colour; rgb16 = packed 5-5-5
+    bool rgb16 = false;
+    auto comps = [&](int b, bool grey) {
+        if (b == 8) return 1;
+        if (b == 16 && grey) return 2;
+        if (b == 15 || b == 16) { rgb16 = true; return 3; }
+        return (b == 24 || b == 32) ? b / 8 : 0;
+    };
+    if (indexed && bits != 8 && bits != 16) return false;
+    const int comp = indexed ? comps(pal_bits, false) : comps(bits, type == 3);
+    if (!comp) return false;
     size_t p = 18 + (size_t)id_len;
-    std::vector<unsigned char> px((size_t)w * h * bpp);
-    if (!rle) {
-        if (s.size() < p + px.size()) return false;
-        memcpy(px.data(), d + p, px.size());
-    } else {
-        size_t o = 0;
-        while (o < px.size()) {
-            if (p >= s.size()) return false;
-            const int c = d[p++], n = (c & 127) + 1;
-            if (c & 128) {
-                if (p + bpp > s.size()) return false;
-                for (int k = 0; k < n && o < px.size(); k++, o += bpp) memcpy(&px[o], d + p, bpp);
-                p += bpp;
-            } else {
-                if (p + (size_t)n * bpp > s.size() || o + (size_t)n * bpp > px.size()) return false;
-                memcpy(&px[o], d + p, (size_t)n * bpp);
-                p += (size_t)n * bpp;
-                o += (size_t)n * bpp;
-            }
+    auto read16 = [&](uint8_t* o) {  // 5-5-5, already in R G B order
+        const int px = d[p] | (d[p + 1] << 8);
+        p += 2;
+        o[0] = (uint8_t)((((px >> 10) & 31) * 255) / 31);
+        o[1] = (uint8_t)((((px >> 5) & 31) * 255) / 31);
+        o[2] = (uint8_t)(((px & 31) * 255) / 31);
+    };
+    std::vector<uint8_t> pal;
+    if (indexed) {
+        if (pal_len == 0) return false;
+        p += (size_t)pal_start;
+        pal.resize((size_t)pal_len * comp);
+        const size_t entry = rgb16 ? 2 : (size_t)comp;
+        if (p + (size_t)pal_len * entry > s.size()) return false;
+        if (rgb16) {
+            for (int i = 0; i < pal_len; i++) read16(&pal[(size_t)i * comp]);
+        } else {
+            memcpy(pal.data(), d + p, pal.size());
+            p += pal.size();
         }
+    }
+    const size_t in_bytes = indexed ? (size_t)bits / 8 : (rgb16 ? 2 : (size_t)comp);
+    std::vector<uint8_t> px((size_t)w * h * comp);
+    uint8_t cur[4] = {0, 0, 0, 0};
+    int run = 0;
+    bool repeat = false, fresh = true;
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        if (rle) {
+            if (run == 0) {
+                if (p >= s.size()) return false;
+                const int c = d[p++];
+                run = (c & 127) + 1;
+                repeat = (c & 128) != 0;
+                fresh = true;
+            } else if (!repeat) {
+                fresh = true;
+            }
+        } else {
+            fresh = true;
+        }
+        if (fresh) {
+            if (p + in_bytes > s.size()) return false;
+            if (indexed) {
+                size_t k = bits == 8 ? d[p] : (size_t)(d[p] | (d[p + 1] << 8));
+                p += in_bytes;
+                if (k >= (size_t)pal_len) k = 0;
+                memcpy(cur, &pal[k * comp], (size_t)comp);
+            } else if (rgb16) {
+                read16(cur);
+            } else {
+                memcpy(cur, d + p, (size_t)comp);
+                p += (size_t)comp;
+            }
+            fresh = false;
+        }
+        memcpy(&px[i * comp], cur, (size_t)comp);
+        --run;
     }
     const bool top_down = (desc & 0x20) != 0;
     rgba.assign((size_t)4 * w * h, 255);
     std::vector<uint8_t> row((size_t)4 * w);
     for (int y = 0; y < h; y++) {
         for (int x = 0; x < w; x++) {
-            const unsigned char* q = &px[((size_t)y * w + x) * bpp];
+            const uint8_t* q = &px[((size_t)y * w + x) * comp];
             uint8_t* o = &row[4 * (size_t)x];
-            if (grey) { o[0] = o[1] = o[2] = q[0]; o[3] = 255; }
-            else { o[0] = q[2]; o[1] = q[1]; o[2] = q[0]; o[3] = bpp == 4 ? q[3] : 255; }  // stored BGR(A)
+            if (comp <= 2) { o[0] = o[1] = o[2] = q[0]; o[3] = comp == 2 ? q[1] : 255; }
+            else if (rgb16) { o[0] = q[0]; o[1] = q[1]; o[2] = q[2]; o[3] = 255; }
+            else { o[0] = q[2]; o[1] = q[1]; o[2] = q[0]; o[3] = comp == 4 ? q[3] : 255; }  // stored B G R (A)
         }
         put_flipped(rgba, w, h, top_down ? y : h - 1 - y, row.data());
     }
     return true;
 }
-
 
 // ---- JPEG: baseline / extended sequential (SOF0 / SOF1) and progressive (SOF2) Huffman, 8-bit, grey or YCbCr (RGB when
 // an Adobe marker says so), any sampling factors, interleaved or one scan per component, restart intervals.
@@ -266,24 +347,26 @@ struct JpegBits {
 };
 
 // one dimension of the inverse DCT on eight values `s`, 12-bit constants; even part in x[0..3], odd part in t[0..3]
-inline void jpeg_idct_1d(const int* s, int stride, int x[4], int t[4]) {
-    auto F = [](double v) { return (int)(v * 4096 + 0.5); };
-    int p2 = s[2 * stride], p3 = s[6 * stride];
-    int p1 = (p2 + p3) * F(0.5411961);
-    const int e2 = p1 + p3 * F(-1.847759065), e3 = p1 + p2 * F(0.765366865);
+// (64-bit intermediates: a corrupt file's coefficients may be anything; valid data never leaves 32 bits)
+typedef long long idct_t;
+inline void jpeg_idct_1d(const idct_t* s, int stride, idct_t x[4], idct_t t[4]) {
+    auto F = [](double v) { return (idct_t)(int)(v * 4096 + 0.5); };
+    idct_t p2 = s[2 * stride], p3 = s[6 * stride];
+    idct_t p1 = (p2 + p3) * F(0.5411961);
+    const idct_t e2 = p1 + p3 * F(-1.847759065), e3 = p1 + p2 * F(0.765366865);
     p2 = s[0];
     p3 = s[4 * stride];
-    const int e0 = (p2 + p3) * 4096, e1 = (p2 - p3) * 4096;
+    const idct_t e0 = (p2 + p3) * 4096, e1 = (p2 - p3) * 4096;
     x[0] = e0 + e3;
     x[3] = e0 - e3;
     x[1] = e1 + e2;
     x[2] = e1 - e2;
-    int t0 = s[7 * stride], t1 = s[5 * stride], t2 = s[3 * stride], t3 = s[1 * stride];
+    idct_t t0 = s[7 * stride], t1 = s[5 * stride], t2 = s[3 * stride], t3 = s[1 * stride];
     p3 = t0 + t2;
-    int p4 = t1 + t3;
+    idct_t p4 = t1 + t3;
     p1 = t0 + t3;
     p2 = t1 + t2;
-    const int p5 = (p3 + p4) * F(1.175875602);
+    const idct_t p5 = (p3 + p4) * F(1.175875602);
     t0 *= F(0.298631336);
     t1 *= F(2.053119869);
     t2 *= F(3.072711026);
@@ -298,13 +381,13 @@ inline void jpeg_idct_1d(const int* s, int stride, int x[4], int t[4]) {
     t[0] = t0 + p1 + p3;
 }
 
-inline uint8_t clamp8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+inline uint8_t clamp8(long long v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
 
 void jpeg_idct_block(const short* coef, uint8_t* out, int out_stride) {
-    int mid[64];
+    idct_t mid[64];
     for (int c = 0; c < 8; c++) {  // columns
         const short* d = coef + c;
-        int col[8];
+        idct_t col[8];
         bool ac = false;
         for (int r = 0; r < 8; r++) {
             col[r] = d[8 * r];
@@ -314,20 +397,20 @@ void jpeg_idct_block(const short* coef, uint8_t* out, int out_stride) {
             for (int r = 0; r < 8; r++) mid[8 * r + c] = col[0] * 4;
             continue;
         }
-        int x[4], t[4];
+        idct_t x[4], t[4];
         jpeg_idct_1d(col, 1, x, t);
         for (int k = 0; k < 4; k++) {
-            const int e = x[k] + 512;
+            const idct_t e = x[k] + 512;
             mid[8 * k + c] = (e + t[3 - k]) >> 10;
             mid[8 * (7 - k) + c] = (e - t[3 - k]) >> 10;
         }
     }
     for (int r = 0; r < 8; r++) {  // rows; +128 and the rounding of the final >> 17 folded into the even part
-        int x[4], t[4];
+        idct_t x[4], t[4];
         jpeg_idct_1d(mid + 8 * r, 1, x, t);
         uint8_t* o = out + (size_t)r * out_stride;
         for (int k = 0; k < 4; k++) {
-            const int e = x[k] + 65536 + (128 << 17);
+            const idct_t e = x[k] + 65536 + (128 << 17);
             o[k] = clamp8((e + t[3 - k]) >> 17);
             o[7 - k] = clamp8((e - t[3 - k]) >> 17);
         }

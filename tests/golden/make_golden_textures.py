@@ -41,6 +41,48 @@ def reference_texels(data, suffix):
     return np.frombuffer(body, np.uint8).reshape(h, w, 4).copy()
 
 
+def png_bytes(px, ctype, depth, interlace=0, palette=None, trns=None, filt=0):
+    """A PNG file of px[h, w, channels] (integers below 2**depth): any colour type / bit depth, optionally Adam7."""
+    import struct
+    import zlib
+
+    h, w, ch = px.shape
+
+    def chunk(t, body):
+        return struct.pack(">I", len(body)) + t + body + struct.pack(">I", zlib.crc32(t + body) & 0xffffffff)
+
+    def rows(sub):
+        out = bytearray()
+        for r in sub:
+            v = r.reshape(-1).astype(np.uint32)
+            if depth == 16:
+                b = np.stack([v >> 8, v & 255], -1).astype(np.uint8).tobytes()
+            elif depth == 8:
+                b = v.astype(np.uint8).tobytes()
+            else:
+                per = 8 // depth
+                pad = (-len(v)) % per
+                vv = np.concatenate([v, np.zeros(pad, np.uint32)]).reshape(-1, per)
+                b = sum(vv[:, i] << (8 - depth * (i + 1)) for i in range(per)).astype(np.uint8).tobytes()
+            out += bytes([0]) + b          # filter 0 (the five filters are covered by test_host_texture_formats)
+        return bytes(out)
+
+    raw = b""
+    if interlace:
+        for x0, y0, dx, dy in ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2)):
+            sub = px[y0::dy, x0::dx]
+            if sub.shape[0] and sub.shape[1]:
+                raw += rows(sub)
+    else:
+        raw = rows(px)
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, interlace))
+    if palette is not None:
+        out += chunk(b"PLTE", bytes(palette))
+    if trns is not None:
+        out += chunk(b"tRNS", bytes(trns))
+    return out + chunk(b"IDAT", zlib.compress(raw)) + chunk(b"IEND", b"")
+
+
 def main():
     if not os.path.exists(STB):
         sys.exit("oracle/_ref/stb_decode is not built: make -C oracle ref_stb (needs /root/reference)")
@@ -93,6 +135,64 @@ def main():
     b = io.BytesIO()
     Image.fromarray(np.concatenate([smooth(rng, 6, 9, 3), smooth(rng, 6, 9, 1)], -1), "RGBA").save(b, format="PNG")
     files["rgba_9x6.png"] = b.getvalue()
+    # PNG: every colour type x bit depth, plain and Adam7 (sizes below 8 leave some passes empty), tRNS on every type
+    for (w, h) in ((13, 9), (3, 2), (1, 1), (8, 8)):
+        for il in (0, 1):
+            tag = "%dx%d_%s" % (w, h, "adam7" if il else "plain")
+            for depth in (1, 2, 4, 8, 16):
+                top = 1 << depth
+                files["g%d_%s.png" % (depth, tag)] = png_bytes(rng.integers(0, top, (h, w, 1)), 0, depth, il)
+                if depth <= 8:
+                    pal = rng.integers(0, 256, 3 * min(top, 256)).astype(np.uint8)
+                    files["p%d_%s.png" % (depth, tag)] = png_bytes(rng.integers(0, min(top, 256), (h, w, 1)), 3, depth, il, palette=pal,
+                                                                   trns=rng.integers(0, 256, min(top, 256) // 2 + 1).astype(np.uint8))
+                if depth >= 8:
+                    files["rgb%d_%s.png" % (depth, tag)] = png_bytes(rng.integers(0, top, (h, w, 3)), 2, depth, il)
+                    files["ga%d_%s.png" % (depth, tag)] = png_bytes(rng.integers(0, top, (h, w, 2)), 4, depth, il)
+                    files["rgba%d_%s.png" % (depth, tag)] = png_bytes(rng.integers(0, top, (h, w, 4)), 6, depth, il)
+    few = rng.integers(0, 3, (9, 13, 3))
+    files["rgb8_trns.png"] = png_bytes(few * 100, 2, 8, 0, trns=[0, 100, 0, 200, 0, 0])
+    files["rgb16_trns.png"] = png_bytes(few * 30000, 2, 16, 1, trns=[0x75, 0x30, 0xea, 0x60, 0, 0])
+    for depth in (1, 2, 4, 8, 16):
+        v = rng.integers(0, min(1 << depth, 4), (9, 13, 1))
+        files["g%d_trns.png" % depth] = png_bytes(v, 0, depth, depth & 1, trns=[0, 1])
+    # TGA: 15 / 16-bit colour, grey + alpha, colour-mapped (24 / 32 / 16-bit palettes, 8- and 16-bit indices, an index
+    # past the palette), run-length encoded forms, top-down, an image id field
+    import struct
+
+    def tga(name, type_, w, h, bits, data, desc=0, cmap=None, cmap_bits=24, idlen=0, cmap_first=0):
+        n_pal = 0 if cmap is None else len(cmap) // ((cmap_bits + 7) // 8)
+        hdr = bytes([idlen, 1 if cmap is not None else 0, type_]) + struct.pack("<HHB", cmap_first, n_pal, cmap_bits if cmap is not None else 0)
+        hdr += struct.pack("<HHHHBB", 0, 0, w, h, bits, desc)
+        files[name + ".tga"] = hdr + bytes(idlen) + (bytes(cmap) if cmap is not None else b"") + bytes(data)
+
+    def rle(units, size):
+        out, i = bytearray(), 0
+        while i < len(units):
+            n = min(3, len(units) - i)
+            out += bytes([n - 1]) + b"".join(units[i:i + n])
+            i += n
+            if i < len(units):
+                n = min(5, len(units) - i)
+                out += bytes([128 | (n - 1)]) + units[i]
+                i += n
+        return out
+
+    w, h = 7, 5
+    tga("t_rgb16", 2, w, h, 16, rng.integers(0, 65536, w * h, dtype=np.uint16).tobytes())
+    tga("t_rgb15", 2, w, h, 15, rng.integers(0, 65536, w * h, dtype=np.uint16).tobytes())
+    tga("t_ga16", 3, w, h, 16, rng.integers(0, 256, w * h * 2, dtype=np.uint8).tobytes())
+    tga("t_g8_top_id", 3, w, h, 8, rng.integers(0, 256, w * h, dtype=np.uint8).tobytes(), desc=0x20, idlen=9)
+    for cb in (24, 32, 16, 15):
+        pal = rng.integers(0, 256, ((cb + 7) // 8) * 16, dtype=np.uint8)
+        tga("t_cm8_pal%d" % cb, 1, w, h, 8, rng.integers(0, 20, w * h, dtype=np.uint8).tobytes(), cmap=pal, cmap_bits=cb)   # 16..19: past the palette
+        idx = [bytes([int(v)]) for v in rng.integers(0, 16, w * h)]
+        tga("t_cm8_rle_pal%d" % cb, 9, w, h, 8, rle(idx, 1), cmap=pal, cmap_bits=cb)
+    pal = rng.integers(0, 256, 3 * 300, dtype=np.uint8)
+    tga("t_cm16_pal24", 1, w, h, 16, rng.integers(0, 300, w * h).astype("<u2").tobytes(), cmap=pal, cmap_bits=24)
+    tga("t_rgba32_rle_top", 10, w, h, 32, rle([rng.integers(0, 256, 4, dtype=np.uint8).tobytes() for _ in range(w * h)], 4), desc=0x28)
+    tga("t_rgb16_rle", 10, w, h, 16, rle([rng.integers(0, 256, 2, dtype=np.uint8).tobytes() for _ in range(w * h)], 2))
+    tga("t_g8_rle", 11, w, h, 8, rle([bytes([int(v)]) for v in rng.integers(0, 256, w * h)], 1))
     b = io.BytesIO()
     Image.fromarray(smooth(rng, 7, 12, 3)).save(b, format="TGA")
     files["rgb_12x7.tga"] = b.getvalue()
