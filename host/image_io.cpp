@@ -1,6 +1,6 @@
 // image_io.cpp -- texture files for `map_Kd`: what the reference reads through stb_image
 // (src/Model.cpp:81-128: stbi_load(..., STBI_rgb_alpha), then mirrored along y) -- PNG (all colour types and bit depths,
-// Adam7 interlace; zlib inflates the IDAT stream), JPEG (baseline and progressive Huffman), TGA (types 2 / 3 / 10 / 11, 8 / 24 / 32 bit) and binary PPM.
+// Adam7 interlace; zlib inflates the IDAT stream), JPEG (baseline and progressive Huffman), TGA, BMP and binary PPM.
 // Output: RGBA8, BOTTOM row first (the reference's mirror), as orb_scene_add_mesh takes it.
 // Own code: stb_image is a third-party library the reference vendors; only its observable result is matched
 // (grey -> (g,g,g,255), palette + tRNS -> RGBA, 16-bit samples keep their high byte).
@@ -257,6 +257,131 @@ bool load_tga(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) 
         }
         put_flipped(rgba, w, h, top_down ? y : h - 1 - y, row.data());
     }
+    return true;
+}
+
+// BMP: uncompressed 4 / 8-bit palette, 24-bit, and 16 / 32-bit with the default or explicit channel masks (info headers
+// of 12, 40, 56, 108 and 124 bytes); run-length encoded and 1-bit files are refused, as the reference's decoder does.
+// Its conventions, which decide texels: a channel of fewer than 8 bits is widened by repeating its bits (v + v >> n
+// + ...) after an ARITHMETIC shift of the masked value taken as a signed int; a 32-bit file whose alpha bytes are all
+// zero is opaque; a positive height means bottom-up rows.
+bool load_bmp(const std::string& s, std::vector<uint8_t>& rgba, int& w, int& h) {
+    const unsigned char* d = (const unsigned char*)s.data();
+    const size_t n = s.size();
+    size_t p = 0;
+    auto g8 = [&]() -> unsigned { return p < n ? d[p++] : (p++, 0u); };  // past the end reads as zero
+    auto g16 = [&]() -> unsigned { const unsigned a = g8(); return a | (g8() << 8); };
+    auto g32 = [&]() -> unsigned { const unsigned a = g16(); return a | (g16() << 16); };
+    if (g8() != 'B' || g8() != 'M') return false;
+    g32(); g16(); g16();
+    const int offset = (int)g32(), hsz = (int)g32();
+    if (hsz != 12 && hsz != 40 && hsz != 56 && hsz != 108 && hsz != 124) return false;
+    int hh;
+    if (hsz == 12) { w = (int)g16(); hh = (int)g16(); }
+    else { w = (int)g32(); hh = (int)g32(); }
+    if (g16() != 1) return false;
+    const int bpp = (int)g16();
+    unsigned mr = 0, mg = 0, mb = 0, ma = 0, all_a = 255;
+    if (bpp == 1) return false;
+    if (hsz != 12) {
+        const unsigned compress = g32();
+        if (compress == 1 || compress == 2) return false;
+        for (int i = 0; i < 5; i++) g32();  // image size, resolutions, colours used / important
+        if (hsz == 40 || hsz == 56) {
+            if (hsz == 56) for (int i = 0; i < 4; i++) g32();
+            if (bpp == 16 || bpp == 32) {
+                if (compress == 0) {
+                    if (bpp == 32) { mr = 0xffu << 16; mg = 0xffu << 8; mb = 0xffu; ma = 0xffu << 24; all_a = 0; }
+                    else { mr = 31u << 10; mg = 31u << 5; mb = 31u; }
+                } else if (compress == 3) {
+                    mr = g32(); mg = g32(); mb = g32();
+                    if (mr == mg && mg == mb) return false;
+                } else {
+                    return false;
+                }
+            }
+        } else {
+            mr = g32(); mg = g32(); mb = g32(); ma = g32();
+            for (int i = 0; i < 13; i++) g32();  // colour space
+            if (hsz == 124) for (int i = 0; i < 4; i++) g32();
+        }
+    }
+    const bool bottom_up = hh > 0;
+    h = hh < 0 ? -hh : hh;
+    if (w <= 0 || h <= 0 || (size_t)w * h > ((size_t)1 << 28)) return false;
+    int psize = 0;
+    if (hsz == 12) { if (bpp < 24) psize = (offset - 14 - 24) / 3; }
+    else if (bpp < 16) psize = (offset - 14 - hsz) >> 2;
+    std::vector<uint8_t> img((size_t)4 * w * h);  // top-down as stored, flipped below
+    size_t z = 0;
+    if (bpp < 16) {
+        if (psize <= 0 || psize > 256 || (bpp != 4 && bpp != 8)) return false;
+        uint8_t pal[256][3] = {};
+        for (int i = 0; i < psize; i++) {
+            pal[i][2] = (uint8_t)g8(); pal[i][1] = (uint8_t)g8(); pal[i][0] = (uint8_t)g8();
+            if (hsz != 12) g8();
+        }
+        p += (size_t)(offset - 14 - hsz - psize * (hsz == 12 ? 3 : 4));
+        const int width = bpp == 4 ? (w + 1) >> 1 : w, pad = (-width) & 3;
+        for (int j = 0; j < h; j++) {
+            for (int i = 0; i < w; i += 2) {
+                unsigned v = g8(), v2 = 0;
+                if (bpp == 4) { v2 = v & 15; v >>= 4; }
+                memcpy(&img[z], pal[v], 3); img[z + 3] = 255; z += 4;
+                if (i + 1 == w) break;
+                v = bpp == 8 ? g8() : v2;
+                memcpy(&img[z], pal[v], 3); img[z + 3] = 255; z += 4;
+            }
+            p += (size_t)pad;
+        }
+    } else {
+        if (bpp != 16 && bpp != 24 && bpp != 32) return false;
+        p += (size_t)(offset - 14 - hsz);
+        const int width = bpp == 24 ? 3 * w : (bpp == 16 ? 2 * w : 0), pad = (-width) & 3;
+        const int easy = bpp == 24 ? 1 : ((bpp == 32 && mb == 0xff && mg == 0xff00 && mr == 0x00ff0000 && ma == 0xff000000) ? 2 : 0);
+        auto high_bit = [](unsigned m) { int k = -1; while (m) { k++; m >>= 1; } return k; };
+        auto bit_count = [](unsigned m) { int k = 0; while (m) { k += m & 1; m >>= 1; } return k; };
+        auto widen = [](unsigned masked, int shift, int bits) -> int {  // to 8 bits, the reference decoder's way
+            long long v = (int)masked;  // signed: a mask that reaches bit 31 shifts arithmetically
+            v = shift < 0 ? (long long)((unsigned long long)v << -shift) : v >> shift;
+            v = (int)v;
+            long long r = v;
+            for (int k = bits; k < 8 && bits > 0; k += bits) r += v >> k;
+            return (int)r;
+        };
+        int rs = 0, gs = 0, bs = 0, as = 0, rc = 0, gc = 0, bc = 0, ac = 0;
+        if (!easy) {
+            if (!mr || !mg || !mb) return false;
+            rs = high_bit(mr) - 7; rc = bit_count(mr);
+            gs = high_bit(mg) - 7; gc = bit_count(mg);
+            bs = high_bit(mb) - 7; bc = bit_count(mb);
+            as = high_bit(ma) - 7; ac = bit_count(ma);
+        }
+        for (int j = 0; j < h; j++) {
+            for (int i = 0; i < w; i++, z += 4) {
+                if (easy) {
+                    img[z + 2] = (uint8_t)g8(); img[z + 1] = (uint8_t)g8(); img[z] = (uint8_t)g8();
+                    const unsigned a = easy == 2 ? g8() : 255u;
+                    all_a |= a;
+                    img[z + 3] = (uint8_t)a;
+                } else {
+                    const unsigned v = bpp == 16 ? g16() : g32();
+                    img[z] = (uint8_t)widen(v & mr, rs, rc);
+                    img[z + 1] = (uint8_t)widen(v & mg, gs, gc);
+                    img[z + 2] = (uint8_t)widen(v & mb, bs, bc);
+                    const int a = ma ? widen(v & ma, as, ac) : 255;
+                    all_a |= (unsigned)a;
+                    img[z + 3] = (uint8_t)a;
+                }
+            }
+            p += (size_t)pad;
+        }
+        if (!ma) for (size_t i = 3; i < img.size(); i += 4) img[i] = 255;  // three components: opaque
+    }
+    if (all_a == 0) for (size_t i = 3; i < img.size(); i += 4) img[i] = 255;
+    rgba.assign((size_t)4 * w * h, 255);
+    for (int y = 0; y < h; y++)  // stored row y is image row (bottom_up ? h-1-y : y) counted from the top
+        put_flipped(rgba, w, h, bottom_up ? h - 1 - y : y, &img[(size_t)4 * w * y]);
     return true;
 }
 
@@ -835,6 +960,7 @@ bool load_image_rgba8(const std::string& path, std::vector<uint8_t>& rgba, int& 
     if (!slurp(path, s) || s.size() < 4) return false;
     if ((unsigned char)s[0] == 0x89 && s[1] == 'P') return load_png(s, rgba, w, h);
     if (s[0] == 'P' && s[1] == '6') return load_ppm_rgba8(path, rgba, w, h);
+    if (s[0] == 'B' && s[1] == 'M') return load_bmp(s, rgba, w, h);
     if ((unsigned char)s[0] == 0xff && (unsigned char)s[1] == 0xd8) return load_jpeg(s, rgba, w, h);
     std::string ext = path.size() >= 4 ? path.substr(path.size() - 4) : "";
     for (auto& c : ext) c = (char)tolower((unsigned char)c);

@@ -354,7 +354,7 @@ bool load_obj(const std::string& obj_file, std::vector<Mesh>& out, std::string* 
                 for (auto& ch : tp)
                     if (ch == '\\') ch = '/';
                 if (!load_image_rgba8(base + tp, m.tex, m.tex_w, m.tex_h) && !warned[tp]++)
-                    fprintf(stderr, "Could not load texture from %s (PNG, JPEG, TGA and binary PPM are read)\n", (base + tp).c_str());
+                    fprintf(stderr, "Could not load texture from %s (PNG, JPEG, TGA, BMP and binary PPM are read)\n", (base + tp).c_str());
             }
             out.push_back(std::move(m));
         }

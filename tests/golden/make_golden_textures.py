@@ -193,6 +193,60 @@ def main():
     tga("t_rgba32_rle_top", 10, w, h, 32, rle([rng.integers(0, 256, 4, dtype=np.uint8).tobytes() for _ in range(w * h)], 4), desc=0x28)
     tga("t_rgb16_rle", 10, w, h, 16, rle([rng.integers(0, 256, 2, dtype=np.uint8).tobytes() for _ in range(w * h)], 2))
     tga("t_g8_rle", 11, w, h, 8, rle([bytes([int(v)]) for v in rng.integers(0, 256, w * h)], 1))
+    # BMP: OS/2 (12-byte) and Windows (40 / 56 / 108 / 124-byte) headers; 4 / 8-bit palette, 16-bit 5-5-5 and 5-6-5 and odd
+    # masks, 24-bit, 32-bit with alpha, with all-zero alpha, with explicit masks up to bit 31; bottom-up and top-down;
+    # row padding (widths 5, 6, 7)
+    def bmp(name, w, h, bpp, rows, hsz=40, compress=0, masks=(), pal=None, top_down=False):
+        pal_bytes = b"" if pal is None else bytes(pal)
+        extra = b"".join(struct.pack("<I", m) for m in masks)
+        if hsz == 12:
+            info = struct.pack("<IHHHH", 12, w, h, 1, bpp)
+        else:
+            info = struct.pack("<IiiHHIIiiII", hsz, w, -h if top_down else h, 1, bpp, compress, 0, 2835, 2835, 0, 0)
+            if hsz == 40:
+                info += extra[:12] if compress == 3 else b""
+            elif hsz == 56:
+                info += struct.pack("<IIII", *(list(masks) + [0] * 4)[:4])
+            else:
+                info += struct.pack("<IIII", *(list(masks) + [0] * 4)[:4]) + bytes(hsz - 40 - 16)
+        offset = 14 + len(info) + len(pal_bytes)
+        body = b"".join(r + bytes((-len(r)) & 3) for r in rows)
+        files[name + ".bmp"] = b"BM" + struct.pack("<IHHI", offset + len(body), 0, 0, offset) + info + pal_bytes + body
+
+    def packed(vals, bpp):
+        if bpp == 8:
+            return bytes(int(v) for v in vals)
+        v = list(vals) + [0]
+        return bytes((int(v[i]) << 4) | int(v[i + 1]) for i in range(0, len(vals), 2))
+
+    for w in (5, 6, 7):
+        h = 4
+        pal3 = rng.integers(0, 256, 3 * 16, dtype=np.uint8)
+        pal4 = rng.integers(0, 256, 4 * 16, dtype=np.uint8)
+        for bpp in (4, 8):
+            idx = rng.integers(0, 16, (h, w))
+            bmp("b_os2_p%d_w%d" % (bpp, w), w, h, bpp, [packed(r, bpp) for r in idx], hsz=12, pal=pal3)
+            bmp("b_p%d_w%d" % (bpp, w), w, h, bpp, [packed(r, bpp) for r in idx], pal=pal4, top_down=(w == 6))
+        px16 = rng.integers(0, 65536, (h, w)).astype("<u2")
+        bmp("b_555_w%d" % w, w, h, 16, [r.tobytes() for r in px16])
+        bmp("b_565_w%d" % w, w, h, 16, [r.tobytes() for r in px16], compress=3, masks=(0xf800, 0x07e0, 0x001f))
+        bmp("b_odd16_w%d" % w, w, h, 16, [r.tobytes() for r in px16], compress=3, masks=(0x7000, 0x0f80, 0x0003))
+        px24 = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        bmp("b_24_w%d" % w, w, h, 24, [r.tobytes() for r in px24], top_down=(w == 5))
+        bmp("b_os2_24_w%d" % w, w, h, 24, [r.tobytes() for r in px24], hsz=12)
+        px32 = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        bmp("b_32_w%d" % w, w, h, 32, [r.tobytes() for r in px32])
+        zero_a = px32.copy()
+        zero_a[..., 3] = 0
+        bmp("b_32_zero_alpha_w%d" % w, w, h, 32, [r.tobytes() for r in zero_a])
+        raw32 = rng.integers(0, 2 ** 32, (h, w), dtype=np.uint64).astype("<u4")
+        bmp("b_32_masks_w%d" % w, w, h, 32, [r.tobytes() for r in raw32], compress=3, masks=(0xffc00000, 0x003ff000, 0x00000ffc))
+        bmp("b_v4_w%d" % w, w, h, 32, [r.tobytes() for r in raw32], hsz=108, compress=3, masks=(0x00ff0000, 0x0000ff00, 0x000000ff, 0xff000000))
+        bmp("b_v5_w%d" % w, w, h, 32, [r.tobytes() for r in raw32], hsz=124, compress=3, masks=(0x000000ff, 0x0000ff00, 0x00ff0000, 0xf0000000))
+        bmp("b_v3_56_w%d" % w, w, h, 16, [r.tobytes() for r in px16], hsz=56)
+    b = io.BytesIO()
+    Image.fromarray(smooth(rng, 7, 12, 3)).save(b, format="BMP")
+    files["pil_rgb.bmp"] = b.getvalue()
     b = io.BytesIO()
     Image.fromarray(smooth(rng, 7, 12, 3)).save(b, format="TGA")
     files["rgb_12x7.tga"] = b.getvalue()

@@ -234,14 +234,16 @@ def test_host_exr_writer(host, tmp_path):
 def test_host_textures_equal_the_reference_decoder(host, tmp_path):
     """map_Kd through JPEG (baseline AND progressive; 4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1, grey, optimised Huffman tables,
     restart intervals, 1x1 and odd sizes), PNG (every colour type x bit depth, plain and Adam7, tRNS on every type) and
-    TGA (15 / 16 / 24 / 32-bit colour, grey, grey + alpha, colour-mapped with 15 ... 32-bit palettes, RLE, top-down): the texels the host hands to orb_scene_add_mesh equal, BIT FOR BIT, what the reference gets
+    TGA (15 / 16 / 24 / 32-bit colour, grey, grey + alpha, colour-mapped with 15 ... 32-bit palettes, RLE, top-down) and
+    BMP (OS/2 and Windows headers, palettes, 16 / 32-bit default and explicit masks, all-zero alpha, top-down): the texels the host hands to orb_scene_add_mesh equal, BIT FOR BIT, what the reference gets
     from the same file -- its vendored stb_image.h behind loadTexture's stbi_load + y mirror (src/Model.cpp:99-118),
     recorded in tests/golden/textures.npz by tests/golden/make_golden_textures.py.  A JPEG's texels are decoder
     defined (IDCT rounding, chroma upsampling filter, fixed-point colour conversion): host/image_io.cpp follows the
     reference's decoder in all three."""
     g = np.load(os.path.join(ROOT, "tests", "golden", "textures.npz"))
     names = [str(n) for n in g["names"]]
-    assert len(names) >= 230 and sum(n.endswith(".jpg") for n in names) >= 85 and sum(n.endswith(".tga") for n in names) >= 15
+    assert len(names) >= 275 and sum(n.endswith(".jpg") for n in names) >= 85 and sum(n.endswith(".tga") for n in names) >= 15
+    assert sum(n.endswith(".bmp") for n in names) >= 45 and sum(n.endswith(".png") for n in names) >= 120
     (tmp_path / "a.obj").write_text("mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0 0\nusemtl m\nf 1/1/1 2/1/1 3/1/1\n")
     (tmp_path / "s.json").write_text(json.dumps({
         "spp": 1, "width": 8, "height": 8, "renderers": [9],
