@@ -8,6 +8,9 @@
 #include <string.h>
 
 #include <fstream>
+#include <array>
+#include <cmath>
+#include <limits>
 #include <map>
 #include <set>
 #include <sstream>
@@ -253,6 +256,75 @@ static bool parse_corner(const std::string& s, int nv, int nt, int nn, Corner& c
     return c.v >= 1 && c.v <= nv && c.t >= 1 && c.t <= nt && c.n >= 1 && c.n <= nn;
 }
 
+// A polygon's triangles as the reference's OBJ reader makes them (the tiny_obj_loader.h it vendors, LoadObj with
+// triangulate = true): ear clipping in the coordinate plane picked from the polygon's first non-degenerate corner.
+// A convex planar polygon comes out as the fan (0, k, k+1); a concave or non-planar one does not, and the order of the
+// triangles and of their corners decides the un-indexed vertex arrays (and through them the primitive ids and the
+// light list), so the procedure is followed step by step -- tests/golden/obj_ingest.json pins it on the reference's
+// own loader.  `V` = positions read so far (corner indices are 1-based and already absolute).
+static void triangulate_polygon(const std::vector<Corner>& face, const std::vector<float>& V,
+                                std::vector<std::array<Corner, 3>>& tris) {
+    size_t n = face.size();
+    auto P = [&](const Corner& c, size_t axis) { return V[3 * (size_t)(c.v - 1) + axis]; };
+    size_t ax[2] = {1, 2};
+    const float eps = std::numeric_limits<float>::epsilon();
+    for (size_t k = 0; k < n; k++) {
+        const Corner &a = face[k % n], &b = face[(k + 1) % n], &c = face[(k + 2) % n];
+        const float e0x = P(b, 0) - P(a, 0), e0y = P(b, 1) - P(a, 1), e0z = P(b, 2) - P(a, 2);
+        const float e1x = P(c, 0) - P(b, 0), e1y = P(c, 1) - P(b, 1), e1z = P(c, 2) - P(b, 2);
+        const float cx = std::fabs(e0y * e1z - e0z * e1y), cy = std::fabs(e0z * e1x - e0x * e1z), cz = std::fabs(e0x * e1y - e0y * e1x);
+        if (cx > eps || cy > eps || cz > eps) {  // a corner: drop the axis its normal points along most
+            if (!(cx > cy && cx > cz)) {
+                ax[0] = 0;
+                if (cz > cx && cz > cy) ax[1] = 1;
+            }
+            break;
+        }
+    }
+    float area = 0;
+    for (size_t k = 0; k < n; k++) {
+        const Corner &a = face[k], &b = face[(k + 1) % n];
+        area += (P(a, ax[0]) * P(b, ax[1]) - P(a, ax[1]) * P(b, ax[0])) * 0.5f;
+    }
+    std::vector<Corner> rest = face;
+    size_t guess = 0, tries = n, before = n;
+    while (rest.size() > 3 && tries > 0) {
+        n = rest.size();
+        if (guess >= n) guess -= n;
+        if (before != n) { before = n; tries = n; }  // a vertex went: start counting again
+        else tries--;
+        Corner ind[3];
+        float vx[3], vy[3];
+        for (size_t k = 0; k < 3; k++) {
+            ind[k] = rest[(guess + k) % n];
+            vx[k] = P(ind[k], ax[0]);
+            vy[k] = P(ind[k], ax[1]);
+        }
+        const float e0x = vx[1] - vx[0], e0y = vy[1] - vy[0], e1x = vx[2] - vx[1], e1y = vy[2] - vy[1];
+        const float cross = e0x * e1y - e0y * e1x;
+        if (cross * area < 0.0f) {  // a reflex corner
+            guess += 1;
+            continue;
+        }
+        bool overlap = false;  // another vertex inside this candidate ear (crossing-number test)
+        for (size_t o = 3; o < n && !overlap; o++) {
+            const Corner& q = rest[(guess + o) % n];
+            const float tx = P(q, ax[0]), ty = P(q, ax[1]);
+            int inside = 0;
+            for (int i = 0, j = 2; i < 3; j = i++)
+                if (((vy[i] > ty) != (vy[j] > ty)) && (tx < (vx[j] - vx[i]) * (ty - vy[i]) / (vy[j] - vy[i]) + vx[i])) inside = !inside;
+            overlap = inside != 0;
+        }
+        if (overlap) {
+            guess += 1;
+            continue;
+        }
+        tris.push_back({ind[0], ind[1], ind[2]});
+        rest.erase(rest.begin() + (long)((guess + 1) % n));  // the ear's tip leaves the polygon
+    }
+    if (rest.size() == 3) tris.push_back({rest[0], rest[1], rest[2]});
+}
+
 bool load_obj(const std::string& obj_file, std::vector<Mesh>& out, std::string* err) {
     std::ifstream f(obj_file.c_str());
     if (!f) {
@@ -314,9 +386,11 @@ bool load_obj(const std::string& obj_file, std::vector<Mesh>& out, std::string* 
                 if (err) *err = obj_file + ": face without a material (the reference indexes materials[-1])";
                 return false;
             }
-            for (size_t k = 1; k + 1 < cs.size(); k++) {  // fan; triangulated input keeps tinyobj's order exactly
+            std::vector<std::array<Corner, 3>> tris;
+            triangulate_polygon(cs, V, tris);
+            for (const auto& t : tris) {
                 Face fc;
-                fc.c[0] = cs[0]; fc.c[1] = cs[k]; fc.c[2] = cs[k + 1];
+                fc.c[0] = t[0]; fc.c[1] = t[1]; fc.c[2] = t[2];
                 fc.mat = cur_mat;
                 shapes.back().faces.push_back(fc);
             }

@@ -129,6 +129,36 @@ def test_host_obj_features(host, tmp_path):
     assert green["vertex_hash"] == fnv1a(fan)
 
 
+def test_host_obj_ingest_equals_the_reference_loader(host, tmp_path):
+    """host/scene_io.cpp load_obj against the reference's OWN ingest -- src/Model.cpp loadOBJ with the tiny_obj_loader.h
+    it vendors, compiled where it lies as oracle/_ref/ref_obj_dump and recorded in tests/golden/obj_ingest.json by
+    tests/golden/make_golden_obj.py: mesh order (shape, then ascending material), polygon triangulation (tinyobj's ear
+    clipping: 80 concave / non-planar / degenerate polygons), the un-indexed vertex / normal / texcoord arrays BIT FOR
+    BIT, Kd / Ns / Ke mapping, materialID = mtl index + 1, map_Kd texels (backslash paths too)."""
+    import base64
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "obj_ingest.json")))
+    assert len(G) >= 8
+    for name, case in sorted(G.items()):
+        d0 = tmp_path / name
+        for k, v in case["files"].items():
+            (d0 / k).parent.mkdir(parents=True, exist_ok=True)
+            (d0 / k).write_bytes(base64.b64decode(v))
+        (d0 / "l.obj").write_text("mtllib a.mtl\nv 0 0 1\nv 1 0 1\nv 0 1 1\nvn 0 0 -1\nvt 0 0\nusemtl green\nf 1/1/1 2/1/1 3/1/1\n")
+        (d0 / "s.json").write_text(json.dumps({
+            "spp": 1, "width": 8, "height": 8, "renderers": [9],
+            "cameras": [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 0.66}],
+            "surface_geometry": "a.obj", "area_lights": "l.obj"}))
+        rc, d, err = dump(host, str(d0 / "s.json"))
+        assert rc == 0, (name, err)
+        got, want = d["meshes"][:d["n_surface_meshes"]], case["reference"]["meshes"]
+        assert len(got) == len(want), name
+        for i, (g, w) in enumerate(zip(got, want)):
+            for k in ("triangles", "material_id", "tex", "tex_hash", "vertex_hash", "normal_hash", "texcoord_hash"):
+                assert g[k] == w[k], (name, i, k)
+            for k in ("diffuse", "alpha", "emit"):
+                assert np.array_equal(np.float32(g[k]), np.float32(w[k])), (name, i, k)
+
+
 def _png(path, arr, ctype, depth=8, palette=None, trns=None):
     """Minimal PNG writer (zlib + CRC), filter type chosen per row to exercise all five."""
     import struct, zlib
