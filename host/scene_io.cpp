@@ -464,11 +464,21 @@ bool parse_scene(const std::string& json_file, Scene& scene, std::string* err) {
     scene.width = (int)v->num;
     if (!(v = root.get("height")) || v->kind != JVal::NUM) return bad("scene: 'height' missing");
     scene.height = (int)v->num;
-    if (!(v = root.get("renderers")) || v->kind != JVal::ARR) return bad("No renderers defined.");
-    for (auto& r : v->arr) {
-        if (r.kind != JVal::NUM) return bad("No renderers defined.");
-        scene.renderers.push_back((int)r.num);
+    // As the reference reads it (src/scene.cpp:44-54; pinned on its parseScene, tests/golden/scene_ingest.json): a
+    // missing "renderers" is an empty list, a lone number a list of one; only a non-number element is an error.
+    if ((v = root.get("renderers"))) {
+        if (v->kind == JVal::NUM) {
+            scene.renderers.push_back((int)v->num);
+        } else if (v->kind == JVal::ARR) {
+            for (auto& r : v->arr) {
+                if (r.kind != JVal::NUM) return bad("No renderers defined.");
+                scene.renderers.push_back((int)r.num);
+            }
+        } else if (v->kind != JVal::NUL) {
+            return bad("No renderers defined.");
+        }
     }
+    // (the reference accepts a scene without cameras and dereferences cameras[0] later; refused here with its message)
     if (!(v = root.get("cameras")) || v->kind != JVal::ARR || v->arr.empty()) return bad("No cameras defined.");
     for (auto& c : v->arr) {
         SceneCamera cam;

@@ -1,6 +1,7 @@
-"""Generate tests/golden/obj_ingest.json: OBJ / MTL / texture files and what the REFERENCE's own ingest makes of each --
+"""Generate tests/golden/obj_ingest.json and scene_ingest.json: OBJ / MTL / texture files (and scene JSON files) and what the REFERENCE's own ingest makes of each --
 src/Model.cpp loadOBJ / loadTexture with the tiny_obj_loader.h and stb_image.h it vendors, compiled where they lie as
-oracle/_ref/ref_obj_dump (oracle/Makefile target ref_host).  host/scene_io.cpp load_obj is pinned against these
+oracle/_ref/ref_obj_dump, and src/scene.cpp parseScene / syncLights as oracle/_ref/ref_scene_dump (oracle/Makefile
+target ref_host).  host/scene_io.cpp load_obj is pinned against these
 (tests/test_host.py::test_host_obj_ingest_equals_the_reference_loader): mesh order, triangulation, un-indexed
 vertex / normal / texcoord arrays bit for bit, material mapping, textures.
 
@@ -91,7 +92,52 @@ def reference_dump(files):
         return json.loads(out.stdout.split("@@DUMP@@", 1)[1])
 
 
+REF_SCENE = os.path.join(ROOT, "oracle", "_ref", "ref_scene_dump")
+
+
+def scene_cases():
+    obj = "mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nv 1 1 0\nvn 0 0 1\nvt 0 0\nusemtl red\nf 1/1/1 2/1/1 3/1/1\nusemtl green\nf 2/1/1 4/1/1 3/1/1\n"
+    lobj = "mtllib a.mtl\nv 0 0 1\nv 1 0 1\nv 0 1 1\nv 1 1 1\nvn 0 0 -1\nvt 0 0\nusemtl green\nf 1/1/1 2/1/1 3/1/1\nf 2/1/1 4/1/1 3/1/1\n"
+    mtl = "newmtl red\nKd 1 0 0\nNs 0.5\nnewmtl green\nKd 0 1 0\nNs 0.25\nKe 2 3 4\n"
+    base = {"spp": 3, "width": 48, "height": 32, "renderers": [8, 9, 7],
+            "cameras": [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 0.66},
+                        {"from": [1, 2, 3], "to": [0.5, 0, 0], "up": [0, 0, 1], "cos_fovy": 0.25}],
+            "surface_geometry": "a.obj", "area_lights": "l.obj", "extra": {"k": [1, 2]}}
+
+    def var(**kw):
+        d = dict(base)
+        for k, v in kw.items():
+            if v is None:
+                d.pop(k, None)
+            else:
+                d[k] = v
+        return json.dumps(d)
+
+    one_cam = [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 1}]
+    texts = {"base": var(), "numbers_as_floats": var(spp=2.7, width=64.0, height=3.2e1, renderers=[8.0, 9.9]),
+             "ints_for_floats": var(cameras=one_cam), "no_renderers_key": var(renderers=None), "empty_renderers": var(renderers=[]),
+             "renderers_a_number": var(renderers=8), "empty_cameras": var(cameras=[]), "no_cameras_key": var(cameras=None),
+             "camera_without_up": var(cameras=[{"from": [0, 0, 3], "to": [0, 0, 0], "cos_fovy": 0.5}]),
+             "no_surface": var(surface_geometry=None), "no_lights": var(area_lights=None), "no_spp": var(spp=None),
+             "malformed": '{"spp": 1,', "string_spp": var(spp="3")}
+    return {k: {"a.obj": obj, "l.obj": lobj, "a.mtl": mtl, "s.json": t} for k, t in texts.items()}
+
+
+def reference_scene(files):
+    with tempfile.TemporaryDirectory() as t:
+        for name, data in files.items():
+            open(os.path.join(t, name), "w").write(data)
+        out = subprocess.run([REF_SCENE, "s.json"], capture_output=True, text=True, cwd=t)   # paths as the reference opens them: cwd
+        if "@@DUMP@@" not in out.stdout:
+            return {"crashed": out.returncode}
+        return json.loads(out.stdout.split("@@DUMP@@", 1)[1])
+
+
 def main():
+    if os.path.exists(REF_SCENE):
+        sc = {name: {"files": files, "reference": reference_scene(files)} for name, files in scene_cases().items()}
+        json.dump(sc, open(os.path.join(HERE, "scene_ingest.json"), "w"), indent=0, sort_keys=True)
+        print("scene_ingest.json:", {k: ("ok" if v["reference"].get("ok") else "refused / threw") for k, v in sc.items()})
     if not os.path.exists(REF):
         sys.exit("oracle/_ref/ref_obj_dump is not built: make -C oracle ref_host (needs /root/reference)")
     out = {}

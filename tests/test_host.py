@@ -85,8 +85,8 @@ def test_host_scene_errors(host, tmp_path):
     p.write_text(json.dumps(bad))
     rc, _, err = dump(host, str(p))
     assert rc != 0 and "No cameras defined." in err
-    # no renderers (:44-54)
-    bad = {k: v for k, v in doc.items() if k != "renderers"}
+    # renderers that are not numbers (:44-54); a MISSING list is an empty one, as in the reference (scene_ingest.json)
+    bad = dict(doc, renderers=["ratio"])
     p = tmp_path / "norend.json"
     p.write_text(json.dumps(bad))
     rc, _, err = dump(host, str(p))
@@ -157,6 +157,48 @@ def test_host_obj_ingest_equals_the_reference_loader(host, tmp_path):
                 assert g[k] == w[k], (name, i, k)
             for k in ("diffuse", "alpha", "emit"):
                 assert np.array_equal(np.float32(g[k]), np.float32(w[k])), (name, i, k)
+
+
+def test_host_scene_ingest_equals_the_reference_parser(host, tmp_path):
+    """host/scene_io.cpp parse_scene against the reference's OWN parseScene + Scene::syncLights (src/scene.cpp with the
+    json.h it vendors, compiled where it lies as oracle/_ref/ref_scene_dump; tests/golden/scene_ingest.json): spp / size /
+    renderers (floats truncate, a missing list is empty, a lone number is a list of one), every camera, the light
+    meshes appended with is_light and materialID 0.  Where the reference refuses or throws, the host refuses; the one
+    deliberate difference: a scene WITHOUT cameras, which the reference accepts and then dereferences cameras[0]."""
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "scene_ingest.json")))
+    assert len(G) >= 14
+    seen_ok = 0
+    for name, case in sorted(G.items()):
+        d0 = tmp_path / name
+        d0.mkdir()
+        for k, v in case["files"].items():
+            (d0 / k).write_text(v)
+        o = subprocess.run([host, "s.json", "--dump-scene"], capture_output=True, text=True, cwd=str(d0))
+        ref = case["reference"]
+        if not ref.get("ok"):
+            assert o.returncode != 0, name
+            continue
+        if not ref["cameras"]:
+            assert o.returncode != 0 and "No cameras defined." in o.stderr, name
+            continue
+        assert o.returncode == 0, (name, o.stderr)
+        d = json.loads(o.stdout)
+        seen_ok += 1
+        assert (d["spp"], d["width"], d["height"], d["renderers"]) == (ref["spp"], ref["width"], ref["height"], ref["renderers"]), name
+        assert d["n_cameras"] == len(ref["cameras"]) and len(d["meshes"]) == len(ref["meshes"]), name
+        for g, w in zip(d["meshes"], ref["meshes"]):
+            for k in ("triangles", "material_id", "is_light", "vertex_hash"):
+                assert g[k] == w[k], (name, k)
+            assert np.array_equal(np.float32(g["emit"]), np.float32(w["emit"])), name
+        for i, cam in enumerate(ref["cameras"]):      # the camera vectors the host derives from camera i of the reference's parse
+            o = subprocess.run([host, "s.json", "--dump-scene", "--camera", str(i)], capture_output=True, text=True, cwd=str(d0))
+            assert o.returncode == 0, (name, o.stderr)
+            want = scenes.camera_from_lookat(np.float32(cam["from"]), np.float32(cam["to"]), np.float32(cam["up"]),
+                                             np.float32(cam["cos_fovy"]), width=ref["width"], height=ref["height"])
+            got = json.loads(o.stdout)["camera"]
+            for k in ("pos", "d00", "du", "dv"):   # two fp32 restatements of viewer.hpp:635-641: equal to an ulp
+                assert np.allclose(np.float32(got[k]), want[k], rtol=3e-7, atol=1e-7), (name, i, k)
+    assert seen_ok >= 6
 
 
 def _png(path, arr, ctype, depth=8, palette=None, trns=None):
