@@ -48,8 +48,17 @@ def upsample_lut(lut, n):
 
 
 def _norm(v):
+    """owl's normalize: v * (1 / sqrt(dot(v, v))), the dot product added left to right in fp32 (np.dot goes through BLAS,
+    whose summation order / FMA use is not defined: one ulp off the C++ host's camera for some inputs)."""
     v = np.asarray(v, F)
-    return (v * (F(1) / np.sqrt(np.dot(v, v), dtype=F))).astype(F)
+    d = F(F(F(v[0] * v[0]) + F(v[1] * v[1])) + F(v[2] * v[2]))
+    return (v * (F(1) / np.sqrt(d, dtype=F))).astype(F)
+
+
+def _cross(a, b):
+    """cross(a, b) in fp32, each component one multiply-subtract pair as the C++ host writes it."""
+    a, b = np.asarray(a, F), np.asarray(b, F)
+    return np.array([F(F(a[1] * b[2]) - F(a[2] * b[1])), F(F(a[2] * b[0]) - F(a[0] * b[2])), F(F(a[0] * b[1]) - F(a[1] * b[0]))], F)
 
 
 def camera_from_lookat(frm, at, up, cos_fovy, width, height):
@@ -57,8 +66,8 @@ def camera_from_lookat(frm, at, up, cos_fovy, width, height):
     frm, at, up = np.asarray(frm, F), np.asarray(at, F), np.asarray(up, F)
     d00 = _norm(at - frm)
     aspect = F(width / float(height))
-    ddu = (F(cos_fovy) * aspect * _norm(np.cross(d00, up).astype(F))).astype(F)
-    ddv = (F(cos_fovy) * _norm(np.cross(ddu, d00).astype(F))).astype(F)
+    ddu = (F(F(cos_fovy) * aspect) * _norm(_cross(d00, up))).astype(F)
+    ddv = (F(cos_fovy) * _norm(_cross(ddu, d00))).astype(F)
     d00 = (d00 - F(0.5) * ddu).astype(F)
     d00 = (d00 - F(0.5) * ddv).astype(F)
     return {"pos": frm.copy(), "d00": d00, "du": ddu, "dv": ddv,

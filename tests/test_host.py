@@ -196,8 +196,8 @@ def test_host_scene_ingest_equals_the_reference_parser(host, tmp_path):
             want = scenes.camera_from_lookat(np.float32(cam["from"]), np.float32(cam["to"]), np.float32(cam["up"]),
                                              np.float32(cam["cos_fovy"]), width=ref["width"], height=ref["height"])
             got = json.loads(o.stdout)["camera"]
-            for k in ("pos", "d00", "du", "dv"):   # two fp32 restatements of viewer.hpp:635-641: equal to an ulp
-                assert np.allclose(np.float32(got[k]), want[k], rtol=3e-7, atol=1e-7), (name, i, k)
+            for k in ("pos", "d00", "du", "dv"):   # the two fp32 restatements of viewer.hpp:635-641 agree bit for bit
+                assert np.array_equal(np.float32(got[k]), want[k]), (name, i, k)
     assert seen_ok >= 6
 
 
