@@ -20,6 +20,30 @@ inline bool operator<(const index_t& a, const index_t& b) {
 #include REF_MODEL_CPP
 #include REF_SCENE_CPP
 #include <cstdio>
+#include "owl_math.h"
+
+// The two pieces of host arithmetic in include/viewer.hpp (which itself needs OpenGL / GLFW / OWL and cannot be
+// compiled): the Makefile cuts the lines out of the file where it lies into temporary .inc files -- the light-list loop
+// :236-265 and the camera vectors :635-641 -- and they are compiled here as the bodies of two functions.
+using owl::common::vec2i;
+using owl::common::vec3f;
+using namespace owl::common;
+struct TriLight { vec3f v1, v2, v3, cg, normal, emit; float area; };   // cuda_include/common.cuh:64-72
+struct MeshLight { float flux; int triIdx; int triCount; };            // :74-78
+struct ViewerPart {
+    std::vector<TriLight> triLightList;
+    std::vector<MeshLight> meshLightList;
+    vec2i fbSize;
+    void lights(Scene& scene) {
+        Model* triLights = scene.triLights;
+#include REF_LIGHTS_INC
+    }
+    void camera(const vec3f lookFrom, const vec3f lookAt, const vec3f lookUp, const float cosFovy, float out[12]) {
+#include REF_CAMERA_INC
+        const vec3f v[4] = {camera_pos, camera_d00, camera_ddu, camera_ddv};
+        for (int i = 0; i < 4; i++) { out[3 * i] = v[i].x; out[3 * i + 1] = v[i].y; out[3 * i + 2] = v[i].z; }
+    }
+};
 
 static unsigned long long fnv1a(const void* p, size_t n, unsigned long long h = 1469598103934665603ull) {
     const unsigned char* b = (const unsigned char*)p;
@@ -50,7 +74,21 @@ int main(int argc, char** argv) {
         printf("%s{\"from\": [%.9g, %.9g, %.9g], \"to\": [%.9g, %.9g, %.9g], \"up\": [%.9g, %.9g, %.9g], \"cos_fovy\": %.9g}", i ? ", " : "",
                c.from.x, c.from.y, c.from.z, c.at.x, c.at.y, c.at.z, c.up.x, c.up.y, c.up.z, c.cosFovy);
     }
-    printf("], \"meshes\": [");
+    printf("], \"camera_vectors\": [");
+    ViewerPart vp;
+    vp.fbSize = vec2i(sc.imgWidth, sc.imgHeight);
+    for (size_t i = 0; i < sc.cameras.size(); i++) {
+        float o[12];
+        vp.camera(sc.cameras[i].from, sc.cameras[i].at, sc.cameras[i].up, sc.cameras[i].cosFovy, o);
+        printf("%s[", i ? ", " : "");
+        for (int k = 0; k < 12; k++) printf("%s%.9g", k ? ", " : "", o[k]);
+        printf("]");
+    }
+    vp.lights(sc);
+    static_assert(sizeof(TriLight) == 76, "TriLight layout");
+    printf("], \"n_tri_lights\": %zu, \"tri_lights_hash\": \"%016llx\"", vp.triLightList.size(),
+           fnv1a(vp.triLightList.data(), vp.triLightList.size() * sizeof(TriLight)));
+    printf(", \"meshes\": [");
     for (size_t i = 0; i < sc.model->meshes.size(); i++) {
         const osc::TriangleMesh& t = *sc.model->meshes[i];
         printf("%s{\"triangles\": %zu, \"material_id\": %u, \"is_light\": %s, \"emit\": [%.9g, %.9g, %.9g], \"vertex_hash\": \"%016llx\"}",

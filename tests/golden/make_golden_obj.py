@@ -97,7 +97,10 @@ REF_SCENE = os.path.join(ROOT, "oracle", "_ref", "ref_scene_dump")
 
 def scene_cases():
     obj = "mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nv 1 1 0\nvn 0 0 1\nvt 0 0\nusemtl red\nf 1/1/1 2/1/1 3/1/1\nusemtl green\nf 2/1/1 4/1/1 3/1/1\n"
-    lobj = "mtllib a.mtl\nv 0 0 1\nv 1 0 1\nv 0 1 1\nv 1 1 1\nvn 0 0 -1\nvt 0 0\nusemtl green\nf 1/1/1 2/1/1 3/1/1\nf 2/1/1 4/1/1 3/1/1\n"
+    rng = np.random.default_rng(5)   # two light meshes, scalene triangles, a different normal at every corner
+    lobj = ("mtllib a.mtl\n" + "".join("v %.6f %.6f %.6f\n" % tuple(v) for v in rng.uniform(-2, 2, (7, 3)) + [0, 0, 4])
+            + "".join("vn %.6f %.6f %.6f\n" % tuple(v) for v in rng.normal(size=(6, 3)) + [0, 0, -2]) + "vt 0 0\n"
+            + "usemtl green\nf 1/1/1 2/1/2 3/1/3\nf 2/1/4 4/1/5 3/1/6\nusemtl red\nf 5/1/1 6/1/3 7/1/5\n")
     mtl = "newmtl red\nKd 1 0 0\nNs 0.5\nnewmtl green\nKd 0 1 0\nNs 0.25\nKe 2 3 4\n"
     base = {"spp": 3, "width": 48, "height": 32, "renderers": [8, 9, 7],
             "cameras": [{"from": [0, 0, 3], "to": [0, 0, 0], "up": [0, 1, 0], "cos_fovy": 0.66},

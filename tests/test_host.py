@@ -163,7 +163,9 @@ def test_host_scene_ingest_equals_the_reference_parser(host, tmp_path):
     """host/scene_io.cpp parse_scene against the reference's OWN parseScene + Scene::syncLights (src/scene.cpp with the
     json.h it vendors, compiled where it lies as oracle/_ref/ref_scene_dump; tests/golden/scene_ingest.json): spp / size /
     renderers (floats truncate, a missing list is empty, a lone number is a list of one), every camera, the light
-    meshes appended with is_light and materialID 0.  Where the reference refuses or throws, the host refuses; the one
+    meshes appended with is_light and materialID 0 -- and against the two pieces of host arithmetic of include/viewer.hpp
+    (which cannot be compiled whole: OpenGL / OWL), cut out of the file where it lies: the TriLight list and the camera
+    vectors, bit for bit.  Where the reference refuses or throws, the host refuses; the one
     deliberate difference: a scene WITHOUT cameras, which the reference accepts and then dereferences cameras[0]."""
     G = json.load(open(os.path.join(ROOT, "tests", "golden", "scene_ingest.json")))
     assert len(G) >= 14
@@ -190,13 +192,18 @@ def test_host_scene_ingest_equals_the_reference_parser(host, tmp_path):
             for k in ("triangles", "material_id", "is_light", "vertex_hash"):
                 assert g[k] == w[k], (name, k)
             assert np.array_equal(np.float32(g["emit"]), np.float32(w["emit"])), name
-        for i, cam in enumerate(ref["cameras"]):      # the camera vectors the host derives from camera i of the reference's parse
+        # the TriLight list (include/viewer.hpp:236-265, cut out of the file where it lies and compiled in the harness): 76-byte
+        # records v1 v2 v3 cg normal emit area, bit for bit
+        assert (d["n_tri_lights"], d["tri_lights_hash"]) == (ref["n_tri_lights"], ref["tri_lights_hash"]), name
+        for i, cam in enumerate(ref["cameras"]):      # the camera vectors (viewer.hpp:635-641, compiled the same way), bit for bit
             o = subprocess.run([host, "s.json", "--dump-scene", "--camera", str(i)], capture_output=True, text=True, cwd=str(d0))
             assert o.returncode == 0, (name, o.stderr)
             want = scenes.camera_from_lookat(np.float32(cam["from"]), np.float32(cam["to"]), np.float32(cam["up"]),
                                              np.float32(cam["cos_fovy"]), width=ref["width"], height=ref["height"])
             got = json.loads(o.stdout)["camera"]
-            for k in ("pos", "d00", "du", "dv"):   # the two fp32 restatements of viewer.hpp:635-641 agree bit for bit
+            flat = np.float32(got["pos"] + got["d00"] + got["du"] + got["dv"])
+            assert np.array_equal(flat, np.float32(ref["camera_vectors"][i])), (name, i)
+            for k in ("pos", "d00", "du", "dv"):   # ... and so does the Python restatement the GPU tests and bench.py use
                 assert np.array_equal(np.float32(got[k]), want[k]), (name, i, k)
     assert seen_ok >= 6
 
